@@ -1,0 +1,116 @@
+// Frame read-back conversions and the texture-fetch roofline microbenchmark.
+#include "vrb_internal.cuh"
+#include <algorithm>
+#include <vector>
+
+namespace vrb {
+
+// RenderFrameToScreen::Draw + glReadPixels (renderoutputframe.cpp:214-258; blend state
+// renderingmanager.cpp:103-110): out = src.rgb*src.a + white*(1-src.a) into an RGB8 unorm buffer.
+__global__ void __launch_bounds__(256) rgb8_over_white_kernel(const uint2* __restrict__ frame, int64_t n, uint8_t* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint2 t = frame[i];
+  const float2 rg = __half22float2(*reinterpret_cast<const __half2*>(&t.x));
+  const float2 ba = __half22float2(*reinterpret_cast<const __half2*>(&t.y));
+  const float a = ba.y, ia = __fsub_rn(1.0f, a);
+  const float c[3] = {rg.x, rg.y, ba.x};
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    float v = __fadd_rn(__fmul_rn(c[k], a), __fmul_rn(1.0f, ia));
+    v = fminf(fmaxf(v, 0.0f), 1.0f);
+    out[3 * i + k] = (uint8_t)floorf(__fadd_rn(__fmul_rn(v, 255.0f), 0.5f));
+  }
+}
+
+__global__ void __launch_bounds__(256) rgba32f_kernel(const uint2* __restrict__ frame, int64_t n, float4* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint2 t = frame[i];
+  const float2 rg = __half22float2(*reinterpret_cast<const __half2*>(&t.x));
+  const float2 ba = __half22float2(*reinterpret_cast<const __half2*>(&t.y));
+  out[i] = make_float4(rg.x, rg.y, ba.x, ba.y);
+}
+
+int frame_to_rgb8_over_white(cudaStream_t s, const __half* frame, int64_t n, uint8_t* dev_out) {
+  rgb8_over_white_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>((const uint2*)frame, n, dev_out);
+  VRB_CUDA(cudaGetLastError());
+  return VRB_OK;
+}
+int frame_to_rgba32f(cudaStream_t s, const __half* frame, int64_t n, float* dev_out) {
+  rgba32f_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>((const uint2*)frame, n, (float4*)dev_out);
+  VRB_CUDA(cudaGetLastError());
+  return VRB_OK;
+}
+
+// P_tex: trilinear R16F tex3D fetches per second with a working set that stays in L1TEX.  Each warp
+// marches 8x4 neighbouring rays through a 32^3 half volume at a 0.5-texel step — the access pattern
+// of the renderer with every miss removed.  4 independent fetch chains per thread hide latency.
+__global__ void __launch_bounds__(256) tex_peak_kernel(cudaTextureObject_t tex, int iters, float* sink) {
+  const int lane = threadIdx.x & 31, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const float x0 = ((lane & 7) + 0.5f) / 32.0f + (warp & 3) * 0.2f, y0 = ((lane >> 3) + 0.5f) / 32.0f + ((warp >> 2) & 3) * 0.2f;
+  float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+  float z = 0.0f;
+  const float dz = 0.5f / 32.0f;
+  for (int i = 0; i < iters; i++) {
+    acc0 += tex3D<float>(tex, x0, y0, z);
+    acc1 += tex3D<float>(tex, x0 + 0.011f, y0 + 0.007f, z + dz);
+    acc2 += tex3D<float>(tex, x0 + 0.022f, y0 + 0.014f, z + 2 * dz);
+    acc3 += tex3D<float>(tex, x0 + 0.033f, y0 + 0.021f, z + 3 * dz);
+    z += 4 * dz;
+    if (z > 1.0f) z -= 1.0f;
+  }
+  const float r = acc0 + acc1 + acc2 + acc3;
+  if (r == 123456.789f) sink[0] = r;
+}
+
+}  // namespace vrb
+
+using namespace vrb;
+
+extern "C" int vrb_bench_tex_peak(vrb_ctx* ctx, double* fetches_per_s) {
+  VRB_REQUIRE(ctx && fetches_per_s, VRB_ERR_INVALID, "vrb_bench_tex_peak: null argument");
+  VRB_CUDA(cudaSetDevice(ctx->device));
+  const int N = 32;
+  std::vector<__half> h((size_t)N * N * N);
+  for (size_t i = 0; i < h.size(); i++) h[i] = __float2half_rn((float)((i * 2654435761u) & 1023) / 1023.0f);
+  cudaArray_t arr = nullptr; cudaTextureObject_t tex = 0; float* sink = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  cudaChannelFormatDesc desc = cudaCreateChannelDescHalf();
+  int rc = VRB_OK;
+  auto body = [&]() -> int {
+    VRB_CUDA(cudaMalloc3DArray(&arr, &desc, make_cudaExtent(N, N, N)));
+    cudaMemcpy3DParms cp{};
+    cp.srcPtr = make_cudaPitchedPtr(h.data(), N * sizeof(__half), N, N);
+    cp.dstArray = arr; cp.extent = make_cudaExtent(N, N, N); cp.kind = cudaMemcpyHostToDevice;
+    VRB_CUDA(cudaMemcpy3D(&cp));
+    cudaResourceDesc rd{}; rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
+    cudaTextureDesc td{};
+    td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+    td.filterMode = cudaFilterModeLinear; td.readMode = cudaReadModeElementType; td.normalizedCoords = 1;
+    VRB_CUDA(cudaCreateTextureObject(&tex, &rd, &td, nullptr));
+    VRB_CUDA(cudaMalloc(&sink, sizeof(float)));
+    VRB_CUDA(cudaEventCreate(&e0)); VRB_CUDA(cudaEventCreate(&e1));
+    const int iters = 4096, threads = 256, blocks = ctx->sm_count * 8;
+    double best = 0.0;
+    for (int rep = 0; rep < 5; rep++) {
+      VRB_CUDA(cudaEventRecord(e0, ctx->stream));
+      tex_peak_kernel<<<blocks, threads, 0, ctx->stream>>>(tex, iters, sink);
+      VRB_CUDA(cudaEventRecord(e1, ctx->stream));
+      VRB_CUDA(cudaStreamSynchronize(ctx->stream));
+      VRB_CUDA(cudaGetLastError());
+      float ms = 0.f; VRB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+      const double f = (double)blocks * threads * iters * 4.0 / (ms * 1e-3);
+      if (rep > 0) best = std::max(best, f);
+    }
+    *fetches_per_s = best;
+    return VRB_OK;
+  };
+  rc = body();
+  if (tex) cudaDestroyTextureObject(tex);
+  if (arr) cudaFreeArray(arr);
+  if (sink) cudaFree(sink);
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
+  return rc;
+}

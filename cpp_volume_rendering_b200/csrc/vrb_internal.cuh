@@ -1,0 +1,108 @@
+// Internal declarations of libvrb200.so (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdarg>
+#include <string>
+#include "../../include/vrb200.h"
+
+namespace vrb {
+
+void set_error(const char* fmt, ...);
+
+#define VRB_CUDA(call)                                                                          \
+  do {                                                                                          \
+    cudaError_t e__ = (call);                                                                   \
+    if (e__ != cudaSuccess) {                                                                   \
+      vrb::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+      return VRB_ERR_CUDA;                                                                      \
+    }                                                                                           \
+  } while (0)
+
+#define VRB_REQUIRE(cond, status, ...)   \
+  do {                                   \
+    if (!(cond)) {                       \
+      vrb::set_error(__VA_ARGS__);       \
+      return (status);                   \
+    }                                    \
+  } while (0)
+
+// Volume resident in HBM: the R16F texture the ray casters sample (GL_LINEAR, CLAMP_TO_EDGE,
+// normalised coordinates) plus the raw voxels for the precompute stages.
+struct Volume {
+  int64_t w = 0, h = 0, d = 0;
+  float sx = 1, sy = 1, sz = 1;
+  int dtype = VRB_U8;
+  void* raw = nullptr;                  // device copy of the voxel array (x fastest)
+  cudaArray_t array = nullptr;          // half, 1 channel
+  cudaTextureObject_t tex = 0;          // linear, clamp, normalised
+  cudaSurfaceObject_t surf = 0;
+  uint64_t generation = 0;
+  size_t voxel_bytes() const { return dtype == VRB_U8 ? 1 : (dtype == VRB_U16 ? 2 : 4); }
+};
+
+// Transfer function: RGBt (extinction) and RGBA (opacity) RGBA16F 1D textures, linear + clamp.
+struct TransferFunction {
+  int n = 0;
+  int extinction_type = 0;
+  cudaArray_t arr_rgbt = nullptr, arr_rgba = nullptr;
+  cudaTextureObject_t tex_rgbt = 0, tex_rgba = 0;
+  __half* lin_rgbt = nullptr;           // linear device copies (n*4 halfs) for smem tables / classification
+  __half* lin_rgba = nullptr;
+  double* table = nullptr;              // device copy of the double table (n*4), for GetExtN-style precompute
+  uint64_t generation = 0;
+};
+
+}  // namespace vrb
+
+struct vrb_ctx {
+  int device = 0;
+  int sm_count = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  vrb::Volume vol;
+  vrb::TransferFunction tf;
+};
+
+namespace vrb {
+
+// Per-kind renderer implementation behind the C entry points.
+struct RendererImpl {
+  vrb_ctx* ctx;
+  int kind;
+  int width = 0, height = 0;
+  bool built = false;
+  __half* frame = nullptr;              // RGBA16F, width*height*4, row 0 = bottom
+  vrb_camera cam{};
+  vrb_light light{};
+  bool have_cam = false;
+  int rank = 0, n_ranks = 1, part_tile = 32;
+  unsigned long long* d_samples = nullptr;
+  uint64_t last_samples = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool timed = false;
+
+  explicit RendererImpl(vrb_ctx* c, int k) : ctx(c), kind(k) {}
+  virtual ~RendererImpl() {}
+  virtual int init(int w, int h) = 0;           // precompute + defaults
+  virtual int set_params(const void* pod, size_t size) = 0;
+  virtual int get_params(void* pod, size_t size) = 0;
+  virtual int redraw(int mode) = 0;             // launches on ctx->stream
+  virtual void clean() {}
+  int alloc_frame(int w, int h);
+  void free_frame();
+};
+
+RendererImpl* make_rc1pass(vrb_ctx* ctx);
+
+// k_frame.cu
+int frame_to_rgb8_over_white(cudaStream_t s, const __half* frame, int64_t n_pixels, uint8_t* dev_out);
+int frame_to_rgba32f(cudaStream_t s, const __half* frame, int64_t n_pixels, float* dev_out);
+
+}  // namespace vrb
+
+struct vrb_renderer {
+  vrb::RendererImpl* impl = nullptr;
+};

@@ -1,0 +1,55 @@
+// Per-ray set-up shared by every ray-casting kernel.  Written with round-to-nearest intrinsics
+// (__fmul_rn/__fadd_rn/__fdiv_rn/__fsqrt_rn are never fused or approximated by nvcc) so that ray
+// direction, entry/exit distances and therefore the sample lattice are bit-identical to the float32
+// evaluation of the reference shader statements (and to oracle/orc_ray.h).
+#pragma once
+#include <cuda_runtime.h>
+
+namespace vrb {
+
+struct f3 { float x, y, z; };
+__device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+// GLSL min/max semantics: min(x,y) = y < x ? y : x ; max(x,y) = x < y ? y : x
+__device__ __forceinline__ float gmin(float x, float y) { return (y < x) ? y : x; }
+__device__ __forceinline__ float gmax(float x, float y) { return (x < y) ? y : x; }
+
+__device__ __forceinline__ float dot_rn(f3 a, f3 b) {
+  return __fadd_rn(__fadd_rn(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y)), __fmul_rn(a.z, b.z));
+}
+__device__ __forceinline__ f3 normalize_rn(f3 a) {
+  float l = __fsqrt_rn(dot_rn(a, a));
+  return mk3(__fdiv_rn(a.x, l), __fdiv_rn(a.y, l), __fdiv_rn(a.z, l));
+}
+
+// ray_marching_1p.comp:93-99 — pixel centre -> NDC -> camera direction (row vector * mat3(LookAt)).
+__device__ __forceinline__ f3 camera_ray_dir(int px, int py, int w, int h, float tan_fovy, float aspect, const float* m3) {
+  float fx = __fadd_rn((float)px, 0.5f), fy = __fadd_rn((float)py, 0.5f);
+  float vx = __fadd_rn(__fmul_rn(__fdiv_rn(fx, (float)w), 2.0f), -1.0f);
+  float vy = __fadd_rn(__fmul_rn(__fdiv_rn(fy, (float)h), 2.0f), -1.0f);
+  f3 v = mk3(__fmul_rn(__fmul_rn(vx, tan_fovy), aspect), __fmul_rn(vy, tan_fovy), -1.0f);
+  f3 d = mk3(dot_rn(v, mk3(m3[0], m3[1], m3[2])), dot_rn(v, mk3(m3[3], m3[4], m3[5])), dot_rn(v, mk3(m3[6], m3[7], m3[8])));
+  return normalize_rn(d);
+}
+
+// _common_shaders/ray_bbox_intersection.comp:18-52 with explicit box [bmin,bmax]; dir is normalised
+// again exactly as RayAABBIntersection does (:40).  Returns hit; tnear is clamped to >= 0 (:46).
+__device__ __forceinline__ bool ray_aabb(f3 eye, f3 dir_in, f3 bmin, f3 bmax, f3& dir, float& tnear, float& tfar) {
+  dir = normalize_rn(dir_in);
+  float ix = __fdiv_rn(1.0f, dir.x), iy = __fdiv_rn(1.0f, dir.y), iz = __fdiv_rn(1.0f, dir.z);
+  float ax = __fmul_rn(ix, __fsub_rn(bmin.x, eye.x)), bx = __fmul_rn(ix, __fsub_rn(bmax.x, eye.x));
+  float ay = __fmul_rn(iy, __fsub_rn(bmin.y, eye.y)), by = __fmul_rn(iy, __fsub_rn(bmax.y, eye.y));
+  float az = __fmul_rn(iz, __fsub_rn(bmin.z, eye.z)), bz = __fmul_rn(iz, __fsub_rn(bmax.z, eye.z));
+  float tn = gmax(gmax(gmin(ax, bx), gmin(ay, by)), gmin(az, bz));
+  float tf = gmin(gmin(gmax(ax, bx), gmax(ay, by)), gmax(az, bz));
+  bool hit = tf > tn;
+  tnear = gmax(tn, 0.0f);
+  tfar = tf;
+  return hit;
+}
+
+__device__ __forceinline__ unsigned pack_half2(float a, float b) {
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<unsigned*>(&h);
+}
+
+}  // namespace vrb

@@ -1,0 +1,184 @@
+// C entry points of the renderer half of the ABI: lifecycle calls that mirror BaseVolumeRenderer
+// (cppvolrend/volrenderbase.h:25-97) and dispatch to the per-kind implementation.
+#include "vrb_internal.cuh"
+#include <vector>
+
+namespace vrb {
+
+int RendererImpl::alloc_frame(int w, int h) {
+  VRB_REQUIRE(w > 0 && h > 0 && w <= 32768 && h <= 32768, VRB_ERR_INVALID, "bad frame size %dx%d", w, h);
+  if (frame && w == width && h == height) return VRB_OK;
+  free_frame();
+  // RenderFrameToScreen::UpdateScreenResolution (renderoutputframe.cpp:64-87): RGBA16F W x H
+  VRB_CUDA(cudaMalloc(&frame, (size_t)w * h * 4 * sizeof(__half)));
+  VRB_CUDA(cudaMemsetAsync(frame, 0, (size_t)w * h * 4 * sizeof(__half), ctx->stream));
+  width = w; height = h;
+  return VRB_OK;
+}
+
+void RendererImpl::free_frame() {
+  if (frame) cudaFree(frame);
+  frame = nullptr; width = height = 0;
+}
+
+}  // namespace vrb
+
+using namespace vrb;
+
+extern "C" {
+
+int vrb_renderer_create(vrb_ctx* ctx, int kind, vrb_renderer** out) {
+  VRB_REQUIRE(ctx && out, VRB_ERR_INVALID, "vrb_renderer_create: null argument");
+  *out = nullptr;
+  VRB_CUDA(cudaSetDevice(ctx->device));
+  RendererImpl* impl = nullptr;
+  switch (kind) {
+    case VRB_RC1PASS: impl = make_rc1pass(ctx); break;
+    default:
+      set_error("vrb_renderer_create: renderer kind %d is not built yet", kind);
+      return VRB_ERR_UNSUPPORTED;
+  }
+  cudaError_t e = cudaMalloc(&impl->d_samples, sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaEventCreate(&impl->ev0);
+  if (e == cudaSuccess) e = cudaEventCreate(&impl->ev1);
+  if (e != cudaSuccess) { set_error("vrb_renderer_create: %s", cudaGetErrorString(e)); delete impl; return VRB_ERR_CUDA; }
+  vrb_renderer* r = new vrb_renderer();
+  r->impl = impl;
+  *out = r;
+  return VRB_OK;
+}
+
+int vrb_renderer_destroy(vrb_renderer* r) {
+  if (!r) return VRB_OK;
+  RendererImpl* p = r->impl;
+  cudaSetDevice(p->ctx->device);
+  cudaStreamSynchronize(p->ctx->stream);
+  p->clean();
+  p->free_frame();
+  if (p->d_samples) cudaFree(p->d_samples);
+  if (p->ev0) cudaEventDestroy(p->ev0);
+  if (p->ev1) cudaEventDestroy(p->ev1);
+  delete p;
+  delete r;
+  return VRB_OK;
+}
+
+// Init must be re-entrant: `if (IsBuilt()) Clean();` (rc1prenderer.cpp:52)
+int vrb_renderer_init(vrb_renderer* r, int width, int height) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_init: null renderer");
+  RendererImpl* p = r->impl;
+  VRB_CUDA(cudaSetDevice(p->ctx->device));
+  if (p->built) { p->clean(); p->built = false; }
+  return p->init(width, height);
+}
+
+int vrb_renderer_reshape(vrb_renderer* r, int width, int height) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_reshape: null renderer");
+  RendererImpl* p = r->impl;
+  VRB_REQUIRE(p->built, VRB_ERR_INVALID, "vrb_renderer_reshape before Init");
+  VRB_CUDA(cudaStreamSynchronize(p->ctx->stream));
+  return p->alloc_frame(width, height);
+}
+
+int vrb_renderer_set_params(vrb_renderer* r, const void* pod, size_t size) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_set_params: null renderer");
+  return r->impl->set_params(pod, size);
+}
+
+int vrb_renderer_get_params(vrb_renderer* r, void* pod, size_t size) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_get_params: null renderer");
+  return r->impl->get_params(pod, size);
+}
+
+int vrb_renderer_update(vrb_renderer* r, const vrb_camera* cam, const vrb_light* light) {
+  VRB_REQUIRE(r && cam, VRB_ERR_INVALID, "vrb_renderer_update: null argument");
+  RendererImpl* p = r->impl;
+  VRB_REQUIRE(p->built, VRB_ERR_INVALID, "vrb_renderer_update before Init");
+  p->cam = *cam;
+  if (light) p->light = *light;
+  p->have_cam = true;
+  return VRB_OK;
+}
+
+int vrb_renderer_redraw(vrb_renderer* r, int mode) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_redraw: null renderer");
+  RendererImpl* p = r->impl;
+  cudaStream_t s = p->ctx->stream;
+  VRB_CUDA(cudaEventRecord(p->ev0, s));
+  int rc = p->redraw(mode);
+  if (rc != VRB_OK) return rc;
+  VRB_CUDA(cudaEventRecord(p->ev1, s));
+  p->timed = true;
+  return VRB_OK;
+}
+
+int vrb_renderer_frame(vrb_renderer* r, void** dev_rgba16f, int* width, int* height) {
+  VRB_REQUIRE(r && dev_rgba16f, VRB_ERR_INVALID, "vrb_renderer_frame: null argument");
+  RendererImpl* p = r->impl;
+  VRB_REQUIRE(p->frame, VRB_ERR_INVALID, "vrb_renderer_frame before Init");
+  *dev_rgba16f = p->frame;
+  if (width) *width = p->width;
+  if (height) *height = p->height;
+  return VRB_OK;
+}
+
+int vrb_renderer_read_frame(vrb_renderer* r, void* host, int format) {
+  VRB_REQUIRE(r && host, VRB_ERR_INVALID, "vrb_renderer_read_frame: null argument");
+  RendererImpl* p = r->impl;
+  VRB_REQUIRE(p->frame, VRB_ERR_INVALID, "vrb_renderer_read_frame before Init");
+  cudaStream_t s = p->ctx->stream;
+  const int64_t n = (int64_t)p->width * p->height;
+  if (format == VRB_FRAME_RGBA16F) {
+    VRB_CUDA(cudaMemcpyAsync(host, p->frame, (size_t)n * 8, cudaMemcpyDeviceToHost, s));
+    VRB_CUDA(cudaStreamSynchronize(s));
+    return VRB_OK;
+  }
+  VRB_REQUIRE(format == VRB_FRAME_RGB8_OVER_WHITE || format == VRB_FRAME_RGBA32F, VRB_ERR_INVALID,
+              "vrb_renderer_read_frame: bad format %d", format);
+  const size_t bytes = format == VRB_FRAME_RGB8_OVER_WHITE ? (size_t)n * 3 : (size_t)n * 16;
+  void* tmp = nullptr;
+  VRB_CUDA(cudaMalloc(&tmp, bytes));
+  int rc = format == VRB_FRAME_RGB8_OVER_WHITE ? frame_to_rgb8_over_white(s, p->frame, n, (uint8_t*)tmp)
+                                               : frame_to_rgba32f(s, p->frame, n, (float*)tmp);
+  cudaError_t e = cudaSuccess;
+  if (rc == VRB_OK) {
+    e = cudaMemcpyAsync(host, tmp, bytes, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  }
+  cudaFree(tmp);
+  if (rc != VRB_OK) return rc;
+  VRB_CUDA(e);
+  return VRB_OK;
+}
+
+int vrb_renderer_counters(vrb_renderer* r, uint64_t* samples, double* ms) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_counters: null renderer");
+  RendererImpl* p = r->impl;
+  cudaStream_t s = p->ctx->stream;
+  VRB_CUDA(cudaStreamSynchronize(s));
+  if (samples) {
+    unsigned long long v = 0;
+    VRB_CUDA(cudaMemcpy(&v, p->d_samples, sizeof(v), cudaMemcpyDeviceToHost));
+    *samples = (uint64_t)v;
+  }
+  if (ms) {
+    float t = 0.f;
+    if (p->timed) VRB_CUDA(cudaEventElapsedTime(&t, p->ev0, p->ev1));
+    *ms = (double)t;
+  }
+  return VRB_OK;
+}
+
+int vrb_renderer_set_partition(vrb_renderer* r, int rank, int n_ranks, int tile) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_set_partition: null renderer");
+  VRB_REQUIRE(n_ranks >= 1 && rank >= 0 && rank < n_ranks, VRB_ERR_INVALID, "bad partition rank %d of %d", rank, n_ranks);
+  VRB_REQUIRE(tile == 16 || tile == 32 || tile == 64 || tile == 128, VRB_ERR_INVALID, "partition tile must be 16, 32, 64 or 128");
+  RendererImpl* p = r->impl;
+  p->rank = rank; p->n_ranks = n_ranks; p->part_tile = tile;
+  if (p->frame) {  // tiles owned by other ranks must read 0
+    VRB_CUDA(cudaMemsetAsync(p->frame, 0, (size_t)p->width * p->height * 8, p->ctx->stream));
+  }
+  return VRB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,151 @@
+/* vrb200 — C ABI of libvrb200.so: B200 (sm_100a) CUDA implementation of cpp_volume_rendering's
+ * structured single-pass ray-casting path.
+ *
+ * This is the drop-in boundary.  The reference has no FFI: its boundary is the C++ virtual interface
+ * BaseVolumeRenderer (cppvolrend/volrenderbase.h:25-97) registered through
+ * RenderingManager::AddVolumeRenderer (cppvolrend/renderingmanager.h:55, .cpp:119-123).  The C++
+ * plugins in cpp_volume_rendering_b200/host/ implement that interface and forward to the entry points
+ * below; each entry point cites the reference call it replaces.
+ *
+ * Conventions: every function returns 0 on success and a negative vrb_status on error, never calls
+ * exit() and never throws across the ABI; vrb_last_error() returns a thread-local message.
+ * Threading: one host thread per context (as in the reference: single GL context, single thread).
+ * Kernels run on the context stream; redraw is asynchronous, read_frame / counters synchronise.
+ * There is no CPU fallback: without a CUDA device vrb_ctx_create fails with VRB_ERR_NO_DEVICE.
+ */
+#ifndef VRB200_H
+#define VRB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VRB_ABI_VERSION 1
+
+typedef enum {
+  VRB_OK = 0,
+  VRB_ERR_INVALID = -1,     /* bad argument / wrong call order */
+  VRB_ERR_NO_DEVICE = -2,   /* no CUDA device / wrong architecture */
+  VRB_ERR_CUDA = -3,        /* CUDA runtime error, text in vrb_last_error() */
+  VRB_ERR_NO_VOLUME = -4,   /* Init without a volume (reference: Init returns false, rc1prenderer.cpp:54) */
+  VRB_ERR_UNSUPPORTED = -5
+} vrb_status;
+
+/* vis::DataStorageSize (libs/volvis_utils/structuredgridvolume.h) */
+typedef enum { VRB_U8 = 0, VRB_U16 = 1, VRB_F32 = 2 } vrb_dtype;
+
+/* One value per reference renderer on the hot path. */
+typedef enum {
+  VRB_RC1PASS = 0,     /* RayCasting1Pass                       structured/rc1pass          */
+  VRB_ISO_ADAPT = 1,   /* RayCasting1PassIsoAdapt               structured/rc1pisoadapt     */
+  VRB_ISO_SKIP_V1 = 2, /* CustomRayCasting1PassIsoAdapt         structured/rc1pisocustom    */
+  VRB_ISO_SKIP_V2 = 3, /* CustomRayCasting1PassIsoDfsAdapt      structured/rc1pisodfscustom */
+  VRB_DOS_CONE = 4,    /* RC1PConeTracingDirOcclusionShading    structured/rc1pdosct        */
+  VRB_EBS_SAT = 5,     /* RC1PExtinctionBasedShading            structured/rc1pextbsd       */
+  VRB_VCT = 6,         /* RC1PVoxelConeTracingSGPU              structured/rc1pvctsg        */
+  VRB_SBTM_DOS = 7     /* SBTMDirectionalOcclusionShading       structured/sbtmdos          */
+} vrb_renderer_kind;
+
+typedef enum { VRB_FRAME_RGBA16F = 0, VRB_FRAME_RGB8_OVER_WHITE = 1, VRB_FRAME_RGBA32F = 2 } vrb_frame_format;
+
+typedef struct vrb_ctx vrb_ctx;
+typedef struct vrb_renderer vrb_renderer;
+
+/* Uniforms every ray caster receives from Update(vis::Camera*) — rc1prenderer.cpp:89-103:
+ * CameraEye, mat3(u_CameraLookAt) column-major (glm::lookAt, camera.cpp:281-284),
+ * u_TanCameraFovY = tan(radians(fovy)/2), u_CameraAspectRatio = W/H (renderingmanager.cpp:326). */
+typedef struct {
+  float eye[3];
+  float lookat[9];
+  float tan_fovy;
+  float aspect;
+} vrb_camera;
+
+/* RenderingParameters Blinn-Phong + first light source (renderingparameters.cpp:17-32,70-172),
+ * the values Update() binds at rc1prenderer.cpp:117-133. */
+typedef struct {
+  float ka, kd, ks, shininess;
+  float ispecular[3];
+  float position[3];
+} vrb_light;
+
+/* Run-time parameters of RayCasting1Pass: its public/ImGui-mutable members (rc1prenderer.h:62,75,
+ * rc1prenderer.cpp:18-27), plus the new-build knobs that have no reference counterpart.
+ * Pass to vrb_renderer_set_params with sizeof(vrb_rc1pass_params). */
+typedef struct {
+  float step_size;               /* m_u_step_size; <= 0 keeps Init's default 0.5/sqrt(3)*|voxel scale| (rc1prenderer.cpp:61-63) */
+  int   apply_gradient_shading;  /* m_apply_gradient_shading (needs a gradient volume) */
+  int   skip_block;              /* 0 = reference march; 4/8/16/32 = lattice-preserving empty-space skipping block edge */
+  int   count_samples;           /* 1 = instrumented kernel that counts march-loop iterations (debug/metric) */
+  int   tf_in_smem;              /* 0 = TF through a 1D texture object (reference semantics); 1 = shared-memory table */
+} vrb_rc1pass_params;
+
+/* ---- library / context ------------------------------------------------------------------- */
+int         vrb_abi_version(void);
+const char* vrb_last_error(void);
+
+/* Replaces the GL context the reference creates in app_freeglut.cpp:113-139.  stream: a cudaStream_t
+ * to run on (may be NULL: the context creates its own non-blocking stream). */
+int vrb_ctx_create(int device, void* stream, vrb_ctx** out);
+int vrb_ctx_destroy(vrb_ctx* ctx);
+int vrb_ctx_synchronize(vrb_ctx* ctx);
+int vrb_ctx_stream(vrb_ctx* ctx, void** out_stream);
+
+/* ---- inputs (DataManager side) ------------------------------------------------------------ */
+/* Replaces vis::GenerateRTexture (libs/volvis_utils/utils.cpp:20-56): voxels (x fastest, HOST memory)
+ * are normalised exactly as StructuredGridVolume::GetNormalizedSample does
+ * (structuredgridvolume.cpp:121-151) and stored as an R16F 3D texture, GL_LINEAR, CLAMP_TO_EDGE.
+ * The raw voxels are also kept on the device for the precompute stages that read the CPU array in the
+ * reference (block min/max, SAT, supervoxels). */
+int vrb_volume_upload(vrb_ctx* ctx, const void* voxels, int dtype, int64_t w, int64_t h, int64_t d,
+                      float sx, float sy, float sz);
+/* Same, voxels already resident in DEVICE memory (used when a step's inputs must be in HBM). */
+int vrb_volume_upload_device(vrb_ctx* ctx, const void* dev_voxels, int dtype, int64_t w, int64_t h, int64_t d,
+                             float sx, float sy, float sz);
+/* Read back the R16F texture contents as float32 (test hook for bit-exactness of the quantisation). */
+int vrb_volume_read_r16f(vrb_ctx* ctx, float* host_out);
+
+/* Replaces TransferFunction1D::GenerateTexture_1D_RGBt / _RGBA (transferfunction1d.cpp:58-118).
+ * table: n x {r,g,b,a} doubles = m_transferfunction after BuildLinear (n = max_density + 1);
+ * extinction_type = TransferFunction1D::extinction_coef_type. Both the RGBt (extinction) and the RGBA
+ * (opacity) RGBA16F textures are built. */
+int vrb_tf_upload(vrb_ctx* ctx, const double* table, int n, int extinction_type);
+/* Test hook: the two RGBA16F textures as float32, n*4 each (either pointer may be NULL). */
+int vrb_tf_read(vrb_ctx* ctx, float* host_rgbt, float* host_rgba);
+
+/* ---- renderers (BaseVolumeRenderer side) -------------------------------------------------- */
+int vrb_renderer_create(vrb_ctx* ctx, int kind, vrb_renderer** out);          /* new X()            main.cpp:62-79 */
+int vrb_renderer_destroy(vrb_renderer* r);                                    /* Clean() + delete   renderingmanager.cpp:372-379 */
+int vrb_renderer_init(vrb_renderer* r, int width, int height);                /* Init(w,h)          volrenderbase.h:47 */
+int vrb_renderer_reshape(vrb_renderer* r, int width, int height);             /* Reshape(w,h)       volrenderbase.cpp:48-75 */
+int vrb_renderer_set_params(vrb_renderer* r, const void* pod, size_t size);   /* ImGui-mutated members */
+int vrb_renderer_get_params(vrb_renderer* r, void* pod, size_t size);
+int vrb_renderer_update(vrb_renderer* r, const vrb_camera* cam, const vrb_light* light); /* Update(camera)  volrenderbase.h:48 */
+int vrb_renderer_redraw(vrb_renderer* r, int multiscaling_mode);              /* Redraw()           volrenderbase.h:49 */
+
+/* Replaces GetScreenTextureID() (volrenderbase.h:73-75): device pointer to the RGBA16F frame, row 0 =
+ * bottom row as in GL.  Valid until the next reshape/destroy. */
+int vrb_renderer_frame(vrb_renderer* r, void** dev_rgba16f, int* width, int* height);
+/* Replaces the blit + glReadPixels of RenderingManager::GetFrontBufferPixelData
+ * (renderingmanager.cpp:476-492).  Synchronises. host must hold W*H*{8,3,16} bytes. */
+int vrb_renderer_read_frame(vrb_renderer* r, void* host, int format);
+/* samples: march-loop iterations of the last redraw (only if count_samples was set, else 0);
+ * ms: device time of the last redraw measured with CUDA events on the context stream. */
+int vrb_renderer_counters(vrb_renderer* r, uint64_t* samples, double* ms);
+
+/* ---- multi-GPU: image-space partition (no reference counterpart) ------------ */
+/* Tiles of tile x tile pixels are dealt round-robin: this rank renders tile t iff t % n_ranks == rank.
+ * The frame keeps full size; tiles of other ranks stay 0. */
+int vrb_renderer_set_partition(vrb_renderer* r, int rank, int n_ranks, int tile);
+
+/* ---- measurement ---------------------------------------------------------------------------- */
+/* Cache-resident trilinear R16F tex3D microbenchmark: the texture-fetch roofline denominator P_tex
+ * (SURVEY.md §8d).  Returns fetches per second of the whole GPU. */
+int vrb_bench_tex_peak(vrb_ctx* ctx, double* fetches_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VRB200_H */

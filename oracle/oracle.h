@@ -1,0 +1,73 @@
+/* ORACLE — TEST INFRASTRUCTURE ONLY (see orc_common.h).  C API of liboracle.so, loaded through
+ * ctypes by tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs.  Never by the product.
+ * Parity status: "parity unpinned" by reference golden vectors (none exist); pinned by KATs. */
+#ifndef ORACLE_H
+#define ORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { ORC_U8 = 0, ORC_U16 = 1, ORC_F32 = 2 };
+
+/* TransferFunction1D::BuildLinear (libs/volvis_utils/transferfunction1d.cpp:319-358).
+ * rgb_pts: n_rgb * {r,g,b,iso}; a_pts: n_a * {alpha,iso} (doubles as read by reader.cpp:793-806,
+ * narrowed to float by TransferControlPoint's glm::vec4).  out: (max_density+1)*4 doubles, zero-filled first. */
+void orc_tf_build_linear(const double* rgb_pts, int n_rgb, const double* a_pts, int n_a,
+                         int max_density, double* out_table);
+
+/* GenerateTexture_1D_RGBt / _RGBA (transferfunction1d.cpp:58-118): table -> float32 RGBA rounded to
+ * RGBA16F.  kind 0 = RGBt (rgb + extinction ln(1/(1-a))), 1 = RGBA (rgb + opacity). */
+void orc_tf_texture(const double* table, int n, int extinction_type, int kind, float* out_rgba);
+
+/* TransferFunction1D::Get / GetExtN / GetOpcN (transferfunction1d.cpp:132-157,159-197). */
+void  orc_tf_get(const double* table, int max_density, double value, double max_data_value, float out[4]);
+float orc_tf_get_extn(const double* table, int max_density, int extinction_type, double normalized_value);
+float orc_tf_get_opcn(const double* table, int max_density, int extinction_type, double normalized_value);
+
+/* GenerateRTexture (libs/volvis_utils/utils.cpp:20-56) over GetNormalizedSample
+ * (structuredgridvolume.cpp:121-151): voxel -> double v/255 | v/65535 | v -> float32 -> R16F.
+ * out: n float32 values already rounded to binary16. */
+void orc_volume_r16f(const void* voxels, int dtype, int64_t n, float* out);
+
+/* Camera basis: glm::lookAt (camera.cpp:281-284), returns the 3x3 upper-left block column-major. */
+void orc_lookat3(const float eye[3], const float center[3], const float up[3], float out_m3[9]);
+
+typedef struct {
+  int   width, height;          /* image size */
+  int   vol_w, vol_h, vol_d;    /* VolumeGridResolution */
+  float voxel[3];               /* VolumeVoxelSize */
+  float eye[3];                 /* CameraEye */
+  float lookat[9];              /* mat3(u_CameraLookAt), column-major */
+  float tan_fovy;               /* u_TanCameraFovY = tan(fovy/2) */
+  float aspect;                 /* u_CameraAspectRatio */
+  float step;                   /* StepSize */
+  int   weight_mode;            /* 0 float32 filter weights, 1 NVIDIA 1.8 fixed-point weights */
+  int   apply_phong;            /* ApplyGradientPhongShading */
+  float ka, kd, ks, shininess;  /* BlinnPhong* */
+  float ispec[3];               /* BlinnPhongIspecular */
+  float light_pos[3];           /* LightSourcePosition */
+  int   row_begin, row_end, row_stride; /* render rows [begin,end) step stride (bounded CPU samples) */
+  int   threads;                /* OpenMP threads, 0 = all */
+} orc_rc1p_params;
+
+/* main() of cppvolrend/structured/rc1pass/ray_marching_1p.comp:85-178 for every pixel.
+ * vol_r16f: W*H*D floats (orc_volume_r16f); tf_rgbt: tf_n*4 floats (orc_tf_texture kind 0);
+ * grad_rgb: optional W*H*D*3 gradient texture or NULL.
+ * out_rgba: width*height*4 float32, row 0 = gl_GlobalInvocationID.y == 0 (bottom of the GL image),
+ * values rounded to RGBA16F as imageStore does; pixels whose ray misses the box stay 0 (ClearTexture).
+ * out_samples (optional): per-pixel count of march-loop iterations. Returns total samples. */
+uint64_t orc_rc1pass_render(const orc_rc1p_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
+                            const float* grad_rgb, float* out_rgba, uint32_t* out_samples);
+
+/* RenderFrameToScreen::Draw + glReadPixels (renderoutputframe.cpp:214-258, renderingmanager.cpp:103-109,476-492):
+ * GL blend (SRC_ALPHA, ONE_MINUS_SRC_ALPHA) of the RGBA16F frame over the white clear colour into an
+ * RGB8 unorm back buffer.  out_rgb8: n_pixels*3. */
+void orc_blit_over_white(const float* rgba, int64_t n_pixels, uint8_t* out_rgb8);
+
+int orc_max_threads(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
