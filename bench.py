@@ -1,0 +1,319 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: RayCasting1Pass frames at BASELINE.json configs[1]
+(512^3 uint16 synthetic volume, bonsai_01.tf1d, 1024x1024, step 0.5 voxel, "Initial State" camera).
+
+A step = one frame (Update + Redraw).  One JSON line on rank 0; see DESIGN.md §Measurement for how
+each field is produced.  `--impl reference` times the CPU oracle (the reference's shader math restated
+in C++, OpenMP over image rows) on the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "ray_samples_per_s"
+UNIT = "samples/s"
+VOL_N, IMG_W, IMG_H, STEP = 512, 1024, 1024, 0.5
+BYTES_PER_SAMPLE_L1TEX = 32.0   # 8 fp16 texels + 2 RGBA16F texels
+
+
+def workload_name(skip):
+    s = f"skip{skip}" if skip else "noskip"
+    return f"rc1pass_{VOL_N}c_u16_{IMG_W}x{IMG_H}_step{STEP}_{s}"
+
+
+def make_inputs(n=VOL_N, w=IMG_W, h=IMG_H):
+    from cpp_volume_rendering_b200 import inputs
+    vox = inputs.synth_volume(n, np.uint16)
+    table = inputs.tf_build_linear(inputs.bonsai_tf())
+    cam = inputs.default_camera(n, w, h)
+    light = inputs.default_light(n)
+    return vox, table, cam, light
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush(); self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [t.strip() for t in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for nme, val in zip(names, c[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(nme)
+        os.unlink(self.f.name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_frame(vox, table, cam, skip_rows=None, repeats=1):
+    """Times the oracle on this box's host cores.  Returns (samples/s, cores, sample description, samples)."""
+    from oracle import pyoracle as O
+    vol = O.volume_r16f(vox)
+    rgbt = O.tf_texture(table)
+    rows = skip_rows or (0, IMG_H, 1)
+    p = O.rc1pass_params(cam, IMG_W, IMG_H, vox.shape, STEP, rows=rows)
+    O.rc1pass_render(O.rc1pass_params(cam, IMG_W, IMG_H, vox.shape, STEP, rows=(0, IMG_H, 64)), vol, rgbt)  # warm-up
+    best, total = None, 0
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        _, total, _ = O.rc1pass_render(p, vol, rgbt)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return total / best, O.max_threads(), total, best
+
+
+def run_reference(args):
+    """Reference arm: the reference's CPU implementation of the path = the oracle port (the GLSL cannot run
+    here: no graphics stack).  Each step is one full frame of the same workload on all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import pyoracle as O
+    vox, table, cam, _ = make_inputs()
+    vol = O.volume_r16f(vox)
+    rgbt = O.tf_texture(table)
+    p = O.rc1pass_params(cam, IMG_W, IMG_H, vox.shape, STEP)
+    for _ in range(max(args.warmup, 1)):
+        O.rc1pass_render(O.rc1pass_params(cam, IMG_W, IMG_H, vox.shape, STEP, rows=(0, IMG_H, 16)), vol, rgbt)
+    times, total = [], 0
+    for _ in range(args.steps):
+        t0 = time.perf_counter()
+        _, total, _ = O.rc1pass_render(p, vol, rgbt)
+        times.append(time.perf_counter() - t0)
+    ms = 1e3 * sum(times) / len(times)
+    val = total / (ms * 1e-3)
+    cores = O.max_threads()
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(0), "samples_per_frame": total, "fps": 1e3 / ms},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": "full 1024x1024 frame per step, OpenMP over rows, oracle/liboracle.so"},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_cuda(args):
+    import torch
+    import torch.distributed as dist
+    from cpp_volume_rendering_b200 import _capi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    stream = torch.cuda.Stream(device=dev)
+
+    vox, table, cam, light = make_inputs()
+    ctx = _capi.Context(local, stream.cuda_stream)
+    # inputs resident in HBM before the timed region: voxels are staged to the device with torch, then the
+    # library quantises device -> R16F texture (vrb_volume_upload_device)
+    t0 = time.perf_counter()
+    vox_dev = torch.from_numpy(vox.view(np.int16)).to(dev)
+    ctx.upload_volume_device(vox_dev.data_ptr(), np.uint16, vox.shape)
+    ctx.upload_tf(table)
+    ctx.synchronize()
+    init_ms = 1e3 * (time.perf_counter() - t0)
+
+    r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
+    r.init(IMG_W, IMG_H)
+    prm = r.get_params(_capi.Rc1PassParams())
+    prm.step_size = STEP
+    prm.skip_block = args.skip
+    prm.tf_in_smem = args.tf_smem
+    if world > 1:
+        r.set_partition(rank, world, 32)
+    frame_ptr, fw, fh = r.frame_ptr()
+
+    # sample count of this frame (instrumented launch, untimed)
+    prm.count_samples = 1
+    r.set_params(prm)
+    r.update(cam, light)
+    r.redraw()
+    fetched_local, _ = r.counters()
+    prm.count_samples = 0
+    r.set_params(prm)
+    fetched = torch.tensor([fetched_local], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(fetched)
+    fetched_total = int(fetched.item())
+
+    frame_t = None
+    if world > 1:
+        # wrap the library's frame as a torch tensor for the NCCL exchange (tiles are disjoint, others' are 0)
+        class _Wrap:
+            __cuda_array_interface__ = {"shape": (fh, fw, 4), "typestr": "<f2", "data": (frame_ptr, False), "version": 3}
+        frame_t = torch.as_tensor(_Wrap(), device=dev)
+
+    def step():
+        r.update(cam, light)
+        r.redraw()
+        if world > 1:
+            with torch.cuda.stream(stream):
+                dist.all_reduce(frame_t)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kernel_ms = []
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    barrier()
+    total_ms = e0.elapsed_time(e1)
+    clk = clocks.stop() if rank == 0 else None
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t.item()) / args.steps
+
+    # dominant kernel alone: per-launch device time from the library's own events on the launching stream
+    for _ in range(min(args.steps, 20)):
+        r.update(cam, light); r.redraw()
+        kernel_ms.append(r.counters()[1])
+    k_ms = float(np.mean(kernel_ms))
+
+    # e2e through the C ABI with host buffers: camera/light structs in, RGBA16F frame out to pinned memory
+    pinned = torch.empty((IMG_H, IMG_W, 4), dtype=torch.float16).pin_memory()
+    d2h = pinned.numel() * 2
+
+    def e2e_step():
+        r.update(cam, light)          # h2d: the step's inputs are the camera + light uniforms (kernel arguments)
+        r.redraw()
+        if world > 1:
+            with torch.cuda.stream(stream):
+                dist.all_reduce(frame_t)
+        if rank == 0 or world == 1:
+            r.read_frame_into(pinned.data_ptr())   # d2h + synchronise
+        else:
+            ctx.synchronize()
+
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_ms = 1e3 * (time.perf_counter() - t0) / args.steps
+    t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t.item())
+
+    if rank == 0:
+        import ctypes
+        tex_peak = ctx.tex_peak() if world == 1 or True else None
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        local_fetch = fetched_local
+        ach_fetch = local_fetch / (k_ms * 1e-3)
+        compulsory = 2.0 * VOL_N ** 3 + 8.0 * IMG_W * IMG_H
+        line = {
+            "metric": METRIC, "value": fetched_total / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args.skip), "volume": f"{VOL_N}^3 u16 -> R16F texture", "image": f"{IMG_W}x{IMG_H}",
+                       "step_voxels": STEP, "tf": "bonsai_01.tf1d", "camera": "Initial State (N,N,2N)",
+                       "partition": f"image tiles 32x32 round-robin over {world} rank(s)" + (", NCCL all_reduce of disjoint tiles" if world > 1 else ""),
+                       "l2_policy": "inputs_larger_than_l2 (256 MiB R16F volume vs 126 MB L2)",
+                       "samples_per_frame": fetched_total, "fps": 1e3 / ms_per_step, "init_ms_volume_upload": init_ms,
+                       "tf_in_smem": args.tf_smem, "skip_block": args.skip},
+            "e2e": {"value": fetched_total / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": ctypes.sizeof(_capi.Camera) + ctypes.sizeof(_capi.Light),
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "fps": 1e3 / e2e_ms},
+            "gpu_launches": args.steps,
+            "clocks": clk,
+            "roofline": {"bound": "l1tex", "kernel": "rc1pass_kernel", "achieved": ach_fetch * BYTES_PER_SAMPLE_L1TEX / 1e9,
+                         "peak": tex_peak * BYTES_PER_SAMPLE_L1TEX / 1e9, "unit": "GB/s", "frac": ach_fetch / tex_peak,
+                         "traffic": None, "kernel_ms": k_ms, "achieved_fetches_per_s": ach_fetch, "peak_fetches_per_s": tex_peak,
+                         "peak_source": "vrb_bench_tex_peak: cache-resident trilinear R16F tex3D microbenchmark, same job (of measured)"},
+            "roofline_hbm": {"bound": "hbm", "achieved": compulsory / (k_ms * 1e-3) / 1e9 / world, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": compulsory / (k_ms * 1e-3) / 1e9 / world / hbm_peak,
+                             "note": "compulsory bytes (R16F volume once + RGBA16F frame) / kernel time; this kernel is texture-bound, not HBM-bound",
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)"},
+        }
+        if world == 1 and not args.no_cpu:
+            v, cores, total, secs = cpu_frame(vox, table, cam, repeats=2)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                                    "sample": f"full {IMG_W}x{IMG_H} frame ({total} samples, best of 2, {secs:.2f} s), oracle/liboracle.so OpenMP over rows"}
+        print(json.dumps(line))
+    r.close()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--skip", type=int, default=0, help="empty-space skipping block edge (0 = off)")
+    ap.add_argument("--tf-smem", type=int, default=0)
+    ap.add_argument("--no-cpu", action="store_true", help="omit the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_cuda(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,207 @@
+"""ctypes binding of libvrb200.so (include/vrb200.h).
+
+This is plumbing for tests and bench.py: every call goes through the C ABI exactly as the C++
+plugins in host/ do.  There is no fallback: if the library is missing or no B200 is present the
+calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvrb200.so")
+
+VRB_U8, VRB_U16, VRB_F32 = 0, 1, 2
+(VRB_RC1PASS, VRB_ISO_ADAPT, VRB_ISO_SKIP_V1, VRB_ISO_SKIP_V2, VRB_DOS_CONE, VRB_EBS_SAT, VRB_VCT,
+ VRB_SBTM_DOS) = range(8)
+VRB_FRAME_RGBA16F, VRB_FRAME_RGB8_OVER_WHITE, VRB_FRAME_RGBA32F = 0, 1, 2
+
+_DTYPES = {np.dtype(np.uint8): VRB_U8, np.dtype(np.uint16): VRB_U16, np.dtype(np.float32): VRB_F32}
+
+
+class VrbError(RuntimeError):
+    pass
+
+
+class Camera(C.Structure):
+    _fields_ = [("eye", C.c_float * 3), ("lookat", C.c_float * 9), ("tan_fovy", C.c_float), ("aspect", C.c_float)]
+
+
+class Light(C.Structure):
+    _fields_ = [("ka", C.c_float), ("kd", C.c_float), ("ks", C.c_float), ("shininess", C.c_float),
+                ("ispecular", C.c_float * 3), ("position", C.c_float * 3)]
+
+
+class Rc1PassParams(C.Structure):
+    _fields_ = [("step_size", C.c_float), ("apply_gradient_shading", C.c_int), ("skip_block", C.c_int),
+                ("count_samples", C.c_int), ("tf_in_smem", C.c_int)]
+
+
+# name -> (restype, argtypes); the list doubles as the "every declared symbol is exported" check.
+_P = C.c_void_p
+SIGNATURES = {
+    "vrb_abi_version": (C.c_int, []),
+    "vrb_last_error": (C.c_char_p, []),
+    "vrb_ctx_create": (C.c_int, [C.c_int, _P, C.POINTER(_P)]),
+    "vrb_ctx_destroy": (C.c_int, [_P]),
+    "vrb_ctx_synchronize": (C.c_int, [_P]),
+    "vrb_ctx_stream": (C.c_int, [_P, C.POINTER(_P)]),
+    "vrb_volume_upload": (C.c_int, [_P, _P, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_float, C.c_float, C.c_float]),
+    "vrb_volume_upload_device": (C.c_int, [_P, _P, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_float, C.c_float, C.c_float]),
+    "vrb_volume_read_r16f": (C.c_int, [_P, _P]),
+    "vrb_tf_upload": (C.c_int, [_P, _P, C.c_int, C.c_int]),
+    "vrb_tf_read": (C.c_int, [_P, _P, _P]),
+    "vrb_renderer_create": (C.c_int, [_P, C.c_int, C.POINTER(_P)]),
+    "vrb_renderer_destroy": (C.c_int, [_P]),
+    "vrb_renderer_init": (C.c_int, [_P, C.c_int, C.c_int]),
+    "vrb_renderer_reshape": (C.c_int, [_P, C.c_int, C.c_int]),
+    "vrb_renderer_set_params": (C.c_int, [_P, _P, C.c_size_t]),
+    "vrb_renderer_get_params": (C.c_int, [_P, _P, C.c_size_t]),
+    "vrb_renderer_update": (C.c_int, [_P, C.POINTER(Camera), C.POINTER(Light)]),
+    "vrb_renderer_redraw": (C.c_int, [_P, C.c_int]),
+    "vrb_renderer_frame": (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "vrb_renderer_read_frame": (C.c_int, [_P, _P, C.c_int]),
+    "vrb_renderer_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_double)]),
+    "vrb_renderer_set_partition": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
+    "vrb_bench_tex_peak": (C.c_int, [_P, C.POINTER(C.c_double)]),
+}
+
+_lib = None
+
+
+def lib():
+    """Load libvrb200.so (built by __graft_entry__.build()).  Fails loudly when it is missing."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise VrbError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'`")
+        _lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(_lib, name)
+            fn.restype, fn.argtypes = res, args
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise VrbError(f"vrb error {rc}: {lib().vrb_last_error().decode(errors='replace')}")
+
+
+class Context:
+    def __init__(self, device=0, stream=None):
+        self._h = _P()
+        _check(lib().vrb_ctx_create(device, _P(stream) if stream else None, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().vrb_ctx_destroy(self._h)
+            self._h = _P()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def synchronize(self):
+        _check(lib().vrb_ctx_synchronize(self._h))
+
+    @property
+    def stream(self):
+        s = _P()
+        _check(lib().vrb_ctx_stream(self._h, C.byref(s)))
+        return s.value or 0
+
+    def upload_volume(self, voxels, scale=(1.0, 1.0, 1.0)):
+        """voxels: numpy array indexed [z, y, x] (x fastest), dtype u8 / u16 / f32 — HOST memory."""
+        v = np.ascontiguousarray(voxels)
+        d, h, w = v.shape
+        _check(lib().vrb_volume_upload(self._h, v.ctypes.data_as(_P), _DTYPES[v.dtype], w, h, d, *map(float, scale)))
+        self.vol_shape = (d, h, w)
+
+    def upload_volume_device(self, dev_ptr, dtype, shape_zyx, scale=(1.0, 1.0, 1.0)):
+        d, h, w = shape_zyx
+        _check(lib().vrb_volume_upload_device(self._h, _P(dev_ptr), _DTYPES[np.dtype(dtype)], w, h, d, *map(float, scale)))
+        self.vol_shape = (d, h, w)
+
+    def read_volume_r16f(self):
+        out = np.empty(self.vol_shape, np.float32)
+        _check(lib().vrb_volume_read_r16f(self._h, out.ctypes.data_as(_P)))
+        return out
+
+    def upload_tf(self, table, extinction_type=False):
+        t = np.ascontiguousarray(table, np.float64)
+        assert t.ndim == 2 and t.shape[1] == 4
+        self.tf_n = t.shape[0]
+        _check(lib().vrb_tf_upload(self._h, t.ctypes.data_as(_P), t.shape[0], int(bool(extinction_type))))
+
+    def read_tf(self):
+        a = np.empty((self.tf_n, 4), np.float32)
+        b = np.empty((self.tf_n, 4), np.float32)
+        _check(lib().vrb_tf_read(self._h, a.ctypes.data_as(_P), b.ctypes.data_as(_P)))
+        return a, b
+
+    def tex_peak(self):
+        v = C.c_double()
+        _check(lib().vrb_bench_tex_peak(self._h, C.byref(v)))
+        return v.value
+
+
+class Renderer:
+    def __init__(self, ctx, kind):
+        self.ctx = ctx
+        self._h = _P()
+        _check(lib().vrb_renderer_create(ctx._h, kind, C.byref(self._h)))
+        self.size = None
+
+    def close(self):
+        if self._h:
+            lib().vrb_renderer_destroy(self._h)
+            self._h = _P()
+
+    def init(self, width, height):
+        _check(lib().vrb_renderer_init(self._h, width, height))
+        self.size = (width, height)
+
+    def reshape(self, width, height):
+        _check(lib().vrb_renderer_reshape(self._h, width, height))
+        self.size = (width, height)
+
+    def set_params(self, pod):
+        _check(lib().vrb_renderer_set_params(self._h, C.byref(pod), C.sizeof(pod)))
+
+    def get_params(self, pod):
+        _check(lib().vrb_renderer_get_params(self._h, C.byref(pod), C.sizeof(pod)))
+        return pod
+
+    def update(self, cam, light=None):
+        _check(lib().vrb_renderer_update(self._h, C.byref(cam), C.byref(light) if light is not None else None))
+
+    def redraw(self, mode=0):
+        _check(lib().vrb_renderer_redraw(self._h, mode))
+
+    def frame_ptr(self):
+        p, w, h = _P(), C.c_int(), C.c_int()
+        _check(lib().vrb_renderer_frame(self._h, C.byref(p), C.byref(w), C.byref(h)))
+        return p.value, w.value, h.value
+
+    def read_frame(self, fmt=VRB_FRAME_RGBA16F, out=None):
+        w, h = self.size
+        if out is None:
+            out = {VRB_FRAME_RGBA16F: np.empty((h, w, 4), np.float16),
+                   VRB_FRAME_RGB8_OVER_WHITE: np.empty((h, w, 3), np.uint8),
+                   VRB_FRAME_RGBA32F: np.empty((h, w, 4), np.float32)}[fmt]
+        _check(lib().vrb_renderer_read_frame(self._h, out.ctypes.data_as(_P), fmt))
+        return out
+
+    def read_frame_into(self, host_ptr, fmt=VRB_FRAME_RGBA16F):
+        _check(lib().vrb_renderer_read_frame(self._h, _P(host_ptr), fmt))
+
+    def counters(self):
+        s, ms = C.c_uint64(), C.c_double()
+        _check(lib().vrb_renderer_counters(self._h, C.byref(s), C.byref(ms)))
+        return s.value, ms.value
+
+    def set_partition(self, rank, n_ranks, tile=32):
+        _check(lib().vrb_renderer_set_partition(self._h, rank, n_ranks, tile))

@@ -1,0 +1,136 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.  ctypes binding of oracle/liboracle.so.
+
+May be imported only by tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs.
+Parity status: "parity unpinned" by reference golden vectors (none exist for this path); see oracle/orc_common.h.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liboracle.so")
+_P = C.c_void_p
+_lib = None
+
+
+class Rc1pParams(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int),
+                ("vol_w", C.c_int), ("vol_h", C.c_int), ("vol_d", C.c_int),
+                ("voxel", C.c_float * 3), ("eye", C.c_float * 3), ("lookat", C.c_float * 9),
+                ("tan_fovy", C.c_float), ("aspect", C.c_float), ("step", C.c_float),
+                ("weight_mode", C.c_int), ("apply_phong", C.c_int),
+                ("ka", C.c_float), ("kd", C.c_float), ("ks", C.c_float), ("shininess", C.c_float),
+                ("ispec", C.c_float * 3), ("light_pos", C.c_float * 3),
+                ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} not built: make -C oracle")
+        L = C.CDLL(LIB_PATH)
+        L.orc_tf_build_linear.argtypes = [_P, C.c_int, _P, C.c_int, C.c_int, _P]
+        L.orc_tf_texture.argtypes = [_P, C.c_int, C.c_int, C.c_int, _P]
+        L.orc_tf_get.argtypes = [_P, C.c_int, C.c_double, C.c_double, _P]
+        L.orc_tf_get_extn.argtypes = [_P, C.c_int, C.c_int, C.c_double]
+        L.orc_tf_get_extn.restype = C.c_float
+        L.orc_tf_get_opcn.argtypes = [_P, C.c_int, C.c_int, C.c_double]
+        L.orc_tf_get_opcn.restype = C.c_float
+        L.orc_volume_r16f.argtypes = [_P, C.c_int, C.c_int64, _P]
+        L.orc_lookat3.argtypes = [_P, _P, _P, _P]
+        L.orc_rc1pass_render.argtypes = [C.POINTER(Rc1pParams), _P, _P, C.c_int, _P, _P, _P]
+        L.orc_rc1pass_render.restype = C.c_uint64
+        L.orc_blit_over_white.argtypes = [_P, C.c_int64, _P]
+        L.orc_max_threads.restype = C.c_int
+        _lib = L
+    return _lib
+
+
+def _ptr(a):
+    return a.ctypes.data_as(_P) if a is not None else None
+
+
+_DT = {np.dtype(np.uint8): 0, np.dtype(np.uint16): 1, np.dtype(np.float32): 2}
+
+
+def tf_build_linear(rgb_pts, a_pts, max_density=255):
+    rgb = np.ascontiguousarray(rgb_pts, np.float64)
+    a = np.ascontiguousarray(a_pts, np.float64)
+    out = np.empty((max_density + 1, 4), np.float64)
+    lib().orc_tf_build_linear(_ptr(rgb), len(rgb), _ptr(a), len(a), max_density, _ptr(out))
+    return out
+
+
+def tf_texture(table, extinction_type=False, kind=0):
+    t = np.ascontiguousarray(table, np.float64)
+    out = np.empty((t.shape[0], 4), np.float32)
+    lib().orc_tf_texture(_ptr(t), t.shape[0], int(extinction_type), kind, _ptr(out))
+    return out
+
+
+def tf_get_extn(table, value, extinction_type=False):
+    t = np.ascontiguousarray(table, np.float64)
+    return lib().orc_tf_get_extn(_ptr(t), t.shape[0] - 1, int(extinction_type), float(value))
+
+
+def tf_get_opcn(table, value, extinction_type=False):
+    t = np.ascontiguousarray(table, np.float64)
+    return lib().orc_tf_get_opcn(_ptr(t), t.shape[0] - 1, int(extinction_type), float(value))
+
+
+def volume_r16f(voxels):
+    v = np.ascontiguousarray(voxels)
+    out = np.empty(v.shape, np.float32)
+    lib().orc_volume_r16f(_ptr(v), _DT[v.dtype], v.size, _ptr(out))
+    return out
+
+
+def lookat3(eye, center, up):
+    e, c, u = (np.ascontiguousarray(t, np.float32) for t in (eye, center, up))
+    out = np.empty(9, np.float32)
+    lib().orc_lookat3(_ptr(e), _ptr(c), _ptr(u), _ptr(out))
+    return out
+
+
+def rc1pass_params(cam, width, height, vol_shape_zyx, step, voxel=(1.0, 1.0, 1.0), weight_mode=0, light=None,
+                   apply_phong=0, rows=None, threads=0):
+    """cam/light: the same ctypes structs handed to the C ABI (cpp_volume_rendering_b200._capi)."""
+    p = Rc1pParams()
+    p.width, p.height = width, height
+    p.vol_d, p.vol_h, p.vol_w = vol_shape_zyx
+    p.voxel[:] = voxel
+    p.eye[:] = list(cam.eye)
+    p.lookat[:] = list(cam.lookat)
+    p.tan_fovy, p.aspect, p.step = cam.tan_fovy, cam.aspect, step
+    p.weight_mode, p.apply_phong = weight_mode, apply_phong
+    if light is not None:
+        p.ka, p.kd, p.ks, p.shininess = light.ka, light.kd, light.ks, light.shininess
+        p.ispec[:] = list(light.ispecular)
+        p.light_pos[:] = list(light.position)
+    r = rows or (0, height, 1)
+    p.row_begin, p.row_end, p.row_stride = r
+    p.threads = threads
+    return p
+
+
+def rc1pass_render(p, vol_r16f, tf_rgbt, grad=None, want_samples=False):
+    """Returns (rgba float32 [H,W,4] (row 0 = bottom), total_samples, per-pixel samples or None)."""
+    vol = np.ascontiguousarray(vol_r16f, np.float32)
+    tf = np.ascontiguousarray(tf_rgbt, np.float32)
+    out = np.zeros((p.height, p.width, 4), np.float32)
+    ns = np.zeros((p.height, p.width), np.uint32) if want_samples else None
+    total = lib().orc_rc1pass_render(C.byref(p), _ptr(vol), _ptr(tf), tf.shape[0], _ptr(grad), _ptr(out), _ptr(ns))
+    return out, int(total), ns
+
+
+def blit_over_white(rgba):
+    a = np.ascontiguousarray(rgba, np.float32)
+    out = np.empty(a.shape[:-1] + (3,), np.uint8)
+    lib().orc_blit_over_white(_ptr(a), a.size // 4, _ptr(out))
+    return out
+
+
+def max_threads():
+    return lib().orc_max_threads()

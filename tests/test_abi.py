@@ -1,0 +1,58 @@
+"""The C-ABI library loads and exports every symbol include/vrb200.h declares (no compute calls)."""
+import ctypes
+import os
+import re
+
+from cpp_volume_rendering_b200 import _capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "vrb200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(vrb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_exported():
+    names = _declared()
+    assert len(names) >= 20
+    lib = ctypes.CDLL(_capi.LIB_PATH)
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, f"declared in vrb200.h but not exported: {missing}"
+
+
+def test_binding_covers_header():
+    assert sorted(_capi.SIGNATURES) == _declared()
+
+
+def test_abi_version_and_error_string():
+    lib = _capi.lib()
+    assert lib.vrb_abi_version() == 1
+    assert isinstance(lib.vrb_last_error(), bytes)
+
+
+def test_struct_sizes_match_header():
+    # vrb_camera: 3+9+1+1 floats; vrb_light: 4+3+3 floats; vrb_rc1pass_params: float + 4 ints
+    assert ctypes.sizeof(_capi.Camera) == 14 * 4
+    assert ctypes.sizeof(_capi.Light) == 10 * 4
+    assert ctypes.sizeof(_capi.Rc1PassParams) == 5 * 4
+
+
+def test_null_arguments_are_errors_not_crashes():
+    lib = _capi.lib()
+    assert lib.vrb_ctx_create(0, None, None) < 0
+    assert b"null" in lib.vrb_last_error()
+    assert lib.vrb_renderer_init(None, 4, 4) < 0
+    assert lib.vrb_ctx_destroy(None) == 0
+    assert lib.vrb_renderer_destroy(None) == 0
+
+
+def test_no_cpu_fallback_without_device():
+    """On a machine without a GPU context creation must fail loudly (no oracle / CPU path behind the ABI)."""
+    import torch
+    if torch.cuda.is_available():
+        return
+    h = ctypes.c_void_p()
+    rc = _capi.lib().vrb_ctx_create(0, None, ctypes.byref(h))
+    assert rc == -2 and b"no CPU fallback" in _capi.lib().vrb_last_error()

@@ -1,0 +1,232 @@
+"""Parity of the CUDA RayCasting1Pass path (through the C ABI) with the oracle.
+
+Bars (BASELINE.json north_star): integer / quantisation stages bit-exact; images within
+max|delta| <= 2/255 per channel (on the RGB8-over-white image and on RGBA16F*255) and SSIM >= 0.995.
+"""
+import numpy as np
+import pytest
+
+from cpp_volume_rendering_b200 import _capi, inputs, metrics
+from oracle import pyoracle as O
+
+pytestmark = pytest.mark.gpu
+
+TOL_255 = 2.0
+SSIM_MIN = 0.995
+
+
+def _render_gpu(ctx, cam, w, h, light=None, **prm_kw):
+    r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
+    try:
+        r.init(w, h)
+        prm = r.get_params(_capi.Rc1PassParams())
+        for k, v in prm_kw.items():
+            setattr(prm, k, v)
+        r.set_params(prm)
+        r.update(cam, light)
+        r.redraw()
+        img = r.read_frame(_capi.VRB_FRAME_RGBA32F)
+        img8 = r.read_frame(_capi.VRB_FRAME_RGB8_OVER_WHITE)
+        f16 = r.read_frame(_capi.VRB_FRAME_RGBA16F)
+        samples, ms = r.counters()
+        prm = r.get_params(_capi.Rc1PassParams())
+    finally:
+        r.close()
+    return img, img8, f16, samples, prm
+
+
+def _check_images(got, got8, ref, label=""):
+    ref8 = O.blit_over_white(ref)
+    d16 = float(np.abs(got - ref).max()) * 255.0
+    d8 = metrics.max_abs_delta(got8, ref8)
+    s = metrics.ssim(got8, ref8)
+    assert d16 <= TOL_255, f"{label}: RGBA16F max|d| = {d16:.3f}/255"
+    assert d8 <= TOL_255, f"{label}: RGB8 max|d| = {d8}/255"
+    assert s >= SSIM_MIN, f"{label}: SSIM = {s}"
+    return d16, d8, s
+
+
+# ---- inputs: bit-exact ----------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32])
+def test_volume_quantisation_bit_exact(ctx, dtype):
+    rng = np.random.default_rng(3)
+    shape = (9, 13, 21)   # ragged: x not a multiple of 4
+    if dtype == np.float32:
+        v = rng.uniform(0, 1, shape).astype(np.float32)
+        v.flat[:4] = [0.0, 1.0, 6e-8, 0.33325195]
+    else:
+        v = rng.integers(0, np.iinfo(dtype).max + 1, shape).astype(dtype)
+    ctx.upload_volume(v)
+    assert np.array_equal(ctx.read_volume_r16f(), O.volume_r16f(v))
+
+
+def test_volume_quantisation_all_u16_values(ctx):
+    v = np.arange(65536, dtype=np.uint16).reshape(16, 64, 64)
+    ctx.upload_volume(v)
+    assert np.array_equal(ctx.read_volume_r16f(), O.volume_r16f(v))
+
+
+def test_tf_textures_bit_exact(ctx, bonsai_table):
+    ctx.upload_tf(bonsai_table)
+    rgbt, rgba = ctx.read_tf()
+    assert np.array_equal(rgbt, O.tf_texture(bonsai_table, False, 0))
+    assert np.array_equal(rgba, O.tf_texture(bonsai_table, False, 1))
+    t = np.zeros((4, 4)); t[:, 3] = [0, 0.5, 2.0, 1.0]
+    ctx.upload_tf(t, extinction_type=True)
+    rgbt, rgba = ctx.read_tf()
+    assert np.array_equal(rgbt, O.tf_texture(t, True, 0)) and np.array_equal(rgba, O.tf_texture(t, True, 1))
+
+
+# ---- image parity ---------------------------------------------------------------------------------
+CASES = [
+    # n, dtype, (w,h), eye scale, up, step (None = Init default)
+    (64, np.uint8, (128, 128), (1, 1, 2), (0, 1, 0), None),
+    (96, np.uint16, (200, 120), (1, 1, 2), (0, 1, 0), None),        # non-square, not a multiple of the CTA tile
+    (64, np.float32, (97, 131), (-1.2, 0.4, 1.1), (0, 1, 0), 0.3),   # odd size, non power-of-two step
+    (128, np.uint8, (256, 256), (0.6, -1.2, -0.2), (0, 0, -1), 1.0), # camera list style view, large step
+    (64, np.uint8, (64, 64), (0.0, 0.0, 0.7), (0, 1, 0), 0.5),       # close: volume overflows the image
+]
+
+
+@pytest.mark.parametrize("n,dtype,size,eye_s,up,step", CASES)
+@pytest.mark.parametrize("tf_in_smem", [0, 1])
+def test_rc1pass_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, up, step, tf_in_smem):
+    w, h = size
+    vox = inputs.synth_volume(n, dtype)
+    ctx.upload_volume(vox)
+    ctx.upload_tf(bonsai_table)
+    cam = inputs.make_camera(tuple(n * e for e in eye_s), (0, 0, 0), up, 45.0, w, h)
+    kw = dict(tf_in_smem=tf_in_smem, count_samples=1)
+    if step is not None:
+        kw["step_size"] = step
+    got, got8, f16, samples, prm = _render_gpu(ctx, cam, w, h, **kw)
+    assert np.array_equal(f16.astype(np.float32), got)
+    p = O.rc1pass_params(cam, w, h, vox.shape, prm.step_size)
+    ref, total, _ = O.rc1pass_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table))
+    _check_images(got, got8, ref, f"n={n} {np.dtype(dtype).name} {w}x{h}")
+    # the sample lattice is bit-identical; only ERT near-ties (dst.a ~ 0.99) may move a ray's last sample
+    assert abs(samples - total) <= 2e-3 * total, (samples, total)
+
+
+def test_default_step_follows_init(ctx, bonsai_table):
+    """m_u_step_size = 0.5/sqrt(3) * |voxel scale| (rc1prenderer.cpp:61-63)."""
+    vox = inputs.synth_volume(32, np.uint8)
+    for scale in [(1, 1, 1), (1.0, 0.5, 2.0)]:
+        ctx.upload_volume(vox, scale)
+        ctx.upload_tf(bonsai_table)
+        r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
+        r.init(16, 16)
+        got = r.get_params(_capi.Rc1PassParams()).step_size
+        r.close()
+        sv = np.array(scale, np.float64)
+        want = np.float32((np.float32(0.5) / np.sqrt(np.float32(3.0))) * np.sqrt((sv * sv).sum()))
+        assert got == want
+
+
+def test_anisotropic_voxels_and_noncubic_volume(ctx, bonsai_table):
+    vox = inputs.synth_volume(0, np.uint8, shape=(80, 48, 33))
+    scale = (1.0, 1.5, 2.0)
+    ctx.upload_volume(vox, scale)
+    ctx.upload_tf(bonsai_table)
+    cam = inputs.make_camera((90.0, 70.0, 160.0), width=160, height=96)
+    got, got8, _, samples, prm = _render_gpu(ctx, cam, 160, 96, count_samples=1)
+    p = O.rc1pass_params(cam, 160, 96, vox.shape, prm.step_size, voxel=scale)
+    ref, total, _ = O.rc1pass_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table))
+    _check_images(got, got8, ref, "anisotropic")
+    assert abs(samples - total) <= 2e-3 * total
+
+
+def test_transparent_volume_sample_count_exact(ctx, bonsai_table):
+    """No ERT can trigger, so the count depends only on the (bit-identical) ray set-up and lattice."""
+    vox = np.full((40, 40, 40), 20, np.uint8)
+    ctx.upload_volume(vox)
+    ctx.upload_tf(bonsai_table)
+    cam = inputs.default_camera(40, 96, 96)
+    for step in (0.5, 0.3, 1.7):
+        got, _, _, samples, _ = _render_gpu(ctx, cam, 96, 96, count_samples=1, step_size=step)
+        p = O.rc1pass_params(cam, 96, 96, vox.shape, step)
+        ref, total, _ = O.rc1pass_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table))
+        assert samples == total and np.all(got == 0) and np.all(ref == 0)
+
+
+def test_camera_inside_and_tiny_volumes(ctx, bonsai_table):
+    ctx.upload_tf(bonsai_table)
+    vox = inputs.synth_volume(48, np.uint8)
+    ctx.upload_volume(vox)
+    cam = inputs.make_camera((3.0, -2.0, 5.0), center=(20, 10, -30), width=80, height=80)
+    got, got8, _, samples, prm = _render_gpu(ctx, cam, 80, 80, count_samples=1)
+    ref, total, _ = O.rc1pass_render(O.rc1pass_params(cam, 80, 80, vox.shape, prm.step_size), O.volume_r16f(vox), O.tf_texture(bonsai_table))
+    _check_images(got, got8, ref, "inside")
+    for shape in [(1, 1, 1), (2, 2, 2), (1, 5, 3)]:
+        v = np.full(shape, 120, np.uint8)
+        ctx.upload_volume(v)
+        cam = inputs.make_camera((2.0, 3.0, 6.0), width=48, height=48)
+        got, got8, _, samples, prm = _render_gpu(ctx, cam, 48, 48, count_samples=1)
+        ref, total, _ = O.rc1pass_render(O.rc1pass_params(cam, 48, 48, v.shape, prm.step_size), O.volume_r16f(v), O.tf_texture(bonsai_table))
+        _check_images(got, got8, ref, f"tiny {shape}")
+        assert samples == total
+
+
+def test_blit_bit_exact_on_same_frame(ctx, bonsai_table):
+    """RGB8-over-white is integer work on the RGBA16F frame: must equal the oracle's blit of the GPU frame."""
+    vox = inputs.synth_volume(64, np.uint8)
+    ctx.upload_volume(vox)
+    ctx.upload_tf(bonsai_table)
+    cam = inputs.default_camera(64, 128, 128)
+    got, got8, _, _, _ = _render_gpu(ctx, cam, 128, 128)
+    assert np.array_equal(got8, O.blit_over_white(got))
+
+
+def test_reinit_reshape_and_errors(ctx, bonsai_table):
+    vox = inputs.synth_volume(32, np.uint8)
+    ctx.upload_volume(vox)
+    ctx.upload_tf(bonsai_table)
+    r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
+    with pytest.raises(_capi.VrbError):
+        r.redraw()                      # Redraw before Init
+    r.init(32, 32)
+    with pytest.raises(_capi.VrbError):
+        r.redraw()                      # Redraw before Update
+    cam = inputs.default_camera(32, 32, 32)
+    r.update(cam)
+    r.redraw()
+    a = r.read_frame(_capi.VRB_FRAME_RGBA32F)
+    r.reshape(48, 40)
+    r.update(inputs.default_camera(32, 48, 40))
+    r.redraw()
+    assert r.read_frame(_capi.VRB_FRAME_RGBA32F).shape == (40, 48, 4)
+    r.init(32, 32)                       # Init is re-entrant (rc1prenderer.cpp:52)
+    r.update(cam)
+    r.redraw()
+    assert np.array_equal(r.read_frame(_capi.VRB_FRAME_RGBA32F), a)
+    bad = _capi.Rc1PassParams(); bad.step_size = 0.5; bad.skip_block = 7
+    with pytest.raises(_capi.VrbError):
+        r.set_params(bad)
+    r.close()
+
+
+def test_image_partition_union_equals_full_frame(ctx, bonsai_table):
+    """Image-space split: tiles dealt round-robin; the sum of the ranks' frames is the full frame."""
+    vox = inputs.synth_volume(64, np.uint8)
+    ctx.upload_volume(vox)
+    ctx.upload_tf(bonsai_table)
+    w, h = 200, 136
+    cam = inputs.default_camera(64, w, h)
+    full, _, _, tot, _ = _render_gpu(ctx, cam, w, h, count_samples=1)
+    for n_ranks, tile in [(2, 32), (3, 16), (8, 32)]:
+        acc = np.zeros_like(full)
+        cnt = 0
+        for rank in range(n_ranks):
+            r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
+            r.init(w, h)
+            prm = r.get_params(_capi.Rc1PassParams()); prm.count_samples = 1
+            r.set_params(prm)
+            r.set_partition(rank, n_ranks, tile)
+            r.update(cam)
+            r.redraw()
+            part = r.read_frame(_capi.VRB_FRAME_RGBA32F)
+            cnt += r.counters()[0]
+            r.close()
+            assert np.all((acc == 0) | (part == 0))   # tiles are disjoint
+            acc += part
+        assert np.array_equal(acc, full) and cnt == tot

@@ -1,0 +1,175 @@
+"""Known-answer tests that pin the oracle (the reference holds no golden vectors for this path:
+SURVEY.md §8c).  Closed-form cases derived from the shader statements themselves."""
+import math
+
+import numpy as np
+import pytest
+
+from cpp_volume_rendering_b200 import inputs
+from oracle import pyoracle as O
+
+
+# ---- binary16 conversion: glTexImage(GL_R16F)/imageStore(rgba16f) rounding ---------------------
+def test_half_rounding_matches_ieee_rne():
+    rng = np.random.default_rng(1)
+    x = np.concatenate([
+        rng.uniform(-2, 2, 20000), rng.uniform(-70000, 70000, 5000), 10.0 ** rng.uniform(-9, 5, 5000),
+        [0.0, -0.0, 1.0, 65504.0, 65519.9, 65520.0, 1e-8, 2.0 ** -24, 2.0 ** -25, 2.0 ** -25 * 1.0001, 2.0 ** -14, np.inf, -np.inf],
+    ]).astype(np.float32)
+    got = O.volume_r16f(x)  # f32 dtype: (double)f/1.0 -> float -> half
+    with np.errstate(over="ignore"):
+        want = x.astype(np.float16).astype(np.float32)
+    assert np.array_equal(got, want)
+
+
+def test_volume_normalisation_u8_u16():
+    v8 = np.arange(256, dtype=np.uint8)
+    want8 = (v8.astype(np.float64) / 255.0).astype(np.float32).astype(np.float16).astype(np.float32)
+    assert np.array_equal(O.volume_r16f(v8), want8)
+    v16 = np.arange(65536, dtype=np.uint16)
+    want16 = (v16.astype(np.float64) / 65535.0).astype(np.float32).astype(np.float16).astype(np.float32)
+    assert np.array_equal(O.volume_r16f(v16), want16)
+    assert O.volume_r16f(np.array([255], np.uint8))[0] == 1.0
+
+
+# ---- transfer function ---------------------------------------------------------------------------
+def test_tf_bonsai_known_values(bonsai_table):
+    t = bonsai_table
+    assert t.shape == (256, 4)
+    # alpha control points (0,0) (0,35) (0.5,40) (0.8,255): linear in between
+    assert np.all(t[:36, 3] == 0.0)
+    assert t[40, 3] == pytest.approx(0.5) and t[255, 3] == pytest.approx(0.8, abs=1e-7)
+    assert t[38, 3] == pytest.approx(0.3, abs=1e-12)
+    assert t[147, 3] == pytest.approx(0.5 + float(np.float32(0.8) - np.float32(0.5)) * (107 / 215), abs=1e-12)
+    # rgb: green up to 58, black at 59, orange ramp 60..255
+    assert np.allclose(t[0:59, :3], [0, np.float32(0.9), 0])
+    assert np.allclose(t[59, :3], 0)
+    assert np.allclose(t[60, :3], [np.float32(0.7), np.float32(0.35), 0])
+    assert np.array_equal(O.tf_build_linear(inputs.bonsai_tf()["rgb_pts"], inputs.bonsai_tf()["a_pts"]), t)
+
+
+def test_tf_texture_extinction_and_opacity(bonsai_table):
+    rgbt = O.tf_texture(bonsai_table, False, 0)
+    rgba = O.tf_texture(bonsai_table, False, 1)
+    a = bonsai_table[:, 3].astype(np.float32)
+    ext = np.log(1.0 / (1.0 - a.astype(np.float64))).astype(np.float32).astype(np.float16).astype(np.float32)
+    assert np.array_equal(rgbt[:, 3], ext)
+    assert np.array_equal(rgba[:, 3], a.astype(np.float16).astype(np.float32))
+    assert np.array_equal(rgbt[:, :3], rgba[:, :3])
+    # alpha == 1 gives +inf extinction (transferfunction.h:79-82), kept as inf in half
+    t = np.zeros((2, 4)); t[1, 3] = 1.0
+    assert np.isinf(O.tf_texture(t, False, 0)[1, 3])
+    # extinction-type TF: RGBt keeps the value, RGBA converts with 1-exp(-x)
+    t[1, 3] = 2.0
+    assert O.tf_texture(t, True, 0)[1, 3] == 2.0
+    assert O.tf_texture(t, True, 1)[1, 3] == np.float32(np.float16(np.float32(1 - math.exp(-2.0))))
+
+
+def test_tf_get_ext_opc(bonsai_table):
+    # Get(): linear interpolation of the double table at value*max_density (transferfunction1d.cpp:132-157)
+    v = 37.5 / 255.0
+    a = 0.5 * (bonsai_table[37, 3] + bonsai_table[38, 3])
+    assert O.tf_get_opcn(bonsai_table, v) == pytest.approx(a, rel=1e-6)
+    assert O.tf_get_extn(bonsai_table, v) == pytest.approx(math.log(1 / (1 - a)), rel=1e-6)
+    assert O.tf_get_opcn(bonsai_table, 1.0) == np.float32(bonsai_table[255, 3])
+    assert O.tf_get_opcn(bonsai_table, -0.1) == 0.0 and O.tf_get_opcn(bonsai_table, 1.1) == 0.0
+
+
+# ---- camera --------------------------------------------------------------------------------------
+def test_lookat_is_orthonormal_and_matches_python():
+    for eye, up in [((256, 256, 512), (0, 1, 0)), ((154.214, -298.045, -54.6573), (0, 0, -1)), ((0, 0, 173), (0, 1, 0))]:
+        m = O.lookat3(eye, (0, 0, 0), up).reshape(3, 3)  # columns
+        assert np.allclose(m @ m.T, np.eye(3), atol=1e-6)
+        assert np.array_equal(m.ravel(), inputs.lookat3(eye, (0, 0, 0), up))
+        f = -np.array([m[0, 2], m[1, 2], m[2, 2]])
+        assert np.allclose(f, -np.array(eye) / np.linalg.norm(eye), atol=1e-6)
+
+
+# ---- the march: constant-density volume has a closed form ----------------------------------------
+def _const_case(density_u8, n=16, size=24, step=0.5):
+    vox = np.full((n, n, n), density_u8, np.uint8)
+    cam = inputs.make_camera((0.0, 0.0, 3.0 * n), width=size, height=size)
+    p = O.rc1pass_params(cam, size, size, vox.shape, step)
+    return vox, cam, p
+
+
+def test_constant_volume_closed_form(bonsai_table):
+    """Homogeneous medium: after k steps of length h, dst.a = 1 - exp(-tau*k*h) and rgb = c * dst.a; the loop
+    stops at the first k with dst.a > 0.99 (ray_marching_1p.comp:160-167)."""
+    rgbt = O.tf_texture(bonsai_table)
+    vox, cam, p = _const_case(100)
+    img, total, ns = O.rc1pass_render(p, O.volume_r16f(vox), rgbt, want_samples=True)
+    # density 100/255 in half, TF fetched with GL_LINEAR at u = d*256 - 0.5
+    d = float(np.float16(np.float32(100 / 255.0)))
+    u = d * 256 - 0.5
+    i0 = int(math.floor(u)); w = u - i0
+    tau = (1 - w) * rgbt[i0, 3] + w * rgbt[i0 + 1, 3]
+    col = (1 - w) * rgbt[i0, :3] + w * rgbt[i0 + 1, :3]
+    k = math.ceil(-math.log(0.01) / (tau * 0.5) - 1e-9)
+    cy = cx = 12
+    assert ns[cy, cx] == k
+    a = 1 - math.exp(-tau * 0.5 * k)
+    assert img[cy, cx, 3] == pytest.approx(a, abs=2e-3)       # fp16 store
+    assert np.allclose(img[cy, cx, :3], col * a, atol=2e-3)
+    assert total == ns.sum()
+
+
+def test_transparent_volume_visits_whole_ray_and_stores_zero(bonsai_table):
+    """density 20/255 has alpha 0: every ray marches ceil(D/step) samples and stores (0,0,0,0)."""
+    vox, cam, p = _const_case(20, n=16, size=24, step=0.5)
+    img, total, ns = O.rc1pass_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table), want_samples=True)
+    assert np.all(img == 0)
+    # the centre ray crosses the box along z: D ~ 16 -> 32 samples (the last may be a remainder step)
+    assert ns[12, 12] in (32, 33)
+    assert (ns > 0).any() and (ns == 0).any()   # corner rays miss the box
+
+
+def test_remainder_step_is_used(bonsai_table):
+    """h = min(StepSize, D - s): with step 0.3 on a 16-voxel chord the last sample uses the short remainder and the
+    total optical depth is tau*D, independent of the step (midpoint rule on a constant)."""
+    rgbt = O.tf_texture(bonsai_table)
+    vox = np.full((16, 16, 16), 37, np.uint8)   # alpha ~0.2 -> small tau, never reaches 0.99 over 16 voxels
+    cam = inputs.make_camera((0.0, 0.0, 48.0), width=1, height=1)
+    vol = O.volume_r16f(vox)
+    out = []
+    for step in (0.3, 0.5, 0.7, 5.0, 100.0):
+        p = O.rc1pass_params(cam, 1, 1, vox.shape, step)
+        img, total, _ = O.rc1pass_render(p, vol, rgbt)
+        out.append(img[0, 0, 3])
+        assert total == math.ceil(16.0 / step - 1e-6) or total == math.ceil(16.0 / step - 1e-6) + 1
+    assert np.allclose(out, out[0], atol=2e-3)
+
+
+def test_rays_missing_the_box_stay_cleared(bonsai_table):
+    vox = np.full((8, 8, 8), 200, np.uint8)
+    cam = inputs.make_camera((0.0, 0.0, 100.0), width=32, height=32)
+    p = O.rc1pass_params(cam, 32, 32, vox.shape, 0.5)
+    img, _, ns = O.rc1pass_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table), want_samples=True)
+    assert np.all(img[ns == 0] == 0) and (ns == 0).sum() > 800 and (ns > 0).sum() > 0
+
+
+def test_camera_inside_volume_starts_at_zero(bonsai_table):
+    """tnear is clamped to 0 (ray_bbox_intersection.comp:46): the march starts at the eye."""
+    vox = np.full((32, 32, 32), 20, np.uint8)
+    cam = inputs.make_camera((0.0, 0.0, 0.0), center=(0, 0, -1), width=3, height=3)
+    p = O.rc1pass_params(cam, 3, 3, vox.shape, 0.5)
+    _, _, ns = O.rc1pass_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table), want_samples=True)
+    assert ns[1, 1] == 32  # 16 voxels to the -z face at step 0.5
+
+
+def test_row_subset_renders_only_those_rows(bonsai_table):
+    vox = inputs.synth_volume(32, np.uint8)
+    cam = inputs.default_camera(32, 40, 40)
+    vol, rgbt = O.volume_r16f(vox), O.tf_texture(bonsai_table)
+    full, tot, _ = O.rc1pass_render(O.rc1pass_params(cam, 40, 40, vox.shape, 0.5), vol, rgbt)
+    part, tot2, _ = O.rc1pass_render(O.rc1pass_params(cam, 40, 40, vox.shape, 0.5, rows=(4, 40, 8)), vol, rgbt)
+    assert np.array_equal(part[4::8], full[4::8]) and np.all(part[5] == 0) and 0 < tot2 < tot
+
+
+# ---- blit ----------------------------------------------------------------------------------------
+def test_blit_over_white():
+    rgba = np.array([[0, 0, 0, 0], [1, 0, 0, 1], [0.25, 0.5, 0.0, 0.5], [2, 2, 2, 1]], np.float32)
+    got = O.blit_over_white(rgba)
+    # out = rgb*a + (1-a): premultiplied colour is multiplied by alpha again
+    want = np.array([[255, 255, 255], [255, 0, 0], [round((0.125 + 0.5) * 255), round(0.75 * 255), round(0.5 * 255)], [255, 255, 255]], np.uint8)
+    assert np.array_equal(got, want)
