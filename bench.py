@@ -163,6 +163,7 @@ def run_cuda(args):
     prm.step_size = STEP
     prm.skip_block = args.skip
     prm.tf_in_smem = args.tf_smem
+    prm.exact_filter = args.exact
     if world > 1:
         r.set_partition(rank, world, 32)
     frame_ptr, fw, fh = r.frame_ptr()
@@ -274,7 +275,7 @@ def run_cuda(args):
                        "partition": f"image tiles 32x32 round-robin over {world} rank(s)" + (", NCCL all_reduce of disjoint tiles" if world > 1 else ""),
                        "l2_policy": "inputs_larger_than_l2 (256 MiB R16F volume vs 126 MB L2)",
                        "samples_per_frame": fetched_total, "fps": 1e3 / ms_per_step, "init_ms_volume_upload": init_ms,
-                       "tf_in_smem": args.tf_smem, "skip_block": args.skip},
+                       "tf_in_smem": args.tf_smem, "exact_filter": args.exact, "skip_block": args.skip},
             "e2e": {"value": fetched_total / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": ctypes.sizeof(_capi.Camera) + ctypes.sizeof(_capi.Light),
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "fps": 1e3 / e2e_ms},
             "gpu_launches": args.steps,
@@ -306,7 +307,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--skip", type=int, default=0, help="empty-space skipping block edge (0 = off)")
-    ap.add_argument("--tf-smem", type=int, default=0)
+    ap.add_argument("--tf-smem", type=int, default=1)
+    ap.add_argument("--exact", type=int, default=1, help="float32 re-filtering of possibly-visible samples")
     ap.add_argument("--no-cpu", action="store_true", help="omit the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -13,10 +13,12 @@
 namespace vrb {
 
 struct Rc1Args {
-  cudaTextureObject_t vol, tf;
+  cudaTextureObject_t vol, vol_pt, tf;
   const uint2* tf_lin;       // RGBA16F table (n entries) for the shared-memory path
-  int tf_n;
+  const uint32_t* vis_mask;  // conservative "may be non-transparent" bit per TF cell (vrb_ctx.cu)
+  int tf_n, vis_words;
   int width, height;
+  float res[3];              // VolumeGridResolution
   float grid[3];             // VolumeGridSize
   float inv_grid[3];
   float eye[3];
@@ -31,21 +33,48 @@ struct Rc1Args {
 };
 
 constexpr int CTA_W = 16, CTA_H = 8;
+constexpr int UNROLL = 4;    // independent texture fetches in flight per ray
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
 }
 
-template <bool COUNT, bool TF_SMEM>
-__global__ void __launch_bounds__(CTA_W* CTA_H) rc1pass_kernel(const __grid_constant__ Rc1Args a) {
-  extern __shared__ uint4 s_tf[];  // TF_SMEM: entry i = {texel i, texel min(i+1,n-1)} as 8 halfs
+// texture(TexVolume, p) with float32 filter weights: the 8 texels through the point-sampled view of the same
+// array (CLAMP_TO_EDGE comes from the address mode), lerped in float32 in the oracle's order
+// (oracle/orc_common.h Tex3D::linear; GL 4.3 §8.14: i0 = floor(u*N - 0.5), alpha = frac(u*N - 0.5)).
+__device__ __noinline__ float tex3d_exact(cudaTextureObject_t pt, float ux, float uy, float uz, const float* res) {
+  const float X = fmaf(ux, res[0], -0.5f), Y = fmaf(uy, res[1], -0.5f), Z = fmaf(uz, res[2], -0.5f);
+  const float fx = floorf(X), fy = floorf(Y), fz = floorf(Z);
+  const float ax = X - fx, ay = Y - fy, az = Z - fz;
+  const float x0 = fx + 0.5f, x1 = fx + 1.5f, y0 = fy + 0.5f, y1 = fy + 1.5f, z0 = fz + 0.5f, z1 = fz + 1.5f;
+  const float c000 = tex3D<float>(pt, x0, y0, z0), c100 = tex3D<float>(pt, x1, y0, z0);
+  const float c010 = tex3D<float>(pt, x0, y1, z0), c110 = tex3D<float>(pt, x1, y1, z0);
+  const float c001 = tex3D<float>(pt, x0, y0, z1), c101 = tex3D<float>(pt, x1, y0, z1);
+  const float c011 = tex3D<float>(pt, x0, y1, z1), c111 = tex3D<float>(pt, x1, y1, z1);
+  const float c00 = fmaf(ax, c100 - c000, c000), c10 = fmaf(ax, c110 - c010, c010);
+  const float c01 = fmaf(ax, c101 - c001, c001), c11 = fmaf(ax, c111 - c011, c011);
+  const float c0 = fmaf(ay, c10 - c00, c00), c1 = fmaf(ay, c11 - c01, c01);
+  return fmaf(az, c1 - c0, c0);
+}
+
+// The march.  Every sample issues ONE hardware-filtered trilinear fetch.  Its density is only used to
+// classify the sample against the conservative visibility mask; samples that may be non-transparent
+// (a few per cent of the lattice for a typical TF) are re-evaluated with float32 filter weights when
+// EXACT is set, so the image matches the float32 evaluation of the shader while the empty space runs at
+// texture-unit rate.  UNROLL fetches are issued back to back before any is consumed.
+template <bool COUNT, bool TF_SMEM, bool EXACT>
+__global__ void __launch_bounds__(CTA_W* CTA_H, 12) rc1pass_kernel(const __grid_constant__ Rc1Args a) {
+  extern __shared__ uint4 s_dyn[];
+  uint4* s_tf = s_dyn;                                   // TF_SMEM: entry i = {texel i, texel min(i+1,n-1)}
+  uint32_t* s_mask = reinterpret_cast<uint32_t*>(s_dyn + (TF_SMEM ? a.tf_n : 0));
   if (TF_SMEM) {
     for (int i = threadIdx.x; i < a.tf_n; i += blockDim.x) {
       uint2 t0 = a.tf_lin[i], t1 = a.tf_lin[min(i + 1, a.tf_n - 1)];
       s_tf[i] = make_uint4(t0.x, t0.y, t1.x, t1.y);
     }
-    __syncthreads();
   }
+  for (int i = threadIdx.x; i < a.vis_words; i += blockDim.x) s_mask[i] = a.vis_mask[i];
+  __syncthreads();
   // CTA -> pixel block.  Blocks are enumerated inside partition tiles so a rank only launches its own.
   const int per_tile_x = a.tile / CTA_W, per_tile = per_tile_x * (a.tile / CTA_H);
   const int local_tile = blockIdx.x / per_tile, sub = blockIdx.x % per_tile;
@@ -78,38 +107,59 @@ __global__ void __launch_bounds__(CTA_W* CTA_H) rc1pass_kernel(const __grid_cons
     const float dux = dir.x * a.inv_grid[0], duy = dir.y * a.inv_grid[1], duz = dir.z * a.inv_grid[2];
     const float step = a.step;
     const float k_l2e = -1.4426950408889634f;
-    for (float s = 0.0f; s < D;) {
-      const float h = fminf(step, __fsub_rn(D, s));
-      const float t = fmaf(h, 0.5f, s);
-      const float density = tex3D<float>(a.vol, fmaf(dux, t, ux0), fmaf(duy, t, uy0), fmaf(duz, t, uz0));
-      float4 src;
-      if (TF_SMEM) {
-        // GL_LINEAR, CLAMP_TO_EDGE on n texels: u' = density*n - 0.5
-        float u = fmaf(density, (float)a.tf_n, -0.5f);
-        u = fminf(fmaxf(u, 0.0f), (float)(a.tf_n - 1));
-        const int i0 = (int)u;
-        const float w = u - (float)i0;
-        const uint4 e = s_tf[i0];
-        const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x));
-        const float2 b0 = __half22float2(*reinterpret_cast<const __half2*>(&e.y));
-        const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z));
-        const float2 b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
-        src.x = fmaf(w, r1.x - r0.x, r0.x); src.y = fmaf(w, r1.y - r0.y, r0.y);
-        src.z = fmaf(w, b1.x - b0.x, b0.x); src.w = fmaf(w, b1.y - b0.y, b0.y);
-      } else {
-        src = tex1D<float4>(a.tf, density);
+    const float tfn = (float)a.tf_n, tfmax = (float)(a.tf_n - 1);
+    float s = 0.0f;
+    bool done = false;
+    while (s < D && !done) {
+      // issue UNROLL lattice samples (s_k = s_{k-1} + h_{k-1}, exactly the reference's accumulation)
+      float hk[UNROLL], tk[UNROLL], dk[UNROLL];
+      float ss = s;
+#pragma unroll
+      for (int k = 0; k < UNROLL; k++) {
+        hk[k] = fminf(step, __fsub_rn(D, ss));            // <= 0 marks a slot past the end of the ray
+        tk[k] = fmaf(hk[k], 0.5f, ss);
+        dk[k] = tex3D<float>(a.vol, fmaf(dux, tk[k], ux0), fmaf(duy, tk[k], uy0), fmaf(duz, tk[k], uz0));
+        ss = __fadd_rn(ss, fmaxf(hk[k], 0.0f));
       }
-      if (COUNT) nsamp++;
-      if (src.w > 0.0f) {
-        const float alpha = 1.0f - ex2_approx(src.w * h * k_l2e);   // 1 - exp(-tau*h) via MUFU.EX2
-        const float wgt = (1.0f - dst.w) * alpha;
-        dst.x = fmaf(wgt, src.x, dst.x);
-        dst.y = fmaf(wgt, src.y, dst.y);
-        dst.z = fmaf(wgt, src.z, dst.z);
-        dst.w += wgt;
-        if (dst.w > 0.99f) break;
+#pragma unroll
+      for (int k = 0; k < UNROLL; k++) {
+        if (done || !(hk[k] > 0.0f)) continue;           // (no break: keeps the slot arrays in registers)
+        if (COUNT) nsamp++;
+        float density = dk[k];
+        float u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
+        int j = (int)u;
+        if ((s_mask[j >> 5] >> (j & 31)) & 1u) {
+          if (EXACT) {
+            density = tex3d_exact(a.vol_pt, fmaf(dux, tk[k], ux0), fmaf(duy, tk[k], uy0), fmaf(duz, tk[k], uz0), a.res);
+            u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
+            j = (int)u;
+          }
+          float4 src;
+          if (TF_SMEM) {
+            // GL_LINEAR, CLAMP_TO_EDGE on n texels with float32 weights
+            const float w = u - (float)j;
+            const uint4 e = s_tf[j];
+            const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x));
+            const float2 b0 = __half22float2(*reinterpret_cast<const __half2*>(&e.y));
+            const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z));
+            const float2 b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
+            src.x = fmaf(w, r1.x - r0.x, r0.x); src.y = fmaf(w, r1.y - r0.y, r0.y);
+            src.z = fmaf(w, b1.x - b0.x, b0.x); src.w = fmaf(w, b1.y - b0.y, b0.y);
+          } else {
+            src = tex1D<float4>(a.tf, density);
+          }
+          if (src.w > 0.0f) {
+            const float alpha = 1.0f - ex2_approx(src.w * hk[k] * k_l2e);   // 1 - exp(-tau*h) via MUFU.EX2
+            const float wgt = (1.0f - dst.w) * alpha;
+            dst.x = fmaf(wgt, src.x, dst.x);
+            dst.y = fmaf(wgt, src.y, dst.y);
+            dst.z = fmaf(wgt, src.z, dst.z);
+            dst.w += wgt;
+            if (dst.w > 0.99f) done = true;
+          }
+        }
       }
-      s = __fadd_rn(s, h);
+      s = ss;
     }
   }
   // imageStore(OutputFrag, storePos, dst) — or the cleared 0 where the ray misses (ClearTexture fused)
@@ -120,7 +170,6 @@ __global__ void __launch_bounds__(CTA_W* CTA_H) rc1pass_kernel(const __grid_cons
   }
 }
 
-
 // ---------------------------------------------------------------------------------------------
 // Host driver: RayCasting1Pass (rc1prenderer.cpp).
 class Rc1Pass : public RendererImpl {
@@ -128,7 +177,7 @@ class Rc1Pass : public RendererImpl {
   explicit Rc1Pass(vrb_ctx* c) : RendererImpl(c, VRB_RC1PASS) {
     prm_.step_size = 0.5f;               // m_u_step_size(0.5f)            rc1prenderer.cpp:21
     prm_.apply_gradient_shading = 0;     // m_apply_gradient_shading(false) rc1prenderer.cpp:22
-    prm_.skip_block = 0; prm_.count_samples = 0; prm_.tf_in_smem = 0;
+    prm_.skip_block = 0; prm_.count_samples = 0; prm_.tf_in_smem = 1; prm_.exact_filter = 1;
   }
 
   // Init (rc1prenderer.cpp:50-70): requires a volume texture, takes the RGBt transfer-function texture,
@@ -166,7 +215,9 @@ class Rc1Pass : public RendererImpl {
     VRB_REQUIRE(built && have_cam, VRB_ERR_INVALID, "RayCasting1Pass::Redraw before Init/Update");
     const Volume& v = ctx->vol;
     Rc1Args a{};
-    a.vol = v.tex; a.tf = ctx->tf.tex_rgbt; a.tf_lin = (const uint2*)ctx->tf.lin_rgbt; a.tf_n = ctx->tf.n;
+    a.vol = v.tex; a.vol_pt = v.tex_pt; a.tf = ctx->tf.tex_rgbt; a.vis_mask = ctx->tf.vis_mask; a.vis_words = ctx->tf.vis_words;
+    a.res[0] = (float)v.w; a.res[1] = (float)v.h; a.res[2] = (float)v.d;
+    a.tf_lin = (const uint2*)ctx->tf.lin_rgbt; a.tf_n = ctx->tf.n;
     a.width = width; a.height = height;
     // CreateRenderingPass (rc1prenderer.cpp:233-241): vol_aabb = vec3(resolution) * vec3(voxel size)
     a.grid[0] = (float)v.w * v.sx; a.grid[1] = (float)v.h * v.sy; a.grid[2] = (float)v.d * v.sz;
@@ -181,17 +232,22 @@ class Rc1Pass : public RendererImpl {
     const int per_tile = (part_tile / CTA_W) * (part_tile / CTA_H);
     const int grid = my_tiles * per_tile;
     if (grid <= 0) return VRB_OK;
-    const size_t smem = prm_.tf_in_smem ? (size_t)a.tf_n * sizeof(uint4) : 0;
+    const size_t smem = (prm_.tf_in_smem ? (size_t)a.tf_n * sizeof(uint4) : 0) + (size_t)a.vis_words * sizeof(uint32_t);
     VRB_REQUIRE(smem <= 200 * 1024, VRB_ERR_UNSUPPORTED, "tf_in_smem: table of %d entries does not fit shared memory", a.tf_n);
     cudaStream_t s = ctx->stream;
     if (prm_.count_samples) VRB_CUDA(cudaMemsetAsync(d_samples, 0, sizeof(unsigned long long), s));
-#define LAUNCH(C, T)                                                                                      \
+#define LAUNCH(C, T, E)                                                                                   \
   do {                                                                                                    \
-    if (smem > 48 * 1024) VRB_CUDA(cudaFuncSetAttribute(rc1pass_kernel<C, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    rc1pass_kernel<C, T><<<grid, CTA_W * CTA_H, smem, s>>>(a);                                            \
+    if (smem > 48 * 1024) VRB_CUDA(cudaFuncSetAttribute(rc1pass_kernel<C, T, E>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    rc1pass_kernel<C, T, E><<<grid, CTA_W * CTA_H, smem, s>>>(a);                                         \
   } while (0)
-    if (prm_.count_samples) { if (prm_.tf_in_smem) LAUNCH(true, true); else LAUNCH(true, false); }
-    else                    { if (prm_.tf_in_smem) LAUNCH(false, true); else LAUNCH(false, false); }
+#define LAUNCH_TE(C)                                                                     \
+  do {                                                                                   \
+    if (prm_.tf_in_smem) { if (prm_.exact_filter) LAUNCH(C, true, true); else LAUNCH(C, true, false); }   \
+    else                 { if (prm_.exact_filter) LAUNCH(C, false, true); else LAUNCH(C, false, false); } \
+  } while (0)
+    if (prm_.count_samples) LAUNCH_TE(true); else LAUNCH_TE(false);
+#undef LAUNCH_TE
 #undef LAUNCH
     VRB_CUDA(cudaGetLastError());
     return VRB_OK;

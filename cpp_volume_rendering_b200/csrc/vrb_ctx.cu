@@ -2,6 +2,7 @@
 #include "vrb_internal.cuh"
 #include <vector>
 #include <cmath>
+#include <algorithm>
 
 namespace vrb {
 
@@ -50,6 +51,7 @@ __global__ void read_r16f_kernel(cudaSurfaceObject_t surf, float* out, int w, in
 
 static void release_volume(Volume& v) {
   if (v.tex) cudaDestroyTextureObject(v.tex);
+  if (v.tex_pt) cudaDestroyTextureObject(v.tex_pt);
   if (v.surf) cudaDestroySurfaceObject(v.surf);
   if (v.array) cudaFreeArray(v.array);
   if (v.raw) cudaFree(v.raw);
@@ -66,6 +68,7 @@ static void release_tf(TransferFunction& t) {
   if (t.lin_rgbt) cudaFree(t.lin_rgbt);
   if (t.lin_rgba) cudaFree(t.lin_rgba);
   if (t.table) cudaFree(t.table);
+  if (t.vis_mask) cudaFree(t.vis_mask);
   uint64_t g = t.generation;
   t = TransferFunction();
   t.generation = g;
@@ -84,6 +87,10 @@ static int build_volume_texture(vrb_ctx* ctx) {
   td.readMode = cudaReadModeElementType;
   td.normalizedCoords = 1;
   VRB_CUDA(cudaCreateTextureObject(&v.tex, &rd, &td, nullptr));
+  cudaTextureDesc tp = td;
+  tp.filterMode = cudaFilterModePoint;
+  tp.normalizedCoords = 0;
+  VRB_CUDA(cudaCreateTextureObject(&v.tex_pt, &rd, &tp, nullptr));
 
   dim3 blk(32, 8, 1), grd((unsigned)((v.w + 127) / 128), (unsigned)((v.h + 7) / 8), (unsigned)v.d);
   if (v.dtype == VRB_U8)
@@ -241,6 +248,26 @@ int vrb_tf_upload(vrb_ctx* ctx, const double* table, int n, int extinction_type)
   }
   VRB_CUDA(cudaMalloc(&t.table, (size_t)n * 4 * sizeof(double)));
   VRB_CUDA(cudaMemcpyAsync(t.table, table, (size_t)n * 4 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  // Conservative visibility mask for the hardware-filtered classification fetch (k_rc1pass.cu): the texture
+  // unit filters with 1.8 fixed-point weights, so its density can be off by up to 3/512 of the local value
+  // range (<= 3/512 in normalised density) from the float32 filter.  Cell j = clamp(floor(d*n - 0.5)) is marked
+  // visible when any RGBt alpha within +-rad cells is > 0 (or NaN), rad = ceil(n * 4/512) + 1.
+  {
+    const int rad = (n * 4 + 511) / 512 + 1;
+    t.vis_words = (n + 31) / 32;
+    std::vector<uint32_t> mask((size_t)t.vis_words, 0u);
+    for (int j = 0; j < n; j++) {
+      bool vis = false;
+      for (int k = std::max(0, j - rad); k <= std::min(n - 1, j + 1 + rad) && !vis; k++) {
+        const float a = __half2float(rgbt[4 * k + 3]);
+        vis = !(a <= 0.0f);
+      }
+      if (vis) mask[j >> 5] |= 1u << (j & 31);
+    }
+    VRB_CUDA(cudaMalloc(&t.vis_mask, mask.size() * sizeof(uint32_t)));
+    VRB_CUDA(cudaMemcpyAsync(t.vis_mask, mask.data(), mask.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    VRB_CUDA(cudaStreamSynchronize(ctx->stream));
+  }
   VRB_CUDA(cudaStreamSynchronize(ctx->stream));  // host vectors go out of scope
   t.generation++;
   return VRB_OK;

@@ -38,6 +38,7 @@ struct Volume {
   void* raw = nullptr;                  // device copy of the voxel array (x fastest)
   cudaArray_t array = nullptr;          // half, 1 channel
   cudaTextureObject_t tex = 0;          // linear, clamp, normalised
+  cudaTextureObject_t tex_pt = 0;       // point, clamp, unnormalised (exact software filtering path)
   cudaSurfaceObject_t surf = 0;
   uint64_t generation = 0;
   size_t voxel_bytes() const { return dtype == VRB_U8 ? 1 : (dtype == VRB_U16 ? 2 : 4); }
@@ -52,6 +53,8 @@ struct TransferFunction {
   __half* lin_rgbt = nullptr;           // linear device copies (n*4 halfs) for smem tables / classification
   __half* lin_rgba = nullptr;
   double* table = nullptr;              // device copy of the double table (n*4), for GetExtN-style precompute
+  uint32_t* vis_mask = nullptr;         // bit j: a sample whose hardware-filtered density maps to TF cell j may have alpha > 0
+  int vis_words = 0;
   uint64_t generation = 0;
 };
 

@@ -79,7 +79,9 @@ typedef struct {
   int   apply_gradient_shading;  /* m_apply_gradient_shading (needs a gradient volume) */
   int   skip_block;              /* 0 = reference march; 4/8/16/32 = lattice-preserving empty-space skipping block edge */
   int   count_samples;           /* 1 = instrumented kernel that counts march-loop iterations (debug/metric) */
-  int   tf_in_smem;              /* 0 = TF through a 1D texture object (reference semantics); 1 = shared-memory table */
+  int   tf_in_smem;              /* 1 (default) = TF in shared memory, float32 lerp; 0 = TF through the RGBA16F 1D texture unit */
+  int   exact_filter;            /* 1 (default) = possibly-visible samples are re-filtered with float32 weights;
+                                    0 = every sample uses the texture unit's 1.8 fixed-point trilinear filter */
 } vrb_rc1pass_params;
 
 /* ---- library / context ------------------------------------------------------------------- */

@@ -33,10 +33,10 @@ def test_abi_version_and_error_string():
 
 
 def test_struct_sizes_match_header():
-    # vrb_camera: 3+9+1+1 floats; vrb_light: 4+3+3 floats; vrb_rc1pass_params: float + 4 ints
+    # vrb_camera: 3+9+1+1 floats; vrb_light: 4+3+3 floats; vrb_rc1pass_params: float + 5 ints
     assert ctypes.sizeof(_capi.Camera) == 14 * 4
     assert ctypes.sizeof(_capi.Light) == 10 * 4
-    assert ctypes.sizeof(_capi.Rc1PassParams) == 5 * 4
+    assert ctypes.sizeof(_capi.Rc1PassParams) == 6 * 4
 
 
 def test_null_arguments_are_errors_not_crashes():

@@ -89,7 +89,7 @@ CASES = [
 
 
 @pytest.mark.parametrize("n,dtype,size,eye_s,up,step", CASES)
-@pytest.mark.parametrize("tf_in_smem", [0, 1])
+@pytest.mark.parametrize("tf_in_smem", [1, 0])
 def test_rc1pass_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, up, step, tf_in_smem):
     w, h = size
     vox = inputs.synth_volume(n, dtype)
@@ -106,6 +106,23 @@ def test_rc1pass_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, up, step
     _check_images(got, got8, ref, f"n={n} {np.dtype(dtype).name} {w}x{h}")
     # the sample lattice is bit-identical; only ERT near-ties (dst.a ~ 0.99) may move a ray's last sample
     assert abs(samples - total) <= 2e-3 * total, (samples, total)
+
+
+def test_hardware_filter_mode_is_close_but_not_the_parity_path(ctx, bonsai_table):
+    """exact_filter=0 leaves every sample to the texture unit's 1.8 fixed-point weights (what a GL driver on the
+    same hardware does).  It keeps SSIM but exceeds 2/255 at a few pixels on the sharp bonsai TF edge, which is why
+    the default path re-filters possibly-visible samples in float32."""
+    n, w, h = 64, 128, 128
+    vox = inputs.synth_volume(n, np.uint8)
+    ctx.upload_volume(vox)
+    ctx.upload_tf(bonsai_table)
+    cam = inputs.default_camera(n, w, h)
+    got, got8, _, samples, prm = _render_gpu(ctx, cam, w, h, exact_filter=0, count_samples=1)
+    ref, total, _ = O.rc1pass_render(O.rc1pass_params(cam, w, h, vox.shape, prm.step_size), O.volume_r16f(vox), O.tf_texture(bonsai_table))
+    ref8 = O.blit_over_white(ref)
+    assert metrics.ssim(got8, ref8) >= SSIM_MIN
+    assert float(np.abs(got - ref).max()) * 255.0 <= 16.0
+    assert abs(samples - total) <= 5e-3 * total
 
 
 def test_default_step_follows_init(ctx, bonsai_table):
