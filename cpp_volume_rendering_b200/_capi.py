@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvrb200.so")
+LIB_PATH = os.environ.get("VRB200_LIB") or os.path.join(_HERE, "libvrb200.so")  # override: tuning experiments only
 
 VRB_U8, VRB_U16, VRB_F32 = 0, 1, 2
 (VRB_RC1PASS, VRB_ISO_ADAPT, VRB_ISO_SKIP_V1, VRB_ISO_SKIP_V2, VRB_DOS_CONE, VRB_EBS_SAT, VRB_VCT,

@@ -3,12 +3,15 @@
 //
 // Mapping: one ray per thread; a warp covers an 8x4 pixel footprint (better 3D-texture locality and
 // ERT coherence than a 32x1 row), a CTA is 4 warps = 16x8 pixels.  Rays inside a warp terminate
-// independently (the loop exits per lane; the warp retires when its last lane does).
-// Per sample: one trilinear R16F tex3D, one TF lookup (1D texture, or a shared-memory table with a
-// software lerp), one ex2.approx, ~12 FMAs.  The frame is written as 8-byte RGBA16F texels; a row of a
-// warp footprint is 64 contiguous bytes.
+// independently (the loop exits per lane; the warp retires when its last lane does).  CTAs visit the
+// image in a scrambled order so that long and short rays are mixed over the whole launch.
+// Per sample: one hardware trilinear R16F tex3D used for CLASSIFICATION, then — only for samples the
+// transfer function may make visible — a float32 re-filter (8 point fetches), a shared-memory TF lookup
+// with float32 lerp, one MUFU.EX2 and the front-to-back blend.  The frame is written as 8-byte RGBA16F
+// texels; a row of a warp footprint is 64 contiguous bytes.
 #include "vrb_internal.cuh"
 #include "vrb_ray.cuh"
+#include "vrb_skipmap.cuh"
 
 namespace vrb {
 
@@ -21,6 +24,7 @@ struct Rc1Args {
   float res[3];              // VolumeGridResolution
   float grid[3];             // VolumeGridSize
   float inv_grid[3];
+  float inv_voxel[3];
   float eye[3];
   float lookat[9];
   float tan_fovy, aspect, step;
@@ -28,11 +32,16 @@ struct Rc1Args {
   unsigned long long* samples;
   // image-space partition: tiles of `tile` pixels dealt round-robin over ranks
   int rank, n_ranks, tile, tiles_x, n_tiles;
-  // empty-space skipping (0 = off): block edge in voxels, grid of blocks, u8 "empty run length" map
-  int skip_block; int bx, by, bz; const uint8_t* skip_map;
+  int grid_blocks; unsigned scramble;   // CTA order: logical block = (blockIdx * scramble) % grid_blocks
+  // empty-space skipping: block edge in voxels, grid of blocks, Chebyshev run map (k_skipmap.cu)
+  int skip_block; int nbx, nby, nbz; const uint8_t* skip_map;
 };
 
 constexpr int CTA_W = 16, CTA_H = 8;
+#ifndef VRB_RC1_MINB
+#define VRB_RC1_MINB 8      // resident CTAs per SM the register allocation is capped for (8 -> 64 registers;
+                            // measured on B200: 0.67 ms vs 0.74 ms per C2 frame against a 40-register cap)
+#endif
 constexpr int UNROLL = 4;    // independent texture fetches in flight per ray
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -57,13 +66,53 @@ __device__ __noinline__ float tex3d_exact(cudaTextureObject_t pt, float ux, floa
   return fmaf(az, c1 - c0, c0);
 }
 
-// The march.  Every sample issues ONE hardware-filtered trilinear fetch.  Its density is only used to
-// classify the sample against the conservative visibility mask; samples that may be non-transparent
-// (a few per cent of the lattice for a typical TF) are re-evaluated with float32 filter weights when
-// EXACT is set, so the image matches the float32 evaluation of the shader while the empty space runs at
-// texture-unit rate.  UNROLL fetches are issued back to back before any is consumed.
-template <bool COUNT, bool TF_SMEM, bool EXACT>
-__global__ void __launch_bounds__(CTA_W* CTA_H, 12) rc1pass_kernel(const __grid_constant__ Rc1Args a) {
+struct RayState {
+  float ux0, uy0, uz0, dux, duy, duz;   // normalised texture coordinate = u0 + du * t
+  float4 dst;
+  bool done;
+};
+
+// ray_marching_1p.comp:133-168 for one lattice sample whose hardware-filtered density is d_hw.
+template <bool TF_SMEM, bool EXACT>
+__device__ __forceinline__ void shade_sample(const Rc1Args& a, const uint4* s_tf, const uint32_t* s_mask, RayState& r,
+                                             float d_hw, float t, float h) {
+  const float tfn = (float)a.tf_n, tfmax = (float)(a.tf_n - 1);
+  float density = d_hw;
+  float u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
+  int j = (int)u;
+  if (!((s_mask[j >> 5] >> (j & 31)) & 1u)) return;       // provably transparent: src.a <= 0 (:142)
+  if (EXACT) {
+    density = tex3d_exact(a.vol_pt, fmaf(r.dux, t, r.ux0), fmaf(r.duy, t, r.uy0), fmaf(r.duz, t, r.uz0), a.res);
+    u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
+    j = (int)u;
+  }
+  float4 src;
+  if (TF_SMEM) {
+    // GL_LINEAR, CLAMP_TO_EDGE on n texels with float32 weights
+    const float w = u - (float)j;
+    const uint4 e = s_tf[j];
+    const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x));
+    const float2 b0 = __half22float2(*reinterpret_cast<const __half2*>(&e.y));
+    const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z));
+    const float2 b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
+    src.x = fmaf(w, r1.x - r0.x, r0.x); src.y = fmaf(w, r1.y - r0.y, r0.y);
+    src.z = fmaf(w, b1.x - b0.x, b0.x); src.w = fmaf(w, b1.y - b0.y, b0.y);
+  } else {
+    src = tex1D<float4>(a.tf, density);
+  }
+  if (src.w > 0.0f) {
+    const float alpha = 1.0f - ex2_approx(src.w * h * -1.4426950408889634f);   // 1 - exp(-tau*h) via MUFU.EX2
+    const float wgt = (1.0f - r.dst.w) * alpha;
+    r.dst.x = fmaf(wgt, src.x, r.dst.x);
+    r.dst.y = fmaf(wgt, src.y, r.dst.y);
+    r.dst.z = fmaf(wgt, src.z, r.dst.z);
+    r.dst.w += wgt;
+    if (r.dst.w > 0.99f) r.done = true;                     // early ray termination (:167)
+  }
+}
+
+template <bool COUNT, bool TF_SMEM, bool EXACT, bool SKIP>
+__global__ void __launch_bounds__(CTA_W* CTA_H, VRB_RC1_MINB) rc1pass_kernel(const __grid_constant__ Rc1Args a) {
   extern __shared__ uint4 s_dyn[];
   uint4* s_tf = s_dyn;                                   // TF_SMEM: entry i = {texel i, texel min(i+1,n-1)}
   uint32_t* s_mask = reinterpret_cast<uint32_t*>(s_dyn + (TF_SMEM ? a.tf_n : 0));
@@ -76,8 +125,9 @@ __global__ void __launch_bounds__(CTA_W* CTA_H, 12) rc1pass_kernel(const __grid_
   for (int i = threadIdx.x; i < a.vis_words; i += blockDim.x) s_mask[i] = a.vis_mask[i];
   __syncthreads();
   // CTA -> pixel block.  Blocks are enumerated inside partition tiles so a rank only launches its own.
+  const int lb = (int)(((unsigned long long)blockIdx.x * a.scramble) % (unsigned)a.grid_blocks);
   const int per_tile_x = a.tile / CTA_W, per_tile = per_tile_x * (a.tile / CTA_H);
-  const int local_tile = blockIdx.x / per_tile, sub = blockIdx.x % per_tile;
+  const int local_tile = lb / per_tile, sub = lb % per_tile;
   const int tile_id = a.rank + local_tile * a.n_ranks;
   if (tile_id >= a.n_tiles) return;
   const int tx = tile_id % a.tiles_x, ty = tile_id / a.tiles_x;
@@ -94,7 +144,9 @@ __global__ void __launch_bounds__(CTA_W* CTA_H, 12) rc1pass_kernel(const __grid_
   f3 dir; float tnear, tfar;
   const bool hit = ray_aabb(eye, cdir, bmin, bmax, dir, tnear, tfar) && valid;
 
-  float4 dst = make_float4(0.f, 0.f, 0.f, 0.f);
+  RayState r;
+  r.dst = make_float4(0.f, 0.f, 0.f, 0.f);
+  r.done = false;
   unsigned nsamp = 0;
   if (hit) {
     const float D = fabsf(__fsub_rn(tfar, tnear));
@@ -103,67 +155,83 @@ __global__ void __launch_bounds__(CTA_W* CTA_H, 12) rc1pass_kernel(const __grid_
     const float tpy = __fadd_rn(__fadd_rn(eye.y, __fmul_rn(dir.y, tnear)), bmax.y);
     const float tpz = __fadd_rn(__fadd_rn(eye.z, __fmul_rn(dir.z, tnear)), bmax.z);
     // normalised texture coordinate = (tex_pos + dir*t) / grid, folded into one FMA per axis
-    const float ux0 = tpx * a.inv_grid[0], uy0 = tpy * a.inv_grid[1], uz0 = tpz * a.inv_grid[2];
-    const float dux = dir.x * a.inv_grid[0], duy = dir.y * a.inv_grid[1], duz = dir.z * a.inv_grid[2];
+    r.ux0 = tpx * a.inv_grid[0]; r.uy0 = tpy * a.inv_grid[1]; r.uz0 = tpz * a.inv_grid[2];
+    r.dux = dir.x * a.inv_grid[0]; r.duy = dir.y * a.inv_grid[1]; r.duz = dir.z * a.inv_grid[2];
     const float step = a.step;
-    const float k_l2e = -1.4426950408889634f;
-    const float tfn = (float)a.tf_n, tfmax = (float)(a.tf_n - 1);
-    float s = 0.0f;
-    bool done = false;
-    while (s < D && !done) {
-      // issue UNROLL lattice samples (s_k = s_{k-1} + h_{k-1}, exactly the reference's accumulation)
-      float hk[UNROLL], tk[UNROLL], dk[UNROLL];
-      float ss = s;
+    if (!SKIP) {
+      float s = 0.0f;
+      while (s < D && !r.done) {
+        // issue UNROLL lattice samples (s_k = s_{k-1} + h_{k-1}, exactly the reference's accumulation)
+        float hk[UNROLL], tk[UNROLL], dk[UNROLL];
+        float ss = s;
 #pragma unroll
-      for (int k = 0; k < UNROLL; k++) {
-        hk[k] = fminf(step, __fsub_rn(D, ss));            // <= 0 marks a slot past the end of the ray
-        tk[k] = fmaf(hk[k], 0.5f, ss);
-        dk[k] = tex3D<float>(a.vol, fmaf(dux, tk[k], ux0), fmaf(duy, tk[k], uy0), fmaf(duz, tk[k], uz0));
-        ss = __fadd_rn(ss, fmaxf(hk[k], 0.0f));
-      }
-#pragma unroll
-      for (int k = 0; k < UNROLL; k++) {
-        if (done || !(hk[k] > 0.0f)) continue;           // (no break: keeps the slot arrays in registers)
-        if (COUNT) nsamp++;
-        float density = dk[k];
-        float u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
-        int j = (int)u;
-        if ((s_mask[j >> 5] >> (j & 31)) & 1u) {
-          if (EXACT) {
-            density = tex3d_exact(a.vol_pt, fmaf(dux, tk[k], ux0), fmaf(duy, tk[k], uy0), fmaf(duz, tk[k], uz0), a.res);
-            u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
-            j = (int)u;
-          }
-          float4 src;
-          if (TF_SMEM) {
-            // GL_LINEAR, CLAMP_TO_EDGE on n texels with float32 weights
-            const float w = u - (float)j;
-            const uint4 e = s_tf[j];
-            const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x));
-            const float2 b0 = __half22float2(*reinterpret_cast<const __half2*>(&e.y));
-            const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z));
-            const float2 b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
-            src.x = fmaf(w, r1.x - r0.x, r0.x); src.y = fmaf(w, r1.y - r0.y, r0.y);
-            src.z = fmaf(w, b1.x - b0.x, b0.x); src.w = fmaf(w, b1.y - b0.y, b0.y);
-          } else {
-            src = tex1D<float4>(a.tf, density);
-          }
-          if (src.w > 0.0f) {
-            const float alpha = 1.0f - ex2_approx(src.w * hk[k] * k_l2e);   // 1 - exp(-tau*h) via MUFU.EX2
-            const float wgt = (1.0f - dst.w) * alpha;
-            dst.x = fmaf(wgt, src.x, dst.x);
-            dst.y = fmaf(wgt, src.y, dst.y);
-            dst.z = fmaf(wgt, src.z, dst.z);
-            dst.w += wgt;
-            if (dst.w > 0.99f) done = true;
-          }
+        for (int k = 0; k < UNROLL; k++) {
+          hk[k] = fminf(step, __fsub_rn(D, ss));            // <= 0 marks a slot past the end of the ray
+          tk[k] = fmaf(hk[k], 0.5f, ss);
+          dk[k] = tex3D<float>(a.vol, fmaf(r.dux, tk[k], r.ux0), fmaf(r.duy, tk[k], r.uy0), fmaf(r.duz, tk[k], r.uz0));
+          ss = __fadd_rn(ss, fmaxf(hk[k], 0.0f));
         }
+#pragma unroll
+        for (int k = 0; k < UNROLL; k++) {
+          if (r.done || !(hk[k] > 0.0f)) continue;         // (no break: keeps the slot arrays in registers)
+          if (COUNT) nsamp++;
+          shade_sample<TF_SMEM, EXACT>(a, s_tf, s_mask, r, dk[k], tk[k], hk[k]);
+        }
+        s = ss;
       }
-      s = ss;
+    } else {
+      // Lattice-preserving empty-space skipping: sample k sits at s_k = k*step (identical to the accumulated
+      // lattice for dyadic steps such as the default 0.5).  Before each group of UNROLL samples the block under
+      // the first one is looked up; if the (2r-1)^3 cube of blocks around it is empty the ray leaps to the
+      // first lattice sample whose midpoint lies beyond the cube.  Samples that are skipped would have had
+      // src.a <= 0 (block range incl. the trilinear apron maps to zero extinction), so the image is unchanged.
+      const float pvx0 = tpx * a.inv_voxel[0], pvy0 = tpy * a.inv_voxel[1], pvz0 = tpz * a.inv_voxel[2];
+      const float dvx = dir.x * a.inv_voxel[0], dvy = dir.y * a.inv_voxel[1], dvz = dir.z * a.inv_voxel[2];
+      const float idx_ = 1.0f / dvx, idy_ = 1.0f / dvy, idz_ = 1.0f / dvz;   // +-inf where the ray is axis-parallel
+      const float fB = (float)a.skip_block, invB = 1.0f / fB, inv_step = 1.0f / step;
+      int k = 0;
+      while (!r.done) {
+        const float s = (float)k * step;
+        if (!(s < D)) break;
+        const float h0 = fminf(step, D - s), t0 = fmaf(h0, 0.5f, s);
+        const int bx = min(max((int)floorf(fmaf(dvx, t0, pvx0) * invB), 0), a.nbx - 1);
+        const int by = min(max((int)floorf(fmaf(dvy, t0, pvy0) * invB), 0), a.nby - 1);
+        const int bz = min(max((int)floorf(fmaf(dvz, t0, pvz0) * invB), 0), a.nbz - 1);
+        const int run = a.skip_map[(size_t)bx + (size_t)a.nbx * ((size_t)by + (size_t)a.nby * bz)];
+        if (run > 0) {
+          // exit of the empty cube [b-(run-1), b+run) * B along the ray
+          const float ex = ((dvx > 0.0f ? (float)(bx + run) : (float)(bx - run + 1)) * fB - pvx0) * idx_;
+          const float ey = ((dvy > 0.0f ? (float)(by + run) : (float)(by - run + 1)) * fB - pvy0) * idy_;
+          const float ez = ((dvz > 0.0f ? (float)(bz + run) : (float)(bz - run + 1)) * fB - pvz0) * idz_;
+          float te = D;
+          if (dvx != 0.0f) te = fminf(te, ex);
+          if (dvy != 0.0f) te = fminf(te, ey);
+          if (dvz != 0.0f) te = fminf(te, ez);
+          // first k' with midpoint (k'+0.5)*step >= te
+          const int kn = (int)ceilf(fmaf(te, inv_step, -0.5f));
+          k = max(kn, k + 1);
+          continue;
+        }
+        float hk[UNROLL], tk[UNROLL], dk[UNROLL];
+#pragma unroll
+        for (int q = 0; q < UNROLL; q++) {
+          const float sq = (float)(k + q) * step;
+          hk[q] = fminf(step, D - sq);
+          tk[q] = fmaf(hk[q], 0.5f, sq);
+          dk[q] = tex3D<float>(a.vol, fmaf(r.dux, tk[q], r.ux0), fmaf(r.duy, tk[q], r.uy0), fmaf(r.duz, tk[q], r.uz0));
+        }
+#pragma unroll
+        for (int q = 0; q < UNROLL; q++) {
+          if (r.done || !(hk[q] > 0.0f)) continue;
+          if (COUNT) nsamp++;
+          shade_sample<TF_SMEM, EXACT>(a, s_tf, s_mask, r, dk[q], tk[q], hk[q]);
+        }
+        k += UNROLL;
+      }
     }
   }
   // imageStore(OutputFrag, storePos, dst) — or the cleared 0 where the ray misses (ClearTexture fused)
-  if (valid) a.frame[(size_t)py * a.width + px] = make_uint2(pack_half2(dst.x, dst.y), pack_half2(dst.z, dst.w));
+  if (valid) a.frame[(size_t)py * a.width + px] = make_uint2(pack_half2(r.dst.x, r.dst.y), pack_half2(r.dst.z, r.dst.w));
   if (COUNT) {
     for (int o = 16; o > 0; o >>= 1) nsamp += __shfl_xor_sync(0xffffffffu, nsamp, o);
     if (lane == 0 && nsamp) atomicAdd(a.samples, (unsigned long long)nsamp);
@@ -194,6 +262,8 @@ class Rc1Pass : public RendererImpl {
     return VRB_OK;
   }
 
+  void clean() override { skip_.release(); }
+
   int set_params(const void* pod, size_t size) override {
     VRB_REQUIRE(pod && size == sizeof(vrb_rc1pass_params), VRB_ERR_INVALID,
                 "RayCasting1Pass::set_params: size %zu != sizeof(vrb_rc1pass_params) %zu", size, sizeof(vrb_rc1pass_params));
@@ -221,6 +291,7 @@ class Rc1Pass : public RendererImpl {
     a.width = width; a.height = height;
     // CreateRenderingPass (rc1prenderer.cpp:233-241): vol_aabb = vec3(resolution) * vec3(voxel size)
     a.grid[0] = (float)v.w * v.sx; a.grid[1] = (float)v.h * v.sy; a.grid[2] = (float)v.d * v.sz;
+    a.inv_voxel[0] = 1.0f / v.sx; a.inv_voxel[1] = 1.0f / v.sy; a.inv_voxel[2] = 1.0f / v.sz;
     for (int i = 0; i < 3; i++) { a.inv_grid[i] = 1.0f / a.grid[i]; a.eye[i] = cam.eye[i]; }
     for (int i = 0; i < 9; i++) a.lookat[i] = cam.lookat[i];
     a.tan_fovy = cam.tan_fovy; a.aspect = cam.aspect; a.step = prm_.step_size;
@@ -232,29 +303,41 @@ class Rc1Pass : public RendererImpl {
     const int per_tile = (part_tile / CTA_W) * (part_tile / CTA_H);
     const int grid = my_tiles * per_tile;
     if (grid <= 0) return VRB_OK;
+    // scrambled CTA order: multiply by an odd constant near grid/golden-ratio that is coprime to grid
+    a.grid_blocks = grid;
+    unsigned sc = (unsigned)(grid * 0.6180339887) | 1u;
+    auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned t = x % y; x = y; y = t; } return x; };
+    while (gcd(sc, (unsigned)grid) != 1u) sc += 2;
+    a.scramble = grid > 2 ? sc : 1u;
+    if (prm_.skip_block) {
+      int rc = skip_.ensure(ctx, prm_.skip_block);
+      if (rc != VRB_OK) return rc;
+      a.skip_block = skip_.B; a.nbx = skip_.nbx; a.nby = skip_.nby; a.nbz = skip_.nbz; a.skip_map = skip_.dist;
+    }
     const size_t smem = (prm_.tf_in_smem ? (size_t)a.tf_n * sizeof(uint4) : 0) + (size_t)a.vis_words * sizeof(uint32_t);
     VRB_REQUIRE(smem <= 200 * 1024, VRB_ERR_UNSUPPORTED, "tf_in_smem: table of %d entries does not fit shared memory", a.tf_n);
     cudaStream_t s = ctx->stream;
     if (prm_.count_samples) VRB_CUDA(cudaMemsetAsync(d_samples, 0, sizeof(unsigned long long), s));
-#define LAUNCH(C, T, E)                                                                                   \
-  do {                                                                                                    \
-    if (smem > 48 * 1024) VRB_CUDA(cudaFuncSetAttribute(rc1pass_kernel<C, T, E>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    rc1pass_kernel<C, T, E><<<grid, CTA_W * CTA_H, smem, s>>>(a);                                         \
-  } while (0)
-#define LAUNCH_TE(C)                                                                     \
-  do {                                                                                   \
-    if (prm_.tf_in_smem) { if (prm_.exact_filter) LAUNCH(C, true, true); else LAUNCH(C, true, false); }   \
-    else                 { if (prm_.exact_filter) LAUNCH(C, false, true); else LAUNCH(C, false, false); } \
-  } while (0)
-    if (prm_.count_samples) LAUNCH_TE(true); else LAUNCH_TE(false);
-#undef LAUNCH_TE
-#undef LAUNCH
+    const int variant = (prm_.count_samples ? 8 : 0) | (prm_.tf_in_smem ? 4 : 0) | (prm_.exact_filter ? 2 : 0) | (prm_.skip_block ? 1 : 0);
+#define CASE(V, C, T, E, S)                                                                                  \
+  case V:                                                                                                    \
+    if (smem > 48 * 1024) VRB_CUDA(cudaFuncSetAttribute(rc1pass_kernel<C, T, E, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    rc1pass_kernel<C, T, E, S><<<grid, CTA_W * CTA_H, smem, s>>>(a);                                         \
+    break;
+    switch (variant) {
+      CASE(0, false, false, false, false) CASE(1, false, false, false, true) CASE(2, false, false, true, false) CASE(3, false, false, true, true)
+      CASE(4, false, true, false, false)  CASE(5, false, true, false, true)  CASE(6, false, true, true, false)  CASE(7, false, true, true, true)
+      CASE(8, true, false, false, false)  CASE(9, true, false, false, true)  CASE(10, true, false, true, false) CASE(11, true, false, true, true)
+      CASE(12, true, true, false, false)  CASE(13, true, true, false, true)  CASE(14, true, true, true, false)  CASE(15, true, true, true, true)
+    }
+#undef CASE
     VRB_CUDA(cudaGetLastError());
     return VRB_OK;
   }
 
  private:
   vrb_rc1pass_params prm_{};
+  SkipMap skip_;
 };
 
 RendererImpl* make_rc1pass(vrb_ctx* ctx) { return new Rc1Pass(ctx); }

@@ -69,6 +69,7 @@ static void release_tf(TransferFunction& t) {
   if (t.lin_rgba) cudaFree(t.lin_rgba);
   if (t.table) cudaFree(t.table);
   if (t.vis_mask) cudaFree(t.vis_mask);
+  if (t.pos_prefix) cudaFree(t.pos_prefix);
   uint64_t g = t.generation;
   t = TransferFunction();
   t.generation = g;
@@ -264,6 +265,10 @@ int vrb_tf_upload(vrb_ctx* ctx, const double* table, int n, int extinction_type)
       }
       if (vis) mask[j >> 5] |= 1u << (j & 31);
     }
+    std::vector<int> prefix((size_t)n + 1, 0);
+    for (int j = 0; j < n; j++) prefix[j + 1] = prefix[j] + (!(__half2float(rgbt[4 * j + 3]) <= 0.0f) ? 1 : 0);
+    VRB_CUDA(cudaMalloc(&t.pos_prefix, prefix.size() * sizeof(int)));
+    VRB_CUDA(cudaMemcpyAsync(t.pos_prefix, prefix.data(), prefix.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     VRB_CUDA(cudaMalloc(&t.vis_mask, mask.size() * sizeof(uint32_t)));
     VRB_CUDA(cudaMemcpyAsync(t.vis_mask, mask.data(), mask.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
     VRB_CUDA(cudaStreamSynchronize(ctx->stream));

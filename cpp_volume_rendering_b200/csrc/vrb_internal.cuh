@@ -55,6 +55,7 @@ struct TransferFunction {
   double* table = nullptr;              // device copy of the double table (n*4), for GetExtN-style precompute
   uint32_t* vis_mask = nullptr;         // bit j: a sample whose hardware-filtered density maps to TF cell j may have alpha > 0
   int vis_words = 0;
+  int* pos_prefix = nullptr;            // n+1 ints: pos_prefix[j] = #texels < j whose RGBt extinction is > 0 (or NaN)
   uint64_t generation = 0;
 };
 

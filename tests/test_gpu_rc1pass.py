@@ -125,6 +125,50 @@ def test_hardware_filter_mode_is_close_but_not_the_parity_path(ctx, bonsai_table
     assert abs(samples - total) <= 5e-3 * total
 
 
+@pytest.mark.parametrize("block", [4, 8, 16, 32])
+def test_empty_space_skipping_preserves_the_lattice(ctx, bonsai_table, block):
+    """Skipped samples are exactly those whose block (incl. trilinear apron) maps to zero extinction, and sample k
+    stays at s = k*step: for the dyadic default step the frame is BIT-IDENTICAL to the reference march, with far
+    fewer fetches.  Non-cubic, non-multiple-of-block volume on purpose."""
+    vox = inputs.synth_volume(0, np.uint8, shape=(100, 77, 90))
+    ctx.upload_volume(vox)
+    ctx.upload_tf(bonsai_table)
+    w, h = 192, 160
+    for eye in [(100.0, 100.0, 200.0), (-30.0, 260.0, 20.0), (10.0, 5.0, -8.0)]:   # outside x2, inside the volume
+        cam = inputs.make_camera(eye, width=w, height=h)
+        base, base8, _, n0, _ = _render_gpu(ctx, cam, w, h, count_samples=1, step_size=0.5)
+        skip, skip8, _, n1, _ = _render_gpu(ctx, cam, w, h, count_samples=1, step_size=0.5, skip_block=block)
+        assert np.array_equal(skip, base) and np.array_equal(skip8, base8)
+        assert n1 <= n0 and (n1 < n0 or eye[2] < 0)   # only the inside-the-volume view may find nothing to skip
+    # oracle parity of the skipping path itself, incl. a non-dyadic step (lattice k*step vs accumulated sum)
+    cam = inputs.make_camera((100.0, 100.0, 200.0), width=w, height=h)
+    for step in (0.5, 0.3):
+        got, got8, _, _, _ = _render_gpu(ctx, cam, w, h, step_size=step, skip_block=block)
+        ref, _, _ = O.rc1pass_render(O.rc1pass_params(cam, w, h, vox.shape, step), O.volume_r16f(vox), O.tf_texture(bonsai_table))
+        _check_images(got, got8, ref, f"skip{block} step{step}")
+
+
+def test_skip_map_follows_tf_and_volume_changes(ctx, bonsai_table):
+    vox = inputs.synth_volume(64, np.uint8)
+    ctx.upload_volume(vox)
+    ctx.upload_tf(bonsai_table)
+    cam = inputs.default_camera(64, 96, 96)
+    r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
+    r.init(96, 96)
+    prm = r.get_params(_capi.Rc1PassParams()); prm.skip_block = 8; prm.step_size = 0.5
+    r.set_params(prm)
+    r.update(cam); r.redraw()
+    a = r.read_frame(_capi.VRB_FRAME_RGBA32F)
+    t2 = bonsai_table.copy(); t2[10:36, 3] = 0.2          # densities that were empty become visible
+    ctx.upload_tf(t2)
+    r.update(cam); r.redraw()
+    b = r.read_frame(_capi.VRB_FRAME_RGBA32F)
+    r.close()
+    ref, _, _ = O.rc1pass_render(O.rc1pass_params(cam, 96, 96, vox.shape, 0.5), O.volume_r16f(vox), O.tf_texture(t2))
+    assert not np.array_equal(a, b)
+    assert float(np.abs(b - ref).max()) * 255.0 <= TOL_255
+
+
 def test_default_step_follows_init(ctx, bonsai_table):
     """m_u_step_size = 0.5/sqrt(3) * |voxel scale| (rc1prenderer.cpp:61-63)."""
     vox = inputs.synth_volume(32, np.uint8)
