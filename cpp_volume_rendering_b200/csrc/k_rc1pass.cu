@@ -6,8 +6,9 @@
 // independently (the loop exits per lane; the warp retires when its last lane does).  CTAs visit the
 // image in a scrambled order so that long and short rays are mixed over the whole launch.
 // Per sample: one hardware trilinear R16F tex3D used for CLASSIFICATION, then — only for samples the
-// transfer function may make visible — a float32 re-filter (8 point fetches), a shared-memory TF lookup
-// with float32 lerp, one MUFU.EX2 and the front-to-back blend.  The frame is written as 8-byte RGBA16F
+// transfer function may make visible — a float32 re-filter (2 point fetches of the 2x2-footprint texture,
+// issued for a whole group of samples at once), a shared-memory TF lookup with float32 lerp, one MUFU.EX2
+// and the front-to-back blend.  The frame is written as 8-byte RGBA16F
 // texels; a row of a warp footprint is 64 contiguous bytes.
 #include "vrb_internal.cuh"
 #include "vrb_ray.cuh"
@@ -16,10 +17,11 @@
 namespace vrb {
 
 struct Rc1Args {
-  cudaTextureObject_t vol, vol_pt, tf;
+  cudaTextureObject_t vol, vol_quad, tf;
   const uint2* tf_lin;       // RGBA16F table (n entries) for the shared-memory path
   const uint32_t* vis_mask;  // conservative "may be non-transparent" bit per TF cell (vrb_ctx.cu)
   int tf_n, vis_words;
+  float vis_lo;              // hardware-filtered densities below this land in transparent TF cells only
   int width, height;
   float res[3];              // VolumeGridResolution
   float grid[3];             // VolumeGridSize
@@ -32,38 +34,28 @@ struct Rc1Args {
   unsigned long long* samples;
   // image-space partition: tiles of `tile` pixels dealt round-robin over ranks
   int rank, n_ranks, tile, tiles_x, n_tiles;
-  int grid_blocks; unsigned scramble;   // CTA order: logical block = (blockIdx * scramble) % grid_blocks
+  int n_items; unsigned scramble;       // item order: item = (ticket * scramble) % n_items
+  unsigned* queue;                      // [0] next ticket, [1] warps finished (self-resetting)
   // empty-space skipping: block edge in voxels, grid of blocks, Chebyshev run map (k_skipmap.cu)
   int skip_block; int nbx, nby, nbz; const uint8_t* skip_map;
 };
 
-constexpr int CTA_W = 16, CTA_H = 8;
-#ifndef VRB_RC1_MINB
-#define VRB_RC1_MINB 8      // resident CTAs per SM the register allocation is capped for (8 -> 64 registers;
-                            // measured on B200: 0.67 ms vs 0.74 ms per C2 frame against a 40-register cap)
+constexpr int WARP_W = 8, WARP_H = 4, CTA_THREADS = 128;
+#ifndef VRB_RC1_QUAD2X2
+#define VRB_RC1_QUAD2X2 1
 #endif
-constexpr int UNROLL = 4;    // independent texture fetches in flight per ray
+#ifndef VRB_RC1_MINB
+#define VRB_RC1_MINB 6      // resident CTAs per SM the register allocation is capped for (6 -> 80 registers: the
+                            // fast empty-space loop then keeps the ray state in registers; measured on B200 for the
+                            // C2 frame: 0.586 ms against 0.604 ms (cap 64, spills) and 0.611 ms (cap 128))
+#endif
+#ifndef VRB_RC1_UNROLL
+#define VRB_RC1_UNROLL 4
+#endif
+constexpr int UNROLL = VRB_RC1_UNROLL;    // independent texture fetches in flight per ray
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
-}
-
-// texture(TexVolume, p) with float32 filter weights: the 8 texels through the point-sampled view of the same
-// array (CLAMP_TO_EDGE comes from the address mode), lerped in float32 in the oracle's order
-// (oracle/orc_common.h Tex3D::linear; GL 4.3 §8.14: i0 = floor(u*N - 0.5), alpha = frac(u*N - 0.5)).
-__device__ __noinline__ float tex3d_exact(cudaTextureObject_t pt, float ux, float uy, float uz, const float* res) {
-  const float X = fmaf(ux, res[0], -0.5f), Y = fmaf(uy, res[1], -0.5f), Z = fmaf(uz, res[2], -0.5f);
-  const float fx = floorf(X), fy = floorf(Y), fz = floorf(Z);
-  const float ax = X - fx, ay = Y - fy, az = Z - fz;
-  const float x0 = fx + 0.5f, x1 = fx + 1.5f, y0 = fy + 0.5f, y1 = fy + 1.5f, z0 = fz + 0.5f, z1 = fz + 1.5f;
-  const float c000 = tex3D<float>(pt, x0, y0, z0), c100 = tex3D<float>(pt, x1, y0, z0);
-  const float c010 = tex3D<float>(pt, x0, y1, z0), c110 = tex3D<float>(pt, x1, y1, z0);
-  const float c001 = tex3D<float>(pt, x0, y0, z1), c101 = tex3D<float>(pt, x1, y0, z1);
-  const float c011 = tex3D<float>(pt, x0, y1, z1), c111 = tex3D<float>(pt, x1, y1, z1);
-  const float c00 = fmaf(ax, c100 - c000, c000), c10 = fmaf(ax, c110 - c010, c010);
-  const float c01 = fmaf(ax, c101 - c001, c001), c11 = fmaf(ax, c111 - c011, c011);
-  const float c0 = fmaf(ay, c10 - c00, c00), c1 = fmaf(ay, c11 - c01, c01);
-  return fmaf(az, c1 - c0, c0);
 }
 
 struct RayState {
@@ -72,23 +64,43 @@ struct RayState {
   bool done;
 };
 
-// ray_marching_1p.comp:133-168 for one lattice sample whose hardware-filtered density is d_hw.
-template <bool TF_SMEM, bool EXACT>
-__device__ __forceinline__ void shade_sample(const Rc1Args& a, const uint4* s_tf, const uint32_t* s_mask, RayState& r,
-                                             float d_hw, float t, float h) {
-  const float tfn = (float)a.tf_n, tfmax = (float)(a.tf_n - 1);
-  float density = d_hw;
-  float u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
-  int j = (int)u;
-  if (!((s_mask[j >> 5] >> (j & 31)) & 1u)) return;       // provably transparent: src.a <= 0 (:142)
-  if (EXACT) {
-    density = tex3d_exact(a.vol_pt, fmaf(r.dux, t, r.ux0), fmaf(r.duy, t, r.uy0), fmaf(r.duz, t, r.uz0), a.res);
-    u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
-    j = (int)u;
-  }
+// texture(TexVolume, p) with float32 filter weights, from the footprint texture (Volume::tex_quad): the two
+// fetches return the 2x2 texel quads of slices z0 and z0+1; lerped in float32 in the oracle's order
+// (oracle/orc_common.h Tex3D::linear; GL 4.3 §8.14: i0 = floor(u*N - 0.5), alpha = frac(u*N - 0.5), CLAMP_TO_EDGE).
+struct Foot3 { float x0, y0, z0; };
+__device__ __forceinline__ Foot3 foot3(const Rc1Args& a, const RayState& r, float t) {
+  Foot3 f;
+  f.x0 = floorf(fmaf(fmaf(r.dux, t, r.ux0), a.res[0], -0.5f));
+  f.y0 = floorf(fmaf(fmaf(r.duy, t, r.uy0), a.res[1], -0.5f));
+  f.z0 = floorf(fmaf(fmaf(r.duz, t, r.uz0), a.res[2], -0.5f));
+  return f;
+}
+__device__ __forceinline__ float quad_lerp(const Rc1Args& a, const RayState& r, float t, uint2 q0, uint2 q1) {
+  const float X = fmaf(fmaf(r.dux, t, r.ux0), a.res[0], -0.5f), Y = fmaf(fmaf(r.duy, t, r.uy0), a.res[1], -0.5f);
+  const float Z = fmaf(fmaf(r.duz, t, r.uz0), a.res[2], -0.5f);
+  const float fx = floorf(X), fy = floorf(Y), fz = floorf(Z);
+  // below texel 0 the clamped fetch returns quad 0 whose second texel is texel 1, but GL clamps i1 to 0 as well
+  const float ax = fx < 0.0f ? 0.0f : X - fx, ay = fy < 0.0f ? 0.0f : Y - fy, az = Z - fz;
+  const float2 a0 = __half22float2(*reinterpret_cast<const __half2*>(&q0.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&q0.y));
+  const float2 a1 = __half22float2(*reinterpret_cast<const __half2*>(&q1.x)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&q1.y));
+  const float c00 = fmaf(ax, a0.y - a0.x, a0.x), c10 = fmaf(ax, b0.y - b0.x, b0.x);
+  const float c01 = fmaf(ax, a1.y - a1.x, a1.x), c11 = fmaf(ax, b1.y - b1.x, b1.x);
+  const float c0 = fmaf(ay, c10 - c00, c00), c1 = fmaf(ay, c11 - c01, c01);
+  return fmaf(az, c1 - c0, c0);
+}
+
+// TF cell of a density: GL_LINEAR / CLAMP_TO_EDGE on n texels -> texels j, j+1 and weight u - j
+__device__ __forceinline__ float tf_coord(const Rc1Args& a, float density) {
+  return fminf(fmaxf(fmaf(density, (float)a.tf_n, -0.5f), 0.0f), (float)(a.tf_n - 1));
+}
+
+// ray_marching_1p.comp:136-168 for one lattice sample of density `density` (u = tf_coord(density)).
+template <bool TF_SMEM>
+__device__ __forceinline__ void composite(const Rc1Args& a, const uint4* s_tf, RayState& r, float density, float u, float h) {
   float4 src;
   if (TF_SMEM) {
     // GL_LINEAR, CLAMP_TO_EDGE on n texels with float32 weights
+    const int j = (int)u;
     const float w = u - (float)j;
     const uint4 e = s_tf[j];
     const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x));
@@ -111,8 +123,53 @@ __device__ __forceinline__ void shade_sample(const Rc1Args& a, const uint4* s_tf
   }
 }
 
+// One group of UNROLL lattice samples (midpoints tk, lengths hk; hk <= 0 marks a slot past the end of the ray;
+// FULL: the caller guarantees every slot is inside the ray with hk == step):
+//   1. UNROLL hardware-filtered fetches in flight (classification); if every density lies below the first
+//      transfer-function cell that can be non-transparent the group is done (the common case in empty space),
+//   2. for the slots the transfer function may make visible, the two footprint fetches, all in flight together,
+//   3. in-order float32 filter + transfer function + blend; a slot after the terminating one is ignored.
+template <bool COUNT, bool TF_SMEM, bool EXACT, bool FULL>
+__device__ __forceinline__ void march_group(const Rc1Args& a, const uint4* s_tf, const uint32_t* s_mask, RayState& r,
+                                            const float (&tk)[UNROLL], const float (&hk)[UNROLL], unsigned& nsamp) {
+  float dk[UNROLL];
+#pragma unroll
+  for (int k = 0; k < UNROLL; k++)
+    dk[k] = tex3D<float>(a.vol, fmaf(r.dux, tk[k], r.ux0), fmaf(r.duy, tk[k], r.uy0), fmaf(r.duz, tk[k], r.uz0));
+  bool below = true;
+#pragma unroll
+  for (int k = 0; k < UNROLL; k++) below = below && (dk[k] < a.vis_lo);      // NaN compares false -> slow path
+  if (below) {
+    if (COUNT) {
+#pragma unroll
+      for (int k = 0; k < UNROLL; k++) nsamp += (FULL || hk[k] > 0.0f) ? 1u : 0u;
+    }
+    return;
+  }
+  bool vis[UNROLL];
+  uint2 q0[UNROLL], q1[UNROLL];
+#pragma unroll
+  for (int k = 0; k < UNROLL; k++) {
+    const int j = (int)tf_coord(a, dk[k]);
+    vis[k] = (FULL || hk[k] > 0.0f) && ((s_mask[j >> 5] >> (j & 31)) & 1u);  // else provably transparent: src.a <= 0 (:142)
+    if (EXACT && vis[k]) {
+      const Foot3 f = foot3(a, r, tk[k]);
+      q0[k] = tex3D<uint2>(a.vol_quad, f.x0 + 0.5f, f.y0 + 0.5f, f.z0 + 0.5f);
+      q1[k] = tex3D<uint2>(a.vol_quad, f.x0 + 0.5f, f.y0 + 0.5f, f.z0 + 1.5f);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < UNROLL; k++) {
+    if (r.done || !(FULL || hk[k] > 0.0f)) continue;       // (no break: keeps the slot arrays in registers)
+    if (COUNT) nsamp++;
+    if (!vis[k]) continue;
+    const float density = EXACT ? quad_lerp(a, r, tk[k], q0[k], q1[k]) : dk[k];
+    composite<TF_SMEM>(a, s_tf, r, density, tf_coord(a, density), hk[k]);
+  }
+}
+
 template <bool COUNT, bool TF_SMEM, bool EXACT, bool SKIP>
-__global__ void __launch_bounds__(CTA_W* CTA_H, VRB_RC1_MINB) rc1pass_kernel(const __grid_constant__ Rc1Args a) {
+__global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(const __grid_constant__ Rc1Args a) {
   extern __shared__ uint4 s_dyn[];
   uint4* s_tf = s_dyn;                                   // TF_SMEM: entry i = {texel i, texel min(i+1,n-1)}
   uint32_t* s_mask = reinterpret_cast<uint32_t*>(s_dyn + (TF_SMEM ? a.tf_n : 0));
@@ -124,17 +181,30 @@ __global__ void __launch_bounds__(CTA_W* CTA_H, VRB_RC1_MINB) rc1pass_kernel(con
   }
   for (int i = threadIdx.x; i < a.vis_words; i += blockDim.x) s_mask[i] = a.vis_mask[i];
   __syncthreads();
-  // CTA -> pixel block.  Blocks are enumerated inside partition tiles so a rank only launches its own.
-  const int lb = (int)(((unsigned long long)blockIdx.x * a.scramble) % (unsigned)a.grid_blocks);
-  const int per_tile_x = a.tile / CTA_W, per_tile = per_tile_x * (a.tile / CTA_H);
-  const int local_tile = lb / per_tile, sub = lb % per_tile;
+  // Work item = one warp footprint of 8x4 pixels.  Items are enumerated inside partition tiles (so a rank only
+  // visits its own) and handed out dynamically: each warp of the persistent grid pulls the next item from a
+  // global counter, so a warp that drew short rays immediately takes more work and the launch has no CTA-sized
+  // tail.  The item order is scrambled so long and short rays are mixed over the whole launch.
+  const int lane = threadIdx.x & 31;
+  const int per_tile_x = a.tile / WARP_W, per_tile = per_tile_x * (a.tile / WARP_H);
+  unsigned nsamp = 0;
+  for (;;) {
+  int raw = 0;
+  if (lane == 0) raw = (int)atomicAdd(a.queue, 1u);
+  raw = __shfl_sync(0xffffffffu, raw, 0);
+  if (raw >= a.n_items) break;
+  const int it = (int)(((unsigned long long)raw * a.scramble) % (unsigned)a.n_items);
+  const int local_tile = it / per_tile, sub = it % per_tile;
   const int tile_id = a.rank + local_tile * a.n_ranks;
-  if (tile_id >= a.n_tiles) return;
   const int tx = tile_id % a.tiles_x, ty = tile_id / a.tiles_x;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // 4 warps: 2x2 arrangement of 8x4 footprints inside 16x8
-  const int px = tx * a.tile + (sub % per_tile_x) * CTA_W + (warp & 1) * 8 + (lane & 7);
-  const int py = ty * a.tile + (sub / per_tile_x) * CTA_H + (warp >> 1) * 4 + (lane >> 3);
+#if VRB_RC1_QUAD2X2
+  // lanes 4q..4q+3 (one texture-unit quad) cover 2x2 pixels; 4x2 quads make the 8x4 footprint
+  const int lx = ((lane >> 2) & 3) * 2 + (lane & 1), ly = (lane >> 4) * 2 + ((lane >> 1) & 1);
+#else
+  const int lx = lane & 7, ly = lane >> 3;
+#endif
+  const int px = tx * a.tile + (sub % per_tile_x) * WARP_W + lx;
+  const int py = ty * a.tile + (sub / per_tile_x) * WARP_H + ly;
   const bool valid = px < a.width && py < a.height;   // no early return: the warp reduces below
 
   const f3 eye = mk3(a.eye[0], a.eye[1], a.eye[2]);
@@ -147,7 +217,6 @@ __global__ void __launch_bounds__(CTA_W* CTA_H, VRB_RC1_MINB) rc1pass_kernel(con
   RayState r;
   r.dst = make_float4(0.f, 0.f, 0.f, 0.f);
   r.done = false;
-  unsigned nsamp = 0;
   if (hit) {
     const float D = fabsf(__fsub_rn(tfar, tnear));
     // tex_pos = (Origin + Dir*tnear) + grid/2   (ray_marching_1p.comp:119-121), rounded as written
@@ -161,23 +230,27 @@ __global__ void __launch_bounds__(CTA_W* CTA_H, VRB_RC1_MINB) rc1pass_kernel(con
     if (!SKIP) {
       float s = 0.0f;
       while (s < D && !r.done) {
-        // issue UNROLL lattice samples (s_k = s_{k-1} + h_{k-1}, exactly the reference's accumulation)
-        float hk[UNROLL], tk[UNROLL], dk[UNROLL];
-        float ss = s;
+        // UNROLL lattice samples (s_k = s_{k-1} + h_{k-1}, exactly the reference's accumulation).  While the last
+        // slot still has a whole step left (h = min(Step, D - s) = Step for it and therefore for all before it)
+        // the group needs no end-of-ray handling.
+        float hk[UNROLL], tk[UNROLL], sk[UNROLL + 1];
+        sk[0] = s;
 #pragma unroll
-        for (int k = 0; k < UNROLL; k++) {
-          hk[k] = fminf(step, __fsub_rn(D, ss));            // <= 0 marks a slot past the end of the ray
-          tk[k] = fmaf(hk[k], 0.5f, ss);
-          dk[k] = tex3D<float>(a.vol, fmaf(r.dux, tk[k], r.ux0), fmaf(r.duy, tk[k], r.uy0), fmaf(r.duz, tk[k], r.uz0));
-          ss = __fadd_rn(ss, fmaxf(hk[k], 0.0f));
-        }
+        for (int k = 0; k < UNROLL; k++) { sk[k + 1] = __fadd_rn(sk[k], step); hk[k] = step; tk[k] = fmaf(step, 0.5f, sk[k]); }
+        if (step <= __fsub_rn(D, sk[UNROLL - 1])) {
+          march_group<COUNT, TF_SMEM, EXACT, true>(a, s_tf, s_mask, r, tk, hk, nsamp);
+          s = sk[UNROLL];
+        } else {
+          float ss = s;
 #pragma unroll
-        for (int k = 0; k < UNROLL; k++) {
-          if (r.done || !(hk[k] > 0.0f)) continue;         // (no break: keeps the slot arrays in registers)
-          if (COUNT) nsamp++;
-          shade_sample<TF_SMEM, EXACT>(a, s_tf, s_mask, r, dk[k], tk[k], hk[k]);
+          for (int k = 0; k < UNROLL; k++) {
+            hk[k] = fminf(step, __fsub_rn(D, ss));            // <= 0 marks a slot past the end of the ray
+            tk[k] = fmaf(hk[k], 0.5f, ss);
+            ss = __fadd_rn(ss, fmaxf(hk[k], 0.0f));
+          }
+          march_group<COUNT, TF_SMEM, EXACT, false>(a, s_tf, s_mask, r, tk, hk, nsamp);
+          s = ss;
         }
-        s = ss;
       }
     } else {
       // Lattice-preserving empty-space skipping: sample k sits at s_k = k*step (identical to the accumulated
@@ -212,29 +285,30 @@ __global__ void __launch_bounds__(CTA_W* CTA_H, VRB_RC1_MINB) rc1pass_kernel(con
           k = max(kn, k + 1);
           continue;
         }
-        float hk[UNROLL], tk[UNROLL], dk[UNROLL];
+        float hk[UNROLL], tk[UNROLL];
 #pragma unroll
         for (int q = 0; q < UNROLL; q++) {
           const float sq = (float)(k + q) * step;
           hk[q] = fminf(step, D - sq);
           tk[q] = fmaf(hk[q], 0.5f, sq);
-          dk[q] = tex3D<float>(a.vol, fmaf(r.dux, tk[q], r.ux0), fmaf(r.duy, tk[q], r.uy0), fmaf(r.duz, tk[q], r.uz0));
         }
-#pragma unroll
-        for (int q = 0; q < UNROLL; q++) {
-          if (r.done || !(hk[q] > 0.0f)) continue;
-          if (COUNT) nsamp++;
-          shade_sample<TF_SMEM, EXACT>(a, s_tf, s_mask, r, dk[q], tk[q], hk[q]);
-        }
+        march_group<COUNT, TF_SMEM, EXACT, false>(a, s_tf, s_mask, r, tk, hk, nsamp);
         k += UNROLL;
       }
     }
   }
   // imageStore(OutputFrag, storePos, dst) — or the cleared 0 where the ray misses (ClearTexture fused)
   if (valid) a.frame[(size_t)py * a.width + px] = make_uint2(pack_half2(r.dst.x, r.dst.y), pack_half2(r.dst.z, r.dst.w));
+  }  // item loop
   if (COUNT) {
     for (int o = 16; o > 0; o >>= 1) nsamp += __shfl_xor_sync(0xffffffffu, nsamp, o);
     if (lane == 0 && nsamp) atomicAdd(a.samples, (unsigned long long)nsamp);
+  }
+  // the last warp of the launch re-arms the queue for the next redraw
+  if (lane == 0) {
+    const unsigned total_warps = gridDim.x * (blockDim.x >> 5);
+    __threadfence();
+    if (atomicAdd(a.queue + 1, 1u) == total_warps - 1) { a.queue[0] = 0u; a.queue[1] = 0u; }
   }
 }
 
@@ -283,9 +357,10 @@ class Rc1Pass : public RendererImpl {
   // Redraw (rc1prenderer.cpp:140-151): ClearTexture + Dispatch fused into one launch.
   int redraw(int /*mode*/) override {
     VRB_REQUIRE(built && have_cam, VRB_ERR_INVALID, "RayCasting1Pass::Redraw before Init/Update");
+    if (prm_.exact_filter) { int rc = ensure_quad(ctx); if (rc != VRB_OK) return rc; }
     const Volume& v = ctx->vol;
     Rc1Args a{};
-    a.vol = v.tex; a.vol_pt = v.tex_pt; a.tf = ctx->tf.tex_rgbt; a.vis_mask = ctx->tf.vis_mask; a.vis_words = ctx->tf.vis_words;
+    a.vol = v.tex; a.vol_quad = v.tex_quad; a.tf = ctx->tf.tex_rgbt; a.vis_mask = ctx->tf.vis_mask; a.vis_words = ctx->tf.vis_words; a.vis_lo = ctx->tf.vis_lo;
     a.res[0] = (float)v.w; a.res[1] = (float)v.h; a.res[2] = (float)v.d;
     a.tf_lin = (const uint2*)ctx->tf.lin_rgbt; a.tf_n = ctx->tf.n;
     a.width = width; a.height = height;
@@ -300,15 +375,16 @@ class Rc1Pass : public RendererImpl {
     a.tiles_x = (width + part_tile - 1) / part_tile;
     a.n_tiles = a.tiles_x * ((height + part_tile - 1) / part_tile);
     const int my_tiles = (a.n_tiles - rank + n_ranks - 1) / n_ranks;
-    const int per_tile = (part_tile / CTA_W) * (part_tile / CTA_H);
-    const int grid = my_tiles * per_tile;
-    if (grid <= 0) return VRB_OK;
-    // scrambled CTA order: multiply by an odd constant near grid/golden-ratio that is coprime to grid
-    a.grid_blocks = grid;
-    unsigned sc = (unsigned)(grid * 0.6180339887) | 1u;
+    a.n_items = my_tiles * (part_tile / WARP_W) * (part_tile / WARP_H);
+    if (a.n_items <= 0) return VRB_OK;
+    // scrambled item order: multiply by an odd constant near n/golden-ratio that is coprime to n
+    unsigned sc = (unsigned)(a.n_items * 0.6180339887) | 1u;
     auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned t = x % y; x = y; y = t; } return x; };
-    while (gcd(sc, (unsigned)grid) != 1u) sc += 2;
-    a.scramble = grid > 2 ? sc : 1u;
+    while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
+    a.scramble = a.n_items > 2 ? sc : 1u;
+    a.queue = d_queue;
+    // persistent grid: as many CTAs as fit on the GPU at once (occupancy query below), never more than there are items
+    const int max_ctas = (a.n_items + CTA_THREADS / 32 - 1) / (CTA_THREADS / 32);
     if (prm_.skip_block) {
       int rc = skip_.ensure(ctx, prm_.skip_block);
       if (rc != VRB_OK) return rc;
@@ -319,10 +395,12 @@ class Rc1Pass : public RendererImpl {
     cudaStream_t s = ctx->stream;
     if (prm_.count_samples) VRB_CUDA(cudaMemsetAsync(d_samples, 0, sizeof(unsigned long long), s));
     const int variant = (prm_.count_samples ? 8 : 0) | (prm_.tf_in_smem ? 4 : 0) | (prm_.exact_filter ? 2 : 0) | (prm_.skip_block ? 1 : 0);
+    int per_sm = 0;
 #define CASE(V, C, T, E, S)                                                                                  \
   case V:                                                                                                    \
     if (smem > 48 * 1024) VRB_CUDA(cudaFuncSetAttribute(rc1pass_kernel<C, T, E, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    rc1pass_kernel<C, T, E, S><<<grid, CTA_W * CTA_H, smem, s>>>(a);                                         \
+    VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rc1pass_kernel<C, T, E, S>, CTA_THREADS, smem)); \
+    rc1pass_kernel<C, T, E, S><<<std::min(std::max(per_sm, 1) * ctx->sm_count, max_ctas), CTA_THREADS, smem, s>>>(a); \
     break;
     switch (variant) {
       CASE(0, false, false, false, false) CASE(1, false, false, false, true) CASE(2, false, false, true, false) CASE(3, false, false, true, true)

@@ -49,7 +49,43 @@ __global__ void read_r16f_kernel(cudaSurfaceObject_t surf, float* out, int w, in
   out[(size_t)x + (size_t)w * ((size_t)y + (size_t)h * (size_t)z)] = __half2float(__ushort_as_half(q));
 }
 
+// Footprint ("quad") texture: see Volume::tex_quad.
+__global__ void __launch_bounds__(256) build_quad_kernel(cudaSurfaceObject_t src, cudaSurfaceObject_t dst, int w, int h, int d) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y, z = blockIdx.z;
+  if (x >= w || y >= h || z >= d) return;
+  const int x1 = min(x + 1, w - 1), y1 = min(y + 1, h - 1);
+  const unsigned a = surf3Dread<unsigned short>(src, x * 2, y, z), b = surf3Dread<unsigned short>(src, x1 * 2, y, z);
+  const unsigned c = surf3Dread<unsigned short>(src, x * 2, y1, z), e = surf3Dread<unsigned short>(src, x1 * 2, y1, z);
+  surf3Dwrite(make_uint2(a | (b << 16), c | (e << 16)), dst, x * 8, y, z);
+}
+
+int ensure_quad(vrb_ctx* ctx) {
+  Volume& v = ctx->vol;
+  if (v.tex_quad) return VRB_OK;
+  VRB_REQUIRE(v.surf, VRB_ERR_NO_VOLUME, "ensure_quad: no volume uploaded");
+  cudaChannelFormatDesc desc = cudaCreateChannelDesc(32, 32, 0, 0, cudaChannelFormatKindUnsigned);
+  VRB_CUDA(cudaMalloc3DArray(&v.quad_array, &desc, make_cudaExtent((size_t)v.w, (size_t)v.h, (size_t)v.d), cudaArraySurfaceLoadStore));
+  cudaResourceDesc rd{}; rd.resType = cudaResourceTypeArray; rd.res.array.array = v.quad_array;
+  cudaSurfaceObject_t dst = 0;
+  VRB_CUDA(cudaCreateSurfaceObject(&dst, &rd));
+  cudaTextureDesc td{};
+  td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+  td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
+  cudaError_t e = cudaCreateTextureObject(&v.tex_quad, &rd, &td, nullptr);
+  if (e == cudaSuccess) {
+    dim3 blk(32, 8, 1), grd((unsigned)((v.w + 31) / 32), (unsigned)((v.h + 7) / 8), (unsigned)v.d);
+    build_quad_kernel<<<grd, blk, 0, ctx->stream>>>(v.surf, dst, (int)v.w, (int)v.h, (int)v.d);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // dst is destroyed below
+  }
+  cudaDestroySurfaceObject(dst);
+  VRB_CUDA(e);
+  return VRB_OK;
+}
+
 static void release_volume(Volume& v) {
+  if (v.tex_quad) cudaDestroyTextureObject(v.tex_quad);
+  if (v.quad_array) cudaFreeArray(v.quad_array);
   if (v.tex) cudaDestroyTextureObject(v.tex);
   if (v.tex_pt) cudaDestroyTextureObject(v.tex_pt);
   if (v.surf) cudaDestroySurfaceObject(v.surf);
@@ -264,6 +300,13 @@ int vrb_tf_upload(vrb_ctx* ctx, const double* table, int n, int extinction_type)
         vis = !(a <= 0.0f);
       }
       if (vis) mask[j >> 5] |= 1u << (j & 31);
+    }
+    // first cell that may be visible: cell j covers densities [(j+0.5)/n, (j+1.5)/n); a small margin keeps the
+    // comparison conservative against the rounding of d*n - 0.5 in the kernel
+    {
+      int jmin = 0;
+      while (jmin < n && !((mask[jmin >> 5] >> (jmin & 31)) & 1u)) jmin++;
+      t.vis_lo = jmin == 0 ? -INFINITY : (jmin >= n ? INFINITY : ((float)jmin + 0.25f) / (float)n);
     }
     std::vector<int> prefix((size_t)n + 1, 0);
     for (int j = 0; j < n; j++) prefix[j + 1] = prefix[j] + (!(__half2float(rgbt[4 * j + 3]) <= 0.0f) ? 1 : 0);

@@ -40,6 +40,11 @@ struct Volume {
   cudaTextureObject_t tex = 0;          // linear, clamp, normalised
   cudaTextureObject_t tex_pt = 0;       // point, clamp, unnormalised (exact software filtering path)
   cudaSurfaceObject_t surf = 0;
+  // Footprint texture for the float32 re-filter (ensure_quad, vrb_ctx.cu): texel (x,y,z) = the four R16F texels
+  // {(x,y),(x+1,y),(x,y+1),(x+1,y+1)} of slice z as 4 x binary16 in a uint2, indices clamped to the edge; point
+  // sampled.  One exact trilinear sample = 2 fetches instead of 8.  Built on first use (8 bytes per voxel).
+  cudaArray_t quad_array = nullptr;
+  cudaTextureObject_t tex_quad = 0;
   uint64_t generation = 0;
   size_t voxel_bytes() const { return dtype == VRB_U8 ? 1 : (dtype == VRB_U16 ? 2 : 4); }
 };
@@ -55,6 +60,7 @@ struct TransferFunction {
   double* table = nullptr;              // device copy of the double table (n*4), for GetExtN-style precompute
   uint32_t* vis_mask = nullptr;         // bit j: a sample whose hardware-filtered density maps to TF cell j may have alpha > 0
   int vis_words = 0;
+  float vis_lo = 0.f;                   // densities below it map to cells below the first set bit of vis_mask
   int* pos_prefix = nullptr;            // n+1 ints: pos_prefix[j] = #texels < j whose RGBt extinction is > 0 (or NaN)
   uint64_t generation = 0;
 };
@@ -84,6 +90,7 @@ struct RendererImpl {
   bool have_cam = false;
   int rank = 0, n_ranks = 1, part_tile = 32;
   unsigned long long* d_samples = nullptr;
+  unsigned* d_queue = nullptr;          // 2 words, zero between launches: dynamic work queue of persistent kernels
   uint64_t last_samples = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool timed = false;
@@ -100,6 +107,9 @@ struct RendererImpl {
 };
 
 RendererImpl* make_rc1pass(vrb_ctx* ctx);
+
+// vrb_ctx.cu: builds Volume::tex_quad on the context stream if it does not exist yet.
+int ensure_quad(vrb_ctx* ctx);
 
 // k_frame.cu
 int frame_to_rgb8_over_white(cudaStream_t s, const __half* frame, int64_t n_pixels, uint8_t* dev_out);

@@ -39,6 +39,8 @@ int vrb_renderer_create(vrb_ctx* ctx, int kind, vrb_renderer** out) {
       return VRB_ERR_UNSUPPORTED;
   }
   cudaError_t e = cudaMalloc(&impl->d_samples, sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMalloc(&impl->d_queue, 2 * sizeof(unsigned));
+  if (e == cudaSuccess) e = cudaMemset(impl->d_queue, 0, 2 * sizeof(unsigned));
   if (e == cudaSuccess) e = cudaEventCreate(&impl->ev0);
   if (e == cudaSuccess) e = cudaEventCreate(&impl->ev1);
   if (e != cudaSuccess) { set_error("vrb_renderer_create: %s", cudaGetErrorString(e)); delete impl; return VRB_ERR_CUDA; }
@@ -56,6 +58,7 @@ int vrb_renderer_destroy(vrb_renderer* r) {
   p->clean();
   p->free_frame();
   if (p->d_samples) cudaFree(p->d_samples);
+  if (p->d_queue) cudaFree(p->d_queue);
   if (p->ev0) cudaEventDestroy(p->ev0);
   if (p->ev1) cudaEventDestroy(p->ev1);
   delete p;

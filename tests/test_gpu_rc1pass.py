@@ -291,3 +291,22 @@ def test_image_partition_union_equals_full_frame(ctx, bonsai_table):
             assert np.all((acc == 0) | (part == 0))   # tiles are disjoint
             acc += part
         assert np.array_equal(acc, full) and cnt == tot
+
+
+@pytest.mark.parametrize("skip", [0, 8])
+def test_full_size_c2_parity(ctx, bonsai_table, skip):
+    """BASELINE config 2 at full size: 512^3 uint16, 1024x1024, step 0.5, "Initial State" camera, against the
+    oracle's full frame (the oracle needs well under a second per frame on the box's host cores)."""
+    n, w, h = 512, 1024, 1024
+    vox = inputs.synth_volume(n, np.uint16)
+    ctx.upload_volume(vox)
+    ctx.upload_tf(bonsai_table)
+    cam = inputs.default_camera(n, w, h)
+    got, got8, _, samples, prm = _render_gpu(ctx, cam, w, h, count_samples=1, step_size=0.5, skip_block=skip)
+    ref, total, _ = O.rc1pass_render(O.rc1pass_params(cam, w, h, vox.shape, 0.5), O.volume_r16f(vox), O.tf_texture(bonsai_table))
+    d16, d8, s = _check_images(got, got8, ref, f"C2 skip={skip}")
+    print(f"C2 skip={skip}: max|d| rgba16f {d16:.3f}/255, rgb8 {d8:.0f}/255, SSIM {s:.6f}, samples {samples} vs oracle {total}")
+    if skip == 0:
+        assert abs(samples - total) <= 2e-3 * total
+    else:
+        assert samples < total
