@@ -1,0 +1,101 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.  ctypes binding of oracle/_ref/libref.so: the REFERENCE's own GL-free host
+code (TransferFunction1D, StructuredGridVolume, SummedAreaTable3D<double>, ParameterSpace) compiled from
+/root/reference by oracle/Makefile.  Only tests/ and bench.py's CPU-baseline legs may import this."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_ref", "libref.so")
+_P = C.c_void_p
+_lib = None
+
+
+def available():
+    return os.path.exists(LIB_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(LIB_PATH)
+        L.ref_tf_create.restype = _P
+        L.ref_tf_create.argtypes = [_P, C.c_int, _P, C.c_int, C.c_int, C.c_int]
+        L.ref_tf_destroy.argtypes = [_P]
+        L.ref_tf_texture.argtypes = [_P, C.c_int, _P, C.c_int]
+        L.ref_tf_get.argtypes = [_P, C.c_double, C.c_double, _P]
+        L.ref_tf_get_extn.argtypes = [_P, C.c_double]
+        L.ref_tf_get_extn.restype = C.c_float
+        L.ref_tf_get_opcn.argtypes = [_P, C.c_double]
+        L.ref_tf_get_opcn.restype = C.c_float
+        L.ref_volume_normalized.argtypes = [_P, C.c_int, C.c_int, C.c_int, C.c_int, _P, C.POINTER(C.c_double)]
+        L.ref_sat3d_build.argtypes = [_P, C.c_int, C.c_int, C.c_int, _P]
+        L.ref_parameterspace_selftest.restype = C.c_int
+        L.ref_parameterspace_sweep.argtypes = [C.c_float] * 6 + [_P, C.c_int]
+        L.ref_parameterspace_sweep.restype = C.c_int
+        _lib = L
+    return _lib
+
+
+def _ptr(a):
+    return a.ctypes.data_as(_P)
+
+
+class RefTF:
+    def __init__(self, rgb_pts, a_pts, max_density=255, extinction_type=False):
+        rgb = np.ascontiguousarray(rgb_pts, np.float64)
+        a = np.ascontiguousarray(a_pts, np.float64)
+        self.n = max_density + 1
+        self.h = lib().ref_tf_create(_ptr(rgb), len(rgb), _ptr(a), len(a), max_density, int(extinction_type))
+
+    def texture(self, kind):
+        out = np.empty((self.n, 4), np.float32)
+        assert lib().ref_tf_texture(self.h, kind, _ptr(out), self.n) == 0
+        return out
+
+    def get(self, value, max_data_value=-1.0):
+        out = np.empty(4, np.float32)
+        lib().ref_tf_get(self.h, float(value), float(max_data_value), _ptr(out))
+        return out
+
+    def get_extn(self, v):
+        return lib().ref_tf_get_extn(self.h, float(v))
+
+    def get_opcn(self, v):
+        return lib().ref_tf_get_opcn(self.h, float(v))
+
+    def close(self):
+        if self.h:
+            lib().ref_tf_destroy(self.h)
+            self.h = None
+
+
+_DT = {np.dtype(np.uint8): 0, np.dtype(np.uint16): 1, np.dtype(np.float32): 2}
+
+
+def volume_normalized(voxels):
+    v = np.ascontiguousarray(voxels)
+    d, h, w = v.shape
+    out = np.empty(v.shape, np.float64)
+    mx = C.c_double()
+    lib().ref_volume_normalized(_ptr(v), _DT[v.dtype], w, h, d, _ptr(out), C.byref(mx))
+    return out, mx.value
+
+
+def sat3d_build(values_zyx):
+    a = np.ascontiguousarray(values_zyx, np.float64)
+    d, h, w = a.shape
+    out = np.empty_like(a)
+    lib().ref_sat3d_build(_ptr(a), w, h, d, _ptr(out))
+    return out
+
+
+def parameterspace_selftest():
+    return lib().ref_parameterspace_selftest()
+
+
+def parameterspace_sweep(a, b, cap=4096):
+    out = np.zeros((cap, 2), np.float32)
+    n = lib().ref_parameterspace_sweep(*map(float, a), *map(float, b), _ptr(out), cap)
+    return n, out[:min(n, cap)]

@@ -1,0 +1,97 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY.  C entry points over the REFERENCE's own GL-free host code, compiled from
+// /root/reference where it lies (see oracle/Makefile, target _ref/libref.so).  Nothing of the reference is copied
+// into this repository: this file only calls it.  Used by tests/test_ref_pins.py to pin the oracle restatement
+// and by bench.py's CPU SAT baseline (cpu_baseline.kind = "reference").
+//
+// Compiled sources: cppvolrend/utils/parameterspace.cpp, libs/volvis_utils/{structuredgridvolume,transferfunction,
+// transferfunction1d}.cpp; header-only: libs/vis_utils/summedareatable.h.  GL types come from ref_shim/stubs.
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include <utils/parameterspace.h>
+#include <vis_utils/summedareatable.h>
+#include <volvis_utils/structuredgridvolume.h>
+#include <volvis_utils/transferfunction1d.h>
+
+extern "C" {
+
+// ---- TransferFunction1D (libs/volvis_utils/transferfunction1d.cpp) -----------------------------------------
+// rgb_pts: n_rgb*{r,g,b,iso}; a_pts: n_a*{alpha,iso}, as TransferFunctionReader::readtf1d (reader.cpp:793-806)
+// feeds AddRGBControlPoint / AddAlphaControlPoint.
+void* ref_tf_create(const double* rgb_pts, int n_rgb, const double* a_pts, int n_a, int max_density, int extinction_type) {
+  vis::TransferFunction1D* tf = new vis::TransferFunction1D(max_density);
+  tf->SetExtinctionCoefficientInput(extinction_type != 0);
+  for (int i = 0; i < n_rgb; i++)
+    tf->AddRGBControlPoint(vis::TransferControlPoint(rgb_pts[4 * i], rgb_pts[4 * i + 1], rgb_pts[4 * i + 2], (int)rgb_pts[4 * i + 3]));
+  for (int i = 0; i < n_a; i++)
+    tf->AddAlphaControlPoint(vis::TransferControlPoint(a_pts[2 * i], (int)a_pts[2 * i + 1]));
+  tf->Build();
+  return tf;
+}
+void ref_tf_destroy(void* h) { delete (vis::TransferFunction1D*)h; }
+// GenerateTexture_1D_RGBt (kind 0) / _RGBA (kind 1): the float data handed to glTexImage1D(GL_RGBA16F), n*4.
+int ref_tf_texture(void* h, int kind, float* out, int n) {
+  vis::TransferFunction1D* tf = (vis::TransferFunction1D*)h;
+  gl::Texture1D* t = kind == 0 ? tf->GenerateTexture_1D_RGBt() : tf->GenerateTexture_1D_RGBA();
+  if (!t || (int)t->GetLength() != n || t->channels != 4 || t->internal != GL_RGBA16F || t->min_filter != GL_LINEAR ||
+      t->wrap_s != GL_CLAMP_TO_EDGE) { delete t; return -1; }
+  std::memcpy(out, t->captured.data(), sizeof(float) * 4 * (size_t)n);
+  delete t;
+  return 0;
+}
+void  ref_tf_get(void* h, double value, double max_data_value, float out[4]) {
+  glm::vec4 v = ((vis::TransferFunction1D*)h)->Get(value, max_data_value);
+  out[0] = v.x; out[1] = v.y; out[2] = v.z; out[3] = v.w;
+}
+float ref_tf_get_extn(void* h, double nv) { return ((vis::TransferFunction1D*)h)->GetExtN(nv); }
+float ref_tf_get_opcn(void* h, double nv) { return ((vis::TransferFunction1D*)h)->GetOpcN(nv); }
+
+// ---- StructuredGridVolume (libs/volvis_utils/structuredgridvolume.cpp) --------------------------------------
+// dtype 0 = u8, 1 = u16, 2 = f32.  out[i] = GetNormalizedSample(x,y,z) for every voxel, x fastest.
+void ref_volume_normalized(const void* voxels, int dtype, int w, int h, int d, double* out, double* max_density) {
+  vis::StructuredGridVolume vol("ref", w, h, d);
+  const size_t n = (size_t)w * h * d, bytes = n * (dtype == 0 ? 1 : (dtype == 1 ? 2 : 4));
+  void* copy = std::malloc(bytes);                    // SetArrayData takes ownership (DestroyData frees it)
+  std::memcpy(copy, voxels, bytes);
+  vol.SetArrayData(copy, dtype == 0 ? vis::DataStorageSize::_8_BITS
+                                    : (dtype == 1 ? vis::DataStorageSize::_16_BITS : vis::DataStorageSize::_NORMALIZED_F));
+  for (int z = 0; z < d; z++)
+    for (int y = 0; y < h; y++)
+      for (int x = 0; x < w; x++) out[(size_t)x + (size_t)w * ((size_t)y + (size_t)h * z)] = vol.GetNormalizedSample(x, y, z);
+  if (max_density) *max_density = vol.GetMaxDensity();
+}
+
+// ---- SummedAreaTable3D<double> (libs/vis_utils/summedareatable.h:171-303) -----------------------------------
+// in: w*h*d doubles (x fastest) written with SetValue; BuildSAT(); out = GetData().
+void ref_sat3d_build(const double* in, int w, int h, int d, double* out) {
+  vis::SummedAreaTable3D<double> sat(w, h, d);
+  for (int z = 0; z < d; z++)
+    for (int y = 0; y < h; y++)
+      for (int x = 0; x < w; x++) sat.SetValue(in[(size_t)x + (size_t)w * ((size_t)y + (size_t)h * z)], x, y, z);
+  sat.BuildSAT();
+  std::memcpy(out, sat.GetData(), sizeof(double) * (size_t)w * h * d);
+}
+
+// ---- ParameterSpace (cppvolrend/utils/parameterspace.{h,cpp}) -----------------------------------------------
+// The reference's only self-test (never called by the reference itself): runs it (it asserts internally).
+int ref_parameterspace_selftest(void) { return ParameterSpaceTest() ? 1 : 0; }
+// Sweep of two float ranges as a renderer's FillParameterSpace would register them; returns the number of
+// samples visited by the odometer and writes the visited (a,b) pairs (up to cap).
+int ref_parameterspace_sweep(float a0, float a1, float da, float b0, float b1, float db, float* out_pairs, int cap) {
+  float a = a0, b = b0;
+  ParameterSpace ps;
+  ps.ClearParameterDimensions();
+  ps.AddParameterDimension(new ParameterRangeFloat("a", &a, a0, a1, da));
+  ps.AddParameterDimension(new ParameterRangeFloat("b", &b, b0, b1, db));
+  ps.StartEvaluation();
+  int n = 0;
+  do {
+    if (n < cap) { out_pairs[2 * n] = a; out_pairs[2 * n + 1] = b; }
+    n++;
+  } while (ps.IncrEvaluation() && n < (1 << 20));
+  ps.EndEvaluation();
+  return n;
+}
+
+}  // extern "C"

@@ -1,0 +1,76 @@
+"""Pins the oracle's host-side restatements against the REFERENCE's own code (oracle/_ref/libref.so, compiled from
+/root/reference by oracle/Makefile; the prebuilt .so travels to the GPU box).  CPU only."""
+import numpy as np
+import pytest
+
+from cpp_volume_rendering_b200 import inputs
+from oracle import pyoracle as O
+from oracle import pyref as R
+
+pytestmark = pytest.mark.skipif(not R.available(), reason="oracle/_ref/libref.so not built (no /root/reference here)")
+
+
+def _f16(a):
+    with np.errstate(over="ignore"):
+        return np.asarray(a, np.float32).astype(np.float16).astype(np.float32)
+
+
+@pytest.fixture(scope="module")
+def ref_bonsai():
+    tf = inputs.bonsai_tf()
+    r = R.RefTF(tf["rgb_pts"], tf["a_pts"], tf["max_density"], tf["extinction_type"])
+    yield r
+    r.close()
+
+
+def test_tf_textures_match_reference(ref_bonsai, bonsai_table):
+    """GenerateTexture_1D_RGBt/_RGBA of the reference (float data handed to GL_RGBA16F) == oracle == numpy build."""
+    tf = inputs.bonsai_tf()
+    assert np.array_equal(O.tf_build_linear(tf["rgb_pts"], tf["a_pts"], 255), bonsai_table)
+    for kind in (0, 1):
+        ref = ref_bonsai.texture(kind)
+        assert np.array_equal(_f16(ref), O.tf_texture(bonsai_table, False, kind), equal_nan=True)
+
+
+def test_tf_extinction_type_and_inf():
+    rgb = np.array([[1, 0, 0, 0], [0, 1, 0, 100], [0, 0, 1, 255]], np.float64)
+    a = np.array([[0, 0], [1.0, 128], [0.25, 255]], np.float64)     # alpha == 1 -> +inf extinction
+    for ext in (False, True):
+        r = R.RefTF(rgb, a, 255, ext)
+        table = O.tf_build_linear(rgb, a, 255)
+        for kind in (0, 1):
+            assert np.array_equal(_f16(r.texture(kind)), O.tf_texture(table, ext, kind), equal_nan=True)
+        r.close()
+
+
+def test_tf_get_extn_opcn_match_reference(ref_bonsai, bonsai_table):
+    vals = np.concatenate([np.linspace(0, 1, 1001), [0.13725491, 0.99999994, 1.0, 1.0000001, -0.001]])
+    for v in vals:
+        assert ref_bonsai.get_extn(v) == O.tf_get_extn(bonsai_table, v), v
+        assert ref_bonsai.get_opcn(v) == O.tf_get_opcn(bonsai_table, v), v
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32])
+def test_volume_normalisation_matches_reference(dtype):
+    rng = np.random.default_rng(5)
+    if dtype == np.float32:
+        v = rng.uniform(0, 1, (5, 7, 9)).astype(np.float32)
+    elif dtype == np.uint16:
+        v = np.arange(65536, dtype=np.uint16).reshape(16, 64, 64)
+    else:
+        v = np.arange(256, dtype=np.uint8).reshape(4, 8, 8)
+    ref, _ = R.volume_normalized(v)
+    # GenerateRTexture: (GLfloat)GetNormalizedSample -> R16F upload
+    assert np.array_equal(_f16(ref.astype(np.float32)), O.volume_r16f(v))
+
+
+def test_parameterspace_selftest_and_sweep():
+    assert R.parameterspace_selftest() == 1
+    # RayCasting1Pass::FillParameterSpace: StepSize 0.2 .. 2.0 step 0.1 (rc1prenderer.cpp:225-229)
+    n, pairs = R.parameterspace_sweep((0.2, 2.0, 0.1), (1.0, 1.0, 1.0))
+    # float accumulation: 0.2 + 18 x 0.1f = 2.0000004 > 2.0, so the reference visits 18 samples, not 19
+    assert n == len(pairs) == 18
+    acc = np.float32(0.2)
+    for a, b in pairs:
+        assert a == acc and b == 1.0
+        acc = np.float32(acc + np.float32(0.1))
