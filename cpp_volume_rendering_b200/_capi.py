@@ -38,6 +38,12 @@ class Rc1PassParams(C.Structure):
                 ("count_samples", C.c_int), ("tf_in_smem", C.c_int), ("exact_filter", C.c_int)]
 
 
+class IsoParams(C.Structure):
+    _fields_ = [("isovalue", C.c_float), ("step_size_small", C.c_float), ("step_size_large", C.c_float),
+                ("step_size_range", C.c_float), ("color", C.c_float * 4), ("apply_gradient_shading", C.c_int),
+                ("num_blocks", C.c_int * 3), ("count_iterations", C.c_int)]
+
+
 # name -> (restype, argtypes); the list doubles as the "every declared symbol is exported" check.
 _P = C.c_void_p
 SIGNATURES = {
@@ -63,6 +69,7 @@ SIGNATURES = {
     "vrb_renderer_frame": (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "vrb_renderer_read_frame": (C.c_int, [_P, _P, C.c_int]),
     "vrb_renderer_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_double)]),
+    "vrb_iso_read_blocks": (C.c_int, [_P, _P, _P]),
     "vrb_renderer_set_partition": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
     "vrb_bench_tex_peak": (C.c_int, [_P, C.POINTER(C.c_double)]),
 }
@@ -202,6 +209,13 @@ class Renderer:
         s, ms = C.c_uint64(), C.c_double()
         _check(lib().vrb_renderer_counters(self._h, C.byref(s), C.byref(ms)))
         return s.value, ms.value
+
+    def read_blocks(self, num_blocks):
+        nbx, nby, nbz = num_blocks
+        mn = np.empty((nbz, nby, nbx), np.float32)
+        mx = np.empty((nbz, nby, nbx), np.float32)
+        _check(lib().vrb_iso_read_blocks(self._h, mn.ctypes.data_as(_P), mx.ctypes.data_as(_P)))
+        return mn, mx
 
     def set_partition(self, rank, n_ranks, tile=32):
         _check(lib().vrb_renderer_set_partition(self._h, rank, n_ranks, tile))

@@ -1,0 +1,388 @@
+// K2/K3/K4 — the iso-surface ray casters, and K5 — per-block min/max.
+//   VRB_ISO_ADAPT    rc1pisoadapt/ray_marching_1p_iso_adapt.comp:91-173
+//   VRB_ISO_SKIP_V1  rc1pisocustom/custom_ray_marching_1p_iso_adapt.comp:92-130,153-246
+//   VRB_ISO_SKIP_V2  rc1pisodfscustom/custom_ray_marching_1p_iso_adapt.comp:93-156,179-262
+//   K5               ComputeBlocksFromVolume, rc1pisocustom/rc1custompisoadaptrenderer.cpp:20-113 (CPU in the reference)
+//
+// These shaders composite a constant opaque colour at the first iso crossing, so the frame is a hit mask: one
+// flipped comparison flips a pixel by the full colour.  Every density the control flow looks at is therefore
+// filtered with float32 weights in exactly the oracle's operation order (tex3d_f32_exact) and all per-step ray
+// arithmetic uses single-rounding intrinsics — the frame is bit-identical to the float32 evaluation of the shader.
+// The march is a dependent chain (the step length depends on the previous density): one ray per thread, persistent
+// warps pulling 8x4-pixel footprints from a ticket counter, the texture unit used for addressing + caching only.
+#include "vrb_internal.cuh"
+#include "vrb_ray.cuh"
+#include <algorithm>
+#include <cfloat>
+
+namespace vrb {
+
+// ---- K5 ------------------------------------------------------------------------------------------------
+// One CTA per block.  min/max of v/maxDataValue in double == (min v)/maxDataValue because the division is monotone,
+// so the reduction runs on the raw voxels and one double division per block reproduces the reference bit for bit.
+template <typename T>
+__global__ void __launch_bounds__(256) block_minmax_kernel(const T* __restrict__ raw, int w, int h, int d, int bsx, int bsy,
+                                                           int bsz, int nbx, int nby, double maxv, float* __restrict__ out_min,
+                                                           float* __restrict__ out_max) {
+  const int b = blockIdx.x;
+  const int bx = b % nbx, by = (b / nbx) % nby, bz = b / (nbx * nby);
+  const int sx = bx * bsx, sy = by * bsy, sz = bz * bsz;
+  const int ex = min(sx + bsx, w), ey = min(sy + bsy, h), ez = min(sz + bsz, d);
+  const int nx = max(ex - sx, 0), ny = max(ey - sy, 0), nz = max(ez - sz, 0);
+  const long long total = (long long)nx * ny * nz;
+  double mn = (double)FLT_MAX, mx = -(double)FLT_MAX;      // numeric_limits<float>::max() / lowest() (:56-57)
+  for (long long i = threadIdx.x; i < total; i += blockDim.x) {
+    const int x = sx + (int)(i % nx), y = sy + (int)((i / nx) % ny), z = sz + (int)(i / ((long long)nx * ny));
+    const double v = (double)raw[(size_t)z * ((size_t)w * h) + (size_t)y * w + x];
+    mn = fmin(mn, v); mx = fmax(mx, v);
+  }
+  // raw values are compared un-normalised; the sentinels must stay above/below every raw value
+  __shared__ double s_mn[256], s_mx[256];
+  __shared__ int s_any[256];
+  s_mn[threadIdx.x] = mn; s_mx[threadIdx.x] = mx; s_any[threadIdx.x] = threadIdx.x < total ? 1 : 0;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) {
+      s_mn[threadIdx.x] = fmin(s_mn[threadIdx.x], s_mn[threadIdx.x + o]);
+      s_mx[threadIdx.x] = fmax(s_mx[threadIdx.x], s_mx[threadIdx.x + o]);
+      s_any[threadIdx.x] |= s_any[threadIdx.x + o];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    if (s_any[0]) { out_min[b] = (float)(s_mn[0] / maxv); out_max[b] = (float)(s_mx[0] / maxv); }
+    else { out_min[b] = FLT_MAX; out_max[b] = -FLT_MAX; }   // block entirely outside the volume: never touched (:104-105)
+  }
+}
+
+struct BlockGrid {
+  float* mn = nullptr; float* mx = nullptr;
+  int nbx = 0, nby = 0, nbz = 0;
+  uint64_t vol_gen = 0;
+  void release() { if (mn) cudaFree(mn); if (mx) cudaFree(mx); mn = mx = nullptr; nbx = nby = nbz = 0; }
+  int ensure(vrb_ctx* ctx, int bx, int by, int bz) {
+    const Volume& v = ctx->vol;
+    if (mn && nbx == bx && nby == by && nbz == bz && vol_gen == v.generation) return VRB_OK;
+    release();
+    VRB_REQUIRE(v.raw, VRB_ERR_NO_VOLUME, "block min/max: no volume uploaded");
+    const size_t nb = (size_t)bx * by * bz;
+    VRB_CUDA(cudaMalloc(&mn, nb * sizeof(float)));
+    VRB_CUDA(cudaMalloc(&mx, nb * sizeof(float)));
+    // blockSize = (N + numBlocks - 1) / numBlocks evaluated in float, truncated to int (:37-39)
+    const int bsx = (int)(((float)(unsigned)v.w + (float)bx - 1.0f) / (float)bx);
+    const int bsy = (int)(((float)(unsigned)v.h + (float)by - 1.0f) / (float)by);
+    const int bsz = (int)(((float)(unsigned)v.d + (float)bz - 1.0f) / (float)bz);
+    cudaStream_t s = ctx->stream;
+    if (v.dtype == VRB_U8)
+      block_minmax_kernel<uint8_t><<<(unsigned)nb, 256, 0, s>>>((const uint8_t*)v.raw, (int)v.w, (int)v.h, (int)v.d, bsx, bsy, bsz, bx, by, 255.0, mn, mx);
+    else if (v.dtype == VRB_U16)
+      block_minmax_kernel<uint16_t><<<(unsigned)nb, 256, 0, s>>>((const uint16_t*)v.raw, (int)v.w, (int)v.h, (int)v.d, bsx, bsy, bsz, bx, by, 65535.0, mn, mx);
+    else
+      block_minmax_kernel<float><<<(unsigned)nb, 256, 0, s>>>((const float*)v.raw, (int)v.w, (int)v.h, (int)v.d, bsx, bsy, bsz, bx, by, 1.0, mn, mx);
+    VRB_CUDA(cudaGetLastError());
+    nbx = bx; nby = by; nbz = bz; vol_gen = v.generation;
+    return VRB_OK;
+  }
+};
+
+// ---- K2/K3/K4 ------------------------------------------------------------------------------------------
+struct IsoArgs {
+  cudaTextureObject_t quad;
+  int width, height;
+  float res[3], grid[3], eye[3], lookat[9];
+  float tan_fovy, aspect;
+  float iso, step_small, step_large, step_range;
+  float color[4];
+  float nb[3]; int nbi[3];
+  const float* bmin; const float* bmax;
+  uint2* frame;
+  unsigned long long* iters;
+  int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble;
+  unsigned* queue;
+};
+
+constexpr int ISO_WARP_W = 8, ISO_WARP_H = 4, ISO_THREADS = 128;
+
+struct IsoRay { f3 org, dir, grid, half, res; };
+
+__device__ __forceinline__ float iso_fetch(const IsoArgs& a, const IsoRay& r, f3 tex_pos) {
+  return tex3d_f32_exact(a.quad, div3(tex_pos, r.grid), r.res);
+}
+__device__ __forceinline__ bool iso_crossing(float prev, float iso, float d) {
+  return (prev <= iso && iso < d) || (prev >= iso && iso > d);
+}
+__device__ __forceinline__ int imod(int v, int n) { int m = v % n; return m < 0 ? m + n : m; }
+
+struct BlockLookup { int x, y, z; float mn, mx; };
+// getBlockIndex + the two GL_NEAREST / GL_REPEAT block-texture fetches
+__device__ __forceinline__ BlockLookup iso_block(const IsoArgs& a, const IsoRay& r, f3 pos) {
+  const f3 np = div3(add3(pos, r.half), r.grid);
+  BlockLookup b;
+  b.x = (int)floorf(__fmul_rn(np.x, a.nb[0])); b.y = (int)floorf(__fmul_rn(np.y, a.nb[1])); b.z = (int)floorf(__fmul_rn(np.z, a.nb[2]));
+  const size_t o = (size_t)imod(b.x, a.nbi[0]) + (size_t)a.nbi[0] * ((size_t)imod(b.y, a.nbi[1]) + (size_t)a.nbi[1] * (size_t)imod(b.z, a.nbi[2]));
+  b.mn = __ldg(a.bmin + o); b.mx = __ldg(a.bmax + o);
+  return b;
+}
+__device__ __forceinline__ void iso_block_bounds(const IsoArgs& a, const IsoRay& r, const BlockLookup& b, f3& bmin, f3& bmax) {
+  const f3 bs = div3(r.grid, mk3(a.nb[0], a.nb[1], a.nb[2]));
+  bmin = add3(scale3(mk3(-r.grid.x, -r.grid.y, -r.grid.z), 0.5f), mul3(bs, mk3((float)b.x, (float)b.y, (float)b.z)));
+  bmax = add3(bmin, bs);
+}
+__device__ __forceinline__ float fsign(float x) { return x > 0.0f ? 1.0f : (x < 0.0f ? -1.0f : 0.0f); }
+
+template <int MODE, bool COUNT>
+__global__ void __launch_bounds__(ISO_THREADS, 6) iso_kernel(const __grid_constant__ IsoArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int per_tile_x = a.tile / ISO_WARP_W, per_tile = per_tile_x * (a.tile / ISO_WARP_H);
+  unsigned nit = 0;
+  for (;;) {
+    int raw = 0;
+    if (lane == 0) raw = (int)atomicAdd(a.queue, 1u);
+    raw = __shfl_sync(0xffffffffu, raw, 0);
+    if (raw >= a.n_items) break;
+    const int it = (int)(((unsigned long long)raw * a.scramble) % (unsigned)a.n_items);
+    const int local_tile = it / per_tile, sub = it % per_tile;
+    const int tile_id = a.rank + local_tile * a.n_ranks;
+    const int tx = tile_id % a.tiles_x, ty = tile_id / a.tiles_x;
+    const int lx = ((lane >> 2) & 3) * 2 + (lane & 1), ly = (lane >> 4) * 2 + ((lane >> 1) & 1);
+    const int px = tx * a.tile + (sub % per_tile_x) * ISO_WARP_W + lx;
+    const int py = ty * a.tile + (sub / per_tile_x) * ISO_WARP_H + ly;
+    if (px >= a.width || py >= a.height) continue;
+
+    IsoRay r;
+    r.org = mk3(a.eye[0], a.eye[1], a.eye[2]);
+    r.grid = mk3(a.grid[0], a.grid[1], a.grid[2]);
+    r.half = scale3(r.grid, 0.5f);
+    r.res = mk3(a.res[0], a.res[1], a.res[2]);
+    const f3 cdir = camera_ray_dir(px, py, a.width, a.height, a.tan_fovy, a.aspect, a.lookat);
+    float tnear, tfar;
+    const bool hit = ray_aabb(r.org, cdir, mk3(-r.half.x, -r.half.y, -r.half.z), r.half, r.dir, tnear, tfar);
+    float4 dst = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (hit) {
+      const float iso = a.iso;
+      bool crossed = false;
+      if (MODE == 0) {
+        const float D = fabsf(__fsub_rn(tfar, tnear));
+        const f3 tex_pos = add3(add3(r.org, scale3(r.dir, tnear)), r.half);
+        float prev = iso_fetch(a, r, tex_pos);
+        for (float s = 0.0f; s < D;) {
+          const float cur_step = (fabsf(__fsub_rn(prev, iso)) < a.step_range) ? a.step_small : a.step_large;
+          const float h = gmin(cur_step, __fsub_rn(D, s));
+          const float density = iso_fetch(a, r, add3(tex_pos, scale3(r.dir, __fadd_rn(s, h))));
+          if (COUNT) nit++;
+          if (iso_crossing(prev, iso, density)) { crossed = true; }
+          if (crossed) {
+            // src = Color; src.rgb *= src.a; dst += (1-dst.a)*src; break at dst.a > 0.99 (:137-155)
+            const float w = 1.0f - dst.w;
+            dst.x = fmaf(w, __fmul_rn(a.color[0], a.color[3]), dst.x); dst.y = fmaf(w, __fmul_rn(a.color[1], a.color[3]), dst.y);
+            dst.z = fmaf(w, __fmul_rn(a.color[2], a.color[3]), dst.z); dst.w = fmaf(w, a.color[3], dst.w);
+            crossed = false;
+            if (dst.w > 0.99f) break;
+          }
+          prev = density;
+          s = __fadd_rn(s, h);
+        }
+      } else {
+        float t = tnear;
+        float prev = iso_fetch(a, r, add3(add3(r.org, scale3(r.dir, t)), r.half));
+        while (t < tfar) {
+          const f3 pos = add3(r.org, scale3(r.dir, t));
+          const BlockLookup b = iso_block(a, r, pos);
+          if (COUNT) nit++;
+          float density, h;
+          if (MODE == 1) {
+            bool tilted = false;
+            if (iso < b.mn || iso > b.mx) {
+              float deltaT;
+              if (fabsf(r.dir.x) < 0.01f || fabsf(r.dir.y) < 0.01f || fabsf(r.dir.z) < 0.01f) { deltaT = -1.0f; tilted = true; }
+              else {
+                f3 bmin, bmax; iso_block_bounds(a, r, b, bmin, bmax);
+                const f3 t1 = div3(sub3(bmin, pos), r.dir), t2 = div3(sub3(bmax, pos), r.dir);
+                const f3 tmn = min3(t1, t2), tmx = max3(t1, t2);
+                deltaT = __fsub_rn(gmin(gmin(tmx.x, tmx.y), tmx.z), gmax(gmax(tmn.x, tmn.y), tmn.z));
+              }
+              if (deltaT <= a.step_small) deltaT = a.step_small;
+              t = __fadd_rn(t, deltaT);
+              if (!tilted) continue;
+            }
+            if (!((iso >= b.mn && iso <= b.mx) || tilted)) continue;
+            const float cur_step = (fabsf(__fsub_rn(prev, iso)) < a.step_range) ? a.step_small : a.step_large;   // stale prev (:227)
+            prev = iso_fetch(a, r, add3(add3(r.org, scale3(r.dir, t)), r.half));
+            h = gmin(cur_step, __fsub_rn(tfar, t));
+            t = __fadd_rn(t, h);
+            density = iso_fetch(a, r, add3(add3(r.org, scale3(r.dir, t)), r.half));
+            if (iso_crossing(prev, iso, density)) {
+              t = __fsub_rn(t, __fdiv_rn(__fsub_rn(density, iso), __fsub_rn(density, prev)));     // :240-241
+              crossed = true;
+            }
+          } else {
+            if (iso < __fsub_rn(b.mn, 0.001f) || iso > __fadd_rn(b.mx, 0.001f)) {
+              const f3 rcp = mk3(fabsf(r.dir.x) > 1e-6f ? __fdiv_rn(1.0f, r.dir.x) : __fmul_rn(fsign(r.dir.x), 1e6f),
+                                 fabsf(r.dir.y) > 1e-6f ? __fdiv_rn(1.0f, r.dir.y) : __fmul_rn(fsign(r.dir.y), 1e6f),
+                                 fabsf(r.dir.z) > 1e-6f ? __fdiv_rn(1.0f, r.dir.z) : __fmul_rn(fsign(r.dir.z), 1e6f));
+              f3 bmin, bmax; iso_block_bounds(a, r, b, bmin, bmax);
+              const f3 tmx = max3(mul3(sub3(bmin, pos), rcp), mul3(sub3(bmax, pos), rcp));
+              float exitT = gmin(gmin(tmx.x, tmx.y), tmx.z);
+              if (fabsf(__fsub_rn(exitT, tmx.x)) < 1e-5f) exitT = __fadd_rn(exitT, 1e-4f);
+              if (fabsf(__fsub_rn(exitT, tmx.y)) < 1e-5f) exitT = __fadd_rn(exitT, 1e-4f);
+              if (fabsf(__fsub_rn(exitT, tmx.z)) < 1e-5f) exitT = __fadd_rn(exitT, 1e-4f);
+              t = __fadd_rn(t, gmax(a.step_small, exitT));
+              continue;   // (the shader re-fetches prevDensity here, :216-217; the value is never read)
+            }
+            const float cur = iso_fetch(a, r, add3(add3(r.org, scale3(r.dir, t)), r.half));
+            float adaptive;
+            if (fabsf(__fsub_rn(cur, iso)) < a.step_range) adaptive = a.step_small;
+            else {
+              const f3 bs = div3(r.grid, mk3(a.nb[0], a.nb[1], a.nb[2]));
+              adaptive = gmin(a.step_large, __fmul_rn(__fsqrt_rn(dot_rn(bs, bs)), 0.5f));
+            }
+            h = gmin(adaptive, __fsub_rn(tfar, t));
+            prev = cur;
+            t = __fadd_rn(t, h);
+            density = iso_fetch(a, r, add3(add3(r.org, scale3(r.dir, t)), r.half));
+            if (iso_crossing(prev, iso, density)) {
+              const float tt = __fdiv_rn(__fsub_rn(iso, prev), __fsub_rn(density, prev));
+              t = __fsub_rn(t, __fmul_rn(h, __fsub_rn(1.0f, tt)));                                 // :246
+              crossed = true;
+            }
+          }
+          if (crossed) {
+            const float w = 1.0f - dst.w;
+            dst.x = fmaf(w, __fmul_rn(a.color[0], a.color[3]), dst.x); dst.y = fmaf(w, __fmul_rn(a.color[1], a.color[3]), dst.y);
+            dst.z = fmaf(w, __fmul_rn(a.color[2], a.color[3]), dst.z); dst.w = fmaf(w, a.color[3], dst.w);
+            crossed = false;
+            if (dst.w > 0.99f) break;
+          }
+        }
+      }
+    }
+    a.frame[(size_t)py * a.width + px] = make_uint2(pack_half2(dst.x, dst.y), pack_half2(dst.z, dst.w));
+  }
+  if (COUNT) {
+    for (int o = 16; o > 0; o >>= 1) nit += __shfl_xor_sync(0xffffffffu, nit, o);
+    if (lane == 0 && nit) atomicAdd(a.iters, (unsigned long long)nit);
+  }
+  if (lane == 0) {
+    const unsigned total_warps = gridDim.x * (blockDim.x >> 5);
+    __threadfence();
+    if (atomicAdd(a.queue + 1, 1u) == total_warps - 1) { a.queue[0] = 0u; a.queue[1] = 0u; }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Host drivers: RayCasting1PassIsoAdapt (rc1pisoadaptrenderer.cpp), CustomRayCasting1PassIsoAdapt
+// (rc1custompisoadaptrenderer.cpp), CustomRayCasting1PassIsodfsAdapt (rc1custompisoadaptdfsrenderer.cpp).
+class IsoRenderer : public RendererImpl {
+ public:
+  IsoRenderer(vrb_ctx* c, int k) : RendererImpl(c, k) {
+    prm_.isovalue = 0.5f; prm_.step_size_small = 0.05f; prm_.step_size_large = 1.0f; prm_.step_size_range = 0.1f;   // ctor :13-19
+    prm_.color[0] = 0.66f; prm_.color[1] = 0.6f; prm_.color[2] = 0.05f; prm_.color[3] = 1.0f;
+    prm_.apply_gradient_shading = 0; prm_.count_iterations = 0;
+    // numBlocks: (4,4,4) in rc1custompisoadaptrenderer.cpp:190, (32,32,32) in rc1custompisoadaptdfsrenderer.cpp:190
+    const int nb = k == VRB_ISO_SKIP_V2 ? 32 : 4;
+    prm_.num_blocks[0] = prm_.num_blocks[1] = prm_.num_blocks[2] = nb;
+  }
+
+  int init(int w, int h) override {
+    VRB_REQUIRE(ctx->vol.tex != 0, VRB_ERR_NO_VOLUME, "iso renderer Init: no volume texture");
+    int rc = ensure_quad(ctx);
+    if (rc != VRB_OK) return rc;
+    if (kind != VRB_ISO_ADAPT) {   // ComputeBlocksFromVolume at Init (:190-193)
+      rc = blocks_.ensure(ctx, prm_.num_blocks[0], prm_.num_blocks[1], prm_.num_blocks[2]);
+      if (rc != VRB_OK) return rc;
+    }
+    rc = alloc_frame(w, h);
+    if (rc != VRB_OK) return rc;
+    built = true;
+    return VRB_OK;
+  }
+  void clean() override { blocks_.release(); }
+
+  int set_params(const void* pod, size_t size) override {
+    VRB_REQUIRE(pod && size == sizeof(vrb_iso_params), VRB_ERR_INVALID, "iso set_params: size %zu != sizeof(vrb_iso_params) %zu", size, sizeof(vrb_iso_params));
+    const vrb_iso_params p = *(const vrb_iso_params*)pod;
+    VRB_REQUIRE(p.step_size_small > 0.0f && p.step_size_large > 0.0f, VRB_ERR_INVALID, "iso set_params: step sizes must be positive");
+    for (int i = 0; i < 3; i++) VRB_REQUIRE(p.num_blocks[i] >= 1 && p.num_blocks[i] <= 1024, VRB_ERR_INVALID, "iso set_params: num_blocks out of range");
+    VRB_REQUIRE(!p.apply_gradient_shading, VRB_ERR_UNSUPPORTED, "iso set_params: gradient shading needs a gradient volume (not uploaded)");
+    prm_ = p;
+    return VRB_OK;
+  }
+  int get_params(void* pod, size_t size) override {
+    VRB_REQUIRE(pod && size == sizeof(vrb_iso_params), VRB_ERR_INVALID, "iso get_params: bad size");
+    *(vrb_iso_params*)pod = prm_;
+    return VRB_OK;
+  }
+
+  int read_blocks(float* host_min, float* host_max) {
+    VRB_REQUIRE(blocks_.mn, VRB_ERR_INVALID, "no block min/max (renderer kind without blocks, or Init not called)");
+    const size_t n = (size_t)blocks_.nbx * blocks_.nby * blocks_.nbz * sizeof(float);
+    VRB_CUDA(cudaMemcpyAsync(host_min, blocks_.mn, n, cudaMemcpyDeviceToHost, ctx->stream));
+    VRB_CUDA(cudaMemcpyAsync(host_max, blocks_.mx, n, cudaMemcpyDeviceToHost, ctx->stream));
+    VRB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VRB_OK;
+  }
+
+  int redraw(int /*mode*/) override {
+    VRB_REQUIRE(built && have_cam, VRB_ERR_INVALID, "iso Redraw before Init/Update");
+    int rc = ensure_quad(ctx);
+    if (rc != VRB_OK) return rc;
+    const Volume& v = ctx->vol;
+    IsoArgs a{};
+    a.quad = v.tex_quad;
+    a.width = width; a.height = height;
+    a.res[0] = (float)v.w; a.res[1] = (float)v.h; a.res[2] = (float)v.d;
+    a.grid[0] = (float)v.w * v.sx; a.grid[1] = (float)v.h * v.sy; a.grid[2] = (float)v.d * v.sz;
+    for (int i = 0; i < 3; i++) a.eye[i] = cam.eye[i];
+    for (int i = 0; i < 9; i++) a.lookat[i] = cam.lookat[i];
+    a.tan_fovy = cam.tan_fovy; a.aspect = cam.aspect;
+    a.iso = prm_.isovalue; a.step_small = prm_.step_size_small; a.step_large = prm_.step_size_large; a.step_range = prm_.step_size_range;
+    for (int i = 0; i < 4; i++) a.color[i] = prm_.color[i];
+    if (kind != VRB_ISO_ADAPT) {
+      rc = blocks_.ensure(ctx, prm_.num_blocks[0], prm_.num_blocks[1], prm_.num_blocks[2]);
+      if (rc != VRB_OK) return rc;
+      for (int i = 0; i < 3; i++) { a.nbi[i] = prm_.num_blocks[i]; a.nb[i] = (float)prm_.num_blocks[i]; }
+      a.bmin = blocks_.mn; a.bmax = blocks_.mx;
+    }
+    a.frame = (uint2*)frame; a.iters = d_samples;
+    a.rank = rank; a.n_ranks = n_ranks; a.tile = part_tile;
+    a.tiles_x = (width + part_tile - 1) / part_tile;
+    a.n_tiles = a.tiles_x * ((height + part_tile - 1) / part_tile);
+    const int my_tiles = (a.n_tiles - rank + n_ranks - 1) / n_ranks;
+    a.n_items = my_tiles * (part_tile / ISO_WARP_W) * (part_tile / ISO_WARP_H);
+    if (a.n_items <= 0) return VRB_OK;
+    unsigned sc = (unsigned)(a.n_items * 0.6180339887) | 1u;
+    auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned t = x % y; x = y; y = t; } return x; };
+    while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
+    a.scramble = a.n_items > 2 ? sc : 1u;
+    a.queue = d_queue;
+    const int max_ctas = (a.n_items + ISO_THREADS / 32 - 1) / (ISO_THREADS / 32);
+    cudaStream_t s = ctx->stream;
+    if (prm_.count_iterations) VRB_CUDA(cudaMemsetAsync(d_samples, 0, sizeof(unsigned long long), s));
+    int per_sm = 0;
+#define LAUNCH(M, C)                                                                                               \
+  do {                                                                                                             \
+    VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, iso_kernel<M, C>, ISO_THREADS, 0));            \
+    iso_kernel<M, C><<<std::min(std::max(per_sm, 1) * ctx->sm_count, max_ctas), ISO_THREADS, 0, s>>>(a);           \
+  } while (0)
+    const bool c = prm_.count_iterations != 0;
+    if (kind == VRB_ISO_ADAPT) { if (c) LAUNCH(0, true); else LAUNCH(0, false); }
+    else if (kind == VRB_ISO_SKIP_V1) { if (c) LAUNCH(1, true); else LAUNCH(1, false); }
+    else { if (c) LAUNCH(2, true); else LAUNCH(2, false); }
+#undef LAUNCH
+    VRB_CUDA(cudaGetLastError());
+    return VRB_OK;
+  }
+
+ private:
+  vrb_iso_params prm_{};
+  BlockGrid blocks_;
+};
+
+RendererImpl* make_iso(vrb_ctx* ctx, int kind) { return new IsoRenderer(ctx, kind); }
+
+int iso_read_blocks(RendererImpl* impl, float* host_min, float* host_max) {
+  VRB_REQUIRE(impl->kind == VRB_ISO_SKIP_V1 || impl->kind == VRB_ISO_SKIP_V2, VRB_ERR_INVALID, "vrb_iso_read_blocks: renderer has no block grid");
+  return static_cast<IsoRenderer*>(impl)->read_blocks(host_min, host_max);
+}
+
+}  // namespace vrb

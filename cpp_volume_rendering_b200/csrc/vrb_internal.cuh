@@ -107,6 +107,8 @@ struct RendererImpl {
 };
 
 RendererImpl* make_rc1pass(vrb_ctx* ctx);
+RendererImpl* make_iso(vrb_ctx* ctx, int kind);
+int iso_read_blocks(RendererImpl* impl, float* host_min, float* host_max);
 
 // vrb_ctx.cu: builds Volume::tex_quad on the context stream if it does not exist yet.
 int ensure_quad(vrb_ctx* ctx);

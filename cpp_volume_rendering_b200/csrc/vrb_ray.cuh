@@ -4,6 +4,7 @@
 // evaluation of the reference shader statements (and to oracle/orc_ray.h).
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda_fp16.h>
 
 namespace vrb {
 
@@ -52,4 +53,38 @@ __device__ __forceinline__ unsigned pack_half2(float a, float b) {
   return *reinterpret_cast<unsigned*>(&h);
 }
 
+}  // namespace vrb
+
+// ---------------------------------------------------------------------------------------------
+// GLSL-statement arithmetic, one IEEE rounding per operation and never contracted: used where a comparison
+// downstream (iso crossing, block index, step choice) must come out exactly as in the float32 evaluation of the
+// shader statement (and oracle/orc_common.h, built with -ffp-contract=off).
+namespace vrb {
+__device__ __forceinline__ f3 add3(f3 a, f3 b) { return mk3(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z)); }
+__device__ __forceinline__ f3 sub3(f3 a, f3 b) { return mk3(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y), __fsub_rn(a.z, b.z)); }
+__device__ __forceinline__ f3 mul3(f3 a, f3 b) { return mk3(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y), __fmul_rn(a.z, b.z)); }
+__device__ __forceinline__ f3 div3(f3 a, f3 b) { return mk3(__fdiv_rn(a.x, b.x), __fdiv_rn(a.y, b.y), __fdiv_rn(a.z, b.z)); }
+__device__ __forceinline__ f3 scale3(f3 a, float s) { return mk3(__fmul_rn(a.x, s), __fmul_rn(a.y, s), __fmul_rn(a.z, s)); }
+__device__ __forceinline__ f3 min3(f3 a, f3 b) { return mk3(gmin(a.x, b.x), gmin(a.y, b.y), gmin(a.z, b.z)); }
+__device__ __forceinline__ f3 max3(f3 a, f3 b) { return mk3(gmax(a.x, b.x), gmax(a.y, b.y), gmax(a.z, b.z)); }
+
+// texture(TexVolume, p) on the R16F volume, GL_LINEAR / CLAMP_TO_EDGE with float32 weights, bit-identical to
+// oracle Tex3D::linear: two point fetches of the footprint texture (Volume::tex_quad) give the 2x2 texel quads of
+// slices i0z and i1z; below texel 0 GL clamps both i0 and i1 to 0, which a zero weight reproduces exactly.
+__device__ __forceinline__ float tex3d_f32_exact(cudaTextureObject_t quad, f3 p, f3 res) {
+  const float X = __fsub_rn(__fmul_rn(p.x, res.x), 0.5f), Y = __fsub_rn(__fmul_rn(p.y, res.y), 0.5f);
+  const float Z = __fsub_rn(__fmul_rn(p.z, res.z), 0.5f);
+  float fx = floorf(X), fy = floorf(Y), fz = floorf(Z);
+  const float ax = fx < 0.0f ? 0.0f : __fsub_rn(X, fx), ay = fy < 0.0f ? 0.0f : __fsub_rn(Y, fy), az = __fsub_rn(Z, fz);
+  // clamp before the +0.5 so that far-away coordinates stay finite texel addresses
+  fx = fminf(fmaxf(fx, -1.0f), res.x); fy = fminf(fmaxf(fy, -1.0f), res.y); fz = fminf(fmaxf(fz, -1.0f), res.z);
+  const uint2 q0 = tex3D<uint2>(quad, fx + 0.5f, fy + 0.5f, fz + 0.5f);
+  const uint2 q1 = tex3D<uint2>(quad, fx + 0.5f, fy + 0.5f, fz + 1.5f);
+  const float2 a0 = __half22float2(*reinterpret_cast<const __half2*>(&q0.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&q0.y));
+  const float2 a1 = __half22float2(*reinterpret_cast<const __half2*>(&q1.x)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&q1.y));
+  const float c00 = __fadd_rn(a0.x, __fmul_rn(ax, __fsub_rn(a0.y, a0.x))), c10 = __fadd_rn(b0.x, __fmul_rn(ax, __fsub_rn(b0.y, b0.x)));
+  const float c01 = __fadd_rn(a1.x, __fmul_rn(ax, __fsub_rn(a1.y, a1.x))), c11 = __fadd_rn(b1.x, __fmul_rn(ax, __fsub_rn(b1.y, b1.x)));
+  const float c0 = __fadd_rn(c00, __fmul_rn(ay, __fsub_rn(c10, c00))), c1 = __fadd_rn(c01, __fmul_rn(ay, __fsub_rn(c11, c01)));
+  return __fadd_rn(c0, __fmul_rn(az, __fsub_rn(c1, c0)));
+}
 }  // namespace vrb

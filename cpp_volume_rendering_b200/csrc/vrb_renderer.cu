@@ -34,6 +34,7 @@ int vrb_renderer_create(vrb_ctx* ctx, int kind, vrb_renderer** out) {
   RendererImpl* impl = nullptr;
   switch (kind) {
     case VRB_RC1PASS: impl = make_rc1pass(ctx); break;
+    case VRB_ISO_ADAPT: case VRB_ISO_SKIP_V1: case VRB_ISO_SKIP_V2: impl = make_iso(ctx, kind); break;
     default:
       set_error("vrb_renderer_create: renderer kind %d is not built yet", kind);
       return VRB_ERR_UNSUPPORTED;
@@ -170,6 +171,11 @@ int vrb_renderer_counters(vrb_renderer* r, uint64_t* samples, double* ms) {
     *ms = (double)t;
   }
   return VRB_OK;
+}
+
+int vrb_iso_read_blocks(vrb_renderer* r, float* host_min, float* host_max) {
+  VRB_REQUIRE(r && host_min && host_max, VRB_ERR_INVALID, "vrb_iso_read_blocks: null argument");
+  return iso_read_blocks(r->impl, host_min, host_max);
 }
 
 int vrb_renderer_set_partition(vrb_renderer* r, int rank, int n_ranks, int tile) {

@@ -84,6 +84,21 @@ typedef struct {
                                     0 = every sample uses the texture unit's 1.8 fixed-point trilinear filter */
 } vrb_rc1pass_params;
 
+/* Run-time parameters of the three iso-surface ray casters: their ImGui-mutable members
+ * (rc1pisoadaptrenderer.h, ctor rc1pisoadaptrenderer.cpp:13-21; numBlocks is a local of Init in the two
+ * skipping renderers: (4,4,4) rc1custompisoadaptrenderer.cpp:190, (32,32,32) rc1custompisoadaptdfsrenderer.cpp:190).
+ * Pass to vrb_renderer_set_params with sizeof(vrb_iso_params). */
+typedef struct {
+  float isovalue;               /* m_u_isovalue        0.5  */
+  float step_size_small;        /* m_u_step_size_small 0.05 */
+  float step_size_large;        /* m_u_step_size_large 1.0  */
+  float step_size_range;        /* m_u_step_size_range 0.1  */
+  float color[4];               /* m_u_color (0.66, 0.6, 0.05, 1) */
+  int   apply_gradient_shading; /* m_apply_gradient_shading (needs a gradient volume) */
+  int   num_blocks[3];          /* numBlocks of the block min/max grid (skipping renderers) */
+  int   count_iterations;       /* 1 = instrumented kernel that counts march-loop iterations */
+} vrb_iso_params;
+
 /* ---- library / context ------------------------------------------------------------------- */
 int         vrb_abi_version(void);
 const char* vrb_last_error(void);
@@ -136,6 +151,10 @@ int vrb_renderer_read_frame(vrb_renderer* r, void* host, int format);
 /* samples: march-loop iterations of the last redraw (only if count_samples was set, else 0);
  * ms: device time of the last redraw measured with CUDA events on the context stream. */
 int vrb_renderer_counters(vrb_renderer* r, uint64_t* samples, double* ms);
+
+/* Test hook for K5 (ComputeBlocksFromVolume, rc1custompisoadaptrenderer.cpp:20-113, moved to the GPU): the block
+ * min / max grids of a VRB_ISO_SKIP_V1 / _V2 renderer, num_blocks[0]*[1]*[2] floats each, x fastest. */
+int vrb_iso_read_blocks(vrb_renderer* r, float* host_min, float* host_max);
 
 /* ---- multi-GPU: image-space partition (no reference counterpart) ------------ */
 /* Tiles of tile x tile pixels are dealt round-robin: this rank renders tile t iff t % n_ranks == rank.

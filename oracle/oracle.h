@@ -65,6 +65,29 @@ uint64_t orc_rc1pass_render(const orc_rc1p_params* p, const float* vol_r16f, con
  * RGB8 unorm back buffer.  out_rgb8: n_pixels*3. */
 void orc_blit_over_white(const float* rgba, int64_t n_pixels, uint8_t* out_rgb8);
 
+/* ---- iso-surface ray casters (K2/K3/K4) and block min/max (K5) ---------------------------------------- */
+typedef struct {
+  int   width, height;
+  int   vol_w, vol_h, vol_d;
+  float voxel[3];
+  float eye[3];
+  float lookat[9];
+  float tan_fovy, aspect;
+  int   mode;                   /* 0 rc1pisoadapt, 1 rc1pisocustom (skipping v1), 2 rc1pisodfscustom (skipping v2) */
+  float isovalue, step_small, step_large, step_range;   /* Isovalue, StepSizeSmall, StepSizeLarge, StepSizeRange */
+  float color[4];               /* Color */
+  int   num_blocks[3];          /* numBlocks (modes 1, 2) */
+  int   weight_mode;
+  int   row_begin, row_end, row_stride, threads;
+} orc_iso_params;
+
+/* ComputeBlocksFromVolume (rc1pisocustom/rc1custompisoadaptrenderer.cpp:20-113): nbx*nby*nbz floats each, x fastest. */
+void orc_block_minmax(const void* voxels, int dtype, int w, int h, int d, int nbx, int nby, int nbz,
+                      float* out_min, float* out_max);
+/* main() of the three iso shaders; block_min/max may be NULL for mode 0.  out_iters: loop iterations per pixel. */
+uint64_t orc_iso_render(const orc_iso_params* p, const float* vol_r16f, const float* block_min, const float* block_max,
+                        float* out_rgba, uint32_t* out_iters);
+
 int orc_max_threads(void);
 
 #ifdef __cplusplus

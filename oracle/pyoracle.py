@@ -25,6 +25,16 @@ class Rc1pParams(C.Structure):
                 ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
 
 
+class IsoParams(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int),
+                ("vol_w", C.c_int), ("vol_h", C.c_int), ("vol_d", C.c_int),
+                ("voxel", C.c_float * 3), ("eye", C.c_float * 3), ("lookat", C.c_float * 9),
+                ("tan_fovy", C.c_float), ("aspect", C.c_float), ("mode", C.c_int),
+                ("isovalue", C.c_float), ("step_small", C.c_float), ("step_large", C.c_float), ("step_range", C.c_float),
+                ("color", C.c_float * 4), ("num_blocks", C.c_int * 3), ("weight_mode", C.c_int),
+                ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -44,6 +54,9 @@ def lib():
         L.orc_rc1pass_render.restype = C.c_uint64
         L.orc_blit_over_white.argtypes = [_P, C.c_int64, _P]
         L.orc_max_threads.restype = C.c_int
+        L.orc_block_minmax.argtypes = [_P, C.c_int] + [C.c_int] * 6 + [_P, _P]
+        L.orc_iso_render.argtypes = [C.POINTER(IsoParams), _P, _P, _P, _P, _P]
+        L.orc_iso_render.restype = C.c_uint64
         _lib = L
     return _lib
 
@@ -134,3 +147,39 @@ def blit_over_white(rgba):
 
 def max_threads():
     return lib().orc_max_threads()
+
+
+def block_minmax(voxels, num_blocks):
+    """ComputeBlocksFromVolume: returns (min, max) float32 arrays indexed [bz, by, bx]."""
+    v = np.ascontiguousarray(voxels)
+    d, h, w = v.shape
+    nbx, nby, nbz = num_blocks
+    mn = np.empty((nbz, nby, nbx), np.float32)
+    mx = np.empty((nbz, nby, nbx), np.float32)
+    lib().orc_block_minmax(_ptr(v), _DT[v.dtype], w, h, d, nbx, nby, nbz, _ptr(mn), _ptr(mx))
+    return mn, mx
+
+
+def iso_params(cam, width, height, vol_shape_zyx, mode, isovalue=0.5, step_small=0.05, step_large=1.0, step_range=0.1,
+               color=(0.66, 0.6, 0.05, 1.0), num_blocks=(4, 4, 4), voxel=(1.0, 1.0, 1.0), rows=None, threads=0):
+    p = IsoParams()
+    p.width, p.height = width, height
+    p.vol_d, p.vol_h, p.vol_w = vol_shape_zyx
+    p.voxel[:] = voxel
+    p.eye[:] = list(cam.eye)
+    p.lookat[:] = list(cam.lookat)
+    p.tan_fovy, p.aspect, p.mode = cam.tan_fovy, cam.aspect, mode
+    p.isovalue, p.step_small, p.step_large, p.step_range = isovalue, step_small, step_large, step_range
+    p.color[:] = color
+    p.num_blocks[:] = num_blocks
+    p.row_begin, p.row_end, p.row_stride = rows or (0, height, 1)
+    p.threads = threads
+    return p
+
+
+def iso_render(p, vol_r16f, block_min=None, block_max=None, want_iters=False):
+    vol = np.ascontiguousarray(vol_r16f, np.float32)
+    out = np.zeros((p.height, p.width, 4), np.float32)
+    it = np.zeros((p.height, p.width), np.uint32) if want_iters else None
+    total = lib().orc_iso_render(C.byref(p), _ptr(vol), _ptr(block_min), _ptr(block_max), _ptr(out), _ptr(it))
+    return out, int(total), it
