@@ -1,0 +1,262 @@
+// BaseVolumeRenderer, the CUDA plugins and the headless RenderingManager (see volrenderbase.h).
+#include "volrenderbase.h"
+#include "vrbapi.h"
+
+#include <sys/stat.h>
+#include <algorithm>
+
+// ---- BaseVolumeRenderer (cppvolrend/volrenderbase.cpp:5-119) -------------------------------------------------
+BaseVolumeRenderer::BaseVolumeRenderer() {}
+BaseVolumeRenderer::~BaseVolumeRenderer() { Clean(); }
+
+void BaseVolumeRenderer::SetExternalResources(vis::DataManager* data_mgr, vis::RenderingParameters* rdr_prm) {
+  m_ext_data_manager = data_mgr;
+  m_ext_rendering_parameters = rdr_prm;
+}
+
+bool BaseVolumeRenderer::Fail(const char* what) {
+  const VrbApi* a = VrbApi::Get();
+  m_err = std::string(what) + ": " + (a ? a->last_error() : "libvrb200.so not loaded");
+  return false;
+}
+
+void BaseVolumeRenderer::Clean() {
+  if (m_dev) { if (const VrbApi* a = VrbApi::Get()) a->renderer_destroy(m_dev); m_dev = nullptr; }
+  SetBuilt(false);
+}
+
+bool BaseVolumeRenderer::CreateDeviceRenderer(int kind, int w, int h) {
+  if (IsBuilt()) Clean();                                               // Init is re-entrant (rc1prenderer.cpp:52)
+  if (!m_ext_data_manager || !m_ext_data_manager->HasVolumeTexture()) { m_err = "no volume texture"; return false; }   // :54
+  const VrbApi* a = VrbApi::Get(&m_err);
+  if (!a) return false;
+  if (a->renderer_create(m_ext_data_manager->Context(), kind, &m_dev) != VRB_OK) { m_dev = nullptr; return Fail("vrb_renderer_create"); }
+  if (a->renderer_init(m_dev, w, h) != VRB_OK) { Fail("vrb_renderer_init"); a->renderer_destroy(m_dev); m_dev = nullptr; return false; }
+  m_width = w; m_height = h;
+  return true;
+}
+
+void BaseVolumeRenderer::Reshape(int w, int h) {
+  if (!m_dev) return;
+  const VrbApi* a = VrbApi::Get();
+  if (a && a->renderer_reshape(m_dev, w, h) == VRB_OK) { m_width = w; m_height = h; }
+  SetOutdated();
+}
+
+void BaseVolumeRenderer::PrepareRender(vis::Camera* camera) {
+  if (IsOutdated()) {
+    if (Update(camera)) vr_outdated = false;
+  }
+}
+
+void BaseVolumeRenderer::Redraw() {
+  if (!m_dev) return;
+  const VrbApi* a = VrbApi::Get();
+  if (a && a->renderer_redraw(m_dev, vr_pixel_multiscaling_mode) != VRB_OK) Fail("vrb_renderer_redraw");
+}
+
+void* BaseVolumeRenderer::GetScreenDevicePointer(int* w, int* h) {
+  void* p = nullptr;
+  const VrbApi* a = VrbApi::Get();
+  if (!m_dev || !a || a->renderer_frame(m_dev, &p, w, h) != VRB_OK) return nullptr;
+  return p;
+}
+bool BaseVolumeRenderer::ReadFrameRGB8(std::vector<uint8_t>& out, int* w, int* h) {
+  const VrbApi* a = VrbApi::Get();
+  if (!m_dev || !a) return false;
+  out.resize((size_t)m_width * m_height * 3);
+  if (a->renderer_read_frame(m_dev, out.data(), VRB_FRAME_RGB8_OVER_WHITE) != VRB_OK) return Fail("vrb_renderer_read_frame");
+  if (w) *w = m_width;
+  if (h) *h = m_height;
+  return true;
+}
+bool BaseVolumeRenderer::ReadFrameRGBA32F(std::vector<float>& out, int* w, int* h) {
+  const VrbApi* a = VrbApi::Get();
+  if (!m_dev || !a) return false;
+  out.resize((size_t)m_width * m_height * 4);
+  if (a->renderer_read_frame(m_dev, out.data(), VRB_FRAME_RGBA32F) != VRB_OK) return Fail("vrb_renderer_read_frame");
+  if (w) *w = m_width;
+  if (h) *h = m_height;
+  return true;
+}
+double BaseVolumeRenderer::LastRedrawMs() {
+  double ms = 0.0;
+  const VrbApi* a = VrbApi::Get();
+  if (m_dev && a) a->renderer_counters(m_dev, nullptr, &ms);
+  return ms;
+}
+
+// ---- CudaRayCasting1Pass -------------------------------------------------------------------------------------
+CudaRayCasting1Pass::CudaRayCasting1Pass() : m_u_step_size(0.5f), m_apply_gradient_shading(false), m_skip_block(0) {}   // rc1prenderer.cpp:18-27
+
+bool CudaRayCasting1Pass::Init(int w, int h) {
+  if (!CreateDeviceRenderer(VRB_RC1PASS, w, h)) return false;
+  vrb_rc1pass_params p;
+  if (VrbApi::Get()->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  m_u_step_size = p.step_size;                 // Init estimates the initial step: 0.5/sqrt(3) * |voxel scale| (:61-63)
+  SetBuilt(true);
+  SetOutdated();
+  return true;
+}
+
+bool CudaRayCasting1Pass::Update(vis::Camera* camera) {
+  if (!m_dev || !camera) return false;
+  const VrbApi* a = VrbApi::Get();
+  vrb_rc1pass_params p;
+  if (a->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  p.step_size = m_u_step_size; p.apply_gradient_shading = m_apply_gradient_shading ? 1 : 0; p.skip_block = m_skip_block;
+  if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
+  vrb_camera c; vrb_light l;
+  camera->FillUniforms(&c);
+  m_ext_rendering_parameters->FillUniforms(&l);
+  if (a->renderer_update(m_dev, &c, &l) != VRB_OK) return Fail("vrb_renderer_update");
+  return true;
+}
+
+void CudaRayCasting1Pass::FillParameterSpace(ParameterSpace& pspace) {
+  pspace.ClearParameterDimensions();
+  pspace.AddParameterDimension(new ParameterRangeFloat("StepSize", &m_u_step_size, 0.2f, 2.0f, 0.1f));
+}
+
+// ---- CudaRayCasting1PassIso ----------------------------------------------------------------------------------
+CudaRayCasting1PassIso::CudaRayCasting1PassIso(int kind)
+    : m_u_isovalue(0.5f), m_u_step_size_small(0.05f), m_u_step_size_large(1.0f), m_u_step_size_range(0.1f), m_kind(kind) {
+  m_u_color[0] = 0.66f; m_u_color[1] = 0.6f; m_u_color[2] = 0.05f; m_u_color[3] = 1.0f;
+  m_num_blocks[0] = m_num_blocks[1] = m_num_blocks[2] = kind == VRB_ISO_SKIP_V2 ? 32 : 4;
+}
+const char* CudaRayCasting1PassIso::GetName() {
+  switch (m_kind) {
+    case VRB_ISO_SKIP_V1: return "1-Pass - Custom Isosurface Raycaster Adaptive (CUDA B200)";
+    case VRB_ISO_SKIP_V2: return "Empty Sapce Skipping V2 (CUDA B200)";
+    default: return "1-Pass - Isosurface Raycaster Adaptive (CUDA B200)";
+  }
+}
+bool CudaRayCasting1PassIso::Init(int w, int h) {
+  if (IsBuilt()) Clean();
+  if (!m_ext_data_manager || !m_ext_data_manager->HasVolumeTexture()) { m_err = "no volume texture"; return false; }
+  const VrbApi* a = VrbApi::Get(&m_err);
+  if (!a) return false;
+  if (a->renderer_create(m_ext_data_manager->Context(), m_kind, &m_dev) != VRB_OK) { m_dev = nullptr; return Fail("vrb_renderer_create"); }
+  vrb_iso_params p;
+  a->renderer_get_params(m_dev, &p, sizeof(p));
+  for (int i = 0; i < 3; i++) p.num_blocks[i] = m_num_blocks[i];       // numBlocks is fixed at Init in the reference
+  if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK || a->renderer_init(m_dev, w, h) != VRB_OK) {
+    Fail("iso Init"); a->renderer_destroy(m_dev); m_dev = nullptr; return false;
+  }
+  m_width = w; m_height = h;
+  SetBuilt(true);
+  SetOutdated();
+  return true;
+}
+bool CudaRayCasting1PassIso::Update(vis::Camera* camera) {
+  if (!m_dev || !camera) return false;
+  const VrbApi* a = VrbApi::Get();
+  vrb_iso_params p;
+  if (a->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  p.isovalue = m_u_isovalue; p.step_size_small = m_u_step_size_small; p.step_size_large = m_u_step_size_large;
+  p.step_size_range = m_u_step_size_range;
+  for (int i = 0; i < 4; i++) p.color[i] = m_u_color[i];
+  if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
+  vrb_camera c; vrb_light l;
+  camera->FillUniforms(&c);
+  m_ext_rendering_parameters->FillUniforms(&l);
+  if (a->renderer_update(m_dev, &c, &l) != VRB_OK) return Fail("vrb_renderer_update");
+  return true;
+}
+void CudaRayCasting1PassIso::FillParameterSpace(ParameterSpace& pspace) {
+  pspace.ClearParameterDimensions();
+  pspace.AddParameterDimension(new ParameterRangeFloat("StepSizeSmall", &m_u_step_size_small, 0.01f, 0.25f, 0.05f));
+  pspace.AddParameterDimension(new ParameterRangeFloat("StepSizeLarge", &m_u_step_size_large, 0.25f, 2.0f, 0.25f));
+  pspace.AddParameterDimension(new ParameterRangeFloat("StepSizeRange", &m_u_step_size_range, 0.05f, 0.26f, 0.05f));
+}
+
+// ---- RenderingManager ----------------------------------------------------------------------------------------
+static RenderingManager* g_instance = nullptr;
+RenderingManager* RenderingManager::Instance() { if (!g_instance) g_instance = new RenderingManager(); return g_instance; }
+void RenderingManager::DestroyInstance() { delete g_instance; g_instance = nullptr; }
+RenderingManager::~RenderingManager() {
+  if (m_eval_csvfile.is_open()) m_eval_csvfile.close();
+  for (auto* r : m_renderers) delete r;                                 // CloseFunc (:372-379)
+}
+
+void RenderingManager::AddVolumeRenderer(BaseVolumeRenderer* volrend) {
+  m_renderers.push_back(volrend);
+  m_names.push_back(volrend->GetName());
+}
+
+bool RenderingManager::InitData(vis::StructuredGridVolume* vol, vis::TransferFunction1D* tf, int device, int w, int h) {
+  m_w = w; m_h = h;
+  if (!m_data_mgr.InitDevice(device)) { m_err = m_data_mgr.LastError(); delete vol; delete tf; return false; }
+  if (!m_data_mgr.SetCurrentVolume(vol)) { m_err = m_data_mgr.LastError(); delete tf; return false; }
+  if (!m_data_mgr.SetCurrentTransferFunction(tf)) { m_err = m_data_mgr.LastError(); return false; }
+  m_camera.UpdateAspectRatio((float)w, (float)h);
+  for (auto* r : m_renderers) r->SetExternalResources(&m_data_mgr, &m_rdr_params);   // :160-161
+  return true;
+}
+
+bool RenderingManager::SetCurrentVolumeRenderer(int id) {
+  if (id < 0 || id >= (int)m_renderers.size()) { m_err = "renderer id out of range"; return false; }
+  if (m_current >= 0) m_renderers[m_current]->Clean();                  // :523
+  m_current = id;
+  BaseVolumeRenderer* r = m_renderers[id];
+  if (r->GetDataTypeSupport() != m_data_mgr.GetInputVolumeDataType()) { m_err = "data type not supported"; m_current = -1; return false; }   // :526-536
+  if (!r->Init(m_w, m_h)) { m_err = r->LastError(); return false; }
+  r->FillParameterSpace(m_eval_paramspace);                             // :539
+  return true;
+}
+
+void RenderingManager::Reshape(int w, int h) {
+  m_w = w; m_h = h;
+  m_camera.UpdateAspectRatio((float)w, (float)h);
+  if (BaseVolumeRenderer* r = CurrentRenderer()) r->Reshape(w, h);
+}
+
+bool RenderingManager::Display() {
+  BaseVolumeRenderer* r = CurrentRenderer();
+  if (!r || !r->IsBuilt()) { m_err = "no current renderer"; return false; }
+  if (m_eval_running) r->SetOutdated();                                 // :176-180
+  r->PrepareRender(&m_camera);                                          // :199
+  switch (r->GetCurrentMultiScalingMode()) {                            // f_render[mode] (:1195-1217)
+    case BaseVolumeRenderer::MULTIPLE_RAYS_PER_PIXEL: r->MultiSampleRedraw(); break;
+    case BaseVolumeRenderer::DOWN_SCALING_RENDER: r->DownScalingRedraw(); break;
+    case BaseVolumeRenderer::UP_SCALING_RENDER: r->UpScalingRedraw(); break;
+    default: r->Redraw();
+  }
+  if (!m_eval_running) return true;
+  // Evaluation bookkeeping (:261-317).  The reference measures wall-clock time between samples; the headless
+  // build has no swap to wait on, so it sums the device time of each Redraw (CUDA events on the launch stream).
+  m_eval_accum_ms += r->LastRedrawMs();
+  if (++m_eval_currframe < m_eval_numframes) return true;
+  const double time_per_frame = m_eval_accum_ms / m_eval_numframes, fps = 1000.0 / time_per_frame;
+  std::string img = std::to_string(m_eval_currsample);
+  img = std::string(4 - std::min<size_t>(4, img.size()), '0') + img + ".png";
+  if (m_sink) {
+    std::vector<uint8_t> rgb; int w = 0, h = 0;
+    if (r->ReadFrameRGB8(rgb, &w, &h)) m_sink(m_sink_user, img.c_str(), rgb.data(), w, h);
+  }
+  for (int i = 0; i < m_eval_paramspace.GetNumDimensions(); i++) m_eval_csvfile << m_eval_paramspace.GetDimensionValue(i) << ",";
+  m_eval_csvfile << std::to_string(time_per_frame) << "," << std::to_string(fps) << ",\"" << img << "\"\n";
+  if (m_eval_paramspace.IncrEvaluation()) {
+    m_eval_currsample++; m_eval_currframe = 0; m_eval_accum_ms = 0.0;
+  } else {
+    m_eval_paramspace.EndEvaluation();
+    m_eval_running = false;
+    m_eval_csvfile.close();
+  }
+  return true;
+}
+
+bool RenderingManager::StartEvaluation(const std::string& dir, int numframes) {
+  BaseVolumeRenderer* r = CurrentRenderer();
+  if (!r) { m_err = "no current renderer"; return false; }
+  ::mkdir(dir.c_str(), 0755);
+  m_eval_csvfile.open(dir + "/eval.csv");
+  if (!m_eval_csvfile.is_open()) { m_err = "cannot open " + dir + "/eval.csv"; return false; }
+  m_eval_numframes = std::max(numframes, 1);
+  m_eval_paramspace.StartEvaluation();                                  // :842
+  for (int i = 0; i < m_eval_paramspace.GetNumDimensions(); i++) m_eval_csvfile << m_eval_paramspace.GetDimensionName(i) << ",";
+  m_eval_csvfile << "TimePerFrame (ms),FramesPerSecond,ImageFile\n";    // :849
+  m_eval_running = true; m_eval_currframe = 0; m_eval_currsample = 0; m_eval_accum_ms = 0.0;
+  r->SetOutdated();
+  return true;
+}

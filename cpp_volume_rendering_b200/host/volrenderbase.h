@@ -1,0 +1,133 @@
+// BaseVolumeRenderer (cppvolrend/volrenderbase.h:25-97) and RenderingManager (cppvolrend/renderingmanager.h:29-167)
+// for the headless build: same virtuals, same call order, GL members replaced by a device frame owned by
+// libvrb200.so.  The CUDA plugins below drop in beside the reference's GLSL renderers through the same
+// AddVolumeRenderer(new X()) call (cppvolrend/main.cpp:62-79).
+#pragma once
+#include "vrbhost.h"
+
+class BaseVolumeRenderer {
+ public:
+  enum MULTISCALING { SINGLE_RAY_PER_PIXEL = 0, MULTIPLE_RAYS_PER_PIXEL = 1, DOWN_SCALING_RENDER = 2, UP_SCALING_RENDER = 3 };
+  BaseVolumeRenderer();
+  virtual ~BaseVolumeRenderer();
+
+  void SetExternalResources(vis::DataManager* data_mgr, vis::RenderingParameters* rdr_prm);   // volrenderbase.cpp:20-24
+
+  virtual const char* GetName() = 0;
+  virtual const char* GetAbbreviationName() = 0;
+  virtual void Clean();
+  virtual void ReloadShaders() {}                       // nothing to reload: kernels are compiled ahead of time
+  virtual bool Init(int shader_width, int shader_height) = 0;
+  virtual bool Update(vis::Camera* camera) = 0;
+  virtual void Redraw();
+  virtual void MultiSampleRedraw() { Redraw(); }        // multiscaling filters are a "next" row
+  virtual void DownScalingRedraw() { Redraw(); }
+  virtual void UpScalingRedraw() { Redraw(); }
+  virtual void Reshape(int w, int h);
+  virtual void SetImGuiComponents() {}
+  virtual vis::GRID_VOLUME_DATA_TYPE GetDataTypeSupport() = 0;
+  virtual void FillParameterSpace(ParameterSpace&) {}
+
+  void PrepareRender(vis::Camera* camera);              // volrenderbase.cpp:77-84: Update() if outdated
+  virtual void SetOutdated() { vr_outdated = true; }
+  bool IsOutdated() const { return vr_outdated; }
+  bool IsBuilt() const { return vr_built; }
+  bool IsPixelMultiScalingSupported() const { return vr_pixel_multiscaling_support; }
+  int GetCurrentMultiScalingMode() const { return vr_pixel_multiscaling_mode; }
+  void SetCurrentMultiScalingMode(int f) { vr_pixel_multiscaling_mode = f; }
+
+  // Replaces GetScreenTextureID() (:73-75): device pointer to the RGBA16F frame (row 0 = bottom).
+  virtual void* GetScreenDevicePointer(int* w, int* h);
+  // Replaces the blit + glReadPixels of the screenshot path (renderingmanager.cpp:409-419,476-492).
+  bool ReadFrameRGB8(std::vector<uint8_t>& out, int* w, int* h);
+  bool ReadFrameRGBA32F(std::vector<float>& out, int* w, int* h);
+  double LastRedrawMs();
+  const std::string& LastError() const { return m_err; }
+
+ protected:
+  void SetBuilt(bool b) { vr_built = b; }
+  bool CreateDeviceRenderer(int kind, int w, int h);    // vrb_renderer_create + init; false on failure
+  bool Fail(const char* what);                          // records vrb_last_error()
+  bool vr_built = false, vr_outdated = true, vr_pixel_multiscaling_support = false;
+  int vr_pixel_multiscaling_mode = 0;
+  vis::DataManager* m_ext_data_manager = nullptr;
+  vis::RenderingParameters* m_ext_rendering_parameters = nullptr;
+  vrb_renderer* m_dev = nullptr;                        // stands where m_rdr_frame_to_screen + cp_geometry_pass stood
+  int m_width = 0, m_height = 0;
+  std::string m_err;
+};
+
+// ---- the CUDA plugins --------------------------------------------------------------------------------------
+// RayCasting1Pass (structured/rc1pass/rc1prenderer.{h,cpp})
+class CudaRayCasting1Pass : public BaseVolumeRenderer {
+ public:
+  CudaRayCasting1Pass();
+  const char* GetName() override { return "1-Pass - Ray Casting (CUDA B200)"; }
+  const char* GetAbbreviationName() override { return "cu_s_1rc"; }
+  vis::GRID_VOLUME_DATA_TYPE GetDataTypeSupport() override { return vis::GRID_VOLUME_DATA_TYPE::STRUCTURED; }
+  bool Init(int w, int h) override;
+  bool Update(vis::Camera* camera) override;
+  void FillParameterSpace(ParameterSpace& pspace) override;    // StepSize 0.2 .. 2.0 step 0.1 (rc1prenderer.cpp:225-229)
+  float m_u_step_size;                 // public ImGui-mutable members, as in rc1prenderer.h:62,75
+  bool m_apply_gradient_shading;
+  int m_skip_block;                    // new: 0 / 4 / 8 / 16 / 32 (lattice-preserving empty-space skipping)
+};
+
+// RayCasting1PassIsoAdapt / CustomRayCasting1PassIsoAdapt / CustomRayCasting1PassIsodfsAdapt
+class CudaRayCasting1PassIso : public BaseVolumeRenderer {
+ public:
+  explicit CudaRayCasting1PassIso(int kind);          // VRB_ISO_ADAPT, VRB_ISO_SKIP_V1, VRB_ISO_SKIP_V2
+  const char* GetName() override;
+  const char* GetAbbreviationName() override { return "cu_iso"; }
+  vis::GRID_VOLUME_DATA_TYPE GetDataTypeSupport() override { return vis::GRID_VOLUME_DATA_TYPE::STRUCTURED; }
+  bool Init(int w, int h) override;
+  bool Update(vis::Camera* camera) override;
+  void FillParameterSpace(ParameterSpace& pspace) override;    // rc1pisoadaptrenderer.cpp:191-197
+  float m_u_isovalue, m_u_step_size_small, m_u_step_size_large, m_u_step_size_range;
+  float m_u_color[4];
+  int m_num_blocks[3];
+ private:
+  int m_kind;
+};
+
+// ---- RenderingManager: registry + Display() order + evaluation loop ----------------------------------------
+class RenderingManager {
+ public:
+  static RenderingManager* Instance();
+  static void DestroyInstance();
+  void AddVolumeRenderer(BaseVolumeRenderer* volrend);                 // renderingmanager.cpp:119-123 (takes ownership)
+  // InitData (:126-172) without the #list_* files: the caller hands the dataset, TF, camera and screen size.
+  bool InitData(vis::StructuredGridVolume* vol, vis::TransferFunction1D* tf, int device, int w, int h);
+  bool SetCurrentVolumeRenderer(int id);                               // :521-540: Clean old, Init new, FillParameterSpace
+  BaseVolumeRenderer* CurrentRenderer() { return m_current < 0 ? nullptr : m_renderers[m_current]; }
+  int NumRenderers() const { return (int)m_renderers.size(); }
+  const char* RendererName(int id) { return m_names[id].c_str(); }
+  vis::Camera* GetCamera() { return &m_camera; }
+  vis::DataManager* GetDataManager() { return &m_data_mgr; }
+  vis::RenderingParameters* GetRenderingParameters() { return &m_rdr_params; }
+  void Reshape(int w, int h);                                          // :321-335
+  bool Display();                                                      // :174-319 (PrepareRender -> Redraw -> eval bookkeeping)
+  // "Start Evaluation" (:819-867): opens <dir>/eval.csv with the reference's header, then Display() advances the
+  // parameter space every m_eval_numframes frames.  write_png_cb (optional) receives each sample's RGB8 frame.
+  bool StartEvaluation(const std::string& dir, int numframes);
+  bool IsEvaluationRunning() const { return m_eval_running; }
+  typedef void (*FrameSink)(void* user, const char* filename, const uint8_t* rgb8, int w, int h);
+  void SetFrameSink(FrameSink cb, void* user) { m_sink = cb; m_sink_user = user; }
+  const std::string& LastError() const { return m_err; }
+ private:
+  RenderingManager() {}
+  ~RenderingManager();
+  std::vector<BaseVolumeRenderer*> m_renderers;
+  std::vector<std::string> m_names;
+  int m_current = -1, m_w = 0, m_h = 0;
+  vis::DataManager m_data_mgr;
+  vis::RenderingParameters m_rdr_params;
+  vis::Camera m_camera;
+  ParameterSpace m_eval_paramspace;
+  bool m_eval_running = false;
+  int m_eval_numframes = 100, m_eval_currframe = 0, m_eval_currsample = 0;
+  double m_eval_accum_ms = 0.0;
+  std::ofstream m_eval_csvfile;
+  FrameSink m_sink = nullptr; void* m_sink_user = nullptr;
+  std::string m_err;
+};

@@ -159,3 +159,39 @@ def default_light(n):
     s = n / 256.0
     l.position[:] = [-206.873 * s, -51.0699 * s, 557.011 * s]
     return l
+
+
+# ---------------------------------------------------------------------------------------------
+# Writers for the reference's on-disk formats (fixtures for the readers in host/vrbhost.cpp).
+def write_raw(directory, name, vox):
+    """<name>.<bytes>.<W>x<H>x<D>.raw (filename grammar of VolumeReader::readraw, reader.cpp:172-205)."""
+    d, h, w = vox.shape
+    path = os.path.join(directory, f"{name}.{vox.dtype.itemsize}.{w}x{h}x{d}.raw")
+    np.ascontiguousarray(vox).tofile(path)
+    return path
+
+
+def write_syn(path, vox):
+    """.syn text volume (reader.cpp:295-353): "W H D", a first record "1 0 0 0 W H D 0" defining the buffer the
+    reference leaves uninitialised, then one box record per run of equal non-zero voxels along x."""
+    assert vox.dtype == np.uint8
+    d, h, w = vox.shape
+    lines = [f"{w} {h} {d}", f"1 0 0 0 {w} {h} {d} 0"]
+    for z in range(d):
+        for y in range(h):
+            row = vox[z, y]
+            change = np.flatnonzero(np.diff(row)) + 1
+            starts = np.concatenate([[0], change]); ends = np.concatenate([change, [w]])
+            for x0, x1 in zip(starts, ends):
+                v = int(row[x0])
+                if v:
+                    lines.append(f"1 {x0} {y} {z} {x1} {y + 1} {z + 1} {v}" if x1 - x0 > 1 else f"0 {x0} {y} {z} {v}")
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    return path
+
+
+def write_tf1d(path, text=BONSAI_TF1D):
+    with open(path, "w") as f:
+        f.write(text + "\n")
+    return path

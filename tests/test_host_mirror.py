@@ -1,0 +1,112 @@
+"""The C++ host mirror of the reference's plugin interface (cpp_volume_rendering_b200/host): ParameterSpace,
+readers, camera uniforms on the CPU; RenderingManager sessions on the GPU."""
+import csv
+import os
+
+import numpy as np
+import pytest
+
+from cpp_volume_rendering_b200 import _capi, hostapi, inputs
+from oracle import pyoracle as O
+from oracle import pyref as R
+
+
+def test_parameterspace_matches_reference_sweep():
+    """Same odometer and float accumulation as cppvolrend/utils/parameterspace.cpp (18 StepSize samples, not 19)."""
+    for a, b in [((0.2, 2.0, 0.1), (1.0, 1.0, 1.0)), ((0.01, 0.25, 0.05), (0.25, 2.0, 0.25)), ((0.05, 0.26, 0.05), (0.0, 0.0, 0.5))]:
+        n, pairs = hostapi.parameterspace_sweep(a, b)
+        if R.available():
+            rn, rpairs = R.parameterspace_sweep(a, b)
+            assert n == rn and np.array_equal(pairs, rpairs)
+    n, pairs = hostapi.parameterspace_sweep((0.2, 2.0, 0.1), (1.0, 1.0, 1.0))
+    assert n == 18 and pairs[-1, 0] == np.float32(1.9000003)
+    L = hostapi.lib()
+    assert L.vrbh_parameterspace_numsteps_f(0.0, 1.0, 0.1) == 11 and L.vrbh_parameterspace_numsteps_i(0, 10, 1) == 11   # ParameterSpaceTest()
+    # the iso sweep of the checked-in eval CSVs (data/*/*.csv): 5 x 8 x 5 = 200 rows although NumSteps() says 6 x 8 x 6
+    counts = [hostapi.parameterspace_sweep(r, (0.0, 0.0, 1.0))[0] for r in [(0.01, 0.25, 0.05), (0.25, 2.0, 0.25), (0.05, 0.26, 0.05)]]
+    assert counts == [5, 8, 5]
+
+
+def test_tf1d_reader_matches_oracle_and_reference(tmp_path, bonsai_table):
+    p = inputs.write_tf1d(str(tmp_path / "bonsai_01.tf1d"))
+    table, ext = hostapi.read_tf1d(p)
+    assert not ext and np.array_equal(table, bonsai_table)
+    q = inputs.write_tf1d(str(tmp_path / "ext.tf1d"), "linear\n2 63 1\n2\n1 0 0 0\n0 0 1 63\n3\n0 0\n2.5 20\n0.5 63")
+    table, ext = hostapi.read_tf1d(q)
+    tf = inputs.parse_tf1d(q)
+    assert ext and table.shape == (64, 4) and np.array_equal(table, inputs.tf_build_linear(tf))
+    assert np.array_equal(table, O.tf_build_linear(tf["rgb_pts"], tf["a_pts"], 63))
+    with pytest.raises(RuntimeError):
+        hostapi.read_tf1d(str(tmp_path / "missing.tf1d"))
+
+
+def test_raw_and_syn_readers_roundtrip(tmp_path):
+    for dt in (np.uint8, np.uint16):
+        vox = inputs.synth_volume(0, dt, shape=(21, 13, 9))
+        p = inputs.write_raw(str(tmp_path), "synth", vox)
+        assert os.path.basename(p) == f"synth.{np.dtype(dt).itemsize}.21x13x9.raw"
+        assert np.array_equal(hostapi.read_volume(p), vox)
+    vox = inputs.synth_volume(0, np.uint8, shape=(17, 11, 6))
+    p = inputs.write_syn(str(tmp_path / "v.syn"), vox)
+    assert np.array_equal(hostapi.read_volume(p), vox)
+    with pytest.raises(RuntimeError):
+        hostapi.read_volume(str(tmp_path / "nope.raw"))
+    bad = tmp_path / "short.1.8x8x8.raw"
+    bad.write_bytes(b"\0" * 100)                      # truncated file
+    with pytest.raises(RuntimeError):
+        hostapi.read_volume(str(bad))
+
+
+def test_camera_uniforms_match_python_and_oracle():
+    for eye, up, size in [((256, 256, 512), (0, 1, 0), (768, 768)), ((-30.0, 260.0, 20.0), (0, 0, 1), (640, 360))]:
+        a = hostapi.camera_uniforms(eye, up=up, width=size[0], height=size[1])
+        b = inputs.make_camera(eye, up=up, width=size[0], height=size[1])
+        assert list(a.eye) == list(b.eye) and a.tan_fovy == b.tan_fovy and a.aspect == b.aspect
+        assert np.array_equal(np.array(a.lookat, np.float32), O.lookat3(eye, (0, 0, 0), up))
+
+
+def test_session_fails_loudly_without_gpu(tmp_path):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    vox = inputs.synth_volume(16, np.uint8)
+    v = inputs.write_raw(str(tmp_path), "s", vox); t = inputs.write_tf1d(str(tmp_path / "b.tf1d"))
+    with pytest.raises(RuntimeError, match="no CPU fallback|InitData"):
+        hostapi.run_session(v, t, "rc1pass", 32, 32, (16, 16, 32))
+
+
+@pytest.mark.gpu
+def test_manager_session_equals_direct_abi_render(tmp_path, ctx, bonsai_table):
+    n, w, h = 64, 160, 128
+    vox = inputs.synth_volume(n, np.uint8)
+    v = inputs.write_raw(str(tmp_path), "synth", vox); t = inputs.write_tf1d(str(tmp_path / "bonsai_01.tf1d"))
+    eye = (float(n), float(n), 2.0 * n)
+    ctx.upload_volume(vox); ctx.upload_tf(bonsai_table)
+    cam = inputs.make_camera(eye, width=w, height=h)
+    for name, kind in [("rc1pass", _capi.VRB_RC1PASS), ("iso", _capi.VRB_ISO_ADAPT), ("iso_skip_v1", _capi.VRB_ISO_SKIP_V1), ("iso_skip_v2", _capi.VRB_ISO_SKIP_V2)]:
+        displays, rgba, rgb8, rname = hostapi.run_session(v, t, name, w, h, eye, numframes=2)
+        assert displays == 2 and rname.endswith("(CUDA B200)")
+        r = _capi.Renderer(ctx, kind)
+        r.init(w, h); r.update(cam, inputs.default_light(256)); r.redraw()
+        direct = r.read_frame(_capi.VRB_FRAME_RGBA32F)
+        r.close()
+        assert np.array_equal(rgba, direct), name
+        assert np.array_equal(rgb8, O.blit_over_white(rgba))
+        assert (rgba[..., 3] > 0).mean() > 0.05
+
+
+@pytest.mark.gpu
+def test_evaluation_writes_reference_csv_schema(tmp_path):
+    vox = inputs.synth_volume(48, np.uint8)
+    v = inputs.write_raw(str(tmp_path), "synth", vox); t = inputs.write_tf1d(str(tmp_path / "bonsai_01.tf1d"))
+    out = str(tmp_path / "eval_rc1p")
+    displays, rgba, _, _ = hostapi.run_session(v, t, "rc1pass", 96, 96, (48.0, 48.0, 96.0), eval_dir=out, numframes=3)
+    rows = list(csv.reader(open(os.path.join(out, "eval.csv"))))
+    assert rows[0] == ["StepSize", "TimePerFrame (ms)", "FramesPerSecond", "ImageFile"]      # renderingmanager.cpp:845-849
+    assert len(rows) == 1 + 18 and displays == 18 * 3
+    assert rows[1][0] == "0.200000" and rows[1][3] == "0000.png" and rows[18][3] == "0017.png"
+    assert all(float(r[1]) > 0 and abs(float(r[2]) - 1000.0 / float(r[1])) < 1e-3 * float(r[2]) + 1e-3 for r in rows[1:])
+    out2 = str(tmp_path / "eval_iso")
+    displays, _, _, _ = hostapi.run_session(v, t, "iso_skip_v2", 64, 64, (48.0, 48.0, 96.0), eval_dir=out2, numframes=1, max_samples=7)
+    rows = list(csv.reader(open(os.path.join(out2, "eval.csv"))))
+    assert rows[0][:3] == ["StepSizeSmall", "StepSizeLarge", "StepSizeRange"] and len(rows) == 1 + 7
