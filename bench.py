@@ -164,9 +164,13 @@ def run_cuda(args):
     prm.skip_block = args.skip
     prm.tf_in_smem = args.tf_smem
     prm.exact_filter = args.exact
+    r.set_params(prm)
     if world > 1:
-        r.set_partition(rank, world, 32)
-    frame_ptr, fw, fh = r.frame_ptr()
+        # image tiles dealt round-robin; every rank's kernel stores its pixels straight into rank 0's frame (CUDA IPC
+        # peer memory over NVLink) — no collective on the frame
+        from cpp_volume_rendering_b200 import multigpu
+        multigpu.setup_fused_gather(r, rank, world, tile=32, mode=_capi.VRB_GATHER_ROOT)
+    flag = torch.zeros(1, dtype=torch.int32, device=dev)
 
     # sample count of this frame (instrumented launch, untimed)
     prm.count_samples = 1
@@ -181,19 +185,12 @@ def run_cuda(args):
         dist.all_reduce(fetched)
     fetched_total = int(fetched.item())
 
-    frame_t = None
-    if world > 1:
-        # wrap the library's frame as a torch tensor for the NCCL exchange (tiles are disjoint, others' are 0)
-        class _Wrap:
-            __cuda_array_interface__ = {"shape": (fh, fw, 4), "typestr": "<f2", "data": (frame_ptr, False), "version": 3}
-        frame_t = torch.as_tensor(_Wrap(), device=dev)
-
     def step():
         r.update(cam, light)
         r.redraw()
         if world > 1:
             with torch.cuda.stream(stream):
-                dist.all_reduce(frame_t)
+                dist.all_reduce(flag)      # 4-byte end-of-frame barrier: rank 0 knows every peer's tiles have landed
 
     def barrier():
         if world > 1:
@@ -226,6 +223,29 @@ def run_cuda(args):
         kernel_ms.append(r.counters()[1])
     k_ms = float(np.mean(kernel_ms))
 
+    # the same frame with the repo's block empty-space skipping (config 2 names 4/8/16/32-voxel blocks): identical image,
+    # fewer fetches — reported beside the headline, which keeps every lattice sample
+    skip_info = {}
+    if not args.skip:
+        for blk in (8,):
+            prm.skip_block = blk
+            r.set_params(prm)
+            for _ in range(3):
+                step()
+            barrier()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record(stream)
+            for _ in range(args.steps):
+                step()
+            s1.record(stream)
+            barrier()
+            tt = torch.tensor([s0.elapsed_time(s1)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            skip_info[f"block{blk}"] = {"ms_per_step": float(tt.item()) / args.steps, "fps": 1e3 * args.steps / float(tt.item())}
+        prm.skip_block = 0
+        r.set_params(prm)
+
     # e2e through the C ABI with host buffers: camera/light structs in, RGBA16F frame out to pinned memory
     pinned = torch.empty((IMG_H, IMG_W, 4), dtype=torch.float16).pin_memory()
     d2h = pinned.numel() * 2
@@ -235,7 +255,7 @@ def run_cuda(args):
         r.redraw()
         if world > 1:
             with torch.cuda.stream(stream):
-                dist.all_reduce(frame_t)
+                dist.all_reduce(flag)
         if rank == 0 or world == 1:
             r.read_frame_into(pinned.data_ptr())   # d2h + synchronise
         else:
@@ -272,10 +292,10 @@ def run_cuda(args):
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(args.skip), "volume": f"{VOL_N}^3 u16 -> R16F texture", "image": f"{IMG_W}x{IMG_H}",
                        "step_voxels": STEP, "tf": "bonsai_01.tf1d", "camera": "Initial State (N,N,2N)",
-                       "partition": f"image tiles 32x32 round-robin over {world} rank(s)" + (", NCCL all_reduce of disjoint tiles" if world > 1 else ""),
+                       "partition": f"image tiles 32x32 round-robin over {world} rank(s)" + (", fused peer-memory gather into rank 0 + 4-byte NCCL end-of-frame barrier" if world > 1 else ""),
                        "l2_policy": "inputs_larger_than_l2 (256 MiB R16F volume vs 126 MB L2)",
                        "samples_per_frame": fetched_total, "fps": 1e3 / ms_per_step, "init_ms_volume_upload": init_ms,
-                       "tf_in_smem": args.tf_smem, "exact_filter": args.exact, "skip_block": args.skip},
+                       "tf_in_smem": args.tf_smem, "exact_filter": args.exact, "skip_block": args.skip, "with_skipping": skip_info},
             "e2e": {"value": fetched_total / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": ctypes.sizeof(_capi.Camera) + ctypes.sizeof(_capi.Light),
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "fps": 1e3 / e2e_ms},
             "gpu_launches": args.steps,
@@ -294,6 +314,10 @@ def run_cuda(args):
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"full {IMG_W}x{IMG_H} frame ({total} samples, best of 2, {secs:.2f} s), oracle/liboracle.so OpenMP over rows"}
         print(json.dumps(line))
+    if world > 1:
+        barrier()
+        r.set_peers([], rank, _capi.VRB_GATHER_NONE)
+        barrier()
     r.close()
     ctx.close()
     if world > 1:

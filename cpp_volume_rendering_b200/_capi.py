@@ -16,6 +16,7 @@ VRB_U8, VRB_U16, VRB_F32 = 0, 1, 2
 (VRB_RC1PASS, VRB_ISO_ADAPT, VRB_ISO_SKIP_V1, VRB_ISO_SKIP_V2, VRB_DOS_CONE, VRB_EBS_SAT, VRB_VCT,
  VRB_SBTM_DOS) = range(8)
 VRB_FRAME_RGBA16F, VRB_FRAME_RGB8_OVER_WHITE, VRB_FRAME_RGBA32F = 0, 1, 2
+VRB_GATHER_NONE, VRB_GATHER_ROOT, VRB_GATHER_ALL = 0, 1, 2
 
 _DTYPES = {np.dtype(np.uint8): VRB_U8, np.dtype(np.uint16): VRB_U16, np.dtype(np.float32): VRB_F32}
 
@@ -71,6 +72,8 @@ SIGNATURES = {
     "vrb_renderer_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_double)]),
     "vrb_iso_read_blocks": (C.c_int, [_P, _P, _P]),
     "vrb_renderer_set_partition": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
+    "vrb_renderer_frame_export": (C.c_int, [_P, _P]),
+    "vrb_renderer_set_peers": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int]),
     "vrb_bench_tex_peak": (C.c_int, [_P, C.POINTER(C.c_double)]),
 }
 
@@ -209,6 +212,16 @@ class Renderer:
         s, ms = C.c_uint64(), C.c_double()
         _check(lib().vrb_renderer_counters(self._h, C.byref(s), C.byref(ms)))
         return s.value, ms.value
+
+    def frame_export(self):
+        buf = C.create_string_buffer(64)
+        _check(lib().vrb_renderer_frame_export(self._h, buf))
+        return buf.raw
+
+    def set_peers(self, handles, rank, mode):
+        """handles: list of 64-byte IPC handles in rank order (own entry ignored); mode VRB_GATHER_*."""
+        blob = b"".join(handles) if handles else b""
+        _check(lib().vrb_renderer_set_peers(self._h, blob if handles else None, len(handles), rank, mode))
 
     def read_blocks(self, num_blocks):
         nbx, nby, nbz = num_blocks

@@ -96,6 +96,7 @@ struct IsoArgs {
   float nb[3]; int nbi[3];
   const float* bmin; const float* bmax;
   uint2* frame;
+  uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
   unsigned long long* iters;
   int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble;
   unsigned* queue;
@@ -256,7 +257,10 @@ __global__ void __launch_bounds__(ISO_THREADS, 6) iso_kernel(const __grid_consta
         }
       }
     }
-    a.frame[(size_t)py * a.width + px] = make_uint2(pack_half2(dst.x, dst.y), pack_half2(dst.z, dst.w));
+    const uint2 texel = make_uint2(pack_half2(dst.x, dst.y), pack_half2(dst.z, dst.w));
+    const size_t o = (size_t)py * a.width + px;
+    a.frame[o] = texel;
+    for (int q = 0; q < a.n_peers; q++) a.peer[q][o] = texel;
   }
   if (COUNT) {
     for (int o = 16; o > 0; o >>= 1) nit += __shfl_xor_sync(0xffffffffu, nit, o);
@@ -344,6 +348,8 @@ class IsoRenderer : public RendererImpl {
       a.bmin = blocks_.mn; a.bmax = blocks_.mx;
     }
     a.frame = (uint2*)frame; a.iters = d_samples;
+    a.n_peers = n_peer_frames;
+    for (int q = 0; q < n_peer_frames; q++) a.peer[q] = (uint2*)peer_frames[q];
     a.rank = rank; a.n_ranks = n_ranks; a.tile = part_tile;
     a.tiles_x = (width + part_tile - 1) / part_tile;
     a.n_tiles = a.tiles_x * ((height + part_tile - 1) / part_tile);

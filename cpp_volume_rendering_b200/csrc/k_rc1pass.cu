@@ -31,6 +31,7 @@ struct Rc1Args {
   float lookat[9];
   float tan_fovy, aspect, step;
   uint2* frame;              // RGBA16F
+  uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;   // frames of other ranks (fused gather over NVLink)
   unsigned long long* samples;
   // image-space partition: tiles of `tile` pixels dealt round-robin over ranks
   int rank, n_ranks, tile, tiles_x, n_tiles;
@@ -298,7 +299,12 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(cons
     }
   }
   // imageStore(OutputFrag, storePos, dst) — or the cleared 0 where the ray misses (ClearTexture fused)
-  if (valid) a.frame[(size_t)py * a.width + px] = make_uint2(pack_half2(r.dst.x, r.dst.y), pack_half2(r.dst.z, r.dst.w));
+  if (valid) {
+    const uint2 texel = make_uint2(pack_half2(r.dst.x, r.dst.y), pack_half2(r.dst.z, r.dst.w));
+    const size_t o = (size_t)py * a.width + px;
+    a.frame[o] = texel;
+    for (int q = 0; q < a.n_peers; q++) a.peer[q][o] = texel;
+  }
   }  // item loop
   if (COUNT) {
     for (int o = 16; o > 0; o >>= 1) nsamp += __shfl_xor_sync(0xffffffffu, nsamp, o);
@@ -371,6 +377,8 @@ class Rc1Pass : public RendererImpl {
     for (int i = 0; i < 9; i++) a.lookat[i] = cam.lookat[i];
     a.tan_fovy = cam.tan_fovy; a.aspect = cam.aspect; a.step = prm_.step_size;
     a.frame = (uint2*)frame; a.samples = d_samples;
+    a.n_peers = n_peer_frames;
+    for (int q = 0; q < n_peer_frames; q++) a.peer[q] = (uint2*)peer_frames[q];
     a.rank = rank; a.n_ranks = n_ranks; a.tile = part_tile;
     a.tiles_x = (width + part_tile - 1) / part_tile;
     a.n_tiles = a.tiles_x * ((height + part_tile - 1) / part_tile);

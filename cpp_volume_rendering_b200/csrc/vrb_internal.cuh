@@ -89,6 +89,13 @@ struct RendererImpl {
   vrb_light light{};
   bool have_cam = false;
   int rank = 0, n_ranks = 1, part_tile = 32;
+  // fused gather (vrb_renderer_set_peers): frames of other ranks mapped through CUDA IPC; the render kernels store
+  // each finished pixel into them as well, over NVLink, so no collective follows the launch
+  static constexpr int MAX_PEERS = 15;
+  void* peer_frames[MAX_PEERS] = {};
+  void* peer_opened[MAX_PEERS] = {};     // base pointers returned by cudaIpcOpenMemHandle (to close)
+  int n_peer_frames = 0;
+  void close_peers();
   unsigned long long* d_samples = nullptr;
   unsigned* d_queue = nullptr;          // 2 words, zero between launches: dynamic work queue of persistent kernels
   uint64_t last_samples = 0;

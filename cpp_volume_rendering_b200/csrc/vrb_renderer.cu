@@ -2,6 +2,7 @@
 // (cppvolrend/volrenderbase.h:25-97) and dispatch to the per-kind implementation.
 #include "vrb_internal.cuh"
 #include <vector>
+#include <cstring>
 
 namespace vrb {
 
@@ -16,7 +17,13 @@ int RendererImpl::alloc_frame(int w, int h) {
   return VRB_OK;
 }
 
+void RendererImpl::close_peers() {
+  for (int i = 0; i < MAX_PEERS; i++) if (peer_opened[i]) { cudaIpcCloseMemHandle(peer_opened[i]); peer_opened[i] = nullptr; }
+  n_peer_frames = 0;
+}
+
 void RendererImpl::free_frame() {
+  close_peers();   // peers hold handles of frames of this size only
   if (frame) cudaFree(frame);
   frame = nullptr; width = height = 0;
 }
@@ -169,6 +176,40 @@ int vrb_renderer_counters(vrb_renderer* r, uint64_t* samples, double* ms) {
     float t = 0.f;
     if (p->timed) VRB_CUDA(cudaEventElapsedTime(&t, p->ev0, p->ev1));
     *ms = (double)t;
+  }
+  return VRB_OK;
+}
+
+int vrb_renderer_frame_export(vrb_renderer* r, void* handle_out) {
+  VRB_REQUIRE(r && handle_out, VRB_ERR_INVALID, "vrb_renderer_frame_export: null argument");
+  RendererImpl* p = r->impl;
+  VRB_REQUIRE(p->frame, VRB_ERR_INVALID, "vrb_renderer_frame_export before Init");
+  static_assert(sizeof(cudaIpcMemHandle_t) == VRB_IPC_HANDLE_BYTES, "IPC handle size");
+  cudaIpcMemHandle_t h;
+  VRB_CUDA(cudaIpcGetMemHandle(&h, p->frame));
+  memcpy(handle_out, &h, sizeof(h));
+  return VRB_OK;
+}
+
+int vrb_renderer_set_peers(vrb_renderer* r, const void* handles, int n_ranks, int rank, int mode) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_set_peers: null renderer");
+  RendererImpl* p = r->impl;
+  VRB_CUDA(cudaSetDevice(p->ctx->device));
+  VRB_CUDA(cudaStreamSynchronize(p->ctx->stream));
+  p->close_peers();
+  if (mode == VRB_GATHER_NONE || n_ranks <= 1) return VRB_OK;
+  VRB_REQUIRE(handles && rank >= 0 && rank < n_ranks && n_ranks - 1 <= RendererImpl::MAX_PEERS, VRB_ERR_INVALID,
+              "vrb_renderer_set_peers: bad rank %d of %d", rank, n_ranks);
+  VRB_REQUIRE(mode == VRB_GATHER_ROOT || mode == VRB_GATHER_ALL, VRB_ERR_INVALID, "vrb_renderer_set_peers: bad mode %d", mode);
+  for (int q = 0; q < n_ranks; q++) {
+    if (q == rank) continue;
+    if (mode == VRB_GATHER_ROOT && q != 0) continue;        // only rank 0 collects
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char*)handles + (size_t)q * VRB_IPC_HANDLE_BYTES, sizeof(h));
+    void* ptr = nullptr;
+    VRB_CUDA(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    p->peer_opened[p->n_peer_frames] = ptr;
+    p->peer_frames[p->n_peer_frames++] = ptr;
   }
   return VRB_OK;
 }

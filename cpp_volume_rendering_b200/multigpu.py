@@ -1,0 +1,43 @@
+"""Image-space partition across ranks (one process per GPU).
+
+Plumbing only: torch.distributed carries the 64-byte IPC handles and the end-of-frame barrier; the pixels themselves
+are stored straight into the peers' frames by the render kernels (vrb_renderer_set_peers), so no collective touches
+the frame.  The reference has no multi-GPU path; parity is defined against the single-GPU frame.
+"""
+import numpy as np
+
+from . import _capi
+
+
+def tile_owner_map(width, height, tile, n_ranks):
+    """rank that renders each pixel: tiles of `tile` x `tile` pixels dealt round-robin in row-major tile order
+    (the rule of vrb_renderer_set_partition).  Returns int array [height, width]."""
+    tx = (width + tile - 1) // tile
+    ty = (height + tile - 1) // tile
+    ids = (np.arange(ty)[:, None] * tx + np.arange(tx)[None, :]) % n_ranks
+    return np.repeat(np.repeat(ids, tile, axis=0), tile, axis=1)[:height, :width]
+
+
+def exchange_handles(handle, group=None):
+    """all-gather of one bytes object per rank, returned in rank order."""
+    import torch.distributed as dist
+    out = [None] * dist.get_world_size(group)
+    dist.all_gather_object(out, handle, group=group)
+    return out
+
+
+def setup_fused_gather(renderer, rank, world, tile=32, mode=_capi.VRB_GATHER_ROOT, group=None):
+    """Partition the image over `world` ranks and map the peers' frames into `renderer`."""
+    renderer.set_partition(rank, world, tile)
+    if world > 1:
+        handles = exchange_handles(renderer.frame_export(), group)
+        renderer.set_peers(handles, rank, mode)
+
+
+def frame_barrier(device=None, group=None):
+    """All ranks' redraws have finished and their peer stores are visible: stream sync + a barrier."""
+    import torch
+    import torch.distributed as dist
+    if device is not None:
+        torch.cuda.synchronize(device)
+    dist.barrier(group=group)

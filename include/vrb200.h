@@ -161,6 +161,18 @@ int vrb_iso_read_blocks(vrb_renderer* r, float* host_min, float* host_max);
  * The frame keeps full size; tiles of other ranks stay 0. */
 int vrb_renderer_set_partition(vrb_renderer* r, int rank, int n_ranks, int tile);
 
+/* Fused gather: instead of a collective after the launch, the render kernels store every finished pixel into the
+ * frames of other ranks as well (peer memory over NVLink / NVSwitch, mapped through CUDA IPC; one process per GPU).
+ * vrb_renderer_frame_export writes this renderer's 64-byte IPC handle; the host exchanges the handles of all ranks
+ * (any transport: torch.distributed, MPI, a pipe) and hands the rank-ordered array to vrb_renderer_set_peers.
+ * mode VRB_GATHER_ROOT: every rank also writes into rank 0's frame; VRB_GATHER_ALL: into every rank's frame.
+ * The frames are complete once all ranks' redraws have finished (the host provides that barrier).
+ * Handles are invalidated by reshape / destroy: call again with VRB_GATHER_NONE or new handles. */
+#define VRB_IPC_HANDLE_BYTES 64
+typedef enum { VRB_GATHER_NONE = 0, VRB_GATHER_ROOT = 1, VRB_GATHER_ALL = 2 } vrb_gather_mode;
+int vrb_renderer_frame_export(vrb_renderer* r, void* handle_out);
+int vrb_renderer_set_peers(vrb_renderer* r, const void* handles, int n_ranks, int rank, int mode);
+
 /* ---- measurement ---------------------------------------------------------------------------- */
 /* Cache-resident trilinear R16F tex3D microbenchmark: the texture-fetch roofline denominator P_tex
  * (SURVEY.md §8d).  Returns fetches per second of the whole GPU. */

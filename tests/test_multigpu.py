@@ -1,0 +1,121 @@
+"""Multi-rank image-space path.  CPU: partition arithmetic and the handle exchange over gloo (world_size 2).
+GPU: two processes sharing cuda:0, rank 1 storing its tiles straight into rank 0's frame through CUDA IPC."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_tile_owner_map_is_a_partition():
+    from cpp_volume_rendering_b200 import multigpu
+    for (w, h, tile, n) in [(1024, 1024, 32, 8), (200, 136, 16, 3), (97, 131, 32, 2), (64, 64, 128, 4)]:
+        m = multigpu.tile_owner_map(w, h, tile, n)
+        assert m.shape == (h, w) and m.min() == 0 and m.max() <= n - 1
+        tx = (w + tile - 1) // tile
+        for (x, y) in [(0, 0), (w - 1, h - 1), (w // 2, h // 3)]:
+            assert m[y, x] == ((y // tile) * tx + x // tile) % n
+    m = multigpu.tile_owner_map(1024, 1024, 32, 8)
+    counts = np.bincount(m.ravel(), minlength=8)
+    assert counts.max() - counts.min() == 0          # 1024 tiles over 8 ranks: perfectly even
+
+
+def _gloo_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from cpp_volume_rendering_b200 import multigpu
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    handle = bytes([rank]) * 64
+    got = multigpu.exchange_handles(handle)
+    multigpu.frame_barrier()
+    q.put((rank, [g[0] for g in got], [len(g) for g in got]))
+    dist.destroy_process_group()
+
+
+def test_handle_exchange_over_gloo_world2():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res == [(0, [0, 1], [64, 64]), (1, [0, 1], [64, 64])]
+
+
+def _gpu_worker(rank, world, port, mode, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from cpp_volume_rendering_b200 import _capi, inputs, multigpu
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    n, w, h = 64, 200, 136
+    vox = inputs.synth_volume(n, np.uint8)
+    table = inputs.tf_build_linear(inputs.bonsai_tf())
+    cam = inputs.default_camera(n, w, h)
+    with _capi.Context(0) as ctx:                    # both ranks share the one GPU of the test box
+        ctx.upload_volume(vox)
+        ctx.upload_tf(table)
+        out = {}
+        for kind in (_capi.VRB_RC1PASS, _capi.VRB_ISO_SKIP_V2):
+            r = _capi.Renderer(ctx, kind)
+            r.init(w, h)
+            multigpu.setup_fused_gather(r, rank, world, tile=16, mode=mode)
+            r.update(cam)
+            r.redraw()
+            ctx.synchronize()
+            dist.barrier()                           # every rank's stores have landed
+            out[kind] = r.read_frame(_capi.VRB_FRAME_RGBA32F)
+            dist.barrier()                           # nobody unmaps before everyone has read
+            r.set_peers([], rank, _capi.VRB_GATHER_NONE)
+            dist.barrier()
+            r.close()
+    q.put((rank, out))
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", [1, 2])
+def test_fused_gather_two_ranks_one_gpu(ctx, bonsai_table, mode):
+    """ROOT: rank 0 ends up with the full frame; ALL: both do.  Bit-identical to the single-rank frame."""
+    import torch.multiprocessing as mp
+    from cpp_volume_rendering_b200 import _capi, inputs
+    n, w, h = 64, 200, 136
+    vox = inputs.synth_volume(n, np.uint8)
+    ctx.upload_volume(vox); ctx.upload_tf(bonsai_table)
+    cam = inputs.default_camera(n, w, h)
+    full = {}
+    for kind in (_capi.VRB_RC1PASS, _capi.VRB_ISO_SKIP_V2):
+        r = _capi.Renderer(ctx, kind); r.init(w, h); r.update(cam); r.redraw()
+        full[kind] = r.read_frame(_capi.VRB_FRAME_RGBA32F); r.close()
+    mpc = mp.get_context("spawn")
+    q = mpc.Queue()
+    port = _free_port()
+    procs = [mpc.Process(target=_gpu_worker, args=(rk, 2, port, mode, q)) for rk in range(2)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=300) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    from cpp_volume_rendering_b200 import multigpu
+    owner = multigpu.tile_owner_map(w, h, 16, 2)
+    for kind in full:
+        assert np.array_equal(res[0][kind], full[kind])
+        if mode == 2:
+            assert np.array_equal(res[1][kind], full[kind])
+        else:                                        # rank 1 keeps only its own tiles
+            mine = owner == 1
+            assert np.array_equal(res[1][kind][mine], full[kind][mine]) and np.all(res[1][kind][~mine] == 0)
