@@ -45,6 +45,16 @@ class IsoParams(C.Structure):
                 ("num_blocks", C.c_int * 3), ("count_iterations", C.c_int)]
 
 
+class EbsParams(C.Structure):
+    _fields_ = [("step_size", C.c_float), ("apply_gradient_shading", C.c_int), ("apply_ambient_occlusion", C.c_int),
+                ("ambient_occlusion_shells", C.c_int), ("ambient_occlusion_radius", C.c_float),
+                ("apply_directional_shadows", C.c_int), ("dir_shadow_cone_samples", C.c_int),
+                ("dir_shadow_cone_angle", C.c_float), ("dir_shadow_sample_interval", C.c_float),
+                ("dir_shadow_initial_step", C.c_float), ("dir_shadow_user_interface_weight", C.c_float),
+                ("dir_cone_max_distance", C.c_float), ("type_of_shadow", C.c_int), ("light_cam_forward", C.c_float * 3),
+                ("fast_sat", C.c_int), ("count_samples", C.c_int)]
+
+
 # name -> (restype, argtypes); the list doubles as the "every declared symbol is exported" check.
 _P = C.c_void_p
 SIGNATURES = {
@@ -70,6 +80,7 @@ SIGNATURES = {
     "vrb_renderer_frame": (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "vrb_renderer_read_frame": (C.c_int, [_P, _P, C.c_int]),
     "vrb_renderer_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_double)]),
+    "vrb_ebs_read_sat": (C.c_int, [_P, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_float)]),
     "vrb_iso_read_blocks": (C.c_int, [_P, _P, _P]),
     "vrb_renderer_set_partition": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
     "vrb_renderer_frame_export": (C.c_int, [_P, _P]),
@@ -222,6 +233,16 @@ class Renderer:
         """handles: list of 64-byte IPC handles in rank order (own entry ignored); mode VRB_GATHER_*."""
         blob = b"".join(handles) if handles else b""
         _check(lib().vrb_renderer_set_peers(self._h, blob if handles else None, len(handles), rank, mode))
+
+    def read_sat(self, want_data=True):
+        """(sat float32 [D+2, H+2, W+2] or None, build_ms)."""
+        dims = (C.c_int * 3)(); ms = C.c_float()
+        _check(lib().vrb_ebs_read_sat(self._h, None, C.byref(dims), C.byref(ms)))
+        out = None
+        if want_data:
+            out = np.empty((dims[2], dims[1], dims[0]), np.float32)
+            _check(lib().vrb_ebs_read_sat(self._h, out.ctypes.data_as(_P), C.byref(dims), C.byref(ms)))
+        return out, ms.value
 
     def read_blocks(self, num_blocks):
         nbx, nby, nbz = num_blocks

@@ -99,6 +99,27 @@ typedef struct {
   int   count_iterations;       /* 1 = instrumented kernel that counts march-loop iterations */
 } vrb_iso_params;
 
+/* Run-time parameters of RC1PExtinctionBasedShading: its ImGui-mutable members (ebsrenderer.cpp:18-42).
+ * Init overwrites step_size (0.5/sqrt(3)*|voxel scale|, :115-116) and dir_cone_max_distance (0.75 * diagonal, :99-105). */
+typedef struct {
+  float step_size;                         /* m_u_step_size */
+  int   apply_gradient_shading;            /* m_apply_gradient_shading (needs a gradient volume) */
+  int   apply_ambient_occlusion;           /* true */
+  int   ambient_occlusion_shells;          /* 15 */
+  float ambient_occlusion_radius;          /* 1.0 */
+  int   apply_directional_shadows;         /* true */
+  int   dir_shadow_cone_samples;           /* 120 (bound as a uniform, never read by the shader) */
+  float dir_shadow_cone_angle;             /* 1.0 degrees */
+  float dir_shadow_sample_interval;        /* 2.0 */
+  float dir_shadow_initial_step;           /* 2.0 */
+  float dir_shadow_user_interface_weight;  /* 1.0 */
+  float dir_cone_max_distance;             /* set by Init */
+  int   type_of_shadow;                    /* 0 point light, 1 directional */
+  float light_cam_forward[3];              /* RenderingParameters::GetBlinnPhongLightSourceCameraForward() */
+  int   fast_sat;                          /* new: 0 = SAT by the reference's recurrence (bit-identical), 1 = separable scan */
+  int   count_samples;
+} vrb_ebs_params;
+
 /* ---- library / context ------------------------------------------------------------------- */
 int         vrb_abi_version(void);
 const char* vrb_last_error(void);
@@ -155,6 +176,11 @@ int vrb_renderer_counters(vrb_renderer* r, uint64_t* samples, double* ms);
 /* Test hook for K5 (ComputeBlocksFromVolume, rc1custompisoadaptrenderer.cpp:20-113, moved to the GPU): the block
  * min / max grids of a VRB_ISO_SKIP_V1 / _V2 renderer, num_blocks[0]*[1]*[2] floats each, x fastest. */
 int vrb_iso_read_blocks(vrb_renderer* r, float* host_min, float* host_max);
+
+/* Test / measurement hook for K12 (GenerateExtinctionSAT3DTex, ebsrenderer.cpp:624-722, moved to the GPU): the
+ * float32 table of a VRB_EBS_SAT renderer, dims = volume + 2 per axis, x fastest; build_ms = device time of the
+ * last fill + scan.  host may be NULL to query dims / time only. */
+int vrb_ebs_read_sat(vrb_renderer* r, float* host, int dims[3], float* build_ms);
 
 /* ---- multi-GPU: image-space partition (no reference counterpart) ------------ */
 /* Tiles of tile x tile pixels are dealt round-robin: this rank renders tile t iff t % n_ranks == rank.

@@ -88,6 +88,31 @@ void orc_block_minmax(const void* voxels, int dtype, int w, int h, int d, int nb
 uint64_t orc_iso_render(const orc_iso_params* p, const float* vol_r16f, const float* block_min, const float* block_max,
                         float* out_rgba, uint32_t* out_iters);
 
+/* ---- extinction-based shading (K12 SAT, K13 ray caster) ------------------------------------------------ */
+typedef struct {
+  int   width, height;
+  int   vol_w, vol_h, vol_d;
+  float voxel[3];
+  float eye[3];
+  float lookat[9];
+  float tan_fovy, aspect, step;
+  int   apply_occlusion, apply_shadow;          /* ApplyOcclusion, ApplyShadow */
+  int   ao_shells; float ao_radius;             /* AmbOccShells, AmbOccRadius */
+  float sdw_cone_angle;                         /* DirSdwConeAngle in RADIANS (ebsrenderer.cpp:161) */
+  float sdw_sample_interval, sdw_initial_step, sdw_weight, sdw_max_distance;
+  int   type_of_shadow;                         /* 0 point light, 1 directional (LightCamForward) */
+  float light_pos[3], light_cam_forward[3];
+  float ka, kd;                                 /* Kambient, Kdiffuse */
+  int   row_begin, row_end, row_stride, threads;
+} orc_ebs_params;
+
+/* GenerateExtinctionSAT3DTex (ebsrenderer.cpp:624-722): (w+2)(h+2)(d+2) float32 SAT; out_ext optional. */
+void orc_ext_sat3d(const void* voxels, int dtype, int w, int h, int d, const double* table, int max_density,
+                   int extinction_type, float* out_sat, float* out_ext);
+/* main() of ebs_ray_bbox_marching.comp.  Returns march-loop iterations; *out_shaded = samples that were shaded. */
+uint64_t orc_ebs_render(const orc_ebs_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
+                        const float* sat, float* out_rgba, uint64_t* out_shaded);
+
 int orc_max_threads(void);
 
 #ifdef __cplusplus

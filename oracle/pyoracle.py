@@ -35,6 +35,17 @@ class IsoParams(C.Structure):
                 ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
 
 
+class EbsParams(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("vol_w", C.c_int), ("vol_h", C.c_int), ("vol_d", C.c_int),
+                ("voxel", C.c_float * 3), ("eye", C.c_float * 3), ("lookat", C.c_float * 9),
+                ("tan_fovy", C.c_float), ("aspect", C.c_float), ("step", C.c_float),
+                ("apply_occlusion", C.c_int), ("apply_shadow", C.c_int), ("ao_shells", C.c_int), ("ao_radius", C.c_float),
+                ("sdw_cone_angle", C.c_float), ("sdw_sample_interval", C.c_float), ("sdw_initial_step", C.c_float),
+                ("sdw_weight", C.c_float), ("sdw_max_distance", C.c_float), ("type_of_shadow", C.c_int),
+                ("light_pos", C.c_float * 3), ("light_cam_forward", C.c_float * 3), ("ka", C.c_float), ("kd", C.c_float),
+                ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -54,6 +65,9 @@ def lib():
         L.orc_rc1pass_render.restype = C.c_uint64
         L.orc_blit_over_white.argtypes = [_P, C.c_int64, _P]
         L.orc_max_threads.restype = C.c_int
+        L.orc_ext_sat3d.argtypes = [_P, C.c_int, C.c_int, C.c_int, C.c_int, _P, C.c_int, C.c_int, _P, _P]
+        L.orc_ebs_render.argtypes = [C.POINTER(EbsParams), _P, _P, C.c_int, _P, _P, C.POINTER(C.c_uint64)]
+        L.orc_ebs_render.restype = C.c_uint64
         L.orc_block_minmax.argtypes = [_P, C.c_int] + [C.c_int] * 6 + [_P, _P]
         L.orc_iso_render.argtypes = [C.POINTER(IsoParams), _P, _P, _P, _P, _P]
         L.orc_iso_render.restype = C.c_uint64
@@ -183,3 +197,47 @@ def iso_render(p, vol_r16f, block_min=None, block_max=None, want_iters=False):
     it = np.zeros((p.height, p.width), np.uint32) if want_iters else None
     total = lib().orc_iso_render(C.byref(p), _ptr(vol), _ptr(block_min), _ptr(block_max), _ptr(out), _ptr(it))
     return out, int(total), it
+
+
+def ext_sat3d(voxels, table, extinction_type=False, want_ext=False):
+    """GenerateExtinctionSAT3DTex: float32 SAT indexed [z, y, x] of shape (d+2, h+2, w+2)."""
+    v = np.ascontiguousarray(voxels)
+    t = np.ascontiguousarray(table, np.float64)
+    d, h, w = v.shape
+    sat = np.empty((d + 2, h + 2, w + 2), np.float32)
+    ext = np.empty_like(sat) if want_ext else None
+    lib().orc_ext_sat3d(_ptr(v), _DT[v.dtype], w, h, d, _ptr(t), t.shape[0] - 1, int(extinction_type), _ptr(sat), _ptr(ext))
+    return (sat, ext) if want_ext else sat
+
+
+def ebs_params(cam, width, height, vol_shape_zyx, step, light_pos, voxel=(1.0, 1.0, 1.0), apply_occlusion=1, apply_shadow=1,
+               ao_shells=15, ao_radius=1.0, cone_angle_deg=1.0, sample_interval=2.0, initial_step=2.0, weight=1.0,
+               max_distance=None, type_of_shadow=0, light_cam_forward=(0.0, 0.0, -1.0), ka=0.5, kd=0.5, rows=None, threads=0):
+    p = EbsParams()
+    p.width, p.height = width, height
+    p.vol_d, p.vol_h, p.vol_w = vol_shape_zyx
+    p.voxel[:] = voxel
+    p.eye[:] = list(cam.eye); p.lookat[:] = list(cam.lookat)
+    p.tan_fovy, p.aspect, p.step = cam.tan_fovy, cam.aspect, step
+    p.apply_occlusion, p.apply_shadow, p.ao_shells, p.ao_radius = apply_occlusion, apply_shadow, ao_shells, ao_radius
+    p.sdw_cone_angle = float(np.float32(cone_angle_deg * np.pi / 180.0))          # ebsrenderer.cpp:161
+    p.sdw_sample_interval, p.sdw_initial_step, p.sdw_weight = sample_interval, initial_step, weight
+    if max_distance is None:                                                       # Init: 0.75 * diagonal (ebsrenderer.cpp:99-105)
+        vw, vh, vd = (np.float32(vol_shape_zyx[2] * voxel[0]), np.float32(vol_shape_zyx[1] * voxel[1]), np.float32(vol_shape_zyx[0] * voxel[2]))
+        max_distance = float(np.float32(0.75) * np.sqrt(np.float32(vw * vw + vh * vh + vd * vd)))
+    p.sdw_max_distance = max_distance
+    p.type_of_shadow = type_of_shadow
+    p.light_pos[:] = light_pos; p.light_cam_forward[:] = light_cam_forward
+    p.ka, p.kd = ka, kd
+    p.row_begin, p.row_end, p.row_stride = rows or (0, height, 1)
+    p.threads = threads
+    return p
+
+
+def ebs_render(p, vol_r16f, tf_rgbt, sat):
+    vol = np.ascontiguousarray(vol_r16f, np.float32); tf = np.ascontiguousarray(tf_rgbt, np.float32)
+    s = np.ascontiguousarray(sat, np.float32)
+    out = np.zeros((p.height, p.width, 4), np.float32)
+    shaded = C.c_uint64()
+    total = lib().orc_ebs_render(C.byref(p), _ptr(vol), _ptr(tf), tf.shape[0], _ptr(s), _ptr(out), C.byref(shaded))
+    return out, int(total), int(shaded.value)
