@@ -101,6 +101,41 @@ def cpu_frame(vox, table, cam, skip_rows=None, repeats=1):
     return total / best, O.max_threads(), total, best
 
 
+def sat_extra(ctx, table, hbm_peak):
+    """Config 4's precompute: extinction SAT of a 512^3 float32 volume, GPU (both builders) beside the reference's
+    own CPU BuildSAT (oracle/_ref, compiled from the reference's summedareatable.h; single thread — it is serial)."""
+    from cpp_volume_rendering_b200 import _capi, inputs
+    n = 512
+    vox = inputs.synth_volume(n, np.float32)
+    ctx.upload_volume(vox)
+    ctx.upload_tf(table)
+    out = {"workload": f"extinction SAT {n}^3 f32 -> {(n + 2)}^3 float32", "algorithmic_bytes": 8 * (n + 2) ** 3}
+    for name, fast in (("exact_wavefront", 0), ("separable_scan", 1)):
+        best = None
+        for _ in range(3):
+            r = _capi.Renderer(ctx, _capi.VRB_EBS_SAT)
+            prm = r.get_params(_capi.EbsParams()); prm.fast_sat = fast
+            r.set_params(prm)
+            r.init(16, 16)
+            _, ms = r.read_sat(want_data=False)
+            r.close()
+            best = ms if best is None else min(best, ms)
+        gbs = out["algorithmic_bytes"] / (best * 1e-3) / 1e9
+        out[name] = {"ms": best, "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / hbm_peak}
+    try:
+        from oracle import pyref as R
+        if R.available():
+            ext = np.zeros((n + 2, n + 2, n + 2), np.float64)
+            ext[1:-1, 1:-1, 1:-1] = 0.25
+            t0 = time.perf_counter()
+            R.sat3d_build(ext)
+            out["cpu_reference_buildsat_s"] = time.perf_counter() - t0
+            out["cpu_reference_kind"] = "reference (libs/vis_utils/summedareatable.h BuildSAT, 1 thread, SetValue fill included)"
+    except Exception as e:  # noqa: BLE001
+        out["cpu_reference_error"] = str(e)
+    return out
+
+
 def run_reference(args):
     """Reference arm: the reference's CPU implementation of the path = the oracle port (the GLSL cannot run
     here: no graphics stack).  Each step is one full frame of the same workload on all host threads."""
@@ -310,6 +345,8 @@ def run_cuda(args):
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)"},
         }
         if world == 1 and not args.no_cpu:
+            r.close(); r = None
+            line["extras"] = {"sat": sat_extra(ctx, table, hbm_peak)}
             v, cores, total, secs = cpu_frame(vox, table, cam, repeats=2)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"full {IMG_W}x{IMG_H} frame ({total} samples, best of 2, {secs:.2f} s), oracle/liboracle.so OpenMP over rows"}
@@ -318,7 +355,8 @@ def run_cuda(args):
         barrier()
         r.set_peers([], rank, _capi.VRB_GATHER_NONE)
         barrier()
-    r.close()
+    if r is not None:
+        r.close()
     ctx.close()
     if world > 1:
         dist.destroy_process_group()

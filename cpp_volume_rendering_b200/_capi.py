@@ -55,6 +55,14 @@ class EbsParams(C.Structure):
                 ("fast_sat", C.c_int), ("count_samples", C.c_int)]
 
 
+class VctParams(C.Structure):
+    _fields_ = [("step_size", C.c_float), ("apply_gradient_shading", C.c_int), ("apply_ambient_occlusion", C.c_int),
+                ("apply_directional_shadows", C.c_int), ("cone_step_size", C.c_float),
+                ("cone_step_increase_rate", C.c_float), ("cone_initial_step", C.c_float), ("cone_apex_angle", C.c_float),
+                ("apply_correction_factor", C.c_int), ("opacity_correction_factor", C.c_float),
+                ("cone_number_of_samples", C.c_int), ("count_samples", C.c_int)]
+
+
 # name -> (restype, argtypes); the list doubles as the "every declared symbol is exported" check.
 _P = C.c_void_p
 SIGNATURES = {
@@ -81,6 +89,8 @@ SIGNATURES = {
     "vrb_renderer_read_frame": (C.c_int, [_P, _P, C.c_int]),
     "vrb_renderer_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_double)]),
     "vrb_ebs_read_sat": (C.c_int, [_P, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_float)]),
+    "vrb_vct_read_level": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int * 3)]),
+    "vrb_vct_read_lut": (C.c_int, [_P, _P, C.POINTER(C.c_int * 2), C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
     "vrb_iso_read_blocks": (C.c_int, [_P, _P, _P]),
     "vrb_renderer_set_partition": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
     "vrb_renderer_frame_export": (C.c_int, [_P, _P]),
@@ -243,6 +253,24 @@ class Renderer:
             out = np.empty((dims[2], dims[1], dims[0]), np.float32)
             _check(lib().vrb_ebs_read_sat(self._h, out.ctypes.data_as(_P), C.byref(dims), C.byref(ms)))
         return out, ms.value
+
+    def read_vct_level(self, level):
+        """RG16F (mean, stddev) texels of one supervoxel level as float32 [d, h, w, 2]."""
+        dims = (C.c_int * 3)()
+        _check(lib().vrb_vct_read_level(self._h, level, None, C.byref(dims)))
+        out = np.empty((dims[2], dims[1], dims[0], 2), np.float32)
+        _check(lib().vrb_vct_read_level(self._h, level, out.ctypes.data_as(_P), C.byref(dims)))
+        return out
+
+    def read_vct_lut(self, want_data=True):
+        """(lut float32 [h, w] or None, max_std, n_levels, build_ms)."""
+        dims = (C.c_int * 2)(); ms = C.c_float(); sd = C.c_double(); nl = C.c_int()
+        _check(lib().vrb_vct_read_lut(self._h, None, C.byref(dims), C.byref(sd), C.byref(nl), C.byref(ms)))
+        out = None
+        if want_data:
+            out = np.empty((dims[1], dims[0]), np.float32)
+            _check(lib().vrb_vct_read_lut(self._h, out.ctypes.data_as(_P), C.byref(dims), C.byref(sd), C.byref(nl), C.byref(ms)))
+        return out, sd.value, nl.value, ms.value
 
     def read_blocks(self, num_blocks):
         nbx, nby, nbz = num_blocks

@@ -1,0 +1,393 @@
+// K15/K16/K17 — RC1PVoxelConeTracingSGPU: voxel cone tracing shadows.
+//   K15 PreProcessSuperVoxels          rc1pvctsg/preprocessingstages.cpp:35-145   (CPU in the reference)
+//   K16 PreProcessPreIntegrationTable  rc1pvctsg/preprocessingstages.cpp:147-202  (CPU in the reference)
+//   K17 vct_ray_bbox_marching.comp:97-264; host defaults vctrenderer.cpp:27-43, uniforms :124-237
+// K15 runs in double with single-rounding intrinsics in the reference's term order, so every (mean, stddev) is
+// bit-identical to the CPU build before the RG16F rounding.  The shader's textureLod on the RG16F mip chain and its
+// bilinear LUT fetch are evaluated with float32 weights from per-level footprint textures (means reach 255, where
+// the texture unit's 1.8 fixed-point weights would move the LUT coordinate by half a density unit).
+#include "vrb_internal.cuh"
+#include "vrb_ray.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+namespace vrb {
+
+constexpr int VCT_MAX_LEVELS = 16;
+
+// ---- K15 -------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ double mean0(const T* raw, size_t i, double maxv) { return __dmul_rn(__ddiv_rn((double)raw[i], maxv), 255.0); }
+
+template <typename T>
+__global__ void __launch_bounds__(256) vct_level0_kernel(const T* __restrict__ raw, size_t n, double maxv, __half2* __restrict__ lin) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) lin[i] = __floats2half2_rn((float)mean0(raw, i, maxv), 0.0f);
+}
+
+// level l >= 1 from the child means (raw voxels when l == 1, doubles otherwise); child dims vw,vh,vd.
+template <typename T>
+__global__ void __launch_bounds__(256) vct_reduce_kernel(const T* __restrict__ raw, double maxv, const double* __restrict__ child,
+                                                         int vw, int vh, int lw, int lh, int ld, double* __restrict__ out_mean,
+                                                         __half2* __restrict__ lin, unsigned long long* __restrict__ max_std_bits) {
+  const int iw = blockIdx.x * blockDim.x + threadIdx.x, ih = blockIdx.y, id = blockIdx.z;
+  if (iw >= lw) return;
+  const int x = iw * 2, y = ih * 2, z = id * 2;
+  double v[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) {   // order vm0..vm7: (x,y,z) (x,y,z+1) (x,y+1,z) (x,y+1,z+1) (x+1,y,z) ... (:76-83)
+    const size_t i = (size_t)(x + (k >> 2)) + ((size_t)(y + ((k >> 1) & 1)) * vw) + ((size_t)(z + (k & 1)) * vw * vh);
+    v[k] = raw ? mean0(raw, i, maxv) : child[i];
+  }
+  double sum = v[0];
+#pragma unroll
+  for (int k = 1; k < 8; k++) sum = __dadd_rn(sum, v[k]);
+  const double vmn = __ddiv_rn(sum, 8.0);
+  double acc = 0.0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) { const double dlt = __dsub_rn(v[k], vmn); const double sq = __dmul_rn(dlt, dlt); acc = k == 0 ? sq : __dadd_rn(acc, sq); }
+  const double sd = __dsqrt_rn(__ddiv_rn(acc, 8.0));
+  const size_t o = (size_t)iw + ((size_t)ih * lw) + ((size_t)id * lw * lh);
+  out_mean[o] = vmn;
+  lin[o] = __floats2half2_rn((float)vmn, (float)sd);
+  atomicMax(max_std_bits, (unsigned long long)__double_as_longlong(sd));     // sd >= 0: the bit pattern orders like the value
+}
+
+__global__ void __launch_bounds__(256) vct_quad_kernel(const unsigned* __restrict__ lin, cudaSurfaceObject_t dst, int w, int h, int d) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
+  if (x >= w) return;
+  const int x1 = min(x + 1, w - 1), y1 = min(y + 1, h - 1);
+  const size_t b = (size_t)w * h * z;
+  surf3Dwrite(make_uint4(lin[b + (size_t)w * y + x], lin[b + (size_t)w * y + x1], lin[b + (size_t)w * y1 + x], lin[b + (size_t)w * y1 + x1]), dst, x * 16, y, z);
+}
+
+// ---- K16 -------------------------------------------------------------------------------------------------
+__device__ inline float tf_get_opc(const double* table, int max_density, int extinction_type, double value, double max_in) {
+  if (max_in >= 0) value = value * ((double)max_density / max_in);           // TransferFunction1D::Get (:132-157)
+  float a;
+  if (value < 0.0f || value > (float)max_density) a = 0.0f;
+  else if (fabs(value - (float)max_density) < 0.000001) a = (float)table[4 * max_density + 3];
+  else { const int iv = (int)value; const double t = value - iv; a = (float)((1.0 - t) * table[4 * iv + 3] + t * table[4 * (iv + 1) + 3]); }
+  if (extinction_type) return (float)(1.0 - exp(-(double)a));               // GetOpc (:159-167)
+  return a;
+}
+__global__ void __launch_bounds__(128) vct_lut_kernel(const double* __restrict__ table, int tf_max_density, int ext_type, int dens_val,
+                                                      int w, int h, float* __restrict__ lut) {
+  const int iw = blockIdx.x * blockDim.x + threadIdx.x, ih = blockIdx.y;
+  if (iw >= w || ih >= h) return;
+  const double mean = iw, stddev = ih;
+  double SumG = 0.0, SumW = 0.0;
+  if (fabs(stddev) > 0.0001) {
+    const double nf = 1.0 / (stddev * sqrt(2.0 * 3.14159265358979323846264338327950288));
+    for (int i = 0; i < dens_val; i++) {
+      const double W = nf * exp(-(((double)i - mean) * ((double)i - mean)) / (2.0 * stddev * stddev));
+      SumG += W * tf_get_opc(table, tf_max_density, ext_type, (double)i, (double)dens_val);
+      SumW += W;
+    }
+    SumG = SumG / SumW;
+  } else SumG = tf_get_opc(table, tf_max_density, ext_type, mean, (double)dens_val);
+  lut[iw + (ih * w)] = __half2float(__float2half_rn((float)SumG));           // SetData(GL_R16F)
+}
+
+struct VctPyramid {
+  int n_levels = 0;
+  int lw[VCT_MAX_LEVELS], lh[VCT_MAX_LEVELS], ld[VCT_MAX_LEVELS];
+  cudaArray_t arr[VCT_MAX_LEVELS] = {};
+  cudaTextureObject_t tex[VCT_MAX_LEVELS] = {};
+  __half2* lin[VCT_MAX_LEVELS] = {};          // linear RG16F copies (test hook)
+  float* lut = nullptr; int lut_w = 0, lut_h = 0;
+  double max_std = 0.0; double vol_max_density = 0.0;
+  uint64_t vol_gen = 0, tf_gen = 0;
+  float build_ms = 0.f;
+  void release_lut() { if (lut) cudaFree(lut); lut = nullptr; lut_w = lut_h = 0; tf_gen = 0; }
+  void release() {
+    for (int l = 0; l < VCT_MAX_LEVELS; l++) {
+      if (tex[l]) cudaDestroyTextureObject(tex[l]);
+      if (arr[l]) cudaFreeArray(arr[l]);
+      if (lin[l]) cudaFree(lin[l]);
+      tex[l] = 0; arr[l] = nullptr; lin[l] = nullptr;
+    }
+    n_levels = 0; vol_gen = 0;
+    release_lut();
+  }
+  int ensure(vrb_ctx* ctx, bool with_lut);
+};
+
+template <typename T>
+static int build_levels(vrb_ctx* ctx, VctPyramid& p, const T* raw, double maxv) {
+  cudaStream_t s = ctx->stream;
+  const Volume& v = ctx->vol;
+  unsigned long long* d_max = nullptr;
+  double* dbl[2] = {nullptr, nullptr};
+  auto body = [&]() -> int {
+    VRB_CUDA(cudaMalloc(&d_max, sizeof(unsigned long long)));
+    VRB_CUDA(cudaMemsetAsync(d_max, 0, sizeof(unsigned long long), s));
+    const size_t n0 = (size_t)v.w * v.h * v.d;
+    VRB_CUDA(cudaMalloc(&p.lin[0], n0 * sizeof(__half2)));
+    vct_level0_kernel<T><<<(unsigned)((n0 + 255) / 256), 256, 0, s>>>(raw, n0, maxv, p.lin[0]);
+    if (p.n_levels > 1) {
+      const size_t n1 = (size_t)p.lw[1] * p.lh[1] * p.ld[1];
+      VRB_CUDA(cudaMalloc(&dbl[0], n1 * sizeof(double)));
+      VRB_CUDA(cudaMalloc(&dbl[1], std::max<size_t>(n1 / 8, 1) * sizeof(double)));
+    }
+    for (int l = 1; l < p.n_levels; l++) {
+      const size_t nl = (size_t)p.lw[l] * p.lh[l] * p.ld[l];
+      VRB_CUDA(cudaMalloc(&p.lin[l], nl * sizeof(__half2)));
+      dim3 g((p.lw[l] + 255) / 256, p.lh[l], p.ld[l]);
+      vct_reduce_kernel<T><<<g, 256, 0, s>>>(l == 1 ? raw : nullptr, maxv, l == 1 ? nullptr : dbl[l & 1], p.lw[l - 1], p.lh[l - 1],
+                                             p.lw[l], p.lh[l], p.ld[l], dbl[(l + 1) & 1], p.lin[l], d_max);
+    }
+    VRB_CUDA(cudaGetLastError());
+    unsigned long long bits = 0;
+    VRB_CUDA(cudaMemcpyAsync(&bits, d_max, sizeof(bits), cudaMemcpyDeviceToHost, s));
+    VRB_CUDA(cudaStreamSynchronize(s));
+    memcpy(&p.max_std, &bits, sizeof(double));
+    return VRB_OK;
+  };
+  const int rc = body();
+  if (d_max) cudaFree(d_max);
+  if (dbl[0]) cudaFree(dbl[0]);
+  if (dbl[1]) cudaFree(dbl[1]);
+  return rc;
+}
+
+int VctPyramid::ensure(vrb_ctx* ctx, bool with_lut) {
+  const Volume& v = ctx->vol;
+  const TransferFunction& t = ctx->tf;
+  cudaStream_t s = ctx->stream;
+  if (!(n_levels && vol_gen == v.generation)) {
+    release();
+    VRB_REQUIRE(v.raw, VRB_ERR_NO_VOLUME, "supervoxels: no volume uploaded");
+    int w = (int)v.w, h = (int)v.h, d = (int)v.d;
+    n_levels = 0;
+    lw[0] = w; lh[0] = h; ld[0] = d; n_levels = 1;
+    w /= 2; h /= 2; d /= 2;
+    while ((long long)w * h * d >= 1 && n_levels < VCT_MAX_LEVELS) { lw[n_levels] = w; lh[n_levels] = h; ld[n_levels] = d; n_levels++; w /= 2; h /= 2; d /= 2; }
+    cudaEvent_t e0, e1;
+    VRB_CUDA(cudaEventCreate(&e0)); VRB_CUDA(cudaEventCreate(&e1));
+    VRB_CUDA(cudaEventRecord(e0, s));
+    int rc;
+    if (v.dtype == VRB_U8) { vol_max_density = 255.0; rc = build_levels<uint8_t>(ctx, *this, (const uint8_t*)v.raw, 256.0 - 1.0); }
+    else if (v.dtype == VRB_U16) { vol_max_density = 65535.0; rc = build_levels<uint16_t>(ctx, *this, (const uint16_t*)v.raw, 65536.0 - 1.0); }
+    else { vol_max_density = 1.0; rc = build_levels<float>(ctx, *this, (const float*)v.raw, 1.0); }
+    if (rc == VRB_OK) {
+      cudaEventRecord(e1, s); cudaEventSynchronize(e1);
+      cudaEventElapsedTime(&build_ms, e0, e1);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (rc != VRB_OK) { release(); return rc; }
+    cudaChannelFormatDesc desc = cudaCreateChannelDesc<uint4>();
+    cudaTextureDesc td{};
+    td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+    td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
+    for (int l = 0; l < n_levels; l++) {
+      VRB_CUDA(cudaMalloc3DArray(&arr[l], &desc, make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]), cudaArraySurfaceLoadStore));
+      cudaResourceDesc rd{}; rd.resType = cudaResourceTypeArray; rd.res.array.array = arr[l];
+      cudaSurfaceObject_t dst = 0;
+      VRB_CUDA(cudaCreateSurfaceObject(&dst, &rd));
+      cudaError_t e = cudaCreateTextureObject(&tex[l], &rd, &td, nullptr);
+      if (e == cudaSuccess) {
+        vct_quad_kernel<<<dim3((lw[l] + 255) / 256, lh[l], ld[l]), 256, 0, s>>>((const unsigned*)lin[l], dst, lw[l], lh[l], ld[l]);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+      }
+      cudaDestroySurfaceObject(dst);
+      VRB_CUDA(e);
+    }
+    vol_gen = v.generation;
+    release_lut();
+  }
+  if (with_lut && !(lut && tf_gen == t.generation)) {
+    release_lut();
+    VRB_REQUIRE(t.table, VRB_ERR_INVALID, "pre-integration table: no transfer function uploaded");
+    lut_w = (int)ceil(vol_max_density);
+    lut_h = std::max((int)ceil(max_std), 1);      // a constant volume has max stddev 0: the reference would create an empty texture
+    VRB_REQUIRE((size_t)lut_w * lut_h <= (size_t)1 << 28, VRB_ERR_UNSUPPORTED, "pre-integration table %dx%d too large", lut_w, lut_h);
+    VRB_CUDA(cudaMalloc(&lut, (size_t)lut_w * lut_h * sizeof(float)));
+    vct_lut_kernel<<<dim3((lut_w + 127) / 128, lut_h), 128, 0, s>>>(t.table, t.n - 1, t.extinction_type, (int)vol_max_density, lut_w, lut_h, lut);
+    VRB_CUDA(cudaGetLastError());
+    tf_gen = t.generation;
+  }
+  return VRB_OK;
+}
+
+}  // namespace vrb
+
+// ---- K17 -------------------------------------------------------------------------------------------------
+#include "vrb_march.cuh"
+
+namespace vrb {
+
+struct VctShader {
+  struct Args {
+    cudaTextureObject_t mip[VCT_MAX_LEVELS];
+    float mip_res[VCT_MAX_LEVELS][3];
+    int n_levels;
+    const float* lut; int lut_w, lut_h;
+    float cone_step, cone_rate, cone_initial, tan_apex, corr_fact, vol_max_density, vol_max_std;
+    int cone_samples;
+  };
+  struct Const { f3 sizes; };
+  static __device__ __forceinline__ Const prepare(const MarchArgs& a, const Args&) { Const c; c.sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]); return c; }
+
+  // texture(sampler3D RG16F, p) on one level: GL_LINEAR / CLAMP_TO_EDGE, float32 weights (oracle sample_level)
+  static __device__ __forceinline__ float2 sample_level(const Args& s, int l, f3 p) {
+    const f3 res = mk3(s.mip_res[l][0], s.mip_res[l][1], s.mip_res[l][2]);
+    const float X = __fsub_rn(__fmul_rn(p.x, res.x), 0.5f), Y = __fsub_rn(__fmul_rn(p.y, res.y), 0.5f), Z = __fsub_rn(__fmul_rn(p.z, res.z), 0.5f);
+    float fx = floorf(X), fy = floorf(Y), fz = floorf(Z);
+    const float ax = fx < 0.0f ? 0.0f : __fsub_rn(X, fx), ay = fy < 0.0f ? 0.0f : __fsub_rn(Y, fy), az = __fsub_rn(Z, fz);
+    fx = fminf(fmaxf(fx, -1.0f), res.x); fy = fminf(fmaxf(fy, -1.0f), res.y); fz = fminf(fmaxf(fz, -1.0f), res.z);
+    const uint4 q0 = tex3D<uint4>(s.mip[l], fx + 0.5f, fy + 0.5f, fz + 0.5f);
+    const uint4 q1 = tex3D<uint4>(s.mip[l], fx + 0.5f, fy + 0.5f, fz + 1.5f);
+    auto H = [](unsigned u) { return __half22float2(*reinterpret_cast<const __half2*>(&u)); };
+    const float2 t000 = H(q0.x), t100 = H(q0.y), t010 = H(q0.z), t110 = H(q0.w), t001 = H(q1.x), t101 = H(q1.y), t011 = H(q1.z), t111 = H(q1.w);
+    auto L = [](float a, float b, float w) { return __fadd_rn(a, __fmul_rn(w, __fsub_rn(b, a))); };
+    float2 r;
+    r.x = L(L(L(t000.x, t100.x, ax), L(t010.x, t110.x, ax), ay), L(L(t001.x, t101.x, ax), L(t011.x, t111.x, ax), ay), az);
+    r.y = L(L(L(t000.y, t100.y, ax), L(t010.y, t110.y, ax), ay), L(L(t001.y, t101.y, ax), L(t011.y, t111.y, ax), ay), az);
+    return r;
+  }
+  // textureLod, min LINEAR_MIPMAP_LINEAR (gl_utils/texture3d.cpp:54-58): lod <= 0 -> level 0; lod >= q -> level q
+  static __device__ __forceinline__ float2 texture_lod(const Args& s, f3 p, float lod) {
+    const int q = s.n_levels - 1;
+    if (!(lod > 0.0f)) return sample_level(s, 0, p);
+    if (lod >= (float)q) return sample_level(s, q, p);
+    const float fl = floorf(lod); const int d1 = (int)fl; const float f = __fsub_rn(lod, fl);
+    const float2 v1 = sample_level(s, d1, p), v2 = sample_level(s, d1 + 1, p);
+    return make_float2(__fadd_rn(__fmul_rn(__fsub_rn(1.0f, f), v1.x), __fmul_rn(f, v2.x)), __fadd_rn(__fmul_rn(__fsub_rn(1.0f, f), v1.y), __fmul_rn(f, v2.y)));
+  }
+  // texture(TexPreIntegrationLookup, uv): R16F 2D, GL_LINEAR / CLAMP_TO_EDGE
+  static __device__ __forceinline__ float lut_fetch(const Args& s, float u, float v) {
+    const float X = __fsub_rn(__fmul_rn(u, (float)s.lut_w), 0.5f), Y = __fsub_rn(__fmul_rn(v, (float)s.lut_h), 0.5f);
+    const float fx = floorf(X), fy = floorf(Y);
+    const float ax = fx < 0.0f ? 0.0f : __fsub_rn(X, fx), ay = fy < 0.0f ? 0.0f : __fsub_rn(Y, fy);
+    const int x0 = (int)fminf(fmaxf(fx, 0.0f), (float)(s.lut_w - 1)), y0 = (int)fminf(fmaxf(fy, 0.0f), (float)(s.lut_h - 1));
+    const int x1 = (int)fminf(fmaxf(fx + 1.0f, 0.0f), (float)(s.lut_w - 1)), y1 = (int)fminf(fmaxf(fy + 1.0f, 0.0f), (float)(s.lut_h - 1));
+    const float t00 = __ldg(s.lut + x0 + s.lut_w * y0), t10 = __ldg(s.lut + x1 + s.lut_w * y0);
+    const float t01 = __ldg(s.lut + x0 + s.lut_w * y1), t11 = __ldg(s.lut + x1 + s.lut_w * y1);
+    const float c0 = __fadd_rn(t00, __fmul_rn(ax, __fsub_rn(t10, t00))), c1 = __fadd_rn(t01, __fmul_rn(ax, __fsub_rn(t11, t01)));
+    return __fadd_rn(c0, __fmul_rn(ay, __fsub_rn(c1, c0)));
+  }
+  // EvaluationVoxelConeTracing (vct_ray_bbox_marching.comp:97-144); the shader's ambient term is unoccluded (:146-189)
+  static __device__ void shade(const MarchArgs& a, const Args& s, const Const& c, f3 tx, float& Iocc, float& Isdw) {
+    Iocc = 1.0f; Isdw = 0.0f;
+    if (!a.apply_shadow) return;
+    float Tvd = 1.0f;
+    const f3 realpos = sub3(tx, scale3(c.sizes, 0.5f));
+    const f3 cone = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), realpos));
+    float apex = s.cone_initial, step = s.cone_step;
+    for (int is = 0; is < s.cone_samples; is++) {
+      const float xl = __fadd_rn(apex, __fmul_rn(step, 0.5f));
+      const float mm = log2f(__fdiv_rn(__fmul_rn(__fmul_rn(2.0f, xl), s.tan_apex), 1.0f));
+      const f3 wpos = add3(tx, scale3(cone, xl));
+      if (wpos.x < 0.0f || wpos.x > c.sizes.x || wpos.y < 0.0f || wpos.y > c.sizes.y || wpos.z < 0.0f || wpos.z > c.sizes.z) break;
+      const float2 g = texture_lod(s, div3(wpos, c.sizes), mm);
+      float opacity = lut_fetch(s, __fdiv_rn(__fadd_rn(g.x, 0.5f), s.vol_max_density), __fdiv_rn(__fadd_rn(g.y, 0.5f), s.vol_max_std));
+      opacity = 1.0f - powf(1.0f - opacity, __fmul_rn(step, s.corr_fact));
+      Tvd *= (1.0f - opacity);
+      apex = __fadd_rn(apex, step);
+      step = __fmul_rn(step, s.cone_rate);
+    }
+    Isdw = Tvd;
+  }
+};
+
+class VctRenderer : public RendererImpl {
+ public:
+  explicit VctRenderer(vrb_ctx* c) : RendererImpl(c, VRB_VCT) {
+    prm_.step_size = 0.5f; prm_.apply_gradient_shading = 0;                                   // vctrenderer.cpp:27-43
+    prm_.apply_ambient_occlusion = 1; prm_.apply_directional_shadows = 1;
+    prm_.cone_step_size = 2.0f; prm_.cone_step_increase_rate = 1.0f; prm_.cone_initial_step = 2.0f;
+    prm_.cone_apex_angle = 2.0f; prm_.apply_correction_factor = 1; prm_.opacity_correction_factor = 2.0f;
+    prm_.cone_number_of_samples = 50; prm_.count_samples = 0;
+  }
+  int init(int w, int h) override {
+    const Volume& v = ctx->vol;
+    VRB_REQUIRE(v.tex != 0, VRB_ERR_NO_VOLUME, "RC1PVoxelConeTracingSGPU::Init: no volume texture");
+    VRB_REQUIRE(ctx->tf.tex_rgbt != 0, VRB_ERR_INVALID, "RC1PVoxelConeTracingSGPU::Init: no transfer function");
+    int rc = ensure_quad(ctx);
+    if (rc == VRB_OK) rc = pyr_.ensure(ctx, false);          // PreProcessSuperVoxels (:86-91); the table follows at the first Redraw
+    if (rc != VRB_OK) return rc;
+    const double sx = v.sx, sy = v.sy, sz = v.sz;
+    prm_.step_size = float((0.5f / sqrtf(3.0f)) * sqrt(sx * sx + sy * sy + sz * sz));
+    rc = alloc_frame(w, h);
+    if (rc != VRB_OK) return rc;
+    built = true;
+    return VRB_OK;
+  }
+  void clean() override { pyr_.release(); }
+  int set_params(const void* pod, size_t size) override {
+    VRB_REQUIRE(pod && size == sizeof(vrb_vct_params), VRB_ERR_INVALID, "vct set_params: size %zu != sizeof(vrb_vct_params) %zu", size, sizeof(vrb_vct_params));
+    const vrb_vct_params p = *(const vrb_vct_params*)pod;
+    VRB_REQUIRE(p.step_size > 0.0f && p.cone_step_size > 0.0f && p.cone_number_of_samples >= 0, VRB_ERR_INVALID, "vct set_params: bad value");
+    VRB_REQUIRE(!p.apply_gradient_shading, VRB_ERR_UNSUPPORTED, "vct set_params: gradient shading needs a gradient volume (not uploaded)");
+    prm_ = p;
+    return VRB_OK;
+  }
+  int get_params(void* pod, size_t size) override {
+    VRB_REQUIRE(pod && size == sizeof(vrb_vct_params), VRB_ERR_INVALID, "vct get_params: bad size");
+    *(vrb_vct_params*)pod = prm_;
+    return VRB_OK;
+  }
+  int read_level(int level, float* host_rg, int dims[3]) {
+    VRB_REQUIRE(pyr_.n_levels > 0, VRB_ERR_INVALID, "vrb_vct_read_level before Init");
+    VRB_REQUIRE(level >= 0 && level < pyr_.n_levels, VRB_ERR_INVALID, "vrb_vct_read_level: level %d of %d", level, pyr_.n_levels);
+    if (dims) { dims[0] = pyr_.lw[level]; dims[1] = pyr_.lh[level]; dims[2] = pyr_.ld[level]; }
+    if (host_rg) {
+      const size_t n = (size_t)pyr_.lw[level] * pyr_.lh[level] * pyr_.ld[level];
+      std::vector<__half2> tmp(n);
+      VRB_CUDA(cudaMemcpyAsync(tmp.data(), pyr_.lin[level], n * sizeof(__half2), cudaMemcpyDeviceToHost, ctx->stream));
+      VRB_CUDA(cudaStreamSynchronize(ctx->stream));
+      for (size_t i = 0; i < n; i++) { const float2 f = __half22float2(tmp[i]); host_rg[2 * i] = f.x; host_rg[2 * i + 1] = f.y; }
+    }
+    return VRB_OK;
+  }
+  int read_lut(float* host, int dims[2], double* max_std, int* n_levels, float* build_ms) {
+    VRB_REQUIRE(pyr_.n_levels > 0, VRB_ERR_INVALID, "vrb_vct_read_lut before Init");
+    if (host) { const int rc = pyr_.ensure(ctx, true); if (rc != VRB_OK) return rc; }
+    if (dims) { dims[0] = (int)ceil(pyr_.vol_max_density); dims[1] = std::max((int)ceil(pyr_.max_std), 1); }
+    if (max_std) *max_std = pyr_.max_std;
+    if (n_levels) *n_levels = pyr_.n_levels;
+    if (build_ms) *build_ms = pyr_.build_ms;
+    if (host) {
+      VRB_CUDA(cudaMemcpyAsync(host, pyr_.lut, (size_t)pyr_.lut_w * pyr_.lut_h * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+      VRB_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return VRB_OK;
+  }
+  int redraw(int) override {
+    VRB_REQUIRE(built && have_cam, VRB_ERR_INVALID, "RC1PVoxelConeTracingSGPU::Redraw before Init/Update");
+    int rc = ensure_quad(ctx);
+    if (rc == VRB_OK) rc = pyr_.ensure(ctx, true);
+    if (rc != VRB_OK) return rc;
+    MarchArgs a{};
+    if (!fill_march_args(*this, prm_.step_size, prm_.apply_ambient_occlusion, prm_.apply_directional_shadows, a)) return VRB_OK;
+    VctShader::Args s{};
+    s.n_levels = pyr_.n_levels;
+    for (int l = 0; l < pyr_.n_levels; l++) { s.mip[l] = pyr_.tex[l]; s.mip_res[l][0] = (float)pyr_.lw[l]; s.mip_res[l][1] = (float)pyr_.lh[l]; s.mip_res[l][2] = (float)pyr_.ld[l]; }
+    s.lut = pyr_.lut; s.lut_w = pyr_.lut_w; s.lut_h = pyr_.lut_h;
+    s.cone_step = prm_.cone_step_size; s.cone_rate = prm_.cone_step_increase_rate; s.cone_initial = prm_.cone_initial_step;
+    s.tan_apex = std::tan(prm_.cone_apex_angle * 3.14159265358979323846f / 180.0f);                  // vctrenderer.cpp:145 (float)
+    s.corr_fact = (float)prm_.apply_correction_factor * prm_.opacity_correction_factor;
+    s.vol_max_density = (float)pyr_.vol_max_density; s.vol_max_std = (float)pyr_.max_std;
+    s.cone_samples = prm_.cone_number_of_samples;
+    return launch_march<VctShader>(*this, a, s, prm_.count_samples != 0);
+  }
+ private:
+  vrb_vct_params prm_{};
+  VctPyramid pyr_;
+};
+
+RendererImpl* make_vct(vrb_ctx* ctx) { return new VctRenderer(ctx); }
+int vct_read_level(RendererImpl* impl, int level, float* host_rg, int dims[3]) {
+  VRB_REQUIRE(impl->kind == VRB_VCT, VRB_ERR_INVALID, "vrb_vct_read_level: not a voxel-cone-tracing renderer");
+  return static_cast<VctRenderer*>(impl)->read_level(level, host_rg, dims);
+}
+int vct_read_lut(RendererImpl* impl, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms) {
+  VRB_REQUIRE(impl->kind == VRB_VCT, VRB_ERR_INVALID, "vrb_vct_read_lut: not a voxel-cone-tracing renderer");
+  return static_cast<VctRenderer*>(impl)->read_lut(host, dims, max_std, n_levels, build_ms);
+}
+
+}  // namespace vrb

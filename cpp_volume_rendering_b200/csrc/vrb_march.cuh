@@ -1,0 +1,174 @@
+// Shared front-to-back march of the shadowed DVR renderers (VCT, DOS cone tracing): the common part of
+// vct_ray_bbox_marching.comp:191-264 and crtgt_ray_bbox_marching.comp — ray setup, half-step sampling, classification,
+// `k*(c*Iocc*ka + c*Isdw*kd)` shading, exp() opacity, ERT at 0.99 — around a per-renderer shading functor.
+//   struct Shader { struct Args {...}; struct Const {...};
+//     static __device__ Const prepare(const MarchArgs&, const Args&);
+//     static __device__ void shade(const MarchArgs&, const Args&, const Const&, f3 tx, float& Iocc, float& Isdw); };
+// Same persistent warp-queue schedule as k_ebs.cu (8x4-pixel warp items, scrambled order, self-resetting counter).
+#pragma once
+#include "vrb_internal.cuh"
+#include "vrb_ray.cuh"
+#include <algorithm>
+
+namespace vrb {
+
+struct MarchArgs {
+  cudaTextureObject_t vol, vol_quad;
+  const uint2* tf_lin; const uint32_t* vis_mask; int tf_n, vis_words;
+  int width, height;
+  float res[3], scales[3], sizes[3];
+  float eye[3], lookat[9], tan_fovy, aspect, step;
+  float light_pos[3], ka, kd;
+  int apply_occlusion, apply_shadow;
+  uint2* frame; uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
+  unsigned long long* samples;
+  int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; unsigned* queue;
+};
+
+constexpr int MARCH_THREADS = 128;
+
+#ifdef __CUDACC__
+template <class S, bool COUNT>
+__global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __grid_constant__ MarchArgs a, const __grid_constant__ typename S::Args sa) {
+  extern __shared__ uint4 s_dyn[];
+  uint4* s_tf = s_dyn;
+  uint32_t* s_mask = reinterpret_cast<uint32_t*>(s_dyn + a.tf_n);
+  for (int i = threadIdx.x; i < a.tf_n; i += blockDim.x) {
+    const uint2 t0 = a.tf_lin[i], t1 = a.tf_lin[min(i + 1, a.tf_n - 1)];
+    s_tf[i] = make_uint4(t0.x, t0.y, t1.x, t1.y);
+  }
+  for (int i = threadIdx.x; i < a.vis_words; i += blockDim.x) s_mask[i] = a.vis_mask[i];
+  __syncthreads();
+  const typename S::Const sc = S::prepare(a, sa);
+  const f3 sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]);
+  const f3 res = mk3(a.res[0], a.res[1], a.res[2]);
+  const f3 inv_sizes = div3(mk3(1.0f, 1.0f, 1.0f), sizes);
+  const int lane = threadIdx.x & 31;
+  const int per_tile_x = a.tile / 8, per_tile = per_tile_x * (a.tile / 4);
+  unsigned nsamp = 0;
+  for (;;) {
+    int raw = 0;
+    if (lane == 0) raw = (int)atomicAdd(a.queue, 1u);
+    raw = __shfl_sync(0xffffffffu, raw, 0);
+    if (raw >= a.n_items) break;
+    const int it = (int)(((unsigned long long)raw * a.scramble) % (unsigned)a.n_items);
+    const int local_tile = it / per_tile, sub = it % per_tile;
+    const int tile_id = a.rank + local_tile * a.n_ranks;
+    const int tx_ = tile_id % a.tiles_x, ty_ = tile_id / a.tiles_x;
+    const int lx = ((lane >> 2) & 3) * 2 + (lane & 1), ly = (lane >> 4) * 2 + ((lane >> 1) & 1);
+    const int px = tx_ * a.tile + (sub % per_tile_x) * 8 + lx, py = ty_ * a.tile + (sub / per_tile_x) * 4 + ly;
+    if (px >= a.width || py >= a.height) continue;
+    const f3 eye = mk3(a.eye[0], a.eye[1], a.eye[2]);
+    const f3 cdir = camera_ray_dir(px, py, a.width, a.height, a.tan_fovy, a.aspect, a.lookat);
+    const f3 half = scale3(sizes, 0.5f);
+    f3 dir; float tnear, tfar;
+    const bool hit = ray_aabb(eye, cdir, mk3(-half.x, -half.y, -half.z), half, dir, tnear, tfar);
+    float4 dst = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (hit) {
+      const float D = fabsf(__fsub_rn(tfar, tnear));
+      const f3 wd = add3(add3(eye, scale3(dir, tnear)), half);
+      const float tfn = (float)a.tf_n, tfmax = (float)(a.tf_n - 1);
+      for (float s = 0.0f; s < D;) {
+        const float h = gmin(a.step, __fsub_rn(D, s));
+        const f3 tx = add3(wd, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));
+        const f3 p = mul3(tx, inv_sizes);
+        if (COUNT) nsamp++;
+        const float d_hw = tex3D<float>(a.vol, p.x, p.y, p.z);
+        int j = (int)fminf(fmaxf(fmaf(d_hw, tfn, -0.5f), 0.0f), tfmax);
+        if ((s_mask[j >> 5] >> (j & 31)) & 1u) {
+          const float density = tex3d_f32_exact(a.vol_quad, p, res);
+          const float u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
+          j = (int)u;
+          const float w = u - (float)j;
+          const uint4 e = s_tf[j];
+          const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&e.y));
+          const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
+          float4 src = make_float4(fmaf(w, r1.x - r0.x, r0.x), fmaf(w, r1.y - r0.y, r0.y), fmaf(w, b1.x - b0.x, b0.x), fmaf(w, b1.y - b0.y, b0.y));
+          if (src.w > 0.0f) {
+            float ka = 0.0f, kd = 0.0f, Iocc = 0.0f, Isdw = 0.0f;
+            if (a.apply_occlusion) ka = a.ka;
+            if (a.apply_shadow) kd = a.kd;
+            S::shade(a, sa, sc, tx, Iocc, Isdw);
+            const float k = 1.0f / (ka + kd);
+            src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
+            src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
+            src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
+            const float alpha = 1.0f - expf(-src.w * h);
+            const float wgt = (1.0f - dst.w) * alpha;
+            dst.x = fmaf(wgt, src.x, dst.x); dst.y = fmaf(wgt, src.y, dst.y); dst.z = fmaf(wgt, src.z, dst.z); dst.w += wgt;
+            if (dst.w > 0.99f) break;
+          }
+        }
+        s = __fadd_rn(s, h);
+      }
+    }
+    const uint2 texel = make_uint2(pack_half2(dst.x, dst.y), pack_half2(dst.z, dst.w));
+    const size_t o = (size_t)py * a.width + px;
+    a.frame[o] = texel;
+    for (int q = 0; q < a.n_peers; q++) a.peer[q][o] = texel;
+  }
+  if (COUNT) {
+    for (int o = 16; o > 0; o >>= 1) nsamp += __shfl_xor_sync(0xffffffffu, nsamp, o);
+    if (lane == 0 && nsamp) atomicAdd(a.samples, (unsigned long long)nsamp);
+  }
+  if (lane == 0) {
+    const unsigned total_warps = gridDim.x * (blockDim.x >> 5);
+    __threadfence();
+    if (atomicAdd(a.queue + 1, 1u) == total_warps - 1) { a.queue[0] = 0u; a.queue[1] = 0u; }
+  }
+}
+
+// Fills the renderer-independent arguments from the renderer state; returns false when this rank owns no tiles.
+inline bool fill_march_args(const RendererImpl& r, float step, int apply_occlusion, int apply_shadow, MarchArgs& a) {
+  const Volume& v = r.ctx->vol;
+  const TransferFunction& t = r.ctx->tf;
+  a.vol = v.tex; a.vol_quad = v.tex_quad;
+  a.tf_lin = (const uint2*)t.lin_rgbt; a.vis_mask = t.vis_mask; a.tf_n = t.n; a.vis_words = t.vis_words;
+  a.width = r.width; a.height = r.height;
+  a.res[0] = (float)v.w; a.res[1] = (float)v.h; a.res[2] = (float)v.d;
+  a.scales[0] = v.sx; a.scales[1] = v.sy; a.scales[2] = v.sz;
+  for (int i = 0; i < 3; i++) { a.sizes[i] = a.res[i] * a.scales[i]; a.eye[i] = r.cam.eye[i]; a.light_pos[i] = r.light.position[i]; }
+  for (int i = 0; i < 9; i++) a.lookat[i] = r.cam.lookat[i];
+  a.tan_fovy = r.cam.tan_fovy; a.aspect = r.cam.aspect; a.step = step;
+  a.ka = r.light.ka; a.kd = r.light.kd; a.apply_occlusion = apply_occlusion; a.apply_shadow = apply_shadow;
+  a.frame = (uint2*)r.frame; a.samples = r.d_samples;
+  a.n_peers = r.n_peer_frames;
+  for (int q = 0; q < r.n_peer_frames; q++) a.peer[q] = (uint2*)r.peer_frames[q];
+  a.rank = r.rank; a.n_ranks = r.n_ranks; a.tile = r.part_tile;
+  a.tiles_x = (r.width + r.part_tile - 1) / r.part_tile;
+  a.n_tiles = a.tiles_x * ((r.height + r.part_tile - 1) / r.part_tile);
+  const int my_tiles = (a.n_tiles - r.rank + r.n_ranks - 1) / r.n_ranks;
+  a.n_items = my_tiles * (r.part_tile / 8) * (r.part_tile / 4);
+  if (a.n_items <= 0) return false;
+  unsigned sc = (unsigned)(a.n_items * 0.6180339887) | 1u;
+  auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned tt = x % y; x = y; y = tt; } return x; };
+  while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
+  a.scramble = a.n_items > 2 ? sc : 1u;
+  a.queue = r.d_queue;
+  return true;
+}
+
+template <class S, bool COUNT>
+int launch_march_t(const RendererImpl& r, const MarchArgs& a, const typename S::Args& sa) {
+  const size_t smem = (size_t)a.tf_n * sizeof(uint4) + (size_t)a.vis_words * sizeof(uint32_t);
+  VRB_REQUIRE(smem <= 200 * 1024, VRB_ERR_UNSUPPORTED, "transfer function of %d entries does not fit shared memory", a.tf_n);
+  auto kern = shaded_march_kernel<S, COUNT>;
+  if (smem > 48 * 1024) VRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH_THREADS, smem));
+  const int max_ctas = (a.n_items + MARCH_THREADS / 32 - 1) / (MARCH_THREADS / 32);
+  kern<<<std::min(std::max(per_sm, 1) * r.ctx->sm_count, max_ctas), MARCH_THREADS, smem, r.ctx->stream>>>(a, sa);
+  VRB_CUDA(cudaGetLastError());
+  return VRB_OK;
+}
+template <class S>
+int launch_march(const RendererImpl& r, const MarchArgs& a, const typename S::Args& sa, bool count) {
+  if (count) {
+    VRB_CUDA(cudaMemsetAsync(r.d_samples, 0, sizeof(unsigned long long), r.ctx->stream));
+    return launch_march_t<S, true>(r, a, sa);
+  }
+  return launch_march_t<S, false>(r, a, sa);
+}
+#endif
+
+}  // namespace vrb

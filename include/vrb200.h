@@ -120,6 +120,23 @@ typedef struct {
   int   count_samples;
 } vrb_ebs_params;
 
+/* Run-time parameters of RC1PVoxelConeTracingSGPU: its ImGui-mutable members (vctrenderer.cpp:27-43).
+ * Init overwrites step_size like the other DVR renderers. */
+typedef struct {
+  float step_size;                  /* m_u_step_size */
+  int   apply_gradient_shading;     /* needs a gradient volume */
+  int   apply_ambient_occlusion;    /* true: ambient term ka (the shader's ambient light is unoccluded) */
+  int   apply_directional_shadows;  /* true: cone-traced shadow term kd */
+  float cone_step_size;             /* 2.0 */
+  float cone_step_increase_rate;    /* 1.0 */
+  float cone_initial_step;          /* 2.0 */
+  float cone_apex_angle;            /* 2.0 degrees */
+  int   apply_correction_factor;    /* true */
+  float opacity_correction_factor;  /* 2.0 */
+  int   cone_number_of_samples;     /* 50 */
+  int   count_samples;
+} vrb_vct_params;
+
 /* ---- library / context ------------------------------------------------------------------- */
 int         vrb_abi_version(void);
 const char* vrb_last_error(void);
@@ -181,6 +198,15 @@ int vrb_iso_read_blocks(vrb_renderer* r, float* host_min, float* host_max);
  * float32 table of a VRB_EBS_SAT renderer, dims = volume + 2 per axis, x fastest; build_ms = device time of the
  * last fill + scan.  host may be NULL to query dims / time only. */
 int vrb_ebs_read_sat(vrb_renderer* r, float* host, int dims[3], float* build_ms);
+
+/* Test / measurement hooks for K15 / K16 (PreProcessSuperVoxels and PreProcessPreIntegrationTable,
+ * rc1pvctsg/preprocessingstages.cpp:35-202, moved to the GPU) of a VRB_VCT renderer.
+ * read_level: the RG16F (mean, stddev) texels of one mip level as 2 floats per supervoxel, x fastest; dims = its size.
+ * read_lut:   the R16F pre-integration table, dims = {w = ceil(max density), h = ceil(max stddev)}, plus the maximum
+ *             standard deviation (double, unrounded), the number of levels and the device time of the pyramid build.
+ * Any output pointer may be NULL. */
+int vrb_vct_read_level(vrb_renderer* r, int level, float* host_rg, int dims[3]);
+int vrb_vct_read_lut(vrb_renderer* r, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms);
 
 /* ---- multi-GPU: image-space partition (no reference counterpart) ------------ */
 /* Tiles of tile x tile pixels are dealt round-robin: this rank renders tile t iff t % n_ranks == rank.

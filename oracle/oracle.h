@@ -113,6 +113,32 @@ void orc_ext_sat3d(const void* voxels, int dtype, int w, int h, int d, const dou
 uint64_t orc_ebs_render(const orc_ebs_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
                         const float* sat, float* out_rgba, uint64_t* out_shaded);
 
+/* ---- voxel cone tracing (K15 supervoxel pyramid, K16 pre-integration LUT, K17 ray caster) --------------- */
+typedef struct {
+  int   width, height;
+  int   vol_w, vol_h, vol_d;
+  float voxel[3];
+  float eye[3];
+  float lookat[9];
+  float tan_fovy, aspect, step;
+  int   apply_occlusion, apply_shadow;                 /* ApplyOcclusion, ApplyShadow */
+  float tan_apex;                                      /* TanRadiusConeApexAngle */
+  float cone_step_size, cone_step_increase_rate, cone_initial_step;
+  float opacity_correction_factor; int apply_correction_factor;
+  int   cone_samples;                                  /* ConeNumberOfSamples */
+  float vol_max_density, vol_max_std;                  /* VolumeMaxDensity, VolumeMaxStandardDeviation */
+  float light_pos[3];
+  float ka, kd;
+  int   row_begin, row_end, row_stride, threads;
+} orc_vct_params;
+
+int    orc_vct_num_levels(int w, int h, int d);
+double orc_vct_supervoxels(const void* voxels, int dtype, int w, int h, int d, float** out_levels);
+void   orc_vct_preintegration(const double* table, int tf_max_density, int extinction_type, double vol_max_density,
+                              double max_std, float* out_lut, int* out_w, int* out_h);
+uint64_t orc_vct_render(const orc_vct_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
+                        const float* const* levels, int n_levels, const float* lut, int lut_w, int lut_h, float* out_rgba);
+
 int orc_max_threads(void);
 
 #ifdef __cplusplus

@@ -46,6 +46,18 @@ class EbsParams(C.Structure):
                 ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
 
 
+class VctParams(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("vol_w", C.c_int), ("vol_h", C.c_int), ("vol_d", C.c_int),
+                ("voxel", C.c_float * 3), ("eye", C.c_float * 3), ("lookat", C.c_float * 9),
+                ("tan_fovy", C.c_float), ("aspect", C.c_float), ("step", C.c_float),
+                ("apply_occlusion", C.c_int), ("apply_shadow", C.c_int), ("tan_apex", C.c_float),
+                ("cone_step_size", C.c_float), ("cone_step_increase_rate", C.c_float), ("cone_initial_step", C.c_float),
+                ("opacity_correction_factor", C.c_float), ("apply_correction_factor", C.c_int), ("cone_samples", C.c_int),
+                ("vol_max_density", C.c_float), ("vol_max_std", C.c_float), ("light_pos", C.c_float * 3),
+                ("ka", C.c_float), ("kd", C.c_float),
+                ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -68,6 +80,12 @@ def lib():
         L.orc_ext_sat3d.argtypes = [_P, C.c_int, C.c_int, C.c_int, C.c_int, _P, C.c_int, C.c_int, _P, _P]
         L.orc_ebs_render.argtypes = [C.POINTER(EbsParams), _P, _P, C.c_int, _P, _P, C.POINTER(C.c_uint64)]
         L.orc_ebs_render.restype = C.c_uint64
+        L.orc_vct_num_levels.argtypes = [C.c_int] * 3
+        L.orc_vct_supervoxels.argtypes = [_P, C.c_int, C.c_int, C.c_int, C.c_int, _P]
+        L.orc_vct_supervoxels.restype = C.c_double
+        L.orc_vct_preintegration.argtypes = [_P, C.c_int, C.c_int, C.c_double, C.c_double, _P, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.orc_vct_render.argtypes = [C.POINTER(VctParams), _P, _P, C.c_int, _P, C.c_int, _P, C.c_int, C.c_int, _P]
+        L.orc_vct_render.restype = C.c_uint64
         L.orc_block_minmax.argtypes = [_P, C.c_int] + [C.c_int] * 6 + [_P, _P]
         L.orc_iso_render.argtypes = [C.POINTER(IsoParams), _P, _P, _P, _P, _P]
         L.orc_iso_render.restype = C.c_uint64
@@ -241,3 +259,62 @@ def ebs_render(p, vol_r16f, tf_rgbt, sat):
     shaded = C.c_uint64()
     total = lib().orc_ebs_render(C.byref(p), _ptr(vol), _ptr(tf), tf.shape[0], _ptr(s), _ptr(out), C.byref(shaded))
     return out, int(total), int(shaded.value)
+
+
+_MAXDENS = {np.dtype(np.uint8): 255.0, np.dtype(np.uint16): 65535.0, np.dtype(np.float32): 1.0}
+
+
+def vct_supervoxels(voxels):
+    """PreProcessSuperVoxels: ([level arrays [ld, lh, lw, 2] float32 (fp16-rounded)], max_stddev)."""
+    v = np.ascontiguousarray(voxels)
+    d, h, w = v.shape
+    n = lib().orc_vct_num_levels(w, h, d)
+    levels, dims = [], (w, h, d)
+    for _ in range(n):
+        levels.append(np.zeros((dims[2], dims[1], dims[0], 2), np.float32))
+        dims = (dims[0] // 2, dims[1] // 2, dims[2] // 2)
+    ptrs = (_P * n)(*[_ptr(a) for a in levels])
+    mx = lib().orc_vct_supervoxels(_ptr(v), _DT[v.dtype], w, h, d, ptrs)
+    return levels, float(mx)
+
+
+def vct_preintegration(table, vol_dtype, max_std, extinction_type=False):
+    t = np.ascontiguousarray(table, np.float64)
+    md = _MAXDENS[np.dtype(vol_dtype)]
+    w, h = C.c_int(), C.c_int()
+    lib().orc_vct_preintegration(_ptr(t), t.shape[0] - 1, int(extinction_type), md, max_std, None, C.byref(w), C.byref(h))
+    lut = np.zeros((max(h.value, 0), w.value), np.float32)
+    if lut.size:
+        lib().orc_vct_preintegration(_ptr(t), t.shape[0] - 1, int(extinction_type), md, max_std, _ptr(lut), C.byref(w), C.byref(h))
+    return lut
+
+
+def vct_params(cam, width, height, vol_shape_zyx, step, light_pos, vol_max_density, vol_max_std, voxel=(1.0, 1.0, 1.0),
+               apply_occlusion=1, apply_shadow=1, apex_angle_deg=2.0, cone_step_size=2.0, increase_rate=1.0, initial_step=2.0,
+               opacity_correction=2.0, apply_correction=1, cone_samples=50, ka=0.5, kd=0.5, rows=None, threads=0):
+    p = VctParams()
+    p.width, p.height = width, height
+    p.vol_d, p.vol_h, p.vol_w = vol_shape_zyx
+    p.voxel[:] = voxel
+    p.eye[:] = list(cam.eye); p.lookat[:] = list(cam.lookat)
+    p.tan_fovy, p.aspect, p.step = cam.tan_fovy, cam.aspect, step
+    p.apply_occlusion, p.apply_shadow = apply_occlusion, apply_shadow
+    p.tan_apex = float(np.tan(np.float32(np.float32(apex_angle_deg) * np.float32(np.pi) / np.float32(180.0))))   # vctrenderer.cpp:151
+    p.cone_step_size, p.cone_step_increase_rate, p.cone_initial_step = cone_step_size, increase_rate, initial_step
+    p.opacity_correction_factor, p.apply_correction_factor, p.cone_samples = opacity_correction, apply_correction, cone_samples
+    p.vol_max_density, p.vol_max_std = vol_max_density, vol_max_std
+    p.light_pos[:] = light_pos
+    p.ka, p.kd = ka, kd
+    p.row_begin, p.row_end, p.row_stride = rows or (0, height, 1)
+    p.threads = threads
+    return p
+
+
+def vct_render(p, vol_r16f, tf_rgbt, levels, lut):
+    vol = np.ascontiguousarray(vol_r16f, np.float32); tf = np.ascontiguousarray(tf_rgbt, np.float32)
+    lv = [np.ascontiguousarray(a, np.float32) for a in levels]
+    ptrs = (_P * len(lv))(*[_ptr(a) for a in lv])
+    l = np.ascontiguousarray(lut, np.float32)
+    out = np.zeros((p.height, p.width, 4), np.float32)
+    total = lib().orc_vct_render(C.byref(p), _ptr(vol), _ptr(tf), tf.shape[0], ptrs, len(lv), _ptr(l), l.shape[1], l.shape[0], _ptr(out))
+    return out, int(total)

