@@ -63,6 +63,12 @@ class VctParams(C.Structure):
                 ("cone_number_of_samples", C.c_int), ("count_samples", C.c_int)]
 
 
+class SbtmParams(C.Structure):
+    _fields_ = [("step_size", C.c_float), ("cone_half_angle", C.c_float), ("evaluate_dir_occlusion", C.c_int),
+                ("grid_size", C.c_int * 2), ("max_number_of_passes", C.c_int), ("occ_ui_weight_percentage", C.c_float),
+                ("count_fragments", C.c_int)]
+
+
 # name -> (restype, argtypes); the list doubles as the "every declared symbol is exported" check.
 _P = C.c_void_p
 SIGNATURES = {
@@ -89,6 +95,7 @@ SIGNATURES = {
     "vrb_renderer_read_frame": (C.c_int, [_P, _P, C.c_int]),
     "vrb_renderer_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_double)]),
     "vrb_ebs_read_sat": (C.c_int, [_P, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_float)]),
+    "vrb_sbtm_read_occlusion": (C.c_int, [_P, _P, C.POINTER(C.c_int)]),
     "vrb_vct_read_level": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int * 3)]),
     "vrb_vct_read_lut": (C.c_int, [_P, _P, C.POINTER(C.c_int * 2), C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
     "vrb_iso_read_blocks": (C.c_int, [_P, _P, _P]),
@@ -271,6 +278,13 @@ class Renderer:
             out = np.empty((dims[1], dims[0]), np.float32)
             _check(lib().vrb_vct_read_lut(self._h, out.ctypes.data_as(_P), C.byref(dims), C.byref(sd), C.byref(nl), C.byref(ms)))
         return out, sd.value, nl.value, ms.value
+
+    def read_sbtm_occlusion(self, width, height):
+        """(occlusion buffer float32 [H, W], slices drawn by the last redraw)."""
+        n = C.c_int()
+        out = np.empty((height, width), np.float32)
+        _check(lib().vrb_sbtm_read_occlusion(self._h, out.ctypes.data_as(_P), C.byref(n)))
+        return out, n.value
 
     def read_blocks(self, num_blocks):
         nbx, nby, nbz = num_blocks

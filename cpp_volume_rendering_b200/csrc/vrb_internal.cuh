@@ -118,6 +118,8 @@ RendererImpl* make_iso(vrb_ctx* ctx, int kind);
 RendererImpl* make_ebs(vrb_ctx* ctx);
 int ebs_read_sat(RendererImpl* impl, float* host, int dims[3], float* build_ms);
 RendererImpl* make_vct(vrb_ctx* ctx);
+RendererImpl* make_sbtm(vrb_ctx* ctx);
+int sbtm_read_occlusion(RendererImpl* impl, float* host, int* n_slices);
 int vct_read_level(RendererImpl* impl, int level, float* host_rg, int dims[3]);
 int vct_read_lut(RendererImpl* impl, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms);
 int iso_read_blocks(RendererImpl* impl, float* host_min, float* host_max);

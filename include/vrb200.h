@@ -137,6 +137,18 @@ typedef struct {
   int   count_samples;
 } vrb_vct_params;
 
+/* Run-time parameters of SBTMDirectionalOcclusionShading: its ImGui-mutable members (sbtmdosrenderer.cpp:20-46).
+ * Init overwrites step_size like the other DVR renderers (:113-114). */
+typedef struct {
+  float step_size;                  /* m_u_step_size: slice spacing */
+  float cone_half_angle;            /* 50 degrees: OcclusionExtent = step * tan(angle) */
+  int   evaluate_dir_occlusion;     /* true (kept for the ImGui mirror; the shader never reads it) */
+  int   grid_size[2];               /* 2 x 2 occlusion taps */
+  int   max_number_of_passes;       /* 90000 */
+  float occ_ui_weight_percentage;   /* 1.0: UITransparencyScale */
+  int   count_fragments;            /* new: count fragments that pass the box test (vrb_renderer_counters) */
+} vrb_sbtm_params;
+
 /* ---- library / context ------------------------------------------------------------------- */
 int         vrb_abi_version(void);
 const char* vrb_last_error(void);
@@ -207,6 +219,11 @@ int vrb_ebs_read_sat(vrb_renderer* r, float* host, int dims[3], float* build_ms)
  * Any output pointer may be NULL. */
 int vrb_vct_read_level(vrb_renderer* r, int level, float* host_rg, int dims[3]);
 int vrb_vct_read_lut(vrb_renderer* r, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms);
+
+/* Test hook for K19 (sbtmdosrenderer.cpp:176-265): the R channel of the occlusion attachment the next slice would
+ * read after the last Redraw of a VRB_SBTM_DOS renderer (width*height floats, row 0 = bottom) and the number of
+ * slices drawn.  host may be NULL. */
+int vrb_sbtm_read_occlusion(vrb_renderer* r, float* host, int* n_slices);
 
 /* ---- multi-GPU: image-space partition (no reference counterpart) ------------ */
 /* Tiles of tile x tile pixels are dealt round-robin: this rank renders tile t iff t % n_ranks == rank.

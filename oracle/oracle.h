@@ -139,6 +139,24 @@ void   orc_vct_preintegration(const double* table, int tf_max_density, int extin
 uint64_t orc_vct_render(const orc_vct_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
                         const float* const* levels, int n_levels, const float* lut, int lut_w, int lut_h, float* out_rgba);
 
+/* ---- slice-based directional occlusion shading (K19) ------------------------------------------------------ */
+typedef struct {
+  int   width, height;
+  int   vol_w, vol_h, vol_d;
+  float voxel[3];
+  float eye[3];
+  float lookat[9];
+  float tan_fovy, aspect, step;
+  float cone_half_angle_deg;      /* cone_half_angle, 50 */
+  int   grid_x, grid_y;           /* GridSize, 2x2 */
+  float ui_weight;                /* UITransparencyScale, 1 */
+  int   max_passes;               /* max_number_of_passes, 90000 */
+  int   threads;
+} orc_sbtm_params;
+int      orc_sbtm_num_slices(const orc_sbtm_params* p);
+uint64_t orc_sbtm_render(const orc_sbtm_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
+                         float* out_rgba, float* out_occ);
+
 int orc_max_threads(void);
 
 #ifdef __cplusplus

@@ -58,6 +58,14 @@ class VctParams(C.Structure):
                 ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
 
 
+class SbtmParams(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("vol_w", C.c_int), ("vol_h", C.c_int), ("vol_d", C.c_int),
+                ("voxel", C.c_float * 3), ("eye", C.c_float * 3), ("lookat", C.c_float * 9),
+                ("tan_fovy", C.c_float), ("aspect", C.c_float), ("step", C.c_float),
+                ("cone_half_angle_deg", C.c_float), ("grid_x", C.c_int), ("grid_y", C.c_int), ("ui_weight", C.c_float),
+                ("max_passes", C.c_int), ("threads", C.c_int)]
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -86,6 +94,9 @@ def lib():
         L.orc_vct_preintegration.argtypes = [_P, C.c_int, C.c_int, C.c_double, C.c_double, _P, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.orc_vct_render.argtypes = [C.POINTER(VctParams), _P, _P, C.c_int, _P, C.c_int, _P, C.c_int, C.c_int, _P]
         L.orc_vct_render.restype = C.c_uint64
+        L.orc_sbtm_num_slices.argtypes = [C.POINTER(SbtmParams)]
+        L.orc_sbtm_render.argtypes = [C.POINTER(SbtmParams), _P, _P, C.c_int, _P, _P]
+        L.orc_sbtm_render.restype = C.c_uint64
         L.orc_block_minmax.argtypes = [_P, C.c_int] + [C.c_int] * 6 + [_P, _P]
         L.orc_iso_render.argtypes = [C.POINTER(IsoParams), _P, _P, _P, _P, _P]
         L.orc_iso_render.restype = C.c_uint64
@@ -318,3 +329,26 @@ def vct_render(p, vol_r16f, tf_rgbt, levels, lut):
     out = np.zeros((p.height, p.width, 4), np.float32)
     total = lib().orc_vct_render(C.byref(p), _ptr(vol), _ptr(tf), tf.shape[0], ptrs, len(lv), _ptr(l), l.shape[1], l.shape[0], _ptr(out))
     return out, int(total)
+
+
+def sbtm_params(cam, width, height, vol_shape_zyx, step, voxel=(1.0, 1.0, 1.0), cone_half_angle=50.0, grid=(2, 2),
+                ui_weight=1.0, max_passes=90000, threads=0):
+    p = SbtmParams()
+    p.width, p.height = width, height
+    p.vol_d, p.vol_h, p.vol_w = vol_shape_zyx
+    p.voxel[:] = voxel
+    p.eye[:] = list(cam.eye); p.lookat[:] = list(cam.lookat)
+    p.tan_fovy, p.aspect, p.step = cam.tan_fovy, cam.aspect, step
+    p.cone_half_angle_deg = cone_half_angle
+    p.grid_x, p.grid_y = grid
+    p.ui_weight, p.max_passes, p.threads = ui_weight, max_passes, threads
+    return p
+
+
+def sbtm_render(p, vol_r16f, tf_rgbt):
+    """(eye buffer [H, W, 4], occlusion buffer [H, W], fragments inside the box, slices)."""
+    vol = np.ascontiguousarray(vol_r16f, np.float32); tf = np.ascontiguousarray(tf_rgbt, np.float32)
+    out = np.zeros((p.height, p.width, 4), np.float32)
+    occ = np.zeros((p.height, p.width), np.float32)
+    total = lib().orc_sbtm_render(C.byref(p), _ptr(vol), _ptr(tf), tf.shape[0], _ptr(out), _ptr(occ))
+    return out, occ, int(total), lib().orc_sbtm_num_slices(C.byref(p))
