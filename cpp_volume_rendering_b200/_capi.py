@@ -69,6 +69,19 @@ class SbtmParams(C.Structure):
                 ("count_fragments", C.c_int)]
 
 
+class DosParams(C.Structure):
+    _fields_ = [("step_size", C.c_float), ("apply_gradient_shading", C.c_int), ("apply_occlusion", C.c_int), ("apply_shadow", C.c_int),
+                ("occ_cone_half_angle", C.c_float), ("occ_initial_step", C.c_float), ("occ_max_packing", C.c_int),
+                ("occ_covered_distance", C.c_float), ("occ_ui_weight", C.c_float),
+                ("sdw_cone_half_angle", C.c_float), ("sdw_initial_step", C.c_float), ("sdw_max_packing", C.c_int),
+                ("sdw_covered_distance", C.c_float), ("sdw_ui_weight", C.c_float),
+                ("integration_half_step_multiplier", C.c_float), ("gaussian_sigma_limit_multiplier", C.c_float),
+                ("type_of_shadow", C.c_int), ("spot_light_max_angle", C.c_float),
+                ("light_cam_forward", C.c_float * 3), ("light_cam_up", C.c_float * 3), ("light_cam_right", C.c_float * 3),
+                ("base_level_sigma0", C.c_float), ("use_custom_resolution", C.c_int), ("custom_resolution", C.c_int * 3),
+                ("count_samples", C.c_int)]
+
+
 # name -> (restype, argtypes); the list doubles as the "every declared symbol is exported" check.
 _P = C.c_void_p
 SIGNATURES = {
@@ -95,6 +108,8 @@ SIGNATURES = {
     "vrb_renderer_read_frame": (C.c_int, [_P, _P, C.c_int]),
     "vrb_renderer_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_double)]),
     "vrb_ebs_read_sat": (C.c_int, [_P, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_float)]),
+    "vrb_dos_read_extcoef": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
+    "vrb_dos_read_sections": (C.c_int, [_P, C.c_int, _P, C.c_int, C.POINTER(C.c_int), _P, _P, C.POINTER(C.c_float)]),
     "vrb_sbtm_read_occlusion": (C.c_int, [_P, _P, C.POINTER(C.c_int)]),
     "vrb_vct_read_level": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int * 3)]),
     "vrb_vct_read_lut": (C.c_int, [_P, _P, C.POINTER(C.c_int * 2), C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
@@ -278,6 +293,26 @@ class Renderer:
             out = np.empty((dims[1], dims[0]), np.float32)
             _check(lib().vrb_vct_read_lut(self._h, out.ctypes.data_as(_P), C.byref(dims), C.byref(sd), C.byref(nl), C.byref(ms)))
         return out, sd.value, nl.value, ms.value
+
+    def read_dos_extcoef(self):
+        """(levels: list of float32 [d, h, w] tau arrays, build_ms)."""
+        dims = (C.c_int * 3)(); nl = C.c_int(); ms = C.c_float()
+        _check(lib().vrb_dos_read_extcoef(self._h, 0, None, C.byref(dims), C.byref(nl), C.byref(ms)))
+        levels = []
+        for l in range(nl.value):
+            _check(lib().vrb_dos_read_extcoef(self._h, l, None, C.byref(dims), None, None))
+            out = np.empty((dims[2], dims[1], dims[0]), np.float32)
+            _check(lib().vrb_dos_read_extcoef(self._h, l, out.ctypes.data_as(_P), C.byref(dims), None, None))
+            levels.append(out)
+        return levels, ms.value
+
+    def read_dos_sections(self, which, cap=1024):
+        """(table float32 [n, 4], axes [10, 3], counts [3], adj7) of the occlusion (0) or shadow (1) cone."""
+        out = np.zeros((cap, 4), np.float32); axes = np.zeros((10, 3), np.float32); counts = np.zeros(3, np.int32)
+        n = C.c_int(); adj = C.c_float()
+        _check(lib().vrb_dos_read_sections(self._h, which, out.ctypes.data_as(_P), cap, C.byref(n), axes.ctypes.data_as(_P),
+                                           counts.ctypes.data_as(_P), C.byref(adj)))
+        return out[:n.value].copy(), axes, counts, adj.value
 
     def read_sbtm_occlusion(self, width, height):
         """(occlusion buffer float32 [H, W], slices drawn by the last redraw)."""

@@ -271,7 +271,7 @@ struct VctShader {
     return __fadd_rn(c0, __fmul_rn(ay, __fsub_rn(c1, c0)));
   }
   // EvaluationVoxelConeTracing (vct_ray_bbox_marching.comp:97-144); the shader's ambient term is unoccluded (:146-189)
-  static __device__ void shade(const MarchArgs& a, const Args& s, const Const& c, f3 tx, float& Iocc, float& Isdw) {
+  static __device__ void shade(const MarchArgs& a, const Args& s, const Const& c, f3 tx, f3, float& Iocc, float& Isdw) {
     Iocc = 1.0f; Isdw = 0.0f;
     if (!a.apply_shadow) return;
     float Tvd = 1.0f;

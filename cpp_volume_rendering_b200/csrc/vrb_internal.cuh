@@ -119,6 +119,9 @@ RendererImpl* make_ebs(vrb_ctx* ctx);
 int ebs_read_sat(RendererImpl* impl, float* host, int dims[3], float* build_ms);
 RendererImpl* make_vct(vrb_ctx* ctx);
 RendererImpl* make_sbtm(vrb_ctx* ctx);
+RendererImpl* make_dos(vrb_ctx* ctx);
+int dos_read_extcoef(RendererImpl* impl, int level, float* host, int dims[3], int* n_levels, float* build_ms);
+int dos_read_sections(RendererImpl* impl, int which, float* rgba, int cap, int* n, float axes30[30], int counts[3], float* adj7);
 int sbtm_read_occlusion(RendererImpl* impl, float* host, int* n_slices);
 int vct_read_level(RendererImpl* impl, int level, float* host_rg, int dims[3]);
 int vct_read_lut(RendererImpl* impl, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms);

@@ -3,7 +3,7 @@
 // `k*(c*Iocc*ka + c*Isdw*kd)` shading, exp() opacity, ERT at 0.99 — around a per-renderer shading functor.
 //   struct Shader { struct Args {...}; struct Const {...};
 //     static __device__ Const prepare(const MarchArgs&, const Args&);
-//     static __device__ void shade(const MarchArgs&, const Args&, const Const&, f3 tx, float& Iocc, float& Isdw); };
+//     static __device__ void shade(const MarchArgs&, const Args&, const Const&, f3 tx, f3 camera_dir, float& Iocc, float& Isdw); };
 // Same persistent warp-queue schedule as k_ebs.cu (8x4-pixel warp items, scrambled order, self-resetting counter).
 #pragma once
 #include "vrb_internal.cuh"
@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
             float ka = 0.0f, kd = 0.0f, Iocc = 0.0f, Isdw = 0.0f;
             if (a.apply_occlusion) ka = a.ka;
             if (a.apply_shadow) kd = a.kd;
-            S::shade(a, sa, sc, tx, Iocc, Isdw);
+            S::shade(a, sa, sc, tx, cdir, Iocc, Isdw);
             const float k = 1.0f / (ka + kd);
             src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
             src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);

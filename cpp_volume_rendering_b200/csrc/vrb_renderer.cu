@@ -44,6 +44,7 @@ int vrb_renderer_create(vrb_ctx* ctx, int kind, vrb_renderer** out) {
     case VRB_ISO_ADAPT: case VRB_ISO_SKIP_V1: case VRB_ISO_SKIP_V2: impl = make_iso(ctx, kind); break;
     case VRB_EBS_SAT: impl = make_ebs(ctx); break;
     case VRB_VCT: impl = make_vct(ctx); break;
+    case VRB_DOS_CONE: impl = make_dos(ctx); break;
     case VRB_SBTM_DOS: impl = make_sbtm(ctx); break;
     default:
       set_error("vrb_renderer_create: renderer kind %d is not built yet", kind);
@@ -235,6 +236,16 @@ int vrb_vct_read_lut(vrb_renderer* r, float* host, int dims[2], double* max_std,
 int vrb_sbtm_read_occlusion(vrb_renderer* r, float* host, int* n_slices) {
   VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_sbtm_read_occlusion: null renderer");
   return sbtm_read_occlusion(r->impl, host, n_slices);
+}
+
+int vrb_dos_read_extcoef(vrb_renderer* r, int level, float* host, int dims[3], int* n_levels, float* build_ms) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_dos_read_extcoef: null renderer");
+  return dos_read_extcoef(r->impl, level, host, dims, n_levels, build_ms);
+}
+
+int vrb_dos_read_sections(vrb_renderer* r, int which, float* rgba, int cap, int* n, float axes30[30], int counts[3], float* adj7) {
+  VRB_REQUIRE(r && (which == 0 || which == 1), VRB_ERR_INVALID, "vrb_dos_read_sections: bad argument");
+  return dos_read_sections(r->impl, which, rgba, cap, n, axes30, counts, adj7);
 }
 
 int vrb_iso_read_blocks(vrb_renderer* r, float* host_min, float* host_max) {

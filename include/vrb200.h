@@ -149,6 +149,38 @@ typedef struct {
   int   count_fragments;            /* new: count fragments that pass the box test (vrb_renderer_counters) */
 } vrb_sbtm_params;
 
+/* Run-time parameters of RC1PConeTracingDirOcclusionShading: the ImGui-mutable members of the renderer, its two
+ * ConeGaussianSamplers and its ExtinctionCoefficientVolume (dosrcrenderer.cpp:29-59, conegaussiansampler.cpp:30-46,
+ * extcoefvolumegenerator.cpp:11-16).  Init overwrites step_size and the two covered distances (0.5 / 0.75 x the
+ * volume diagonal, dosrcrenderer.cpp:111-112).  max_packing: 0, 1, 2 = CONEPACKING _1, _3, _7. */
+typedef struct {
+  float step_size;
+  int   apply_gradient_shading;              /* needs a gradient volume */
+  int   apply_occlusion;                     /* glsl_apply_occlusion, true */
+  int   apply_shadow;                        /* glsl_apply_shadow, false */
+  float occ_cone_half_angle;                 /* 20 degrees */
+  float occ_initial_step;                    /* 3.0 */
+  int   occ_max_packing;                     /* _3 */
+  float occ_covered_distance;                /* set by Init */
+  float occ_ui_weight;                       /* 0.35 */
+  float sdw_cone_half_angle;                 /* 0.5 degrees */
+  float sdw_initial_step;                    /* 3.0 */
+  int   sdw_max_packing;                     /* _1 */
+  float sdw_covered_distance;                /* set by Init */
+  float sdw_ui_weight;                       /* 1.0 */
+  float integration_half_step_multiplier;    /* d_sigma, 1.25 (both samplers) */
+  float gaussian_sigma_limit_multiplier;     /* r_sigma, 2.0 (both samplers) */
+  int   type_of_shadow;                      /* 0 point, 1 spot, 2 directional */
+  float spot_light_max_angle;                /* degrees; RenderingParameters::GetSpotLightMaxAngle() */
+  float light_cam_forward[3];                /* RenderingParameters::GetBlinnPhongLightSourceCameraForward/Up/Right() */
+  float light_cam_up[3];
+  float light_cam_right[3];
+  float base_level_sigma0;                   /* 1.0 */
+  int   use_custom_resolution;               /* true: the pyramid base is custom_resolution, else the volume's size */
+  int   custom_resolution[3];                /* 128^3 */
+  int   count_samples;
+} vrb_dos_params;
+
 /* ---- library / context ------------------------------------------------------------------- */
 int         vrb_abi_version(void);
 const char* vrb_last_error(void);
@@ -219,6 +251,16 @@ int vrb_ebs_read_sat(vrb_renderer* r, float* host, int dims[3], float* build_ms)
  * Any output pointer may be NULL. */
 int vrb_vct_read_level(vrb_renderer* r, int level, float* host_rg, int dims[3]);
 int vrb_vct_read_lut(vrb_renderer* r, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms);
+
+/* Test / measurement hooks for K6 / K7 of a VRB_DOS_CONE renderer.
+ * read_extcoef:  one level of the extinction-coefficient pyramid (R16F tau values as floats, x fastest), its dims, the
+ *                number of levels and the device time of the last pyramid build.
+ * read_sections: the cone section table (which = 0 occlusion, 1 shadow) as the RGBA16F texels the shader fetches,
+ *                [distance to next, mip level, trapezoid half interval, amplitude] per section, at most cap sections;
+ *                plus the 3 + 7 ray axes (30 floats), the per-packing section counts and the 7-ray adjacency weight.
+ * Any output pointer may be NULL. */
+int vrb_dos_read_extcoef(vrb_renderer* r, int level, float* host, int dims[3], int* n_levels, float* build_ms);
+int vrb_dos_read_sections(vrb_renderer* r, int which, float* rgba, int cap, int* n, float axes30[30], int counts[3], float* adj7);
 
 /* Test hook for K19 (sbtmdosrenderer.cpp:176-265): the R channel of the occlusion attachment the next slice would
  * read after the last Redraw of a VRB_SBTM_DOS renderer (width*height floats, row 0 = bottom) and the number of

@@ -157,6 +157,33 @@ int      orc_sbtm_num_slices(const orc_sbtm_params* p);
 uint64_t orc_sbtm_render(const orc_sbtm_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
                          float* out_rgba, float* out_occ);
 
+/* ---- directional occlusion shading by cone tracing (K6 ext-coef pyramid, K7 cone sections, K9 ray caster) ---- */
+int  orc_dos_cone_sections(float half_angle, float initial_step, int max_packing, float covered_distance,
+                           double sigma0, float d_sigma, float r_sigma, float* out_rgba, int cap,
+                           float* axes30, int* counts3, double* adj3, double* adj7);
+int  orc_dos_extcoef_num_levels(int rw, int rh, int rd);
+void orc_dos_extcoef_volume(const float* vol_r16f, int w, int h, int d, const float voxel[3], const float* tf_rgba,
+                            int tf_n, const int res[3], float s0, float** out_levels);
+typedef struct {
+  int   width, height;
+  int   vol_w, vol_h, vol_d;
+  float voxel[3];
+  float eye[3];
+  float lookat[9];
+  float tan_fovy, aspect, step;
+  int   apply_occlusion, apply_shadow;
+  int   ext_res[3];                                     /* base resolution of the extinction-coefficient pyramid */
+  int   occ_counts[3]; float occ_axes[30]; float occ_initial_step, occ_adj7, occ_ui_weight;
+  int   sdw_counts[3]; float sdw_axes[30]; float sdw_initial_step, sdw_adj7, sdw_ui_weight;
+  int   type_of_shadow; float spot_light_max_angle_cos;
+  float light_pos[3], light_cam_forward[3], light_cam_up[3], light_cam_right[3];
+  float ka, kd;
+  int   row_begin, row_end, row_stride, threads;
+} orc_dos_params;
+uint64_t orc_dos_render(const orc_dos_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
+                        const float* const* levels, int n_levels, const float* occ_sections, const float* sdw_sections,
+                        float* out_rgba, uint64_t* out_shaded);
+
 int orc_max_threads(void);
 
 #ifdef __cplusplus

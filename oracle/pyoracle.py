@@ -66,6 +66,21 @@ class SbtmParams(C.Structure):
                 ("max_passes", C.c_int), ("threads", C.c_int)]
 
 
+class DosParams(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("vol_w", C.c_int), ("vol_h", C.c_int), ("vol_d", C.c_int),
+                ("voxel", C.c_float * 3), ("eye", C.c_float * 3), ("lookat", C.c_float * 9),
+                ("tan_fovy", C.c_float), ("aspect", C.c_float), ("step", C.c_float),
+                ("apply_occlusion", C.c_int), ("apply_shadow", C.c_int), ("ext_res", C.c_int * 3),
+                ("occ_counts", C.c_int * 3), ("occ_axes", C.c_float * 30), ("occ_initial_step", C.c_float),
+                ("occ_adj7", C.c_float), ("occ_ui_weight", C.c_float),
+                ("sdw_counts", C.c_int * 3), ("sdw_axes", C.c_float * 30), ("sdw_initial_step", C.c_float),
+                ("sdw_adj7", C.c_float), ("sdw_ui_weight", C.c_float),
+                ("type_of_shadow", C.c_int), ("spot_light_max_angle_cos", C.c_float),
+                ("light_pos", C.c_float * 3), ("light_cam_forward", C.c_float * 3), ("light_cam_up", C.c_float * 3),
+                ("light_cam_right", C.c_float * 3), ("ka", C.c_float), ("kd", C.c_float),
+                ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -97,6 +112,12 @@ def lib():
         L.orc_sbtm_num_slices.argtypes = [C.POINTER(SbtmParams)]
         L.orc_sbtm_render.argtypes = [C.POINTER(SbtmParams), _P, _P, C.c_int, _P, _P]
         L.orc_sbtm_render.restype = C.c_uint64
+        L.orc_dos_cone_sections.argtypes = [C.c_float, C.c_float, C.c_int, C.c_float, C.c_double, C.c_float, C.c_float, _P, C.c_int,
+                                            _P, _P, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.orc_dos_extcoef_num_levels.argtypes = [C.c_int] * 3
+        L.orc_dos_extcoef_volume.argtypes = [_P, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, _P, C.c_float, _P]
+        L.orc_dos_render.argtypes = [C.POINTER(DosParams), _P, _P, C.c_int, _P, C.c_int, _P, _P, _P, C.POINTER(C.c_uint64)]
+        L.orc_dos_render.restype = C.c_uint64
         L.orc_block_minmax.argtypes = [_P, C.c_int] + [C.c_int] * 6 + [_P, _P]
         L.orc_iso_render.argtypes = [C.POINTER(IsoParams), _P, _P, _P, _P, _P]
         L.orc_iso_render.restype = C.c_uint64
@@ -352,3 +373,63 @@ def sbtm_render(p, vol_r16f, tf_rgbt):
     occ = np.zeros((p.height, p.width), np.float32)
     total = lib().orc_sbtm_render(C.byref(p), _ptr(vol), _ptr(tf), tf.shape[0], _ptr(out), _ptr(occ))
     return out, occ, int(total), lib().orc_sbtm_num_slices(C.byref(p))
+
+
+class ConeSections:
+    """ConeGaussianSampler output: RGBA16F section table, the 3 + 7 ray axes, per-packing counts, adjacency weights."""
+    def __init__(self, half_angle, initial_step, max_packing, covered_distance, sigma0=1.0, ui_weight=1.0, d_sigma=1.25, r_sigma=2.0,
+                 cap=512):
+        out = np.zeros((cap, 4), np.float32); self.axes = np.zeros((10, 3), np.float32); self.counts = np.zeros(3, np.int32)
+        a3, a7 = C.c_double(), C.c_double()
+        n = lib().orc_dos_cone_sections(half_angle, initial_step, max_packing, covered_distance, sigma0, d_sigma, r_sigma, _ptr(out),
+                                        cap, _ptr(self.axes), _ptr(self.counts), C.byref(a3), C.byref(a7))
+        self.table = out[:n].copy(); self.adj3, self.adj7 = a3.value, a7.value
+        self.initial_step, self.ui_weight = max(initial_step, 0.0), ui_weight
+
+
+def dos_extcoef_volume(vol_r16f, tf_rgba, voxel=(1.0, 1.0, 1.0), res=(128, 128, 128), s0=1.0):
+    """Levels of the extinction-coefficient pyramid (list of float32 [d, h, w], R16F-rounded tau)."""
+    vol = np.ascontiguousarray(vol_r16f, np.float32); tf = np.ascontiguousarray(tf_rgba, np.float32)
+    d, h, w = vol.shape
+    n = lib().orc_dos_extcoef_num_levels(*res)
+    levels = [np.zeros((max(res[2] >> l, 1), max(res[1] >> l, 1), max(res[0] >> l, 1)), np.float32) for l in range(n)]
+    ptrs = (_P * n)(*[_ptr(a) for a in levels])
+    vx = (C.c_float * 3)(*voxel); rs = (C.c_int * 3)(*res)
+    lib().orc_dos_extcoef_volume(_ptr(vol), w, h, d, vx, _ptr(tf), tf.shape[0], rs, s0, ptrs)
+    return levels
+
+
+def dos_params(cam, width, height, vol_shape_zyx, step, light_pos, occ, sdw, ext_res, voxel=(1.0, 1.0, 1.0), apply_occlusion=1,
+               apply_shadow=0, type_of_shadow=0, spot_max_angle_deg=30.0, light_cam_forward=(0, 0, -1), light_cam_up=(0, 1, 0),
+               light_cam_right=(1, 0, 0), ka=0.5, kd=0.5, rows=None, threads=0):
+    p = DosParams()
+    p.width, p.height = width, height
+    p.vol_d, p.vol_h, p.vol_w = vol_shape_zyx
+    p.voxel[:] = voxel
+    p.eye[:] = list(cam.eye); p.lookat[:] = list(cam.lookat)
+    p.tan_fovy, p.aspect, p.step = cam.tan_fovy, cam.aspect, step
+    p.apply_occlusion, p.apply_shadow = apply_occlusion, apply_shadow
+    p.ext_res[:] = ext_res
+    p.occ_counts[:] = [int(x) for x in occ.counts]; p.occ_axes[:] = [float(x) for x in occ.axes.ravel()]
+    p.occ_initial_step, p.occ_adj7, p.occ_ui_weight = occ.initial_step, occ.adj7, occ.ui_weight
+    p.sdw_counts[:] = [int(x) for x in sdw.counts]; p.sdw_axes[:] = [float(x) for x in sdw.axes.ravel()]
+    p.sdw_initial_step, p.sdw_adj7, p.sdw_ui_weight = sdw.initial_step, sdw.adj7, sdw.ui_weight
+    p.type_of_shadow = type_of_shadow
+    p.spot_light_max_angle_cos = float(np.cos(np.float32(np.pi) * np.float32(spot_max_angle_deg) / np.float32(180.0)))
+    p.light_pos[:] = light_pos
+    p.light_cam_forward[:] = light_cam_forward; p.light_cam_up[:] = light_cam_up; p.light_cam_right[:] = light_cam_right
+    p.ka, p.kd = ka, kd
+    p.row_begin, p.row_end, p.row_stride = rows or (0, height, 1)
+    p.threads = threads
+    return p
+
+
+def dos_render(p, vol_r16f, tf_rgbt, levels, occ, sdw):
+    vol = np.ascontiguousarray(vol_r16f, np.float32); tf = np.ascontiguousarray(tf_rgbt, np.float32)
+    lv = [np.ascontiguousarray(a, np.float32) for a in levels]
+    ptrs = (_P * len(lv))(*[_ptr(a) for a in lv])
+    ot = np.ascontiguousarray(occ.table, np.float32); st = np.ascontiguousarray(sdw.table, np.float32)
+    out = np.zeros((p.height, p.width, 4), np.float32)
+    shaded = C.c_uint64()
+    total = lib().orc_dos_render(C.byref(p), _ptr(vol), _ptr(tf), tf.shape[0], ptrs, len(lv), _ptr(ot), _ptr(st), _ptr(out), C.byref(shaded))
+    return out, int(total), int(shaded.value)

@@ -33,6 +33,8 @@ def lib():
         L.ref_sat3d_build.argtypes = [_P, C.c_int, C.c_int, C.c_int, _P]
         L.ref_parameterspace_selftest.restype = C.c_int
         L.ref_parameterspace_sweep.argtypes = [C.c_float] * 6 + [_P, C.c_int]
+        L.ref_cone_sections.argtypes = [C.c_float, C.c_float, C.c_int, C.c_float, C.c_double, _P, C.c_int, _P, _P,
+                                        C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.ref_parameterspace_sweep.restype = C.c_int
         _lib = L
     return _lib
@@ -99,3 +101,13 @@ def parameterspace_sweep(a, b, cap=4096):
     out = np.zeros((cap, 2), np.float32)
     n = lib().ref_parameterspace_sweep(*map(float, a), *map(float, b), _ptr(out), cap)
     return n, out[:min(n, cap)]
+
+
+def cone_sections(half_angle, initial_step, max_packing, covered_distance, sigma0, cap=512):
+    """ConeGaussianSampler: (float32 section table [n, 4] as handed to glTexImage1D, axes [10, 3], counts [3], adj3, adj7)."""
+    import numpy as np
+    out = np.zeros((cap, 4), np.float32); axes = np.zeros((10, 3), np.float32); counts = np.zeros(3, np.int32)
+    a3, a7 = C.c_double(), C.c_double()
+    n = lib().ref_cone_sections(half_angle, initial_step, max_packing, covered_distance, sigma0, _ptr(out), cap, _ptr(axes),
+                                _ptr(counts), C.byref(a3), C.byref(a7))
+    return out[:n].copy(), axes, counts, a3.value, a7.value

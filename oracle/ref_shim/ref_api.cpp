@@ -4,7 +4,8 @@
 // and by bench.py's CPU SAT baseline (cpu_baseline.kind = "reference").
 //
 // Compiled sources: cppvolrend/utils/parameterspace.cpp, libs/volvis_utils/{structuredgridvolume,transferfunction,
-// transferfunction1d}.cpp; header-only: libs/vis_utils/summedareatable.h.  GL types come from ref_shim/stubs.
+// transferfunction1d}.cpp, cppvolrend/structured/rc1pdosct/conegaussiansampler.cpp,
+// RodriguesRotation from libs/math_utils/utils.cpp (extracted, see stubs/math_utils/utils.h); header-only: libs/vis_utils/summedareatable.h.  GL types come from ref_shim/stubs.
 #include <cstdint>
 #include <cstring>
 #include <vector>
@@ -13,6 +14,9 @@
 #include <vis_utils/summedareatable.h>
 #include <volvis_utils/structuredgridvolume.h>
 #include <volvis_utils/transferfunction1d.h>
+#include <structured/rc1pdosct/conegaussiansampler.h>
+#include <math_utils/utils.h>
+#include <rodrigues_excerpt.inc>   // the reference's RodriguesRotation bodies, extracted by the Makefile
 
 extern "C" {
 
@@ -91,6 +95,29 @@ int ref_parameterspace_sweep(float a0, float a1, float da, float b0, float b1, f
     n++;
   } while (ps.IncrEvaluation() && n < (1 << 20));
   ps.EndEvaluation();
+  return n;
+}
+
+// ---- ConeGaussianSampler (cppvolrend/structured/rc1pdosct/conegaussiansampler.cpp) -------------------------------
+// The section table exactly as GetConeSectionsInfoTex hands it to glTexImage1D (float32, before the RGBA16F store).
+int ref_cone_sections(float half_angle, float initial_step, int max_packing, float covered_distance, double sigma0,
+                      float* out_rgba, int cap, float* axes30, int* counts3, double* adj3, double* adj7) {
+  ConeGaussianSampler s;
+  s.SetConeHalfAngle(half_angle);
+  s.SetInitialStep(initial_step);
+  s.SetMaxGaussianPacking(max_packing);
+  s.SetCoveredDistance(covered_distance);
+  s.ComputeConeIntegrationSteps(sigma0);
+  gl::Texture1D* t = s.GetConeSectionsInfoTex();
+  int n = s.GetNumberOfComputedConeSections();
+  if (t) {
+    for (int i = 0; i < n * 4 && i < cap * 4; i++) out_rgba[i] = t->captured[i];
+    delete t;
+  }
+  for (int i = 0; i < 3; i++) { glm::vec3 a = s.Get3ConeRayID(i); axes30[3 * i] = a.x; axes30[3 * i + 1] = a.y; axes30[3 * i + 2] = a.z; }
+  for (int i = 0; i < 7; i++) { glm::vec3 a = s.Get7ConeRayID(i); axes30[9 + 3 * i] = a.x; axes30[9 + 3 * i + 1] = a.y; axes30[9 + 3 * i + 2] = a.z; }
+  counts3[0] = s.gaussian_samples_1; counts3[1] = s.gaussian_samples_3; counts3[2] = s.gaussian_samples_7;
+  *adj3 = s.GetRay3AdjacentWeight(); *adj7 = s.GetRay7AdjacentWeight();
   return n;
 }
 

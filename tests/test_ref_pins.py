@@ -74,3 +74,17 @@ def test_parameterspace_selftest_and_sweep():
     for a, b in pairs:
         assert a == acc and b == 1.0
         acc = np.float32(acc + np.float32(0.1))
+
+
+@pytest.mark.parametrize("half_angle,initial_step,packing,covered", [(20.0, 3.0, 1, 443.4), (0.5, 3.0, 0, 665.1), (30.0, 3.0, 2, 100.0),
+                                                                    (45.0, 1.0, 2, 300.0), (10.0, 3.0, 0, 50.0), (89.0, 0.0, 2, 5.0)])
+def test_cone_sections_match_the_reference_sampler(half_angle, initial_step, packing, covered):
+    """oracle restatement == the reference's own ConeGaussianSampler (compiled into libref): section table as stored in
+    the RGBA16F texture, the 3 + 7 ray axes, per-packing counts and adjacency weights."""
+    from oracle import pyoracle as O
+    c = O.ConeSections(half_angle, initial_step, packing, covered)
+    table, axes, counts, a3, a7 = R.cone_sections(half_angle, initial_step, packing, covered, 1.0)
+    assert len(table) == len(c.table) and len(table) > 0
+    assert np.array_equal(c.table, table.astype(np.float16).astype(np.float32), equal_nan=True)   # initial_step 0: 0/0 amplitude on both sides
+    assert np.array_equal(c.axes, axes) and np.array_equal(c.counts, counts)
+    assert c.adj3 == a3 and c.adj7 == a7
