@@ -69,8 +69,12 @@ static void register_all(RenderingManager* m) {
   m->AddVolumeRenderer(new CudaRayCasting1PassIso(VRB_ISO_ADAPT));      // 1
   m->AddVolumeRenderer(new CudaRayCasting1PassIso(VRB_ISO_SKIP_V1));    // 2
   m->AddVolumeRenderer(new CudaRayCasting1PassIso(VRB_ISO_SKIP_V2));    // 3
+  m->AddVolumeRenderer(new CudaRC1PConeTracingDirOcclusionShading());   // 4
+  m->AddVolumeRenderer(new CudaRC1PExtinctionBasedShading());           // 5
+  m->AddVolumeRenderer(new CudaRC1PVoxelConeTracingSGPU());             // 6
+  m->AddVolumeRenderer(new CudaSBTMDirectionalOcclusionShading());      // 7
 }
-int vrbh_num_renderers(void) { return 4; }
+int vrbh_num_renderers(void) { return 8; }
 
 // One headless session: read the dataset + TF from disk, register the plugins, select `renderer`, optionally run
 // the evaluation sweep (eval_dir != NULL; `numframes` frames per sample, CSV in the reference's schema), else

@@ -170,6 +170,136 @@ void CudaRayCasting1PassIso::FillParameterSpace(ParameterSpace& pspace) {
   pspace.AddParameterDimension(new ParameterRangeFloat("StepSizeRange", &m_u_step_size_range, 0.05f, 0.26f, 0.05f));
 }
 
+// ---- shadowed DVR plugins -----------------------------------------------------------------------------------------
+bool BaseVolumeRenderer::PushCameraAndLight(vis::Camera* camera) {
+  vrb_camera c; vrb_light l;
+  camera->FillUniforms(&c);
+  m_ext_rendering_parameters->FillUniforms(&l);
+  if (VrbApi::Get()->renderer_update(m_dev, &c, &l) != VRB_OK) return Fail("vrb_renderer_update");
+  return true;
+}
+
+CudaRC1PConeTracingDirOcclusionShading::CudaRC1PConeTracingDirOcclusionShading()       // dosrcrenderer.cpp:29-59
+    : m_u_step_size(0.5f), glsl_apply_occlusion(true), glsl_apply_shadow(false), type_of_shadow(0),
+      occ_cone_half_angle(20.0f), occ_initial_step(3.0f), occ_covered_distance(100.0f), occ_ui_weight(0.350f), occ_max_packing(1),
+      sdw_cone_half_angle(0.5f), sdw_initial_step(3.0f), sdw_covered_distance(100.0f), sdw_ui_weight(1.0f), sdw_max_packing(0),
+      base_level_sigma0(1.0f), use_custom_resolution(true) {
+  custom_resolution[0] = custom_resolution[1] = custom_resolution[2] = 128;
+}
+bool CudaRC1PConeTracingDirOcclusionShading::Init(int w, int h) {
+  if (!CreateDeviceRenderer(VRB_DOS_CONE, w, h)) return false;
+  vrb_dos_params p;
+  if (VrbApi::Get()->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  m_u_step_size = p.step_size;                                    // :124-125
+  occ_covered_distance = p.occ_covered_distance;                  // SetCoveredDistance(diagonal * 0.50 / 0.75), :111-112
+  sdw_covered_distance = p.sdw_covered_distance;
+  SetBuilt(true);
+  SetOutdated();
+  return true;
+}
+bool CudaRC1PConeTracingDirOcclusionShading::Update(vis::Camera* camera) {
+  if (!m_dev || !camera) return false;
+  const VrbApi* a = VrbApi::Get();
+  vrb_dos_params p;
+  if (a->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  p.step_size = m_u_step_size; p.apply_occlusion = glsl_apply_occlusion ? 1 : 0; p.apply_shadow = glsl_apply_shadow ? 1 : 0;
+  p.type_of_shadow = type_of_shadow;
+  p.occ_cone_half_angle = occ_cone_half_angle; p.occ_initial_step = occ_initial_step; p.occ_covered_distance = occ_covered_distance;
+  p.occ_ui_weight = occ_ui_weight; p.occ_max_packing = occ_max_packing;
+  p.sdw_cone_half_angle = sdw_cone_half_angle; p.sdw_initial_step = sdw_initial_step; p.sdw_covered_distance = sdw_covered_distance;
+  p.sdw_ui_weight = sdw_ui_weight; p.sdw_max_packing = sdw_max_packing;
+  p.base_level_sigma0 = base_level_sigma0; p.use_custom_resolution = use_custom_resolution ? 1 : 0;
+  for (int i = 0; i < 3; i++) p.custom_resolution[i] = custom_resolution[i];
+  if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
+  return PushCameraAndLight(camera);
+}
+
+CudaRC1PExtinctionBasedShading::CudaRC1PExtinctionBasedShading()                       // ebsrenderer.cpp:18-42
+    : m_u_step_size(0.5f), apply_ambient_occlusion(true), ambient_occlusion_shells(15), ambient_occlusion_radius(1.0f),
+      apply_directional_shadows(true), dir_shadow_cone_angle(1.0f), dir_shadow_sample_interval(2.0f), dir_shadow_initial_step(2.0f),
+      dir_shadow_user_interface_weight(1.0f), dir_cone_max_distance(0.0f), type_of_shadow(0), fast_sat(false) {}
+bool CudaRC1PExtinctionBasedShading::Init(int w, int h) {
+  if (!CreateDeviceRenderer(VRB_EBS_SAT, w, h)) return false;
+  vrb_ebs_params p;
+  if (VrbApi::Get()->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  m_u_step_size = p.step_size;                                    // :115-116
+  dir_cone_max_distance = p.dir_cone_max_distance;                // :99-105
+  SetBuilt(true);
+  SetOutdated();
+  return true;
+}
+bool CudaRC1PExtinctionBasedShading::Update(vis::Camera* camera) {
+  if (!m_dev || !camera) return false;
+  const VrbApi* a = VrbApi::Get();
+  vrb_ebs_params p;
+  if (a->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  p.step_size = m_u_step_size;
+  p.apply_ambient_occlusion = apply_ambient_occlusion ? 1 : 0; p.ambient_occlusion_shells = ambient_occlusion_shells;
+  p.ambient_occlusion_radius = ambient_occlusion_radius;
+  p.apply_directional_shadows = apply_directional_shadows ? 1 : 0; p.dir_shadow_cone_angle = dir_shadow_cone_angle;
+  p.dir_shadow_sample_interval = dir_shadow_sample_interval; p.dir_shadow_initial_step = dir_shadow_initial_step;
+  p.dir_shadow_user_interface_weight = dir_shadow_user_interface_weight; p.dir_cone_max_distance = dir_cone_max_distance;
+  p.type_of_shadow = type_of_shadow; p.fast_sat = fast_sat ? 1 : 0;
+  if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
+  return PushCameraAndLight(camera);
+}
+void CudaRC1PExtinctionBasedShading::FillParameterSpace(ParameterSpace& pspace) {
+  pspace.ClearParameterDimensions();
+  pspace.AddParameterDimension(new ParameterRangeInt("AmbientOccShells", &ambient_occlusion_shells, 1, 20, 1));
+  pspace.AddParameterDimension(new ParameterRangeFloat("AmbientOccRadius", &ambient_occlusion_radius, 0.1f, 1.5f, 0.1f));
+}
+
+CudaRC1PVoxelConeTracingSGPU::CudaRC1PVoxelConeTracingSGPU()                           // vctrenderer.cpp:27-43
+    : m_u_step_size(0.5f), apply_ambient_occlusion(true), apply_directional_shadows(true), apply_correction_factor(true),
+      cone_step_size(2.0f), cone_step_increase_rate(1.0f), cone_initial_step(2.0f), cone_apex_angle(2.0f),
+      opacity_correction_factor(2.0f), cone_number_of_samples(50) {}
+bool CudaRC1PVoxelConeTracingSGPU::Init(int w, int h) {
+  if (!CreateDeviceRenderer(VRB_VCT, w, h)) return false;
+  vrb_vct_params p;
+  if (VrbApi::Get()->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  m_u_step_size = p.step_size;
+  SetBuilt(true);
+  SetOutdated();
+  return true;
+}
+bool CudaRC1PVoxelConeTracingSGPU::Update(vis::Camera* camera) {
+  if (!m_dev || !camera) return false;
+  const VrbApi* a = VrbApi::Get();
+  vrb_vct_params p;
+  if (a->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  p.step_size = m_u_step_size;
+  p.apply_ambient_occlusion = apply_ambient_occlusion ? 1 : 0; p.apply_directional_shadows = apply_directional_shadows ? 1 : 0;
+  p.cone_step_size = cone_step_size; p.cone_step_increase_rate = cone_step_increase_rate; p.cone_initial_step = cone_initial_step;
+  p.cone_apex_angle = cone_apex_angle; p.apply_correction_factor = apply_correction_factor ? 1 : 0;
+  p.opacity_correction_factor = opacity_correction_factor; p.cone_number_of_samples = cone_number_of_samples;
+  if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
+  return PushCameraAndLight(camera);
+}
+
+CudaSBTMDirectionalOcclusionShading::CudaSBTMDirectionalOcclusionShading()             // sbtmdosrenderer.cpp:20-46
+    : m_u_step_size(0.5f), cone_half_angle(50.0f), occ_ui_weight_percentage(1.0f), max_number_of_passes(90000) {
+  grid_size[0] = grid_size[1] = 2;
+}
+bool CudaSBTMDirectionalOcclusionShading::Init(int w, int h) {
+  if (!CreateDeviceRenderer(VRB_SBTM_DOS, w, h)) return false;
+  vrb_sbtm_params p;
+  if (VrbApi::Get()->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  m_u_step_size = p.step_size;                                    // :113-114
+  SetBuilt(true);
+  SetOutdated();
+  return true;
+}
+bool CudaSBTMDirectionalOcclusionShading::Update(vis::Camera* camera) {
+  if (!m_dev || !camera) return false;
+  const VrbApi* a = VrbApi::Get();
+  vrb_sbtm_params p;
+  if (a->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  p.step_size = m_u_step_size; p.cone_half_angle = cone_half_angle; p.occ_ui_weight_percentage = occ_ui_weight_percentage;
+  p.grid_size[0] = grid_size[0]; p.grid_size[1] = grid_size[1]; p.max_number_of_passes = max_number_of_passes;
+  if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
+  return PushCameraAndLight(camera);
+}
+
 // ---- RenderingManager ----------------------------------------------------------------------------------------
 static RenderingManager* g_instance = nullptr;
 RenderingManager* RenderingManager::Instance() { if (!g_instance) g_instance = new RenderingManager(); return g_instance; }

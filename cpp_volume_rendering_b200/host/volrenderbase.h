@@ -48,6 +48,7 @@ class BaseVolumeRenderer {
   void SetBuilt(bool b) { vr_built = b; }
   bool CreateDeviceRenderer(int kind, int w, int h);    // vrb_renderer_create + init; false on failure
   bool Fail(const char* what);                          // records vrb_last_error()
+  bool PushCameraAndLight(vis::Camera* camera);         // the CameraEye / LookAt / light uniforms every Update() binds
   bool vr_built = false, vr_outdated = true, vr_pixel_multiscaling_support = false;
   int vr_pixel_multiscaling_mode = 0;
   vis::DataManager* m_ext_data_manager = nullptr;
@@ -88,6 +89,71 @@ class CudaRayCasting1PassIso : public BaseVolumeRenderer {
   int m_num_blocks[3];
  private:
   int m_kind;
+};
+
+// RC1PConeTracingDirOcclusionShading (structured/rc1pdosct/dosrcrenderer.{h,cpp}); the public members stand for the
+// renderer's own flags and for the setters of its two ConeGaussianSamplers and its ExtinctionCoefficientVolume.
+class CudaRC1PConeTracingDirOcclusionShading : public BaseVolumeRenderer {
+ public:
+  CudaRC1PConeTracingDirOcclusionShading();
+  const char* GetName() override { return "1-Pass - Ray Casting - Dir. Occlusion Shading (CUDA B200)"; }
+  const char* GetAbbreviationName() override { return "cu_s_1rc_dos"; }
+  vis::GRID_VOLUME_DATA_TYPE GetDataTypeSupport() override { return vis::GRID_VOLUME_DATA_TYPE::STRUCTURED; }
+  bool Init(int w, int h) override;
+  bool Update(vis::Camera* camera) override;
+  float m_u_step_size;
+  bool glsl_apply_occlusion, glsl_apply_shadow;
+  int type_of_shadow;
+  float occ_cone_half_angle, occ_initial_step, occ_covered_distance, occ_ui_weight;   int occ_max_packing;
+  float sdw_cone_half_angle, sdw_initial_step, sdw_covered_distance, sdw_ui_weight;   int sdw_max_packing;
+  float base_level_sigma0;
+  bool use_custom_resolution;
+  int custom_resolution[3];
+};
+
+// RC1PExtinctionBasedShading (structured/rc1pextbsd/ebsrenderer.{h,cpp})
+class CudaRC1PExtinctionBasedShading : public BaseVolumeRenderer {
+ public:
+  CudaRC1PExtinctionBasedShading();
+  const char* GetName() override { return "1-Pass - Ray Casting - Extinction-based (CUDA B200)"; }
+  const char* GetAbbreviationName() override { return "cu_s_1rc_eb"; }
+  vis::GRID_VOLUME_DATA_TYPE GetDataTypeSupport() override { return vis::GRID_VOLUME_DATA_TYPE::STRUCTURED; }
+  bool Init(int w, int h) override;
+  bool Update(vis::Camera* camera) override;
+  void FillParameterSpace(ParameterSpace& pspace) override;    // ebsrenderer.cpp:430-435
+  float m_u_step_size;
+  bool apply_ambient_occlusion; int ambient_occlusion_shells; float ambient_occlusion_radius;
+  bool apply_directional_shadows; float dir_shadow_cone_angle, dir_shadow_sample_interval, dir_shadow_initial_step;
+  float dir_shadow_user_interface_weight, dir_cone_max_distance; int type_of_shadow;
+  bool fast_sat;                        // new: separable-scan SAT builder instead of the reference's recurrence
+};
+
+// RC1PVoxelConeTracingSGPU (structured/rc1pvctsg/vctrenderer.{h,cpp})
+class CudaRC1PVoxelConeTracingSGPU : public BaseVolumeRenderer {
+ public:
+  CudaRC1PVoxelConeTracingSGPU();
+  const char* GetName() override { return "1-Pass - Ray Casting - Voxel Cone Tracing (CUDA B200)"; }
+  const char* GetAbbreviationName() override { return "cu_s_1rc_vct"; }
+  vis::GRID_VOLUME_DATA_TYPE GetDataTypeSupport() override { return vis::GRID_VOLUME_DATA_TYPE::STRUCTURED; }
+  bool Init(int w, int h) override;
+  bool Update(vis::Camera* camera) override;
+  float m_u_step_size;
+  bool apply_ambient_occlusion, apply_directional_shadows, apply_correction_factor;
+  float cone_step_size, cone_step_increase_rate, cone_initial_step, cone_apex_angle, opacity_correction_factor;
+  int cone_number_of_samples;
+};
+
+// SBTMDirectionalOcclusionShading (structured/sbtmdos/sbtmdosrenderer.{h,cpp})
+class CudaSBTMDirectionalOcclusionShading : public BaseVolumeRenderer {
+ public:
+  CudaSBTMDirectionalOcclusionShading();
+  const char* GetName() override { return "Slice-based - Directional Occlusion (CUDA B200)"; }
+  const char* GetAbbreviationName() override { return "cu_s_sbtm_dos"; }
+  vis::GRID_VOLUME_DATA_TYPE GetDataTypeSupport() override { return vis::GRID_VOLUME_DATA_TYPE::STRUCTURED; }
+  bool Init(int w, int h) override;
+  bool Update(vis::Camera* camera) override;
+  float m_u_step_size, cone_half_angle, occ_ui_weight_percentage;
+  int grid_size[2], max_number_of_passes;
 };
 
 // ---- RenderingManager: registry + Display() order + evaluation loop ----------------------------------------

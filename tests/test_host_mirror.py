@@ -83,7 +83,8 @@ def test_manager_session_equals_direct_abi_render(tmp_path, ctx, bonsai_table):
     eye = (float(n), float(n), 2.0 * n)
     ctx.upload_volume(vox); ctx.upload_tf(bonsai_table)
     cam = inputs.make_camera(eye, width=w, height=h)
-    for name, kind in [("rc1pass", _capi.VRB_RC1PASS), ("iso", _capi.VRB_ISO_ADAPT), ("iso_skip_v1", _capi.VRB_ISO_SKIP_V1), ("iso_skip_v2", _capi.VRB_ISO_SKIP_V2)]:
+    for name, kind in [("rc1pass", _capi.VRB_RC1PASS), ("iso", _capi.VRB_ISO_ADAPT), ("iso_skip_v1", _capi.VRB_ISO_SKIP_V1), ("iso_skip_v2", _capi.VRB_ISO_SKIP_V2),
+                       ("dos", _capi.VRB_DOS_CONE), ("ebs", _capi.VRB_EBS_SAT), ("vct", _capi.VRB_VCT), ("sbtm", _capi.VRB_SBTM_DOS)]:
         displays, rgba, rgb8, rname = hostapi.run_session(v, t, name, w, h, eye, numframes=2)
         assert displays == 2 and rname.endswith("(CUDA B200)")
         r = _capi.Renderer(ctx, kind)
@@ -110,3 +111,10 @@ def test_evaluation_writes_reference_csv_schema(tmp_path):
     displays, _, _, _ = hostapi.run_session(v, t, "iso_skip_v2", 64, 64, (48.0, 48.0, 96.0), eval_dir=out2, numframes=1, max_samples=7)
     rows = list(csv.reader(open(os.path.join(out2, "eval.csv"))))
     assert rows[0][:3] == ["StepSizeSmall", "StepSizeLarge", "StepSizeRange"] and len(rows) == 1 + 7
+    out3 = str(tmp_path / "eval_ebs")
+    displays, _, _, _ = hostapi.run_session(v, t, "ebs", 64, 64, (48.0, 48.0, 96.0), eval_dir=out3, numframes=1, max_samples=25)
+    rows = list(csv.reader(open(os.path.join(out3, "eval.csv"))))
+    assert rows[0][:2] == ["AmbientOccShells", "AmbientOccRadius"] and len(rows) == 1 + 25      # ebsrenderer.cpp:430-435
+    assert rows[1][:2] == ["1", "0.100000"] and rows[2][:2] == ["2", "0.100000"]
+    wrap = [i for i in range(2, 26) if rows[i][0] == "1"]
+    assert wrap and rows[wrap[0]][1] == "0.200000"                  # first dimension runs fastest, then the radius advances
