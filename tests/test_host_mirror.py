@@ -115,6 +115,6 @@ def test_evaluation_writes_reference_csv_schema(tmp_path):
     displays, _, _, _ = hostapi.run_session(v, t, "ebs", 64, 64, (48.0, 48.0, 96.0), eval_dir=out3, numframes=1, max_samples=25)
     rows = list(csv.reader(open(os.path.join(out3, "eval.csv"))))
     assert rows[0][:2] == ["AmbientOccShells", "AmbientOccRadius"] and len(rows) == 1 + 25      # ebsrenderer.cpp:430-435
-    assert rows[1][:2] == ["1", "0.100000"] and rows[2][:2] == ["2", "0.100000"]
-    wrap = [i for i in range(2, 26) if rows[i][0] == "1"]
-    assert wrap and rows[wrap[0]][1] == "0.200000"                  # first dimension runs fastest, then the radius advances
+    assert rows[1][:2] == ["1", "0.100000"] and rows[2][:2] == ["1", "0.200000"]
+    wrap = [i for i in range(2, 26) if rows[i][1] == "0.100000"]
+    assert wrap and rows[wrap[0]][0] == "2"                         # the last dimension runs fastest (validated against libref)
