@@ -201,11 +201,11 @@ def run_cuda(args):
     prm.exact_filter = args.exact
     r.set_params(prm)
     if world > 1:
-        # image tiles dealt round-robin; every rank's kernel stores its pixels straight into rank 0's frame (CUDA IPC
-        # peer memory over NVLink) — no collective on the frame
+        # image tiles dealt round-robin; every rank's kernel stores its pixels straight into every peer's frame (CUDA
+        # IPC peer memory over NVLink) and then raises a per-frame flag there; the stream waits on the flags
+        # (cuStreamWaitValue32) — no collective on the frame and none for the end-of-frame synchronisation
         from cpp_volume_rendering_b200 import multigpu
-        multigpu.setup_fused_gather(r, rank, world, tile=32, mode=_capi.VRB_GATHER_ROOT)
-    flag = torch.zeros(1, dtype=torch.int32, device=dev)
+        multigpu.setup_fused_gather(r, rank, world, tile=32, mode=_capi.VRB_GATHER_ALL)
 
     # sample count of this frame (instrumented launch, untimed)
     prm.count_samples = 1
@@ -224,8 +224,7 @@ def run_cuda(args):
         r.update(cam, light)
         r.redraw()
         if world > 1:
-            with torch.cuda.stream(stream):
-                dist.all_reduce(flag)      # 4-byte end-of-frame barrier: rank 0 knows every peer's tiles have landed
+            r.wait_peers()                 # every peer's tiles of this frame have landed in this rank's frame
 
     def barrier():
         if world > 1:
@@ -289,8 +288,7 @@ def run_cuda(args):
         r.update(cam, light)          # h2d: the step's inputs are the camera + light uniforms (kernel arguments)
         r.redraw()
         if world > 1:
-            with torch.cuda.stream(stream):
-                dist.all_reduce(flag)
+            r.wait_peers()
         if rank == 0 or world == 1:
             r.read_frame_into(pinned.data_ptr())   # d2h + synchronise
         else:

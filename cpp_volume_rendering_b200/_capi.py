@@ -116,6 +116,7 @@ SIGNATURES = {
     "vrb_iso_read_blocks": (C.c_int, [_P, _P, _P]),
     "vrb_renderer_set_partition": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
     "vrb_renderer_frame_export": (C.c_int, [_P, _P]),
+    "vrb_renderer_wait_peers": (C.c_int, [_P]),
     "vrb_renderer_set_peers": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int]),
     "vrb_bench_tex_peak": (C.c_int, [_P, C.POINTER(C.c_double)]),
 }
@@ -265,6 +266,9 @@ class Renderer:
         """handles: list of 64-byte IPC handles in rank order (own entry ignored); mode VRB_GATHER_*."""
         blob = b"".join(handles) if handles else b""
         _check(lib().vrb_renderer_set_peers(self._h, blob if handles else None, len(handles), rank, mode))
+
+    def wait_peers(self):
+        _check(lib().vrb_renderer_wait_peers(self._h))
 
     def read_sat(self, want_data=True):
         """(sat float32 [D+2, H+2, W+2] or None, build_ms)."""

@@ -23,6 +23,7 @@ struct EbsArgs {
   float cone_angle, interval, initial_step, weight, max_distance; int type_of_shadow;
   float light_pos[3], light_fwd[3], ka, kd;
   uint2* frame; uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
+  PeerSignal sig;
   unsigned long long* samples;
   int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; unsigned* queue;
 };
@@ -209,11 +210,7 @@ __global__ void __launch_bounds__(EBS_THREADS, 4) ebs_kernel(const __grid_consta
     for (int o = 16; o > 0; o >>= 1) nsamp += __shfl_xor_sync(0xffffffffu, nsamp, o);
     if (lane == 0 && nsamp) atomicAdd(a.samples, (unsigned long long)nsamp);
   }
-  if (lane == 0) {
-    const unsigned total_warps = gridDim.x * (blockDim.x >> 5);
-    __threadfence();
-    if (atomicAdd(a.queue + 1, 1u) == total_warps - 1) { a.queue[0] = 0u; a.queue[1] = 0u; }
-  }
+  finish_launch(a.queue, a.sig);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -305,6 +302,7 @@ class EbsRenderer : public RendererImpl {
     while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
     a.scramble = a.n_items > 2 ? sc : 1u;
     a.queue = d_queue;
+    fill_peer_signal(*this, a.sig);
     const size_t smem = (size_t)a.tf_n * sizeof(uint4) + (size_t)a.vis_words * sizeof(uint32_t);
     VRB_REQUIRE(smem <= 200 * 1024, VRB_ERR_UNSUPPORTED, "transfer function of %d entries does not fit shared memory", a.tf_n);
     cudaStream_t s = ctx->stream;

@@ -97,6 +97,7 @@ struct IsoArgs {
   const float* bmin; const float* bmax;
   uint2* frame;
   uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
+  PeerSignal sig;
   unsigned long long* iters;
   int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble;
   unsigned* queue;
@@ -266,11 +267,7 @@ __global__ void __launch_bounds__(ISO_THREADS, 6) iso_kernel(const __grid_consta
     for (int o = 16; o > 0; o >>= 1) nit += __shfl_xor_sync(0xffffffffu, nit, o);
     if (lane == 0 && nit) atomicAdd(a.iters, (unsigned long long)nit);
   }
-  if (lane == 0) {
-    const unsigned total_warps = gridDim.x * (blockDim.x >> 5);
-    __threadfence();
-    if (atomicAdd(a.queue + 1, 1u) == total_warps - 1) { a.queue[0] = 0u; a.queue[1] = 0u; }
-  }
+  finish_launch(a.queue, a.sig);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -361,6 +358,7 @@ class IsoRenderer : public RendererImpl {
     while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
     a.scramble = a.n_items > 2 ? sc : 1u;
     a.queue = d_queue;
+    fill_peer_signal(*this, a.sig);
     const int max_ctas = (a.n_items + ISO_THREADS / 32 - 1) / (ISO_THREADS / 32);
     cudaStream_t s = ctx->stream;
     if (prm_.count_iterations) VRB_CUDA(cudaMemsetAsync(d_samples, 0, sizeof(unsigned long long), s));

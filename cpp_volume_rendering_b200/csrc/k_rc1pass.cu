@@ -32,6 +32,7 @@ struct Rc1Args {
   float tan_fovy, aspect, step;
   uint2* frame;              // RGBA16F
   uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;   // frames of other ranks (fused gather over NVLink)
+  PeerSignal sig;
   unsigned long long* samples;
   // image-space partition: tiles of `tile` pixels dealt round-robin over ranks
   int rank, n_ranks, tile, tiles_x, n_tiles;
@@ -310,12 +311,7 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(cons
     for (int o = 16; o > 0; o >>= 1) nsamp += __shfl_xor_sync(0xffffffffu, nsamp, o);
     if (lane == 0 && nsamp) atomicAdd(a.samples, (unsigned long long)nsamp);
   }
-  // the last warp of the launch re-arms the queue for the next redraw
-  if (lane == 0) {
-    const unsigned total_warps = gridDim.x * (blockDim.x >> 5);
-    __threadfence();
-    if (atomicAdd(a.queue + 1, 1u) == total_warps - 1) { a.queue[0] = 0u; a.queue[1] = 0u; }
-  }
+  finish_launch(a.queue, a.sig);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -391,6 +387,7 @@ class Rc1Pass : public RendererImpl {
     while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
     a.scramble = a.n_items > 2 ? sc : 1u;
     a.queue = d_queue;
+    fill_peer_signal(*this, a.sig);
     // persistent grid: as many CTAs as fit on the GPU at once (occupancy query below), never more than there are items
     const int max_ctas = (a.n_items + CTA_THREADS / 32 - 1) / (CTA_THREADS / 32);
     if (prm_.skip_block) {

@@ -84,7 +84,15 @@ struct RendererImpl {
   int kind;
   int width = 0, height = 0;
   bool built = false;
-  __half* frame = nullptr;              // RGBA16F, width*height*4, row 0 = bottom
+  __half* frame = nullptr;              // RGBA16F, width*height*4, row 0 = bottom: the buffer of the current / last redraw
+  // One allocation: [frame buffer 0][frame buffer 1][FRAME_FLAGS words].  Single-GPU renders always use buffer 0.
+  // With peers (fused gather) redraw k renders into buffer k & 1 and, when the launch has finished, writes k into
+  // flag[rank] of every peer; vrb_renderer_wait_peers makes the stream wait for flag[q] >= k of every sender.
+  // Two buffers so that a peer may start frame k + 1 while this rank still reads frame k.
+  static constexpr int FRAME_FLAGS = 64;
+  void* frame_base = nullptr;
+  size_t frame_bytes = 0;
+  unsigned frame_seq = 0;
   vrb_camera cam{};
   vrb_light light{};
   bool have_cam = false;
@@ -92,10 +100,14 @@ struct RendererImpl {
   // fused gather (vrb_renderer_set_peers): frames of other ranks mapped through CUDA IPC; the render kernels store
   // each finished pixel into them as well, over NVLink, so no collective follows the launch
   static constexpr int MAX_PEERS = 15;
-  void* peer_frames[MAX_PEERS] = {};
+  void* peer_frames[MAX_PEERS] = {};     // peers' buffer (frame_seq & 1), refreshed by begin_frame()
   void* peer_opened[MAX_PEERS] = {};     // base pointers returned by cudaIpcOpenMemHandle (to close)
+  unsigned* peer_flags[MAX_PEERS] = {};  // this rank's word in each peer's flag block
   int n_peer_frames = 0;
+  int gather_mode = 0, gather_ranks = 1;
   void close_peers();
+  void begin_frame();                    // advances frame_seq and selects the buffers (vrb_renderer_redraw)
+  unsigned* flags() const { return (unsigned*)((char*)frame_base + 2 * frame_bytes); }
   unsigned long long* d_samples = nullptr;
   unsigned* d_queue = nullptr;          // 2 words, zero between launches: dynamic work queue of persistent kernels
   uint64_t last_samples = 0;
@@ -112,6 +124,32 @@ struct RendererImpl {
   int alloc_frame(int w, int h);
   void free_frame();
 };
+
+// End-of-frame signal of the fused gather, passed to every partitioned render kernel.
+struct PeerSignal { unsigned* flag[RendererImpl::MAX_PEERS]; int n; unsigned seq; };
+inline void fill_peer_signal(const RendererImpl& r, PeerSignal& ps) {
+  ps.n = r.n_peer_frames; ps.seq = r.frame_seq;
+  for (int q = 0; q < r.n_peer_frames; q++) ps.flag[q] = r.peer_flags[q];
+}
+#ifdef __CUDACC__
+// Called by every warp when it has no more work (all lanes).  The last warp of the launch re-arms the work queue for
+// the next redraw and, with peers, publishes the frame number: every warp's pixel stores to peer memory are made
+// visible system-wide before its increment, so a peer that sees the flag also sees the pixels.
+__device__ __forceinline__ void finish_launch(unsigned* queue, const PeerSignal& ps) {
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) {
+    const unsigned total_warps = gridDim.x * (blockDim.x >> 5);
+    if (ps.n) __threadfence_system(); else __threadfence();
+    if (atomicAdd(queue + 1, 1u) == total_warps - 1) {
+      queue[0] = 0u; queue[1] = 0u;
+      if (ps.n) {
+        __threadfence_system();
+        for (int q = 0; q < ps.n; q++) *(volatile unsigned*)ps.flag[q] = ps.seq;
+      }
+    }
+  }
+}
+#endif
 
 RendererImpl* make_rc1pass(vrb_ctx* ctx);
 RendererImpl* make_iso(vrb_ctx* ctx, int kind);

@@ -21,6 +21,7 @@ struct MarchArgs {
   float light_pos[3], ka, kd;
   int apply_occlusion, apply_shadow;
   uint2* frame; uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
+  PeerSignal sig;
   unsigned long long* samples;
   int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; unsigned* queue;
 };
@@ -111,11 +112,7 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
     for (int o = 16; o > 0; o >>= 1) nsamp += __shfl_xor_sync(0xffffffffu, nsamp, o);
     if (lane == 0 && nsamp) atomicAdd(a.samples, (unsigned long long)nsamp);
   }
-  if (lane == 0) {
-    const unsigned total_warps = gridDim.x * (blockDim.x >> 5);
-    __threadfence();
-    if (atomicAdd(a.queue + 1, 1u) == total_warps - 1) { a.queue[0] = 0u; a.queue[1] = 0u; }
-  }
+  finish_launch(a.queue, a.sig);
 }
 
 // Fills the renderer-independent arguments from the renderer state; returns false when this rank owns no tiles.
@@ -145,6 +142,7 @@ inline bool fill_march_args(const RendererImpl& r, float step, int apply_occlusi
   while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
   a.scramble = a.n_items > 2 ? sc : 1u;
   a.queue = r.d_queue;
+  fill_peer_signal(r, a.sig);
   return true;
 }
 

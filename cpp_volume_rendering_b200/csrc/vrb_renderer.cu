@@ -10,22 +10,37 @@ int RendererImpl::alloc_frame(int w, int h) {
   VRB_REQUIRE(w > 0 && h > 0 && w <= 32768 && h <= 32768, VRB_ERR_INVALID, "bad frame size %dx%d", w, h);
   if (frame && w == width && h == height) return VRB_OK;
   free_frame();
-  // RenderFrameToScreen::UpdateScreenResolution (renderoutputframe.cpp:64-87): RGBA16F W x H
-  VRB_CUDA(cudaMalloc(&frame, (size_t)w * h * 4 * sizeof(__half)));
-  VRB_CUDA(cudaMemsetAsync(frame, 0, (size_t)w * h * 4 * sizeof(__half), ctx->stream));
+  // RenderFrameToScreen::UpdateScreenResolution (renderoutputframe.cpp:64-87): RGBA16F W x H (two buffers + flags,
+  // see RendererImpl::frame_base)
+  frame_bytes = (size_t)w * h * 4 * sizeof(__half);
+  const size_t total = 2 * frame_bytes + FRAME_FLAGS * sizeof(unsigned);
+  VRB_CUDA(cudaMalloc(&frame_base, total));
+  VRB_CUDA(cudaMemsetAsync(frame_base, 0, total, ctx->stream));
+  frame = (__half*)frame_base;
+  frame_seq = 0;
   width = w; height = h;
   return VRB_OK;
 }
 
 void RendererImpl::close_peers() {
   for (int i = 0; i < MAX_PEERS; i++) if (peer_opened[i]) { cudaIpcCloseMemHandle(peer_opened[i]); peer_opened[i] = nullptr; }
-  n_peer_frames = 0;
+  n_peer_frames = 0; gather_mode = 0; gather_ranks = 1;
+  frame_seq = 0;
+  if (frame_base) frame = (__half*)frame_base;
 }
 
 void RendererImpl::free_frame() {
   close_peers();   // peers hold handles of frames of this size only
-  if (frame) cudaFree(frame);
-  frame = nullptr; width = height = 0;
+  if (frame_base) cudaFree(frame_base);
+  frame_base = nullptr; frame = nullptr; frame_bytes = 0; width = height = 0;
+}
+
+void RendererImpl::begin_frame() {
+  if (gather_mode == VRB_GATHER_NONE) return;       // single GPU: buffer 0, no sequence
+  frame_seq++;
+  const size_t off = (size_t)(frame_seq & 1u) * frame_bytes;
+  frame = (__half*)((char*)frame_base + off);
+  for (int q = 0; q < n_peer_frames; q++) peer_frames[q] = (char*)peer_opened[q] + off;
 }
 
 }  // namespace vrb
@@ -120,6 +135,7 @@ int vrb_renderer_redraw(vrb_renderer* r, int mode) {
   RendererImpl* p = r->impl;
   cudaStream_t s = p->ctx->stream;
   VRB_CUDA(cudaEventRecord(p->ev0, s));
+  p->begin_frame();
   int rc = p->redraw(mode);
   if (rc != VRB_OK) return rc;
   VRB_CUDA(cudaEventRecord(p->ev1, s));
@@ -190,7 +206,7 @@ int vrb_renderer_frame_export(vrb_renderer* r, void* handle_out) {
   VRB_REQUIRE(p->frame, VRB_ERR_INVALID, "vrb_renderer_frame_export before Init");
   static_assert(sizeof(cudaIpcMemHandle_t) == VRB_IPC_HANDLE_BYTES, "IPC handle size");
   cudaIpcMemHandle_t h;
-  VRB_CUDA(cudaIpcGetMemHandle(&h, p->frame));
+  VRB_CUDA(cudaIpcGetMemHandle(&h, p->frame_base));
   memcpy(handle_out, &h, sizeof(h));
   return VRB_OK;
 }
@@ -213,7 +229,43 @@ int vrb_renderer_set_peers(vrb_renderer* r, const void* handles, int n_ranks, in
     void* ptr = nullptr;
     VRB_CUDA(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
     p->peer_opened[p->n_peer_frames] = ptr;
+    p->peer_flags[p->n_peer_frames] = (unsigned*)((char*)ptr + 2 * p->frame_bytes) + rank;
     p->peer_frames[p->n_peer_frames++] = ptr;
+  }
+  p->gather_mode = mode; p->gather_ranks = n_ranks;
+  // flags restart from 0 with the sequence; the caller synchronises the ranks before the first redraw (multigpu.py)
+  VRB_CUDA(cudaMemsetAsync(p->flags(), 0, RendererImpl::FRAME_FLAGS * sizeof(unsigned), p->ctx->stream));
+  VRB_CUDA(cudaStreamSynchronize(p->ctx->stream));
+  return VRB_OK;
+}
+
+// cuStreamWaitValue32 through the runtime's driver entry point lookup (no link against libcuda)
+typedef int (*stream_wait_value32_fn)(cudaStream_t, unsigned long long, unsigned, unsigned);
+static stream_wait_value32_fn get_stream_wait_value32() {
+  static stream_wait_value32_fn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &f, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = (stream_wait_value32_fn)f;
+    else cudaGetLastError();
+  }
+  return fn;
+}
+
+int vrb_renderer_wait_peers(vrb_renderer* r) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_wait_peers: null renderer");
+  RendererImpl* p = r->impl;
+  if (p->gather_mode == VRB_GATHER_NONE || p->gather_ranks <= 1) return VRB_OK;
+  if (p->gather_mode == VRB_GATHER_ROOT && p->rank != 0) return VRB_OK;      // only rank 0 collects
+  stream_wait_value32_fn wait = get_stream_wait_value32();
+  VRB_REQUIRE(wait, VRB_ERR_UNSUPPORTED, "vrb_renderer_wait_peers: cuStreamWaitValue32 is not available");
+  for (int q = 0; q < p->gather_ranks; q++) {
+    if (q == p->rank) continue;
+    const int rc = wait(p->ctx->stream, (unsigned long long)(uintptr_t)(p->flags() + q), p->frame_seq, 0x0u /* CU_STREAM_WAIT_VALUE_GEQ */);
+    VRB_REQUIRE(rc == 0, VRB_ERR_CUDA, "cuStreamWaitValue32 failed: %d", rc);
   }
   return VRB_OK;
 }
@@ -260,7 +312,7 @@ int vrb_renderer_set_partition(vrb_renderer* r, int rank, int n_ranks, int tile)
   RendererImpl* p = r->impl;
   p->rank = rank; p->n_ranks = n_ranks; p->part_tile = tile;
   if (p->frame) {  // tiles owned by other ranks must read 0
-    VRB_CUDA(cudaMemsetAsync(p->frame, 0, (size_t)p->width * p->height * 8, p->ctx->stream));
+    VRB_CUDA(cudaMemsetAsync(p->frame_base, 0, 2 * p->frame_bytes, p->ctx->stream));
   }
   return VRB_OK;
 }

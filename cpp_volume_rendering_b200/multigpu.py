@@ -1,8 +1,8 @@
 """Image-space partition across ranks (one process per GPU).
 
-Plumbing only: torch.distributed carries the 64-byte IPC handles and the end-of-frame barrier; the pixels themselves
-are stored straight into the peers' frames by the render kernels (vrb_renderer_set_peers), so no collective touches
-the frame.  The reference has no multi-GPU path; parity is defined against the single-GPU frame.
+Plumbing only: torch.distributed carries the 64-byte IPC handles once; the pixels themselves are stored straight into
+the peers' frames by the render kernels (vrb_renderer_set_peers), followed by a per-frame flag the consumer's stream
+waits on (vrb_renderer_wait_peers), so no collective touches the frame or the end-of-frame synchronisation.  The reference has no multi-GPU path; parity is defined against the single-GPU frame.
 """
 import numpy as np
 
@@ -30,8 +30,10 @@ def setup_fused_gather(renderer, rank, world, tile=32, mode=_capi.VRB_GATHER_ROO
     """Partition the image over `world` ranks and map the peers' frames into `renderer`."""
     renderer.set_partition(rank, world, tile)
     if world > 1:
+        import torch.distributed as dist
         handles = exchange_handles(renderer.frame_export(), group)
         renderer.set_peers(handles, rank, mode)
+        dist.barrier(group=group)      # every rank has zeroed its flags before the first peer writes one
 
 
 def frame_barrier(device=None, group=None):

@@ -284,6 +284,14 @@ typedef enum { VRB_GATHER_NONE = 0, VRB_GATHER_ROOT = 1, VRB_GATHER_ALL = 2 } vr
 int vrb_renderer_frame_export(vrb_renderer* r, void* handle_out);
 int vrb_renderer_set_peers(vrb_renderer* r, const void* handles, int n_ranks, int rank, int mode);
 
+/* End-of-frame synchronisation of the fused gather, without a collective: every render launch, when its last warp
+ * retires, stores the frame number into this rank's flag word in each peer's frame allocation; wait_peers makes the
+ * context stream wait (cuStreamWaitValue32, no spinning kernel) until every sender's flag has reached the frame number
+ * of this rank's last redraw.  Frames are double-buffered, so a peer may already render frame k + 1 into this rank's
+ * other buffer while frame k is read here.  All ranks must call redraw the same number of times.
+ * VRB_GATHER_ROOT: only rank 0 waits; other ranks return at once. */
+int vrb_renderer_wait_peers(vrb_renderer* r);
+
 /* ---- measurement ---------------------------------------------------------------------------- */
 /* Cache-resident trilinear R16F tex3D microbenchmark: the texture-fetch roofline denominator P_tex
  * (SURVEY.md §8d).  Returns fetches per second of the whole GPU. */

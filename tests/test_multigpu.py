@@ -74,9 +74,9 @@ def _gpu_worker(rank, world, port, mode, q):
             r.init(w, h)
             multigpu.setup_fused_gather(r, rank, world, tile=16, mode=mode)
             r.update(cam)
-            r.redraw()
-            ctx.synchronize()
-            dist.barrier()                           # every rank's stores have landed
+            for _ in range(3):                       # three frames: the flags count frames, the buffers alternate
+                r.redraw()
+                r.wait_peers()                       # stream-ordered: every sender's tiles of this frame have landed
             out[kind] = r.read_frame(_capi.VRB_FRAME_RGBA32F)
             dist.barrier()                           # nobody unmaps before everyone has read
             r.set_peers([], rank, _capi.VRB_GATHER_NONE)
@@ -106,10 +106,15 @@ def test_fused_gather_two_ranks_one_gpu(ctx, bonsai_table, mode):
     procs = [mpc.Process(target=_gpu_worker, args=(rk, 2, port, mode, q)) for rk in range(2)]
     for p in procs:
         p.start()
-    res = dict(q.get(timeout=300) for _ in range(2))
-    for p in procs:
-        p.join(timeout=60)
-        assert p.exitcode == 0
+    try:
+        res = dict(q.get(timeout=150) for _ in range(2))
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+    finally:
+        for p in procs:                              # a rank stuck on a flag must not outlive the test
+            if p.is_alive():
+                p.kill()
     from cpp_volume_rendering_b200 import multigpu
     owner = multigpu.tile_owner_map(w, h, 16, 2)
     for kind in full:
