@@ -38,6 +38,7 @@ struct Rc1Args {
   int rank, n_ranks, tile, tiles_x, n_tiles;
   int n_items; unsigned scramble;       // item order: item = (ticket * scramble) % n_items
   unsigned* queue;                      // [0] next ticket, [1] warps finished (self-resetting)
+  const int* tile_order;                // this rank's tiles, centre of the image first (scramble == 0)
   // empty-space skipping: block edge in voxels, grid of blocks, Chebyshev run map (k_skipmap.cu)
   int skip_block; int nbx, nby, nbz; const uint8_t* skip_map;
 };
@@ -195,9 +196,9 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(cons
   if (lane == 0) raw = (int)atomicAdd(a.queue, 1u);
   raw = __shfl_sync(0xffffffffu, raw, 0);
   if (raw >= a.n_items) break;
-  const int it = (int)(((unsigned long long)raw * a.scramble) % (unsigned)a.n_items);
+  const int it = a.scramble ? (int)(((unsigned long long)raw * a.scramble) % (unsigned)a.n_items) : raw;
   const int local_tile = it / per_tile, sub = it % per_tile;
-  const int tile_id = a.rank + local_tile * a.n_ranks;
+  const int tile_id = a.scramble ? a.rank + local_tile * a.n_ranks : __ldg(a.tile_order + local_tile);
   const int tx = tile_id % a.tiles_x, ty = tile_id / a.tiles_x;
 #if VRB_RC1_QUAD2X2
   // lanes 4q..4q+3 (one texture-unit quad) cover 2x2 pixels; 4x2 quads make the 8x4 footprint
@@ -386,6 +387,12 @@ class Rc1Pass : public RendererImpl {
     auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned t = x % y; x = y; y = t; } return x; };
     while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
     a.scramble = a.n_items > 2 ? sc : 1u;
+    static const bool lpt = []() { const char* e = getenv("VRB_ITEM_ORDER"); return !(e && e[0] == '0'); }();   // 0: scrambled order
+    if (lpt) {
+      const int rc = ensure_tile_order();
+      if (rc != VRB_OK) return rc;
+      a.tile_order = d_tile_order; a.scramble = 0u;
+    }
     a.queue = d_queue;
     fill_peer_signal(*this, a.sig);
     // persistent grid: as many CTAs as fit on the GPU at once (occupancy query below), never more than there are items

@@ -110,6 +110,11 @@ struct RendererImpl {
   unsigned* flags() const { return (unsigned*)((char*)frame_base + 2 * frame_bytes); }
   unsigned long long* d_samples = nullptr;
   unsigned* d_queue = nullptr;          // 2 words, zero between launches: dynamic work queue of persistent kernels
+  // This rank's partition tiles, centre of the image first: rays through the middle of the volume are the longest, so
+  // the dynamic queue hands the long items out first and the launch ends on short ones (longest-processing-time order).
+  int* d_tile_order = nullptr;
+  int tile_order_key[5] = {0, 0, 0, 0, 0};      // width, height, tile, rank, n_ranks the list was built for
+  int ensure_tile_order();
   uint64_t last_samples = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool timed = false;

@@ -1,6 +1,9 @@
 // C entry points of the renderer half of the ABI: lifecycle calls that mirror BaseVolumeRenderer
 // (cppvolrend/volrenderbase.h:25-97) and dispatch to the per-kind implementation.
 #include "vrb_internal.cuh"
+#include <algorithm>
+#include <cstdlib>
+#include <utility>
 #include <vector>
 #include <cstring>
 
@@ -33,6 +36,25 @@ void RendererImpl::free_frame() {
   close_peers();   // peers hold handles of frames of this size only
   if (frame_base) cudaFree(frame_base);
   frame_base = nullptr; frame = nullptr; frame_bytes = 0; width = height = 0;
+}
+
+int RendererImpl::ensure_tile_order() {
+  const int key[5] = {width, height, part_tile, rank, n_ranks};
+  if (d_tile_order && memcmp(key, tile_order_key, sizeof(key)) == 0) return VRB_OK;
+  const int tx = (width + part_tile - 1) / part_tile, ty = (height + part_tile - 1) / part_tile;
+  std::vector<std::pair<float, int>> mine;
+  for (int t = rank; t < tx * ty; t += n_ranks) {
+    const float cx = ((t % tx) + 0.5f) * part_tile - 0.5f * width, cy = ((t / tx) + 0.5f) * part_tile - 0.5f * height;
+    mine.push_back(std::make_pair(cx * cx + cy * cy, t));
+  }
+  std::sort(mine.begin(), mine.end());
+  std::vector<int> order(mine.size());
+  for (size_t i = 0; i < mine.size(); i++) order[i] = mine[i].second;
+  if (d_tile_order) { cudaFree(d_tile_order); d_tile_order = nullptr; }
+  VRB_CUDA(cudaMalloc(&d_tile_order, std::max<size_t>(order.size(), 1) * sizeof(int)));
+  if (!order.empty()) VRB_CUDA(cudaMemcpy(d_tile_order, order.data(), order.size() * sizeof(int), cudaMemcpyHostToDevice));
+  memcpy(tile_order_key, key, sizeof(key));
+  return VRB_OK;
 }
 
 void RendererImpl::begin_frame() {
@@ -86,6 +108,7 @@ int vrb_renderer_destroy(vrb_renderer* r) {
   p->free_frame();
   if (p->d_samples) cudaFree(p->d_samples);
   if (p->d_queue) cudaFree(p->d_queue);
+  if (p->d_tile_order) cudaFree(p->d_tile_order);
   if (p->ev0) cudaEventDestroy(p->ev0);
   if (p->ev1) cudaEventDestroy(p->ev1);
   delete p;
