@@ -25,7 +25,7 @@ struct EbsArgs {
   uint2* frame; uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
   PeerSignal sig;
   unsigned long long* samples;
-  int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; unsigned* queue;
+  int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; const int* tile_order; unsigned* queue;
 };
 
 struct EbsConst { f3 scales, sizes, min_sat, max_sat, min_vol, max_vol, inv_vol_scaled, sat_res; };
@@ -150,9 +150,9 @@ __global__ void __launch_bounds__(EBS_THREADS, 4) ebs_kernel(const __grid_consta
     if (lane == 0) raw = (int)atomicAdd(a.queue, 1u);
     raw = __shfl_sync(0xffffffffu, raw, 0);
     if (raw >= a.n_items) break;
-    const int it = (int)(((unsigned long long)raw * a.scramble) % (unsigned)a.n_items);
+    const int it = a.scramble ? (int)(((unsigned long long)raw * a.scramble) % (unsigned)a.n_items) : raw;
     const int local_tile = it / per_tile, sub = it % per_tile;
-    const int tile_id = a.rank + local_tile * a.n_ranks;
+    const int tile_id = a.scramble ? a.rank + local_tile * a.n_ranks : __ldg(a.tile_order + local_tile);
     const int tx_ = tile_id % a.tiles_x, ty_ = tile_id / a.tiles_x;
     const int lx = ((lane >> 2) & 3) * 2 + (lane & 1), ly = (lane >> 4) * 2 + ((lane >> 1) & 1);
     const int px = tx_ * a.tile + (sub % per_tile_x) * 8 + lx, py = ty_ * a.tile + (sub / per_tile_x) * 4 + ly;
@@ -301,6 +301,11 @@ class EbsRenderer : public RendererImpl {
     auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned t = x % y; x = y; y = t; } return x; };
     while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
     a.scramble = a.n_items > 2 ? sc : 1u;
+    if (use_lpt_order()) {
+      const int rc_o = ensure_tile_order();
+      if (rc_o != VRB_OK) return rc_o;
+      a.tile_order = d_tile_order; a.scramble = 0u;
+    }
     a.queue = d_queue;
     fill_peer_signal(*this, a.sig);
     const size_t smem = (size_t)a.tf_n * sizeof(uint4) + (size_t)a.vis_words * sizeof(uint32_t);

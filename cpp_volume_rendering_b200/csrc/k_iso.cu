@@ -99,7 +99,7 @@ struct IsoArgs {
   uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
   PeerSignal sig;
   unsigned long long* iters;
-  int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble;
+  int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; const int* tile_order;
   unsigned* queue;
 };
 
@@ -142,9 +142,9 @@ __global__ void __launch_bounds__(ISO_THREADS, 6) iso_kernel(const __grid_consta
     if (lane == 0) raw = (int)atomicAdd(a.queue, 1u);
     raw = __shfl_sync(0xffffffffu, raw, 0);
     if (raw >= a.n_items) break;
-    const int it = (int)(((unsigned long long)raw * a.scramble) % (unsigned)a.n_items);
+    const int it = a.scramble ? (int)(((unsigned long long)raw * a.scramble) % (unsigned)a.n_items) : raw;
     const int local_tile = it / per_tile, sub = it % per_tile;
-    const int tile_id = a.rank + local_tile * a.n_ranks;
+    const int tile_id = a.scramble ? a.rank + local_tile * a.n_ranks : __ldg(a.tile_order + local_tile);
     const int tx = tile_id % a.tiles_x, ty = tile_id / a.tiles_x;
     const int lx = ((lane >> 2) & 3) * 2 + (lane & 1), ly = (lane >> 4) * 2 + ((lane >> 1) & 1);
     const int px = tx * a.tile + (sub % per_tile_x) * ISO_WARP_W + lx;
@@ -357,6 +357,11 @@ class IsoRenderer : public RendererImpl {
     auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned t = x % y; x = y; y = t; } return x; };
     while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
     a.scramble = a.n_items > 2 ? sc : 1u;
+    if (use_lpt_order()) {
+      const int rc_o = ensure_tile_order();
+      if (rc_o != VRB_OK) return rc_o;
+      a.tile_order = d_tile_order; a.scramble = 0u;
+    }
     a.queue = d_queue;
     fill_peer_signal(*this, a.sig);
     const int max_ctas = (a.n_items + ISO_THREADS / 32 - 1) / (ISO_THREADS / 32);

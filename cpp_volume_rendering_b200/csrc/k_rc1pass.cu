@@ -387,8 +387,7 @@ class Rc1Pass : public RendererImpl {
     auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned t = x % y; x = y; y = t; } return x; };
     while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
     a.scramble = a.n_items > 2 ? sc : 1u;
-    static const bool lpt = []() { const char* e = getenv("VRB_ITEM_ORDER"); return !(e && e[0] == '0'); }();   // 0: scrambled order
-    if (lpt) {
+    if (use_lpt_order()) {
       const int rc = ensure_tile_order();
       if (rc != VRB_OK) return rc;
       a.tile_order = d_tile_order; a.scramble = 0u;

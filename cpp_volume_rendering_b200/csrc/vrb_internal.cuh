@@ -1,6 +1,7 @@
 // Internal declarations of libvrb200.so (not part of the ABI).
 #pragma once
 #include <cuda_runtime.h>
+#include <cstdlib>
 #include <cuda_fp16.h>
 #include <cstdint>
 #include <cstdio>
@@ -129,6 +130,9 @@ struct RendererImpl {
   int alloc_frame(int w, int h);
   void free_frame();
 };
+
+// VRB_ITEM_ORDER=0 restores the scrambled item order (A/B measurements); default: longest first.
+inline bool use_lpt_order() { static const bool v = []() { const char* e = getenv("VRB_ITEM_ORDER"); return !(e && e[0] == '0'); }(); return v; }
 
 // End-of-frame signal of the fused gather, passed to every partitioned render kernel.
 struct PeerSignal { unsigned* flag[RendererImpl::MAX_PEERS]; int n; unsigned seq; };

@@ -23,7 +23,7 @@ struct MarchArgs {
   uint2* frame; uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
   PeerSignal sig;
   unsigned long long* samples;
-  int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; unsigned* queue;
+  int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; const int* tile_order; unsigned* queue;
 };
 
 constexpr int MARCH_THREADS = 128;
@@ -52,9 +52,9 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
     if (lane == 0) raw = (int)atomicAdd(a.queue, 1u);
     raw = __shfl_sync(0xffffffffu, raw, 0);
     if (raw >= a.n_items) break;
-    const int it = (int)(((unsigned long long)raw * a.scramble) % (unsigned)a.n_items);
+    const int it = a.scramble ? (int)(((unsigned long long)raw * a.scramble) % (unsigned)a.n_items) : raw;
     const int local_tile = it / per_tile, sub = it % per_tile;
-    const int tile_id = a.rank + local_tile * a.n_ranks;
+    const int tile_id = a.scramble ? a.rank + local_tile * a.n_ranks : __ldg(a.tile_order + local_tile);
     const int tx_ = tile_id % a.tiles_x, ty_ = tile_id / a.tiles_x;
     const int lx = ((lane >> 2) & 3) * 2 + (lane & 1), ly = (lane >> 4) * 2 + ((lane >> 1) & 1);
     const int px = tx_ * a.tile + (sub % per_tile_x) * 8 + lx, py = ty_ * a.tile + (sub / per_tile_x) * 4 + ly;
@@ -141,6 +141,10 @@ inline bool fill_march_args(const RendererImpl& r, float step, int apply_occlusi
   auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned tt = x % y; x = y; y = tt; } return x; };
   while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
   a.scramble = a.n_items > 2 ? sc : 1u;
+  if (use_lpt_order()) {
+    if (const_cast<RendererImpl&>(r).ensure_tile_order() != VRB_OK) return false;
+    a.tile_order = r.d_tile_order; a.scramble = 0u;
+  }
   a.queue = r.d_queue;
   fill_peer_signal(r, a.sig);
   return true;
