@@ -199,6 +199,9 @@ def run_cuda(args):
     prm.skip_block = args.skip
     prm.tf_in_smem = args.tf_smem
     prm.exact_filter = args.exact
+    # few pixels per GPU: the per-ray dependent chain bounds the frame, so more lanes share a ray (include/vrb200.h)
+    depth_split = args.depth_split if args.depth_split >= 0 else (0 if world == 1 else (2 if world == 2 else (4 if world == 4 else 8)))
+    prm.depth_split = depth_split
     r.set_params(prm)
     if world > 1:
         # image tiles dealt round-robin; every rank's kernel stores its pixels straight into every peer's frame (CUDA
@@ -328,7 +331,7 @@ def run_cuda(args):
                        "partition": f"image tiles 32x32 round-robin over {world} rank(s)" + (", fused peer-memory gather into rank 0 + 4-byte NCCL end-of-frame barrier" if world > 1 else ""),
                        "l2_policy": "inputs_larger_than_l2 (256 MiB R16F volume vs 126 MB L2)",
                        "samples_per_frame": fetched_total, "fps": 1e3 / ms_per_step, "init_ms_volume_upload": init_ms,
-                       "tf_in_smem": args.tf_smem, "exact_filter": args.exact, "skip_block": args.skip, "with_skipping": skip_info},
+                       "tf_in_smem": args.tf_smem, "exact_filter": args.exact, "skip_block": args.skip, "depth_split": depth_split, "with_skipping": skip_info},
             "e2e": {"value": fetched_total / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": ctypes.sizeof(_capi.Camera) + ctypes.sizeof(_capi.Light),
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "fps": 1e3 / e2e_ms},
             "gpu_launches": args.steps,
@@ -370,6 +373,7 @@ def main():
     ap.add_argument("--tf-smem", type=int, default=1)
     ap.add_argument("--exact", type=int, default=1, help="float32 re-filtering of possibly-visible samples")
     ap.add_argument("--no-cpu", action="store_true", help="omit the cpu_baseline leg")
+    ap.add_argument("--depth-split", type=int, default=-1, help="lanes per ray (0/1, 2, 4, 8); -1 = by the number of GPUs")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -316,13 +316,157 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(cons
 }
 
 // ---------------------------------------------------------------------------------------------
+// Depth-split variant (vrb_rc1pass_params::depth_split = K in {2, 4, 8}).  The march of one ray is a dependent chain
+// of texture round trips; with few pixels per GPU (image split over 8 GPUs) the longest rays, not the texture unit,
+// bound the frame.  Here the K lanes {p, p + PIX, ...} of a warp share pixel p's ray (PIX = 32 / K pixels per warp
+// item) and walk it in chunks of K * SPLIT_G groups of UNROLL samples:
+//   1. lane k composites groups [(c*K + k)*G, (c*K + k + 1)*G) of chunk c from dst = 0 (stopping early only if its own
+//      alpha passes 0.99, which the sequential march would have done no later);
+//   2. the K partial results are folded front to back onto the running prefix with the over operator (associative);
+//      at the first segment where the running alpha passes 0.99 that segment — SPLIT_G groups — is marched again
+//      from the exact prefix, sequentially, so the ray ends on the same sample as the reference loop.
+// Same samples, same termination sample; the sums are re-associated (differences ~1e-7), a segment starts at
+// s = (group index * UNROLL) * step instead of the reference's accumulated s (identical for dyadic steps such as 0.5),
+// and at most one chunk beyond the terminating sample is fetched for nothing.
+template <int K> struct SplitGeom;
+template <> struct SplitGeom<2> { static constexpr int FW = 4, FH = 4; };
+template <> struct SplitGeom<4> { static constexpr int FW = 4, FH = 2; };
+template <> struct SplitGeom<8> { static constexpr int FW = 2, FH = 2; };
+constexpr int SPLIT_G = 2;
+
+// Marches groups [g0, g0 + ng) of the ray into r.dst.
+template <bool COUNT>
+__device__ __forceinline__ void march_groups(const Rc1Args& a, const uint4* s_tf, const uint32_t* s_mask, RayState& r, float D,
+                                             int g0, int ng, unsigned& nsamp) {
+  const float step = a.step;
+  float s = (float)(g0 * UNROLL) * step;
+  for (int g = 0; g < ng && s < D && !r.done; g++) {
+    float hk[UNROLL], tk[UNROLL], sk[UNROLL + 1];
+    sk[0] = s;
+#pragma unroll
+    for (int k = 0; k < UNROLL; k++) { sk[k + 1] = __fadd_rn(sk[k], step); hk[k] = step; tk[k] = fmaf(step, 0.5f, sk[k]); }
+    if (step <= __fsub_rn(D, sk[UNROLL - 1])) {
+      march_group<COUNT, true, true, true>(a, s_tf, s_mask, r, tk, hk, nsamp);
+      s = sk[UNROLL];
+    } else {
+      float ss = s;
+#pragma unroll
+      for (int k = 0; k < UNROLL; k++) {
+        hk[k] = fminf(step, __fsub_rn(D, ss));
+        tk[k] = fmaf(hk[k], 0.5f, ss);
+        ss = __fadd_rn(ss, fmaxf(hk[k], 0.0f));
+      }
+      march_group<COUNT, true, true, false>(a, s_tf, s_mask, r, tk, hk, nsamp);
+      s = ss;
+    }
+  }
+}
+
+template <bool COUNT, int K>
+__global__ void __launch_bounds__(CTA_THREADS, 4) rc1pass_split_kernel(const __grid_constant__ Rc1Args a) {
+  constexpr int PIX = 32 / K, FW = SplitGeom<K>::FW, FH = SplitGeom<K>::FH;
+  extern __shared__ uint4 s_dyn[];
+  uint4* s_tf = s_dyn;
+  uint32_t* s_mask = reinterpret_cast<uint32_t*>(s_dyn + a.tf_n);
+  for (int i = threadIdx.x; i < a.tf_n; i += blockDim.x) {
+    uint2 t0 = a.tf_lin[i], t1 = a.tf_lin[min(i + 1, a.tf_n - 1)];
+    s_tf[i] = make_uint4(t0.x, t0.y, t1.x, t1.y);
+  }
+  for (int i = threadIdx.x; i < a.vis_words; i += blockDim.x) s_mask[i] = a.vis_mask[i];
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int seg = lane / PIX, pi = lane % PIX;              // lanes 4q..4q+3: one 2x2 pixel quad of one segment
+  const int lx = ((pi >> 2) % (FW / 2)) * 2 + (pi & 1), ly = ((pi >> 2) / (FW / 2)) * 2 + ((pi >> 1) & 1);
+  const int per_tile_x = a.tile / FW, per_tile = per_tile_x * (a.tile / FH);
+  unsigned nsamp = 0;
+  for (;;) {
+    int raw = 0;
+    if (lane == 0) raw = (int)atomicAdd(a.queue, 1u);
+    raw = __shfl_sync(0xffffffffu, raw, 0);
+    if (raw >= a.n_items) break;
+    const int local_tile = raw / per_tile, sub = raw % per_tile;
+    const int tile_id = __ldg(a.tile_order + local_tile);
+    const int tx = tile_id % a.tiles_x, ty = tile_id / a.tiles_x;
+    const int px = tx * a.tile + (sub % per_tile_x) * FW + lx, py = ty * a.tile + (sub / per_tile_x) * FH + ly;
+    const bool valid = px < a.width && py < a.height;
+    const f3 eye = mk3(a.eye[0], a.eye[1], a.eye[2]);
+    const f3 cdir = camera_ray_dir(px, py, a.width, a.height, a.tan_fovy, a.aspect, a.lookat);
+    const f3 bmax = mk3(__fmul_rn(a.grid[0], 0.5f), __fmul_rn(a.grid[1], 0.5f), __fmul_rn(a.grid[2], 0.5f));
+    f3 dir; float tnear, tfar;
+    const bool hit = ray_aabb(eye, cdir, mk3(-bmax.x, -bmax.y, -bmax.z), bmax, dir, tnear, tfar) && valid;
+    RayState r;
+    r.dst = make_float4(0.f, 0.f, 0.f, 0.f);
+    r.done = false;
+    float D = 0.0f;
+    if (hit) {
+      D = fabsf(__fsub_rn(tfar, tnear));
+      const float tpx = __fadd_rn(__fadd_rn(eye.x, __fmul_rn(dir.x, tnear)), bmax.x);
+      const float tpy = __fadd_rn(__fadd_rn(eye.y, __fmul_rn(dir.y, tnear)), bmax.y);
+      const float tpz = __fadd_rn(__fadd_rn(eye.z, __fmul_rn(dir.z, tnear)), bmax.z);
+      r.ux0 = tpx * a.inv_grid[0]; r.uy0 = tpy * a.inv_grid[1]; r.uz0 = tpz * a.inv_grid[2];
+      r.dux = dir.x * a.inv_grid[0]; r.duy = dir.y * a.inv_grid[1]; r.duz = dir.z * a.inv_grid[2];
+    }
+    const float chunk_len = (float)(K * SPLIT_G * UNROLL) * a.step;
+    float4 P = make_float4(0.f, 0.f, 0.f, 0.f);               // running prefix, identical in the K lanes of a pixel
+    unsigned nseq = 0;                                        // samples of the sequential march so far
+    bool open = hit;                                          // this pixel's ray has neither ended nor terminated
+    for (int c = 0; __any_sync(0xffffffffu, open); c++) {
+      r.dst = make_float4(0.f, 0.f, 0.f, 0.f); r.done = false;
+      unsigned n1 = 0;
+      const int g0 = (c * K + seg) * SPLIT_G;
+      if (open) march_groups<true>(a, s_tf, s_mask, r, D, g0, SPLIT_G, n1);
+      float4 Pstar = P;
+      int kstar = -1;
+#pragma unroll
+      for (int j = 0; j < K; j++) {
+        const int src = pi + j * PIX;
+        const float sx = __shfl_sync(0xffffffffu, r.dst.x, src), sy = __shfl_sync(0xffffffffu, r.dst.y, src);
+        const float sz = __shfl_sync(0xffffffffu, r.dst.z, src), sw = __shfl_sync(0xffffffffu, r.dst.w, src);
+        const unsigned nj = __shfl_sync(0xffffffffu, n1, src);
+        if (kstar < 0 && open) {
+          const float t = 1.0f - P.w;
+          const float4 m = make_float4(fmaf(t, sx, P.x), fmaf(t, sy, P.y), fmaf(t, sz, P.z), fmaf(t, sw, P.w));
+          if (m.w > 0.99f) { kstar = j; Pstar = P; } else { P = m; nseq += nj; }
+        }
+      }
+      if (open && kstar == seg) {                             // this lane's segment holds the terminating sample
+        r.dst = Pstar; r.done = false;
+        unsigned n2 = 0;
+        march_groups<true>(a, s_tf, s_mask, r, D, g0, SPLIT_G, n2);
+        P = r.dst; nseq += n2;
+      }
+      {
+        const int src = kstar >= 0 ? pi + kstar * PIX : lane;   // kstar differs per pixel: unconditional shuffles
+        P.x = __shfl_sync(0xffffffffu, P.x, src); P.y = __shfl_sync(0xffffffffu, P.y, src);
+        P.z = __shfl_sync(0xffffffffu, P.z, src); P.w = __shfl_sync(0xffffffffu, P.w, src);
+        nseq = __shfl_sync(0xffffffffu, nseq, src);
+      }
+      if (kstar >= 0 || !((float)(c + 1) * chunk_len < D)) open = false;
+    }
+    if (seg == 0 && valid) {
+      const float4 o4 = hit ? P : make_float4(0.f, 0.f, 0.f, 0.f);
+      const uint2 texel = make_uint2(pack_half2(o4.x, o4.y), pack_half2(o4.z, o4.w));
+      const size_t o = (size_t)py * a.width + px;
+      a.frame[o] = texel;
+      for (int q = 0; q < a.n_peers; q++) a.peer[q][o] = texel;
+      if (COUNT && hit) nsamp += nseq;
+    }
+  }
+  if (COUNT) {
+    for (int o = 16; o > 0; o >>= 1) nsamp += __shfl_xor_sync(0xffffffffu, nsamp, o);
+    if (lane == 0 && nsamp) atomicAdd(a.samples, (unsigned long long)nsamp);
+  }
+  finish_launch(a.queue, a.sig);
+}
+
+// ---------------------------------------------------------------------------------------------
 // Host driver: RayCasting1Pass (rc1prenderer.cpp).
 class Rc1Pass : public RendererImpl {
  public:
   explicit Rc1Pass(vrb_ctx* c) : RendererImpl(c, VRB_RC1PASS) {
     prm_.step_size = 0.5f;               // m_u_step_size(0.5f)            rc1prenderer.cpp:21
     prm_.apply_gradient_shading = 0;     // m_apply_gradient_shading(false) rc1prenderer.cpp:22
-    prm_.skip_block = 0; prm_.count_samples = 0; prm_.tf_in_smem = 1; prm_.exact_filter = 1;
+    prm_.skip_block = 0; prm_.count_samples = 0; prm_.tf_in_smem = 1; prm_.exact_filter = 1; prm_.depth_split = 0;
   }
 
   // Init (rc1prenderer.cpp:50-70): requires a volume texture, takes the RGBt transfer-function texture,
@@ -348,6 +492,8 @@ class Rc1Pass : public RendererImpl {
     if (p.step_size <= 0.0f) p.step_size = prm_.step_size;
     VRB_REQUIRE(p.skip_block == 0 || p.skip_block == 4 || p.skip_block == 8 || p.skip_block == 16 || p.skip_block == 32,
                 VRB_ERR_INVALID, "RayCasting1Pass::set_params: skip_block must be 0, 4, 8, 16 or 32");
+    VRB_REQUIRE(p.depth_split == 0 || p.depth_split == 1 || p.depth_split == 2 || p.depth_split == 4 || p.depth_split == 8,
+                VRB_ERR_INVALID, "RayCasting1Pass::set_params: depth_split must be 0, 1, 2, 4 or 8");
     prm_ = p;
     return VRB_OK;
   }
@@ -405,6 +551,28 @@ class Rc1Pass : public RendererImpl {
     VRB_REQUIRE(smem <= 200 * 1024, VRB_ERR_UNSUPPORTED, "tf_in_smem: table of %d entries does not fit shared memory", a.tf_n);
     cudaStream_t s = ctx->stream;
     if (prm_.count_samples) VRB_CUDA(cudaMemsetAsync(d_samples, 0, sizeof(unsigned long long), s));
+    if (prm_.depth_split > 1 && !prm_.skip_block && prm_.tf_in_smem && prm_.exact_filter) {
+      // depth-split march (see rc1pass_split_kernel): smaller pixel footprint per warp item, K lanes per ray
+      const int K = prm_.depth_split;
+      const int fw = K == 8 ? 2 : 4, fh = K == 2 ? 4 : 2;
+      const int rc_o = ensure_tile_order();
+      if (rc_o != VRB_OK) return rc_o;
+      a.tile_order = d_tile_order; a.scramble = 0u;
+      a.n_items = my_tiles * (part_tile / fw) * (part_tile / fh);
+      const int ctas = (a.n_items + CTA_THREADS / 32 - 1) / (CTA_THREADS / 32);
+      int occ = 0;
+#define SPLIT(C, KK)                                                                                                          \
+  {                                                                                                                          \
+    if (smem > 48 * 1024) VRB_CUDA(cudaFuncSetAttribute(rc1pass_split_kernel<C, KK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rc1pass_split_kernel<C, KK>, CTA_THREADS, smem));           \
+    rc1pass_split_kernel<C, KK><<<std::min(std::max(occ, 1) * ctx->sm_count, ctas), CTA_THREADS, smem, s>>>(a);             \
+  }
+      if (prm_.count_samples) { if (K == 2) SPLIT(true, 2) else if (K == 4) SPLIT(true, 4) else SPLIT(true, 8) }
+      else { if (K == 2) SPLIT(false, 2) else if (K == 4) SPLIT(false, 4) else SPLIT(false, 8) }
+#undef SPLIT
+      VRB_CUDA(cudaGetLastError());
+      return VRB_OK;
+    }
     const int variant = (prm_.count_samples ? 8 : 0) | (prm_.tf_in_smem ? 4 : 0) | (prm_.exact_filter ? 2 : 0) | (prm_.skip_block ? 1 : 0);
     int per_sm = 0;
 #define CASE(V, C, T, E, S)                                                                                  \

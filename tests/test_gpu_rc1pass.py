@@ -293,6 +293,28 @@ def test_image_partition_union_equals_full_frame(ctx, bonsai_table):
         assert np.array_equal(acc, full) and cnt == tot
 
 
+@pytest.mark.parametrize("n,dtype,size,eye_s,up,step", CASES)
+@pytest.mark.parametrize("K", [2, 4, 8])
+def test_depth_split_march_parity(ctx, bonsai_table, n, dtype, size, eye_s, up, step, K):
+    """K lanes per ray, segments folded with the over operator, terminating segment re-marched from the exact prefix:
+    same tolerance as the one-lane march, same sample count (the termination sample is found sequentially)."""
+    w, h = size
+    vox = inputs.synth_volume(n, dtype)
+    ctx.upload_volume(vox)
+    ctx.upload_tf(bonsai_table)
+    cam = inputs.make_camera(tuple(n * e for e in eye_s), (0, 0, 0), up, 45.0, w, h)
+    kw = dict(count_samples=1, depth_split=K)
+    if step is not None:
+        kw["step_size"] = step
+    got, got8, _, samples, prm = _render_gpu(ctx, cam, w, h, **kw)
+    one, _, _, samples1, _ = _render_gpu(ctx, cam, w, h, **dict(kw, depth_split=0))
+    ref, total, _ = O.rc1pass_render(O.rc1pass_params(cam, w, h, vox.shape, prm.step_size), O.volume_r16f(vox), O.tf_texture(bonsai_table))
+    _check_images(got, got8, ref, f"K={K} n={n}")
+    d = float(np.abs(got - one).max()) * 255.0
+    assert d <= 0.5, d                                   # re-association only (fp16 store: half an 8-bit step at most)
+    assert abs(samples - total) <= 2e-3 * total and abs(samples - samples1) <= 2e-3 * total, (samples, samples1, total)
+
+
 @pytest.mark.parametrize("skip", [0, 8])
 def test_full_size_c2_parity(ctx, bonsai_table, skip):
     """BASELINE config 2 at full size: 512^3 uint16, 1024x1024, step 0.5, "Initial State" camera, against the
