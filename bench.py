@@ -200,7 +200,7 @@ def run_cuda(args):
     prm.tf_in_smem = args.tf_smem
     prm.exact_filter = args.exact
     # few pixels per GPU: the per-ray dependent chain bounds the frame, so more lanes share a ray (include/vrb200.h)
-    depth_split = args.depth_split if args.depth_split >= 0 else (0 if world == 1 else (2 if world == 2 else (4 if world == 4 else 8)))
+    depth_split = args.depth_split if args.depth_split >= 0 else (0 if world == 1 else (2 if world == 2 else 4))   # tools/partition_sweep.py: best K per split
     prm.depth_split = depth_split
     r.set_params(prm)
     if world > 1:
@@ -328,7 +328,7 @@ def run_cuda(args):
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(args.skip), "volume": f"{VOL_N}^3 u16 -> R16F texture", "image": f"{IMG_W}x{IMG_H}",
                        "step_voxels": STEP, "tf": "bonsai_01.tf1d", "camera": "Initial State (N,N,2N)",
-                       "partition": f"image tiles 32x32 round-robin over {world} rank(s)" + (", fused peer-memory gather into rank 0 + 4-byte NCCL end-of-frame barrier" if world > 1 else ""),
+                       "partition": f"image tiles 32x32 round-robin over {world} rank(s)" + (", fused peer-memory gather into every rank's frame + per-frame flag wait (no collective)" if world > 1 else ""),
                        "l2_policy": "inputs_larger_than_l2 (256 MiB R16F volume vs 126 MB L2)",
                        "samples_per_frame": fetched_total, "fps": 1e3 / ms_per_step, "init_ms_volume_upload": init_ms,
                        "tf_in_smem": args.tf_smem, "exact_filter": args.exact, "skip_block": args.skip, "depth_split": depth_split, "with_skipping": skip_info},

@@ -39,6 +39,7 @@ struct Rc1Args {
   int n_items; unsigned scramble;       // item order: item = (ticket * scramble) % n_items
   unsigned* queue;                      // [0] next ticket, [1] warps finished (self-resetting)
   const int* tile_order;                // this rank's tiles, centre of the image first (scramble == 0)
+  int split_g;                          // depth-split kernels: groups per lane per chunk
   // empty-space skipping: block edge in voxels, grid of blocks, Chebyshev run map (k_skipmap.cu)
   int skip_block; int nbx, nby, nbz; const uint8_t* skip_map;
 };
@@ -132,13 +133,15 @@ __device__ __forceinline__ void composite(const Rc1Args& a, const uint4* s_tf, R
 //      transfer-function cell that can be non-transparent the group is done (the common case in empty space),
 //   2. for the slots the transfer function may make visible, the two footprint fetches, all in flight together,
 //   3. in-order float32 filter + transfer function + blend; a slot after the terminating one is ignored.
-template <bool COUNT, bool TF_SMEM, bool EXACT, bool FULL>
-__device__ __forceinline__ void march_group(const Rc1Args& a, const uint4* s_tf, const uint32_t* s_mask, RayState& r,
-                                            const float (&tk)[UNROLL], const float (&hk)[UNROLL], unsigned& nsamp) {
-  float dk[UNROLL];
+__device__ __forceinline__ void fetch_group(const Rc1Args& a, const RayState& r, const float (&tk)[UNROLL], float (&dk)[UNROLL]) {
 #pragma unroll
   for (int k = 0; k < UNROLL; k++)
     dk[k] = tex3D<float>(a.vol, fmaf(r.dux, tk[k], r.ux0), fmaf(r.duy, tk[k], r.uy0), fmaf(r.duz, tk[k], r.uz0));
+}
+
+template <bool COUNT, bool TF_SMEM, bool EXACT, bool FULL>
+__device__ __forceinline__ void process_group(const Rc1Args& a, const uint4* s_tf, const uint32_t* s_mask, RayState& r,
+                                              const float (&tk)[UNROLL], const float (&hk)[UNROLL], const float (&dk)[UNROLL], unsigned& nsamp) {
   bool below = true;
 #pragma unroll
   for (int k = 0; k < UNROLL; k++) below = below && (dk[k] < a.vis_lo);      // NaN compares false -> slow path
@@ -169,6 +172,46 @@ __device__ __forceinline__ void march_group(const Rc1Args& a, const uint4* s_tf,
     const float density = EXACT ? quad_lerp(a, r, tk[k], q0[k], q1[k]) : dk[k];
     composite<TF_SMEM>(a, s_tf, r, density, tf_coord(a, density), hk[k]);
   }
+}
+
+template <bool COUNT, bool TF_SMEM, bool EXACT, bool FULL>
+__device__ __forceinline__ void march_group(const Rc1Args& a, const uint4* s_tf, const uint32_t* s_mask, RayState& r,
+                                            const float (&tk)[UNROLL], const float (&hk)[UNROLL], unsigned& nsamp) {
+  float dk[UNROLL];
+  fetch_group(a, r, tk, dk);
+  process_group<COUNT, TF_SMEM, EXACT, FULL>(a, s_tf, s_mask, r, tk, hk, dk, nsamp);
+}
+
+// Geometry of the group of UNROLL lattice samples that starts at s (s_k = s_{k-1} + h_{k-1}, exactly the reference's
+// accumulation).  While the last slot still has a whole step left (h = min(Step, D - s) = Step for it and therefore
+// for all before it) the group is FULL and needs no end-of-ray handling; else hk <= 0 marks a slot past the end.
+// Returns s of the next group.
+// FULL groups only: positions of the group starting at s and the start of the next group; false if the group holds
+// the end of the ray.
+__device__ __forceinline__ bool full_geom(float s, float D, float step, float (&tk)[UNROLL], float& s_end) {
+  float sk[UNROLL + 1];
+  sk[0] = s;
+#pragma unroll
+  for (int k = 0; k < UNROLL; k++) { sk[k + 1] = __fadd_rn(sk[k], step); tk[k] = fmaf(step, 0.5f, sk[k]); }
+  s_end = sk[UNROLL];
+  return step <= __fsub_rn(D, sk[UNROLL - 1]);
+}
+
+__device__ __forceinline__ float group_geom(float s, float D, float step, float (&tk)[UNROLL], float (&hk)[UNROLL], bool& full) {
+  float sk[UNROLL + 1];
+  sk[0] = s;
+#pragma unroll
+  for (int k = 0; k < UNROLL; k++) { sk[k + 1] = __fadd_rn(sk[k], step); hk[k] = step; tk[k] = fmaf(step, 0.5f, sk[k]); }
+  full = step <= __fsub_rn(D, sk[UNROLL - 1]);
+  if (full) return sk[UNROLL];
+  float ss = s;
+#pragma unroll
+  for (int k = 0; k < UNROLL; k++) {
+    hk[k] = fminf(step, __fsub_rn(D, ss));            // <= 0 marks a slot past the end of the ray
+    tk[k] = fmaf(hk[k], 0.5f, ss);
+    ss = __fadd_rn(ss, fmaxf(hk[k], 0.0f));
+  }
+  return ss;
 }
 
 template <bool COUNT, bool TF_SMEM, bool EXACT, bool SKIP>
@@ -231,29 +274,36 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(cons
     r.dux = dir.x * a.inv_grid[0]; r.duy = dir.y * a.inv_grid[1]; r.duz = dir.z * a.inv_grid[2];
     const float step = a.step;
     if (!SKIP) {
+      // Software-pipelined march over the FULL groups of the ray: the hardware-filtered fetches of the next group are
+      // issued before the current group is classified, re-filtered and composited, so a ray keeps 2 * UNROLL fetches
+      // in flight and the per-ray dependent chain is one texture round trip per group instead of up to two.  Only the
+      // group start s and the UNROLL fetched densities are carried; sample positions are recomputed from s.
       float s = 0.0f;
+      float hk[UNROLL], tk[UNROLL], dkc[UNROLL];
+#pragma unroll
+      for (int k = 0; k < UNROLL; k++) hk[k] = step;
+      float s_end = 0.0f;
+      bool fc = full_geom(s, D, step, tk, s_end);
+      if (fc) fetch_group(a, r, tk, dkc);
+      while (fc && !r.done) {
+        float tkn[UNROLL], dkn[UNROLL];
+        float s_end_n = s_end;
+        const bool fn = full_geom(s_end, D, step, tkn, s_end_n);
+        if (fn) fetch_group(a, r, tkn, dkn);
+        float s_dummy;
+        full_geom(s, D, step, tk, s_dummy);                  // positions of the current group again (cheaper than carrying them)
+        process_group<COUNT, TF_SMEM, EXACT, true>(a, s_tf, s_mask, r, tk, hk, dkc, nsamp);
+        s = s_end;
+#pragma unroll
+        for (int k = 0; k < UNROLL; k++) dkc[k] = dkn[k];
+        s_end = s_end_n; fc = fn;
+      }
+      // at most one group is left: the one that holds the end of the ray
       while (s < D && !r.done) {
-        // UNROLL lattice samples (s_k = s_{k-1} + h_{k-1}, exactly the reference's accumulation).  While the last
-        // slot still has a whole step left (h = min(Step, D - s) = Step for it and therefore for all before it)
-        // the group needs no end-of-ray handling.
-        float hk[UNROLL], tk[UNROLL], sk[UNROLL + 1];
-        sk[0] = s;
-#pragma unroll
-        for (int k = 0; k < UNROLL; k++) { sk[k + 1] = __fadd_rn(sk[k], step); hk[k] = step; tk[k] = fmaf(step, 0.5f, sk[k]); }
-        if (step <= __fsub_rn(D, sk[UNROLL - 1])) {
-          march_group<COUNT, TF_SMEM, EXACT, true>(a, s_tf, s_mask, r, tk, hk, nsamp);
-          s = sk[UNROLL];
-        } else {
-          float ss = s;
-#pragma unroll
-          for (int k = 0; k < UNROLL; k++) {
-            hk[k] = fminf(step, __fsub_rn(D, ss));            // <= 0 marks a slot past the end of the ray
-            tk[k] = fmaf(hk[k], 0.5f, ss);
-            ss = __fadd_rn(ss, fmaxf(hk[k], 0.0f));
-          }
-          march_group<COUNT, TF_SMEM, EXACT, false>(a, s_tf, s_mask, r, tk, hk, nsamp);
-          s = ss;
-        }
+        bool full;
+        const float s_n = group_geom(s, D, step, tk, hk, full);
+        march_group<COUNT, TF_SMEM, EXACT, false>(a, s_tf, s_mask, r, tk, hk, nsamp);
+        s = s_n;
       }
     } else {
       // Lattice-preserving empty-space skipping: sample k sits at s_k = k*step (identical to the accumulated
@@ -332,7 +382,6 @@ template <int K> struct SplitGeom;
 template <> struct SplitGeom<2> { static constexpr int FW = 4, FH = 4; };
 template <> struct SplitGeom<4> { static constexpr int FW = 4, FH = 2; };
 template <> struct SplitGeom<8> { static constexpr int FW = 2, FH = 2; };
-constexpr int SPLIT_G = 2;
 
 // Marches groups [g0, g0 + ng) of the ray into r.dst.
 template <bool COUNT>
@@ -406,6 +455,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 4) rc1pass_split_kernel(const __g
       r.ux0 = tpx * a.inv_grid[0]; r.uy0 = tpy * a.inv_grid[1]; r.uz0 = tpz * a.inv_grid[2];
       r.dux = dir.x * a.inv_grid[0]; r.duy = dir.y * a.inv_grid[1]; r.duz = dir.z * a.inv_grid[2];
     }
+    const int SPLIT_G = a.split_g;
     const float chunk_len = (float)(K * SPLIT_G * UNROLL) * a.step;
     float4 P = make_float4(0.f, 0.f, 0.f, 0.f);               // running prefix, identical in the K lanes of a pixel
     unsigned nseq = 0;                                        // samples of the sequential march so far
@@ -414,7 +464,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 4) rc1pass_split_kernel(const __g
       r.dst = make_float4(0.f, 0.f, 0.f, 0.f); r.done = false;
       unsigned n1 = 0;
       const int g0 = (c * K + seg) * SPLIT_G;
-      if (open) march_groups<true>(a, s_tf, s_mask, r, D, g0, SPLIT_G, n1);
+      if (open) march_groups<COUNT>(a, s_tf, s_mask, r, D, g0, SPLIT_G, n1);
       float4 Pstar = P;
       int kstar = -1;
 #pragma unroll
@@ -422,7 +472,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 4) rc1pass_split_kernel(const __g
         const int src = pi + j * PIX;
         const float sx = __shfl_sync(0xffffffffu, r.dst.x, src), sy = __shfl_sync(0xffffffffu, r.dst.y, src);
         const float sz = __shfl_sync(0xffffffffu, r.dst.z, src), sw = __shfl_sync(0xffffffffu, r.dst.w, src);
-        const unsigned nj = __shfl_sync(0xffffffffu, n1, src);
+        const unsigned nj = COUNT ? __shfl_sync(0xffffffffu, n1, src) : 0u;
         if (kstar < 0 && open) {
           const float t = 1.0f - P.w;
           const float4 m = make_float4(fmaf(t, sx, P.x), fmaf(t, sy, P.y), fmaf(t, sz, P.z), fmaf(t, sw, P.w));
@@ -432,14 +482,14 @@ __global__ void __launch_bounds__(CTA_THREADS, 4) rc1pass_split_kernel(const __g
       if (open && kstar == seg) {                             // this lane's segment holds the terminating sample
         r.dst = Pstar; r.done = false;
         unsigned n2 = 0;
-        march_groups<true>(a, s_tf, s_mask, r, D, g0, SPLIT_G, n2);
+        march_groups<COUNT>(a, s_tf, s_mask, r, D, g0, SPLIT_G, n2);
         P = r.dst; nseq += n2;
       }
       {
         const int src = kstar >= 0 ? pi + kstar * PIX : lane;   // kstar differs per pixel: unconditional shuffles
         P.x = __shfl_sync(0xffffffffu, P.x, src); P.y = __shfl_sync(0xffffffffu, P.y, src);
         P.z = __shfl_sync(0xffffffffu, P.z, src); P.w = __shfl_sync(0xffffffffu, P.w, src);
-        nseq = __shfl_sync(0xffffffffu, nseq, src);
+        if (COUNT) nseq = __shfl_sync(0xffffffffu, nseq, src);
       }
       if (kstar >= 0 || !((float)(c + 1) * chunk_len < D)) open = false;
     }
@@ -558,6 +608,8 @@ class Rc1Pass : public RendererImpl {
       const int rc_o = ensure_tile_order();
       if (rc_o != VRB_OK) return rc_o;
       a.tile_order = d_tile_order; a.scramble = 0u;
+      static const int env_g = []() { const char* e = getenv("VRB_SPLIT_G"); return e ? atoi(e) : 0; }();
+      a.split_g = env_g > 0 ? env_g : 2;
       a.n_items = my_tiles * (part_tile / fw) * (part_tile / fh);
       const int ctas = (a.n_items + CTA_THREADS / 32 - 1) / (CTA_THREADS / 32);
       int occ = 0;

@@ -76,7 +76,11 @@ def _gpu_worker(rank, world, port, mode, q):
             r.update(cam)
             for _ in range(3):                       # three frames: the flags count frames, the buffers alternate
                 r.redraw()
-                r.wait_peers()                       # stream-ordered: every sender's tiles of this frame have landed
+                # The two ranks share ONE GPU here, so the stream wait must never be the thing that blocks: finish
+                # both launches first (host barrier), then enqueue the wait, which finds its flags already raised.
+                ctx.synchronize()
+                dist.barrier()
+                r.wait_peers()                       # flag[q] >= frame number for every sender q, else this hangs
             out[kind] = r.read_frame(_capi.VRB_FRAME_RGBA32F)
             dist.barrier()                           # nobody unmaps before everyone has read
             r.set_peers([], rank, _capi.VRB_GATHER_NONE)
