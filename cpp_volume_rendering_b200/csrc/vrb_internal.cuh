@@ -135,10 +135,14 @@ struct RendererImpl {
 inline bool use_lpt_order() { static const bool v = []() { const char* e = getenv("VRB_ITEM_ORDER"); return !(e && e[0] == '0'); }(); return v; }
 
 // End-of-frame signal of the fused gather, passed to every partitioned render kernel.
-struct PeerSignal { unsigned* flag[RendererImpl::MAX_PEERS]; int n; unsigned seq; };
+// counter != 0 (VRB_GATHER_ALL): instead of its own flag word each sender bumps ONE arrival counter per consumer, so
+// the consumer needs a single stream wait (counter >= frame * senders).  Sound because in that mode every rank waits
+// for frame k before it launches frame k + 1: no arrival of frame k + 1 can precede the last arrival of frame k.
+struct PeerSignal { unsigned* flag[RendererImpl::MAX_PEERS]; int n; unsigned seq; int counter; };
 inline void fill_peer_signal(const RendererImpl& r, PeerSignal& ps) {
-  ps.n = r.n_peer_frames; ps.seq = r.frame_seq;
-  for (int q = 0; q < r.n_peer_frames; q++) ps.flag[q] = r.peer_flags[q];
+  ps.n = r.n_peer_frames; ps.seq = r.frame_seq; ps.counter = r.gather_mode == VRB_GATHER_ALL ? 1 : 0;
+  for (int q = 0; q < r.n_peer_frames; q++)
+    ps.flag[q] = ps.counter ? (unsigned*)((char*)r.peer_opened[q] + 2 * r.frame_bytes) + (RendererImpl::FRAME_FLAGS - 1) : r.peer_flags[q];
 }
 #ifdef __CUDACC__
 // Called by every warp when it has no more work (all lanes).  The last warp of the launch re-arms the work queue for
@@ -153,7 +157,8 @@ __device__ __forceinline__ void finish_launch(unsigned* queue, const PeerSignal&
       queue[0] = 0u; queue[1] = 0u;
       if (ps.n) {
         __threadfence_system();
-        for (int q = 0; q < ps.n; q++) *(volatile unsigned*)ps.flag[q] = ps.seq;
+        if (ps.counter) { for (int q = 0; q < ps.n; q++) atomicAdd_system(ps.flag[q], 1u); }
+        else { for (int q = 0; q < ps.n; q++) *(volatile unsigned*)ps.flag[q] = ps.seq; }
       }
     }
   }

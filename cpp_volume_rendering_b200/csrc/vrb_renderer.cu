@@ -285,6 +285,12 @@ int vrb_renderer_wait_peers(vrb_renderer* r) {
   if (p->gather_mode == VRB_GATHER_ROOT && p->rank != 0) return VRB_OK;      // only rank 0 collects
   stream_wait_value32_fn wait = get_stream_wait_value32();
   VRB_REQUIRE(wait, VRB_ERR_UNSUPPORTED, "vrb_renderer_wait_peers: cuStreamWaitValue32 is not available");
+  if (p->gather_mode == VRB_GATHER_ALL) {       // one arrival counter (see PeerSignal)
+    const unsigned want = p->frame_seq * (unsigned)(p->gather_ranks - 1);
+    const int rc = wait(p->ctx->stream, (unsigned long long)(uintptr_t)(p->flags() + RendererImpl::FRAME_FLAGS - 1), want, 0x0u /* GEQ */);
+    VRB_REQUIRE(rc == 0, VRB_ERR_CUDA, "cuStreamWaitValue32 failed: %d", rc);
+    return VRB_OK;
+  }
   for (int q = 0; q < p->gather_ranks; q++) {
     if (q == p->rank) continue;
     const int rc = wait(p->ctx->stream, (unsigned long long)(uintptr_t)(p->flags() + q), p->frame_seq, 0x0u /* CU_STREAM_WAIT_VALUE_GEQ */);
