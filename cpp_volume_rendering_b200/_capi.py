@@ -93,6 +93,7 @@ SIGNATURES = {
     "vrb_ctx_stream": (C.c_int, [_P, C.POINTER(_P)]),
     "vrb_volume_upload": (C.c_int, [_P, _P, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_float, C.c_float, C.c_float]),
     "vrb_volume_upload_device": (C.c_int, [_P, _P, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_float, C.c_float, C.c_float]),
+    "vrb_volume_gradient": (C.c_int, [_P, C.c_int, _P]),
     "vrb_volume_read_r16f": (C.c_int, [_P, _P]),
     "vrb_tf_upload": (C.c_int, [_P, _P, C.c_int, C.c_int]),
     "vrb_tf_read": (C.c_int, [_P, _P, _P]),
@@ -178,6 +179,13 @@ class Context:
         d, h, w = shape_zyx
         _check(lib().vrb_volume_upload_device(self._h, _P(dev_ptr), _DTYPES[np.dtype(dtype)], w, h, d, *map(float, scale)))
         self.vol_shape = (d, h, w)
+
+    def volume_gradient(self, model, want_data=False):
+        """Builds (model 1 Sobel-Feldman, 2 central differences) or frees (0) the gradient texture; optionally returns
+        its RGB16F texels as float32 [d, h, w, 3]."""
+        out = np.empty(self.vol_shape + (3,), np.float32) if want_data and model else None
+        _check(lib().vrb_volume_gradient(self._h, model, out.ctypes.data_as(_P) if out is not None else None))
+        return out
 
     def read_volume_r16f(self):
         out = np.empty(self.vol_shape, np.float32)

@@ -40,6 +40,8 @@ struct Rc1Args {
   unsigned* queue;                      // [0] next ticket, [1] warps finished (self-resetting)
   const int* tile_order;                // this rank's tiles, centre of the image first (scramble == 0)
   int split_g;                          // depth-split kernels: groups per lane per chunk
+  // gradient (Blinn-Phong) shading, ray_marching_1p.comp:48-81; grad == 0: off
+  cudaTextureObject_t grad; float ka, kd, ks, shininess, ispec[3], light_pos[3];
   // empty-space skipping: block edge in voxels, grid of blocks, Chebyshev run map (k_skipmap.cu)
   int skip_block; int nbx, nby, nbz; const uint8_t* skip_map;
 };
@@ -98,9 +100,29 @@ __device__ __forceinline__ float tf_coord(const Rc1Args& a, float density) {
   return fminf(fmaxf(fmaf(density, (float)a.tf_n, -0.5f), 0.0f), (float)(a.tf_n - 1));
 }
 
+// ShadeBlinnPhong (ray_marching_1p.comp:48-81).  Kept out of line: off by default, and the march loop's register
+// allocation must not pay for it.  The gradient texture is filtered by the texture unit (RGBA16F, 1.8 fixed-point
+// weights): it only feeds the normal of a shading term.
+__device__ __noinline__ float3 shade_blinn_phong(const Rc1Args& a, float ux, float uy, float uz, float3 clr) {
+  const float4 g4 = tex3D<float4>(a.grad, ux, uy, uz);
+  f3 g = mk3(g4.x, g4.y, g4.z);
+  if (g.x != 0.0f || g.y != 0.0f || g.z != 0.0f) {
+    const f3 grid = mk3(a.grid[0], a.grid[1], a.grid[2]);
+    const f3 Wpos = sub3(mul3(mk3(ux, uy, uz), grid), scale3(grid, 0.5f));
+    g = normalize_rn(g);
+    const f3 light_direction = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), Wpos));
+    const f3 eye_direction = normalize_rn(sub3(mk3(a.eye[0], a.eye[1], a.eye[2]), Wpos));
+    const f3 halfway = normalize_rn(add3(eye_direction, light_direction));
+    const float dot_diff = gmax(0.0f, dot_rn(g, light_direction)), dot_spec = gmax(0.0f, dot_rn(halfway, g));
+    const float amb = a.ka + a.kd * dot_diff, spec = a.ks * powf(dot_spec, a.shininess);
+    clr = make_float3(clr.x * amb + a.ispec[0] * spec, clr.y * amb + a.ispec[1] * spec, clr.z * amb + a.ispec[2] * spec);
+  }
+  return clr;
+}
+
 // ray_marching_1p.comp:136-168 for one lattice sample of density `density` (u = tf_coord(density)).
-template <bool TF_SMEM>
-__device__ __forceinline__ void composite(const Rc1Args& a, const uint4* s_tf, RayState& r, float density, float u, float h) {
+template <bool TF_SMEM, bool GRAD>
+__device__ __forceinline__ void composite(const Rc1Args& a, const uint4* s_tf, RayState& r, float density, float u, float h, float t) {
   float4 src;
   if (TF_SMEM) {
     // GL_LINEAR, CLAMP_TO_EDGE on n texels with float32 weights
@@ -117,6 +139,10 @@ __device__ __forceinline__ void composite(const Rc1Args& a, const uint4* s_tf, R
     src = tex1D<float4>(a.tf, density);
   }
   if (src.w > 0.0f) {
+    if (GRAD) {                                               // ApplyGradientPhongShading == 1 (:145-146)
+      const float3 c = shade_blinn_phong(a, fmaf(r.dux, t, r.ux0), fmaf(r.duy, t, r.uy0), fmaf(r.duz, t, r.uz0), make_float3(src.x, src.y, src.z));
+      src.x = c.x; src.y = c.y; src.z = c.z;
+    }
     const float alpha = 1.0f - ex2_approx(src.w * h * -1.4426950408889634f);   // 1 - exp(-tau*h) via MUFU.EX2
     const float wgt = (1.0f - r.dst.w) * alpha;
     r.dst.x = fmaf(wgt, src.x, r.dst.x);
@@ -139,7 +165,7 @@ __device__ __forceinline__ void fetch_group(const Rc1Args& a, const RayState& r,
     dk[k] = tex3D<float>(a.vol, fmaf(r.dux, tk[k], r.ux0), fmaf(r.duy, tk[k], r.uy0), fmaf(r.duz, tk[k], r.uz0));
 }
 
-template <bool COUNT, bool TF_SMEM, bool EXACT, bool FULL>
+template <bool COUNT, bool TF_SMEM, bool EXACT, bool FULL, bool GRAD = false>
 __device__ __forceinline__ void process_group(const Rc1Args& a, const uint4* s_tf, const uint32_t* s_mask, RayState& r,
                                               const float (&tk)[UNROLL], const float (&hk)[UNROLL], const float (&dk)[UNROLL], unsigned& nsamp) {
   bool below = true;
@@ -170,16 +196,16 @@ __device__ __forceinline__ void process_group(const Rc1Args& a, const uint4* s_t
     if (COUNT) nsamp++;
     if (!vis[k]) continue;
     const float density = EXACT ? quad_lerp(a, r, tk[k], q0[k], q1[k]) : dk[k];
-    composite<TF_SMEM>(a, s_tf, r, density, tf_coord(a, density), hk[k]);
+    composite<TF_SMEM, GRAD>(a, s_tf, r, density, tf_coord(a, density), hk[k], tk[k]);
   }
 }
 
-template <bool COUNT, bool TF_SMEM, bool EXACT, bool FULL>
+template <bool COUNT, bool TF_SMEM, bool EXACT, bool FULL, bool GRAD = false>
 __device__ __forceinline__ void march_group(const Rc1Args& a, const uint4* s_tf, const uint32_t* s_mask, RayState& r,
                                             const float (&tk)[UNROLL], const float (&hk)[UNROLL], unsigned& nsamp) {
   float dk[UNROLL];
   fetch_group(a, r, tk, dk);
-  process_group<COUNT, TF_SMEM, EXACT, FULL>(a, s_tf, s_mask, r, tk, hk, dk, nsamp);
+  process_group<COUNT, TF_SMEM, EXACT, FULL, GRAD>(a, s_tf, s_mask, r, tk, hk, dk, nsamp);
 }
 
 // Geometry of the group of UNROLL lattice samples that starts at s (s_k = s_{k-1} + h_{k-1}, exactly the reference's
@@ -214,7 +240,7 @@ __device__ __forceinline__ float group_geom(float s, float D, float step, float 
   return ss;
 }
 
-template <bool COUNT, bool TF_SMEM, bool EXACT, bool SKIP>
+template <bool COUNT, bool TF_SMEM, bool EXACT, bool SKIP, bool GRAD = false>
 __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(const __grid_constant__ Rc1Args a) {
   extern __shared__ uint4 s_dyn[];
   uint4* s_tf = s_dyn;                                   // TF_SMEM: entry i = {texel i, texel min(i+1,n-1)}
@@ -292,7 +318,7 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(cons
         if (fn) fetch_group(a, r, tkn, dkn);
         float s_dummy;
         full_geom(s, D, step, tk, s_dummy);                  // positions of the current group again (cheaper than carrying them)
-        process_group<COUNT, TF_SMEM, EXACT, true>(a, s_tf, s_mask, r, tk, hk, dkc, nsamp);
+        process_group<COUNT, TF_SMEM, EXACT, true, GRAD>(a, s_tf, s_mask, r, tk, hk, dkc, nsamp);
         s = s_end;
 #pragma unroll
         for (int k = 0; k < UNROLL; k++) dkc[k] = dkn[k];
@@ -302,7 +328,7 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(cons
       while (s < D && !r.done) {
         bool full;
         const float s_n = group_geom(s, D, step, tk, hk, full);
-        march_group<COUNT, TF_SMEM, EXACT, false>(a, s_tf, s_mask, r, tk, hk, nsamp);
+        march_group<COUNT, TF_SMEM, EXACT, false, GRAD>(a, s_tf, s_mask, r, tk, hk, nsamp);
         s = s_n;
       }
     } else {
@@ -345,7 +371,7 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(cons
           hk[q] = fminf(step, D - sq);
           tk[q] = fmaf(hk[q], 0.5f, sq);
         }
-        march_group<COUNT, TF_SMEM, EXACT, false>(a, s_tf, s_mask, r, tk, hk, nsamp);
+        march_group<COUNT, TF_SMEM, EXACT, false, GRAD>(a, s_tf, s_mask, r, tk, hk, nsamp);
         k += UNROLL;
       }
     }
@@ -569,6 +595,12 @@ class Rc1Pass : public RendererImpl {
     for (int i = 0; i < 3; i++) { a.inv_grid[i] = 1.0f / a.grid[i]; a.eye[i] = cam.eye[i]; }
     for (int i = 0; i < 9; i++) a.lookat[i] = cam.lookat[i];
     a.tan_fovy = cam.tan_fovy; a.aspect = cam.aspect; a.step = prm_.step_size;
+    a.grad = 0;
+    if (prm_.apply_gradient_shading) {      // m_apply_gradient_shading && GetCurrentGradientTexture() (rc1prenderer.cpp:112-115)
+      VRB_REQUIRE(v.tex_grad && v.grad_gen == v.generation, VRB_ERR_INVALID, "RayCasting1Pass: gradient shading needs vrb_volume_gradient() for the current volume");
+      a.grad = v.tex_grad; a.ka = light.ka; a.kd = light.kd; a.ks = light.ks; a.shininess = light.shininess;
+      for (int i = 0; i < 3; i++) { a.ispec[i] = light.ispecular[i]; a.light_pos[i] = light.position[i]; }
+    }
     a.frame = (uint2*)frame; a.samples = d_samples;
     a.n_peers = n_peer_frames;
     for (int q = 0; q < n_peer_frames; q++) a.peer[q] = (uint2*)peer_frames[q];
@@ -601,6 +633,24 @@ class Rc1Pass : public RendererImpl {
     VRB_REQUIRE(smem <= 200 * 1024, VRB_ERR_UNSUPPORTED, "tf_in_smem: table of %d entries does not fit shared memory", a.tf_n);
     cudaStream_t s = ctx->stream;
     if (prm_.count_samples) VRB_CUDA(cudaMemsetAsync(d_samples, 0, sizeof(unsigned long long), s));
+    if (a.grad) {
+      VRB_REQUIRE(!prm_.skip_block && prm_.tf_in_smem && prm_.exact_filter, VRB_ERR_UNSUPPORTED,
+                  "RayCasting1Pass: gradient shading runs with skip_block = 0, tf_in_smem = 1, exact_filter = 1");
+      int occ = 0;
+      if (smem > 48 * 1024) {
+        VRB_CUDA(cudaFuncSetAttribute(rc1pass_kernel<false, true, true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VRB_CUDA(cudaFuncSetAttribute(rc1pass_kernel<true, true, true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      }
+      if (prm_.count_samples) {
+        VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rc1pass_kernel<true, true, true, false, true>, CTA_THREADS, smem));
+        rc1pass_kernel<true, true, true, false, true><<<std::min(std::max(occ, 1) * ctx->sm_count, max_ctas), CTA_THREADS, smem, s>>>(a);
+      } else {
+        VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rc1pass_kernel<false, true, true, false, true>, CTA_THREADS, smem));
+        rc1pass_kernel<false, true, true, false, true><<<std::min(std::max(occ, 1) * ctx->sm_count, max_ctas), CTA_THREADS, smem, s>>>(a);
+      }
+      VRB_CUDA(cudaGetLastError());
+      return VRB_OK;
+    }
     if (prm_.depth_split > 1 && !prm_.skip_block && prm_.tf_in_smem && prm_.exact_filter) {
       // depth-split march (see rc1pass_split_kernel): smaller pixel footprint per warp item, K lanes per ray
       const int K = prm_.depth_split;

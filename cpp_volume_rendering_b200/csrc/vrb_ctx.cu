@@ -84,6 +84,7 @@ int ensure_quad(vrb_ctx* ctx) {
 }
 
 static void release_volume(Volume& v) {
+  release_gradient(v);
   if (v.tex_quad) cudaDestroyTextureObject(v.tex_quad);
   if (v.quad_array) cudaFreeArray(v.quad_array);
   if (v.tex) cudaDestroyTextureObject(v.tex);

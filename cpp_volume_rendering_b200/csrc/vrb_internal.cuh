@@ -46,6 +46,11 @@ struct Volume {
   // sampled.  One exact trilinear sample = 2 fetches instead of 8.  Built on first use (8 bytes per voxel).
   cudaArray_t quad_array = nullptr;
   cudaTextureObject_t tex_quad = 0;
+  // RGB16F gradient texture for the Blinn-Phong path (k_gradient.cu), built on request (vrb_volume_gradient)
+  cudaArray_t grad_array = nullptr;
+  cudaTextureObject_t tex_grad = 0;
+  int grad_model = 0;
+  uint64_t grad_gen = 0;
   uint64_t generation = 0;
   size_t voxel_bytes() const { return dtype == VRB_U8 ? 1 : (dtype == VRB_U16 ? 2 : 4); }
 };
@@ -178,6 +183,10 @@ int sbtm_read_occlusion(RendererImpl* impl, float* host, int* n_slices);
 int vct_read_level(RendererImpl* impl, int level, float* host_rg, int dims[3]);
 int vct_read_lut(RendererImpl* impl, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms);
 int iso_read_blocks(RendererImpl* impl, float* host_min, float* host_max);
+
+// k_gradient.cu
+void release_gradient(Volume& v);
+int build_gradient(vrb_ctx* ctx, int model, float* host_rgb);
 
 // vrb_ctx.cu: builds Volume::tex_quad on the context stream if it does not exist yet.
 int ensure_quad(vrb_ctx* ctx);

@@ -205,6 +205,13 @@ int vrb_ctx_stream(vrb_ctx* ctx, void** out_stream);
  * reference (block min/max, SAT, supervoxels). */
 int vrb_volume_upload(vrb_ctx* ctx, const void* voxels, int dtype, int64_t w, int64_t h, int64_t d,
                       float sx, float sy, float sz);
+/* DataManager::GenerateStructuredGradientTexture (datamanager.cpp:332-352), moved to the GPU: builds the RGB16F gradient
+ * texture of the current volume that gradient (Blinn-Phong) shading samples.  model 0 = none (frees it; the reference's
+ * default, datamanager.cpp:27), 1 = SOBEL_FELDMAN_FILTER (utils.cpp:287-350), 2 = FINITE_DIFERENCES (utils.cpp:146-285
+ * with its default arguments).  The compute-shader Sobel variant is not provided.  host_rgb (optional, test hook):
+ * receives the w*h*d*3 texel values.  Must be called again after a new volume upload. */
+int vrb_volume_gradient(vrb_ctx* ctx, int model, float* host_rgb);
+
 /* Same, voxels already resident in DEVICE memory (used when a step's inputs must be in HBM). */
 int vrb_volume_upload_device(vrb_ctx* ctx, const void* dev_voxels, int dtype, int64_t w, int64_t h, int64_t d,
                              float sx, float sy, float sz);

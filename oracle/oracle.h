@@ -51,6 +51,10 @@ typedef struct {
   int   threads;                /* OpenMP threads, 0 = all */
 } orc_rc1p_params;
 
+/* DataManager::GenerateStructuredGradientTexture: model 1 = Sobel-Feldman (utils.cpp:287-350), 2 = central differences,
+ * normalised (utils.cpp:146-285 with its default arguments).  out_rgb: w*h*d*3 floats holding RGB16F values. */
+void orc_gradient(const void* voxels, int dtype, int w, int h, int d, int model, float* out_rgb);
+
 /* main() of cppvolrend/structured/rc1pass/ray_marching_1p.comp:85-178 for every pixel.
  * vol_r16f: W*H*D floats (orc_volume_r16f); tf_rgbt: tf_n*4 floats (orc_tf_texture kind 0);
  * grad_rgb: optional W*H*D*3 gradient texture or NULL.

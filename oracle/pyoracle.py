@@ -118,6 +118,7 @@ def lib():
         L.orc_dos_extcoef_volume.argtypes = [_P, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, _P, C.c_float, _P]
         L.orc_dos_render.argtypes = [C.POINTER(DosParams), _P, _P, C.c_int, _P, C.c_int, _P, _P, _P, C.POINTER(C.c_uint64)]
         L.orc_dos_render.restype = C.c_uint64
+        L.orc_gradient.argtypes = [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]
         L.orc_block_minmax.argtypes = [_P, C.c_int] + [C.c_int] * 6 + [_P, _P]
         L.orc_iso_render.argtypes = [C.POINTER(IsoParams), _P, _P, _P, _P, _P]
         L.orc_iso_render.restype = C.c_uint64
@@ -433,3 +434,12 @@ def dos_render(p, vol_r16f, tf_rgbt, levels, occ, sdw):
     shaded = C.c_uint64()
     total = lib().orc_dos_render(C.byref(p), _ptr(vol), _ptr(tf), tf.shape[0], ptrs, len(lv), _ptr(ot), _ptr(st), _ptr(out), C.byref(shaded))
     return out, int(total), int(shaded.value)
+
+
+def gradient(voxels, model=1):
+    """RGB16F gradient texture [d, h, w, 3]: model 1 Sobel-Feldman, 2 normalised central differences."""
+    v = np.ascontiguousarray(voxels)
+    d, h, w = v.shape
+    out = np.zeros((d, h, w, 3), np.float32)
+    lib().orc_gradient(_ptr(v), _DT[v.dtype], w, h, d, model, _ptr(out))
+    return out

@@ -32,11 +32,20 @@ def test_abi_version_and_error_string():
     assert isinstance(lib.vrb_last_error(), bytes)
 
 
-def test_struct_sizes_match_header():
-    # vrb_camera: 3+9+1+1 floats; vrb_light: 4+3+3 floats; vrb_rc1pass_params: float + 5 ints
-    assert ctypes.sizeof(_capi.Camera) == 14 * 4
-    assert ctypes.sizeof(_capi.Light) == 10 * 4
-    assert ctypes.sizeof(_capi.Rc1PassParams) == 6 * 4
+def test_struct_sizes_match_header(tmp_path):
+    """sizeof of every POD struct of include/vrb200.h, as gcc lays it out, equals the ctypes mirror."""
+    import subprocess
+    pairs = [("vrb_camera", _capi.Camera), ("vrb_light", _capi.Light), ("vrb_rc1pass_params", _capi.Rc1PassParams),
+             ("vrb_iso_params", _capi.IsoParams), ("vrb_ebs_params", _capi.EbsParams), ("vrb_vct_params", _capi.VctParams),
+             ("vrb_sbtm_params", _capi.SbtmParams), ("vrb_dos_params", _capi.DosParams)]
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "vrb200.h"\nint main(void) {\n' +
+                   "".join(f'  printf("%zu\\n", sizeof({c}));\n' for c, _ in pairs) + "  return 0;\n}\n")
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    sizes = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
+    for (cname, cls), sz in zip(pairs, sizes):
+        assert ctypes.sizeof(cls) == sz, cname
 
 
 def test_null_arguments_are_errors_not_crashes():
