@@ -104,7 +104,9 @@ bool CudaRayCasting1Pass::Update(vis::Camera* camera) {
   const VrbApi* a = VrbApi::Get();
   vrb_rc1pass_params p;
   if (a->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
-  p.step_size = m_u_step_size; p.apply_gradient_shading = m_apply_gradient_shading ? 1 : 0; p.skip_block = m_skip_block;
+  p.step_size = m_u_step_size; p.skip_block = m_skip_block;
+  // ApplyGradientPhongShading = m_apply_gradient_shading && GetCurrentGradientTexture() (rc1prenderer.cpp:112-115)
+  p.apply_gradient_shading = (m_apply_gradient_shading && m_ext_data_manager->HasGradientTexture()) ? 1 : 0;
   if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
   vrb_camera c; vrb_light l;
   camera->FillUniforms(&c);

@@ -12,6 +12,7 @@ struct VrbApi {
   int (*ctx_synchronize)(vrb_ctx*);
   int (*volume_upload)(vrb_ctx*, const void*, int, int64_t, int64_t, int64_t, float, float, float);
   int (*tf_upload)(vrb_ctx*, const double*, int, int);
+  int (*volume_gradient)(vrb_ctx*, int, float*);
   int (*renderer_create)(vrb_ctx*, int, vrb_renderer**);
   int (*renderer_destroy)(vrb_renderer*);
   int (*renderer_init)(vrb_renderer*, int, int);

@@ -34,6 +34,7 @@ const VrbApi* VrbApi::Get(std::string* why) {
 #define SYM(field, name) do { *(void**)(&api.field) = dlsym(h, name); if (!api.field) { err = std::string("missing symbol ") + name; all = false; } } while (0)
     SYM(last_error, "vrb_last_error"); SYM(ctx_create, "vrb_ctx_create"); SYM(ctx_destroy, "vrb_ctx_destroy");
     SYM(ctx_synchronize, "vrb_ctx_synchronize"); SYM(volume_upload, "vrb_volume_upload"); SYM(tf_upload, "vrb_tf_upload");
+    SYM(volume_gradient, "vrb_volume_gradient");
     SYM(renderer_create, "vrb_renderer_create"); SYM(renderer_destroy, "vrb_renderer_destroy");
     SYM(renderer_init, "vrb_renderer_init"); SYM(renderer_reshape, "vrb_renderer_reshape");
     SYM(renderer_set_params, "vrb_renderer_set_params"); SYM(renderer_get_params, "vrb_renderer_get_params");
@@ -261,7 +262,23 @@ bool DataManager::SetCurrentVolume(StructuredGridVolume* vol) {
   if (a->volume_upload(m_ctx, vol->GetArrayData(), dt, vol->GetWidth(), vol->GetHeight(), vol->GetDepth(), (float)vol->GetScaleX(),
                        (float)vol->GetScaleY(), (float)vol->GetScaleZ()) != VRB_OK) { m_err = a->last_error(); return false; }
   m_vol_uploaded = true;
+  return GenerateStructuredGradientTexture();                            // datamanager.cpp:322-330: after the volume texture
+}
+// datamanager.cpp:332-352; NONE (the default, :27) frees the texture and reports "no gradient" like the reference
+bool DataManager::GenerateStructuredGradientTexture() {
+  m_has_gradient = false;
+  if (!m_vol_uploaded) return true;
+  const VrbApi* a = VrbApi::Get(&m_err);
+  if (!a) return false;
+  const int model = curr_gradient_comp_model == STRUCTURED_GRADIENT_TYPE::SOBEL_FELDMAN_FILTER ? 1
+                  : (curr_gradient_comp_model == STRUCTURED_GRADIENT_TYPE::FINITE_DIFERENCES ? 2 : 0);
+  if (a->volume_gradient(m_ctx, model, nullptr) != VRB_OK) { m_err = a->last_error(); return false; }
+  m_has_gradient = model != 0;
   return true;
+}
+bool DataManager::SetCurrentGradientGenerator(STRUCTURED_GRADIENT_TYPE t) {
+  curr_gradient_comp_model = t;
+  return GenerateStructuredGradientTexture();
 }
 bool DataManager::SetCurrentTransferFunction(TransferFunction1D* tf) {
   delete m_tf; m_tf = tf;

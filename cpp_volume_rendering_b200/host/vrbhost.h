@@ -154,6 +154,9 @@ class RenderingParameters {
 // ---- libs/volvis_utils/datamanager.h:82-99: what renderers read through m_ext_data_manager -----------------
 // Owns the vrb context: SetCurrentVolume / SetCurrentTransferFunction replace GenerateRTexture and
 // GenerateTexture_1D_* (the device textures live in libvrb200.so).
+// libs/volvis_utils/datamanager.h: how the gradient texture of the Blinn-Phong path is computed
+enum class STRUCTURED_GRADIENT_TYPE { NONE_GRADIENT = 0, SOBEL_FELDMAN_FILTER = 1, FINITE_DIFERENCES = 2 };
+
 class DataManager {
  public:
   DataManager();
@@ -164,6 +167,10 @@ class DataManager {
   StructuredGridVolume* GetCurrentStructuredVolume() { return m_vol; }
   TransferFunction1D* GetCurrentTransferFunction() { return m_tf; }
   bool HasVolumeTexture() const { return m_vol_uploaded; }               // GetCurrentVolumeTexture() != nullptr
+  bool HasGradientTexture() const { return m_has_gradient; }             // GetCurrentGradientTexture() != nullptr
+  bool SetCurrentGradientGenerator(STRUCTURED_GRADIENT_TYPE t);          // + GenerateStructuredGradientTexture (datamanager.cpp:332-352)
+  bool GenerateStructuredGradientTexture();
+  STRUCTURED_GRADIENT_TYPE curr_gradient_comp_model = STRUCTURED_GRADIENT_TYPE::NONE_GRADIENT;   // datamanager.cpp:27
   GRID_VOLUME_DATA_TYPE GetInputVolumeDataType() const { return GRID_VOLUME_DATA_TYPE::STRUCTURED; }
   vrb_ctx* Context() { return m_ctx; }
   const std::string& LastError() const { return m_err; }
@@ -171,7 +178,7 @@ class DataManager {
   vrb_ctx* m_ctx = nullptr;
   StructuredGridVolume* m_vol = nullptr;
   TransferFunction1D* m_tf = nullptr;
-  bool m_vol_uploaded = false;
+  bool m_vol_uploaded = false, m_has_gradient = false;
   std::string m_err;
 };
 
