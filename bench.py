@@ -101,6 +101,26 @@ def cpu_frame(vox, table, cam, skip_rows=None, repeats=1):
     return total / best, O.max_threads(), total, best
 
 
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed ncu --set full
+    capture of this same command (profiles/, written by tools/ncusum.py); None when no capture is committed."""
+    import csv
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_rc1pass_noskip.csv")))
+    if not files:
+        return None, None
+    vals = {}
+    for row in csv.reader(open(files[-1])):
+        if row and row[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(row[1], None)
+            if scale is None:
+                return None, None
+            vals[row[0]] = float(row[2]) * scale
+    if len(vals) != 2:
+        return None, None
+    return sum(vals.values()), os.path.relpath(files[-1], ROOT)
+
+
 def sat_extra(ctx, table, hbm_peak):
     """Config 4's precompute: extinction SAT of a 512^3 float32 volume, GPU (both builders) beside the reference's
     own CPU BuildSAT (oracle/_ref, compiled from the reference's summedareatable.h; single thread — it is serial)."""
@@ -322,6 +342,7 @@ def run_cuda(args):
         local_fetch = fetched_local
         ach_fetch = local_fetch / (k_ms * 1e-3)
         compulsory = 2.0 * VOL_N ** 3 + 8.0 * IMG_W * IMG_H
+        traffic, traffic_src = ncu_traffic()
         line = {
             "metric": METRIC, "value": fetched_total / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
@@ -338,7 +359,7 @@ def run_cuda(args):
             "clocks": clk,
             "roofline": {"bound": "l1tex", "kernel": "rc1pass_kernel", "achieved": ach_fetch * BYTES_PER_SAMPLE_L1TEX / 1e9,
                          "peak": tex_peak * BYTES_PER_SAMPLE_L1TEX / 1e9, "unit": "GB/s", "frac": ach_fetch / tex_peak,
-                         "traffic": None, "kernel_ms": k_ms, "achieved_fetches_per_s": ach_fetch, "peak_fetches_per_s": tex_peak,
+                         "traffic": traffic if world == 1 and not args.skip else None, "traffic_source": traffic_src, "kernel_ms": k_ms, "achieved_fetches_per_s": ach_fetch, "peak_fetches_per_s": tex_peak,
                          "peak_source": "vrb_bench_tex_peak: cache-resident trilinear R16F tex3D microbenchmark, same job (of measured)"},
             "roofline_hbm": {"bound": "hbm", "achieved": compulsory / (k_ms * 1e-3) / 1e9 / world, "peak": hbm_peak, "unit": "GB/s",
                              "frac": compulsory / (k_ms * 1e-3) / 1e9 / world / hbm_peak,
