@@ -52,7 +52,8 @@ class EbsParams(C.Structure):
                 ("dir_shadow_cone_angle", C.c_float), ("dir_shadow_sample_interval", C.c_float),
                 ("dir_shadow_initial_step", C.c_float), ("dir_shadow_user_interface_weight", C.c_float),
                 ("dir_cone_max_distance", C.c_float), ("type_of_shadow", C.c_int), ("light_cam_forward", C.c_float * 3),
-                ("fast_sat", C.c_int), ("count_samples", C.c_int)]
+                ("fast_sat", C.c_int), ("count_samples", C.c_int),
+                ("use_light_cache", C.c_int), ("light_cache_resolution", C.c_int * 3)]
 
 
 class VctParams(C.Structure):
@@ -60,7 +61,8 @@ class VctParams(C.Structure):
                 ("apply_directional_shadows", C.c_int), ("cone_step_size", C.c_float),
                 ("cone_step_increase_rate", C.c_float), ("cone_initial_step", C.c_float), ("cone_apex_angle", C.c_float),
                 ("apply_correction_factor", C.c_int), ("opacity_correction_factor", C.c_float),
-                ("cone_number_of_samples", C.c_int), ("count_samples", C.c_int)]
+                ("cone_number_of_samples", C.c_int), ("count_samples", C.c_int),
+                ("use_light_cache", C.c_int), ("light_cache_resolution", C.c_int * 3)]
 
 
 class SbtmParams(C.Structure):
@@ -79,7 +81,7 @@ class DosParams(C.Structure):
                 ("type_of_shadow", C.c_int), ("spot_light_max_angle", C.c_float),
                 ("light_cam_forward", C.c_float * 3), ("light_cam_up", C.c_float * 3), ("light_cam_right", C.c_float * 3),
                 ("base_level_sigma0", C.c_float), ("use_custom_resolution", C.c_int), ("custom_resolution", C.c_int * 3),
-                ("count_samples", C.c_int)]
+                ("count_samples", C.c_int), ("use_light_cache", C.c_int), ("light_cache_resolution", C.c_int * 3)]
 
 
 # name -> (restype, argtypes); the list doubles as the "every declared symbol is exported" check.
@@ -111,6 +113,7 @@ SIGNATURES = {
     "vrb_ebs_read_sat": (C.c_int, [_P, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_float)]),
     "vrb_dos_read_extcoef": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
     "vrb_dos_read_sections": (C.c_int, [_P, C.c_int, _P, C.c_int, C.POINTER(C.c_int), _P, _P, C.POINTER(C.c_float)]),
+    "vrb_light_cache_read": (C.c_int, [_P, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_float)]),
     "vrb_sbtm_read_occlusion": (C.c_int, [_P, _P, C.POINTER(C.c_int)]),
     "vrb_vct_read_level": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int * 3)]),
     "vrb_vct_read_lut": (C.c_int, [_P, _P, C.POINTER(C.c_int * 2), C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
@@ -317,6 +320,16 @@ class Renderer:
             _check(lib().vrb_dos_read_extcoef(self._h, l, out.ctypes.data_as(_P), C.byref(dims), None, None))
             levels.append(out)
         return levels, ms.value
+
+    def read_light_cache(self, want_data=True):
+        """(cache float32 [d, h, w, 2] or None, device ms of the cache pass) of the last Redraw with use_light_cache."""
+        dims = (C.c_int * 3)(); ms = C.c_float()
+        _check(lib().vrb_light_cache_read(self._h, None, C.byref(dims), C.byref(ms)))
+        if not want_data:
+            return None, ms.value
+        out = np.zeros((dims[2], dims[1], dims[0], 2), np.float32)
+        _check(lib().vrb_light_cache_read(self._h, out.ctypes.data_as(_P), None, None))
+        return out, ms.value
 
     def read_dos_sections(self, which, cap=1024):
         """(table float32 [n, 4], axes [10, 3], counts [3], adj7) of the occlusion (0) or shadow (1) cone."""

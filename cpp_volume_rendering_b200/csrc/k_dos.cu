@@ -10,7 +10,7 @@
 // float32-filtered, and opacity -> extinction goes through a 64 Ki-entry table over all binary16 values.
 #include "vrb_internal.cuh"
 #include "vrb_ray.cuh"
-#include "vrb_march.cuh"
+#include "vrb_lightcache.cuh"
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -312,6 +312,7 @@ struct DosCone {
 };
 
 struct DosShader {
+  static constexpr bool OBJECT_SPACE = false;
   struct Args {
     cudaTextureObject_t mip[DOS_MAX_LEVELS]; float mip_res[DOS_MAX_LEVELS][3]; int n_levels;
     DosCone occ, sdw;
@@ -403,7 +404,24 @@ struct DosShader {
     return (expf(-rays[0]) + (expf(-rays[1]) + expf(-rays[2]) + expf(-rays[3]) + expf(-rays[4]) + expf(-rays[5]) + expf(-rays[6])) * cn.adj7) /
            (1.0f + cn.adj7 * 6.0f);
   }
-  // ShadeSample (:607-656): OcclusionEvaluationKernel (:326-335) and ShadowEvaluationKernel (:522-562)
+  // ShadowEvaluationKernel (:522-562); false: outside the spot cone (Isdw stays 0)
+  static __device__ __forceinline__ float shadow_term(const MarchArgs& a, const Args& s, const Const& c, f3 tx) {
+    const f3 lf = mk3(s.light_fwd[0], s.light_fwd[1], s.light_fwd[2]), lu = mk3(s.light_up[0], s.light_up[1], s.light_up[2]);
+    const f3 lr = mk3(s.light_right[0], s.light_right[1], s.light_right[2]);
+    f3 k, u, v;
+    if (s.type_of_shadow == 0 || s.type_of_shadow == 1) {
+      // (pos_from_zero - VolumeScaledSizes / 2.0): division, not the 0.5 product of the occlusion kernel
+      const f3 cone_vec = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), sub3(tx, div3(c.sizes, mk3(2.0f, 2.0f, 2.0f)))));
+      k = cone_vec;
+      u = normalize_rn(cross_rn(k, lr));
+      v = normalize_rn(cross_rn(k, u));
+      if (s.type_of_shadow == 1 && dot_rn(cone_vec, lf) < s.spot_cos) return 0.0f;
+    } else if (s.type_of_shadow == 2) { k = lf; v = lu; u = lr; }
+    else { k = u = v = mk3(0.f, 0.f, 0.f); }
+    // Cone1RayShadow declares (k, v, u) but is called with (k, u, v): the 3/7-ray stages see the two swapped
+    return cone_trace(s, c, s.sdw, tx, k, v, u);
+  }
+  // ShadeSample (:607-656): OcclusionEvaluationKernel (:326-335) and ShadowEvaluationKernel
   static __device__ void shade(const MarchArgs& a, const Args& s, const Const& c, f3 tx, f3 camera_dir, float& Iocc, float& Isdw) {
     Iocc = 0.0f; Isdw = 0.0f;
     const f3 realpos = sub3(tx, scale3(c.sizes, 0.5f));
@@ -412,22 +430,19 @@ struct DosShader {
       const f3 v_up = normalize_rn(cross_rn(mk3(-camera_dir.x, -camera_dir.y, -camera_dir.z), v_right));
       Iocc = cone_trace(s, c, s.occ, tx, normalize_rn(sub3(c.eye, realpos)), v_up, v_right);
     }
-    if (a.apply_shadow) {
-      const f3 lf = mk3(s.light_fwd[0], s.light_fwd[1], s.light_fwd[2]), lu = mk3(s.light_up[0], s.light_up[1], s.light_up[2]);
-      const f3 lr = mk3(s.light_right[0], s.light_right[1], s.light_right[2]);
-      f3 k, u, v;
-      if (s.type_of_shadow == 0 || s.type_of_shadow == 1) {
-        // (pos_from_zero - VolumeScaledSizes / 2.0): division, not the 0.5 product of the occlusion kernel
-        const f3 cone_vec = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), sub3(tx, div3(c.sizes, mk3(2.0f, 2.0f, 2.0f)))));
-        k = cone_vec;
-        u = normalize_rn(cross_rn(k, lr));
-        v = normalize_rn(cross_rn(k, u));
-        if (s.type_of_shadow == 1 && dot_rn(cone_vec, lf) < s.spot_cos) return;
-      } else if (s.type_of_shadow == 2) { k = lf; v = lu; u = lr; }
-      else { k = u = v = mk3(0.f, 0.f, 0.f); }
-      // Cone1RayShadow declares (k, v, u) but is called with (k, u, v): the 3/7-ray stages see the two swapped
-      Isdw = cone_trace(s, c, s.sdw, tx, k, v, u);
+    if (a.apply_shadow) Isdw = shadow_term(a, s, c, tx);
+  }
+  // main() of rc1pdosct/lightcachecomputation.comp (:534-560): same cones, but the occlusion basis comes from the per-cell eye
+  // vector and EyeCamUp (:280-292) — the up row of the view matrix (Camera::GetCameraVectors, camera.cpp:336-341)
+  static __device__ void shade_cell(const MarchArgs& a, const Args& s, const Const& c, f3 tx, float& Iocc, float& Isdw) {
+    const f3 realpos = sub3(tx, scale3(c.sizes, 0.5f));
+    if (a.apply_occlusion) {
+      const f3 cone_vec = normalize_rn(sub3(c.eye, realpos));
+      const f3 v_right = normalize_rn(cross_rn(mk3(-cone_vec.x, -cone_vec.y, -cone_vec.z), mk3(a.lookat[1], a.lookat[4], a.lookat[7])));
+      const f3 v_up = normalize_rn(cross_rn(cone_vec, v_right));
+      Iocc = cone_trace(s, c, s.occ, tx, cone_vec, v_up, v_right);
     }
+    if (a.apply_shadow) Isdw = shadow_term(a, s, c, tx);
   }
 };
 
@@ -447,8 +462,11 @@ class DosRenderer : public RendererImpl {
     prm_.base_level_sigma0 = 1.0f; prm_.use_custom_resolution = 1;                              // extcoefvolumegenerator.cpp:11-16
     prm_.custom_resolution[0] = prm_.custom_resolution[1] = prm_.custom_resolution[2] = 128;
     prm_.count_samples = 0;
+    prm_.use_light_cache = 0;                                                                   // :63-64
+    prm_.light_cache_resolution[0] = prm_.light_cache_resolution[1] = prm_.light_cache_resolution[2] = 32;
   }
   ~DosRenderer() override { clean(); }
+  LightCache* light_cache() override { return &cache_; }
   int init(int w, int h) override {
     const Volume& v = ctx->vol;
     VRB_REQUIRE(v.tex != 0, VRB_ERR_NO_VOLUME, "RC1PConeTracingDirOcclusionShading::Init: no volume texture");
@@ -467,7 +485,7 @@ class DosRenderer : public RendererImpl {
     return VRB_OK;
   }
   void clean() override {
-    pyr_.release();
+    pyr_.release(); cache_.release();
     if (d_occ_) cudaFree(d_occ_);
     if (d_sdw_) cudaFree(d_sdw_);
     d_occ_ = d_sdw_ = nullptr; cones_valid_ = false;
@@ -480,6 +498,7 @@ class DosRenderer : public RendererImpl {
                     p.gaussian_sigma_limit_multiplier > 0.0f,
                 VRB_ERR_INVALID, "dos set_params: bad value");
     VRB_REQUIRE(!p.apply_gradient_shading, VRB_ERR_UNSUPPORTED, "dos set_params: gradient shading needs a gradient volume (not uploaded)");
+    VRB_REQUIRE(light_cache_params_ok(p.use_light_cache, p.light_cache_resolution), VRB_ERR_INVALID, "dos set_params: bad light cache resolution");
     if (memcmp(&p, &prm_, sizeof(p)) != 0) cones_valid_ = false;
     prm_ = p;
     return VRB_OK;
@@ -540,6 +559,7 @@ class DosRenderer : public RendererImpl {
     s.type_of_shadow = prm_.type_of_shadow;
     s.spot_cos = std::cos(3.14159265358979323846f * prm_.spot_light_max_angle / 180.f);          // :158
     for (int i = 0; i < 3; i++) { s.light_fwd[i] = prm_.light_cam_forward[i]; s.light_up[i] = prm_.light_cam_up[i]; s.light_right[i] = prm_.light_cam_right[i]; }
+    if (prm_.use_light_cache) return redraw_object_space<DosShader>(*this, cache_, prm_.light_cache_resolution, a, s, prm_.count_samples != 0);
     return launch_march<DosShader>(*this, a, s, prm_.count_samples != 0);
   }
  private:
@@ -572,6 +592,7 @@ class DosRenderer : public RendererImpl {
   ConeTable occ_, sdw_;
   float* d_occ_ = nullptr; float* d_sdw_ = nullptr;
   bool cones_valid_ = false;
+  LightCache cache_;
 };
 
 RendererImpl* make_dos(vrb_ctx* ctx) { return new DosRenderer(ctx); }

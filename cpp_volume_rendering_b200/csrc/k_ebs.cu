@@ -9,6 +9,7 @@
 #include "vrb_internal.cuh"
 #include "vrb_ray.cuh"
 #include "vrb_sat.cuh"
+#include "vrb_lightcache.cuh"
 #include <algorithm>
 
 namespace vrb {
@@ -120,6 +121,30 @@ __device__ float directional_shadows(const EbsArgs& a, const EbsConst& c, f3 tx)
   return expf(-Stau);
 }
 
+// ebsrenderer.cpp:568-580 (MinSATPosition ... InvVolumeScaledSizes)
+__device__ __forceinline__ EbsConst make_ebs_const(const EbsArgs& a) {
+  EbsConst c;
+  c.scales = mk3(a.scales[0], a.scales[1], a.scales[2]); c.sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]);
+  c.min_sat = scale3(c.scales, 0.5f); c.max_sat = add3(c.sizes, scale3(c.scales, 1.5f));
+  c.min_vol = scale3(c.scales, 0.5f); c.max_vol = sub3(c.sizes, scale3(c.scales, 0.5f));
+  c.inv_vol_scaled = div3(mk3(1.0f, 1.0f, 1.0f), add3(c.sizes, scale3(c.scales, 2.0f)));
+  c.sat_res = mk3(a.sat_res[0], a.sat_res[1], a.sat_res[2]);
+  return c;
+}
+
+// Cell functor of the object-space mode (vrb_lightcache.cuh): main() of rc1pextbsd/lightcachecomputation.comp.  With the defines that
+// file enables its ExtinctionAmbientOcclusion / ExtinctionDirectionalShadows are the image-space shader's functions above.
+struct EbsShader {
+  static constexpr bool OBJECT_SPACE = false;
+  typedef EbsArgs Args;
+  typedef EbsConst Const;
+  static __device__ __forceinline__ Const prepare(const MarchArgs&, const Args& s) { return make_ebs_const(s); }
+  static __device__ void shade_cell(const MarchArgs& a, const Args& s, const Const& c, f3 tx, float& Iocc, float& Isdw) {
+    if (a.apply_occlusion) Iocc = extinction_ao(s, c, tx);
+    if (a.apply_shadow) Isdw = directional_shadows(s, c, tx);
+  }
+};
+
 constexpr int EBS_THREADS = 128;
 
 template <bool COUNT>
@@ -133,12 +158,7 @@ __global__ void __launch_bounds__(EBS_THREADS, 4) ebs_kernel(const __grid_consta
   }
   for (int i = threadIdx.x; i < a.vis_words; i += blockDim.x) s_mask[i] = a.vis_mask[i];
   __syncthreads();
-  EbsConst c;
-  c.scales = mk3(a.scales[0], a.scales[1], a.scales[2]); c.sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]);
-  c.min_sat = scale3(c.scales, 0.5f); c.max_sat = add3(c.sizes, scale3(c.scales, 1.5f));
-  c.min_vol = scale3(c.scales, 0.5f); c.max_vol = sub3(c.sizes, scale3(c.scales, 0.5f));
-  c.inv_vol_scaled = div3(mk3(1.0f, 1.0f, 1.0f), add3(c.sizes, scale3(c.scales, 2.0f)));
-  c.sat_res = mk3(a.sat_res[0], a.sat_res[1], a.sat_res[2]);
+  const EbsConst c = make_ebs_const(a);
   const f3 res = mk3(a.res[0], a.res[1], a.res[2]);
   const f3 inv_sizes = div3(mk3(1.0f, 1.0f, 1.0f), c.sizes);
   const int lane = threadIdx.x & 31;
@@ -224,7 +244,10 @@ class EbsRenderer : public RendererImpl {
     prm_.dir_cone_max_distance = 0.0f; prm_.type_of_shadow = 0;
     prm_.light_cam_forward[0] = 0.f; prm_.light_cam_forward[1] = 0.f; prm_.light_cam_forward[2] = -1.f;
     prm_.fast_sat = 0; prm_.count_samples = 0;
+    prm_.use_light_cache = 0;                                                                  // ebsrenderer.cpp:46-47
+    prm_.light_cache_resolution[0] = prm_.light_cache_resolution[1] = prm_.light_cache_resolution[2] = 32;
   }
+  LightCache* light_cache() override { return &cache_; }
   int init(int w, int h) override {
     const Volume& v = ctx->vol;
     VRB_REQUIRE(v.tex != 0, VRB_ERR_NO_VOLUME, "RC1PExtinctionBasedShading::Init: no volume texture");
@@ -242,12 +265,13 @@ class EbsRenderer : public RendererImpl {
     built = true;
     return VRB_OK;
   }
-  void clean() override { sat_.release(); }
+  void clean() override { sat_.release(); cache_.release(); }
   int set_params(const void* pod, size_t size) override {
     VRB_REQUIRE(pod && size == sizeof(vrb_ebs_params), VRB_ERR_INVALID, "ebs set_params: size %zu != sizeof(vrb_ebs_params) %zu", size, sizeof(vrb_ebs_params));
     const vrb_ebs_params p = *(const vrb_ebs_params*)pod;
     VRB_REQUIRE(p.step_size > 0.0f && p.ambient_occlusion_shells >= 1 && p.dir_shadow_sample_interval > 0.0f, VRB_ERR_INVALID, "ebs set_params: bad value");
     VRB_REQUIRE(!p.apply_gradient_shading, VRB_ERR_UNSUPPORTED, "ebs set_params: gradient shading needs a gradient volume (not uploaded)");
+    VRB_REQUIRE(light_cache_params_ok(p.use_light_cache, p.light_cache_resolution), VRB_ERR_INVALID, "ebs set_params: bad light cache resolution");
     prm_ = p;
     return VRB_OK;
   }
@@ -288,6 +312,11 @@ class EbsRenderer : public RendererImpl {
     a.interval = prm_.dir_shadow_sample_interval; a.initial_step = prm_.dir_shadow_initial_step;
     a.weight = prm_.dir_shadow_user_interface_weight; a.max_distance = prm_.dir_cone_max_distance; a.type_of_shadow = prm_.type_of_shadow;
     a.ka = light.ka; a.kd = light.kd;
+    if (prm_.use_light_cache) {                                                                // :127-135
+      MarchArgs m{};
+      if (!fill_march_args(*this, prm_.step_size, a.apply_occlusion, a.apply_shadow, m)) return VRB_OK;
+      return redraw_object_space<EbsShader>(*this, cache_, prm_.light_cache_resolution, m, a, prm_.count_samples != 0);
+    }
     a.frame = (uint2*)frame; a.samples = d_samples;
     a.n_peers = n_peer_frames;
     for (int q = 0; q < n_peer_frames; q++) a.peer[q] = (uint2*)peer_frames[q];
@@ -329,6 +358,7 @@ class EbsRenderer : public RendererImpl {
  private:
   vrb_ebs_params prm_{};
   ExtSat sat_;
+  LightCache cache_;
 };
 
 RendererImpl* make_ebs(vrb_ctx* ctx) { return new EbsRenderer(ctx); }

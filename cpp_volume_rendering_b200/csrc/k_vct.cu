@@ -216,11 +216,12 @@ int VctPyramid::ensure(vrb_ctx* ctx, bool with_lut) {
 }  // namespace vrb
 
 // ---- K17 -------------------------------------------------------------------------------------------------
-#include "vrb_march.cuh"
+#include "vrb_lightcache.cuh"
 
 namespace vrb {
 
 struct VctShader {
+  static constexpr bool OBJECT_SPACE = false;
   struct Args {
     cudaTextureObject_t mip[VCT_MAX_LEVELS];
     float mip_res[VCT_MAX_LEVELS][3];
@@ -292,6 +293,11 @@ struct VctShader {
     }
     Isdw = Tvd;
   }
+  // main() of rc1pvctsg/lightcachecomputation.comp: Iao stays 1, Ivd = EvaluationVoxelConeTracing at the cell centre
+  static __device__ void shade_cell(const MarchArgs& a, const Args& s, const Const& c, f3 tx, float&, float& Isdw) {
+    float unused;
+    if (a.apply_shadow) shade(a, s, c, tx, mk3(0.f, 0.f, 0.f), unused, Isdw);
+  }
 };
 
 class VctRenderer : public RendererImpl {
@@ -302,7 +308,10 @@ class VctRenderer : public RendererImpl {
     prm_.cone_step_size = 2.0f; prm_.cone_step_increase_rate = 1.0f; prm_.cone_initial_step = 2.0f;
     prm_.cone_apex_angle = 2.0f; prm_.apply_correction_factor = 1; prm_.opacity_correction_factor = 2.0f;
     prm_.cone_number_of_samples = 50; prm_.count_samples = 0;
+    prm_.use_light_cache = 0;                                                                  // :47-48
+    prm_.light_cache_resolution[0] = prm_.light_cache_resolution[1] = prm_.light_cache_resolution[2] = 32;
   }
+  LightCache* light_cache() override { return &cache_; }
   int init(int w, int h) override {
     const Volume& v = ctx->vol;
     VRB_REQUIRE(v.tex != 0, VRB_ERR_NO_VOLUME, "RC1PVoxelConeTracingSGPU::Init: no volume texture");
@@ -317,12 +326,13 @@ class VctRenderer : public RendererImpl {
     built = true;
     return VRB_OK;
   }
-  void clean() override { pyr_.release(); }
+  void clean() override { pyr_.release(); cache_.release(); }
   int set_params(const void* pod, size_t size) override {
     VRB_REQUIRE(pod && size == sizeof(vrb_vct_params), VRB_ERR_INVALID, "vct set_params: size %zu != sizeof(vrb_vct_params) %zu", size, sizeof(vrb_vct_params));
     const vrb_vct_params p = *(const vrb_vct_params*)pod;
     VRB_REQUIRE(p.step_size > 0.0f && p.cone_step_size > 0.0f && p.cone_number_of_samples >= 0, VRB_ERR_INVALID, "vct set_params: bad value");
     VRB_REQUIRE(!p.apply_gradient_shading, VRB_ERR_UNSUPPORTED, "vct set_params: gradient shading needs a gradient volume (not uploaded)");
+    VRB_REQUIRE(light_cache_params_ok(p.use_light_cache, p.light_cache_resolution), VRB_ERR_INVALID, "vct set_params: bad light cache resolution");
     prm_ = p;
     return VRB_OK;
   }
@@ -373,11 +383,13 @@ class VctRenderer : public RendererImpl {
     s.corr_fact = (float)prm_.apply_correction_factor * prm_.opacity_correction_factor;
     s.vol_max_density = (float)pyr_.vol_max_density; s.vol_max_std = (float)pyr_.max_std;
     s.cone_samples = prm_.cone_number_of_samples;
+    if (prm_.use_light_cache) return redraw_object_space<VctShader>(*this, cache_, prm_.light_cache_resolution, a, s, prm_.count_samples != 0);
     return launch_march<VctShader>(*this, a, s, prm_.count_samples != 0);
   }
  private:
   vrb_vct_params prm_{};
   VctPyramid pyr_;
+  LightCache cache_;
 };
 
 RendererImpl* make_vct(vrb_ctx* ctx) { return new VctRenderer(ctx); }

@@ -84,6 +84,19 @@ struct vrb_ctx {
 
 namespace vrb {
 
+// RG16F light cache of the object-space mode (cppvolrend/utils/preillumination.{h,cpp}): one (occlusion, shadow) pair per
+// cell, x fastest; rebuilt by every Redraw of a renderer whose use_light_cache is set (vrb_lightcache.cuh).
+struct LightCache {
+  __half2* data = nullptr;
+  int dims[3] = {0, 0, 0};
+  float build_ms = 0.f;
+  bool built = false;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  int ensure(const int res[3]);
+  void release();
+  int read(cudaStream_t s, float* host_rg, int out_dims[3], float* ms);
+};
+
 // Per-kind renderer implementation behind the C entry points.
 struct RendererImpl {
   vrb_ctx* ctx;
@@ -132,6 +145,7 @@ struct RendererImpl {
   virtual int get_params(void* pod, size_t size) = 0;
   virtual int redraw(int mode) = 0;             // launches on ctx->stream
   virtual void clean() {}
+  virtual LightCache* light_cache() { return nullptr; }   // renderers with an object-space mode
   int alloc_frame(int w, int h);
   void free_frame();
 };

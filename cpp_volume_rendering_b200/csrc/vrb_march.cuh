@@ -1,7 +1,7 @@
 // Shared front-to-back march of the shadowed DVR renderers (VCT, DOS cone tracing): the common part of
 // vct_ray_bbox_marching.comp:191-264 and crtgt_ray_bbox_marching.comp — ray setup, half-step sampling, classification,
 // `k*(c*Iocc*ka + c*Isdw*kd)` shading, exp() opacity, ERT at 0.99 — around a per-renderer shading functor.
-//   struct Shader { struct Args {...}; struct Const {...};
+//   struct Shader { static constexpr bool OBJECT_SPACE; struct Args {...}; struct Const {...};
 //     static __device__ Const prepare(const MarchArgs&, const Args&);
 //     static __device__ void shade(const MarchArgs&, const Args&, const Const&, f3 tx, f3 camera_dir, float& Iocc, float& Isdw); };
 // Same persistent warp-queue schedule as k_ebs.cu (8x4-pixel warp items, scrambled order, self-resetting counter).
@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
           const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&e.y));
           const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
           float4 src = make_float4(fmaf(w, r1.x - r0.x, r0.x), fmaf(w, r1.y - r0.y, r0.y), fmaf(w, b1.x - b0.x, b0.x), fmaf(w, b1.y - b0.y, b0.y));
-          if (src.w > 0.0f) {
+          if (src.w > 0.0f && (!S::OBJECT_SPACE || a.apply_occlusion || a.apply_shadow)) {   // obj_ray_marching.comp:312
             float ka = 0.0f, kd = 0.0f, Iocc = 0.0f, Isdw = 0.0f;
             if (a.apply_occlusion) ka = a.ka;
             if (a.apply_shadow) kd = a.kd;

@@ -38,6 +38,35 @@ void RendererImpl::free_frame() {
   frame_base = nullptr; frame = nullptr; frame_bytes = 0; width = height = 0;
 }
 
+int LightCache::ensure(const int res[3]) {
+  if (!e0) { VRB_CUDA(cudaEventCreate(&e0)); VRB_CUDA(cudaEventCreate(&e1)); }
+  if (data && res[0] == dims[0] && res[1] == dims[1] && res[2] == dims[2]) return VRB_OK;
+  if (data) cudaFree(data);
+  data = nullptr; built = false;
+  // PreIlluminationStructuredVolume::GenerateLightCacheTexture (preillumination.cpp:56-80): RG16F, W x H x D
+  VRB_CUDA(cudaMalloc(&data, (size_t)res[0] * res[1] * res[2] * sizeof(__half2)));
+  dims[0] = res[0]; dims[1] = res[1]; dims[2] = res[2];
+  return VRB_OK;
+}
+void LightCache::release() {
+  if (data) cudaFree(data);
+  if (e0) { cudaEventDestroy(e0); cudaEventDestroy(e1); }
+  data = nullptr; e0 = e1 = nullptr; built = false; dims[0] = dims[1] = dims[2] = 0;
+}
+int LightCache::read(cudaStream_t s, float* host_rg, int out_dims[3], float* ms) {
+  VRB_REQUIRE(built, VRB_ERR_INVALID, "vrb_light_cache_read: no Redraw with use_light_cache yet");
+  VRB_CUDA(cudaStreamSynchronize(s));
+  if (out_dims) { out_dims[0] = dims[0]; out_dims[1] = dims[1]; out_dims[2] = dims[2]; }
+  if (ms) { VRB_CUDA(cudaEventElapsedTime(&build_ms, e0, e1)); *ms = build_ms; }
+  if (host_rg) {
+    const size_t n = (size_t)dims[0] * dims[1] * dims[2];
+    std::vector<__half2> tmp(n);
+    VRB_CUDA(cudaMemcpy(tmp.data(), data, n * sizeof(__half2), cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < n; i++) { const float2 f = __half22float2(tmp[i]); host_rg[2 * i] = f.x; host_rg[2 * i + 1] = f.y; }
+  }
+  return VRB_OK;
+}
+
 int RendererImpl::ensure_tile_order() {
   const int key[5] = {width, height, part_tile, rank, n_ranks};
   if (d_tile_order && memcmp(key, tile_order_key, sizeof(key)) == 0) return VRB_OK;
@@ -322,6 +351,13 @@ int vrb_sbtm_read_occlusion(vrb_renderer* r, float* host, int* n_slices) {
 int vrb_dos_read_extcoef(vrb_renderer* r, int level, float* host, int dims[3], int* n_levels, float* build_ms) {
   VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_dos_read_extcoef: null renderer");
   return dos_read_extcoef(r->impl, level, host, dims, n_levels, build_ms);
+}
+
+int vrb_light_cache_read(vrb_renderer* r, float* host_rg, int dims[3], float* build_ms) {
+  VRB_REQUIRE(r && r->impl, VRB_ERR_INVALID, "vrb_light_cache_read: null renderer");
+  LightCache* lc = r->impl->light_cache();
+  VRB_REQUIRE(lc, VRB_ERR_INVALID, "vrb_light_cache_read: renderer kind %d has no object-space mode", r->impl->kind);
+  return lc->read(r->impl->ctx->stream, host_rg, dims, build_ms);
 }
 
 int vrb_dos_read_sections(vrb_renderer* r, int which, float* rgba, int cap, int* n, float axes30[30], int counts[3], float* adj7) {

@@ -76,6 +76,21 @@ static void register_all(RenderingManager* m) {
 }
 int vrbh_num_renderers(void) { return 8; }
 
+// Test hook: what the ImGui "light cache" checkbox / resolution fields (PreIlluminationStructuredVolume::SetImGuiComponents,
+// preillumination.cpp:82-116) would set on the next session's DOS / EBS / VCT renderer.  active < 0 leaves the constructor's state.
+static int g_lc_active = -1, g_lc_res[3] = {32, 32, 32};
+void vrbh_session_light_cache(int active, int w, int h, int d) { g_lc_active = active; g_lc_res[0] = w; g_lc_res[1] = h; g_lc_res[2] = d; }
+static void apply_light_cache(BaseVolumeRenderer* r) {
+  if (g_lc_active < 0) return;
+  PreIlluminationStructuredVolume* pv = nullptr;
+  if (auto* p = dynamic_cast<CudaRC1PConeTracingDirOcclusionShading*>(r)) pv = &p->m_pre_illum_str_vol;
+  else if (auto* p = dynamic_cast<CudaRC1PExtinctionBasedShading*>(r)) pv = &p->m_pre_illum_str_vol;
+  else if (auto* p = dynamic_cast<CudaRC1PVoxelConeTracingSGPU*>(r)) pv = &p->m_pre_illum_str_vol;
+  if (!pv) return;
+  pv->SetActive(g_lc_active != 0); pv->SetLightCacheResolution(g_lc_res[0], g_lc_res[1], g_lc_res[2]);
+  r->SetOutdated();
+}
+
 // One headless session: read the dataset + TF from disk, register the plugins, select `renderer`, optionally run
 // the evaluation sweep (eval_dir != NULL; `numframes` frames per sample, CSV in the reference's schema), else
 // render `numframes` frames.  The last frame is returned as RGBA32F (w*h*4 floats, row 0 = bottom) and RGB8.
@@ -95,6 +110,7 @@ int vrbh_run_session(const char* volume_path, const char* tf_path, int renderer,
     vis::vec3 e, c, u; e.x = eye[0]; e.y = eye[1]; e.z = eye[2]; u.y = 1.0f;
     m->GetCamera()->SetInitialConfig(e, c, u);
     if (!m->SetCurrentVolumeRenderer(renderer)) { fail("SetCurrentVolumeRenderer: " + m->LastError()); break; }
+    apply_light_cache(m->CurrentRenderer());
     if (out_name && name_cap > 0) { std::strncpy(out_name, m->CurrentRenderer()->GetName(), name_cap - 1); out_name[name_cap - 1] = 0; }
     bool ok = true;
     if (eval_dir) {

@@ -187,6 +187,7 @@ CudaRC1PConeTracingDirOcclusionShading::CudaRC1PConeTracingDirOcclusionShading()
       sdw_cone_half_angle(0.5f), sdw_initial_step(3.0f), sdw_covered_distance(100.0f), sdw_ui_weight(1.0f), sdw_max_packing(0),
       base_level_sigma0(1.0f), use_custom_resolution(true) {
   custom_resolution[0] = custom_resolution[1] = custom_resolution[2] = 128;
+  m_pre_illum_str_vol.SetActive(false); m_pre_illum_str_vol.SetLightCacheResolution(32, 32, 32);   // :63-64
 }
 bool CudaRC1PConeTracingDirOcclusionShading::Init(int w, int h) {
   if (!CreateDeviceRenderer(VRB_DOS_CONE, w, h)) return false;
@@ -212,6 +213,8 @@ bool CudaRC1PConeTracingDirOcclusionShading::Update(vis::Camera* camera) {
   p.sdw_ui_weight = sdw_ui_weight; p.sdw_max_packing = sdw_max_packing;
   p.base_level_sigma0 = base_level_sigma0; p.use_custom_resolution = use_custom_resolution ? 1 : 0;
   for (int i = 0; i < 3; i++) p.custom_resolution[i] = custom_resolution[i];
+  p.use_light_cache = m_pre_illum_str_vol.IsActive() ? 1 : 0;
+  for (int i = 0; i < 3; i++) p.light_cache_resolution[i] = m_pre_illum_str_vol.GetLightCacheResolution()[i];
   if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
   return PushCameraAndLight(camera);
 }
@@ -219,7 +222,9 @@ bool CudaRC1PConeTracingDirOcclusionShading::Update(vis::Camera* camera) {
 CudaRC1PExtinctionBasedShading::CudaRC1PExtinctionBasedShading()                       // ebsrenderer.cpp:18-42
     : m_u_step_size(0.5f), apply_ambient_occlusion(true), ambient_occlusion_shells(15), ambient_occlusion_radius(1.0f),
       apply_directional_shadows(true), dir_shadow_cone_angle(1.0f), dir_shadow_sample_interval(2.0f), dir_shadow_initial_step(2.0f),
-      dir_shadow_user_interface_weight(1.0f), dir_cone_max_distance(0.0f), type_of_shadow(0), fast_sat(false) {}
+      dir_shadow_user_interface_weight(1.0f), dir_cone_max_distance(0.0f), type_of_shadow(0), fast_sat(false) {
+  m_pre_illum_str_vol.SetActive(false); m_pre_illum_str_vol.SetLightCacheResolution(32, 32, 32);   // :46-47
+}
 bool CudaRC1PExtinctionBasedShading::Init(int w, int h) {
   if (!CreateDeviceRenderer(VRB_EBS_SAT, w, h)) return false;
   vrb_ebs_params p;
@@ -242,6 +247,8 @@ bool CudaRC1PExtinctionBasedShading::Update(vis::Camera* camera) {
   p.dir_shadow_sample_interval = dir_shadow_sample_interval; p.dir_shadow_initial_step = dir_shadow_initial_step;
   p.dir_shadow_user_interface_weight = dir_shadow_user_interface_weight; p.dir_cone_max_distance = dir_cone_max_distance;
   p.type_of_shadow = type_of_shadow; p.fast_sat = fast_sat ? 1 : 0;
+  p.use_light_cache = m_pre_illum_str_vol.IsActive() ? 1 : 0;
+  for (int i = 0; i < 3; i++) p.light_cache_resolution[i] = m_pre_illum_str_vol.GetLightCacheResolution()[i];
   if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
   return PushCameraAndLight(camera);
 }
@@ -254,7 +261,9 @@ void CudaRC1PExtinctionBasedShading::FillParameterSpace(ParameterSpace& pspace) 
 CudaRC1PVoxelConeTracingSGPU::CudaRC1PVoxelConeTracingSGPU()                           // vctrenderer.cpp:27-43
     : m_u_step_size(0.5f), apply_ambient_occlusion(true), apply_directional_shadows(true), apply_correction_factor(true),
       cone_step_size(2.0f), cone_step_increase_rate(1.0f), cone_initial_step(2.0f), cone_apex_angle(2.0f),
-      opacity_correction_factor(2.0f), cone_number_of_samples(50) {}
+      opacity_correction_factor(2.0f), cone_number_of_samples(50) {
+  m_pre_illum_str_vol.SetActive(false); m_pre_illum_str_vol.SetLightCacheResolution(32, 32, 32);   // :47-48
+}
 bool CudaRC1PVoxelConeTracingSGPU::Init(int w, int h) {
   if (!CreateDeviceRenderer(VRB_VCT, w, h)) return false;
   vrb_vct_params p;
@@ -274,6 +283,8 @@ bool CudaRC1PVoxelConeTracingSGPU::Update(vis::Camera* camera) {
   p.cone_step_size = cone_step_size; p.cone_step_increase_rate = cone_step_increase_rate; p.cone_initial_step = cone_initial_step;
   p.cone_apex_angle = cone_apex_angle; p.apply_correction_factor = apply_correction_factor ? 1 : 0;
   p.opacity_correction_factor = opacity_correction_factor; p.cone_number_of_samples = cone_number_of_samples;
+  p.use_light_cache = m_pre_illum_str_vol.IsActive() ? 1 : 0;
+  for (int i = 0; i < 3; i++) p.light_cache_resolution[i] = m_pre_illum_str_vol.GetLightCacheResolution()[i];
   if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
   return PushCameraAndLight(camera);
 }

@@ -91,6 +91,21 @@ class CudaRayCasting1PassIso : public BaseVolumeRenderer {
   int m_kind;
 };
 
+// PreIlluminationStructuredVolume (cppvolrend/utils/preillumination.{h,cpp}): the switch and the resolution of the light cache of the
+// object-space mode.  The RG16F texture itself lives in the device library (vrb_light_cache_read); this mirror only carries the state
+// the three renderers forward through use_light_cache / light_cache_resolution.
+class PreIlluminationStructuredVolume {
+ public:
+  PreIlluminationStructuredVolume() : m_active(false) { m_res[0] = m_res[1] = m_res[2] = 8; }   // preillumination.cpp:7-17
+  bool IsActive() const { return m_active; }
+  void SetActive(bool f) { m_active = f; }
+  const int* GetLightCacheResolution() const { return m_res; }
+  void SetLightCacheResolution(int w, int h, int d) { m_res[0] = w; m_res[1] = h; m_res[2] = d; }
+ private:
+  bool m_active;
+  int m_res[3];
+};
+
 // RC1PConeTracingDirOcclusionShading (structured/rc1pdosct/dosrcrenderer.{h,cpp}); the public members stand for the
 // renderer's own flags and for the setters of its two ConeGaussianSamplers and its ExtinctionCoefficientVolume.
 class CudaRC1PConeTracingDirOcclusionShading : public BaseVolumeRenderer {
@@ -109,6 +124,7 @@ class CudaRC1PConeTracingDirOcclusionShading : public BaseVolumeRenderer {
   float base_level_sigma0;
   bool use_custom_resolution;
   int custom_resolution[3];
+  PreIlluminationStructuredVolume m_pre_illum_str_vol;   // SetActive(false), 32^3 in the constructor
 };
 
 // RC1PExtinctionBasedShading (structured/rc1pextbsd/ebsrenderer.{h,cpp})
@@ -126,6 +142,7 @@ class CudaRC1PExtinctionBasedShading : public BaseVolumeRenderer {
   bool apply_directional_shadows; float dir_shadow_cone_angle, dir_shadow_sample_interval, dir_shadow_initial_step;
   float dir_shadow_user_interface_weight, dir_cone_max_distance; int type_of_shadow;
   bool fast_sat;                        // new: separable-scan SAT builder instead of the reference's recurrence
+  PreIlluminationStructuredVolume m_pre_illum_str_vol;   // SetActive(false), 32^3 in the constructor
 };
 
 // RC1PVoxelConeTracingSGPU (structured/rc1pvctsg/vctrenderer.{h,cpp})
@@ -141,6 +158,7 @@ class CudaRC1PVoxelConeTracingSGPU : public BaseVolumeRenderer {
   bool apply_ambient_occlusion, apply_directional_shadows, apply_correction_factor;
   float cone_step_size, cone_step_increase_rate, cone_initial_step, cone_apex_angle, opacity_correction_factor;
   int cone_number_of_samples;
+  PreIlluminationStructuredVolume m_pre_illum_str_vol;   // SetActive(false), 32^3 in the constructor
 };
 
 // SBTMDirectionalOcclusionShading (structured/sbtmdos/sbtmdosrenderer.{h,cpp})

@@ -65,6 +65,11 @@ def camera_uniforms(eye, center=(0, 0, 0), up=(0, 1, 0), fovy_deg=45.0, width=1,
     return cam
 
 
+def session_light_cache(active, res=(32, 32, 32)):
+    """Sets (active: 0/1) or resets (active < 0) the light-cache switch the next run_session applies to a dos/ebs/vct renderer."""
+    lib().vrbh_session_light_cache(int(active), int(res[0]), int(res[1]), int(res[2]))
+
+
 def run_session(volume_path, tf_path, renderer, width, height, eye, eval_dir=None, numframes=1, max_samples=0, device=0):
     """Returns (displays, rgba32f [H,W,4], rgb8 [H,W,3], renderer name).  Raises on failure (no CPU fallback)."""
     e = np.asarray(eye, np.float32)

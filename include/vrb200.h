@@ -123,6 +123,8 @@ typedef struct {
   float light_cam_forward[3];              /* RenderingParameters::GetBlinnPhongLightSourceCameraForward() */
   int   fast_sat;                          /* new: 0 = SAT by the reference's recurrence (bit-identical), 1 = separable scan */
   int   count_samples;
+  int   use_light_cache;                   /* PreIlluminationStructuredVolume::IsActive(), false: object-space mode (see vrb_light_cache_read) */
+  int   light_cache_resolution[3];         /* 32^3 (SetLightCacheResolution in the renderer's constructor) */
 } vrb_ebs_params;
 
 /* Run-time parameters of RC1PVoxelConeTracingSGPU: its ImGui-mutable members (vctrenderer.cpp:27-43).
@@ -140,6 +142,8 @@ typedef struct {
   float opacity_correction_factor;  /* 2.0 */
   int   cone_number_of_samples;     /* 50 */
   int   count_samples;
+  int   use_light_cache;                   /* PreIlluminationStructuredVolume::IsActive(), false: object-space mode (see vrb_light_cache_read) */
+  int   light_cache_resolution[3];         /* 32^3 (SetLightCacheResolution in the renderer's constructor) */
 } vrb_vct_params;
 
 /* Run-time parameters of SBTMDirectionalOcclusionShading: its ImGui-mutable members (sbtmdosrenderer.cpp:20-46).
@@ -184,6 +188,8 @@ typedef struct {
   int   use_custom_resolution;               /* true: the pyramid base is custom_resolution, else the volume's size */
   int   custom_resolution[3];                /* 128^3 */
   int   count_samples;
+  int   use_light_cache;                   /* PreIlluminationStructuredVolume::IsActive(), false: object-space mode (see vrb_light_cache_read) */
+  int   light_cache_resolution[3];         /* 32^3 (SetLightCacheResolution in the renderer's constructor) */
 } vrb_dos_params;
 
 /* ---- library / context ------------------------------------------------------------------- */
@@ -278,6 +284,15 @@ int vrb_dos_read_sections(vrb_renderer* r, int which, float* rgba, int cap, int*
  * read after the last Redraw of a VRB_SBTM_DOS renderer (width*height floats, row 0 = bottom) and the number of
  * slices drawn.  host may be NULL. */
 int vrb_sbtm_read_occlusion(vrb_renderer* r, float* host, int* n_slices);
+
+/* Light-cache ("object space") mode of the DOS-cone, EBS and VCT renderers (cppvolrend/utils/preillumination.{h,cpp},
+ * the three structured lightcachecomputation.comp and _common_shaders/obj_ray_marching.comp): with use_light_cache
+ * set, every Redraw first evaluates the renderer's occlusion / shadow terms once per cell of an RG16F grid of
+ * light_cache_resolution cells (PreComputeLightCache) and the march then shades each sample with a trilinear fetch
+ * of that grid instead of tracing cones per sample.
+ * Test / measurement hook: the (R, G) = (occlusion, shadow) cells of the last Redraw as 2 floats per cell, x fastest,
+ * its dims and the device time of the cache pass.  Any output pointer may be NULL. */
+int vrb_light_cache_read(vrb_renderer* r, float* host_rg, int dims[3], float* build_ms);
 
 /* ---- multi-GPU: image-space partition (no reference counterpart) ------------ */
 /* Tiles of tile x tile pixels are dealt round-robin: this rank renders tile t iff t % n_ranks == rank.

@@ -188,6 +188,28 @@ uint64_t orc_dos_render(const orc_dos_params* p, const float* vol_r16f, const fl
                         const float* const* levels, int n_levels, const float* occ_sections, const float* sdw_sections,
                         float* out_rgba, uint64_t* out_shaded);
 
+/* ---- light-cache ("object space") mode of the DOS / VCT / EBS renderers (row a23) -------------------------- */
+/* main() of the three lightcachecomputation.comp: dims[0]*dims[1]*dims[2] cells, x fastest, 2 floats (R, G) per cell, rounded to fp16. */
+void orc_dos_light_cache(const orc_dos_params* p, const float* const* levels, int n_levels, const float* occ_sections,
+                         const float* sdw_sections, const int dims[3], float* out_rg);
+void orc_vct_light_cache(const orc_vct_params* p, const float* const* levels, int n_levels, const float* lut, int lut_w, int lut_h,
+                         const int dims[3], float* out_rg);
+void orc_ebs_light_cache(const orc_ebs_params* p, const float* sat, const int dims[3], float* out_rg);
+typedef struct {
+  int   width, height;
+  int   vol_w, vol_h, vol_d;
+  float voxel[3];
+  float eye[3];
+  float lookat[9];
+  float tan_fovy, aspect, step;
+  int   apply_occlusion, apply_shadow;
+  float ka, kd;
+  int   row_begin, row_end, row_stride, threads;
+} orc_obj_params;
+/* main() of _common_shaders/obj_ray_marching.comp over a light cache.  Returns march-loop iterations. */
+uint64_t orc_obj_render(const orc_obj_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n, const float* cache_rg,
+                        const int dims[3], float* out_rgba);
+
 int orc_max_threads(void);
 
 #ifdef __cplusplus

@@ -364,10 +364,10 @@ uint32_t dos_pixel(const DosCtx& c, int px, int py, float out[4], bool* hit, uin
 
 }  // namespace
 
-extern "C" uint64_t orc_dos_render(const orc_dos_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
-                                   const float* const* levels, int n_levels, const float* occ_sections, const float* sdw_sections,
-                                   float* out_rgba, uint64_t* out_shaded) {
-  DosCtx c; c.p = p;
+namespace {
+void dos_setup(DosCtx& c, const orc_dos_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n, const float* const* levels, int n_levels,
+               const float* occ_sections, const float* sdw_sections) {
+  c.p = p;
   c.vol.w = p->vol_w; c.vol.h = p->vol_h; c.vol.d = p->vol_d; c.vol.data = vol_r16f;
   c.tf.n = tf_n; c.tf.data = tf_rgbt;
   for (int l = 0; l < n_levels; l++) { Level m; level_dims(p->ext_res, l, m.w, m.h, m.d); m.data = levels[l]; c.mips.push_back(m); }
@@ -379,6 +379,46 @@ extern "C" uint64_t orc_dos_render(const orc_dos_params* p, const float* vol_r16
   };
   fill(c.occ, occ_sections, p->occ_counts, p->occ_axes, p->occ_initial_step, p->occ_adj7, p->occ_ui_weight);
   fill(c.sdw, sdw_sections, p->sdw_counts, p->sdw_axes, p->sdw_initial_step, p->sdw_adj7, p->sdw_ui_weight);
+}
+}  // namespace
+
+// main() of rc1pdosct/lightcachecomputation.comp (:534-560): one (Idao, Idcs) pair per light-cache cell, stored RG16F.  The cone
+// functions are the image-space shader's; only the occlusion basis differs (:280-292: built from the per-cell eye vector and EyeCamUp,
+// which Camera::GetCameraVectors (libs/vis_utils/camera.cpp:336-341) makes the up row of the view matrix).
+extern "C" void orc_dos_light_cache(const orc_dos_params* p, const float* const* levels, int n_levels, const float* occ_sections,
+                                    const float* sdw_sections, const int dims[3], float* out_rg) {
+  DosCtx c;
+  dos_setup(c, p, nullptr, nullptr, 0, levels, n_levels, occ_sections, sdw_sections);
+  const vec3 eye(p->eye[0], p->eye[1], p->eye[2]), cam_up(p->lookat[1], p->lookat[4], p->lookat[7]);
+  const vec3 cell = vec3(p->voxel[0], p->voxel[1], p->voxel[2]) *
+                    (vec3((float)p->vol_w, (float)p->vol_h, (float)p->vol_d) / vec3((float)dims[0], (float)dims[1], (float)dims[2]));
+#ifdef _OPENMP
+  int nt = p->threads > 0 ? p->threads : omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 1) collapse(2) num_threads(nt)
+#endif
+  for (int z = 0; z < dims[2]; z++)
+    for (int y = 0; y < dims[1]; y++)
+      for (int x = 0; x < dims[0]; x++) {
+        float Idao = 1.0f, Idcs = 1.0f;
+        vec3 tex_pos = (vec3((float)x, (float)y, (float)z) + vec3(0.5f)) * cell;
+        vec3 realpos = tex_pos - (c.sizes * 0.5f);
+        if (p->apply_occlusion == 1) {
+          vec3 cone_vec = normalize(eye - realpos);
+          vec3 v_right = normalize(cross(-cone_vec, cam_up));
+          vec3 v_up = normalize(cross(cone_vec, v_right));
+          Idao = cone_trace(c, c.occ, tex_pos, cone_vec, v_up, v_right);
+        }
+        if (p->apply_shadow == 1) Idcs = shadow_kernel(c, tex_pos);
+        size_t i = (size_t)x + (size_t)dims[0] * ((size_t)y + (size_t)dims[1] * (size_t)z);
+        out_rg[2 * i] = round_f16(Idao); out_rg[2 * i + 1] = round_f16(Idcs);
+      }
+}
+
+extern "C" uint64_t orc_dos_render(const orc_dos_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
+                                   const float* const* levels, int n_levels, const float* occ_sections, const float* sdw_sections,
+                                   float* out_rgba, uint64_t* out_shaded) {
+  DosCtx c;
+  dos_setup(c, p, vol_r16f, tf_rgbt, tf_n, levels, n_levels, occ_sections, sdw_sections);
   int r0 = p->row_begin, r1 = p->row_end > 0 ? p->row_end : p->height, rs = p->row_stride > 0 ? p->row_stride : 1;
   uint64_t total = 0, shaded = 0;
 #ifdef _OPENMP

@@ -203,9 +203,9 @@ uint32_t shade_pixel(const EbsCtx& c, int px, int py, float out[4], bool* hit, u
 
 }  // namespace
 
-extern "C" uint64_t orc_ebs_render(const orc_ebs_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
-                                   const float* sat, float* out_rgba, uint64_t* out_shaded) {
-  EbsCtx c; c.p = p;
+namespace {
+void ebs_setup(EbsCtx& c, const orc_ebs_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n, const float* sat) {
+  c.p = p;
   c.vol.w = p->vol_w; c.vol.h = p->vol_h; c.vol.d = p->vol_d; c.vol.data = vol_r16f;
   c.sat.w = p->vol_w + 2; c.sat.h = p->vol_h + 2; c.sat.d = p->vol_d + 2; c.sat.data = sat;
   c.tf.n = tf_n; c.tf.data = tf_rgbt;
@@ -214,6 +214,35 @@ extern "C" uint64_t orc_ebs_render(const orc_ebs_params* p, const float* vol_r16
   c.min_sat = c.scales * 0.5f; c.max_sat = c.sizes + c.scales * 1.5f;
   c.min_vol = c.scales * 0.5f; c.max_vol = c.sizes - c.scales * 0.5f;
   c.inv_vol_scaled = vec3(1.0f) / (c.sizes + c.scales * 2.0f);
+}
+}  // namespace
+
+// main() of rc1pextbsd/lightcachecomputation.comp: (Iao, Ids) per light-cache cell, stored RG16F.  With the defines that file
+// enables (CONE_RESCALE_CEIL_INTERVAL, CUT_WHEN_AWAY_FROM_VOLUME) its occlusion and shadow functions are the image-space shader's.
+extern "C" void orc_ebs_light_cache(const orc_ebs_params* p, const float* sat, const int dims[3], float* out_rg) {
+  EbsCtx c;
+  ebs_setup(c, p, nullptr, nullptr, 0, sat);
+  const vec3 cell = c.scales * (vec3((float)p->vol_w, (float)p->vol_h, (float)p->vol_d) / vec3((float)dims[0], (float)dims[1], (float)dims[2]));
+#ifdef _OPENMP
+  int nt = p->threads > 0 ? p->threads : omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 1) collapse(2) num_threads(nt)
+#endif
+  for (int z = 0; z < dims[2]; z++)
+    for (int y = 0; y < dims[1]; y++)
+      for (int x = 0; x < dims[0]; x++) {
+        vec3 tex_pos = (vec3((float)x, (float)y, (float)z) + vec3(0.5f)) * cell;
+        float Iao = 1.0f, Ids = 1.0f;
+        if (p->apply_occlusion == 1) Iao = extinction_ao(c, tex_pos);
+        if (p->apply_shadow == 1) Ids = directional_shadows(c, tex_pos);
+        size_t i = (size_t)x + (size_t)dims[0] * ((size_t)y + (size_t)dims[1] * (size_t)z);
+        out_rg[2 * i] = round_f16(Iao); out_rg[2 * i + 1] = round_f16(Ids);
+      }
+}
+
+extern "C" uint64_t orc_ebs_render(const orc_ebs_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
+                                   const float* sat, float* out_rgba, uint64_t* out_shaded) {
+  EbsCtx c;
+  ebs_setup(c, p, vol_r16f, tf_rgbt, tf_n, sat);
   int r0 = p->row_begin, r1 = p->row_end > 0 ? p->row_end : p->height, rs = p->row_stride > 0 ? p->row_stride : 1;
   uint64_t total = 0, shaded = 0;
 #ifdef _OPENMP

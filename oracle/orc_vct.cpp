@@ -217,6 +217,30 @@ uint32_t shade_pixel(const VctCtx& c, int px, int py, float out[4], bool* hit) {
 
 }  // namespace
 
+// main() of rc1pvctsg/lightcachecomputation.comp: (Iao = 1, Ivd) per light-cache cell, stored RG16F.
+extern "C" void orc_vct_light_cache(const orc_vct_params* p, const float* const* levels, int n_levels, const float* lut, int lut_w, int lut_h,
+                                    const int dims[3], float* out_rg) {
+  VctCtx c; c.p = p;
+  for (int l = 0; l < n_levels; l++) { Mip m; level_dims(p->vol_w, p->vol_h, p->vol_d, l, m.w, m.h, m.d); m.data = levels[l]; c.mips.push_back(m); }
+  c.lut = lut; c.lut_w = lut_w; c.lut_h = lut_h;
+  c.sizes = vec3((float)p->vol_w, (float)p->vol_h, (float)p->vol_d) * vec3(p->voxel[0], p->voxel[1], p->voxel[2]);
+  const vec3 cell = vec3(p->voxel[0], p->voxel[1], p->voxel[2]) *
+                    (vec3((float)p->vol_w, (float)p->vol_h, (float)p->vol_d) / vec3((float)dims[0], (float)dims[1], (float)dims[2]));
+#ifdef _OPENMP
+  int nt = p->threads > 0 ? p->threads : omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 1) collapse(2) num_threads(nt)
+#endif
+  for (int z = 0; z < dims[2]; z++)
+    for (int y = 0; y < dims[1]; y++)
+      for (int x = 0; x < dims[0]; x++) {
+        vec3 tex_pos = (vec3((float)x, (float)y, (float)z) + vec3(0.5f)) * cell;
+        float Ivd = 1.0f;
+        if (p->apply_shadow == 1) Ivd = cone_tracing(c, tex_pos);
+        size_t i = (size_t)x + (size_t)dims[0] * ((size_t)y + (size_t)dims[1] * (size_t)z);
+        out_rg[2 * i] = 1.0f; out_rg[2 * i + 1] = round_f16(Ivd);
+      }
+}
+
 extern "C" uint64_t orc_vct_render(const orc_vct_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n,
                                    const float* const* levels, int n_levels, const float* lut, int lut_w, int lut_h, float* out_rgba) {
   VctCtx c; c.p = p;

@@ -81,6 +81,14 @@ class DosParams(C.Structure):
                 ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
 
 
+class ObjParams(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("vol_w", C.c_int), ("vol_h", C.c_int), ("vol_d", C.c_int),
+                ("voxel", C.c_float * 3), ("eye", C.c_float * 3), ("lookat", C.c_float * 9),
+                ("tan_fovy", C.c_float), ("aspect", C.c_float), ("step", C.c_float),
+                ("apply_occlusion", C.c_int), ("apply_shadow", C.c_int), ("ka", C.c_float), ("kd", C.c_float),
+                ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -118,6 +126,11 @@ def lib():
         L.orc_dos_extcoef_volume.argtypes = [_P, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, _P, C.c_float, _P]
         L.orc_dos_render.argtypes = [C.POINTER(DosParams), _P, _P, C.c_int, _P, C.c_int, _P, _P, _P, C.POINTER(C.c_uint64)]
         L.orc_dos_render.restype = C.c_uint64
+        L.orc_dos_light_cache.argtypes = [C.POINTER(DosParams), _P, C.c_int, _P, _P, _P, _P]
+        L.orc_vct_light_cache.argtypes = [C.POINTER(VctParams), _P, C.c_int, _P, C.c_int, C.c_int, _P, _P]
+        L.orc_ebs_light_cache.argtypes = [C.POINTER(EbsParams), _P, _P, _P]
+        L.orc_obj_render.argtypes = [C.POINTER(ObjParams), _P, _P, C.c_int, _P, _P, _P]
+        L.orc_obj_render.restype = C.c_uint64
         L.orc_gradient.argtypes = [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]
         L.orc_block_minmax.argtypes = [_P, C.c_int] + [C.c_int] * 6 + [_P, _P]
         L.orc_iso_render.argtypes = [C.POINTER(IsoParams), _P, _P, _P, _P, _P]
@@ -443,3 +456,53 @@ def gradient(voxels, model=1):
     out = np.zeros((d, h, w, 3), np.float32)
     lib().orc_gradient(_ptr(v), _DT[v.dtype], w, h, d, model, _ptr(out))
     return out
+
+
+# ---- light-cache ("object space") mode, row a23 -------------------------------------------------------------
+def _dims(res):
+    return (C.c_int * 3)(*[int(x) for x in res])
+
+
+def dos_light_cache(p, levels, occ, sdw, res=(32, 32, 32)):
+    """RG light cache [d, h, w, 2] of rc1pdosct/lightcachecomputation.comp (fp16-rounded)."""
+    lv = [np.ascontiguousarray(a, np.float32) for a in levels]
+    ptrs = (_P * len(lv))(*[_ptr(a) for a in lv])
+    ot = np.ascontiguousarray(occ.table, np.float32); st = np.ascontiguousarray(sdw.table, np.float32)
+    out = np.zeros((res[2], res[1], res[0], 2), np.float32)
+    lib().orc_dos_light_cache(C.byref(p), ptrs, len(lv), _ptr(ot), _ptr(st), _dims(res), _ptr(out))
+    return out
+
+
+def vct_light_cache(p, levels, lut, res=(32, 32, 32)):
+    lv = [np.ascontiguousarray(a, np.float32) for a in levels]
+    ptrs = (_P * len(lv))(*[_ptr(a) for a in lv])
+    l = np.ascontiguousarray(lut, np.float32)
+    out = np.zeros((res[2], res[1], res[0], 2), np.float32)
+    lib().orc_vct_light_cache(C.byref(p), ptrs, len(lv), _ptr(l), l.shape[1], l.shape[0], _dims(res), _ptr(out))
+    return out
+
+
+def ebs_light_cache(p, sat, res=(32, 32, 32)):
+    s = np.ascontiguousarray(sat, np.float32)
+    out = np.zeros((res[2], res[1], res[0], 2), np.float32)
+    lib().orc_ebs_light_cache(C.byref(p), _ptr(s), _dims(res), _ptr(out))
+    return out
+
+
+def obj_params(src):
+    """Object-space march parameters taken from a dos/vct/ebs parameter block (same camera, step, switches, ka/kd)."""
+    p = ObjParams()
+    for k in ("width", "height", "vol_w", "vol_h", "vol_d", "tan_fovy", "aspect", "step", "apply_occlusion", "apply_shadow", "ka", "kd",
+              "row_begin", "row_end", "row_stride", "threads"):
+        setattr(p, k, getattr(src, k))
+    p.voxel[:] = list(src.voxel); p.eye[:] = list(src.eye); p.lookat[:] = list(src.lookat)
+    return p
+
+
+def obj_render(p, vol_r16f, tf_rgbt, cache):
+    """main() of obj_ray_marching.comp over the light cache [d, h, w, 2]."""
+    vol = np.ascontiguousarray(vol_r16f, np.float32); tf = np.ascontiguousarray(tf_rgbt, np.float32)
+    c = np.ascontiguousarray(cache, np.float32)
+    out = np.zeros((p.height, p.width, 4), np.float32)
+    total = lib().orc_obj_render(C.byref(p), _ptr(vol), _ptr(tf), tf.shape[0], _ptr(c), _dims((c.shape[2], c.shape[1], c.shape[0])), _ptr(out))
+    return out, int(total)

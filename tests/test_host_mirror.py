@@ -97,6 +97,34 @@ def test_manager_session_equals_direct_abi_render(tmp_path, ctx, bonsai_table):
 
 
 @pytest.mark.gpu
+def test_light_cache_switch_of_the_plugins(tmp_path, ctx, bonsai_table):
+    """m_pre_illum_str_vol.SetActive(true) on the DOS / EBS / VCT plugins renders through the object-space mode of the device library."""
+    n, w, h = 48, 96, 80
+    vox = inputs.synth_volume(n, np.uint8)
+    v = inputs.write_raw(str(tmp_path), "synth", vox); t = inputs.write_tf1d(str(tmp_path / "bonsai_01.tf1d"))
+    eye = (float(n), float(n), 2.0 * n)
+    ctx.upload_volume(vox); ctx.upload_tf(bonsai_table)
+    cam = inputs.make_camera(eye, width=w, height=h)
+    try:
+        for name, kind, cls in [("dos", _capi.VRB_DOS_CONE, _capi.DosParams), ("ebs", _capi.VRB_EBS_SAT, _capi.EbsParams), ("vct", _capi.VRB_VCT, _capi.VctParams)]:
+            hostapi.session_light_cache(1, (16, 20, 24))
+            _, rgba, _, _ = hostapi.run_session(v, t, name, w, h, eye)
+            hostapi.session_light_cache(0)
+            _, plain, _, _ = hostapi.run_session(v, t, name, w, h, eye)
+            r = _capi.Renderer(ctx, kind)
+            r.init(w, h)
+            prm = r.get_params(cls()); prm.use_light_cache = 1; prm.light_cache_resolution[:] = (16, 20, 24); r.set_params(prm)
+            r.update(cam, inputs.default_light(256)); r.redraw()
+            direct = r.read_frame(_capi.VRB_FRAME_RGBA32F)
+            r.close()
+            assert np.array_equal(rgba, direct), name
+            assert not np.array_equal(rgba, plain), name
+            assert (rgba[..., 3] > 0).mean() > 0.05
+    finally:
+        hostapi.session_light_cache(-1)
+
+
+@pytest.mark.gpu
 def test_evaluation_writes_reference_csv_schema(tmp_path):
     vox = inputs.synth_volume(48, np.uint8)
     v = inputs.write_raw(str(tmp_path), "synth", vox); t = inputs.write_tf1d(str(tmp_path / "bonsai_01.tf1d"))

@@ -73,6 +73,17 @@ def main():
         line.update(extra)
         print(json.dumps(line), flush=True)
 
+    def emit_object_space(name, cfg, r, params_cls):
+        """Row a23: the same renderer in light-cache mode (cache pass + object-space march per frame)."""
+        for res in (32, 64):
+            prm = r.get_params(params_cls())
+            prm.use_light_cache = 1; prm.light_cache_resolution[:] = (res, res, res)
+            r.set_params(prm)
+            r.update(cam, light); r.redraw(); r.counters()
+            _, lc_ms = r.read_light_cache(want_data=False)
+            emit(f"{name}[light cache {res}^3]", cfg, r, params_cls, {"light_cache_ms": lc_ms, "note": "ms_per_frame = cache pass + object-space march"})
+        prm = r.get_params(params_cls()); prm.use_light_cache = 0; r.set_params(prm)
+
     def cpu_scale(t, total_rows_rendered):
         return t * h / total_rows_rendered
 
@@ -99,6 +110,8 @@ def main():
                 extra["cpu_oracle"] = {"frame_s_extrapolated": cpu_scale(time.perf_counter() - t0, len(range(*rows))), "rows": len(range(*rows)), "threads": O.lib().orc_max_threads(),
                                        "note": "ray caster only, pyramid taken from the GPU build"}
             emit("dos_cone" + ("+shadow" if shadow else ""), "C3", r, _capi.DosParams, extra)
+            if shadow:
+                emit_object_space("dos_cone+shadow", "C3", r, _capi.DosParams)
             r.close()
 
     if not only or "vct" in only:
@@ -108,6 +121,7 @@ def main():
         r.update(cam, light); r.redraw(); r.counters()
         lut, max_std, nl, build_ms = r.read_vct_lut()
         emit("vct", "C5 (512^3)", r, _capi.VctParams, {"precompute": {"supervoxel_pyramid_ms": build_ms, "levels": nl, "lut": list(lut.shape), "max_std": max_std, "init_wall_s": init_s}})
+        emit_object_space("vct", "C5 (512^3)", r, _capi.VctParams)
         r.close()
 
     if not only or "sbtm" in only:
@@ -128,6 +142,8 @@ def main():
             r.init(w, h)
             _, sat_ms = r.read_sat(want_data=False)
             emit("ebs_sat" + ("(scan)" if fast else "(exact)"), "C4", r, _capi.EbsParams, {"precompute": {"sat_ms": sat_ms, "builder": "separable_scan" if fast else "exact_wavefront"}})
+            if fast:
+                emit_object_space("ebs_sat", "C4", r, _capi.EbsParams)
             r.close()
 
     if not only or "iso" in only:
