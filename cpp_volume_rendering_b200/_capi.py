@@ -114,6 +114,7 @@ SIGNATURES = {
     "vrb_dos_read_extcoef": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
     "vrb_dos_read_sections": (C.c_int, [_P, C.c_int, _P, C.c_int, C.POINTER(C.c_int), _P, _P, C.POINTER(C.c_float)]),
     "vrb_light_cache_read": (C.c_int, [_P, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_float)]),
+    "vrb_renderer_set_bricks": (C.c_int, [_P, C.c_int, C.c_int, C.POINTER(C.c_int * 3)]),
     "vrb_sbtm_read_occlusion": (C.c_int, [_P, _P, C.POINTER(C.c_int)]),
     "vrb_vct_read_level": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int * 3)]),
     "vrb_vct_read_lut": (C.c_int, [_P, _P, C.POINTER(C.c_int * 2), C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
@@ -320,6 +321,11 @@ class Renderer:
             _check(lib().vrb_dos_read_extcoef(self._h, l, out.ctypes.data_as(_P), C.byref(dims), None, None))
             levels.append(out)
         return levels, ms.value
+
+    def set_bricks(self, rank, n_ranks, grid=None):
+        """Sort-last bricks (vrb_renderer_set_bricks); rank -1: all bricks on this renderer; n_ranks 0: off."""
+        g = (C.c_int * 3)(*[int(x) for x in grid]) if grid is not None else None
+        _check(lib().vrb_renderer_set_bricks(self._h, rank, n_ranks, C.byref(g) if g is not None else None))
 
     def read_light_cache(self, want_data=True):
         """(cache float32 [d, h, w, 2] or None, device ms of the cache pass) of the last Redraw with use_light_cache."""

@@ -11,6 +11,7 @@
 #include "vrb_internal.cuh"
 #include "vrb_ray.cuh"
 #include "vrb_lightcache.cuh"
+#include "vrb_sortlast.cuh"
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -559,6 +560,10 @@ class DosRenderer : public RendererImpl {
     s.type_of_shadow = prm_.type_of_shadow;
     s.spot_cos = std::cos(3.14159265358979323846f * prm_.spot_light_max_angle / 180.f);          // :158
     for (int i = 0; i < 3; i++) { s.light_fwd[i] = prm_.light_cam_forward[i]; s.light_up[i] = prm_.light_cam_up[i]; s.light_right[i] = prm_.light_cam_right[i]; }
+    if (brick_ranks > 0) {
+      VRB_REQUIRE(!prm_.use_light_cache, VRB_ERR_UNSUPPORTED, "sort-last bricks and the light-cache mode do not combine");
+      return redraw_sort_last<DosShader>(*this, a, s, prm_.count_samples != 0);
+    }
     if (prm_.use_light_cache) return redraw_object_space<DosShader>(*this, cache_, prm_.light_cache_resolution, a, s, prm_.count_samples != 0);
     return launch_march<DosShader>(*this, a, s, prm_.count_samples != 0);
   }

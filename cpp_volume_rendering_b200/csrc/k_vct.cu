@@ -217,6 +217,7 @@ int VctPyramid::ensure(vrb_ctx* ctx, bool with_lut) {
 
 // ---- K17 -------------------------------------------------------------------------------------------------
 #include "vrb_lightcache.cuh"
+#include "vrb_sortlast.cuh"
 
 namespace vrb {
 
@@ -383,6 +384,10 @@ class VctRenderer : public RendererImpl {
     s.corr_fact = (float)prm_.apply_correction_factor * prm_.opacity_correction_factor;
     s.vol_max_density = (float)pyr_.vol_max_density; s.vol_max_std = (float)pyr_.max_std;
     s.cone_samples = prm_.cone_number_of_samples;
+    if (brick_ranks > 0) {
+      VRB_REQUIRE(!prm_.use_light_cache, VRB_ERR_UNSUPPORTED, "sort-last bricks and the light-cache mode do not combine");
+      return redraw_sort_last<VctShader>(*this, a, s, prm_.count_samples != 0);
+    }
     if (prm_.use_light_cache) return redraw_object_space<VctShader>(*this, cache_, prm_.light_cache_resolution, a, s, prm_.count_samples != 0);
     return launch_march<VctShader>(*this, a, s, prm_.count_samples != 0);
   }

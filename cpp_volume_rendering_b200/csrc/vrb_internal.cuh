@@ -127,6 +127,22 @@ struct RendererImpl {
   void close_peers();
   void begin_frame();                    // advances frame_seq and selects the buffers (vrb_renderer_redraw)
   unsigned* flags() const { return (unsigned*)((char*)frame_base + 2 * frame_bytes); }
+  // Sort-last bricks (vrb_renderer_set_bricks, vrb_sortlast.cuh): the volume box is cut into brick_grid[0] x [1] x [2] bricks, one per
+  // rank.  Every rank marches, for ALL pixels, the lattice samples inside its brick; the premultiplied float32 partials go to the rank
+  // that owns the pixel's strip of rows (peer stores), which composites them front to back and stores the finished strip into every
+  // rank's frame.  Staging follows the flag words in the frame allocation: two buffers of [source brick][strip row][x] float4.
+  int brick_grid[3] = {0, 0, 0};
+  int brick_rank = 0, brick_ranks = 0;   // brick_ranks == 0: off; brick_rank == -1: this renderer marches every brick in turn (one GPU)
+  size_t staging_bytes = 0;              // one staging buffer
+  unsigned* d_done = nullptr;            // block counter of the composite kernel
+  // after the staging buffers: one float opacity plane [brick][y][x] per brick (opacity pre-pass, vrb_sortlast.cuh)
+  float* alpha_planes(const void* base) const { return (float*)((char*)staging(base, 2)); }
+  int strip_rows() const { return (height + brick_ranks - 1) / brick_ranks; }
+  float4* staging(const void* base, int buf) const {
+    return (float4*)((char*)base + 2 * frame_bytes + FRAME_FLAGS * sizeof(unsigned) + (size_t)buf * staging_bytes);
+  }
+  float* d_lattice = nullptr; int lattice_n = 0; float lattice_step = 0.f;
+  int ensure_lattice(float step);        // S[k] of the march for this step, long enough for the volume's diagonal
   unsigned long long* d_samples = nullptr;
   unsigned* d_queue = nullptr;          // 2 words, zero between launches: dynamic work queue of persistent kernels
   // This rank's partition tiles, centre of the image first: rays through the middle of the volume are the longest, so
@@ -197,6 +213,9 @@ int sbtm_read_occlusion(RendererImpl* impl, float* host, int* n_slices);
 int vct_read_level(RendererImpl* impl, int level, float* host_rg, int dims[3]);
 int vct_read_lut(RendererImpl* impl, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms);
 int iso_read_blocks(RendererImpl* impl, float* host_min, float* host_max);
+
+// vrb_renderer.cu: cuStreamWaitValue32(stream, addr, value, GEQ) through the runtime's driver entry point lookup
+int stream_wait_geq(cudaStream_t s, const unsigned* addr, unsigned value);
 
 // k_gradient.cu
 void release_gradient(Volume& v);

@@ -24,12 +24,24 @@ struct MarchArgs {
   PeerSignal sig;
   unsigned long long* samples;
   int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; const int* tile_order; unsigned* queue;
+  // sort-last bricks (vrb_sortlast.cuh): only lattice samples with brick_lo <= tx < brick_hi are marched; the premultiplied partial
+  // goes to slot brick_id of the staging buffer of the rank that owns the pixel's strip of strip_h rows
+  float brick_lo[3], brick_hi[3];
+  float4* stage[RendererImpl::MAX_PEERS + 1];
+  int brick_id, strip_h;
+  // opacity pre-pass (SL == 1): this brick's opacity of every pixel goes to plane brick_id of every rank; shaded pass (SL == 2): the
+  // planes of the n_front bricks in front of this one give the transparency the ray arrives with
+  float* alpha_out[RendererImpl::MAX_PEERS + 1]; int n_alpha_out;
+  const float* alpha_planes; int n_front, front[RendererImpl::MAX_PEERS + 1];
+  // S[k] = the march's s after k whole steps (s = s + Step accumulated in float32, the same for every ray): lets a brick start at
+  // the lattice sample in front of its entry point instead of walking there
+  const float* lattice; int lattice_n;
 };
 
 constexpr int MARCH_THREADS = 128;
 
 #ifdef __CUDACC__
-template <class S, bool COUNT>
+template <class S, bool COUNT, int SL = 0>
 __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __grid_constant__ MarchArgs a, const __grid_constant__ typename S::Args sa) {
   extern __shared__ uint4 s_dyn[];
   uint4* s_tf = s_dyn;
@@ -65,13 +77,45 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
     f3 dir; float tnear, tfar;
     const bool hit = ray_aabb(eye, cdir, mk3(-half.x, -half.y, -half.z), half, dir, tnear, tfar);
     float4 dst = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (hit) {
+    float t_front = 1.0f;                      // SL == 2: transparency accumulated by the bricks in front of this one
+    if (SL == 2) {
+      for (int f = 0; f < a.n_front; f++) t_front *= 1.0f - __ldg(a.alpha_planes + ((size_t)a.front[f] * a.height + py) * a.width + px);
+    }
+    if (hit && !(SL == 2 && 1.0f - t_front > 0.99f)) {   // the single march has stopped in front of this brick
       const float D = fabsf(__fsub_rn(tfar, tnear));
       const f3 wd = add3(add3(eye, scale3(dir, tnear)), half);
       const float tfn = (float)a.tf_n, tfmax = (float)(a.tf_n - 1);
-      for (float s = 0.0f; s < D;) {
+      bool entered = false;
+      float s0 = 0.0f;
+      if (SL) {
+        // distance at which the ray enters the brick's slabs (open faces and axes the ray runs parallel to do not bound it)
+        float t_in = 0.0f;
+        const float dd[3] = {dir.x, dir.y, dir.z}, ww[3] = {wd.x, wd.y, wd.z};
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+          const float bound = dd[i] > 0.0f ? a.brick_lo[i] : a.brick_hi[i];
+          if (fabsf(dd[i]) > 1e-12f && fabsf(bound) < 3.0e38f) t_in = fmaxf(t_in, (bound - ww[i]) / dd[i]);
+        }
+        int k = (int)fminf(fmaxf(floorf(t_in / a.step) - 2.0f, 0.0f), (float)(a.lattice_n - 1));
+        // S[k] is the reference's s only while every earlier step was a whole one: Step <= D - S[k - 1]
+        while (k > 0 && !(a.step <= __fsub_rn(D, __ldg(a.lattice + k - 1)))) k--;
+        s0 = __ldg(a.lattice + k);
+      }
+      for (float s = s0; s < D;) {
         const float h = gmin(a.step, __fsub_rn(D, s));
         const f3 tx = add3(wd, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));
+        if (SL) {
+          // every rank evaluates the same float32 lattice, so each sample belongs to exactly one brick; a brick is convex:
+          // once the ray has left it, it is done
+          const bool in = tx.x >= a.brick_lo[0] && tx.x < a.brick_hi[0] && tx.y >= a.brick_lo[1] && tx.y < a.brick_hi[1] &&
+                          tx.z >= a.brick_lo[2] && tx.z < a.brick_hi[2];
+          if (!in) {
+            if (entered) break;
+            s = __fadd_rn(s, h);
+            continue;
+          }
+          entered = true;
+        }
         const f3 p = mul3(tx, inv_sizes);
         if (COUNT) nsamp++;
         const float d_hw = tex3D<float>(a.vol, p.x, p.y, p.z);
@@ -85,7 +129,12 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
           const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&e.y));
           const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
           float4 src = make_float4(fmaf(w, r1.x - r0.x, r0.x), fmaf(w, r1.y - r0.y, r0.y), fmaf(w, b1.x - b0.x, b0.x), fmaf(w, b1.y - b0.y, b0.y));
-          if (src.w > 0.0f && (!S::OBJECT_SPACE || a.apply_occlusion || a.apply_shadow)) {   // obj_ray_marching.comp:312
+          if (SL == 1) {                       // opacity only: what the bricks behind need to know
+            if (src.w > 0.0f) {
+              dst.w += (1.0f - dst.w) * (1.0f - expf(-src.w * h));
+              if (dst.w > 0.99f) break;
+            }
+          } else if (src.w > 0.0f && (!S::OBJECT_SPACE || a.apply_occlusion || a.apply_shadow)) {   // obj_ray_marching.comp:312
             float ka = 0.0f, kd = 0.0f, Iocc = 0.0f, Isdw = 0.0f;
             if (a.apply_occlusion) ka = a.ka;
             if (a.apply_shadow) kd = a.kd;
@@ -97,11 +146,21 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
             const float alpha = 1.0f - expf(-src.w * h);
             const float wgt = (1.0f - dst.w) * alpha;
             dst.x = fmaf(wgt, src.x, dst.x); dst.y = fmaf(wgt, src.y, dst.y); dst.z = fmaf(wgt, src.z, dst.z); dst.w += wgt;
-            if (dst.w > 0.99f) break;
+            if (SL == 2) { if (1.0f - t_front * (1.0f - dst.w) > 0.99f) break; }   // the single march's accumulated opacity
+            else if (dst.w > 0.99f) break;
           }
         }
         s = __fadd_rn(s, h);
       }
+    }
+    if (SL == 1) {
+      for (int q = 0; q < a.n_alpha_out; q++) a.alpha_out[q][((size_t)a.brick_id * a.height + py) * a.width + px] = dst.w;
+      continue;
+    }
+    if (SL) {
+      const int owner = py / a.strip_h;
+      a.stage[owner][((size_t)a.brick_id * a.strip_h + (py - owner * a.strip_h)) * a.width + px] = dst;
+      continue;
     }
     const uint2 texel = make_uint2(pack_half2(dst.x, dst.y), pack_half2(dst.z, dst.w));
     const size_t o = (size_t)py * a.width + px;
@@ -150,11 +209,11 @@ inline bool fill_march_args(const RendererImpl& r, float step, int apply_occlusi
   return true;
 }
 
-template <class S, bool COUNT>
+template <class S, bool COUNT, int SL = 0>
 int launch_march_t(const RendererImpl& r, const MarchArgs& a, const typename S::Args& sa) {
   const size_t smem = (size_t)a.tf_n * sizeof(uint4) + (size_t)a.vis_words * sizeof(uint32_t);
   VRB_REQUIRE(smem <= 200 * 1024, VRB_ERR_UNSUPPORTED, "transfer function of %d entries does not fit shared memory", a.tf_n);
-  auto kern = shaded_march_kernel<S, COUNT>;
+  auto kern = shaded_march_kernel<S, COUNT, SL>;
   if (smem > 48 * 1024) VRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
   VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH_THREADS, smem));

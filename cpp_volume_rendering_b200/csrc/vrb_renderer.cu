@@ -6,6 +6,7 @@
 #include <utility>
 #include <vector>
 #include <cstring>
+#include <cmath>
 
 namespace vrb {
 
@@ -16,9 +17,14 @@ int RendererImpl::alloc_frame(int w, int h) {
   // RenderFrameToScreen::UpdateScreenResolution (renderoutputframe.cpp:64-87): RGBA16F W x H (two buffers + flags,
   // see RendererImpl::frame_base)
   frame_bytes = (size_t)w * h * 4 * sizeof(__half);
-  const size_t total = 2 * frame_bytes + FRAME_FLAGS * sizeof(unsigned);
+  staging_bytes = 0;
+  if (brick_ranks > 0) {   // per local owner: [source brick][strip row][x] float4
+    const size_t owners = brick_rank < 0 ? (size_t)brick_ranks : 1;
+    staging_bytes = owners * brick_ranks * (size_t)((h + brick_ranks - 1) / brick_ranks) * w * sizeof(float4);
+  }
+  const size_t total = 2 * frame_bytes + FRAME_FLAGS * sizeof(unsigned) + 2 * staging_bytes + (size_t)brick_ranks * w * h * sizeof(float);
   VRB_CUDA(cudaMalloc(&frame_base, total));
-  VRB_CUDA(cudaMemsetAsync(frame_base, 0, total, ctx->stream));
+  VRB_CUDA(cudaMemsetAsync(frame_base, 0, 2 * frame_bytes + FRAME_FLAGS * sizeof(unsigned), ctx->stream));
   frame = (__half*)frame_base;
   frame_seq = 0;
   width = w; height = h;
@@ -64,6 +70,25 @@ int LightCache::read(cudaStream_t s, float* host_rg, int out_dims[3], float* ms)
     VRB_CUDA(cudaMemcpy(tmp.data(), data, n * sizeof(__half2), cudaMemcpyDeviceToHost));
     for (size_t i = 0; i < n; i++) { const float2 f = __half22float2(tmp[i]); host_rg[2 * i] = f.x; host_rg[2 * i + 1] = f.y; }
   }
+  return VRB_OK;
+}
+
+int RendererImpl::ensure_lattice(float step) {
+  const Volume& v = ctx->vol;
+  const double sx = (double)v.w * v.sx, sy = (double)v.h * v.sy, sz = (double)v.d * v.sz;
+  const double need = std::sqrt(sx * sx + sy * sy + sz * sz) / (double)step + 8.0;
+  VRB_REQUIRE(step > 0.0f && need < (double)(1 << 24), VRB_ERR_INVALID, "march lattice of %.0f samples", need);
+  const int n = (int)need;
+  if (d_lattice && lattice_step == step && lattice_n >= n) return VRB_OK;
+  std::vector<float> S((size_t)n);
+  volatile float s = 0.0f;                 // one float32 rounding per step, as the shader's `s = s + h`
+  for (int k = 0; k < n; k++) { S[k] = s; s = s + step; }
+  if (d_lattice) cudaFree(d_lattice);
+  d_lattice = nullptr;
+  VRB_CUDA(cudaMalloc(&d_lattice, (size_t)n * sizeof(float)));
+  VRB_CUDA(cudaMemcpyAsync(d_lattice, S.data(), (size_t)n * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+  VRB_CUDA(cudaStreamSynchronize(ctx->stream));
+  lattice_n = n; lattice_step = step;
   return VRB_OK;
 }
 
@@ -136,6 +161,8 @@ int vrb_renderer_destroy(vrb_renderer* r) {
   p->clean();
   p->free_frame();
   if (p->d_samples) cudaFree(p->d_samples);
+  if (p->d_done) cudaFree(p->d_done);
+  if (p->d_lattice) cudaFree(p->d_lattice);
   if (p->d_queue) cudaFree(p->d_queue);
   if (p->d_tile_order) cudaFree(p->d_tile_order);
   if (p->ev0) cudaEventDestroy(p->ev0);
@@ -307,6 +334,38 @@ static stream_wait_value32_fn get_stream_wait_value32() {
   return fn;
 }
 
+}  // extern "C"
+namespace vrb {
+int stream_wait_geq(cudaStream_t s, const unsigned* addr, unsigned value) {
+  stream_wait_value32_fn wait = get_stream_wait_value32();
+  VRB_REQUIRE(wait, VRB_ERR_UNSUPPORTED, "cuStreamWaitValue32 is not available");
+  const int rc = wait(s, (unsigned long long)(uintptr_t)addr, value, 0x0u /* CU_STREAM_WAIT_VALUE_GEQ */);
+  VRB_REQUIRE(rc == 0, VRB_ERR_CUDA, "cuStreamWaitValue32 failed: %d", rc);
+  return VRB_OK;
+}
+}  // namespace vrb
+extern "C" {
+
+int vrb_renderer_set_bricks(vrb_renderer* r, int rank, int n_ranks, const int grid[3]) {
+  VRB_REQUIRE(r && r->impl, VRB_ERR_INVALID, "vrb_renderer_set_bricks: null renderer");
+  RendererImpl* p = r->impl;
+  VRB_REQUIRE(p->kind == VRB_VCT || p->kind == VRB_DOS_CONE, VRB_ERR_UNSUPPORTED, "vrb_renderer_set_bricks: renderer kind %d has no sort-last mode", p->kind);
+  VRB_REQUIRE(p->frame, VRB_ERR_INVALID, "vrb_renderer_set_bricks before Init");
+  VRB_CUDA(cudaStreamSynchronize(p->ctx->stream));
+  const int w = p->width, h = p->height;
+  if (n_ranks <= 0 || !grid) { p->brick_ranks = 0; p->brick_rank = 0; p->free_frame(); return p->alloc_frame(w, h); }
+  VRB_REQUIRE(grid[0] >= 1 && grid[1] >= 1 && grid[2] >= 1 && grid[0] * grid[1] * grid[2] == n_ranks && n_ranks <= RendererImpl::MAX_PEERS + 1,
+              VRB_ERR_INVALID, "vrb_renderer_set_bricks: grid %dx%dx%d does not make %d bricks (at most %d)", grid[0], grid[1], grid[2], n_ranks,
+              RendererImpl::MAX_PEERS + 1);
+  VRB_REQUIRE(rank >= -1 && rank < n_ranks, VRB_ERR_INVALID, "vrb_renderer_set_bricks: bad rank %d of %d", rank, n_ranks);
+  for (int i = 0; i < 3; i++) p->brick_grid[i] = grid[i];
+  p->brick_rank = rank; p->brick_ranks = n_ranks;
+  p->rank = 0; p->n_ranks = 1;                     // every rank marches all pixels
+  if (!p->d_done) { VRB_CUDA(cudaMalloc(&p->d_done, sizeof(unsigned))); VRB_CUDA(cudaMemset(p->d_done, 0, sizeof(unsigned))); }
+  p->free_frame();                                 // staging lives in the frame allocation: peers must re-export
+  return p->alloc_frame(w, h);
+}
+
 int vrb_renderer_wait_peers(vrb_renderer* r) {
   VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_wait_peers: null renderer");
   RendererImpl* p = r->impl;
@@ -314,6 +373,8 @@ int vrb_renderer_wait_peers(vrb_renderer* r) {
   if (p->gather_mode == VRB_GATHER_ROOT && p->rank != 0) return VRB_OK;      // only rank 0 collects
   stream_wait_value32_fn wait = get_stream_wait_value32();
   VRB_REQUIRE(wait, VRB_ERR_UNSUPPORTED, "vrb_renderer_wait_peers: cuStreamWaitValue32 is not available");
+  if (p->brick_ranks > 0)                       // sort-last: the finished strips of the other owners (vrb_sortlast.cuh)
+    return stream_wait_geq(p->ctx->stream, p->flags() + RendererImpl::FRAME_FLAGS - 2, p->frame_seq * (unsigned)(p->gather_ranks - 1));
   if (p->gather_mode == VRB_GATHER_ALL) {       // one arrival counter (see PeerSignal)
     const unsigned want = p->frame_seq * (unsigned)(p->gather_ranks - 1);
     const int rc = wait(p->ctx->stream, (unsigned long long)(uintptr_t)(p->flags() + RendererImpl::FRAME_FLAGS - 1), want, 0x0u /* GEQ */);

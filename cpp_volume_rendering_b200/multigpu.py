@@ -36,6 +36,33 @@ def setup_fused_gather(renderer, rank, world, tile=32, mode=_capi.VRB_GATHER_ROO
         dist.barrier(group=group)      # every rank has zeroed its flags before the first peer writes one
 
 
+def brick_grid(world):
+    """grid[0] x grid[1] x grid[2] = world, as cubic as the factorisation allows (8 -> 2x2x2, 4 -> 2x2x1, 2 -> 2x1x1)."""
+    g = [1, 1, 1]
+    n, f = world, 2
+    factors = []
+    while n > 1:
+        while n % f == 0:
+            factors.append(f); n //= f
+        f += 1
+    for x in sorted(factors, reverse=True):
+        g[g.index(min(g))] *= x
+    return tuple(sorted(g, reverse=True))
+
+
+def setup_sort_last(renderer, rank, world, grid=None, group=None):
+    """Sort-last bricks over `world` ranks (vrb_renderer_set_bricks): one brick per rank, partials exchanged and the finished strips
+    gathered through peer memory.  The frame is re-allocated with its staging area, so handles are exported afterwards."""
+    grid = tuple(grid) if grid is not None else brick_grid(world)
+    renderer.set_bricks(rank, world, grid)
+    if world > 1:
+        import torch.distributed as dist
+        handles = exchange_handles(renderer.frame_export(), group)
+        renderer.set_peers(handles, rank, _capi.VRB_GATHER_ALL)
+        dist.barrier(group=group)
+    return grid
+
+
 def frame_barrier(device=None, group=None):
     """All ranks' redraws have finished and their peer stores are visible: stream sync + a barrier."""
     import torch

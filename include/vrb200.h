@@ -299,6 +299,22 @@ int vrb_light_cache_read(vrb_renderer* r, float* host_rg, int dims[3], float* bu
  * The frame keeps full size; tiles of other ranks stay 0. */
 int vrb_renderer_set_partition(vrb_renderer* r, int rank, int n_ranks, int tile);
 
+/* Sort-last bricks (the ray-casting half of config C5; VRB_VCT and VRB_DOS_CONE renderers): the volume box is cut
+ * into grid[0] x grid[1] x grid[2] = n_ranks bricks at voxel boundaries, brick b = x + grid[0] * (y + grid[1] * z) belongs to rank b.
+ * A Redraw then (1) accumulates, for ALL pixels, the opacity of the lattice samples inside this rank's brick and stores that plane
+ * into every rank (peer stores); (2) with the planes of the bricks in front, marches and shades exactly the in-brick samples the
+ * single-GPU march would visit (the lattice is the single-GPU one, early ray termination uses the opacity the ray arrives with) and
+ * sends the premultiplied float32 partials to the rank that owns each pixel's strip of ceil(height / n_ranks) rows; (3) waits for
+ * the partials of its own strip, composites them front to back for the current eye and stores the finished RGBA16F strip into every
+ * rank's frame; vrb_renderer_wait_peers then waits for the other strips.
+ * Call order: Init, set_bricks (re-allocates the frame with its staging area: previously exported handles die), frame_export,
+ * set_peers(..., VRB_GATHER_ALL), then Update / Redraw / wait_peers per frame.
+ * rank = -1: this one renderer marches every brick in turn and composites all strips (single-GPU form, no peers).
+ * n_ranks = 0 (grid may be NULL): back to the unpartitioned renderer.
+ * The frame equals the single-GPU frame up to the blending order of the partials (same samples, same termination).  The shading
+ * pyramids / tables and, in this version, the classification volume stay replicated on every rank. */
+int vrb_renderer_set_bricks(vrb_renderer* r, int rank, int n_ranks, const int grid[3]);
+
 /* Fused gather: instead of a collective after the launch, the render kernels store every finished pixel into the
  * frames of other ranks as well (peer memory over NVLink / NVSwitch, mapped through CUDA IPC; one process per GPU).
  * vrb_renderer_frame_export writes this renderer's 64-byte IPC handle; the host exchanges the handles of all ranks

@@ -128,3 +128,70 @@ def test_fused_gather_two_ranks_one_gpu(ctx, bonsai_table, mode):
         else:                                        # rank 1 keeps only its own tiles
             mine = owner == 1
             assert np.array_equal(res[1][kind][mine], full[kind][mine]) and np.all(res[1][kind][~mine] == 0)
+
+
+def _sort_last_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from cpp_volume_rendering_b200 import _capi, inputs, multigpu
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    n, w, h = 48, 120, 90
+    vox = inputs.synth_volume(n, np.uint8)
+    table = inputs.tf_build_linear(inputs.bonsai_tf())
+    cam = inputs.default_camera(n, w, h)
+    light = inputs.default_light(n)
+    with _capi.Context(0) as ctx:                    # both ranks share the one GPU of the test box
+        ctx.upload_volume(vox)
+        ctx.upload_tf(table)
+        r = _capi.Renderer(ctx, _capi.VRB_VCT)
+        r.init(w, h)
+        multigpu.setup_sort_last(r, rank, world, (1, 2, 1))
+        r.update(cam, light)
+        for _ in range(3):
+            # Redraw = opacity pre-pass -> stream wait for the other brick's plane -> brick march -> stream wait for the other
+            # brick's partials -> composite of the own strip.  The waits are semaphore acquires of the stream, not spinning
+            # kernels: the other process's launches run meanwhile.
+            r.redraw()
+            ctx.synchronize()
+            dist.barrier()
+            r.wait_peers()                           # the other rank's finished strip
+        out = r.read_frame(_capi.VRB_FRAME_RGBA32F)
+        dist.barrier()
+        r.set_peers([], rank, _capi.VRB_GATHER_NONE)
+        dist.barrier()
+        r.close()
+    q.put((rank, out))
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_sort_last_two_ranks_one_gpu(ctx, bonsai_table):
+    """Two processes, one brick each, partials and finished strips exchanged through peer memory: both end up with the frame the
+    single-GPU brick-by-brick form renders (bit-identical: same partials, same compositing order)."""
+    import torch.multiprocessing as mp
+    from cpp_volume_rendering_b200 import _capi, inputs
+    n, w, h = 48, 120, 90
+    vox = inputs.synth_volume(n, np.uint8)
+    ctx.upload_volume(vox); ctx.upload_tf(bonsai_table)
+    r = _capi.Renderer(ctx, _capi.VRB_VCT); r.init(w, h)
+    r.update(inputs.default_camera(n, w, h), inputs.default_light(n)); r.redraw()
+    plain = r.read_frame(_capi.VRB_FRAME_RGBA32F)
+    r.set_bricks(-1, 2, (1, 2, 1)); r.redraw()
+    local = r.read_frame(_capi.VRB_FRAME_RGBA32F); r.close()
+    mpc = mp.get_context("spawn")
+    q = mpc.Queue()
+    port = _free_port()
+    procs = [mpc.Process(target=_sort_last_worker, args=(rk, 2, port, q)) for rk in range(2)]
+    for p in procs:
+        p.start()
+    try:
+        res = dict(q.get(timeout=100) for _ in range(2))
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+    finally:
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+    assert np.array_equal(res[0], local) and np.array_equal(res[1], local)
+    assert np.abs(local - plain).max() <= 2.0 ** -9 and (local[..., 3] > 0).mean() > 0.05
