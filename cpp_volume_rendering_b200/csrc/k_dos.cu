@@ -321,8 +321,12 @@ struct DosShader {
     float light_fwd[3], light_up[3], light_right[3];
   };
   struct Const { f3 sizes, eye; };
+  static __device__ __forceinline__ void prepare_block(const MarchArgs&, const Args&) {}
   static __device__ __forceinline__ Const prepare(const MarchArgs& a, const Args&) {
     Const c; c.sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]); c.eye = mk3(a.eye[0], a.eye[1], a.eye[2]); return c;
+  }
+  static __device__ __forceinline__ void shade_warp(const MarchArgs& a, const Args& s, const Const& c, bool need, f3 tx, f3 cd, float& Iocc, float& Isdw) {
+    if (need) shade(a, s, c, tx, cd, Iocc, Isdw);
   }
   static __device__ __forceinline__ f3 cross_rn(f3 a, f3 b) {
     return mk3(__fsub_rn(__fmul_rn(a.y, b.z), __fmul_rn(b.y, a.z)), __fsub_rn(__fmul_rn(a.z, b.x), __fmul_rn(b.z, a.x)),

@@ -221,6 +221,11 @@ int VctPyramid::ensure(vrb_ctx* ctx, bool with_lut) {
 
 namespace vrb {
 
+// Per-CTA table of the cone's step geometry: xl, mip level and opacity exponent of step i depend only on the renderer parameters
+// (vct_ray_bbox_marching.comp:108-141: apex += step; step *= rate), not on the sample, so each CTA runs the recurrence once.
+constexpr int VCT_CONE_TABLE = 256;
+__shared__ float s_vct_cone[3][VCT_CONE_TABLE];
+
 struct VctShader {
   static constexpr bool OBJECT_SPACE = false;
   struct Args {
@@ -233,6 +238,19 @@ struct VctShader {
   };
   struct Const { f3 sizes; };
   static __device__ __forceinline__ Const prepare(const MarchArgs& a, const Args&) { Const c; c.sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]); return c; }
+  static __device__ __forceinline__ void prepare_block(const MarchArgs&, const Args& s) {
+    if (threadIdx.x == 0) {
+      float apex = s.cone_initial, step = s.cone_step;
+      for (int is = 0; is < min(s.cone_samples, VCT_CONE_TABLE); is++) {
+        const float xl = __fadd_rn(apex, __fmul_rn(step, 0.5f));
+        s_vct_cone[0][is] = xl;
+        s_vct_cone[1][is] = log2f(__fdiv_rn(__fmul_rn(__fmul_rn(2.0f, xl), s.tan_apex), 1.0f));
+        s_vct_cone[2][is] = __fmul_rn(step, s.corr_fact);
+        apex = __fadd_rn(apex, step);
+        step = __fmul_rn(step, s.cone_rate);
+      }
+    }
+  }
 
   // texture(sampler3D RG16F, p) on one level: GL_LINEAR / CLAMP_TO_EDGE, float32 weights (oracle sample_level)
   static __device__ __forceinline__ float2 sample_level(const Args& s, int l, f3 p) {
@@ -293,6 +311,37 @@ struct VctShader {
       step = __fmul_rn(step, s.cone_rate);
     }
     Isdw = Tvd;
+  }
+  // The same, with the cone of one sample spread over the warp: the steps of a cone are independent fetches (only the product of the
+  // transmittances chains them), so for every lane that has a sample to shade the 32 lanes take steps lane, lane + 32, ... and
+  // multiply their factors together.  A sample costs ceil(n / 32) dependent fetch rounds instead of n, and lanes without a visible
+  // sample work instead of idling.  Leaving the volume: the steps lie on a ray, so "this step is outside" equals the shader's break.
+  static __device__ void shade_warp(const MarchArgs& a, const Args& s, const Const& c, bool need, f3 tx, f3 cd, float& Iocc, float& Isdw) {
+    Iocc = 1.0f; Isdw = 0.0f;
+    if (!a.apply_shadow) return;
+    if (s.cone_samples > VCT_CONE_TABLE) { if (need) shade(a, s, c, tx, cd, Iocc, Isdw); return; }
+    const int lane = threadIdx.x & 31;
+    unsigned m = __ballot_sync(0xffffffffu, need);
+    while (m) {
+      const int src = __ffs(m) - 1;
+      m &= m - 1;
+      const f3 p = mk3(__shfl_sync(0xffffffffu, tx.x, src), __shfl_sync(0xffffffffu, tx.y, src), __shfl_sync(0xffffffffu, tx.z, src));
+      const f3 realpos = sub3(p, scale3(c.sizes, 0.5f));
+      const f3 cone = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), realpos));
+      float T = 1.0f;
+      for (int is = lane; is < s.cone_samples; is += 32) {
+        const float xl = s_vct_cone[0][is];
+        const f3 wpos = add3(p, scale3(cone, xl));
+        if (wpos.x < 0.0f || wpos.x > c.sizes.x || wpos.y < 0.0f || wpos.y > c.sizes.y || wpos.z < 0.0f || wpos.z > c.sizes.z) continue;
+        const float2 g = texture_lod(s, div3(wpos, c.sizes), s_vct_cone[1][is]);
+        float opacity = lut_fetch(s, __fdiv_rn(__fadd_rn(g.x, 0.5f), s.vol_max_density), __fdiv_rn(__fadd_rn(g.y, 0.5f), s.vol_max_std));
+        opacity = 1.0f - powf(1.0f - opacity, s_vct_cone[2][is]);
+        T *= (1.0f - opacity);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) T *= __shfl_xor_sync(0xffffffffu, T, o);
+      if (lane == src) Isdw = T;
+    }
   }
   // main() of rc1pvctsg/lightcachecomputation.comp: Iao stays 1, Ivd = EvaluationVoxelConeTracing at the cell centre
   static __device__ void shade_cell(const MarchArgs& a, const Args& s, const Const& c, f3 tx, float&, float& Isdw) {

@@ -16,7 +16,11 @@ struct LightCacheShader {
   static constexpr bool OBJECT_SPACE = true;
   struct Args { const __half2* cache; int dims[3]; };
   struct Const { f3 sizes; };
+  static __device__ __forceinline__ void prepare_block(const MarchArgs&, const Args&) {}
   static __device__ __forceinline__ Const prepare(const MarchArgs& a, const Args&) { Const c; c.sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]); return c; }
+  static __device__ __forceinline__ void shade_warp(const MarchArgs& a, const Args& s, const Const& c, bool need, f3 tx, f3 cd, float& Iocc, float& Isdw) {
+    if (need) shade(a, s, c, tx, cd, Iocc, Isdw);
+  }
   struct Foot { int i0, i1; float w; };
   static __device__ __forceinline__ Foot foot(float p, int n) {
     const float t = __fsub_rn(__fmul_rn(p, (float)n), 0.5f);

@@ -2,8 +2,10 @@
 // vct_ray_bbox_marching.comp:191-264 and crtgt_ray_bbox_marching.comp — ray setup, half-step sampling, classification,
 // `k*(c*Iocc*ka + c*Isdw*kd)` shading, exp() opacity, ERT at 0.99 — around a per-renderer shading functor.
 //   struct Shader { static constexpr bool OBJECT_SPACE; struct Args {...}; struct Const {...};
+//     static __device__ void  prepare_block(const MarchArgs&, const Args&);   // all threads, before the CTA barrier: shared tables
 //     static __device__ Const prepare(const MarchArgs&, const Args&);
-//     static __device__ void shade(const MarchArgs&, const Args&, const Const&, f3 tx, f3 camera_dir, float& Iocc, float& Isdw); };
+//     // called by all 32 lanes of the converged warp; lanes with need == true get their sample at tx shaded
+//     static __device__ void shade_warp(const MarchArgs&, const Args&, const Const&, bool need, f3 tx, f3 camera_dir, float& Iocc, float& Isdw); };
 // Same persistent warp-queue schedule as k_ebs.cu (8x4-pixel warp items, scrambled order, self-resetting counter).
 #pragma once
 #include "vrb_internal.cuh"
@@ -51,6 +53,7 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
     s_tf[i] = make_uint4(t0.x, t0.y, t1.x, t1.y);
   }
   for (int i = threadIdx.x; i < a.vis_words; i += blockDim.x) s_mask[i] = a.vis_mask[i];
+  S::prepare_block(a, sa);                     // per-CTA tables of the shader (static shared memory)
   __syncthreads();
   const typename S::Const sc = S::prepare(a, sa);
   const f3 sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]);
@@ -58,6 +61,7 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
   const f3 inv_sizes = div3(mk3(1.0f, 1.0f, 1.0f), sizes);
   const int lane = threadIdx.x & 31;
   const int per_tile_x = a.tile / 8, per_tile = per_tile_x * (a.tile / 4);
+  const float tfn = (float)a.tf_n, tfmax = (float)(a.tf_n - 1);
   unsigned nsamp = 0;
   for (;;) {
     int raw = 0;
@@ -70,7 +74,7 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
     const int tx_ = tile_id % a.tiles_x, ty_ = tile_id / a.tiles_x;
     const int lx = ((lane >> 2) & 3) * 2 + (lane & 1), ly = (lane >> 4) * 2 + ((lane >> 1) & 1);
     const int px = tx_ * a.tile + (sub % per_tile_x) * 8 + lx, py = ty_ * a.tile + (sub / per_tile_x) * 4 + ly;
-    if (px >= a.width || py >= a.height) continue;
+    const bool in_image = px < a.width && py < a.height;
     const f3 eye = mk3(a.eye[0], a.eye[1], a.eye[2]);
     const f3 cdir = camera_ray_dir(px, py, a.width, a.height, a.tan_fovy, a.aspect, a.lookat);
     const f3 half = scale3(sizes, 0.5f);
@@ -78,81 +82,94 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
     const bool hit = ray_aabb(eye, cdir, mk3(-half.x, -half.y, -half.z), half, dir, tnear, tfar);
     float4 dst = make_float4(0.f, 0.f, 0.f, 0.f);
     float t_front = 1.0f;                      // SL == 2: transparency accumulated by the bricks in front of this one
-    if (SL == 2) {
+    if (SL == 2 && in_image) {
       for (int f = 0; f < a.n_front; f++) t_front *= 1.0f - __ldg(a.alpha_planes + ((size_t)a.front[f] * a.height + py) * a.width + px);
     }
-    if (hit && !(SL == 2 && 1.0f - t_front > 0.99f)) {   // the single march has stopped in front of this brick
-      const float D = fabsf(__fsub_rn(tfar, tnear));
-      const f3 wd = add3(add3(eye, scale3(dir, tnear)), half);
-      const float tfn = (float)a.tf_n, tfmax = (float)(a.tf_n - 1);
-      bool entered = false;
-      float s0 = 0.0f;
-      if (SL) {
-        // distance at which the ray enters the brick's slabs (open faces and axes the ray runs parallel to do not bound it)
-        float t_in = 0.0f;
-        const float dd[3] = {dir.x, dir.y, dir.z}, ww[3] = {wd.x, wd.y, wd.z};
+    // The warp walks its 32 rays in lockstep, one lattice sample per lane and iteration, and stays converged so that the shader
+    // may spread the shading of a sample over all lanes (S::shade_warp); a lane whose ray has ended idles until the last one has.
+    bool alive = in_image && hit && !(SL == 2 && 1.0f - t_front > 0.99f);   // else the single march has stopped in front of this brick
+    const float D = fabsf(__fsub_rn(tfar, tnear));
+    const f3 wd = add3(add3(eye, scale3(dir, tnear)), half);
+    bool entered = false;
+    float s = 0.0f;
+    if (SL && alive) {
+      // distance at which the ray enters the brick's slabs (open faces and axes the ray runs parallel to do not bound it)
+      float t_in = 0.0f;
+      const float dd[3] = {dir.x, dir.y, dir.z}, ww[3] = {wd.x, wd.y, wd.z};
 #pragma unroll
-        for (int i = 0; i < 3; i++) {
-          const float bound = dd[i] > 0.0f ? a.brick_lo[i] : a.brick_hi[i];
-          if (fabsf(dd[i]) > 1e-12f && fabsf(bound) < 3.0e38f) t_in = fmaxf(t_in, (bound - ww[i]) / dd[i]);
-        }
-        int k = (int)fminf(fmaxf(floorf(t_in / a.step) - 2.0f, 0.0f), (float)(a.lattice_n - 1));
-        // S[k] is the reference's s only while every earlier step was a whole one: Step <= D - S[k - 1]
-        while (k > 0 && !(a.step <= __fsub_rn(D, __ldg(a.lattice + k - 1)))) k--;
-        s0 = __ldg(a.lattice + k);
+      for (int i = 0; i < 3; i++) {
+        const float bound = dd[i] > 0.0f ? a.brick_lo[i] : a.brick_hi[i];
+        if (fabsf(dd[i]) > 1e-12f && fabsf(bound) < 3.0e38f) t_in = fmaxf(t_in, (bound - ww[i]) / dd[i]);
       }
-      for (float s = s0; s < D;) {
-        const float h = gmin(a.step, __fsub_rn(D, s));
-        const f3 tx = add3(wd, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));
+      int k = (int)fminf(fmaxf(floorf(t_in / a.step) - 2.0f, 0.0f), (float)(a.lattice_n - 1));
+      // S[k] is the reference's s only while every earlier step was a whole one: Step <= D - S[k - 1]
+      while (k > 0 && !(a.step <= __fsub_rn(D, __ldg(a.lattice + k - 1)))) k--;
+      s = __ldg(a.lattice + k);
+    }
+    while (__any_sync(0xffffffffu, alive)) {
+      bool need = false;                       // this lane has a sample to shade in this iteration
+      float h = 0.0f;
+      f3 tx = mk3(0.f, 0.f, 0.f);
+      float4 src = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (alive && !(s < D)) alive = false;
+      if (alive) {
+        h = gmin(a.step, __fsub_rn(D, s));
+        tx = add3(wd, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));
+        bool inside = true;
         if (SL) {
           // every rank evaluates the same float32 lattice, so each sample belongs to exactly one brick; a brick is convex:
           // once the ray has left it, it is done
-          const bool in = tx.x >= a.brick_lo[0] && tx.x < a.brick_hi[0] && tx.y >= a.brick_lo[1] && tx.y < a.brick_hi[1] &&
-                          tx.z >= a.brick_lo[2] && tx.z < a.brick_hi[2];
-          if (!in) {
-            if (entered) break;
-            s = __fadd_rn(s, h);
-            continue;
-          }
-          entered = true;
+          inside = tx.x >= a.brick_lo[0] && tx.x < a.brick_hi[0] && tx.y >= a.brick_lo[1] && tx.y < a.brick_hi[1] &&
+                   tx.z >= a.brick_lo[2] && tx.z < a.brick_hi[2];
+          if (!inside && entered) alive = false;
+          entered = entered || inside;
         }
-        const f3 p = mul3(tx, inv_sizes);
-        if (COUNT) nsamp++;
-        const float d_hw = tex3D<float>(a.vol, p.x, p.y, p.z);
-        int j = (int)fminf(fmaxf(fmaf(d_hw, tfn, -0.5f), 0.0f), tfmax);
-        if ((s_mask[j >> 5] >> (j & 31)) & 1u) {
-          const float density = tex3d_f32_exact(a.vol_quad, p, res);
-          const float u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
-          j = (int)u;
-          const float w = u - (float)j;
-          const uint4 e = s_tf[j];
-          const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&e.y));
-          const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
-          float4 src = make_float4(fmaf(w, r1.x - r0.x, r0.x), fmaf(w, r1.y - r0.y, r0.y), fmaf(w, b1.x - b0.x, b0.x), fmaf(w, b1.y - b0.y, b0.y));
-          if (SL == 1) {                       // opacity only: what the bricks behind need to know
-            if (src.w > 0.0f) {
-              dst.w += (1.0f - dst.w) * (1.0f - expf(-src.w * h));
-              if (dst.w > 0.99f) break;
+        if (alive && inside) {
+          const f3 p = mul3(tx, inv_sizes);
+          if (COUNT) nsamp++;
+          const float d_hw = tex3D<float>(a.vol, p.x, p.y, p.z);
+          int j = (int)fminf(fmaxf(fmaf(d_hw, tfn, -0.5f), 0.0f), tfmax);
+          if ((s_mask[j >> 5] >> (j & 31)) & 1u) {
+            const float density = tex3d_f32_exact(a.vol_quad, p, res);
+            const float u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
+            j = (int)u;
+            const float w = u - (float)j;
+            const uint4 e = s_tf[j];
+            const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&e.y));
+            const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
+            src = make_float4(fmaf(w, r1.x - r0.x, r0.x), fmaf(w, r1.y - r0.y, r0.y), fmaf(w, b1.x - b0.x, b0.x), fmaf(w, b1.y - b0.y, b0.y));
+            if (SL == 1) {                     // opacity only: what the bricks behind need to know
+              if (src.w > 0.0f) {
+                dst.w += (1.0f - dst.w) * (1.0f - expf(-src.w * h));
+                if (dst.w > 0.99f) alive = false;
+              }
+            } else {
+              need = src.w > 0.0f && (!S::OBJECT_SPACE || a.apply_occlusion || a.apply_shadow);   // obj_ray_marching.comp:312
             }
-          } else if (src.w > 0.0f && (!S::OBJECT_SPACE || a.apply_occlusion || a.apply_shadow)) {   // obj_ray_marching.comp:312
-            float ka = 0.0f, kd = 0.0f, Iocc = 0.0f, Isdw = 0.0f;
-            if (a.apply_occlusion) ka = a.ka;
-            if (a.apply_shadow) kd = a.kd;
-            S::shade(a, sa, sc, tx, cdir, Iocc, Isdw);
-            const float k = 1.0f / (ka + kd);
-            src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
-            src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
-            src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
-            const float alpha = 1.0f - expf(-src.w * h);
-            const float wgt = (1.0f - dst.w) * alpha;
-            dst.x = fmaf(wgt, src.x, dst.x); dst.y = fmaf(wgt, src.y, dst.y); dst.z = fmaf(wgt, src.z, dst.z); dst.w += wgt;
-            if (SL == 2) { if (1.0f - t_front * (1.0f - dst.w) > 0.99f) break; }   // the single march's accumulated opacity
-            else if (dst.w > 0.99f) break;
           }
         }
-        s = __fadd_rn(s, h);
       }
+      if (SL != 1) {
+        float Iocc = 0.0f, Isdw = 0.0f;
+        S::shade_warp(a, sa, sc, need, tx, cdir, Iocc, Isdw);
+        if (need) {
+          float ka = 0.0f, kd = 0.0f;
+          if (a.apply_occlusion) ka = a.ka;
+          if (a.apply_shadow) kd = a.kd;
+          const float k = 1.0f / (ka + kd);
+          src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
+          src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
+          src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
+          const float alpha = 1.0f - expf(-src.w * h);
+          const float wgt = (1.0f - dst.w) * alpha;
+          dst.x = fmaf(wgt, src.x, dst.x); dst.y = fmaf(wgt, src.y, dst.y); dst.z = fmaf(wgt, src.z, dst.z); dst.w += wgt;
+          if (SL == 2) { if (1.0f - t_front * (1.0f - dst.w) > 0.99f) alive = false; }   // the single march's accumulated opacity
+          else if (dst.w > 0.99f) alive = false;
+        }
+      }
+      if (alive) s = __fadd_rn(s, h);
     }
+    if (!in_image) continue;
     if (SL == 1) {
       for (int q = 0; q < a.n_alpha_out; q++) a.alpha_out[q][((size_t)a.brick_id * a.height + py) * a.width + px] = dst.w;
       continue;
