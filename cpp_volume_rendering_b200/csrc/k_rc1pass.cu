@@ -51,14 +51,27 @@ constexpr int WARP_W = 8, WARP_H = 4, CTA_THREADS = 128;
 #define VRB_RC1_QUAD2X2 1
 #endif
 #ifndef VRB_RC1_MINB
-#define VRB_RC1_MINB 6      // resident CTAs per SM the register allocation is capped for (6 -> 80 registers: the
-                            // fast empty-space loop then keeps the ray state in registers; measured on B200 for the
-                            // C2 frame: 0.586 ms against 0.604 ms (cap 64, spills) and 0.611 ms (cap 128))
+#define VRB_RC1_MINB 5      // resident CTAs per SM the register allocation is capped for.  5 -> 96 registers, no spills in
+                            // the pipelined march; measured on B200 for the C2 frame (L2 flushed, tools/partition_sweep.py):
+                            // 0.503 ms (6 CTAs, 80 registers, 12 B spilled), 0.449 ms (5 CTAs), 0.452 ms (4 CTAs, 128 registers)
 #endif
 #ifndef VRB_RC1_UNROLL
 #define VRB_RC1_UNROLL 4
 #endif
-constexpr int UNROLL = VRB_RC1_UNROLL;    // independent texture fetches in flight per ray
+constexpr int UNROLL = VRB_RC1_UNROLL;    // independent texture fetches in flight per ray and group
+#ifndef VRB_RC1_PIPE
+#define VRB_RC1_PIPE 1      // groups fetched ahead of the one being composited (software pipeline depth)
+#endif
+constexpr int PIPE = VRB_RC1_PIPE;
+#ifndef VRB_RC1_BF
+#define VRB_RC1_BF 1        // branch-free compositing of a group (see process_group)
+#endif
+#ifndef VRB_SPLIT_PIPE
+#define VRB_SPLIT_PIPE 0
+#endif
+#ifndef VRB_SPLIT_MINB
+#define VRB_SPLIT_MINB 4
+#endif
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
@@ -190,6 +203,52 @@ __device__ __forceinline__ void process_group(const Rc1Args& a, const uint4* s_t
       q1[k] = tex3D<uint2>(a.vol_quad, f.x0 + 0.5f, f.y0 + 0.5f, f.z0 + 1.5f);
     }
   }
+#if VRB_RC1_BF
+  // Branch-free: filter, transfer function and alpha of all slots first (independent of each other, so their latencies
+  // overlap), then the short sequential blend.  A slot that is past the end of the ray, provably transparent or behind
+  // the terminating sample contributes wgt = 0, which leaves dst bit for bit unchanged — the same values as the
+  // branching loop of ray_marching_1p.comp:136-168.
+  float4 sk[UNROLL]; float ak[UNROLL];
+#pragma unroll
+  for (int k = 0; k < UNROLL; k++) {
+    const bool on = (FULL || hk[k] > 0.0f) && vis[k];
+    const float density = on ? (EXACT ? quad_lerp(a, r, tk[k], q0[k], q1[k]) : dk[k]) : 0.0f;
+    float4 src;
+    if (TF_SMEM) {
+      const float u = tf_coord(a, density);
+      const int j = (int)u;
+      const float w = u - (float)j;
+      const uint4 e = s_tf[j];
+      const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x));
+      const float2 b0 = __half22float2(*reinterpret_cast<const __half2*>(&e.y));
+      const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z));
+      const float2 b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
+      src.x = fmaf(w, r1.x - r0.x, r0.x); src.y = fmaf(w, r1.y - r0.y, r0.y);
+      src.z = fmaf(w, b1.x - b0.x, b0.x); src.w = fmaf(w, b1.y - b0.y, b0.y);
+    } else {
+      src = tex1D<float4>(a.tf, density);
+    }
+    const bool pos = on && src.w > 0.0f;
+    if (GRAD) {
+      if (pos && !r.done) {
+        const float3 c = shade_blinn_phong(a, fmaf(r.dux, tk[k], r.ux0), fmaf(r.duy, tk[k], r.uy0), fmaf(r.duz, tk[k], r.uz0), make_float3(src.x, src.y, src.z));
+        src.x = c.x; src.y = c.y; src.z = c.z;
+      }
+    }
+    ak[k] = pos ? 1.0f - ex2_approx(src.w * hk[k] * -1.4426950408889634f) : 0.0f;
+    sk[k] = src;
+  }
+#pragma unroll
+  for (int k = 0; k < UNROLL; k++) {
+    if (COUNT) nsamp += (!r.done && (FULL || hk[k] > 0.0f)) ? 1u : 0u;
+    const float wgt = r.done ? 0.0f : (1.0f - r.dst.w) * ak[k];
+    r.dst.x = fmaf(wgt, sk[k].x, r.dst.x);
+    r.dst.y = fmaf(wgt, sk[k].y, r.dst.y);
+    r.dst.z = fmaf(wgt, sk[k].z, r.dst.z);
+    r.dst.w += wgt;
+    r.done = r.done || r.dst.w > 0.99f;
+  }
+#else
 #pragma unroll
   for (int k = 0; k < UNROLL; k++) {
     if (r.done || !(FULL || hk[k] > 0.0f)) continue;       // (no break: keeps the slot arrays in registers)
@@ -198,6 +257,7 @@ __device__ __forceinline__ void process_group(const Rc1Args& a, const uint4* s_t
     const float density = EXACT ? quad_lerp(a, r, tk[k], q0[k], q1[k]) : dk[k];
     composite<TF_SMEM, GRAD>(a, s_tf, r, density, tf_coord(a, density), hk[k], tk[k]);
   }
+#endif
 }
 
 template <bool COUNT, bool TF_SMEM, bool EXACT, bool FULL, bool GRAD = false>
@@ -305,25 +365,37 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(cons
       // in flight and the per-ray dependent chain is one texture round trip per group instead of up to two.  Only the
       // group start s and the UNROLL fetched densities are carried; sample positions are recomputed from s.
       float s = 0.0f;
-      float hk[UNROLL], tk[UNROLL], dkc[UNROLL];
+      float hk[UNROLL], tk[UNROLL];
 #pragma unroll
       for (int k = 0; k < UNROLL; k++) hk[k] = step;
-      float s_end = 0.0f;
-      bool fc = full_geom(s, D, step, tk, s_end);
-      if (fc) fetch_group(a, r, tk, dkc);
-      while (fc && !r.done) {
-        float tkn[UNROLL], dkn[UNROLL];
-        float s_end_n = s_end;
-        const bool fn = full_geom(s_end, D, step, tkn, s_end_n);
-        if (fn) fetch_group(a, r, tkn, dkn);
-        float s_dummy;
-        full_geom(s, D, step, tk, s_dummy);                  // positions of the current group again (cheaper than carrying them)
-        process_group<COUNT, TF_SMEM, EXACT, true, GRAD>(a, s_tf, s_mask, r, tk, hk, dkc, nsamp);
-        s = s_end;
+      // PIPE groups are prefetched ahead of the one being composited: sg[i] / fg[i] / dg[i] = start, FULL flag and
+      // fetched densities of the i-th group from the current one (all indices are compile-time after unrolling).
+      float sg[PIPE + 2], dg[PIPE + 1][UNROLL];
+      bool fg[PIPE + 1];
+      sg[0] = 0.0f;
 #pragma unroll
-        for (int k = 0; k < UNROLL; k++) dkc[k] = dkn[k];
-        s_end = s_end_n; fc = fn;
+      for (int i = 0; i < PIPE; i++) {
+        fg[i] = (i == 0 || fg[i > 0 ? i - 1 : 0]) && full_geom(sg[i], D, step, tk, sg[i + 1]);
+        if (!fg[i]) sg[i + 1] = sg[i];
+        if (fg[i]) fetch_group(a, r, tk, dg[i]);
       }
+      while (fg[0] && !r.done) {
+        float tkn[UNROLL];
+        fg[PIPE] = fg[PIPE - 1] && full_geom(sg[PIPE], D, step, tkn, sg[PIPE + 1]);
+        if (fg[PIPE]) fetch_group(a, r, tkn, dg[PIPE]);
+        float s_dummy;
+        full_geom(sg[0], D, step, tk, s_dummy);              // positions of the current group again (cheaper than carrying them)
+        process_group<COUNT, TF_SMEM, EXACT, true, GRAD>(a, s_tf, s_mask, r, tk, hk, dg[0], nsamp);
+#pragma unroll
+        for (int i = 0; i < PIPE; i++) {
+          fg[i] = fg[i + 1];
+#pragma unroll
+          for (int k = 0; k < UNROLL; k++) dg[i][k] = dg[i + 1][k];
+        }
+#pragma unroll
+        for (int i = 0; i <= PIPE; i++) sg[i] = sg[i + 1];
+      }
+      s = sg[0];
       // at most one group is left: the one that holds the end of the ray
       while (s < D && !r.done) {
         bool full;
@@ -415,7 +487,32 @@ __device__ __forceinline__ void march_groups(const Rc1Args& a, const uint4* s_tf
                                              int g0, int ng, unsigned& nsamp) {
   const float step = a.step;
   float s = (float)(g0 * UNROLL) * step;
-  for (int g = 0; g < ng && s < D && !r.done; g++) {
+  int g = 0;
+#if VRB_SPLIT_PIPE
+  {
+    // software pipeline over the FULL groups of the segment, as in rc1pass_kernel
+    float hk[UNROLL], tk[UNROLL], dkc[UNROLL];
+#pragma unroll
+    for (int k = 0; k < UNROLL; k++) hk[k] = step;
+    float s_end = s;
+    bool fc = ng > 0 && full_geom(s, D, step, tk, s_end);
+    if (fc) fetch_group(a, r, tk, dkc);
+    while (fc && !r.done) {
+      float tkn[UNROLL], dkn[UNROLL];
+      float s_end_n = s_end;
+      const bool fn = (g + 1 < ng) && full_geom(s_end, D, step, tkn, s_end_n);
+      if (fn) fetch_group(a, r, tkn, dkn);
+      float s_dummy;
+      full_geom(s, D, step, tk, s_dummy);
+      process_group<COUNT, true, true, true>(a, s_tf, s_mask, r, tk, hk, dkc, nsamp);
+      s = s_end; g++;
+#pragma unroll
+      for (int k = 0; k < UNROLL; k++) dkc[k] = dkn[k];
+      s_end = s_end_n; fc = fn;
+    }
+  }
+#endif
+  for (; g < ng && s < D && !r.done; g++) {
     float hk[UNROLL], tk[UNROLL], sk[UNROLL + 1];
     sk[0] = s;
 #pragma unroll
@@ -438,7 +535,7 @@ __device__ __forceinline__ void march_groups(const Rc1Args& a, const uint4* s_tf
 }
 
 template <bool COUNT, int K>
-__global__ void __launch_bounds__(CTA_THREADS, 4) rc1pass_split_kernel(const __grid_constant__ Rc1Args a) {
+__global__ void __launch_bounds__(CTA_THREADS, VRB_SPLIT_MINB) rc1pass_split_kernel(const __grid_constant__ Rc1Args a) {
   constexpr int PIX = 32 / K, FW = SplitGeom<K>::FW, FH = SplitGeom<K>::FH;
   extern __shared__ uint4 s_dyn[];
   uint4* s_tf = s_dyn;

@@ -20,8 +20,10 @@ def main():
     ctx = _capi.Context(0)
     ctx.upload_volume(vox); ctx.upload_tf(table)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:0")
-    for world in (1, 2, 4, 8):
-        for K in (0, 2, 4, 8):
+    worlds = [int(x) for x in os.environ.get("SWEEP_WORLDS", "1,2,4,8").split(",")]
+    ks = [int(x) for x in os.environ.get("SWEEP_KS", "0,2,4,8").split(",")]
+    for world in worlds:
+        for K in ks:
             worst = 0.0
             for rank in sorted({0, world - 1, world // 2}):
                 r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
@@ -37,7 +39,7 @@ def main():
                     ms.append(r.counters()[1])
                 worst = max(worst, float(np.median(ms[3:])))
                 r.close()
-            print(json.dumps({"n_ranks": world, "depth_split": K, "kernel_ms_worst_rank": worst}), flush=True)
+            print(json.dumps({"lib": os.path.basename(_capi.LIB_PATH), "split_g": os.environ.get("VRB_SPLIT_G", ""), "n_ranks": world, "depth_split": K, "kernel_ms_worst_rank": worst}), flush=True)
 
 
 if __name__ == "__main__":
