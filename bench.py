@@ -130,7 +130,7 @@ def sat_extra(ctx, table, hbm_peak):
     ctx.upload_volume(vox)
     ctx.upload_tf(table)
     out = {"workload": f"extinction SAT {n}^3 f32 -> {(n + 2)}^3 float32", "algorithmic_bytes": 8 * (n + 2) ** 3}
-    for name, fast in (("exact_wavefront", 0), ("separable_scan", 1)):
+    for name, fast in (("exact_wavefront", 0), ("reduce_then_scan", 1), ("separable_scan", 2)):
         best = None
         for _ in range(3):
             r = _capi.Renderer(ctx, _capi.VRB_EBS_SAT)

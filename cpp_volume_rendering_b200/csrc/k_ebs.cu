@@ -254,7 +254,7 @@ class EbsRenderer : public RendererImpl {
     VRB_REQUIRE(ctx->tf.tex_rgbt != 0, VRB_ERR_INVALID, "RC1PExtinctionBasedShading::Init: no transfer function");
     int rc = ensure_quad(ctx);
     if (rc != VRB_OK) return rc;
-    rc = sat_.ensure(ctx, prm_.fast_sat != 0);           // GenerateExtinctionSAT3DTex (:95-96)
+    rc = sat_.ensure(ctx, prm_.fast_sat);           // GenerateExtinctionSAT3DTex (:95-96)
     if (rc != VRB_OK) return rc;
     const float vw = (float)v.w * v.sx, vh = (float)v.h * v.sy, vd = (float)v.d * v.sz;
     prm_.dir_cone_max_distance = 0.75f * sqrtf(vw * vw + vh * vh + vd * vd);      // :99-105
@@ -293,7 +293,7 @@ class EbsRenderer : public RendererImpl {
   int redraw(int) override {
     VRB_REQUIRE(built && have_cam, VRB_ERR_INVALID, "RC1PExtinctionBasedShading::Redraw before Init/Update");
     int rc = ensure_quad(ctx);
-    if (rc == VRB_OK) rc = sat_.ensure(ctx, prm_.fast_sat != 0);   // volume / TF / builder changed (transfer_function_changed, :136-141)
+    if (rc == VRB_OK) rc = sat_.ensure(ctx, prm_.fast_sat);   // volume / TF / builder changed (transfer_function_changed, :136-141)
     if (rc != VRB_OK) return rc;
     const Volume& v = ctx->vol;
     EbsArgs a{};

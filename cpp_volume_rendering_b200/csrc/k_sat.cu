@@ -5,11 +5,12 @@
 // (W+2)(H+2)(D+2) cells, zero border, interior = TransferFunction1D::GetExtN(normalised voxel) (a float, widened to
 // double), inclusive 3D prefix sum accumulated in double, stored as float32.
 //
-// Two builders:
+// Three builders (vrb_ebs_params::fast_sat = 0 / 1 / 2):
 //  * EXACT (default): the reference's own 8-term inclusion-exclusion recurrence, term for term, evaluated as a
 //    wavefront over the planes x+y+z = k (every cell depends only on cells of earlier planes).  The double results —
 //    and so the float32 table — are bit-identical to the CPU build for any input.
-//  * FAST: separable scan (x by warp shuffles, then y, then z fused with the float32 store).  HBM-bound: 36 B/cell
+//  * FAST (1): the reduce-then-scan of `namespace sat2` below when the volume's x extent allows it, else the separable scan.
+//  * SEPARABLE (2): separable scan (x by warp shuffles, then y, then z fused with the float32 store).  HBM-bound: 56 B/cell
 //    moved against 8 B/cell algorithmic.  Re-associates the double sums: identical after the float32 cast except for
 //    rare 1-ulp cells, and bit-identical whenever the sums are exact in double (quantised extinctions).
 #include "vrb_internal.cuh"
@@ -30,7 +31,7 @@ __host__ __device__ inline float tf_get_extn(const double* table, int max_densit
     const double t = value - iv;
     a = (float)((1.0 - t) * table[4 * iv + 3] + t * table[4 * (iv + 1) + 3]);
   }
-  if (!extinction_type) return (float)log(1.0 / (1.0 - (double)a));
+  if (!extinction_type) return a == 0.0f ? 0.0f : (float)log(1.0 / (1.0 - (double)a));   // log(1/1) = 0 exactly: skip the double log in empty space
   return a;
 }
 
@@ -112,6 +113,315 @@ __global__ void __launch_bounds__(256) sat_scan_z_kernel(const double* __restric
   for (int z = 0; z < D; z++) { run += a[base + sz * z]; out[base + sz * z] = (float)run; }
 }
 
+// ---- FAST v2: reduce-then-scan, the volume is read twice and the table written once -------------------------------
+// A CTA of 16 warps owns a tile of 512 (x) x 32 (y) cells — thread = 4 consecutive x, 8 consecutive y — and marches a
+// segment of z slices.  Slices are staged global -> shared by cp.async (two stages in flight, every thread reads back
+// only the bytes it copied itself, so the staging needs no barrier).
+//   pass 1 `sat_reduce_kernel`: extinction E(x,y,z) (float32, written out so GetExtN — a double log for float volumes —
+//           runs once), per slice the column sums of the 32-row band cs(x, band, z), per segment the z sums zs(x,y,seg)
+//           and their band sums;
+//   mid    `sat_mid_kernel`: exclusive prefixes of those carries over bands / segments (tens of MB);
+//   pass 2 `sat_scan_kernel`: per slice the tile-local 2D inclusive scan (x: 3 adds + a warp shuffle scan per row,
+//           y: running sums), accumulated over z in registers (so the 32 accumulators of a thread hold the z-accumulated
+//           tile-local scan); the carry from the bands above enters as an extra addend of the band's first row, the
+//           carry from the slices before the segment as the accumulators' initial value; warps exchange their tile's
+//           right edge and bottom row through shared memory (one barrier per slice); float32 store.
+// All sums in double.  HBM traffic: 16 B/cell for float volumes (4 raw + 4 E, 4 E + 4 table), 10-11 B/cell for integer
+// volumes, plus < 1 B/cell of carries — against 56 B/cell of the separable scan.  Needs w % 4 == 0 and w <= 512.
+namespace sat2 {
+constexpr int XW = 4, YW = 4, R = 8, C = 4;
+constexpr int THREADS = 32 * XW * YW;       // 512
+constexpr int XSPAN = 32 * XW * C;          // 512 columns per CTA
+constexpr int BAND = YW * R;                // 32 rows per CTA
+constexpr int STAGES = 2;
+
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void* smem, const void* gmem, bool pred) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  const int n = pred ? BYTES : 0;                     // src-size 0: nothing is read, the destination is zero-filled
+  if (BYTES == 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gmem), "r"(n) : "memory");
+  else asm volatile("cp.async.ca.shared.global [%0], [%1], %2, %3;" ::"r"(s), "l"(gmem), "n"(BYTES), "r"(n) : "memory");
+}
+__device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <typename T> struct Raw4;
+template <> struct alignas(4) Raw4<uint8_t> { uint8_t v[4]; };
+template <> struct alignas(8) Raw4<uint16_t> { uint16_t v[4]; };
+template <> struct alignas(16) Raw4<float> { float v[4]; };
+
+struct Geo {
+  int w, h, d, seglen, nbands, nseg;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(THREADS, 1) sat_reduce_kernel(const T* __restrict__ raw, const float* __restrict__ lut,
+                                                                const double* __restrict__ table, int max_density, int ext_type, Geo g,
+                                                                float* __restrict__ E, double* __restrict__ cs, double* __restrict__ zs,
+                                                                double* __restrict__ bandzs) {
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  using V = Raw4<T>;
+  V* stage = reinterpret_cast<V*>(s_raw);                                                   // [STAGES][R][THREADS]
+  double* red = reinterpret_cast<double*>(s_raw + (size_t)STAGES * R * THREADS * sizeof(V));  // [2][YW][XSPAN]
+  const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5, wx = wq & (XW - 1), wy = wq / XW;
+  const int band = blockIdx.x, seg = blockIdx.y;
+  const int xl = wx * 32 * C + lane * C, x0 = xl, yb = band * BAND + wy * R;
+  const int z0 = seg * g.seglen, z1 = min(g.d, z0 + g.seglen);
+  const bool xin = x0 < g.w;
+  auto issue = [&](int z, int st) {
+    if (z < z1) {
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+        const int y = yb + r;
+        const bool p = xin && y < g.h;
+        const T* src = p ? raw + ((size_t)x0 + (size_t)g.w * ((size_t)y + (size_t)g.h * (size_t)z)) : raw;
+        cp_async<(int)sizeof(V)>(&stage[(st * R + r) * THREADS + tid], src, p);
+      }
+    }
+    cp_commit();
+  };
+  double acc[R][C], bz[C];
+#pragma unroll
+  for (int r = 0; r < R; r++)
+#pragma unroll
+    for (int c = 0; c < C; c++) acc[r][c] = 0.0;
+#pragma unroll
+  for (int c = 0; c < C; c++) bz[c] = 0.0;
+#pragma unroll
+  for (int s = 0; s < STAGES; s++) issue(z0 + s, s);
+  for (int z = z0; z < z1; z++) {
+    const int st = (z - z0) % STAGES, par = (z - z0) & 1;
+    cp_wait<STAGES - 1>();
+    double col[C];
+#pragma unroll
+    for (int c = 0; c < C; c++) col[c] = 0.0;
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const int y = yb + r;
+      const bool p = xin && y < g.h;
+      const V v = stage[(st * R + r) * THREADS + tid];
+      float e[C];
+#pragma unroll
+      for (int c = 0; c < C; c++) {
+        if (!p) e[c] = 0.0f;
+        else if (sizeof(T) != 4) e[c] = lut[(unsigned)v.v[c]];
+        else e[c] = tf_get_extn(table, max_density, ext_type, (double)v.v[c] / 1.0);
+      }
+      if (p) *reinterpret_cast<float4*>(E + ((size_t)x0 + (size_t)g.w * ((size_t)y + (size_t)g.h * (size_t)z))) = make_float4(e[0], e[1], e[2], e[3]);
+#pragma unroll
+      for (int c = 0; c < C; c++) { acc[r][c] += (double)e[c]; col[c] += (double)e[c]; }
+    }
+    double* rd = red + ((size_t)(par * YW + wy) * XSPAN + xl);
+    *reinterpret_cast<double2*>(rd) = make_double2(col[0], col[1]);
+    *reinterpret_cast<double2*>(rd + 2) = make_double2(col[2], col[3]);
+    issue(z + STAGES, st);                      // refills the stage this thread has just consumed
+    __syncthreads();
+    if (wy == 0 && xin) {
+      double s4[C] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+      for (int q = 0; q < YW; q++) {
+        const double2 a = *reinterpret_cast<const double2*>(red + ((size_t)(par * YW + q) * XSPAN + xl));
+        const double2 b = *reinterpret_cast<const double2*>(red + ((size_t)(par * YW + q) * XSPAN + xl + 2));
+        s4[0] += a.x; s4[1] += a.y; s4[2] += b.x; s4[3] += b.y;
+      }
+      double* o = cs + ((size_t)z * g.nbands + band) * (size_t)g.w + x0;
+      *reinterpret_cast<double2*>(o) = make_double2(s4[0], s4[1]);
+      *reinterpret_cast<double2*>(o + 2) = make_double2(s4[2], s4[3]);
+#pragma unroll
+      for (int c = 0; c < C; c++) bz[c] += s4[c];
+    }
+  }
+  cp_wait<0>();
+  if (xin) {
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const int y = yb + r;
+      if (y < g.h) {
+        double* o = zs + ((size_t)seg * g.h + y) * (size_t)g.w + x0;
+        *reinterpret_cast<double2*>(o) = make_double2(acc[r][0], acc[r][1]);
+        *reinterpret_cast<double2*>(o + 2) = make_double2(acc[r][2], acc[r][3]);
+      }
+    }
+    if (wy == 0) {
+      double* o = bandzs + ((size_t)seg * g.nbands + band) * (size_t)g.w + x0;
+      *reinterpret_cast<double2*>(o) = make_double2(bz[0], bz[1]);
+      *reinterpret_cast<double2*>(o + 2) = make_double2(bz[2], bz[3]);
+    }
+  }
+}
+
+// Exclusive prefixes of the carries: cs over bands (per x, z) and zs over segments (per x, y) in place, bandzs over
+// bands and segments into zsy.
+__global__ void __launch_bounds__(256) sat_mid_kernel(double* __restrict__ cs, double* __restrict__ zs, const double* __restrict__ bandzs,
+                                                      double* __restrict__ zsy, Geo g, unsigned blocks_a, unsigned blocks_b) {
+  const size_t w = (size_t)g.w;
+  if (blockIdx.x < blocks_a) {
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= w * g.d) return;
+    const size_t x = i % w, z = i / w;
+    double run = 0.0;
+    for (int b = 0; b < g.nbands; b++) { double* p = cs + (z * g.nbands + b) * w + x; const double t = *p; *p = run; run += t; }
+  } else if (blockIdx.x < blocks_a + blocks_b) {
+    const size_t i = (size_t)(blockIdx.x - blocks_a) * 256 + threadIdx.x;
+    if (i >= w * g.h) return;
+    double run = 0.0;
+    for (int s = 0; s < g.nseg; s++) { double* p = zs + (size_t)s * g.h * w + i; const double t = *p; *p = run; run += t; }
+  } else {
+    // zsy(x, band, seg) = sum of bandzs over bands < band and segments < seg; read-only input, so the loads pipeline
+    const size_t i = (size_t)(blockIdx.x - blocks_a - blocks_b) * 256 + threadIdx.x;
+    if (i >= w * g.nbands) return;
+    const size_t x = i % w; const int band = (int)(i / w);
+    double run = 0.0;
+    for (int s = 0; s < g.nseg; s++) {
+      zsy[((size_t)s * g.nbands + band) * w + x] = run;
+      double t = 0.0;
+      for (int b = 0; b < band; b++) t += bandzs[((size_t)s * g.nbands + b) * w + x];
+      run += t;
+    }
+  }
+}
+
+__device__ __forceinline__ double warp_incl_scan(double v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const double t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += t; }
+  return v;
+}
+
+// One row of the tile-local 2D scan: a[] = the row's 4 values; x-scan over the warp's 128 columns, then onto the
+// running column sums run[] (y-scan), then onto the z accumulators.
+__device__ __forceinline__ void scan_row(double (&a)[C], double (&run)[C], double (&acc)[C], int lane) {
+  a[1] += a[0]; a[2] += a[1]; a[3] += a[2];
+  const double incl = warp_incl_scan(a[3], lane);
+  double excl = __shfl_up_sync(0xffffffffu, incl, 1);
+  if (lane == 0) excl = 0.0;
+#pragma unroll
+  for (int c = 0; c < C; c++) { run[c] += a[c] + excl; acc[c] += run[c]; }
+}
+
+__global__ void __launch_bounds__(THREADS, 1) sat_scan_kernel(const float* __restrict__ E, const double* __restrict__ csx, const double* __restrict__ ZS,
+                                                              const double* __restrict__ ZSY, Geo g, float* __restrict__ out) {
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  float4* stage = reinterpret_cast<float4*>(s_raw);                                   // [STAGES][R][THREADS]
+  double2* cstage = reinterpret_cast<double2*>(stage + STAGES * R * THREADS);         // [STAGES][2][32 * XW] (wy == 0 warps)
+  double* right = reinterpret_cast<double*>(cstage + STAGES * 2 * 32 * XW);          // [2][YW][R][XW]
+  double* bottom = right + 2 * YW * R * XW;                                           // [2][YW][XSPAN]
+  const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5, wx = wq & (XW - 1), wy = wq / XW;
+  const int band = blockIdx.x, seg = blockIdx.y;
+  const int xl = wx * 32 * C + lane * C, x0 = xl, yb = band * BAND + wy * R;
+  const int z0 = seg * g.seglen, z1 = min(g.d, z0 + g.seglen);
+  const bool xin = x0 < g.w;
+  const int W = g.w + 2, H = g.h + 2;
+  auto issue = [&](int z, int st) {
+    if (z < z1) {
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+        const int y = yb + r;
+        const bool p = xin && y < g.h;
+        const float* src = p ? E + ((size_t)x0 + (size_t)g.w * ((size_t)y + (size_t)g.h * (size_t)z)) : E;
+        cp_async<16>(&stage[(st * R + r) * THREADS + tid], src, p);
+      }
+      if (wy == 0) {
+        const double* src = xin ? csx + ((size_t)z * g.nbands + band) * (size_t)g.w + x0 : csx;
+        cp_async<16>(&cstage[(st * 2 + 0) * 32 * XW + wx * 32 + lane], src, xin);
+        cp_async<16>(&cstage[(st * 2 + 1) * 32 * XW + wx * 32 + lane], xin ? src + 2 : src, xin);
+      }
+    }
+    cp_commit();
+  };
+#pragma unroll
+  for (int s = 0; s < STAGES; s++) issue(z0 + s, s);
+  // accumulators start at the tile-local scan of the z carry (sum of the slices before the segment), its first row
+  // carrying the band carry of those slices
+  double acc[R][C];
+  {
+    double run[C] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const int y = yb + r;
+      double a[C] = {0.0, 0.0, 0.0, 0.0};
+      if (xin && y < g.h) {
+        const double* p = ZS + ((size_t)seg * g.h + y) * (size_t)g.w + x0;
+        const double2 u = *reinterpret_cast<const double2*>(p), v = *reinterpret_cast<const double2*>(p + 2);
+        a[0] = u.x; a[1] = u.y; a[2] = v.x; a[3] = v.y;
+      }
+      if (r == 0 && wy == 0 && xin) {
+        const double* p = ZSY + ((size_t)seg * g.nbands + band) * (size_t)g.w + x0;
+        const double2 u = *reinterpret_cast<const double2*>(p), v = *reinterpret_cast<const double2*>(p + 2);
+        a[0] += u.x; a[1] += u.y; a[2] += v.x; a[3] += v.y;
+      }
+#pragma unroll
+      for (int c = 0; c < C; c++) acc[r][c] = 0.0;
+      scan_row(a, run, acc[r], lane);
+    }
+  }
+  for (int z = z0; z < z1; z++) {
+    const int st = (z - z0) % STAGES, par = (z - z0) & 1;
+    cp_wait<STAGES - 1>();
+    {
+      double run[C] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+        const float4 v = stage[(st * R + r) * THREADS + tid];       // zero-filled outside the volume
+        double a[C] = {(double)v.x, (double)v.y, (double)v.z, (double)v.w};
+        if (r == 0 && wy == 0) {
+          const double2 u = cstage[(st * 2 + 0) * 32 * XW + wx * 32 + lane], t = cstage[(st * 2 + 1) * 32 * XW + wx * 32 + lane];
+          a[0] += u.x; a[1] += u.y; a[2] += t.x; a[3] += t.y;
+        }
+        scan_row(a, run, acc[r], lane);
+      }
+    }
+    // tile edges of the z-accumulated local scan
+    if (lane == 31) {
+#pragma unroll
+      for (int r = 0; r < R; r++) right[((par * YW + wy) * R + r) * XW + wx] = acc[r][C - 1];
+    }
+    {
+      double* b = bottom + (size_t)(par * YW + wy) * XSPAN + xl;
+      *reinterpret_cast<double2*>(b) = make_double2(acc[R - 1][0], acc[R - 1][1]);
+      *reinterpret_cast<double2*>(b + 2) = make_double2(acc[R - 1][2], acc[R - 1][3]);
+    }
+    issue(z + STAGES, st);
+    __syncthreads();
+    double corner = 0.0, colc[C] = {0.0, 0.0, 0.0, 0.0};
+    for (int q = 0; q < wy; q++) {
+      for (int k = 0; k < wx; k++) corner += right[((par * YW + q) * R + (R - 1)) * XW + k];
+      const double* b = bottom + (size_t)(par * YW + q) * XSPAN + xl;
+      const double2 u = *reinterpret_cast<const double2*>(b), v = *reinterpret_cast<const double2*>(b + 2);
+      colc[0] += u.x; colc[1] += u.y; colc[2] += v.x; colc[3] += v.y;
+    }
+#pragma unroll
+    for (int c = 0; c < C; c++) colc[c] += corner;
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const int y = yb + r;
+      double rowc = 0.0;
+      for (int k = 0; k < wx; k++) rowc += right[((par * YW + wy) * R + r) * XW + k];
+      if (xin && y < g.h) {
+        float* o = out + ((size_t)(x0 + 1) + (size_t)W * ((size_t)(y + 1) + (size_t)H * (size_t)(z + 1)));
+#pragma unroll
+        for (int c = 0; c < C; c++) o[c] = (float)(acc[r][c] + (rowc + colc[c]));
+      }
+    }
+  }
+  cp_wait<0>();
+}
+
+// The zero planes X/Y/Z = 0 and the repeated planes X = w+1, Y = h+1, Z = d+1 of the bordered table.
+__global__ void __launch_bounds__(256) sat_border_kernel(float* __restrict__ out, int w, int h, int d) {
+  const int W = w + 2, H = h + 2, D = d + 2;
+  const size_t nx = (size_t)H * D, ny = (size_t)W * D, nz = (size_t)W * H;
+  size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+  int X, Y, Z;
+  if (i < 2 * nx) { X = i < nx ? 0 : W - 1; i %= nx; Y = (int)(i % H); Z = (int)(i / H); }
+  else if (i < 2 * nx + 2 * ny) { i -= 2 * nx; Y = i < ny ? 0 : H - 1; i %= ny; X = (int)(i % W); Z = (int)(i / W); }
+  else if (i < 2 * nx + 2 * ny + 2 * nz) { i -= 2 * nx + 2 * ny; Z = i < nz ? 0 : D - 1; i %= nz; X = (int)(i % W); Y = (int)(i / W); }
+  else return;
+  float v = 0.0f;
+  if (X > 0 && Y > 0 && Z > 0) v = out[(size_t)min(X, w) + (size_t)W * ((size_t)min(Y, h) + (size_t)H * (size_t)min(Z, d))];
+  out[(size_t)X + (size_t)W * ((size_t)Y + (size_t)H * (size_t)Z)] = v;
+}
+}  // namespace sat2
+
 // Footprint texture of the float32 table: texel (x,y,z) = {S(x,y), S(x+1,y), S(x,y+1), S(x+1,y+1)} of slice z,
 // edge-clamped; the shader's GL_LINEAR fetch of the R32F SAT (ebsrenderer.cpp:716) becomes two point fetches and a
 // float32 lerp in the oracle's order (the hardware's 1.8 fixed-point weights are useless on values of this size).
@@ -131,7 +441,7 @@ void ExtSat::release() {
   tex_quad = 0; quad = nullptr; sat = nullptr; W = H = D = 0; vol_gen = tf_gen = 0;
 }
 
-int ExtSat::ensure(vrb_ctx* ctx, bool fast) {
+int ExtSat::ensure(vrb_ctx* ctx, int fast) {
   const Volume& v = ctx->vol;
   const TransferFunction& t = ctx->tf;
   if (sat && vol_gen == v.generation && tf_gen == t.generation && built_fast == fast) return VRB_OK;
@@ -141,9 +451,11 @@ int ExtSat::ensure(vrb_ctx* ctx, bool fast) {
   const size_t n = (size_t)W * H * D;
   cudaStream_t s = ctx->stream;
   double* acc = nullptr; float* lut = nullptr;
+  float* E = nullptr; double *cs = nullptr, *zs = nullptr, *bzs = nullptr;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   auto body = [&]() -> int {
-    VRB_CUDA(cudaMalloc(&acc, n * sizeof(double)));
+    const bool v2 = fast == 1 && (v.w % 4) == 0 && v.w <= sat2::XSPAN;
+    if (!v2) VRB_CUDA(cudaMalloc(&acc, n * sizeof(double)));
     VRB_CUDA(cudaMalloc(&sat, n * sizeof(float)));
     VRB_CUDA(cudaEventCreate(&e0)); VRB_CUDA(cudaEventCreate(&e1));
     const int maxd = t.n - 1;
@@ -160,7 +472,48 @@ int ExtSat::ensure(vrb_ctx* ctx, bool fast) {
       VRB_CUDA(cudaMemcpyAsync(lut, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice, s));
       VRB_CUDA(cudaStreamSynchronize(s));
     }
+    sat2::Geo g{};
+    if (v2) {
+      g.w = (int)v.w; g.h = (int)v.h; g.d = (int)v.d;
+      g.nbands = (g.h + sat2::BAND - 1) / sat2::BAND;
+      // one CTA per SM (512 threads, ~170 KB shared memory): bands x segments = one wave, segments of >= 8 slices
+      g.nseg = std::max(1, std::min(std::max(1, ctx->sm_count / g.nbands), std::max(1, g.d / 8)));
+      g.seglen = (g.d + g.nseg - 1) / g.nseg;
+      g.nseg = (g.d + g.seglen - 1) / g.seglen;
+      const size_t wz = (size_t)g.w;
+      VRB_CUDA(cudaMalloc(&E, wz * g.h * g.d * sizeof(float)));
+      VRB_CUDA(cudaMalloc(&cs, wz * g.nbands * g.d * sizeof(double)));
+      VRB_CUDA(cudaMalloc(&zs, wz * g.h * g.nseg * sizeof(double)));
+      VRB_CUDA(cudaMalloc(&bzs, 2 * wz * g.nbands * g.nseg * sizeof(double)));
+    }
     VRB_CUDA(cudaEventRecord(e0, s));
+    if (v2) {
+      const size_t wz = (size_t)g.w;
+      double* zsy = bzs + wz * g.nbands * g.nseg;
+      const dim3 grid(g.nbands, g.nseg);
+      const size_t esz = v.dtype == VRB_U8 ? 4 : (v.dtype == VRB_U16 ? 8 : 16);
+      const size_t sm1 = (size_t)sat2::STAGES * sat2::R * sat2::THREADS * esz + (size_t)2 * sat2::YW * sat2::XSPAN * sizeof(double);
+      const size_t sm2 = (size_t)sat2::STAGES * sat2::R * sat2::THREADS * 16 + (size_t)sat2::STAGES * 2 * 32 * sat2::XW * 16 +
+                         (size_t)2 * sat2::YW * sat2::R * sat2::XW * sizeof(double) + (size_t)2 * sat2::YW * sat2::XSPAN * sizeof(double);
+      const int maxd2 = t.n - 1;
+      if (v.dtype == VRB_U8) {
+        VRB_CUDA(cudaFuncSetAttribute(sat2::sat_reduce_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
+        sat2::sat_reduce_kernel<uint8_t><<<grid, sat2::THREADS, sm1, s>>>((const uint8_t*)v.raw, lut, t.table, maxd2, t.extinction_type, g, E, cs, zs, bzs);
+      } else if (v.dtype == VRB_U16) {
+        VRB_CUDA(cudaFuncSetAttribute(sat2::sat_reduce_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
+        sat2::sat_reduce_kernel<uint16_t><<<grid, sat2::THREADS, sm1, s>>>((const uint16_t*)v.raw, lut, t.table, maxd2, t.extinction_type, g, E, cs, zs, bzs);
+      } else {
+        VRB_CUDA(cudaFuncSetAttribute(sat2::sat_reduce_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
+        sat2::sat_reduce_kernel<float><<<grid, sat2::THREADS, sm1, s>>>((const float*)v.raw, nullptr, t.table, maxd2, t.extinction_type, g, E, cs, zs, bzs);
+      }
+      VRB_CUDA(cudaGetLastError());
+      const unsigned ba = (unsigned)((wz * g.d + 255) / 256), bb = (unsigned)((wz * g.h + 255) / 256), bc = (unsigned)((wz * g.nbands + 255) / 256);
+      sat2::sat_mid_kernel<<<ba + bb + bc, 256, 0, s>>>(cs, zs, bzs, zsy, g, ba, bb);
+      VRB_CUDA(cudaFuncSetAttribute(sat2::sat_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+      sat2::sat_scan_kernel<<<grid, sat2::THREADS, sm2, s>>>(E, cs, zs, zsy, g, sat);
+      const size_t faces = 2 * ((size_t)H * D + (size_t)W * D + (size_t)W * H);
+      sat2::sat_border_kernel<<<(unsigned)((faces + 255) / 256), 256, 0, s>>>(sat, g.w, g.h, g.d);
+    } else {
     dim3 fb(256), fg((W + 255) / 256, H, D);
     if (v.dtype == VRB_U8) sat_fill_kernel<uint8_t><<<fg, fb, 0, s>>>((const uint8_t*)v.raw, lut, t.table, maxd, t.extinction_type, (int)v.w, (int)v.h, (int)v.d, acc);
     else if (v.dtype == VRB_U16) sat_fill_kernel<uint16_t><<<fg, fb, 0, s>>>((const uint16_t*)v.raw, lut, t.table, maxd, t.extinction_type, (int)v.w, (int)v.h, (int)v.d, acc);
@@ -177,6 +530,7 @@ int ExtSat::ensure(vrb_ctx* ctx, bool fast) {
         sat_wavefront_kernel<<<dim3((W + 255) / 256, y_hi - y_lo + 1), 256, 0, s>>>(acc, W, H, D, k, y_lo);
       }
       sat_to_float_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(acc, sat, n);
+    }
     }
     VRB_CUDA(cudaGetLastError());
     VRB_CUDA(cudaEventRecord(e1, s));
@@ -204,6 +558,10 @@ int ExtSat::ensure(vrb_ctx* ctx, bool fast) {
   };
   const int rc = body();
   if (acc) cudaFree(acc);
+  if (E) cudaFree(E);
+  if (cs) cudaFree(cs);
+  if (zs) cudaFree(zs);
+  if (bzs) cudaFree(bzs);
   if (lut) cudaFree(lut);
   if (e0) cudaEventDestroy(e0);
   if (e1) cudaEventDestroy(e1);

@@ -13,9 +13,9 @@ struct ExtSat {
   cudaTextureObject_t tex_quad = 0;
   int W = 0, H = 0, D = 0;              // bordered sizes = volume + 2
   uint64_t vol_gen = 0, tf_gen = 0;
-  bool built_fast = false;
+  int built_fast = 0;                   // vrb_ebs_params::fast_sat of the table that is resident
   float build_ms = 0.f;                 // device time of fill + scan of the last build
-  int ensure(vrb_ctx* ctx, bool fast);  // (re)builds when the volume, the TF or the builder changed
+  int ensure(vrb_ctx* ctx, int fast);   // (re)builds when the volume, the TF or the builder (0 exact, 1 fast, 2 separable) changed
   void release();
 };
 

@@ -121,7 +121,7 @@ typedef struct {
   float dir_cone_max_distance;             /* set by Init */
   int   type_of_shadow;                    /* 0 point light, 1 directional */
   float light_cam_forward[3];              /* RenderingParameters::GetBlinnPhongLightSourceCameraForward() */
-  int   fast_sat;                          /* new: 0 = SAT by the reference's recurrence (bit-identical), 1 = separable scan */
+  int   fast_sat;                          /* new: 0 = SAT by the reference's recurrence (bit-identical), 1 = reduce-then-scan (<= 1 ulp), 2 = separable scan */
   int   count_samples;
   int   use_light_cache;                   /* PreIlluminationStructuredVolume::IsActive(), false: object-space mode (see vrb_light_cache_read) */
   int   light_cache_resolution[3];         /* 32^3 (SetLightCacheResolution in the renderer's constructor) */

@@ -141,7 +141,7 @@ def main():
             prm = r.get_params(_capi.EbsParams()); prm.fast_sat = fast; r.set_params(prm)
             r.init(w, h)
             _, sat_ms = r.read_sat(want_data=False)
-            emit("ebs_sat" + ("(scan)" if fast else "(exact)"), "C4", r, _capi.EbsParams, {"precompute": {"sat_ms": sat_ms, "builder": "separable_scan" if fast else "exact_wavefront"}})
+            emit("ebs_sat" + ("(scan)" if fast else "(exact)"), "C4", r, _capi.EbsParams, {"precompute": {"sat_ms": sat_ms, "builder": "reduce_then_scan" if fast else "exact_wavefront"}})
             if fast:
                 emit_object_space("ebs_sat", "C4", r, _capi.EbsParams)
             r.close()
