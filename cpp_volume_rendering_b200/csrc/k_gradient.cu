@@ -49,8 +49,9 @@ __global__ void __launch_bounds__(128) gradient_kernel(const T* __restrict__ v, 
 
 void release_gradient(Volume& v) {
   if (v.tex_grad) cudaDestroyTextureObject(v.tex_grad);
+  if (v.tex_grad_pt) cudaDestroyTextureObject(v.tex_grad_pt);
   if (v.grad_array) cudaFreeArray(v.grad_array);
-  v.tex_grad = 0; v.grad_array = nullptr; v.grad_model = 0;
+  v.tex_grad = 0; v.tex_grad_pt = 0; v.grad_array = nullptr; v.grad_model = 0;
 }
 
 // Builds (or frees, model 0) the gradient texture of the current volume; host_rgb (optional) receives the texels.
@@ -69,6 +70,8 @@ int build_gradient(vrb_ctx* ctx, int model, float* host_rgb) {
     td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
     td.filterMode = cudaFilterModeLinear; td.readMode = cudaReadModeElementType; td.normalizedCoords = 1;
     VRB_CUDA(cudaCreateTextureObject(&v.tex_grad, &rd, &td, nullptr));
+    td.filterMode = cudaFilterModePoint; td.normalizedCoords = 0;
+    VRB_CUDA(cudaCreateTextureObject(&v.tex_grad_pt, &rd, &td, nullptr));
     cudaSurfaceObject_t dst = 0;
     VRB_CUDA(cudaCreateSurfaceObject(&dst, &rd));
     float* lin = nullptr;

@@ -93,6 +93,8 @@ struct IsoArgs {
   float tan_fovy, aspect;
   float iso, step_small, step_large, step_range;
   float color[4];
+  // ShadeBlinnPhong at the hit (ApplyGradientPhongShading == 1); grad == 0: off
+  cudaTextureObject_t grad, grad_pt; float ka, kd, ks, shininess, ispec[3], light_pos[3];
   float nb[3]; int nbi[3];
   const float* bmin; const float* bmax;
   uint2* frame;
@@ -114,6 +116,34 @@ __device__ __forceinline__ bool iso_crossing(float prev, float iso, float d) {
   return (prev <= iso && iso < d) || (prev >= iso && iso > d);
 }
 __device__ __forceinline__ int imod(int v, int n) { int m = v % n; return m < 0 ? m + n : m; }
+
+// ShadeBlinnPhong (ray_marching_1p_iso_adapt.comp:48-88 and the copies in the two custom shaders) + the front-to-back
+// composition of the hit (:137-152).  Out of line: runs once per ray.
+__device__ __noinline__ void iso_composite(const IsoArgs& a, float4& dst, f3 Tpos) {
+  float cr = a.color[0], cg = a.color[1], cb = a.color[2];
+  if (a.grad) {
+    const f3 grid = mk3(a.grid[0], a.grid[1], a.grid[2]);
+    // texture(TexVolumeGradient, Tpos / VolumeGridSize).xyz with float32 weights (the hit colour is a single opaque sample,
+    // so the texture unit's 1.8 fixed-point weights would show: 2.2/255)
+    f3 g = tex3d_rgb_exact(a.grad_pt, div3(Tpos, grid), mk3(a.res[0], a.res[1], a.res[2]));
+    if (g.x != 0.0f || g.y != 0.0f || g.z != 0.0f) {
+      const f3 Wpos = sub3(Tpos, scale3(grid, 0.5f));
+      const f3 light_direction = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), Wpos));
+      const f3 eye_direction = normalize_rn(sub3(mk3(a.eye[0], a.eye[1], a.eye[2]), Wpos));
+      const f3 halfway = normalize_rn(add3(eye_direction, light_direction));
+      g = normalize_rn(g);
+      const float dot_diff = gmax(0.0f, dot_rn(g, light_direction)), dot_spec = gmax(0.0f, dot_rn(halfway, g));
+      const float amb = __fadd_rn(a.ka, __fmul_rn(a.kd, dot_diff)), spec = __fmul_rn(a.ks, powf(dot_spec, a.shininess));
+      cr = __fadd_rn(__fmul_rn(cr, amb), __fmul_rn(a.ispec[0], spec));
+      cg = __fadd_rn(__fmul_rn(cg, amb), __fmul_rn(a.ispec[1], spec));
+      cb = __fadd_rn(__fmul_rn(cb, amb), __fmul_rn(a.ispec[2], spec));
+    }
+  }
+  // src = Color; src.rgb *= src.a; dst += (1-dst.a)*src
+  const float w = 1.0f - dst.w;
+  dst.x = fmaf(w, __fmul_rn(cr, a.color[3]), dst.x); dst.y = fmaf(w, __fmul_rn(cg, a.color[3]), dst.y);
+  dst.z = fmaf(w, __fmul_rn(cb, a.color[3]), dst.z); dst.w = fmaf(w, a.color[3], dst.w);
+}
 
 struct BlockLookup { int x, y, z; float mn, mx; };
 // getBlockIndex + the two GL_NEAREST / GL_REPEAT block-texture fetches
@@ -174,10 +204,9 @@ __global__ void __launch_bounds__(ISO_THREADS, 6) iso_kernel(const __grid_consta
           if (COUNT) nit++;
           if (iso_crossing(prev, iso, density)) { crossed = true; }
           if (crossed) {
-            // src = Color; src.rgb *= src.a; dst += (1-dst.a)*src; break at dst.a > 0.99 (:137-155)
-            const float w = 1.0f - dst.w;
-            dst.x = fmaf(w, __fmul_rn(a.color[0], a.color[3]), dst.x); dst.y = fmaf(w, __fmul_rn(a.color[1], a.color[3]), dst.y);
-            dst.z = fmaf(w, __fmul_rn(a.color[2], a.color[3]), dst.z); dst.w = fmaf(w, a.color[3], dst.w);
+            // refine (:137-138), shade and composite (:141-152), break at dst.a > 0.99 (:155)
+            const float tr = __fdiv_rn(__fsub_rn(iso, prev), __fsub_rn(density, prev));
+            iso_composite(a, dst, add3(tex_pos, scale3(r.dir, __fadd_rn(s, __fmul_rn(tr, h)))));
             crossed = false;
             if (dst.w > 0.99f) break;
           }
@@ -249,9 +278,7 @@ __global__ void __launch_bounds__(ISO_THREADS, 6) iso_kernel(const __grid_consta
             }
           }
           if (crossed) {
-            const float w = 1.0f - dst.w;
-            dst.x = fmaf(w, __fmul_rn(a.color[0], a.color[3]), dst.x); dst.y = fmaf(w, __fmul_rn(a.color[1], a.color[3]), dst.y);
-            dst.z = fmaf(w, __fmul_rn(a.color[2], a.color[3]), dst.z); dst.w = fmaf(w, a.color[3], dst.w);
+            iso_composite(a, dst, add3(add3(r.org, scale3(r.dir, t)), r.half));      // s_tex_pos at the refined t (v1 :227, v2 :247)
             crossed = false;
             if (dst.w > 0.99f) break;
           }
@@ -304,7 +331,6 @@ class IsoRenderer : public RendererImpl {
     const vrb_iso_params p = *(const vrb_iso_params*)pod;
     VRB_REQUIRE(p.step_size_small > 0.0f && p.step_size_large > 0.0f, VRB_ERR_INVALID, "iso set_params: step sizes must be positive");
     for (int i = 0; i < 3; i++) VRB_REQUIRE(p.num_blocks[i] >= 1 && p.num_blocks[i] <= 1024, VRB_ERR_INVALID, "iso set_params: num_blocks out of range");
-    VRB_REQUIRE(!p.apply_gradient_shading, VRB_ERR_UNSUPPORTED, "iso set_params: gradient shading needs a gradient volume (not uploaded)");
     prm_ = p;
     return VRB_OK;
   }
@@ -338,6 +364,12 @@ class IsoRenderer : public RendererImpl {
     a.tan_fovy = cam.tan_fovy; a.aspect = cam.aspect;
     a.iso = prm_.isovalue; a.step_small = prm_.step_size_small; a.step_large = prm_.step_size_large; a.step_range = prm_.step_size_range;
     for (int i = 0; i < 4; i++) a.color[i] = prm_.color[i];
+    a.grad = 0;
+    if (prm_.apply_gradient_shading) {      // m_apply_gradient_shading && GetCurrentGradientTexture() (rc1pisoadaptrenderer.cpp Update)
+      VRB_REQUIRE(v.tex_grad && v.grad_gen == v.generation, VRB_ERR_INVALID, "iso renderer: gradient shading needs vrb_volume_gradient() for the current volume");
+      a.grad = v.tex_grad; a.grad_pt = v.tex_grad_pt; a.ka = light.ka; a.kd = light.kd; a.ks = light.ks; a.shininess = light.shininess;
+      for (int i = 0; i < 3; i++) { a.ispec[i] = light.ispecular[i]; a.light_pos[i] = light.position[i]; }
+    }
     if (kind != VRB_ISO_ADAPT) {
       rc = blocks_.ensure(ctx, prm_.num_blocks[0], prm_.num_blocks[1], prm_.num_blocks[2]);
       if (rc != VRB_OK) return rc;

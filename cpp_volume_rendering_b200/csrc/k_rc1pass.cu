@@ -114,11 +114,10 @@ __device__ __forceinline__ float tf_coord(const Rc1Args& a, float density) {
 }
 
 // ShadeBlinnPhong (ray_marching_1p.comp:48-81).  Kept out of line: off by default, and the march loop's register
-// allocation must not pay for it.  The gradient texture is filtered by the texture unit (RGBA16F, 1.8 fixed-point
-// weights): it only feeds the normal of a shading term.
+// allocation must not pay for it.  The RGBA16F gradient texture is filtered with float32 weights (eight point fetches;
+// the texture unit's 1.8 fixed-point weights cost up to 1.9/255 on a specular highlight).
 __device__ __noinline__ float3 shade_blinn_phong(const Rc1Args& a, float ux, float uy, float uz, float3 clr) {
-  const float4 g4 = tex3D<float4>(a.grad, ux, uy, uz);
-  f3 g = mk3(g4.x, g4.y, g4.z);
+  f3 g = tex3d_rgb_exact(a.grad, mk3(ux, uy, uz), mk3(a.res[0], a.res[1], a.res[2]));
   if (g.x != 0.0f || g.y != 0.0f || g.z != 0.0f) {
     const f3 grid = mk3(a.grid[0], a.grid[1], a.grid[2]);
     const f3 Wpos = sub3(mul3(mk3(ux, uy, uz), grid), scale3(grid, 0.5f));
@@ -695,7 +694,7 @@ class Rc1Pass : public RendererImpl {
     a.grad = 0;
     if (prm_.apply_gradient_shading) {      // m_apply_gradient_shading && GetCurrentGradientTexture() (rc1prenderer.cpp:112-115)
       VRB_REQUIRE(v.tex_grad && v.grad_gen == v.generation, VRB_ERR_INVALID, "RayCasting1Pass: gradient shading needs vrb_volume_gradient() for the current volume");
-      a.grad = v.tex_grad; a.ka = light.ka; a.kd = light.kd; a.ks = light.ks; a.shininess = light.shininess;
+      a.grad = v.tex_grad_pt; a.ka = light.ka; a.kd = light.kd; a.ks = light.ks; a.shininess = light.shininess;
       for (int i = 0; i < 3; i++) { a.ispec[i] = light.ispecular[i]; a.light_pos[i] = light.position[i]; }
     }
     a.frame = (uint2*)frame; a.samples = d_samples;

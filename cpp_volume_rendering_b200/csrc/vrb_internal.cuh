@@ -49,6 +49,7 @@ struct Volume {
   // RGB16F gradient texture for the Blinn-Phong path (k_gradient.cu), built on request (vrb_volume_gradient)
   cudaArray_t grad_array = nullptr;
   cudaTextureObject_t tex_grad = 0;
+  cudaTextureObject_t tex_grad_pt = 0;     // the same array, point sampled with texel coordinates (float32-weight filtering in the kernel)
   int grad_model = 0;
   uint64_t grad_gen = 0;
   uint64_t generation = 0;

@@ -87,4 +87,29 @@ __device__ __forceinline__ float tex3d_f32_exact(cudaTextureObject_t quad, f3 p,
   const float c0 = __fadd_rn(c00, __fmul_rn(ay, __fsub_rn(c10, c00))), c1 = __fadd_rn(c01, __fmul_rn(ay, __fsub_rn(c11, c01)));
   return __fadd_rn(c0, __fmul_rn(az, __fsub_rn(c1, c0)));
 }
+
+// texture(TexVolumeGradient, p).xyz on the RGBA16F gradient texture, GL_LINEAR / CLAMP_TO_EDGE with float32 weights in the
+// order of oracle sample_grad: eight point fetches (texel coordinates, clamp addressing) of Volume::tex_grad_pt.
+__device__ __forceinline__ f3 tex3d_rgb_exact(cudaTextureObject_t pt, f3 p, f3 res) {
+  const float X = __fsub_rn(__fmul_rn(p.x, res.x), 0.5f), Y = __fsub_rn(__fmul_rn(p.y, res.y), 0.5f), Z = __fsub_rn(__fmul_rn(p.z, res.z), 0.5f);
+  float fx = floorf(X), fy = floorf(Y), fz = floorf(Z);
+  const float ax = __fsub_rn(X, fx), ay = __fsub_rn(Y, fy), az = __fsub_rn(Z, fz);   // below texel 0 both taps clamp to texel 0
+  fx = fminf(fmaxf(fx, -1.0f), res.x); fy = fminf(fmaxf(fy, -1.0f), res.y); fz = fminf(fmaxf(fz, -1.0f), res.z);
+  float4 t[2][2][2];
+#pragma unroll
+  for (int k = 0; k < 2; k++)
+#pragma unroll
+    for (int j = 0; j < 2; j++)
+#pragma unroll
+      for (int i = 0; i < 2; i++) t[k][j][i] = tex3D<float4>(pt, fx + 0.5f + (float)i, fy + 0.5f + (float)j, fz + 0.5f + (float)k);
+  auto lerp3 = [&](float v000, float v100, float v010, float v110, float v001, float v101, float v011, float v111) {
+    const float c00 = __fadd_rn(v000, __fmul_rn(ax, __fsub_rn(v100, v000))), c10 = __fadd_rn(v010, __fmul_rn(ax, __fsub_rn(v110, v010)));
+    const float c01 = __fadd_rn(v001, __fmul_rn(ax, __fsub_rn(v101, v001))), c11 = __fadd_rn(v011, __fmul_rn(ax, __fsub_rn(v111, v011)));
+    const float c0 = __fadd_rn(c00, __fmul_rn(ay, __fsub_rn(c10, c00))), c1 = __fadd_rn(c01, __fmul_rn(ay, __fsub_rn(c11, c01)));
+    return __fadd_rn(c0, __fmul_rn(az, __fsub_rn(c1, c0)));
+  };
+  return mk3(lerp3(t[0][0][0].x, t[0][0][1].x, t[0][1][0].x, t[0][1][1].x, t[1][0][0].x, t[1][0][1].x, t[1][1][0].x, t[1][1][1].x),
+             lerp3(t[0][0][0].y, t[0][0][1].y, t[0][1][0].y, t[0][1][1].y, t[1][0][0].y, t[1][0][1].y, t[1][1][0].y, t[1][1][1].y),
+             lerp3(t[0][0][0].z, t[0][0][1].z, t[0][1][0].z, t[0][1][1].z, t[1][0][0].z, t[1][0][1].z, t[1][1][0].z, t[1][1][1].z));
+}
 }  // namespace vrb

@@ -122,7 +122,8 @@ void CudaRayCasting1Pass::FillParameterSpace(ParameterSpace& pspace) {
 
 // ---- CudaRayCasting1PassIso ----------------------------------------------------------------------------------
 CudaRayCasting1PassIso::CudaRayCasting1PassIso(int kind)
-    : m_u_isovalue(0.5f), m_u_step_size_small(0.05f), m_u_step_size_large(1.0f), m_u_step_size_range(0.1f), m_kind(kind) {
+    : m_u_isovalue(0.5f), m_u_step_size_small(0.05f), m_u_step_size_large(1.0f), m_u_step_size_range(0.1f),
+      m_apply_gradient_shading(false), m_kind(kind) {   // rc1pisoadaptrenderer.cpp:13-20
   m_u_color[0] = 0.66f; m_u_color[1] = 0.6f; m_u_color[2] = 0.05f; m_u_color[3] = 1.0f;
   m_num_blocks[0] = m_num_blocks[1] = m_num_blocks[2] = kind == VRB_ISO_SKIP_V2 ? 32 : 4;
 }
@@ -158,6 +159,8 @@ bool CudaRayCasting1PassIso::Update(vis::Camera* camera) {
   p.isovalue = m_u_isovalue; p.step_size_small = m_u_step_size_small; p.step_size_large = m_u_step_size_large;
   p.step_size_range = m_u_step_size_range;
   for (int i = 0; i < 4; i++) p.color[i] = m_u_color[i];
+  // ApplyGradientPhongShading = m_apply_gradient_shading && GetCurrentGradientTexture() (rc1pisoadaptrenderer.cpp:92,157)
+  p.apply_gradient_shading = (m_apply_gradient_shading && m_ext_data_manager->HasGradientTexture()) ? 1 : 0;
   if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
   vrb_camera c; vrb_light l;
   camera->FillUniforms(&c);

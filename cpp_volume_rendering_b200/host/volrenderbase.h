@@ -86,6 +86,7 @@ class CudaRayCasting1PassIso : public BaseVolumeRenderer {
   void FillParameterSpace(ParameterSpace& pspace) override;    // rc1pisoadaptrenderer.cpp:191-197
   float m_u_isovalue, m_u_step_size_small, m_u_step_size_large, m_u_step_size_range;
   float m_u_color[4];
+  bool m_apply_gradient_shading;                                // rc1pisoadaptrenderer.h (off by default)
   int m_num_blocks[3];
  private:
   int m_kind;

@@ -83,14 +83,19 @@ typedef struct {
   int   num_blocks[3];          /* numBlocks (modes 1, 2) */
   int   weight_mode;
   int   row_begin, row_end, row_stride, threads;
+  int   apply_phong;            /* ApplyGradientPhongShading (needs grad_rgb) */
+  float ka, kd, ks, shininess;  /* BlinnPhong* */
+  float ispec[3];               /* BlinnPhongIspecular */
+  float light_pos[3];           /* LightSourcePosition */
 } orc_iso_params;
 
 /* ComputeBlocksFromVolume (rc1pisocustom/rc1custompisoadaptrenderer.cpp:20-113): nbx*nby*nbz floats each, x fastest. */
 void orc_block_minmax(const void* voxels, int dtype, int w, int h, int d, int nbx, int nby, int nbz,
                       float* out_min, float* out_max);
-/* main() of the three iso shaders; block_min/max may be NULL for mode 0.  out_iters: loop iterations per pixel. */
+/* main() of the three iso shaders; block_min/max may be NULL for mode 0.  out_iters: loop iterations per pixel.
+ * grad_rgb: optional W*H*D*3 gradient texture (ShadeBlinnPhong when p->apply_phong) or NULL. */
 uint64_t orc_iso_render(const orc_iso_params* p, const float* vol_r16f, const float* block_min, const float* block_max,
-                        float* out_rgba, uint32_t* out_iters);
+                        float* out_rgba, uint32_t* out_iters, const float* grad_rgb);
 
 /* ---- extinction-based shading (K12 SAT, K13 ray caster) ------------------------------------------------ */
 typedef struct {

@@ -10,6 +10,7 @@
 #include "oracle.h"
 #include "orc_common.h"
 #include "orc_ray.h"
+#include "orc_shade.h"
 #include <limits>
 #ifdef _OPENMP
 #include <omp.h>
@@ -24,6 +25,7 @@ struct IsoCtx {
   Tex3D vol;
   const float* bmin; const float* bmax;   // numBlocks.x * y * z floats, x fastest (order bz,by,bx of push_back)
   vec3 grid_size, nb;
+  PhongCtx ph;                            // ApplyGradientPhongShading == 1: gradient texture + light (ph.grad != NULL)
 };
 
 inline float sgn(float x) { return x > 0.0f ? 1.0f : (x < 0.0f ? -1.0f : 0.0f); }
@@ -81,8 +83,13 @@ float next_block_v2(const IsoCtx& c, vec3 ro, vec3 rd, ivec3 cur) {
 
 inline float fetch(const IsoCtx& c, vec3 tex_pos) { return c.vol.linear(tex_pos / c.grid_size); }
 inline bool crossing(float prev, float iso, float d) { return (prev <= iso && iso < d) || (prev >= iso && iso > d); }
-inline void composite(const orc_iso_params& p, vec4& dst) {
+inline void composite(const IsoCtx& c, vec4& dst, vec3 s_tex_pos) {
+  const orc_iso_params& p = *c.p;
   vec4 src(p.color[0], p.color[1], p.color[2], p.color[3]);
+  if (p.apply_phong && c.ph.grad) {                                                // adapt :143-146, v1 :233-236, v2 :251-253
+    vec3 rgb = shade_blinn_phong(c.ph, s_tex_pos, vec3(src.x, src.y, src.z));
+    src.x = rgb.x; src.y = rgb.y; src.z = rgb.z;
+  }
   src.x = src.x * src.w; src.y = src.y * src.w; src.z = src.z * src.w;
   dst = dst + (1.0f - dst.w) * src;
 }
@@ -109,7 +116,8 @@ uint32_t shade_pixel(const IsoCtx& c, int px, int py, float out[4], bool* hit) {
       float density = fetch(c, s_tex_pos);                                         // :130
       n++;
       if (crossing(prev, iso, density)) {                                          // :133-134
-        composite(p, dst);                                                         // :137-152 (shading off)
+        float tr = (iso - prev) / (density - prev);                                // :137 refine position
+        composite(c, dst, tex_pos + r.Dir * (s + tr * h));                         // :138-152
         if (dst.w > 0.99f) break;                                                  // :155
       }
       prev = density;                                                              // :159
@@ -141,7 +149,7 @@ uint32_t shade_pixel(const IsoCtx& c, int px, int py, float out[4], bool* hit) {
         if (crossing(prev, iso, density)) {
           float tt = (density - iso) / (density - prev);                           // :240
           t -= tt;                                                                 // :241 (quirk: fraction, not length)
-          composite(p, dst);
+          composite(c, dst, r.Origin + r.Dir * t + half);                          // :227
           if (dst.w > 0.99f) break;
         }
       }
@@ -176,7 +184,7 @@ uint32_t shade_pixel(const IsoCtx& c, int px, int py, float out[4], bool* hit) {
       if (crossing(prev, iso, density)) {
         float tt = (iso - prev) / (density - prev);
         t = t - h * (1.0f - tt);                                                   // :246
-        composite(p, dst);
+        composite(c, dst, r.Origin + r.Dir * t + half);                            // :247
         if (dst.w > 0.99f) break;
       }
     }
@@ -219,12 +227,16 @@ extern "C" void orc_block_minmax(const void* voxels, int dtype, int w, int h, in
 }
 
 extern "C" uint64_t orc_iso_render(const orc_iso_params* p, const float* vol_r16f, const float* block_min,
-                                   const float* block_max, float* out_rgba, uint32_t* out_iters) {
+                                   const float* block_max, float* out_rgba, uint32_t* out_iters, const float* grad_rgb) {
   IsoCtx c; c.p = p;
   c.vol.w = p->vol_w; c.vol.h = p->vol_h; c.vol.d = p->vol_d; c.vol.data = vol_r16f; c.vol.wmode = p->weight_mode;
   c.bmin = block_min; c.bmax = block_max;
   c.grid_size = vec3((float)p->vol_w, (float)p->vol_h, (float)p->vol_d) * vec3(p->voxel[0], p->voxel[1], p->voxel[2]);
   c.nb = vec3((float)p->num_blocks[0], (float)p->num_blocks[1], (float)p->num_blocks[2]);
+  c.ph.grad = grad_rgb; c.ph.w = p->vol_w; c.ph.h = p->vol_h; c.ph.d = p->vol_d; c.ph.wmode = p->weight_mode; c.ph.grid_size = c.grid_size;
+  c.ph.ka = p->ka; c.ph.kd = p->kd; c.ph.ks = p->ks; c.ph.shininess = p->shininess;
+  c.ph.ispec = vec3(p->ispec[0], p->ispec[1], p->ispec[2]); c.ph.light_pos = vec3(p->light_pos[0], p->light_pos[1], p->light_pos[2]);
+  c.ph.eye = vec3(p->eye[0], p->eye[1], p->eye[2]);
   int r0 = p->row_begin, r1 = p->row_end > 0 ? p->row_end : p->height, rs = p->row_stride > 0 ? p->row_stride : 1;
   uint64_t total = 0;
 #ifdef _OPENMP

@@ -32,7 +32,9 @@ class IsoParams(C.Structure):
                 ("tan_fovy", C.c_float), ("aspect", C.c_float), ("mode", C.c_int),
                 ("isovalue", C.c_float), ("step_small", C.c_float), ("step_large", C.c_float), ("step_range", C.c_float),
                 ("color", C.c_float * 4), ("num_blocks", C.c_int * 3), ("weight_mode", C.c_int),
-                ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
+                ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int),
+                ("apply_phong", C.c_int), ("ka", C.c_float), ("kd", C.c_float), ("ks", C.c_float), ("shininess", C.c_float),
+                ("ispec", C.c_float * 3), ("light_pos", C.c_float * 3)]
 
 
 class EbsParams(C.Structure):
@@ -133,7 +135,7 @@ def lib():
         L.orc_obj_render.restype = C.c_uint64
         L.orc_gradient.argtypes = [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]
         L.orc_block_minmax.argtypes = [_P, C.c_int] + [C.c_int] * 6 + [_P, _P]
-        L.orc_iso_render.argtypes = [C.POINTER(IsoParams), _P, _P, _P, _P, _P]
+        L.orc_iso_render.argtypes = [C.POINTER(IsoParams), _P, _P, _P, _P, _P, _P]
         L.orc_iso_render.restype = C.c_uint64
         _lib = L
     return _lib
@@ -239,7 +241,8 @@ def block_minmax(voxels, num_blocks):
 
 
 def iso_params(cam, width, height, vol_shape_zyx, mode, isovalue=0.5, step_small=0.05, step_large=1.0, step_range=0.1,
-               color=(0.66, 0.6, 0.05, 1.0), num_blocks=(4, 4, 4), voxel=(1.0, 1.0, 1.0), rows=None, threads=0):
+               color=(0.66, 0.6, 0.05, 1.0), num_blocks=(4, 4, 4), voxel=(1.0, 1.0, 1.0), rows=None, threads=0,
+               light=None, apply_phong=0):
     p = IsoParams()
     p.width, p.height = width, height
     p.vol_d, p.vol_h, p.vol_w = vol_shape_zyx
@@ -252,14 +255,19 @@ def iso_params(cam, width, height, vol_shape_zyx, mode, isovalue=0.5, step_small
     p.num_blocks[:] = num_blocks
     p.row_begin, p.row_end, p.row_stride = rows or (0, height, 1)
     p.threads = threads
+    p.apply_phong = apply_phong
+    if light is not None:
+        p.ka, p.kd, p.ks, p.shininess = light.ka, light.kd, light.ks, light.shininess
+        p.ispec[:] = list(light.ispecular)
+        p.light_pos[:] = list(light.position)
     return p
 
 
-def iso_render(p, vol_r16f, block_min=None, block_max=None, want_iters=False):
+def iso_render(p, vol_r16f, block_min=None, block_max=None, want_iters=False, grad=None):
     vol = np.ascontiguousarray(vol_r16f, np.float32)
     out = np.zeros((p.height, p.width, 4), np.float32)
     it = np.zeros((p.height, p.width), np.uint32) if want_iters else None
-    total = lib().orc_iso_render(C.byref(p), _ptr(vol), _ptr(block_min), _ptr(block_max), _ptr(out), _ptr(it))
+    total = lib().orc_iso_render(C.byref(p), _ptr(vol), _ptr(block_min), _ptr(block_max), _ptr(out), _ptr(it), _ptr(grad))
     return out, int(total), it
 
 

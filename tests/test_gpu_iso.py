@@ -122,3 +122,56 @@ def test_iso_errors(ctx):
     with pytest.raises(_capi.VrbError):
         r.read_blocks((4, 4, 4))
     r.close()
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+@pytest.mark.parametrize("n,dtype,size,eye_s,iso,model", [(64, np.uint8, (128, 96), (1, 1, 2), 0.5, 1), (80, np.uint16, (96, 120), (-1.2, 0.4, 1.1), 0.3, 2)])
+def test_iso_blinn_phong_parity(ctx, mode, n, dtype, size, eye_s, iso, model):
+    """ApplyGradientPhongShading == 1 (the iso shaders' ShadeBlinnPhong copy): the hit is shaded from the
+    gradient texture at the refined position.  Hit mask identical to the oracle, colour within 2/255."""
+    w, h = size
+    vox = inputs.synth_volume(n, dtype)
+    ctx.upload_volume(vox)
+    ctx.volume_gradient(model)
+    cam = inputs.make_camera(tuple(n * e for e in eye_s), (0, 0, 0), (0, 1, 0), 45.0, w, h)
+    light = inputs.default_light(n)
+    r = _capi.Renderer(ctx, KINDS[mode])
+    try:
+        prm = r.get_params(_capi.IsoParams()); prm.isovalue = iso; prm.apply_gradient_shading = 1
+        r.set_params(prm)
+        r.init(w, h)
+        r.update(cam, light); r.redraw()
+        got = r.read_frame(_capi.VRB_FRAME_RGBA32F); got8 = r.read_frame(_capi.VRB_FRAME_RGB8_OVER_WHITE)
+        prm.apply_gradient_shading = 0; r.set_params(prm); r.redraw()
+        plain = r.read_frame(_capi.VRB_FRAME_RGBA32F)
+        nb = tuple(prm.num_blocks)
+    finally:
+        r.close()
+        ctx.volume_gradient(0)
+    mn, mx = O.block_minmax(vox, nb)
+    p = O.iso_params(cam, w, h, vox.shape, mode, isovalue=iso, num_blocks=nb, light=light, apply_phong=1)
+    ref, _, _ = O.iso_render(p, O.volume_r16f(vox), mn, mx, grad=O.gradient(vox, model))
+    ref8 = O.blit_over_white(ref)
+    assert np.array_equal(got[..., 3], ref[..., 3])
+    d16 = float(np.abs(got - ref).max()) * 255.0
+    d8 = metrics.max_abs_delta(got8, ref8)
+    s = metrics.ssim(got8, ref8)
+    print(f"iso mode {mode} Blinn-Phong: max|d| {d16:.3f}/255 rgb8 {d8:.0f} SSIM {s:.5f}; shading changes the frame by {np.abs(got - plain).max() * 255:.1f}/255")
+    assert d16 <= 2.0 and d8 <= 2 and s >= 0.995
+    assert np.abs(got - plain).max() > 0.02
+
+
+def test_iso_gradient_shading_needs_a_gradient_texture(ctx):
+    vox = inputs.synth_volume(32, np.uint8)
+    ctx.upload_volume(vox)
+    cam = inputs.make_camera((32, 32, 64), (0, 0, 0), (0, 1, 0), 45.0, 32, 32)
+    r = _capi.Renderer(ctx, _capi.VRB_ISO_ADAPT)
+    try:
+        prm = r.get_params(_capi.IsoParams()); prm.apply_gradient_shading = 1
+        r.set_params(prm)
+        r.init(32, 32)
+        r.update(cam, inputs.default_light(32))
+        with pytest.raises(_capi.VrbError):
+            r.redraw()
+    finally:
+        r.close()
