@@ -220,7 +220,7 @@ def run_cuda(args):
     prm.tf_in_smem = args.tf_smem
     prm.exact_filter = args.exact
     # few pixels per GPU: the per-ray dependent chain bounds the frame, so more lanes share a ray (include/vrb200.h)
-    depth_split = args.depth_split if args.depth_split >= 0 else (0 if world == 1 else (2 if world == 2 else 4))   # tools/partition_sweep.py: best K per split
+    depth_split = args.depth_split if args.depth_split >= 0 else (0 if world == 1 else (2 if world <= 4 else 4))   # tools/partition_sweep.py: best K per split
     prm.depth_split = depth_split
     r.set_params(prm)
     if world > 1:

@@ -51,23 +51,24 @@ constexpr int WARP_W = 8, WARP_H = 4, CTA_THREADS = 128;
 #define VRB_RC1_QUAD2X2 1
 #endif
 #ifndef VRB_RC1_MINB
-#define VRB_RC1_MINB 5      // resident CTAs per SM the register allocation is capped for.  5 -> 96 registers, no spills in
-                            // the pipelined march; measured on B200 for the C2 frame (L2 flushed, tools/partition_sweep.py):
-                            // 0.503 ms (6 CTAs, 80 registers, 12 B spilled), 0.449 ms (5 CTAs), 0.452 ms (4 CTAs, 128 registers)
+#define VRB_RC1_MINB 4      // resident CTAs per SM the register allocation is capped for.  Measured on B200 for the C2 frame
+                            // (L2 flushed, tools/partition_sweep.py): 6 CTAs / 80 registers (22 B spilled) 0.502 ms,
+                            // 5 CTAs / 96 registers 0.443 ms, 4 CTAs / 128 registers (no spills, pipeline depth 2) 0.442 ms —
+                            // and with the image split over 8 GPUs 0.228 / 0.204 / 0.147 ms per rank
 #endif
 #ifndef VRB_RC1_UNROLL
 #define VRB_RC1_UNROLL 4
 #endif
 constexpr int UNROLL = VRB_RC1_UNROLL;    // independent texture fetches in flight per ray and group
 #ifndef VRB_RC1_PIPE
-#define VRB_RC1_PIPE 1      // groups fetched ahead of the one being composited (software pipeline depth)
+#define VRB_RC1_PIPE 2      // groups fetched ahead of the one being composited (software pipeline depth; 3 brings nothing more)
 #endif
 constexpr int PIPE = VRB_RC1_PIPE;
 #ifndef VRB_RC1_BF
 #define VRB_RC1_BF 1        // branch-free compositing of a group (see process_group)
 #endif
 #ifndef VRB_SPLIT_PIPE
-#define VRB_SPLIT_PIPE 0
+#define VRB_SPLIT_PIPE 1      // depth-split kernels: the fetches of a segment's two groups are issued together
 #endif
 #ifndef VRB_SPLIT_MINB
 #define VRB_SPLIT_MINB 4
@@ -367,9 +368,13 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(cons
       float hk[UNROLL], tk[UNROLL];
 #pragma unroll
       for (int k = 0; k < UNROLL; k++) hk[k] = step;
-      // PIPE groups are prefetched ahead of the one being composited: sg[i] / fg[i] / dg[i] = start, FULL flag and
-      // fetched densities of the i-th group from the current one (all indices are compile-time after unrolling).
-      float sg[PIPE + 2], dg[PIPE + 1][UNROLL];
+      // PIPE groups are prefetched ahead of the one being composited: sg[i] / fg[i] = start and FULL flag of the i-th group
+      // from the current one.  The fetched densities live in NB = PIPE + 1 register buffers that are ROTATED BY NAME —
+      // the loop body is unrolled NB times with compile-time buffer indices — never copied: a register move out of the
+      // destination of an in-flight texture fetch waits for that fetch, which would put the whole round trip back on the
+      // ray's dependent chain every iteration.
+      constexpr int NB = PIPE + 1;
+      float sg[PIPE + 2], dg[NB][UNROLL];
       bool fg[PIPE + 1];
       sg[0] = 0.0f;
 #pragma unroll
@@ -378,21 +383,22 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(cons
         if (!fg[i]) sg[i + 1] = sg[i];
         if (fg[i]) fetch_group(a, r, tk, dg[i]);
       }
-      while (fg[0] && !r.done) {
-        float tkn[UNROLL];
-        fg[PIPE] = fg[PIPE - 1] && full_geom(sg[PIPE], D, step, tkn, sg[PIPE + 1]);
-        if (fg[PIPE]) fetch_group(a, r, tkn, dg[PIPE]);
-        float s_dummy;
-        full_geom(sg[0], D, step, tk, s_dummy);              // positions of the current group again (cheaper than carrying them)
-        process_group<COUNT, TF_SMEM, EXACT, true, GRAD>(a, s_tf, s_mask, r, tk, hk, dg[0], nsamp);
+      bool run = true;
+      while (run) {
 #pragma unroll
-        for (int i = 0; i < PIPE; i++) {
-          fg[i] = fg[i + 1];
+        for (int j = 0; j < NB; j++) {
+          if (!(fg[0] && !r.done)) { run = false; break; }
+          float tkn[UNROLL];
+          fg[PIPE] = fg[PIPE - 1] && full_geom(sg[PIPE], D, step, tkn, sg[PIPE + 1]);
+          if (fg[PIPE]) fetch_group(a, r, tkn, dg[(j + PIPE) % NB]);
+          float s_dummy;
+          full_geom(sg[0], D, step, tk, s_dummy);            // positions of the current group again (cheaper than carrying them)
+          process_group<COUNT, TF_SMEM, EXACT, true, GRAD>(a, s_tf, s_mask, r, tk, hk, dg[j], nsamp);
 #pragma unroll
-          for (int k = 0; k < UNROLL; k++) dg[i][k] = dg[i + 1][k];
+          for (int i = 0; i < PIPE; i++) fg[i] = fg[i + 1];
+#pragma unroll
+          for (int i = 0; i <= PIPE; i++) sg[i] = sg[i + 1];
         }
-#pragma unroll
-        for (int i = 0; i <= PIPE; i++) sg[i] = sg[i + 1];
       }
       s = sg[0];
       // at most one group is left: the one that holds the end of the ray
@@ -488,26 +494,21 @@ __device__ __forceinline__ void march_groups(const Rc1Args& a, const uint4* s_tf
   float s = (float)(g0 * UNROLL) * step;
   int g = 0;
 #if VRB_SPLIT_PIPE
-  {
-    // software pipeline over the FULL groups of the segment, as in rc1pass_kernel
-    float hk[UNROLL], tk[UNROLL], dkc[UNROLL];
+  if (ng == 2 && s < D) {
+    // both groups of the segment FULL: their 2 * UNROLL classification fetches are issued together (one texture round trip
+    // per segment instead of two), then the groups are composited in order
+    float tk0[UNROLL], tk1[UNROLL], d0[UNROLL], d1[UNROLL], hk[UNROLL];
 #pragma unroll
     for (int k = 0; k < UNROLL; k++) hk[k] = step;
-    float s_end = s;
-    bool fc = ng > 0 && full_geom(s, D, step, tk, s_end);
-    if (fc) fetch_group(a, r, tk, dkc);
-    while (fc && !r.done) {
-      float tkn[UNROLL], dkn[UNROLL];
-      float s_end_n = s_end;
-      const bool fn = (g + 1 < ng) && full_geom(s_end, D, step, tkn, s_end_n);
-      if (fn) fetch_group(a, r, tkn, dkn);
-      float s_dummy;
-      full_geom(s, D, step, tk, s_dummy);
-      process_group<COUNT, true, true, true>(a, s_tf, s_mask, r, tk, hk, dkc, nsamp);
-      s = s_end; g++;
-#pragma unroll
-      for (int k = 0; k < UNROLL; k++) dkc[k] = dkn[k];
-      s_end = s_end_n; fc = fn;
+    float s1 = s, s2 = s;
+    const bool f0 = full_geom(s, D, step, tk0, s1);
+    const bool f1 = f0 && full_geom(s1, D, step, tk1, s2);
+    if (f1) {
+      fetch_group(a, r, tk0, d0);
+      fetch_group(a, r, tk1, d1);
+      process_group<COUNT, true, true, true>(a, s_tf, s_mask, r, tk0, hk, d0, nsamp);
+      if (!r.done) process_group<COUNT, true, true, true>(a, s_tf, s_mask, r, tk1, hk, d1, nsamp);
+      return;
     }
   }
 #endif
@@ -582,38 +583,40 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_SPLIT_MINB) rc1pass_split_ker
     float4 P = make_float4(0.f, 0.f, 0.f, 0.f);               // running prefix, identical in the K lanes of a pixel
     unsigned nseq = 0;                                        // samples of the sequential march so far
     bool open = hit;                                          // this pixel's ray has neither ended nor terminated
-    for (int c = 0; __any_sync(0xffffffffu, open); c++) {
-      r.dst = make_float4(0.f, 0.f, 0.f, 0.f); r.done = false;
+    // One march call per loop iteration: a pixel whose running alpha passes 0.99 inside segment kstar goes into the
+    // "redo" state — in the next iteration only its lane kstar marches, the same segment again but from the exact prefix —
+    // while the other pixels of the warp walk their next chunk.
+    int c = 0;                                                // chunk index of this pixel
+    int redo_k = -1;                                          // >= 0: redo state, segment that holds the terminating sample
+    float4 Pstar = P;
+    while (__any_sync(0xffffffffu, open)) {
+      const bool redo = redo_k >= 0;
+      if (redo) r.dst = Pstar; else r.dst = make_float4(0.f, 0.f, 0.f, 0.f);
+      r.done = false;
       unsigned n1 = 0;
       const int g0 = (c * K + seg) * SPLIT_G;
-      if (open) march_groups<COUNT>(a, s_tf, s_mask, r, D, g0, SPLIT_G, n1);
-      float4 Pstar = P;
+      if (open && (!redo || redo_k == seg)) march_groups<COUNT>(a, s_tf, s_mask, r, D, g0, SPLIT_G, n1);
       int kstar = -1;
+      float4 Pnew = P;
+      unsigned nnew = nseq;
 #pragma unroll
       for (int j = 0; j < K; j++) {
         const int src = pi + j * PIX;
         const float sx = __shfl_sync(0xffffffffu, r.dst.x, src), sy = __shfl_sync(0xffffffffu, r.dst.y, src);
         const float sz = __shfl_sync(0xffffffffu, r.dst.z, src), sw = __shfl_sync(0xffffffffu, r.dst.w, src);
         const unsigned nj = COUNT ? __shfl_sync(0xffffffffu, n1, src) : 0u;
-        if (kstar < 0 && open) {
-          const float t = 1.0f - P.w;
-          const float4 m = make_float4(fmaf(t, sx, P.x), fmaf(t, sy, P.y), fmaf(t, sz, P.z), fmaf(t, sw, P.w));
-          if (m.w > 0.99f) { kstar = j; Pstar = P; } else { P = m; nseq += nj; }
+        if (redo) {
+          if (j == redo_k) { Pnew = make_float4(sx, sy, sz, sw); nnew = nseq + nj; }   // the exact sequential result
+        } else if (kstar < 0 && open) {
+          const float t = 1.0f - Pnew.w;
+          const float4 m = make_float4(fmaf(t, sx, Pnew.x), fmaf(t, sy, Pnew.y), fmaf(t, sz, Pnew.z), fmaf(t, sw, Pnew.w));
+          if (m.w > 0.99f) { kstar = j; Pstar = Pnew; } else { Pnew = m; nnew += nj; }
         }
       }
-      if (open && kstar == seg) {                             // this lane's segment holds the terminating sample
-        r.dst = Pstar; r.done = false;
-        unsigned n2 = 0;
-        march_groups<COUNT>(a, s_tf, s_mask, r, D, g0, SPLIT_G, n2);
-        P = r.dst; nseq += n2;
-      }
-      {
-        const int src = kstar >= 0 ? pi + kstar * PIX : lane;   // kstar differs per pixel: unconditional shuffles
-        P.x = __shfl_sync(0xffffffffu, P.x, src); P.y = __shfl_sync(0xffffffffu, P.y, src);
-        P.z = __shfl_sync(0xffffffffu, P.z, src); P.w = __shfl_sync(0xffffffffu, P.w, src);
-        if (COUNT) nseq = __shfl_sync(0xffffffffu, nseq, src);
-      }
-      if (kstar >= 0 || !((float)(c + 1) * chunk_len < D)) open = false;
+      P = Pnew; nseq = nnew;
+      if (redo) { open = false; redo_k = -1; }
+      else if (kstar >= 0) redo_k = kstar;                    // same chunk again, lane kstar only
+      else { if (!((float)(c + 1) * chunk_len < D)) open = false; c++; }
     }
     if (seg == 0 && valid) {
       const float4 o4 = hit ? P : make_float4(0.f, 0.f, 0.f, 0.f);
