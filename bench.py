@@ -25,6 +25,19 @@ VOL_N, IMG_W, IMG_H, STEP = 512, 1024, 1024, 0.5
 BYTES_PER_SAMPLE_L1TEX = 32.0   # 8 fp16 texels + 2 RGBA16F texels
 
 
+_RESULT_FD = None
+
+
+def emit(line):
+    """Writes the result line to the process's real stdout (see main())."""
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def workload_name(skip):
     s = f"skip{skip}" if skip else "noskip"
     return f"rc1pass_{VOL_N}c_u16_{IMG_W}x{IMG_H}_step{STEP}_{s}"
@@ -184,7 +197,7 @@ def run_reference(args):
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": "full 1024x1024 frame per step, OpenMP over rows, oracle/liboracle.so"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_cuda(args):
@@ -372,7 +385,7 @@ def run_cuda(args):
             v, cores, total, secs = cpu_frame(vox, table, cam, repeats=2)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"full {IMG_W}x{IMG_H} frame ({total} samples, best of 2, {secs:.2f} s), oracle/liboracle.so OpenMP over rows"}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         barrier()
         r.set_peers([], rank, _capi.VRB_GATHER_NONE)
@@ -396,6 +409,13 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="omit the cpu_baseline leg")
     ap.add_argument("--depth-split", type=int, default=-1, help="lanes per ray (0/1, 2, 4, 8); -1 = by the number of GPUs")
     args = ap.parse_args()
+    # The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on the first
+    # collective), so everything but the result line goes to stderr: fd 1 is pointed at fd 2 and the line is written to the
+    # saved descriptor by emit().
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
