@@ -418,6 +418,8 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(cons
       const float dvx = dir.x * a.inv_voxel[0], dvy = dir.y * a.inv_voxel[1], dvz = dir.z * a.inv_voxel[2];
       const float idx_ = 1.0f / dvx, idy_ = 1.0f / dvy, idz_ = 1.0f / dvz;   // +-inf where the ray is axis-parallel
       const float fB = (float)a.skip_block, invB = 1.0f / fB, inv_step = 1.0f / step;
+      // (A software-pipelined version of this loop — block look-up and classification fetches issued one group ahead —
+      // was measured and is 10 % slower at every rank count: the fetches wasted at each leap cost more than the overlap gains.)
       int k = 0;
       while (!r.done) {
         const float s = (float)k * step;

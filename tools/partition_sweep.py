@@ -29,7 +29,7 @@ def main():
                 r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
                 r.init(w, h)
                 prm = r.get_params(_capi.Rc1PassParams()); prm.step_size = 0.5; prm.depth_split = K
-                prm.exact_filter = int(os.environ.get("SWEEP_EXACT", "1")); prm.tf_in_smem = int(os.environ.get("SWEEP_TFSMEM", "1"))
+                prm.exact_filter = int(os.environ.get("SWEEP_EXACT", "1")); prm.tf_in_smem = int(os.environ.get("SWEEP_TFSMEM", "1")); prm.skip_block = int(os.environ.get("SWEEP_SKIP", "0"))
                 r.set_params(prm)
                 r.set_partition(rank, world, 32)
                 r.update(cam, inputs.default_light(n))
@@ -40,7 +40,7 @@ def main():
                     ms.append(r.counters()[1])
                 worst = max(worst, float(np.median(ms[3:])))
                 r.close()
-            print(json.dumps({"lib": os.path.basename(_capi.LIB_PATH), "split_g": os.environ.get("VRB_SPLIT_G", ""), "exact": os.environ.get("SWEEP_EXACT", "1"), "tf_smem": os.environ.get("SWEEP_TFSMEM", "1"), "n_ranks": world, "depth_split": K, "kernel_ms_worst_rank": worst}), flush=True)
+            print(json.dumps({"lib": os.path.basename(_capi.LIB_PATH), "split_g": os.environ.get("VRB_SPLIT_G", ""), "exact": os.environ.get("SWEEP_EXACT", "1"), "tf_smem": os.environ.get("SWEEP_TFSMEM", "1"), "skip_block": os.environ.get("SWEEP_SKIP", "0"), "n_ranks": world, "depth_split": K, "kernel_ms_worst_rank": worst}), flush=True)
 
 
 if __name__ == "__main__":
