@@ -314,6 +314,7 @@ struct DosCone {
 
 struct DosShader {
   static constexpr bool OBJECT_SPACE = false;
+  static constexpr int PHONG_KIND = 0;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   struct Args {
     cudaTextureObject_t mip[DOS_MAX_LEVELS]; float mip_res[DOS_MAX_LEVELS][3]; int n_levels;
     DosCone occ, sdw;
@@ -502,7 +503,6 @@ class DosRenderer : public RendererImpl {
                     p.type_of_shadow >= 0 && p.type_of_shadow <= 2 && p.base_level_sigma0 > 0.0f && p.integration_half_step_multiplier > 0.0f &&
                     p.gaussian_sigma_limit_multiplier > 0.0f,
                 VRB_ERR_INVALID, "dos set_params: bad value");
-    VRB_REQUIRE(!p.apply_gradient_shading, VRB_ERR_UNSUPPORTED, "dos set_params: gradient shading needs a gradient volume (not uploaded)");
     VRB_REQUIRE(light_cache_params_ok(p.use_light_cache, p.light_cache_resolution), VRB_ERR_INVALID, "dos set_params: bad light cache resolution");
     if (memcmp(&p, &prm_, sizeof(p)) != 0) cones_valid_ = false;
     prm_ = p;
@@ -549,7 +549,9 @@ class DosRenderer : public RendererImpl {
     if (rc == VRB_OK) rc = ensure_precompute();
     if (rc != VRB_OK) return rc;
     MarchArgs a{};
-    if (!fill_march_args(*this, prm_.step_size, prm_.apply_occlusion, prm_.apply_shadow, a)) return VRB_OK;
+    const bool phong = prm_.apply_gradient_shading != 0;   // ApplyPhongShading = m_apply_gradient_shading && GetCurrentGradientTexture()
+    VRB_REQUIRE(!phong || (ctx->vol.tex_grad_pt && ctx->vol.grad_gen == ctx->vol.generation), VRB_ERR_INVALID, "RC1PConeTracingDirOcclusionShading: gradient shading needs vrb_volume_gradient() for the current volume");
+    if (!fill_march_args(*this, prm_.step_size, prm_.apply_occlusion, prm_.apply_shadow, a, phong)) return VRB_OK;
     DosShader::Args s{};
     s.n_levels = pyr_.n_levels;
     for (int l = 0; l < pyr_.n_levels; l++) { s.mip[l] = pyr_.tex[l]; s.mip_res[l][0] = (float)pyr_.lw[l]; s.mip_res[l][1] = (float)pyr_.lh[l]; s.mip_res[l][2] = (float)pyr_.ld[l]; }

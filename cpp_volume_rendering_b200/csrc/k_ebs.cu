@@ -23,6 +23,7 @@ struct EbsArgs {
   int apply_occlusion, apply_shadow, ao_shells; float ao_radius;
   float cone_angle, interval, initial_step, weight, max_distance; int type_of_shadow;
   float light_pos[3], light_fwd[3], ka, kd;
+  PhongParams phong;                 // ApplyPhongShading (grad_pt == 0: off)
   uint2* frame; uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
   PeerSignal sig;
   unsigned long long* samples;
@@ -136,6 +137,7 @@ __device__ __forceinline__ EbsConst make_ebs_const(const EbsArgs& a) {
 // file enables its ExtinctionAmbientOcclusion / ExtinctionDirectionalShadows are the image-space shader's functions above.
 struct EbsShader {
   static constexpr bool OBJECT_SPACE = false;
+  static constexpr int PHONG_KIND = 1;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   typedef EbsArgs Args;
   typedef EbsConst Const;
   static __device__ __forceinline__ Const prepare(const MarchArgs&, const Args& s) { return make_ebs_const(s); }
@@ -204,14 +206,17 @@ __global__ void __launch_bounds__(EBS_THREADS, 4) ebs_kernel(const __grid_consta
           const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
           float4 src = make_float4(fmaf(w, r1.x - r0.x, r0.x), fmaf(w, r1.y - r0.y, r0.y), fmaf(w, b1.x - b0.x, b0.x), fmaf(w, b1.y - b0.y, b0.y));
           if (src.w > 0.0f) {
-            // ShadeSample (:500-551), ApplyPhongShading == 0
+            // ShadeSample (:500-551)
             float ka = 0.0f, kd = 0.0f, Iocc = 0.0f, Isdw = 0.0f;
             if (a.apply_occlusion) { ka = a.ka; Iocc = extinction_ao(a, c, tx); }
             if (a.apply_shadow) { kd = a.kd; Isdw = directional_shadows(a, c, tx); }
-            const float k = 1.0f / (ka + kd);
-            src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
-            src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
-            src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
+            if (!phong_shade_sample(1, a.phong, tx, c.sizes, res, mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]),
+                                    mk3(a.eye[0], a.eye[1], a.eye[2]), ka, kd, a.apply_shadow != 0, Iocc, Isdw, src)) {   // :524-545
+              const float k = 1.0f / (ka + kd);
+              src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
+              src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
+              src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
+            }
             const float alpha = 1.0f - expf(-src.w * h);
             const float wgt = (1.0f - dst.w) * alpha;
             dst.x = fmaf(wgt, src.x, dst.x); dst.y = fmaf(wgt, src.y, dst.y); dst.z = fmaf(wgt, src.z, dst.z); dst.w += wgt;
@@ -270,7 +275,6 @@ class EbsRenderer : public RendererImpl {
     VRB_REQUIRE(pod && size == sizeof(vrb_ebs_params), VRB_ERR_INVALID, "ebs set_params: size %zu != sizeof(vrb_ebs_params) %zu", size, sizeof(vrb_ebs_params));
     const vrb_ebs_params p = *(const vrb_ebs_params*)pod;
     VRB_REQUIRE(p.step_size > 0.0f && p.ambient_occlusion_shells >= 1 && p.dir_shadow_sample_interval > 0.0f, VRB_ERR_INVALID, "ebs set_params: bad value");
-    VRB_REQUIRE(!p.apply_gradient_shading, VRB_ERR_UNSUPPORTED, "ebs set_params: gradient shading needs a gradient volume (not uploaded)");
     VRB_REQUIRE(light_cache_params_ok(p.use_light_cache, p.light_cache_resolution), VRB_ERR_INVALID, "ebs set_params: bad light cache resolution");
     prm_ = p;
     return VRB_OK;
@@ -312,9 +316,12 @@ class EbsRenderer : public RendererImpl {
     a.interval = prm_.dir_shadow_sample_interval; a.initial_step = prm_.dir_shadow_initial_step;
     a.weight = prm_.dir_shadow_user_interface_weight; a.max_distance = prm_.dir_cone_max_distance; a.type_of_shadow = prm_.type_of_shadow;
     a.ka = light.ka; a.kd = light.kd;
+    const bool phong = prm_.apply_gradient_shading != 0;   // ApplyPhongShading = m_apply_gradient_shading && GetCurrentGradientTexture()
+    VRB_REQUIRE(!phong || (v.tex_grad_pt && v.grad_gen == v.generation), VRB_ERR_INVALID, "RC1PExtinctionBasedShading: gradient shading needs vrb_volume_gradient() for the current volume");
+    fill_phong(*this, phong, a.phong);
     if (prm_.use_light_cache) {                                                                // :127-135
       MarchArgs m{};
-      if (!fill_march_args(*this, prm_.step_size, a.apply_occlusion, a.apply_shadow, m)) return VRB_OK;
+      if (!fill_march_args(*this, prm_.step_size, a.apply_occlusion, a.apply_shadow, m, phong)) return VRB_OK;
       return redraw_object_space<EbsShader>(*this, cache_, prm_.light_cache_resolution, m, a, prm_.count_samples != 0);
     }
     a.frame = (uint2*)frame; a.samples = d_samples;

@@ -228,6 +228,7 @@ __shared__ float s_vct_cone[3][VCT_CONE_TABLE];
 
 struct VctShader {
   static constexpr bool OBJECT_SPACE = false;
+  static constexpr int PHONG_KIND = 1;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   struct Args {
     cudaTextureObject_t mip[VCT_MAX_LEVELS];
     float mip_res[VCT_MAX_LEVELS][3];
@@ -381,7 +382,6 @@ class VctRenderer : public RendererImpl {
     VRB_REQUIRE(pod && size == sizeof(vrb_vct_params), VRB_ERR_INVALID, "vct set_params: size %zu != sizeof(vrb_vct_params) %zu", size, sizeof(vrb_vct_params));
     const vrb_vct_params p = *(const vrb_vct_params*)pod;
     VRB_REQUIRE(p.step_size > 0.0f && p.cone_step_size > 0.0f && p.cone_number_of_samples >= 0, VRB_ERR_INVALID, "vct set_params: bad value");
-    VRB_REQUIRE(!p.apply_gradient_shading, VRB_ERR_UNSUPPORTED, "vct set_params: gradient shading needs a gradient volume (not uploaded)");
     VRB_REQUIRE(light_cache_params_ok(p.use_light_cache, p.light_cache_resolution), VRB_ERR_INVALID, "vct set_params: bad light cache resolution");
     prm_ = p;
     return VRB_OK;
@@ -423,7 +423,9 @@ class VctRenderer : public RendererImpl {
     if (rc == VRB_OK) rc = pyr_.ensure(ctx, true);
     if (rc != VRB_OK) return rc;
     MarchArgs a{};
-    if (!fill_march_args(*this, prm_.step_size, prm_.apply_ambient_occlusion, prm_.apply_directional_shadows, a)) return VRB_OK;
+    const bool phong = prm_.apply_gradient_shading != 0;   // ApplyPhongShading = m_apply_gradient_shading && GetCurrentGradientTexture() (vctrenderer.cpp:211)
+    VRB_REQUIRE(!phong || (ctx->vol.tex_grad_pt && ctx->vol.grad_gen == ctx->vol.generation), VRB_ERR_INVALID, "RC1PVoxelConeTracingSGPU: gradient shading needs vrb_volume_gradient() for the current volume");
+    if (!fill_march_args(*this, prm_.step_size, prm_.apply_ambient_occlusion, prm_.apply_directional_shadows, a, phong)) return VRB_OK;
     VctShader::Args s{};
     s.n_levels = pyr_.n_levels;
     for (int l = 0; l < pyr_.n_levels; l++) { s.mip[l] = pyr_.tex[l]; s.mip_res[l][0] = (float)pyr_.lw[l]; s.mip_res[l][1] = (float)pyr_.lh[l]; s.mip_res[l][2] = (float)pyr_.ld[l]; }

@@ -14,6 +14,7 @@ namespace vrb {
 #ifdef __CUDACC__
 struct LightCacheShader {
   static constexpr bool OBJECT_SPACE = true;
+  static constexpr int PHONG_KIND = 1;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   struct Args { const __half2* cache; int dims[3]; };
   struct Const { f3 sizes; };
   static __device__ __forceinline__ void prepare_block(const MarchArgs&, const Args&) {}

@@ -1,7 +1,7 @@
 // Shared front-to-back march of the shadowed DVR renderers (VCT, DOS cone tracing): the common part of
 // vct_ray_bbox_marching.comp:191-264 and crtgt_ray_bbox_marching.comp — ray setup, half-step sampling, classification,
 // `k*(c*Iocc*ka + c*Isdw*kd)` shading, exp() opacity, ERT at 0.99 — around a per-renderer shading functor.
-//   struct Shader { static constexpr bool OBJECT_SPACE; struct Args {...}; struct Const {...};
+//   struct Shader { static constexpr bool OBJECT_SPACE; static constexpr int PHONG_KIND; struct Args {...}; struct Const {...};
 //     static __device__ void  prepare_block(const MarchArgs&, const Args&);   // all threads, before the CTA barrier: shared tables
 //     static __device__ Const prepare(const MarchArgs&, const Args&);
 //     // called by all 32 lanes of the converged warp; lanes with need == true get their sample at tx shaded
@@ -22,6 +22,7 @@ struct MarchArgs {
   float eye[3], lookat[9], tan_fovy, aspect, step;
   float light_pos[3], ka, kd;
   int apply_occlusion, apply_shadow;
+  PhongParams phong;                 // ApplyPhongShading (grad_pt == 0: off)
   uint2* frame; uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
   PeerSignal sig;
   unsigned long long* samples;
@@ -156,10 +157,13 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
           float ka = 0.0f, kd = 0.0f;
           if (a.apply_occlusion) ka = a.ka;
           if (a.apply_shadow) kd = a.kd;
-          const float k = 1.0f / (ka + kd);
-          src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
-          src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
-          src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
+          if (!phong_shade_sample(S::PHONG_KIND, a.phong, tx, sizes, res, mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]),
+                                  mk3(a.eye[0], a.eye[1], a.eye[2]), ka, kd, a.apply_shadow != 0, Iocc, Isdw, src)) {
+            const float k = 1.0f / (ka + kd);
+            src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
+            src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
+            src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
+          }
           const float alpha = 1.0f - expf(-src.w * h);
           const float wgt = (1.0f - dst.w) * alpha;
           dst.x = fmaf(wgt, src.x, dst.x); dst.y = fmaf(wgt, src.y, dst.y); dst.z = fmaf(wgt, src.z, dst.z); dst.w += wgt;
@@ -192,7 +196,14 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
 }
 
 // Fills the renderer-independent arguments from the renderer state; returns false when this rank owns no tiles.
-inline bool fill_march_args(const RendererImpl& r, float step, int apply_occlusion, int apply_shadow, MarchArgs& a) {
+inline void fill_phong(const RendererImpl& r, bool on, PhongParams& ph) {
+  ph.grad_pt = 0;
+  if (!on) return;
+  ph.grad_pt = r.ctx->vol.tex_grad_pt; ph.ks = r.light.ks; ph.shininess = r.light.shininess;
+  for (int i = 0; i < 3; i++) ph.ispec[i] = r.light.ispecular[i];
+}
+
+inline bool fill_march_args(const RendererImpl& r, float step, int apply_occlusion, int apply_shadow, MarchArgs& a, bool phong = false) {
   const Volume& v = r.ctx->vol;
   const TransferFunction& t = r.ctx->tf;
   a.vol = v.tex; a.vol_quad = v.tex_quad;
@@ -204,6 +215,7 @@ inline bool fill_march_args(const RendererImpl& r, float step, int apply_occlusi
   for (int i = 0; i < 9; i++) a.lookat[i] = r.cam.lookat[i];
   a.tan_fovy = r.cam.tan_fovy; a.aspect = r.cam.aspect; a.step = step;
   a.ka = r.light.ka; a.kd = r.light.kd; a.apply_occlusion = apply_occlusion; a.apply_shadow = apply_shadow;
+  fill_phong(r, phong, a.phong);
   a.frame = (uint2*)r.frame; a.samples = r.d_samples;
   a.n_peers = r.n_peer_frames;
   for (int q = 0; q < r.n_peer_frames; q++) a.peer[q] = (uint2*)r.peer_frames[q];

@@ -112,4 +112,44 @@ __device__ __forceinline__ f3 tex3d_rgb_exact(cudaTextureObject_t pt, f3 p, f3 r
              lerp3(t[0][0][0].y, t[0][0][1].y, t[0][1][0].y, t[0][1][1].y, t[1][0][0].y, t[1][0][1].y, t[1][1][0].y, t[1][1][1].y),
              lerp3(t[0][0][0].z, t[0][0][1].z, t[0][1][0].z, t[0][1][1].z, t[1][0][0].z, t[1][0][1].z, t[1][1][0].z, t[1][1][1].z));
 }
+
+// ApplyPhongShading == 1 branch of the ShadeSample functions of the shadowed DVR shaders (rc1pdosct/ray_bbox_marching.comp:630-649,
+// rc1pextbsd/ebs_ray_bbox_marching.comp:524-545, rc1pvctsg/vct_ray_bbox_marching.comp:163-183, _common_shaders/obj_ray_marching.comp:
+// 236-255).  kind 0: the DOS cone tracer's formula; kind 1: EBS / VCT (Iocc = 1) / object-space march.  Returns false when the
+// branch is off (grad_pt == 0) and the caller applies the plain formula; with a zero gradient L keeps the unshaded colour.
+struct PhongParams { cudaTextureObject_t grad_pt; float ks, shininess, ispec[3]; };
+static __device__ __noinline__ bool phong_shade_sample(int kind, const PhongParams& ph, f3 tx, f3 sizes, f3 res, f3 light_pos, f3 eye,
+                                                float ka, float kd, bool apply_shadow, float Iocc, float Isdw, float4& L) {
+  if (!ph.grad_pt) return false;
+  const float ks = apply_shadow ? ph.ks : 0.0f;
+  f3 g = tex3d_rgb_exact(ph.grad_pt, div3(tx, sizes), res);
+  if (g.x != 0.0f || g.y != 0.0f || g.z != 0.0f) {
+    const f3 Wpos = sub3(tx, scale3(sizes, 0.5f));
+    g = normalize_rn(g);
+    const f3 light_direction = normalize_rn(sub3(light_pos, Wpos));
+    const f3 eye_direction = normalize_rn(sub3(eye, Wpos));
+    const f3 halfway = normalize_rn(add3(eye_direction, light_direction));
+    const float dd = gmax(0.0f, dot_rn(g, light_direction)), ds = gmax(0.0f, dot_rn(halfway, g));
+    const float pw = powf(ds, ph.shininess);
+    const float k = __fdiv_rn(1.0f, __fadd_rn(ka, kd));
+    const float rgb[3] = {L.x, L.y, L.z};
+    float o[3];
+    if (kind == 0) {
+      const float sc = __fmul_rn(k, __fadd_rn(__fmul_rn(Iocc, ka), __fmul_rn(__fmul_rn(Isdw, kd), dd)));
+      const float sp = __fmul_rn(__fmul_rn(Isdw, ks), pw);
+#pragma unroll
+      for (int i = 0; i < 3; i++) o[i] = __fadd_rn(__fmul_rn(rgb[i], sc), __fmul_rn(ph.ispec[i], sp));
+    } else {
+#pragma unroll
+      for (int i = 0; i < 3; i++) {
+        const float amb = __fmul_rn(__fmul_rn(rgb[i], Iocc), ka);
+        const float dif = __fmul_rn(Isdw, __fmul_rn(__fmul_rn(rgb[i], kd), dd));
+        const float spe = __fmul_rn(Isdw, __fmul_rn(__fmul_rn(ks, ph.ispec[i]), pw));
+        o[i] = __fadd_rn(__fmul_rn(k, __fadd_rn(amb, dif)), spe);
+      }
+    }
+    L.x = o[0]; L.y = o[1]; L.z = o[2];
+  }
+  return true;
+}
 }  // namespace vrb

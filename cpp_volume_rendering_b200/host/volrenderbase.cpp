@@ -209,6 +209,7 @@ bool CudaRC1PConeTracingDirOcclusionShading::Update(vis::Camera* camera) {
   vrb_dos_params p;
   if (a->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
   p.step_size = m_u_step_size; p.apply_occlusion = glsl_apply_occlusion ? 1 : 0; p.apply_shadow = glsl_apply_shadow ? 1 : 0;
+  p.apply_gradient_shading = (m_apply_gradient_shading && m_ext_data_manager->HasGradientTexture()) ? 1 : 0;
   p.type_of_shadow = type_of_shadow;
   p.occ_cone_half_angle = occ_cone_half_angle; p.occ_initial_step = occ_initial_step; p.occ_covered_distance = occ_covered_distance;
   p.occ_ui_weight = occ_ui_weight; p.occ_max_packing = occ_max_packing;
@@ -244,6 +245,7 @@ bool CudaRC1PExtinctionBasedShading::Update(vis::Camera* camera) {
   vrb_ebs_params p;
   if (a->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
   p.step_size = m_u_step_size;
+  p.apply_gradient_shading = (m_apply_gradient_shading && m_ext_data_manager->HasGradientTexture()) ? 1 : 0;
   p.apply_ambient_occlusion = apply_ambient_occlusion ? 1 : 0; p.ambient_occlusion_shells = ambient_occlusion_shells;
   p.ambient_occlusion_radius = ambient_occlusion_radius;
   p.apply_directional_shadows = apply_directional_shadows ? 1 : 0; p.dir_shadow_cone_angle = dir_shadow_cone_angle;
@@ -282,6 +284,7 @@ bool CudaRC1PVoxelConeTracingSGPU::Update(vis::Camera* camera) {
   vrb_vct_params p;
   if (a->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
   p.step_size = m_u_step_size;
+  p.apply_gradient_shading = (m_apply_gradient_shading && m_ext_data_manager->HasGradientTexture()) ? 1 : 0;
   p.apply_ambient_occlusion = apply_ambient_occlusion ? 1 : 0; p.apply_directional_shadows = apply_directional_shadows ? 1 : 0;
   p.cone_step_size = cone_step_size; p.cone_step_increase_rate = cone_step_increase_rate; p.cone_initial_step = cone_initial_step;
   p.cone_apex_angle = cone_apex_angle; p.apply_correction_factor = apply_correction_factor ? 1 : 0;

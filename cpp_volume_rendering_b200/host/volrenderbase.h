@@ -118,6 +118,7 @@ class CudaRC1PConeTracingDirOcclusionShading : public BaseVolumeRenderer {
   bool Init(int w, int h) override;
   bool Update(vis::Camera* camera) override;
   float m_u_step_size;
+  bool m_apply_gradient_shading = false;    // ApplyPhongShading = this && GetCurrentGradientTexture()
   bool glsl_apply_occlusion, glsl_apply_shadow;
   int type_of_shadow;
   float occ_cone_half_angle, occ_initial_step, occ_covered_distance, occ_ui_weight;   int occ_max_packing;
@@ -139,6 +140,7 @@ class CudaRC1PExtinctionBasedShading : public BaseVolumeRenderer {
   bool Update(vis::Camera* camera) override;
   void FillParameterSpace(ParameterSpace& pspace) override;    // ebsrenderer.cpp:430-435
   float m_u_step_size;
+  bool m_apply_gradient_shading = false;    // ApplyPhongShading = this && GetCurrentGradientTexture()
   bool apply_ambient_occlusion; int ambient_occlusion_shells; float ambient_occlusion_radius;
   bool apply_directional_shadows; float dir_shadow_cone_angle, dir_shadow_sample_interval, dir_shadow_initial_step;
   float dir_shadow_user_interface_weight, dir_cone_max_distance; int type_of_shadow;
@@ -156,6 +158,7 @@ class CudaRC1PVoxelConeTracingSGPU : public BaseVolumeRenderer {
   bool Init(int w, int h) override;
   bool Update(vis::Camera* camera) override;
   float m_u_step_size;
+  bool m_apply_gradient_shading = false;    // ApplyPhongShading = this && GetCurrentGradientTexture()
   bool apply_ambient_occlusion, apply_directional_shadows, apply_correction_factor;
   float cone_step_size, cone_step_increase_rate, cone_initial_step, cone_apex_angle, opacity_correction_factor;
   int cone_number_of_samples;

@@ -211,6 +211,9 @@ typedef struct {
   float ka, kd;
   int   row_begin, row_end, row_stride, threads;
 } orc_obj_params;
+/* ApplyPhongShading of the DOS / EBS / VCT / object-space oracles (orc_shade.h): gradient texture W*H*D*3 (kept by pointer until
+ * cleared with enable = 0), Kspecular, Nshininess, Ispecular, WorldLightingPos. */
+void orc_set_phong(const float* grad_rgb, int enable, float ks, float shininess, const float* ispec, const float* light_pos);
 /* main() of _common_shaders/obj_ray_marching.comp over a light cache.  Returns march-loop iterations. */
 uint64_t orc_obj_render(const orc_obj_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n, const float* cache_rg,
                         const int dims[3], float* out_rgba);

@@ -10,6 +10,7 @@
 #include "oracle.h"
 #include "orc_common.h"
 #include "orc_ray.h"
+#include "orc_shade.h"
 #ifdef _OPENMP
 #include <omp.h>
 #endif
@@ -347,10 +348,13 @@ uint32_t dos_pixel(const DosCtx& c, int px, int py, float out[4], bool* hit, uin
         Iocc = cone_trace(c, c.occ, tx, cone_vec, v_up, v_right);
       }
       if (p.apply_shadow == 1) { kd = p.kd; Isdw = shadow_kernel(c, tx); }
-      float k = 1.0f / (ka + kd);
-      src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
-      src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
-      src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
+      if (!phong_shade_sample(0, c.vol, c.sizes, tx, vec3(p.light_pos[0], p.light_pos[1], p.light_pos[2]), eye, ka, kd,
+                              p.apply_shadow == 1, Iocc, Isdw, src)) {          // ApplyPhongShading == 1 (:630-649)
+        float k = 1.0f / (ka + kd);
+        src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
+        src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
+        src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
+      }
       src.w = 1.0f - std::exp(-src.w * h);
       src.x = src.x * src.w; src.y = src.y * src.w; src.z = src.z * src.w;
       dst = dst + (1.0f - dst.w) * src;

@@ -6,6 +6,7 @@
 #include "oracle.h"
 #include "orc_common.h"
 #include "orc_ray.h"
+#include "orc_shade.h"
 #ifdef _OPENMP
 #include <omp.h>
 #endif
@@ -161,6 +162,8 @@ vec4 shade_sample(const EbsCtx& c, vec4 clr, vec3 tx) {
   if (p.apply_shadow == 1) { kd = p.kd; Isdw = directional_shadows(c, tx); }
   float k = 1.0f / (ka + kd);
   vec4 L = clr;
+  if (phong_shade_sample(1, c.vol, c.sizes, tx, vec3(p.light_pos[0], p.light_pos[1], p.light_pos[2]), vec3(p.eye[0], p.eye[1], p.eye[2]),
+                         ka, kd, p.apply_shadow == 1, Iocc, Isdw, L)) return L;       // ApplyPhongShading == 1 (:524-545)
   L.x = k * (clr.x * Iocc * ka + clr.x * Isdw * kd);
   L.y = k * (clr.y * Iocc * ka + clr.y * Isdw * kd);
   L.z = k * (clr.z * Iocc * ka + clr.z * Isdw * kd);

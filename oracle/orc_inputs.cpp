@@ -131,3 +131,11 @@ int orc_max_threads(void) {
 }
 
 }  // extern "C"
+
+// ---- ApplyPhongShading state of the shadowed DVR oracles (orc_shade.h) ----------------------------------------------
+#include "orc_shade.h"
+namespace orc { PhongGlobal g_phong = {nullptr, 0, 0.0f, 0.0f, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}}; }
+extern "C" void orc_set_phong(const float* grad_rgb, int enable, float ks, float shininess, const float* ispec, const float* light_pos) {
+  orc::g_phong.grad = grad_rgb; orc::g_phong.enable = enable; orc::g_phong.ks = ks; orc::g_phong.shininess = shininess;
+  for (int i = 0; i < 3; i++) { orc::g_phong.ispec[i] = ispec ? ispec[i] : 0.0f; orc::g_phong.light_pos[i] = light_pos ? light_pos[i] : 0.0f; }
+}

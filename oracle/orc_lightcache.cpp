@@ -1,11 +1,12 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see orc_common.h).
 // Object-space ("light cache") mode of the shadowed DVR renderers: main() and ShadeSample() of
-// cppvolrend/structured/_common_shaders/obj_ray_marching.comp (:210-333, the compiled #else branch) with ApplyPhongShading == 0.
+// cppvolrend/structured/_common_shaders/obj_ray_marching.comp (:210-333, the compiled #else branch) (ApplyPhongShading through orc_set_phong, orc_shade.h).
 // The per-renderer cache contents come from orc_{dos,vct,ebs}_light_cache; the cache texture is RG16F, GL_LINEAR,
 // CLAMP_TO_EDGE (cppvolrend/utils/preillumination.cpp:63-78).
 #include "oracle.h"
 #include "orc_common.h"
 #include "orc_ray.h"
+#include "orc_shade.h"
 #ifdef _OPENMP
 #include <omp.h>
 #endif
@@ -52,10 +53,13 @@ extern "C" uint64_t orc_obj_render(const orc_obj_params* p, const float* vol_r16
           float ka = 0.0f, kd = 0.0f, Iocc = 0.0f, Isdw = 0.0f;
           if (p->apply_occlusion == 1) { ka = p->ka; Iocc = ca.linear(q); }
           if (p->apply_shadow == 1) { kd = p->kd; Isdw = cs.linear(q); }
-          float k = 1.0f / (ka + kd);
-          src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
-          src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
-          src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
+          if (!phong_shade_sample(1, vol, sizes, tx, vec3(g_phong.light_pos[0], g_phong.light_pos[1], g_phong.light_pos[2]), eye, ka, kd,
+                                  p->apply_shadow == 1, Iocc, Isdw, src)) {     // ApplyPhongShading == 1 (:236-255)
+            float k = 1.0f / (ka + kd);
+            src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
+            src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
+            src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
+          }
           src.w = 1.0f - std::exp(-src.w * h);
           src.x = src.x * src.w; src.y = src.y * src.w; src.z = src.z * src.w;
           color = color + (1.0f - color.w) * src;

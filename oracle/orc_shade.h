@@ -46,4 +46,42 @@ inline vec3 shade_blinn_phong(const PhongCtx& c, vec3 Tpos, vec3 clr) {
   return clr;
 }
 
+
+// ---- ApplyPhongShading == 1 branch of the ShadeSample functions of the shadowed DVR shaders --------------------------
+//   rc1pdosct/ray_bbox_marching.comp:630-649, rc1pextbsd/ebs_ray_bbox_marching.comp:524-545,
+//   rc1pvctsg/vct_ray_bbox_marching.comp:163-183, _common_shaders/obj_ray_marching.comp:236-255.
+// The gradient texture and the specular terms are the same for the four oracles, so tests set them once
+// (orc_set_phong); enable == 0 or grad == NULL: ApplyPhongShading == 0.
+struct PhongGlobal { const float* grad; int enable; float ks, shininess; float ispec[3]; float light_pos[3]; };
+extern PhongGlobal g_phong;
+
+// kind 0: the DOS cone tracer's formula, kind 1: EBS / VCT (Iocc = 1) / object-space march.  Returns false when
+// ApplyPhongShading == 0 (the caller applies its plain formula); with a zero gradient L keeps the unshaded colour.
+inline bool phong_shade_sample(int kind, const Tex3D& vol, vec3 sizes, vec3 tx, vec3 light_pos, vec3 eye,
+                               float ka, float kd, bool apply_shadow, float Iocc, float Isdw, vec4& L) {
+  if (!g_phong.enable || !g_phong.grad) return false;
+  PhongCtx c; c.grad = g_phong.grad; c.w = vol.w; c.h = vol.h; c.d = vol.d; c.wmode = vol.wmode; c.grid_size = sizes;
+  const float ks = apply_shadow ? g_phong.ks : 0.0f;
+  vec3 Wpos = tx - (sizes * 0.5f);
+  vec3 g = sample_grad(c, tx / sizes);
+  if (g.x != 0.0f || g.y != 0.0f || g.z != 0.0f) {
+    g = normalize(g);
+    vec3 light_direction = normalize(light_pos - Wpos);
+    vec3 eye_direction = normalize(eye - Wpos);
+    vec3 halfway = normalize(eye_direction + light_direction);
+    float dot_diff = gmax(0.0f, dot(g, light_direction));
+    float dot_spec = gmax(0.0f, dot(halfway, g));
+    vec3 ispec(g_phong.ispec[0], g_phong.ispec[1], g_phong.ispec[2]);
+    float pw = std::pow(dot_spec, g_phong.shininess);
+    vec3 rgb(L.x, L.y, L.z), o;
+    if (kind == 0) {
+      o = rgb * ((1.0f / (ka + kd)) * (Iocc * ka + Isdw * kd * dot_diff)) + ispec * (Isdw * ks * pw);
+    } else {
+      o = (1.0f / (ka + kd)) * (rgb * Iocc * ka + Isdw * (rgb * kd * dot_diff)) + Isdw * (ks * ispec * pw);
+    }
+    L.x = o.x; L.y = o.y; L.z = o.z;
+  }
+  return true;
+}
+
 }  // namespace orc

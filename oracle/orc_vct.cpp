@@ -6,6 +6,7 @@
 #include "oracle.h"
 #include "orc_common.h"
 #include "orc_ray.h"
+#include "orc_shade.h"
 #ifdef _OPENMP
 #include <omp.h>
 #endif
@@ -200,10 +201,13 @@ uint32_t shade_pixel(const VctCtx& c, int px, int py, float out[4], bool* hit) {
       float ka = 0.0f, kd = 0.0f, Ivd = 0.0f;                       // ShadeSample (:146-189), ApplyPhongShading == 0
       if (p.apply_occlusion == 1) ka = p.ka;
       if (p.apply_shadow == 1) { kd = p.kd; Ivd = cone_tracing(c, tx); }
-      float k = 1.0f / (ka + kd);
-      src.x = k * (src.x * ka + src.x * Ivd * kd);
-      src.y = k * (src.y * ka + src.y * Ivd * kd);
-      src.z = k * (src.z * ka + src.z * Ivd * kd);
+      if (!phong_shade_sample(1, c.vol, c.sizes, tx, vec3(p.light_pos[0], p.light_pos[1], p.light_pos[2]), eye, ka, kd,
+                              p.apply_shadow == 1, 1.0f, Ivd, src)) {           // ApplyPhongShading == 1 (:163-183)
+        float k = 1.0f / (ka + kd);
+        src.x = k * (src.x * ka + src.x * Ivd * kd);
+        src.y = k * (src.y * ka + src.y * Ivd * kd);
+        src.z = k * (src.z * ka + src.z * Ivd * kd);
+      }
       src.w = 1.0f - std::exp(-src.w * h);
       src.x = src.x * src.w; src.y = src.y * src.w; src.z = src.z * src.w;
       dst = dst + (1.0f - dst.w) * src;

@@ -137,6 +137,8 @@ def lib():
         L.orc_block_minmax.argtypes = [_P, C.c_int] + [C.c_int] * 6 + [_P, _P]
         L.orc_iso_render.argtypes = [C.POINTER(IsoParams), _P, _P, _P, _P, _P, _P]
         L.orc_iso_render.restype = C.c_uint64
+        L.orc_set_phong.argtypes = [_P, C.c_int, C.c_float, C.c_float, _P, _P]
+        L.orc_set_phong.restype = None
         _lib = L
     return _lib
 
@@ -238,6 +240,23 @@ def block_minmax(voxels, num_blocks):
     mx = np.empty((nbz, nby, nbx), np.float32)
     lib().orc_block_minmax(_ptr(v), _DT[v.dtype], w, h, d, nbx, nby, nbz, _ptr(mn), _ptr(mx))
     return mn, mx
+
+
+_phong_keep = []
+
+
+def set_phong(grad, light):
+    """ApplyPhongShading == 1 for the DOS / EBS / VCT / object-space oracles: gradient texture [z, y, x, 3] float32 and the light
+    (ks, shininess, ispecular, position).  grad = None switches it off."""
+    _phong_keep.clear()
+    if grad is None:
+        lib().orc_set_phong(None, 0, 0.0, 0.0, None, None)
+        return
+    g = np.ascontiguousarray(grad, np.float32)
+    isp = np.array(list(light.ispecular), np.float32)
+    lp = np.array(list(light.position), np.float32)
+    _phong_keep.extend([g, isp, lp])
+    lib().orc_set_phong(_ptr(g), 1, float(light.ks), float(light.shininess), _ptr(isp), _ptr(lp))
 
 
 def iso_params(cam, width, height, vol_shape_zyx, mode, isovalue=0.5, step_small=0.05, step_large=1.0, step_range=0.1,

@@ -71,6 +71,8 @@ CASES = [
                                                               light_cam_forward=(0.3, -0.5, -0.8124), light_cam_up=(0.0, 0.8517, -0.5241), light_cam_right=(0.9539, 0.1572, 0.2555))),
     (40, np.uint8, (64, 64), (1, 1, 2), (1.0, 0.5, 2.0), dict(occ_cone_half_angle=35.0, occ_max_packing=2, apply_shadow=1, type_of_shadow=1, spot_light_max_angle=25.0,
                                                           light_cam_forward=(-0.577, -0.577, -0.577))),
+    (48, np.uint8, (80, 64), (1, 1, 2), (1, 1, 1), dict(apply_gradient_shading=1, apply_shadow=1)),       # ApplyPhongShading == 1 (:630-649)
+    (40, np.uint16, (64, 64), (-1.2, 0.4, 1.1), (1, 1, 1), dict(apply_gradient_shading=1)),
 ]
 
 
@@ -82,6 +84,9 @@ def test_dos_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, scale, kw):
     cam = inputs.make_camera(tuple(n * e * s for e, s in zip(eye_s, scale)), (0, 0, 0), (0, 1, 0), 45.0, w, h)
     light = inputs.default_light(n)
     r = _make(ctx, vox, bonsai_table, size, scale=scale, res=res, count_samples=1, **kw)
+    phong = kw.get("apply_gradient_shading", 0)
+    if phong:
+        ctx.volume_gradient(1)
     try:
         r.update(cam, light); r.redraw()
         got = r.read_frame(_capi.VRB_FRAME_RGBA32F); got8 = r.read_frame(_capi.VRB_FRAME_RGB8_OVER_WHITE)
@@ -89,6 +94,7 @@ def test_dos_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, scale, kw):
         prm = r.get_params(_capi.DosParams())
     finally:
         r.close()
+        ctx.volume_gradient(0)
     occ = O.ConeSections(prm.occ_cone_half_angle, prm.occ_initial_step, prm.occ_max_packing, prm.occ_covered_distance, ui_weight=prm.occ_ui_weight)
     sdw = O.ConeSections(prm.sdw_cone_half_angle, prm.sdw_initial_step, prm.sdw_max_packing, prm.sdw_covered_distance, ui_weight=prm.sdw_ui_weight)
     levels = O.dos_extcoef_volume(O.volume_r16f(vox), O.tf_texture(bonsai_table, kind=1), voxel=scale, res=res)
@@ -96,7 +102,11 @@ def test_dos_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, scale, kw):
                      apply_occlusion=prm.apply_occlusion, apply_shadow=prm.apply_shadow, type_of_shadow=prm.type_of_shadow,
                      spot_max_angle_deg=prm.spot_light_max_angle, light_cam_forward=tuple(prm.light_cam_forward),
                      light_cam_up=tuple(prm.light_cam_up), light_cam_right=tuple(prm.light_cam_right), ka=light.ka, kd=light.kd)
-    ref, total, shaded = O.dos_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table), levels, occ, sdw)
+    O.set_phong(O.gradient(vox, 1) if phong else None, light)
+    try:
+        ref, total, shaded = O.dos_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table), levels, occ, sdw)
+    finally:
+        O.set_phong(None, None)
     ref8 = O.blit_over_white(ref)
     d16 = float(np.abs(got - ref).max()) * 255.0
     d8 = metrics.max_abs_delta(got8, ref8)

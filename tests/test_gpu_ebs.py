@@ -89,6 +89,7 @@ CASES = [
     (48, np.uint8, (80, 80), (0.6, -1.2, -0.2), dict(apply_ambient_occlusion=0)),
     (40, np.uint8, (64, 64), (1, 1, 2), dict(ambient_occlusion_shells=6, ambient_occlusion_radius=1.5, dir_shadow_cone_angle=4.0,
                                              dir_shadow_sample_interval=1.0, dir_shadow_initial_step=1.0, type_of_shadow=1)),
+    (40, np.uint8, (64, 56), (1, 1, 2), dict(apply_gradient_shading=1)),                          # ApplyPhongShading == 1 (:524-545)
 ]
 
 
@@ -103,7 +104,13 @@ def test_ebs_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, kw):
     r_kw = dict(kw)
     if kw.get("type_of_shadow") == 1:
         r = None
-    got, got8, samples, prm = _render_with_fwd(ctx, cam, light, w, h, fwd, **r_kw)
+    phong = kw.get("apply_gradient_shading", 0)
+    if phong:
+        ctx.volume_gradient(1)
+    try:
+        got, got8, samples, prm = _render_with_fwd(ctx, cam, light, w, h, fwd, **r_kw)
+    finally:
+        ctx.volume_gradient(0)
     p = O.ebs_params(cam, w, h, vox.shape, prm.step_size, list(light.position),
                      apply_occlusion=prm.apply_ambient_occlusion, apply_shadow=prm.apply_directional_shadows,
                      ao_shells=prm.ambient_occlusion_shells, ao_radius=prm.ambient_occlusion_radius,
@@ -111,7 +118,11 @@ def test_ebs_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, kw):
                      initial_step=prm.dir_shadow_initial_step, weight=prm.dir_shadow_user_interface_weight,
                      max_distance=prm.dir_cone_max_distance, type_of_shadow=prm.type_of_shadow, light_cam_forward=fwd,
                      ka=light.ka, kd=light.kd)
-    ref, total, shaded = O.ebs_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table), O.ext_sat3d(vox, bonsai_table))
+    O.set_phong(O.gradient(vox, 1) if phong else None, light)
+    try:
+        ref, total, shaded = O.ebs_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table), O.ext_sat3d(vox, bonsai_table))
+    finally:
+        O.set_phong(None, None)
     ref8 = O.blit_over_white(ref)
     d16 = float(np.abs(got - ref).max()) * 255.0
     d8 = metrics.max_abs_delta(got8, ref8)

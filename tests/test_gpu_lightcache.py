@@ -85,6 +85,7 @@ def test_dos_light_cache_mode(ctx, bonsai_table, n, dtype, size, eye_s, scale, l
     (48, (96, 96), (1, 1, 2), (32, 32, 32), dict()),
     (48, (80, 64), (-1.2, 0.4, 1.1), (20, 12, 28), dict(cone_apex_angle=6.0, cone_step_increase_rate=1.15, cone_number_of_samples=20)),
     (40, (64, 64), (1, 1, 2), (8, 8, 8), dict(apply_directional_shadows=0)),
+    (48, (80, 64), (1, 1, 2), (24, 24, 24), dict(apply_gradient_shading=1)),       # ApplyPhongShading == 1 of obj_ray_marching.comp (:236-255)
 ])
 def test_vct_light_cache_mode(ctx, bonsai_table, n, size, eye_s, lc, kw):
     w, h = size
@@ -92,6 +93,9 @@ def test_vct_light_cache_mode(ctx, bonsai_table, n, size, eye_s, lc, kw):
     cam = inputs.make_camera(tuple(n * e for e in eye_s), (0, 0, 0), (0, 1, 0), 45.0, w, h)
     light = inputs.default_light(n)
     ctx.upload_volume(vox); ctx.upload_tf(bonsai_table)
+    phong = kw.get("apply_gradient_shading", 0)
+    if phong:
+        ctx.volume_gradient(1)
     r = _capi.Renderer(ctx, _capi.VRB_VCT)
     try:
         r.init(w, h)
@@ -108,6 +112,7 @@ def test_vct_light_cache_mode(ctx, bonsai_table, n, size, eye_s, lc, kw):
         lut, max_std, _, _ = r.read_vct_lut()
     finally:
         r.close()
+        ctx.volume_gradient(0)
     levels, ref_max = O.vct_supervoxels(vox)
     assert ref_max == max_std
     p = O.vct_params(cam, w, h, vox.shape, prm.step_size, list(light.position), 255.0, ref_max,
@@ -117,7 +122,11 @@ def test_vct_light_cache_mode(ctx, bonsai_table, n, size, eye_s, lc, kw):
                      apply_correction=prm.apply_correction_factor, cone_samples=prm.cone_number_of_samples, ka=light.ka, kd=light.kd)
     # the table the GPU built (its parity is test_gpu_vct's subject): the cache comparison then isolates K20
     ref_cache = O.vct_light_cache(p, levels, lut, lc)
-    ref, total = O.obj_render(O.obj_params(p), O.volume_r16f(vox), O.tf_texture(bonsai_table), ref_cache)
+    O.set_phong(O.gradient(vox, 1) if phong else None, light)
+    try:
+        ref, total = O.obj_render(O.obj_params(p), O.volume_r16f(vox), O.tf_texture(bonsai_table), ref_cache)
+    finally:
+        O.set_phong(None, None)
     _check(f"VCT light cache {lc} {kw}", got, got8, ref, cache, ref_cache, samples, total)
     assert np.all(cache[..., 0] == 1.0)               # Iao = 1.0 (lightcachecomputation.comp main)
     assert (ref[..., 3] > 0).mean() > 0.05

@@ -55,6 +55,8 @@ CASES = [
     (48, np.uint8, (80, 80), (0.6, -1.2, -0.2), dict(apply_ambient_occlusion=0, cone_step_size=1.0, cone_initial_step=1.0)),
     (40, np.uint8, (64, 64), (1, 1, 2), dict(apply_directional_shadows=0)),
     (48, np.uint8, (72, 72), (1, 1, 2), dict(apply_correction_factor=1, opacity_correction_factor=0.5, cone_apex_angle=20.0)),
+    (48, np.uint8, (80, 64), (1, 1, 2), dict(apply_gradient_shading=1)),                      # ApplyPhongShading == 1 (:163-183)
+    (40, np.uint16, (64, 64), (-1.2, 0.4, 1.1), dict(apply_gradient_shading=1, apply_ambient_occlusion=0)),
 ]
 
 
@@ -65,6 +67,9 @@ def test_vct_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, kw):
     cam = inputs.make_camera(tuple(n * e for e in eye_s), (0, 0, 0), (0, 1, 0), 45.0, w, h)
     light = inputs.default_light(n)
     r = _make(ctx, vox, bonsai_table, size)
+    phong = kw.get("apply_gradient_shading", 0)
+    if phong:
+        ctx.volume_gradient(1)
     try:
         prm = r.get_params(_capi.VctParams())
         for k, v in kw.items():
@@ -77,6 +82,7 @@ def test_vct_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, kw):
         lut, max_std, _, _ = r.read_vct_lut()
     finally:
         r.close()
+        ctx.volume_gradient(0)
     levels, ref_max = O.vct_supervoxels(vox)
     assert ref_max == max_std
     ref_lut = O.vct_preintegration(bonsai_table, dtype, ref_max)
@@ -85,7 +91,11 @@ def test_vct_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, kw):
                      apex_angle_deg=prm.cone_apex_angle, cone_step_size=prm.cone_step_size, increase_rate=prm.cone_step_increase_rate,
                      initial_step=prm.cone_initial_step, opacity_correction=prm.opacity_correction_factor,
                      apply_correction=prm.apply_correction_factor, cone_samples=prm.cone_number_of_samples, ka=light.ka, kd=light.kd)
-    ref, total = O.vct_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table), levels, ref_lut)
+    O.set_phong(O.gradient(vox, 1) if phong else None, light)
+    try:
+        ref, total = O.vct_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table), levels, ref_lut)
+    finally:
+        O.set_phong(None, None)
     ref8 = O.blit_over_white(ref)
     d16 = float(np.abs(got - ref).max()) * 255.0
     d8 = metrics.max_abs_delta(got8, ref8)
@@ -105,9 +115,11 @@ def test_vct_defaults_follow_the_reference_constructor(ctx, bonsai_table):
         assert (p.apply_correction_factor, p.opacity_correction_factor, p.cone_number_of_samples) == (1, 2.0, 50)
         assert (p.apply_ambient_occlusion, p.apply_directional_shadows) == (1, 1)
         assert abs(p.step_size - 0.5 / np.sqrt(3.0) * np.sqrt(1 + 0.25 + 4)) < 1e-6
-        p.apply_gradient_shading = 1
+        p.apply_gradient_shading = 1              # accepted; the Redraw then needs a gradient texture for the current volume
+        r.set_params(p)
+        r.update(inputs.make_camera((16, 16, 32), (0, 0, 0), (0, 1, 0), 45.0, 16, 16), inputs.default_light(16))
         with pytest.raises(_capi.VrbError):
-            r.set_params(p)
+            r.redraw()
     finally:
         r.close()
 
