@@ -236,12 +236,15 @@ def run_cuda(args):
     depth_split = args.depth_split if args.depth_split >= 0 else (0 if world == 1 else (2 if world <= 4 else 4))   # tools/partition_sweep.py: best K per split
     prm.depth_split = depth_split
     r.set_params(prm)
+    # partition tile: 16x16 deals the long central rays more evenly over 8 ranks (tools/rank_skew.py: slowest rank 0.086 ms against
+    # 0.093 ms with 32x32); at 2 and 4 ranks 32x32 is as even and keeps more texture locality
+    PART_TILE = 16 if world >= 8 else 32
     if world > 1:
         # image tiles dealt round-robin; every rank's kernel stores its pixels straight into every peer's frame (CUDA
         # IPC peer memory over NVLink) and then raises a per-frame flag there; the stream waits on the flags
         # (cuStreamWaitValue32) — no collective on the frame and none for the end-of-frame synchronisation
         from cpp_volume_rendering_b200 import multigpu
-        multigpu.setup_fused_gather(r, rank, world, tile=32, mode=_capi.VRB_GATHER_ALL)
+        multigpu.setup_fused_gather(r, rank, world, tile=PART_TILE, mode=_capi.VRB_GATHER_ALL)
 
     # sample count of this frame (instrumented launch, untimed)
     prm.count_samples = 1
@@ -362,7 +365,7 @@ def run_cuda(args):
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(args.skip), "volume": f"{VOL_N}^3 u16 -> R16F texture", "image": f"{IMG_W}x{IMG_H}",
                        "step_voxels": STEP, "tf": "bonsai_01.tf1d", "camera": "Initial State (N,N,2N)",
-                       "partition": f"image tiles 32x32 round-robin over {world} rank(s)" + (", fused peer-memory gather into every rank's frame + per-frame flag wait (no collective)" if world > 1 else ""),
+                       "partition": f"image tiles {PART_TILE}x{PART_TILE} round-robin over {world} rank(s)" + (", fused peer-memory gather into every rank's frame + per-frame flag wait (no collective)" if world > 1 else ""),
                        "l2_policy": "inputs_larger_than_l2 (256 MiB R16F volume vs 126 MB L2)",
                        "samples_per_frame": fetched_total, "fps": 1e3 / ms_per_step, "init_ms_volume_upload": init_ms,
                        "tf_in_smem": args.tf_smem, "exact_filter": args.exact, "skip_block": args.skip, "depth_split": depth_split, "with_skipping": skip_info},
