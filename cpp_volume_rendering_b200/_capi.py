@@ -16,6 +16,9 @@ VRB_U8, VRB_U16, VRB_F32 = 0, 1, 2
 (VRB_RC1PASS, VRB_ISO_ADAPT, VRB_ISO_SKIP_V1, VRB_ISO_SKIP_V2, VRB_DOS_CONE, VRB_EBS_SAT, VRB_VCT,
  VRB_SBTM_DOS) = range(8)
 VRB_FRAME_RGBA16F, VRB_FRAME_RGB8_OVER_WHITE, VRB_FRAME_RGBA32F = 0, 1, 2
+VRB_FRAME_GENERATED = 0x100
+VRB_MS_SINGLE, VRB_MS_MULTIPLE_RAYS_PER_PIXEL, VRB_MS_DOWN_SCALING, VRB_MS_UP_SCALING = 0, 1, 2, 3
+VRB_K1_BOX, VRB_K2_HAT, VRB_K4_CATMULL_ROM, VRB_K4_MITCHELL_NETRAVALI, VRB_K4_CARDINAL_BSPLINE_3, VRB_K4_CARDINAL_OMOMS3 = range(6)
 VRB_GATHER_NONE, VRB_GATHER_ROOT, VRB_GATHER_ALL = 0, 1, 2
 
 _DTYPES = {np.dtype(np.uint8): VRB_U8, np.dtype(np.uint16): VRB_U16, np.dtype(np.float32): VRB_F32}
@@ -107,6 +110,9 @@ SIGNATURES = {
     "vrb_renderer_get_params": (C.c_int, [_P, _P, C.c_size_t]),
     "vrb_renderer_update": (C.c_int, [_P, C.POINTER(Camera), C.POINTER(Light)]),
     "vrb_renderer_redraw": (C.c_int, [_P, C.c_int]),
+    "vrb_renderer_set_multiscaling": (C.c_int, [_P, C.c_int, C.c_int]),
+    "vrb_renderer_render_size": (C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "vrb_frame_multiscale": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_int, C.c_int, _P, C.c_int, C.c_int]),
     "vrb_renderer_frame": (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "vrb_renderer_read_frame": (C.c_int, [_P, _P, C.c_int]),
     "vrb_renderer_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_double)]),
@@ -202,6 +208,15 @@ class Context:
         self.tf_n = t.shape[0]
         _check(lib().vrb_tf_upload(self._h, t.ctypes.data_as(_P), t.shape[0], int(bool(extinction_type))))
 
+    def frame_multiscale(self, mode, kernel, src_rgba16f, target_wh):
+        """RenderFrameToScreen's filter pass alone: [h, w, 4] float16 -> [th, tw, 4] float16."""
+        src = np.ascontiguousarray(src_rgba16f, np.float16)
+        tw, th = target_wh
+        dst = np.empty((th, tw, 4), np.float16)
+        _check(lib().vrb_frame_multiscale(self._h, mode, kernel, src.ctypes.data_as(_P), src.shape[1], src.shape[0],
+                                          dst.ctypes.data_as(_P), tw, th))
+        return dst
+
     def read_tf(self):
         a = np.empty((self.tf_n, 4), np.float32)
         b = np.empty((self.tf_n, 4), np.float32)
@@ -247,17 +262,29 @@ class Renderer:
     def redraw(self, mode=0):
         _check(lib().vrb_renderer_redraw(self._h, mode))
 
+    def set_multiscaling(self, mode, kernel=0):
+        _check(lib().vrb_renderer_set_multiscaling(self._h, mode, kernel))
+
+    def render_size(self):
+        w, h = C.c_int(), C.c_int()
+        _check(lib().vrb_renderer_render_size(self._h, C.byref(w), C.byref(h)))
+        return w.value, h.value
+
     def frame_ptr(self):
         p, w, h = _P(), C.c_int(), C.c_int()
         _check(lib().vrb_renderer_frame(self._h, C.byref(p), C.byref(w), C.byref(h)))
         return p.value, w.value, h.value
 
     def read_frame(self, fmt=VRB_FRAME_RGBA16F, out=None):
-        w, h = self.size
+        if fmt & VRB_FRAME_GENERATED:                 # the renderer's own frame: the size the device pointer had before the filter
+            w, h = self.render_size()
+        else:
+            _, w, h = self.frame_ptr()
+        base = fmt & ~VRB_FRAME_GENERATED
         if out is None:
             out = {VRB_FRAME_RGBA16F: np.empty((h, w, 4), np.float16),
                    VRB_FRAME_RGB8_OVER_WHITE: np.empty((h, w, 3), np.uint8),
-                   VRB_FRAME_RGBA32F: np.empty((h, w, 4), np.float32)}[fmt]
+                   VRB_FRAME_RGBA32F: np.empty((h, w, 4), np.float32)}[base]
         _check(lib().vrb_renderer_read_frame(self._h, out.ctypes.data_as(_P), fmt))
         return out
 

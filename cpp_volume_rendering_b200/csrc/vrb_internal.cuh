@@ -165,6 +165,15 @@ struct RendererImpl {
   virtual LightCache* light_cache() { return nullptr; }   // renderers with an object-space mode
   int alloc_frame(int w, int h);
   void free_frame();
+  // Output-frame multiscaling (k_multiscale.cu; RenderFrameToScreen::UpdateScreenResolutionMultiScaling, renderoutputframe.cpp:89-146):
+  // with ms_mode != 0 `frame` is the generated frame at the scaled size (screen * 2 for modes 1 and 2, screen / 2 for mode 3)
+  // and `filtered` the screen-size RGBA16F result of the filter pass that follows the render.
+  int ms_mode = 0, ms_kernel = 1;         // m_kernel_filter(K2_HAT), renderoutputframe.cpp:34
+  int screen_w = 0, screen_h = 0;        // size given to Init / Reshape
+  __half* filtered = nullptr;
+  bool show_filtered = false;            // the last redraw ran the filter pass: vrb_renderer_frame / read_frame return `filtered`
+  int render_size(int sw, int sh, int* rw, int* rh) const;
+  int alloc_filtered();
 };
 
 // VRB_ITEM_ORDER=0 restores the scrambled item order (A/B measurements); default: longest first.
@@ -228,6 +237,8 @@ int ensure_quad(vrb_ctx* ctx);
 // k_frame.cu
 int frame_to_rgb8_over_white(cudaStream_t s, const __half* frame, int64_t n_pixels, uint8_t* dev_out);
 int frame_to_rgba32f(cudaStream_t s, const __half* frame, int64_t n_pixels, float* dev_out);
+// k_multiscale.cu: mode 1 multisample, 2 downscale, 3 upscale (filters `src` in place for kernels 4 and 5); kernel 0..5
+int frame_multiscale(cudaStream_t s, int mode, int kernel, __half* src, int sw, int sh, __half* dst, int tw, int th);
 
 }  // namespace vrb
 

@@ -31,6 +31,24 @@ int RendererImpl::alloc_frame(int w, int h) {
   return VRB_OK;
 }
 
+// BaseVolumeRenderer::Reshape (volrenderbase.cpp:48-75): multiplier (+2, +2) for MULTIPLE_RAYS_PER_PIXEL and DOWN_SCALING_RENDER,
+// (-2, -2) for UP_SCALING_RENDER; a negative multiplier divides (renderoutputframe.cpp:102-112)
+int RendererImpl::render_size(int sw, int sh, int* rw, int* rh) const {
+  *rw = ms_mode == 0 ? sw : (ms_mode == 3 ? sw / 2 : sw * 2);
+  *rh = ms_mode == 0 ? sh : (ms_mode == 3 ? sh / 2 : sh * 2);
+  VRB_REQUIRE(*rw > 0 && *rh > 0, VRB_ERR_INVALID, "multiscaling mode %d of a %dx%d screen", ms_mode, sw, sh);
+  return VRB_OK;
+}
+
+int RendererImpl::alloc_filtered() {
+  if (filtered) { cudaFree(filtered); filtered = nullptr; }
+  show_filtered = false;
+  if (ms_mode == 0) return VRB_OK;
+  VRB_CUDA(cudaMalloc(&filtered, (size_t)screen_w * screen_h * 4 * sizeof(__half)));
+  VRB_CUDA(cudaMemsetAsync(filtered, 0, (size_t)screen_w * screen_h * 4 * sizeof(__half), ctx->stream));
+  return VRB_OK;
+}
+
 void RendererImpl::close_peers() {
   for (int i = 0; i < MAX_PEERS; i++) if (peer_opened[i]) { cudaIpcCloseMemHandle(peer_opened[i]); peer_opened[i] = nullptr; }
   n_peer_frames = 0; gather_mode = 0; gather_ranks = 1;
@@ -160,6 +178,7 @@ int vrb_renderer_destroy(vrb_renderer* r) {
   cudaStreamSynchronize(p->ctx->stream);
   p->clean();
   p->free_frame();
+  if (p->filtered) cudaFree(p->filtered);
   if (p->d_samples) cudaFree(p->d_samples);
   if (p->d_done) cudaFree(p->d_done);
   if (p->d_lattice) cudaFree(p->d_lattice);
@@ -178,7 +197,12 @@ int vrb_renderer_init(vrb_renderer* r, int width, int height) {
   RendererImpl* p = r->impl;
   VRB_CUDA(cudaSetDevice(p->ctx->device));
   if (p->built) { p->clean(); p->built = false; }
-  return p->init(width, height);
+  p->screen_w = width; p->screen_h = height;
+  int rw = 0, rh = 0;
+  int rc = p->render_size(width, height, &rw, &rh);
+  if (rc == VRB_OK) rc = p->init(rw, rh);
+  if (rc == VRB_OK) rc = p->alloc_filtered();
+  return rc;
 }
 
 int vrb_renderer_reshape(vrb_renderer* r, int width, int height) {
@@ -186,7 +210,65 @@ int vrb_renderer_reshape(vrb_renderer* r, int width, int height) {
   RendererImpl* p = r->impl;
   VRB_REQUIRE(p->built, VRB_ERR_INVALID, "vrb_renderer_reshape before Init");
   VRB_CUDA(cudaStreamSynchronize(p->ctx->stream));
-  return p->alloc_frame(width, height);
+  int rw = 0, rh = 0;
+  const int old_w = p->screen_w, old_h = p->screen_h;
+  p->screen_w = width; p->screen_h = height;
+  int rc = p->render_size(width, height, &rw, &rh);
+  if (rc != VRB_OK) { p->screen_w = old_w; p->screen_h = old_h; return rc; }
+  rc = p->alloc_frame(rw, rh);
+  if (rc == VRB_OK) rc = p->alloc_filtered();
+  return rc;
+}
+
+// SetCurrentMultiScalingMode (volrenderbase.h:71) + RenderFrameToScreen::SetImageFilterKernel (renderoutputframe.cpp:541-546) and the
+// Reshape that follows them in RenderingManager: the generated frame takes the scaled size, a screen-size filtered frame is added.
+int vrb_renderer_set_multiscaling(vrb_renderer* r, int mode, int kernel) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_set_multiscaling: null renderer");
+  RendererImpl* p = r->impl;
+  VRB_REQUIRE(mode >= 0 && mode <= 3 && kernel >= 0 && kernel <= 5, VRB_ERR_INVALID, "vrb_renderer_set_multiscaling: mode %d kernel %d", mode, kernel);
+  // vr_pixel_multiscaling_support: rc1prenderer.cpp:25, ebsrenderer.cpp:51, vctrenderer.cpp:52, dosrcrenderer.cpp:68, sbtmdosrenderer.cpp:46
+  VRB_REQUIRE(mode == 0 || p->kind == VRB_RC1PASS || p->kind == VRB_EBS_SAT || p->kind == VRB_VCT || p->kind == VRB_DOS_CONE || p->kind == VRB_SBTM_DOS,
+              VRB_ERR_UNSUPPORTED, "vrb_renderer_set_multiscaling: renderer kind %d has no pixel multiscaling", p->kind);
+  VRB_REQUIRE(mode == 0 || (p->gather_mode == VRB_GATHER_NONE && p->brick_ranks == 0 && p->n_ranks == 1), VRB_ERR_UNSUPPORTED,
+              "vrb_renderer_set_multiscaling: not with an image partition, peers or bricks (filter the gathered frame on one rank)");
+  const bool resize = mode != p->ms_mode;
+  p->ms_mode = mode; p->ms_kernel = kernel;
+  if (!p->built || !resize) return VRB_OK;
+  VRB_CUDA(cudaStreamSynchronize(p->ctx->stream));
+  int rw = 0, rh = 0;
+  int rc = p->render_size(p->screen_w, p->screen_h, &rw, &rh);
+  if (rc == VRB_OK) rc = p->alloc_frame(rw, rh);
+  if (rc == VRB_OK) rc = p->alloc_filtered();
+  return rc;
+}
+
+// RenderFrameToScreen::GetWidth / GetHeight (renderoutputframe.cpp:148-158): the size the renderer dispatches over
+int vrb_renderer_render_size(vrb_renderer* r, int* width, int* height) {
+  VRB_REQUIRE(r && width && height, VRB_ERR_INVALID, "vrb_renderer_render_size: null argument");
+  VRB_REQUIRE(r->impl->frame, VRB_ERR_INVALID, "vrb_renderer_render_size before Init");
+  *width = r->impl->width; *height = r->impl->height;
+  return VRB_OK;
+}
+
+// The filter pass alone, over host frames (test and tooling entry): src sw*sh and dst tw*th RGBA16F pixels, row 0 = bottom.
+int vrb_frame_multiscale(vrb_ctx* ctx, int mode, int kernel, const void* host_src_rgba16f, int sw, int sh, void* host_dst_rgba16f, int tw, int th) {
+  VRB_REQUIRE(ctx && host_src_rgba16f && host_dst_rgba16f, VRB_ERR_INVALID, "vrb_frame_multiscale: null argument");
+  VRB_REQUIRE(sw > 0 && sh > 0 && tw > 0 && th > 0 && sw <= 32768 && sh <= 32768 && tw <= 32768 && th <= 32768, VRB_ERR_INVALID,
+              "vrb_frame_multiscale: %dx%d -> %dx%d", sw, sh, tw, th);
+  VRB_CUDA(cudaSetDevice(ctx->device));
+  const size_t sb = (size_t)sw * sh * 8, tb = (size_t)tw * th * 8;
+  __half* d = nullptr;
+  VRB_CUDA(cudaMalloc(&d, sb + tb));
+  cudaStream_t s = ctx->stream;
+  cudaError_t e = cudaMemcpyAsync(d, host_src_rgba16f, sb, cudaMemcpyHostToDevice, s);
+  int rc = VRB_OK;
+  if (e == cudaSuccess) rc = frame_multiscale(s, mode, kernel, d, sw, sh, (__half*)((char*)d + sb), tw, th);
+  if (e == cudaSuccess && rc == VRB_OK) e = cudaMemcpyAsync(host_dst_rgba16f, (char*)d + sb, tb, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  cudaFree(d);
+  if (rc != VRB_OK) return rc;
+  VRB_CUDA(e);
+  return VRB_OK;
 }
 
 int vrb_renderer_set_params(vrb_renderer* r, const void* pod, size_t size) {
@@ -215,8 +297,15 @@ int vrb_renderer_redraw(vrb_renderer* r, int mode) {
   cudaStream_t s = p->ctx->stream;
   VRB_CUDA(cudaEventRecord(p->ev0, s));
   p->begin_frame();
+  VRB_REQUIRE(mode == 0 || mode == p->ms_mode, VRB_ERR_INVALID, "vrb_renderer_redraw: mode %d but multiscaling mode %d is set", mode, p->ms_mode);
   int rc = p->redraw(mode);
   if (rc != VRB_OK) return rc;
+  // DrawMultiSampleHigherResolutionMode / DrawHigherResolutionWithDownScale / DrawLowerResolutionWithUpScale (renderoutputframe.cpp:265-539)
+  p->show_filtered = mode != 0;
+  if (mode != 0) {
+    rc = frame_multiscale(s, mode, p->ms_kernel, p->frame, p->width, p->height, p->filtered, p->screen_w, p->screen_h);
+    if (rc != VRB_OK) return rc;
+  }
   VRB_CUDA(cudaEventRecord(p->ev1, s));
   p->timed = true;
   return VRB_OK;
@@ -226,9 +315,9 @@ int vrb_renderer_frame(vrb_renderer* r, void** dev_rgba16f, int* width, int* hei
   VRB_REQUIRE(r && dev_rgba16f, VRB_ERR_INVALID, "vrb_renderer_frame: null argument");
   RendererImpl* p = r->impl;
   VRB_REQUIRE(p->frame, VRB_ERR_INVALID, "vrb_renderer_frame before Init");
-  *dev_rgba16f = p->frame;
-  if (width) *width = p->width;
-  if (height) *height = p->height;
+  *dev_rgba16f = p->show_filtered ? p->filtered : p->frame;
+  if (width) *width = p->show_filtered ? p->screen_w : p->width;
+  if (height) *height = p->show_filtered ? p->screen_h : p->height;
   return VRB_OK;
 }
 
@@ -237,9 +326,13 @@ int vrb_renderer_read_frame(vrb_renderer* r, void* host, int format) {
   RendererImpl* p = r->impl;
   VRB_REQUIRE(p->frame, VRB_ERR_INVALID, "vrb_renderer_read_frame before Init");
   cudaStream_t s = p->ctx->stream;
-  const int64_t n = (int64_t)p->width * p->height;
+  // VRB_FRAME_GENERATED: the frame the renderer wrote (scaled size), not the filtered one
+  const bool gen = (format & VRB_FRAME_GENERATED) != 0 || !p->show_filtered;
+  format &= ~VRB_FRAME_GENERATED;
+  const __half* src = gen ? p->frame : p->filtered;
+  const int64_t n = gen ? (int64_t)p->width * p->height : (int64_t)p->screen_w * p->screen_h;
   if (format == VRB_FRAME_RGBA16F) {
-    VRB_CUDA(cudaMemcpyAsync(host, p->frame, (size_t)n * 8, cudaMemcpyDeviceToHost, s));
+    VRB_CUDA(cudaMemcpyAsync(host, src, (size_t)n * 8, cudaMemcpyDeviceToHost, s));
     VRB_CUDA(cudaStreamSynchronize(s));
     return VRB_OK;
   }
@@ -248,8 +341,8 @@ int vrb_renderer_read_frame(vrb_renderer* r, void* host, int format) {
   const size_t bytes = format == VRB_FRAME_RGB8_OVER_WHITE ? (size_t)n * 3 : (size_t)n * 16;
   void* tmp = nullptr;
   VRB_CUDA(cudaMalloc(&tmp, bytes));
-  int rc = format == VRB_FRAME_RGB8_OVER_WHITE ? frame_to_rgb8_over_white(s, p->frame, n, (uint8_t*)tmp)
-                                               : frame_to_rgba32f(s, p->frame, n, (float*)tmp);
+  int rc = format == VRB_FRAME_RGB8_OVER_WHITE ? frame_to_rgb8_over_white(s, src, n, (uint8_t*)tmp)
+                                               : frame_to_rgba32f(s, src, n, (float*)tmp);
   cudaError_t e = cudaSuccess;
   if (rc == VRB_OK) {
     e = cudaMemcpyAsync(host, tmp, bytes, cudaMemcpyDeviceToHost, s);
@@ -297,6 +390,7 @@ int vrb_renderer_set_peers(vrb_renderer* r, const void* handles, int n_ranks, in
   VRB_CUDA(cudaStreamSynchronize(p->ctx->stream));
   p->close_peers();
   if (mode == VRB_GATHER_NONE || n_ranks <= 1) return VRB_OK;
+  VRB_REQUIRE(p->ms_mode == 0, VRB_ERR_UNSUPPORTED, "vrb_renderer_set_peers: multiscaling mode %d is set", p->ms_mode);
   VRB_REQUIRE(handles && rank >= 0 && rank < n_ranks && n_ranks - 1 <= RendererImpl::MAX_PEERS, VRB_ERR_INVALID,
               "vrb_renderer_set_peers: bad rank %d of %d", rank, n_ranks);
   VRB_REQUIRE(mode == VRB_GATHER_ROOT || mode == VRB_GATHER_ALL, VRB_ERR_INVALID, "vrb_renderer_set_peers: bad mode %d", mode);
@@ -351,6 +445,7 @@ int vrb_renderer_set_bricks(vrb_renderer* r, int rank, int n_ranks, const int gr
   RendererImpl* p = r->impl;
   VRB_REQUIRE(p->kind == VRB_VCT || p->kind == VRB_DOS_CONE, VRB_ERR_UNSUPPORTED, "vrb_renderer_set_bricks: renderer kind %d has no sort-last mode", p->kind);
   VRB_REQUIRE(p->frame, VRB_ERR_INVALID, "vrb_renderer_set_bricks before Init");
+  VRB_REQUIRE(n_ranks <= 0 || !grid || p->ms_mode == 0, VRB_ERR_UNSUPPORTED, "vrb_renderer_set_bricks: multiscaling mode %d is set", p->ms_mode);
   VRB_CUDA(cudaStreamSynchronize(p->ctx->stream));
   const int w = p->width, h = p->height;
   if (n_ranks <= 0 || !grid) { p->brick_ranks = 0; p->brick_rank = 0; p->free_frame(); return p->alloc_frame(w, h); }
@@ -436,6 +531,7 @@ int vrb_renderer_set_partition(vrb_renderer* r, int rank, int n_ranks, int tile)
   VRB_REQUIRE(n_ranks >= 1 && rank >= 0 && rank < n_ranks, VRB_ERR_INVALID, "bad partition rank %d of %d", rank, n_ranks);
   VRB_REQUIRE(tile == 16 || tile == 32 || tile == 64 || tile == 128, VRB_ERR_INVALID, "partition tile must be 16, 32, 64 or 128");
   RendererImpl* p = r->impl;
+  VRB_REQUIRE(n_ranks == 1 || p->ms_mode == 0, VRB_ERR_UNSUPPORTED, "vrb_renderer_set_partition: multiscaling mode %d is set", p->ms_mode);
   p->rank = rank; p->n_ranks = n_ranks; p->part_tile = tile;
   if (p->frame) {  // tiles owned by other ranks must read 0
     VRB_CUDA(cudaMemsetAsync(p->frame_base, 0, 2 * p->frame_bytes, p->ctx->stream));

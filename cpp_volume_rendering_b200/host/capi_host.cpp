@@ -91,6 +91,16 @@ static void apply_light_cache(BaseVolumeRenderer* r) {
   r->SetOutdated();
 }
 
+// Test hook: the multiscaling radio buttons and filter-kernel combo of AddImGuiMultiSampleOptions (volrenderbase.cpp:120-200)
+// for the next session's renderer.  mode < 0 leaves the constructor's state (single ray per pixel, hat kernel).
+static int g_ms_mode = -1, g_ms_kernel = 1;
+void vrbh_session_multiscaling(int mode, int kernel) { g_ms_mode = mode; g_ms_kernel = kernel; }
+static void apply_multiscaling(BaseVolumeRenderer* r) {
+  if (g_ms_mode < 0) return;
+  r->SetImageFilterKernel(g_ms_kernel);
+  r->SetCurrentMultiScalingMode(g_ms_mode);
+}
+
 // One headless session: read the dataset + TF from disk, register the plugins, select `renderer`, optionally run
 // the evaluation sweep (eval_dir != NULL; `numframes` frames per sample, CSV in the reference's schema), else
 // render `numframes` frames.  The last frame is returned as RGBA32F (w*h*4 floats, row 0 = bottom) and RGB8.
@@ -111,6 +121,7 @@ int vrbh_run_session(const char* volume_path, const char* tf_path, int renderer,
     m->GetCamera()->SetInitialConfig(e, c, u);
     if (!m->SetCurrentVolumeRenderer(renderer)) { fail("SetCurrentVolumeRenderer: " + m->LastError()); break; }
     apply_light_cache(m->CurrentRenderer());
+    apply_multiscaling(m->CurrentRenderer());
     if (out_name && name_cap > 0) { std::strncpy(out_name, m->CurrentRenderer()->GetName(), name_cap - 1); out_name[name_cap - 1] = 0; }
     bool ok = true;
     if (eval_dir) {

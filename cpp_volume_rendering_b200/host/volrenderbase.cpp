@@ -31,6 +31,10 @@ bool BaseVolumeRenderer::CreateDeviceRenderer(int kind, int w, int h) {
   const VrbApi* a = VrbApi::Get(&m_err);
   if (!a) return false;
   if (a->renderer_create(m_ext_data_manager->Context(), kind, &m_dev) != VRB_OK) { m_dev = nullptr; return Fail("vrb_renderer_create"); }
+  // Init draws at m_rdr_frame_to_screen's size: a multiscaling mode chosen before Init applies from the first frame
+  if (GetCurrentMultiScalingMode() > 0 && a->renderer_set_multiscaling(m_dev, GetCurrentMultiScalingMode(), m_image_filter_kernel) != VRB_OK) {
+    Fail("vrb_renderer_set_multiscaling"); a->renderer_destroy(m_dev); m_dev = nullptr; return false;
+  }
   if (a->renderer_init(m_dev, w, h) != VRB_OK) { Fail("vrb_renderer_init"); a->renderer_destroy(m_dev); m_dev = nullptr; return false; }
   m_width = w; m_height = h;
   return true;
@@ -39,8 +43,31 @@ bool BaseVolumeRenderer::CreateDeviceRenderer(int kind, int w, int h) {
 void BaseVolumeRenderer::Reshape(int w, int h) {
   if (!m_dev) return;
   const VrbApi* a = VrbApi::Get();
+  // volrenderbase.cpp:48-75: UpdateScreenResolutionMultiScaling(w, h, +-2, +-2) in a multiscaling mode, else UpdateScreenResolution
+  if (a && a->renderer_set_multiscaling(m_dev, GetCurrentMultiScalingMode(), m_image_filter_kernel) != VRB_OK) Fail("vrb_renderer_set_multiscaling");
   if (a && a->renderer_reshape(m_dev, w, h) == VRB_OK) { m_width = w; m_height = h; }
   SetOutdated();
+}
+
+// The radio buttons of AddImGuiMultiSampleOptions (volrenderbase.cpp:120-172): mode, screen multiplier and resize in one call
+void BaseVolumeRenderer::SetCurrentMultiScalingMode(int f) {
+  vr_pixel_multiscaling_mode = f;
+  const VrbApi* a = VrbApi::Get();
+  if (m_dev && a && a->renderer_set_multiscaling(m_dev, GetCurrentMultiScalingMode(), m_image_filter_kernel) != VRB_OK) Fail("vrb_renderer_set_multiscaling");
+  SetOutdated();
+}
+
+// RenderFrameToScreen::SetImageFilterKernel (renderoutputframe.cpp:541-546)
+void BaseVolumeRenderer::SetImageFilterKernel(int k) {
+  m_image_filter_kernel = k;
+  const VrbApi* a = VrbApi::Get();
+  if (m_dev && a && a->renderer_set_multiscaling(m_dev, GetCurrentMultiScalingMode(), m_image_filter_kernel) != VRB_OK) Fail("vrb_renderer_set_multiscaling");
+}
+
+void BaseVolumeRenderer::RedrawMode(int mode) {
+  if (!m_dev) return;
+  const VrbApi* a = VrbApi::Get();
+  if (a && a->renderer_redraw(m_dev, mode) != VRB_OK) Fail("vrb_renderer_redraw");
 }
 
 void BaseVolumeRenderer::PrepareRender(vis::Camera* camera) {
@@ -52,7 +79,7 @@ void BaseVolumeRenderer::PrepareRender(vis::Camera* camera) {
 void BaseVolumeRenderer::Redraw() {
   if (!m_dev) return;
   const VrbApi* a = VrbApi::Get();
-  if (a && a->renderer_redraw(m_dev, vr_pixel_multiscaling_mode) != VRB_OK) Fail("vrb_renderer_redraw");
+  if (a && a->renderer_redraw(m_dev, 0) != VRB_OK) Fail("vrb_renderer_redraw");
 }
 
 void* BaseVolumeRenderer::GetScreenDevicePointer(int* w, int* h) {
@@ -64,19 +91,23 @@ void* BaseVolumeRenderer::GetScreenDevicePointer(int* w, int* h) {
 bool BaseVolumeRenderer::ReadFrameRGB8(std::vector<uint8_t>& out, int* w, int* h) {
   const VrbApi* a = VrbApi::Get();
   if (!m_dev || !a) return false;
-  out.resize((size_t)m_width * m_height * 3);
+  int fw = 0, fh = 0; void* fp = nullptr;
+  if (a->renderer_frame(m_dev, &fp, &fw, &fh) != VRB_OK) return Fail("vrb_renderer_frame");
+  out.resize((size_t)fw * fh * 3);
   if (a->renderer_read_frame(m_dev, out.data(), VRB_FRAME_RGB8_OVER_WHITE) != VRB_OK) return Fail("vrb_renderer_read_frame");
-  if (w) *w = m_width;
-  if (h) *h = m_height;
+  if (w) *w = fw;
+  if (h) *h = fh;
   return true;
 }
 bool BaseVolumeRenderer::ReadFrameRGBA32F(std::vector<float>& out, int* w, int* h) {
   const VrbApi* a = VrbApi::Get();
   if (!m_dev || !a) return false;
-  out.resize((size_t)m_width * m_height * 4);
+  int fw = 0, fh = 0; void* fp = nullptr;
+  if (a->renderer_frame(m_dev, &fp, &fw, &fh) != VRB_OK) return Fail("vrb_renderer_frame");
+  out.resize((size_t)fw * fh * 4);
   if (a->renderer_read_frame(m_dev, out.data(), VRB_FRAME_RGBA32F) != VRB_OK) return Fail("vrb_renderer_read_frame");
-  if (w) *w = m_width;
-  if (h) *h = m_height;
+  if (w) *w = fw;
+  if (h) *h = fh;
   return true;
 }
 double BaseVolumeRenderer::LastRedrawMs() {
@@ -87,7 +118,7 @@ double BaseVolumeRenderer::LastRedrawMs() {
 }
 
 // ---- CudaRayCasting1Pass -------------------------------------------------------------------------------------
-CudaRayCasting1Pass::CudaRayCasting1Pass() : m_u_step_size(0.5f), m_apply_gradient_shading(false), m_skip_block(0) {}   // rc1prenderer.cpp:18-27
+CudaRayCasting1Pass::CudaRayCasting1Pass() : m_u_step_size(0.5f), m_apply_gradient_shading(false), m_skip_block(0) { vr_pixel_multiscaling_support = true; }   // rc1prenderer.cpp:18-27
 
 bool CudaRayCasting1Pass::Init(int w, int h) {
   if (!CreateDeviceRenderer(VRB_RC1PASS, w, h)) return false;
@@ -189,6 +220,7 @@ CudaRC1PConeTracingDirOcclusionShading::CudaRC1PConeTracingDirOcclusionShading()
       occ_cone_half_angle(20.0f), occ_initial_step(3.0f), occ_covered_distance(100.0f), occ_ui_weight(0.350f), occ_max_packing(1),
       sdw_cone_half_angle(0.5f), sdw_initial_step(3.0f), sdw_covered_distance(100.0f), sdw_ui_weight(1.0f), sdw_max_packing(0),
       base_level_sigma0(1.0f), use_custom_resolution(true) {
+  vr_pixel_multiscaling_support = true;
   custom_resolution[0] = custom_resolution[1] = custom_resolution[2] = 128;
   m_pre_illum_str_vol.SetActive(false); m_pre_illum_str_vol.SetLightCacheResolution(32, 32, 32);   // :63-64
 }
@@ -227,6 +259,7 @@ CudaRC1PExtinctionBasedShading::CudaRC1PExtinctionBasedShading()                
     : m_u_step_size(0.5f), apply_ambient_occlusion(true), ambient_occlusion_shells(15), ambient_occlusion_radius(1.0f),
       apply_directional_shadows(true), dir_shadow_cone_angle(1.0f), dir_shadow_sample_interval(2.0f), dir_shadow_initial_step(2.0f),
       dir_shadow_user_interface_weight(1.0f), dir_cone_max_distance(0.0f), type_of_shadow(0), fast_sat(false) {
+  vr_pixel_multiscaling_support = true;
   m_pre_illum_str_vol.SetActive(false); m_pre_illum_str_vol.SetLightCacheResolution(32, 32, 32);   // :46-47
 }
 bool CudaRC1PExtinctionBasedShading::Init(int w, int h) {
@@ -267,6 +300,7 @@ CudaRC1PVoxelConeTracingSGPU::CudaRC1PVoxelConeTracingSGPU()                    
     : m_u_step_size(0.5f), apply_ambient_occlusion(true), apply_directional_shadows(true), apply_correction_factor(true),
       cone_step_size(2.0f), cone_step_increase_rate(1.0f), cone_initial_step(2.0f), cone_apex_angle(2.0f),
       opacity_correction_factor(2.0f), cone_number_of_samples(50) {
+  vr_pixel_multiscaling_support = true;
   m_pre_illum_str_vol.SetActive(false); m_pre_illum_str_vol.SetLightCacheResolution(32, 32, 32);   // :47-48
 }
 bool CudaRC1PVoxelConeTracingSGPU::Init(int w, int h) {
@@ -297,6 +331,7 @@ bool CudaRC1PVoxelConeTracingSGPU::Update(vis::Camera* camera) {
 
 CudaSBTMDirectionalOcclusionShading::CudaSBTMDirectionalOcclusionShading()             // sbtmdosrenderer.cpp:20-46
     : m_u_step_size(0.5f), cone_half_angle(50.0f), occ_ui_weight_percentage(1.0f), max_number_of_passes(90000) {
+  vr_pixel_multiscaling_support = true;
   grid_size[0] = grid_size[1] = 2;
 }
 bool CudaSBTMDirectionalOcclusionShading::Init(int w, int h) {

@@ -20,9 +20,9 @@ class BaseVolumeRenderer {
   virtual bool Init(int shader_width, int shader_height) = 0;
   virtual bool Update(vis::Camera* camera) = 0;
   virtual void Redraw();
-  virtual void MultiSampleRedraw() { Redraw(); }        // multiscaling filters are a "next" row
-  virtual void DownScalingRedraw() { Redraw(); }
-  virtual void UpScalingRedraw() { Redraw(); }
+  virtual void MultiSampleRedraw() { RedrawMode(MULTIPLE_RAYS_PER_PIXEL); }   // render + DrawMultiSampleHigherResolutionMode (rc1prenderer.cpp:153-164)
+  virtual void DownScalingRedraw() { RedrawMode(DOWN_SCALING_RENDER); }       // render + DrawHigherResolutionWithDownScale (:166-177)
+  virtual void UpScalingRedraw() { RedrawMode(UP_SCALING_RENDER); }           // render + DrawLowerResolutionWithUpScale (:179-190)
   virtual void Reshape(int w, int h);
   virtual void SetImGuiComponents() {}
   virtual vis::GRID_VOLUME_DATA_TYPE GetDataTypeSupport() = 0;
@@ -33,8 +33,10 @@ class BaseVolumeRenderer {
   bool IsOutdated() const { return vr_outdated; }
   bool IsBuilt() const { return vr_built; }
   bool IsPixelMultiScalingSupported() const { return vr_pixel_multiscaling_support; }
-  int GetCurrentMultiScalingMode() const { return vr_pixel_multiscaling_mode; }
-  void SetCurrentMultiScalingMode(int f) { vr_pixel_multiscaling_mode = f; }
+  int GetCurrentMultiScalingMode() const { return vr_pixel_multiscaling_support ? vr_pixel_multiscaling_mode : 0; }   // volrenderbase.cpp:105-108
+  void SetCurrentMultiScalingMode(int f);
+  void SetImageFilterKernel(int k);                     // vis::IMAGE_FILTER_KERNEL, 0 .. 5 (renderoutputframe.cpp:541-546)
+  int GetImageFilterKernel() const { return m_image_filter_kernel; }
 
   // Replaces GetScreenTextureID() (:73-75): device pointer to the RGBA16F frame (row 0 = bottom).
   virtual void* GetScreenDevicePointer(int* w, int* h);
@@ -46,11 +48,13 @@ class BaseVolumeRenderer {
 
  protected:
   void SetBuilt(bool b) { vr_built = b; }
+  void RedrawMode(int mode);
   bool CreateDeviceRenderer(int kind, int w, int h);    // vrb_renderer_create + init; false on failure
   bool Fail(const char* what);                          // records vrb_last_error()
   bool PushCameraAndLight(vis::Camera* camera);         // the CameraEye / LookAt / light uniforms every Update() binds
   bool vr_built = false, vr_outdated = true, vr_pixel_multiscaling_support = false;
   int vr_pixel_multiscaling_mode = 0;
+  int m_image_filter_kernel = 1;                        // RenderFrameToScreen::m_kernel_filter (K2_HAT, renderoutputframe.cpp:34)
   vis::DataManager* m_ext_data_manager = nullptr;
   vis::RenderingParameters* m_ext_rendering_parameters = nullptr;
   vrb_renderer* m_dev = nullptr;                        // stands where m_rdr_frame_to_screen + cp_geometry_pass stood

@@ -21,6 +21,7 @@ struct VrbApi {
   int (*renderer_get_params)(vrb_renderer*, void*, size_t);
   int (*renderer_update)(vrb_renderer*, const vrb_camera*, const vrb_light*);
   int (*renderer_redraw)(vrb_renderer*, int);
+  int (*renderer_set_multiscaling)(vrb_renderer*, int, int);
   int (*renderer_frame)(vrb_renderer*, void**, int*, int*);
   int (*renderer_read_frame)(vrb_renderer*, void*, int);
   int (*renderer_counters)(vrb_renderer*, uint64_t*, double*);

@@ -40,7 +40,7 @@ const VrbApi* VrbApi::Get(std::string* why) {
     SYM(renderer_set_params, "vrb_renderer_set_params"); SYM(renderer_get_params, "vrb_renderer_get_params");
     SYM(renderer_update, "vrb_renderer_update"); SYM(renderer_redraw, "vrb_renderer_redraw");
     SYM(renderer_frame, "vrb_renderer_frame"); SYM(renderer_read_frame, "vrb_renderer_read_frame");
-    SYM(renderer_counters, "vrb_renderer_counters");
+    SYM(renderer_counters, "vrb_renderer_counters"); SYM(renderer_set_multiscaling, "vrb_renderer_set_multiscaling");
 #undef SYM
     ok = all;
   });

@@ -70,6 +70,11 @@ def session_light_cache(active, res=(32, 32, 32)):
     lib().vrbh_session_light_cache(int(active), int(res[0]), int(res[1]), int(res[2]))
 
 
+def session_multiscaling(mode, kernel=1):
+    """Sets (mode 0..3, vis::IMAGE_FILTER_KERNEL 0..5) or resets (mode < 0) the multiscaling choice of the next run_session."""
+    lib().vrbh_session_multiscaling(int(mode), int(kernel))
+
+
 def run_session(volume_path, tf_path, renderer, width, height, eye, eval_dir=None, numframes=1, max_samples=0, device=0):
     """Returns (displays, rgba32f [H,W,4], rgb8 [H,W,3], renderer name).  Raises on failure (no CPU fallback)."""
     e = np.asarray(eye, np.float32)

@@ -49,6 +49,13 @@ typedef enum {
 } vrb_renderer_kind;
 
 typedef enum { VRB_FRAME_RGBA16F = 0, VRB_FRAME_RGB8_OVER_WHITE = 1, VRB_FRAME_RGBA32F = 2 } vrb_frame_format;
+/* OR-ed into a vrb_frame_format for vrb_renderer_read_frame: the frame the renderer wrote (at the multiscaled size), not the
+ * filtered screen-size one. */
+#define VRB_FRAME_GENERATED 0x100
+/* BaseVolumeRenderer::MULTISCALING (volrenderbase.h:28-33) and vis::IMAGE_FILTER_KERNEL (libs/vis_utils/filters/utils.hpp:7-15) */
+typedef enum { VRB_MS_SINGLE = 0, VRB_MS_MULTIPLE_RAYS_PER_PIXEL = 1, VRB_MS_DOWN_SCALING = 2, VRB_MS_UP_SCALING = 3 } vrb_multiscaling;
+typedef enum { VRB_K1_BOX = 0, VRB_K2_HAT = 1, VRB_K4_CATMULL_ROM = 2, VRB_K4_MITCHELL_NETRAVALI = 3, VRB_K4_CARDINAL_BSPLINE_3 = 4,
+               VRB_K4_CARDINAL_OMOMS3 = 5 } vrb_image_filter_kernel;
 
 typedef struct vrb_ctx vrb_ctx;
 typedef struct vrb_renderer vrb_renderer;
@@ -240,7 +247,19 @@ int vrb_renderer_reshape(vrb_renderer* r, int width, int height);             /*
 int vrb_renderer_set_params(vrb_renderer* r, const void* pod, size_t size);   /* ImGui-mutated members */
 int vrb_renderer_get_params(vrb_renderer* r, void* pod, size_t size);
 int vrb_renderer_update(vrb_renderer* r, const vrb_camera* cam, const vrb_light* light); /* Update(camera)  volrenderbase.h:48 */
-int vrb_renderer_redraw(vrb_renderer* r, int multiscaling_mode);              /* Redraw()           volrenderbase.h:49 */
+/* multiscaling_mode 0: Redraw() (volrenderbase.h:49); 1 / 2 / 3: MultiSampleRedraw() / DownScalingRedraw() / UpScalingRedraw()
+ * (volrenderbase.h:50-52) = the render followed by RenderFrameToScreen's filter pass; must equal the mode set below. */
+int vrb_renderer_redraw(vrb_renderer* r, int multiscaling_mode);
+/* Replaces SetCurrentMultiScalingMode (volrenderbase.h:71) + RenderFrameToScreen::SetImageFilterKernel (renderoutputframe.cpp:541-546)
+ * + the Reshape that follows (volrenderbase.cpp:48-75): the renderer draws at screen * 2 (modes 1, 2) or screen / 2 (mode 3); a
+ * redraw in that mode filters the generated frame to the size given to Init / Reshape.  Renderers with
+ * vr_pixel_multiscaling_support only (1-pass, EBS, VCT, DOS, SBTM); not with a partition, peers or bricks. */
+int vrb_renderer_set_multiscaling(vrb_renderer* r, int mode, int image_filter_kernel);
+/* Replaces RenderFrameToScreen::GetWidth / GetHeight (renderoutputframe.cpp:148-158): the size the renderer draws at. */
+int vrb_renderer_render_size(vrb_renderer* r, int* width, int* height);
+/* The filter pass alone over host RGBA16F frames (row 0 = bottom): renderoutputframe.cpp:265-539. */
+int vrb_frame_multiscale(vrb_ctx* ctx, int mode, int image_filter_kernel, const void* host_src_rgba16f, int src_w, int src_h,
+                         void* host_dst_rgba16f, int dst_w, int dst_h);
 
 /* Replaces GetScreenTextureID() (volrenderbase.h:73-75): device pointer to the RGBA16F frame, row 0 =
  * bottom row as in GL.  Valid until the next reshape/destroy. */

@@ -218,6 +218,13 @@ void orc_set_phong(const float* grad_rgb, int enable, float ks, float shininess,
 uint64_t orc_obj_render(const orc_obj_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n, const float* cache_rg,
                         const int dims[3], float* out_rgba);
 
+/* Output-frame multiscaling (orc_frame.cpp; renderoutputframe.cpp:265-539): mode 1 multisample, 2 downscale, 3 upscale; kernel
+ * 0 box, 1 hat, 2 Catmull-Rom, 3 Mitchell-Netravali, 4 cardinal B-spline 3, 5 cardinal O-MOMS 3.  src: sw*sh*4 floats (rounded to
+ * half on entry, row 0 = bottom), dst: tw*th*4 floats holding half-representable values. */
+void orc_frame_multiscale(int mode, int kernel, const float* src_rgba, int sw, int sh, float* dst_rgba, int tw, int th);
+float orc_frame_kernel_weight(int kernel, float x);
+void orc_frame_digital_filter(int kernel, float* rgba, int w, int h, int round_half);
+
 int orc_max_threads(void);
 
 #ifdef __cplusplus

@@ -259,6 +259,32 @@ def set_phong(grad, light):
     lib().orc_set_phong(_ptr(g), 1, float(light.ks), float(light.shininess), _ptr(isp), _ptr(lp))
 
 
+def frame_multiscale(mode, kernel, src_rgba, target_wh):
+    """RenderFrameToScreen's filter pass (orc_frame.cpp): src [h, w, 4] float32 -> [th, tw, 4] float32 (half-representable)."""
+    src = np.ascontiguousarray(src_rgba, np.float32)
+    tw, th = target_wh
+    dst = np.zeros((th, tw, 4), np.float32)
+    f = lib().orc_frame_multiscale
+    f.argtypes = [C.c_int, C.c_int, _P, C.c_int, C.c_int, _P, C.c_int, C.c_int]
+    f.restype = None
+    f(int(mode), int(kernel), _ptr(src), src.shape[1], src.shape[0], _ptr(dst), tw, th)
+    return dst
+
+
+def frame_kernel_weight(kernel, xs):
+    f = lib().orc_frame_kernel_weight
+    f.argtypes = [C.c_int, C.c_float]; f.restype = C.c_float
+    return np.array([f(int(kernel), float(x)) for x in xs], np.float32)
+
+
+def frame_digital_filter(kernel, rgba, round_half=True):
+    a = np.ascontiguousarray(rgba, np.float32).copy()
+    f = lib().orc_frame_digital_filter
+    f.argtypes = [C.c_int, _P, C.c_int, C.c_int, C.c_int]; f.restype = None
+    f(int(kernel), _ptr(a), a.shape[1], a.shape[0], 1 if round_half else 0)
+    return a
+
+
 def iso_params(cam, width, height, vol_shape_zyx, mode, isovalue=0.5, step_small=0.05, step_large=1.0, step_range=0.1,
                color=(0.66, 0.6, 0.05, 1.0), num_blocks=(4, 4, 4), voxel=(1.0, 1.0, 1.0), rows=None, threads=0,
                light=None, apply_phong=0):

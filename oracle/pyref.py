@@ -36,6 +36,10 @@ def lib():
         L.ref_cone_sections.argtypes = [C.c_float, C.c_float, C.c_int, C.c_float, C.c_double, _P, C.c_int, _P, _P,
                                         C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.ref_parameterspace_sweep.restype = C.c_int
+        L.ref_filter_weight.argtypes = [C.c_int, C.c_float]
+        L.ref_filter_weight.restype = C.c_float
+        L.ref_filter_digital2d.argtypes = [C.c_int, _P, C.c_int, C.c_int]
+        L.ref_filter_digital2d.restype = None
         _lib = L
     return _lib
 
@@ -111,3 +115,16 @@ def cone_sections(half_angle, initial_step, max_packing, covered_distance, sigma
     n = lib().ref_cone_sections(half_angle, initial_step, max_packing, covered_distance, sigma0, _ptr(out), cap, _ptr(axes),
                                 _ptr(counts), C.byref(a3), C.byref(a7))
     return out[:n].copy(), axes, counts, a3.value, a7.value
+
+
+def filter_weight(kernel, xs):
+    """vis::Box / Hat / CatmullRom / MitchellNetravali / CardinalBspline3 / CardinalOMOMS3 ::operator()(x) (filters/*.hpp)."""
+    f = lib().ref_filter_weight
+    return np.array([f(int(kernel), float(x)) for x in xs], np.float32)
+
+
+def filter_digital2d(kernel, img):
+    """digital_filter2D of kernel 4 / 5 on a [h, w] float32 image (filters/bspline3.hpp:27-45, omoms3.hpp)."""
+    a = np.ascontiguousarray(img, np.float32).copy()
+    lib().ref_filter_digital2d(int(kernel), _ptr(a), a.shape[1], a.shape[0])
+    return a

@@ -16,6 +16,15 @@
 #include <volvis_utils/transferfunction1d.h>
 #include <structured/rc1pdosct/conegaussiansampler.h>
 #include <math_utils/utils.h>
+#include <stdlib.h>                 // ::abs(float) overloads, as MSVC's <cmath> gives the filter headers (`x = abs(x)`)
+#include <math.h>
+#include <filters_utils_gxx.inc>    // the reference's filters/utils.hpp, see the Makefile
+#include <vis_utils/filters/box.hpp>
+#include <vis_utils/filters/hat.hpp>
+#include <vis_utils/filters/catmullrom.hpp>
+#include <vis_utils/filters/mitchellnetravali.hpp>
+#include <vis_utils/filters/bspline3.hpp>
+#include <vis_utils/filters/omoms3.hpp>
 #include <rodrigues_excerpt.inc>   // the reference's RodriguesRotation bodies, extracted by the Makefile
 
 extern "C" {
@@ -119,6 +128,26 @@ int ref_cone_sections(float half_angle, float initial_step, int max_packing, flo
   counts3[0] = s.gaussian_samples_1; counts3[1] = s.gaussian_samples_3; counts3[2] = s.gaussian_samples_7;
   *adj3 = s.GetRay3AdjacentWeight(); *adj7 = s.GetRay7AdjacentWeight();
   return n;
+}
+
+// ---- image filter kernels (libs/vis_utils/filters/*.hpp): the CPU twins of renderoutputframe/*_filter.comp -----
+// kernel: vis::IMAGE_FILTER_KERNEL (filters/utils.hpp:7-15)
+float ref_filter_weight(int kernel, float x) {
+  switch (kernel) {
+    case 0: return vis::Box()(x);
+    case 1: return vis::Hat()(x);
+    case 2: return vis::CatmullRom()(x);
+    case 3: return vis::MitchellNetravali()(x);
+    case 4: return vis::CardinalBspline3()(x);
+    default: return vis::CardinalOMOMS3()(x);
+  }
+}
+// digital_filter2D of the cardinal B-spline (4) / O-MOMS (5) kernel on a single-channel float image, rows then columns
+void ref_filter_digital2d(int kernel, float* img, int w, int h) {
+  std::vector<std::vector<float>> f(h, std::vector<float>(w));
+  for (int y = 0; y < h; y++) for (int x = 0; x < w; x++) f[y][x] = img[(size_t)y * w + x];
+  if (kernel == 4) vis::CardinalBspline3().digital_filter2D(f); else vis::CardinalOMOMS3().digital_filter2D(f);
+  for (int y = 0; y < h; y++) for (int x = 0; x < w; x++) img[(size_t)y * w + x] = f[y][x];
 }
 
 }  // extern "C"

@@ -88,3 +88,26 @@ def test_cone_sections_match_the_reference_sampler(half_angle, initial_step, pac
     assert np.array_equal(c.table, table.astype(np.float16).astype(np.float32), equal_nan=True)   # initial_step 0: 0/0 amplitude on both sides
     assert np.array_equal(c.axes, axes) and np.array_equal(c.counts, counts)
     assert c.adj3 == a3 and c.adj7 == a7
+
+
+@pytest.mark.parametrize("kernel", range(6))
+def test_image_filter_kernel_weights_match_reference(kernel):
+    """kernel_weight of the *_filter.comp restatement (orc_frame.cpp) == operator() of the reference's CPU twins
+    (libs/vis_utils/filters/{box,hat,catmullrom,mitchellnetravali,bspline3,omoms3}.hpp), bit for bit, on a dense grid
+    and at the piece boundaries."""
+    xs = np.concatenate([np.linspace(-2.5, 2.5, 4001, dtype=np.float32),
+                         np.float32([-2, -1, -0.5, 0, 0.5, 1, 2, np.nextafter(np.float32(0.5), np.float32(1)), np.nextafter(np.float32(-0.5), np.float32(-1))])])
+    assert np.array_equal(O.frame_kernel_weight(kernel, xs), R.filter_weight(kernel, xs))
+
+
+@pytest.mark.parametrize("kernel", [4, 5])
+@pytest.mark.parametrize("shape", [(37, 29), (10, 64), (64, 10)])
+def test_digital_filter_matches_reference(kernel, shape):
+    """cbs_digital_filter.comp / comoms_digital_filter.comp restated (rows, then columns) with float32 stores ==
+    digital_filter2D of the reference's CardinalBspline3 / CardinalOMOMS3 (filters/utils.hpp:19-42 linear_solve) for lines
+    longer than the LU table (the shader has no reflection padding for shorter ones)."""
+    img = np.random.default_rng(kernel).random(shape, dtype=np.float32)
+    got = O.frame_digital_filter(kernel, np.repeat(img[..., None], 4, axis=2), round_half=False)
+    ref = R.filter_digital2d(kernel, img)
+    for c in range(4):
+        assert np.array_equal(got[..., c], ref)
