@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("VRB200_LIB") or os.path.join(_HERE, "libvrb200.so")  
 
 VRB_U8, VRB_U16, VRB_F32 = 0, 1, 2
 (VRB_RC1PASS, VRB_ISO_ADAPT, VRB_ISO_SKIP_V1, VRB_ISO_SKIP_V2, VRB_DOS_CONE, VRB_EBS_SAT, VRB_VCT,
- VRB_SBTM_DOS) = range(8)
+ VRB_SBTM_DOS, VRB_ISO_FORWARD, VRB_ISO_DEFERRED) = range(10)
 VRB_FRAME_RGBA16F, VRB_FRAME_RGB8_OVER_WHITE, VRB_FRAME_RGBA32F = 0, 1, 2
 VRB_FRAME_GENERATED = 0x100
 VRB_MS_SINGLE, VRB_MS_MULTIPLE_RAYS_PER_PIXEL, VRB_MS_DOWN_SCALING, VRB_MS_UP_SCALING = 0, 1, 2, 3
@@ -125,6 +125,7 @@ SIGNATURES = {
     "vrb_vct_read_level": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int * 3)]),
     "vrb_vct_read_lut": (C.c_int, [_P, _P, C.POINTER(C.c_int * 2), C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
     "vrb_iso_read_blocks": (C.c_int, [_P, _P, _P]),
+    "vrb_iso_read_gbuffers": (C.c_int, [_P, _P, _P]),
     "vrb_renderer_set_partition": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
     "vrb_renderer_frame_export": (C.c_int, [_P, _P]),
     "vrb_renderer_wait_peers": (C.c_int, [_P]),
@@ -385,6 +386,13 @@ class Renderer:
         mx = np.empty((nbz, nby, nbx), np.float32)
         _check(lib().vrb_iso_read_blocks(self._h, mn.ctypes.data_as(_P), mx.ctypes.data_as(_P)))
         return mn, mx
+
+    def read_gbuffers(self):
+        """VRB_ISO_DEFERRED: (gPosition, gNormal) of the geometry pass, [h, w, 4] float32 each."""
+        w, h = self.render_size()
+        pos = np.empty((h, w, 4), np.float32); nrm = np.empty((h, w, 4), np.float32)
+        _check(lib().vrb_iso_read_gbuffers(self._h, pos.ctypes.data_as(_P), nrm.ctypes.data_as(_P)))
+        return pos, nrm
 
     def set_partition(self, rank, n_ranks, tile=32):
         _check(lib().vrb_renderer_set_partition(self._h, rank, n_ranks, tile))

@@ -98,6 +98,7 @@ struct IsoArgs {
   float nb[3]; int nbi[3];
   const float* bmin; const float* bmax;
   uint2* frame;
+  float4* gpos; float4* gnrm;     // MODE 4 test hook: the geometry pass's G-buffers (0: not kept, they never leave registers)
   uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
   PeerSignal sig;
   unsigned long long* iters;
@@ -145,6 +146,60 @@ __device__ __noinline__ void iso_composite(const IsoArgs& a, float4& dst, f3 Tpo
   dst.z = fmaf(w, __fmul_rn(cb, a.color[3]), dst.z); dst.w = fmaf(w, a.color[3], dst.w);
 }
 
+// CalculateGradient (ForwardRendering.comp:98-118, geometry_pass.comp:55-75): central differences of the density texture one
+// unit of the box either side, normalised (a zero gradient gives NaN, as normalize() does)
+__device__ __forceinline__ f3 iso_calculate_gradient(const IsoArgs& a, f3 pos) {
+  IsoRay r; r.grid = mk3(a.grid[0], a.grid[1], a.grid[2]); r.res = mk3(a.res[0], a.res[1], a.res[2]);
+  f3 g;
+  g.x = __fdiv_rn(__fsub_rn(iso_fetch(a, r, mk3(__fadd_rn(pos.x, 1.0f), pos.y, pos.z)), iso_fetch(a, r, mk3(__fsub_rn(pos.x, 1.0f), pos.y, pos.z))), 2.0f);
+  g.y = __fdiv_rn(__fsub_rn(iso_fetch(a, r, mk3(pos.x, __fadd_rn(pos.y, 1.0f), pos.z)), iso_fetch(a, r, mk3(pos.x, __fsub_rn(pos.y, 1.0f), pos.z))), 2.0f);
+  g.z = __fdiv_rn(__fsub_rn(iso_fetch(a, r, mk3(pos.x, pos.y, __fadd_rn(pos.z, 1.0f))), iso_fetch(a, r, mk3(pos.x, pos.y, __fsub_rn(pos.z, 1.0f)))), 2.0f);
+  return normalize_rn(g);
+}
+__device__ __forceinline__ float fmax_nv(float x, float y) { return fmaxf(x, y); }      // max(NaN, 0) = 0, as FMNMX
+
+// ShadeBlinnPhong of ForwardRendering.comp:119-144 + the composition of the hit (:262-270).  Out of line: once per hit.
+__device__ __noinline__ void iso_composite_forward(const IsoArgs& a, float4& dst, f3 Tpos) {
+  const f3 clr = mk3(a.color[0], a.color[1], a.color[2]);
+  const f3 N = iso_calculate_gradient(a, Tpos);
+  f3 rgb = clr;
+  if (!(__fsqrt_rn(dot_rn(N, N)) < 0.0001f)) {
+    const f3 Wpos = sub3(Tpos, scale3(mk3(a.grid[0], a.grid[1], a.grid[2]), 0.5f));
+    const f3 L = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), Wpos));
+    const f3 V = normalize_rn(sub3(mk3(a.eye[0], a.eye[1], a.eye[2]), Wpos));
+    const f3 H = normalize_rn(add3(L, V));
+    const float NdotL = fmax_nv(dot_rn(N, L), 0.0f), NdotH = fmax_nv(dot_rn(N, H), 0.0f);
+    const float sp = powf(NdotH, a.shininess);
+    const f3 amb = scale3(clr, a.ka), dif = scale3(scale3(clr, a.kd), NdotL), spc = scale3(scale3(mk3(a.ispec[0], a.ispec[1], a.ispec[2]), a.ks), sp);
+    rgb = add3(add3(amb, dif), spc);
+  }
+  const float w = 1.0f - dst.w;
+  dst.x = fmaf(w, __fmul_rn(rgb.x, a.color[3]), dst.x); dst.y = fmaf(w, __fmul_rn(rgb.y, a.color[3]), dst.y);
+  dst.z = fmaf(w, __fmul_rn(rgb.z, a.color[3]), dst.z); dst.w = fmaf(w, a.color[3], dst.w);
+}
+
+// lighting_pass.comp:26-58 + post_process.frag:14-26 (exposure 1, gamma 2.2: DeferredShading.cpp:538-539) on the G-buffer
+// values of one pixel, which the reference round-trips through two RGBA32F textures and an RGBA32F lighting texture
+__device__ __noinline__ float4 iso_deferred_light(const IsoArgs& a, f3 pos, f3 normal) {
+  float4 lit;
+  if (__fsqrt_rn(dot_rn(pos, pos)) < 0.001f || __fsqrt_rn(dot_rn(normal, normal)) < 0.001f) lit = make_float4(1.f, 1.f, 1.f, 1.f);
+  else {
+    const f3 lightDir = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), pos));
+    const f3 viewDir = normalize_rn(sub3(mk3(a.eye[0], a.eye[1], a.eye[2]), pos));
+    const f3 halfDir = normalize_rn(add3(lightDir, viewDir));
+    const float diff = fmax_nv(dot_rn(normal, lightDir), 0.0f);
+    const float spec = powf(fmax_nv(dot_rn(normal, halfDir), 0.0f), a.shininess);
+    const f3 obj = mk3(a.color[0], a.color[1], a.color[2]);
+    const f3 r = add3(add3(scale3(obj, a.ka), scale3(obj, __fmul_rn(a.kd, diff))), mk3(__fmul_rn(a.ks, spec), __fmul_rn(a.ks, spec), __fmul_rn(a.ks, spec)));
+    lit = make_float4(r.x, r.y, r.z, a.color[3]);
+  }
+  const float inv_gamma = 1.0f / 2.2f;
+  lit.x = powf(__fsub_rn(1.0f, expf(-lit.x)), inv_gamma);
+  lit.y = powf(__fsub_rn(1.0f, expf(-lit.y)), inv_gamma);
+  lit.z = powf(__fsub_rn(1.0f, expf(-lit.z)), inv_gamma);
+  return lit;
+}
+
 struct BlockLookup { int x, y, z; float mn, mx; };
 // getBlockIndex + the two GL_NEAREST / GL_REPEAT block-texture fetches
 __device__ __forceinline__ BlockLookup iso_block(const IsoArgs& a, const IsoRay& r, f3 pos) {
@@ -190,6 +245,7 @@ __global__ void __launch_bounds__(ISO_THREADS, 6) iso_kernel(const __grid_consta
     float tnear, tfar;
     const bool hit = ray_aabb(r.org, cdir, mk3(-r.half.x, -r.half.y, -r.half.z), r.half, r.dir, tnear, tfar);
     float4 dst = make_float4(0.f, 0.f, 0.f, 0.f);
+    f3 gp = mk3(0.f, 0.f, 0.f), gn = mk3(0.f, 0.f, 0.f); float gw = 0.0f;     // MODE 4: G-buffer texel of this pixel
     if (hit) {
       const float iso = a.iso;
       bool crossed = false;
@@ -278,15 +334,22 @@ __global__ void __launch_bounds__(ISO_THREADS, 6) iso_kernel(const __grid_consta
             }
           }
           if (crossed) {
-            iso_composite(a, dst, add3(add3(r.org, scale3(r.dir, t)), r.half));      // s_tex_pos at the refined t (v1 :227, v2 :247)
+            const f3 s_tex_pos = add3(add3(r.org, scale3(r.dir, t)), r.half);        // at the refined t (v1 :227, v2 :247)
+            if (MODE == 4) { gp = s_tex_pos; gn = iso_calculate_gradient(a, s_tex_pos); gw = 1.0f; break; }   // geometry_pass.comp:225-235
+            if (MODE == 3) iso_composite_forward(a, dst, s_tex_pos);
+            else iso_composite(a, dst, s_tex_pos);
             crossed = false;
             if (dst.w > 0.99f) break;
           }
         }
       }
     }
-    const uint2 texel = make_uint2(pack_half2(dst.x, dst.y), pack_half2(dst.z, dst.w));
     const size_t o = (size_t)py * a.width + px;
+    if (MODE == 4) {
+      dst = iso_deferred_light(a, gp, gn);
+      if (a.gpos) { a.gpos[o] = make_float4(gp.x, gp.y, gp.z, gw); a.gnrm[o] = make_float4(gn.x, gn.y, gn.z, gw); }
+    }
+    const uint2 texel = make_uint2(pack_half2(dst.x, dst.y), pack_half2(dst.z, dst.w));
     a.frame[o] = texel;
     for (int q = 0; q < a.n_peers; q++) a.peer[q][o] = texel;
   }
@@ -307,6 +370,7 @@ class IsoRenderer : public RendererImpl {
     prm_.color[0] = 0.66f; prm_.color[1] = 0.6f; prm_.color[2] = 0.05f; prm_.color[3] = 1.0f;
     prm_.apply_gradient_shading = 0; prm_.count_iterations = 0;
     // numBlocks: (4,4,4) in rc1custompisoadaptrenderer.cpp:190, (32,32,32) in rc1custompisoadaptdfsrenderer.cpp:190
+    // and (4,4,4) again in FowardRendering.cpp:190 and DeferredShading.cpp (geometry pass set-up)
     const int nb = k == VRB_ISO_SKIP_V2 ? 32 : 4;
     prm_.num_blocks[0] = prm_.num_blocks[1] = prm_.num_blocks[2] = nb;
   }
@@ -324,7 +388,32 @@ class IsoRenderer : public RendererImpl {
     built = true;
     return VRB_OK;
   }
-  void clean() override { blocks_.release(); }
+  void clean() override {
+    blocks_.release();
+    if (gbuf_) { cudaFree(gbuf_); gbuf_ = nullptr; gbuf_px_ = 0; }
+  }
+
+  // Test hook: the deferred renderer's G-buffers.  They exist only for this call: the frame is redrawn with the two
+  // buffers attached, then they are copied out.
+  int read_gbuffers(float* host_pos, float* host_nrm) {
+    VRB_REQUIRE(kind == VRB_ISO_DEFERRED, VRB_ERR_INVALID, "vrb_iso_read_gbuffers: not a deferred-shading renderer");
+    VRB_REQUIRE(built && have_cam, VRB_ERR_INVALID, "vrb_iso_read_gbuffers before Init/Update");
+    const size_t px = (size_t)width * height;
+    if (gbuf_px_ != px) {
+      if (gbuf_) cudaFree(gbuf_);
+      gbuf_ = nullptr; gbuf_px_ = 0;
+      VRB_CUDA(cudaMalloc(&gbuf_, 2 * px * sizeof(float4)));
+      gbuf_px_ = px;
+    }
+    keep_gbuffers_ = true;
+    const int rc = redraw(0);
+    keep_gbuffers_ = false;
+    if (rc != VRB_OK) return rc;
+    VRB_CUDA(cudaMemcpyAsync(host_pos, gbuf_, px * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    VRB_CUDA(cudaMemcpyAsync(host_nrm, gbuf_ + px, px * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    VRB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VRB_OK;
+  }
 
   int set_params(const void* pod, size_t size) override {
     VRB_REQUIRE(pod && size == sizeof(vrb_iso_params), VRB_ERR_INVALID, "iso set_params: size %zu != sizeof(vrb_iso_params) %zu", size, sizeof(vrb_iso_params));
@@ -365,7 +454,13 @@ class IsoRenderer : public RendererImpl {
     a.iso = prm_.isovalue; a.step_small = prm_.step_size_small; a.step_large = prm_.step_size_large; a.step_range = prm_.step_size_range;
     for (int i = 0; i < 4; i++) a.color[i] = prm_.color[i];
     a.grad = 0;
-    if (prm_.apply_gradient_shading) {      // m_apply_gradient_shading && GetCurrentGradientTexture() (rc1pisoadaptrenderer.cpp Update)
+    if (kind == VRB_ISO_FORWARD || kind == VRB_ISO_DEFERRED) {
+      // ForwardRendering.comp shades every hit from the density texture (its ApplyGradientPhongShading uniform is never read);
+      // the deferred lighting pass takes Ka/Kd/Ks/shininess from the rendering parameters (DeferredShading.cpp:474-484)
+      a.ka = light.ka; a.kd = light.kd; a.ks = light.ks; a.shininess = light.shininess;
+      for (int i = 0; i < 3; i++) { a.ispec[i] = light.ispecular[i]; a.light_pos[i] = light.position[i]; }
+      if (keep_gbuffers_) { a.gpos = gbuf_; a.gnrm = gbuf_ + gbuf_px_; }
+    } else if (prm_.apply_gradient_shading) {      // m_apply_gradient_shading && GetCurrentGradientTexture() (rc1pisoadaptrenderer.cpp Update)
       VRB_REQUIRE(v.tex_grad && v.grad_gen == v.generation, VRB_ERR_INVALID, "iso renderer: gradient shading needs vrb_volume_gradient() for the current volume");
       a.grad = v.tex_grad; a.grad_pt = v.tex_grad_pt; a.ka = light.ka; a.kd = light.kd; a.ks = light.ks; a.shininess = light.shininess;
       for (int i = 0; i < 3; i++) { a.ispec[i] = light.ispecular[i]; a.light_pos[i] = light.position[i]; }
@@ -408,7 +503,9 @@ class IsoRenderer : public RendererImpl {
     const bool c = prm_.count_iterations != 0;
     if (kind == VRB_ISO_ADAPT) { if (c) LAUNCH(0, true); else LAUNCH(0, false); }
     else if (kind == VRB_ISO_SKIP_V1) { if (c) LAUNCH(1, true); else LAUNCH(1, false); }
-    else { if (c) LAUNCH(2, true); else LAUNCH(2, false); }
+    else if (kind == VRB_ISO_SKIP_V2) { if (c) LAUNCH(2, true); else LAUNCH(2, false); }
+    else if (kind == VRB_ISO_FORWARD) { if (c) LAUNCH(3, true); else LAUNCH(3, false); }
+    else { if (c) LAUNCH(4, true); else LAUNCH(4, false); }
 #undef LAUNCH
     VRB_CUDA(cudaGetLastError());
     return VRB_OK;
@@ -417,13 +514,20 @@ class IsoRenderer : public RendererImpl {
  private:
   vrb_iso_params prm_{};
   BlockGrid blocks_;
+  float4* gbuf_ = nullptr; size_t gbuf_px_ = 0; bool keep_gbuffers_ = false;
 };
 
 RendererImpl* make_iso(vrb_ctx* ctx, int kind) { return new IsoRenderer(ctx, kind); }
 
 int iso_read_blocks(RendererImpl* impl, float* host_min, float* host_max) {
-  VRB_REQUIRE(impl->kind == VRB_ISO_SKIP_V1 || impl->kind == VRB_ISO_SKIP_V2, VRB_ERR_INVALID, "vrb_iso_read_blocks: renderer has no block grid");
+  VRB_REQUIRE(impl->kind == VRB_ISO_SKIP_V1 || impl->kind == VRB_ISO_SKIP_V2 || impl->kind == VRB_ISO_FORWARD || impl->kind == VRB_ISO_DEFERRED,
+              VRB_ERR_INVALID, "vrb_iso_read_blocks: renderer has no block grid");
   return static_cast<IsoRenderer*>(impl)->read_blocks(host_min, host_max);
+}
+
+int iso_read_gbuffers(RendererImpl* impl, float* host_pos, float* host_nrm) {
+  VRB_REQUIRE(impl->kind == VRB_ISO_DEFERRED, VRB_ERR_INVALID, "vrb_iso_read_gbuffers: not a deferred-shading renderer");
+  return static_cast<IsoRenderer*>(impl)->read_gbuffers(host_pos, host_nrm);
 }
 
 }  // namespace vrb

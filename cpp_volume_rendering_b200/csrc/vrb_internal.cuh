@@ -223,6 +223,7 @@ int sbtm_read_occlusion(RendererImpl* impl, float* host, int* n_slices);
 int vct_read_level(RendererImpl* impl, int level, float* host_rg, int dims[3]);
 int vct_read_lut(RendererImpl* impl, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms);
 int iso_read_blocks(RendererImpl* impl, float* host_min, float* host_max);
+int iso_read_gbuffers(RendererImpl* impl, float* host_pos, float* host_nrm);
 
 // vrb_renderer.cu: cuStreamWaitValue32(stream, addr, value, GEQ) through the runtime's driver entry point lookup
 int stream_wait_geq(cudaStream_t s, const unsigned* addr, unsigned value);

@@ -150,7 +150,7 @@ int vrb_renderer_create(vrb_ctx* ctx, int kind, vrb_renderer** out) {
   RendererImpl* impl = nullptr;
   switch (kind) {
     case VRB_RC1PASS: impl = make_rc1pass(ctx); break;
-    case VRB_ISO_ADAPT: case VRB_ISO_SKIP_V1: case VRB_ISO_SKIP_V2: impl = make_iso(ctx, kind); break;
+    case VRB_ISO_ADAPT: case VRB_ISO_SKIP_V1: case VRB_ISO_SKIP_V2: case VRB_ISO_FORWARD: case VRB_ISO_DEFERRED: impl = make_iso(ctx, kind); break;
     case VRB_EBS_SAT: impl = make_ebs(ctx); break;
     case VRB_VCT: impl = make_vct(ctx); break;
     case VRB_DOS_CONE: impl = make_dos(ctx); break;
@@ -519,6 +519,11 @@ int vrb_light_cache_read(vrb_renderer* r, float* host_rg, int dims[3], float* bu
 int vrb_dos_read_sections(vrb_renderer* r, int which, float* rgba, int cap, int* n, float axes30[30], int counts[3], float* adj7) {
   VRB_REQUIRE(r && (which == 0 || which == 1), VRB_ERR_INVALID, "vrb_dos_read_sections: bad argument");
   return dos_read_sections(r->impl, which, rgba, cap, n, axes30, counts, adj7);
+}
+
+int vrb_iso_read_gbuffers(vrb_renderer* r, float* host_position, float* host_normal) {
+  VRB_REQUIRE(r && host_position && host_normal, VRB_ERR_INVALID, "vrb_iso_read_gbuffers: null argument");
+  return iso_read_gbuffers(r->impl, host_position, host_normal);
 }
 
 int vrb_iso_read_blocks(vrb_renderer* r, float* host_min, float* host_max) {

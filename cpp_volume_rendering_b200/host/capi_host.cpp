@@ -73,8 +73,10 @@ static void register_all(RenderingManager* m) {
   m->AddVolumeRenderer(new CudaRC1PExtinctionBasedShading());           // 5
   m->AddVolumeRenderer(new CudaRC1PVoxelConeTracingSGPU());             // 6
   m->AddVolumeRenderer(new CudaSBTMDirectionalOcclusionShading());      // 7
+  m->AddVolumeRenderer(new CudaRayCasting1PassIso(VRB_ISO_FORWARD));    // 8  (main.cpp:75)
+  m->AddVolumeRenderer(new CudaRayCasting1PassIso(VRB_ISO_DEFERRED));   // 9  (main.cpp:73)
 }
-int vrbh_num_renderers(void) { return 8; }
+int vrbh_num_renderers(void) { return 10; }
 
 // Test hook: what the ImGui "light cache" checkbox / resolution fields (PreIlluminationStructuredVolume::SetImGuiComponents,
 // preillumination.cpp:82-116) would set on the next session's DOS / EBS / VCT renderer.  active < 0 leaves the constructor's state.

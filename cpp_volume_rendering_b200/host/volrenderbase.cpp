@@ -162,6 +162,8 @@ const char* CudaRayCasting1PassIso::GetName() {
   switch (m_kind) {
     case VRB_ISO_SKIP_V1: return "1-Pass - Custom Isosurface Raycaster Adaptive (CUDA B200)";
     case VRB_ISO_SKIP_V2: return "Empty Sapce Skipping V2 (CUDA B200)";
+    case VRB_ISO_FORWARD: return "Forward Bulin Phong Shading (CUDA B200)";      // FowardRendering.cpp:136-139
+    case VRB_ISO_DEFERRED: return "Deferred Rendering (CUDA B200)";               // DeferredShading.cpp:139-142
     default: return "1-Pass - Isosurface Raycaster Adaptive (CUDA B200)";
   }
 }

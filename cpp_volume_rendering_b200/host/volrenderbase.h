@@ -78,10 +78,11 @@ class CudaRayCasting1Pass : public BaseVolumeRenderer {
   int m_skip_block;                    // new: 0 / 4 / 8 / 16 / 32 (lattice-preserving empty-space skipping)
 };
 
-// RayCasting1PassIsoAdapt / CustomRayCasting1PassIsoAdapt / CustomRayCasting1PassIsodfsAdapt
+// RayCasting1PassIsoAdapt / CustomRayCasting1PassIsoAdapt / CustomRayCasting1PassIsodfsAdapt / FowardRendering
+// (structured/ForwardRender) / DeferredShading (structured/DeferredShading): same members, same parameter space
 class CudaRayCasting1PassIso : public BaseVolumeRenderer {
  public:
-  explicit CudaRayCasting1PassIso(int kind);          // VRB_ISO_ADAPT, VRB_ISO_SKIP_V1, VRB_ISO_SKIP_V2
+  explicit CudaRayCasting1PassIso(int kind);          // VRB_ISO_ADAPT, VRB_ISO_SKIP_V1, VRB_ISO_SKIP_V2, VRB_ISO_FORWARD, VRB_ISO_DEFERRED
   const char* GetName() override;
   const char* GetAbbreviationName() override { return "cu_iso"; }
   vis::GRID_VOLUME_DATA_TYPE GetDataTypeSupport() override { return vis::GRID_VOLUME_DATA_TYPE::STRUCTURED; }

@@ -12,7 +12,8 @@ LIB_PATH = os.path.join(_HERE, "libvrbhost.so")
 _P = C.c_void_p
 _lib = None
 
-RENDERERS = {"rc1pass": 0, "iso": 1, "iso_skip_v1": 2, "iso_skip_v2": 3, "dos": 4, "ebs": 5, "vct": 6, "sbtm": 7}
+RENDERERS = {"rc1pass": 0, "iso": 1, "iso_skip_v1": 2, "iso_skip_v2": 3, "dos": 4, "ebs": 5, "vct": 6, "sbtm": 7, "iso_forward": 8,
+             "iso_deferred": 9}
 
 
 def lib():

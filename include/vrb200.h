@@ -45,7 +45,9 @@ typedef enum {
   VRB_DOS_CONE = 4,    /* RC1PConeTracingDirOcclusionShading    structured/rc1pdosct        */
   VRB_EBS_SAT = 5,     /* RC1PExtinctionBasedShading            structured/rc1pextbsd       */
   VRB_VCT = 6,         /* RC1PVoxelConeTracingSGPU              structured/rc1pvctsg        */
-  VRB_SBTM_DOS = 7     /* SBTMDirectionalOcclusionShading       structured/sbtmdos          */
+  VRB_SBTM_DOS = 7,    /* SBTMDirectionalOcclusionShading       structured/sbtmdos          */
+  VRB_ISO_FORWARD = 8, /* FowardRendering                       structured/ForwardRender    */
+  VRB_ISO_DEFERRED = 9 /* DeferredShading                       structured/DeferredShading  */
 } vrb_renderer_kind;
 
 typedef enum { VRB_FRAME_RGBA16F = 0, VRB_FRAME_RGB8_OVER_WHITE = 1, VRB_FRAME_RGBA32F = 2 } vrb_frame_format;
@@ -274,6 +276,9 @@ int vrb_renderer_counters(vrb_renderer* r, uint64_t* samples, double* ms);
 /* Test hook for K5 (ComputeBlocksFromVolume, rc1custompisoadaptrenderer.cpp:20-113, moved to the GPU): the block
  * min / max grids of a VRB_ISO_SKIP_V1 / _V2 renderer, num_blocks[0]*[1]*[2] floats each, x fastest. */
 int vrb_iso_read_blocks(vrb_renderer* r, float* host_min, float* host_max);
+/* Test hook of a VRB_ISO_DEFERRED renderer: the gPosition / gNormal attachments of the geometry pass (geometry_pass.comp:4-5,
+ * RGBA32F, width*height*4 floats each, row 0 = bottom).  The render keeps them in registers; this call redraws with both attached. */
+int vrb_iso_read_gbuffers(vrb_renderer* r, float* host_position, float* host_normal);
 
 /* Test / measurement hook for K12 (GenerateExtinctionSAT3DTex, ebsrenderer.cpp:624-722, moved to the GPU): the
  * float32 table of a VRB_EBS_SAT renderer, dims = volume + 2 per axis, x fastest; build_ms = device time of the

@@ -77,7 +77,7 @@ typedef struct {
   float eye[3];
   float lookat[9];
   float tan_fovy, aspect;
-  int   mode;                   /* 0 rc1pisoadapt, 1 rc1pisocustom (skipping v1), 2 rc1pisodfscustom (skipping v2) */
+  int   mode;                   /* 0 rc1pisoadapt, 1 rc1pisocustom (skipping v1), 2 rc1pisodfscustom (skipping v2), 3 ForwardRender, 4 DeferredShading */
   float isovalue, step_small, step_large, step_range;   /* Isovalue, StepSizeSmall, StepSizeLarge, StepSizeRange */
   float color[4];               /* Color */
   int   num_blocks[3];          /* numBlocks (modes 1, 2) */
@@ -96,6 +96,9 @@ void orc_block_minmax(const void* voxels, int dtype, int w, int h, int d, int nb
  * grad_rgb: optional W*H*D*3 gradient texture (ShadeBlinnPhong when p->apply_phong) or NULL. */
 uint64_t orc_iso_render(const orc_iso_params* p, const float* vol_r16f, const float* block_min, const float* block_max,
                         float* out_rgba, uint32_t* out_iters, const float* grad_rgb);
+/* mode 4 (DeferredShading) with the geometry pass's G-buffers: position and normal, width*height*4 floats each. */
+uint64_t orc_iso_render_deferred(const orc_iso_params* p, const float* vol_r16f, const float* block_min, const float* block_max,
+                                 float* out_rgba, uint32_t* out_iters, float* out_gpos, float* out_gnrm);
 
 /* ---- extinction-based shading (K12 SAT, K13 ray caster) ------------------------------------------------ */
 typedef struct {

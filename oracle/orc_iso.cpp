@@ -3,6 +3,15 @@
 //   mode 0  cppvolrend/structured/rc1pisoadapt/ray_marching_1p_iso_adapt.comp:91-173
 //   mode 1  cppvolrend/structured/rc1pisocustom/custom_ray_marching_1p_iso_adapt.comp:92-130,153-246   (skipping v1)
 //   mode 2  cppvolrend/structured/rc1pisodfscustom/custom_ray_marching_1p_iso_adapt.comp:93-156,179-262 (skipping v2)
+//   mode 3  cppvolrend/structured/ForwardRender/ForwardRendering.comp:98-144,196-276: the v2 march, every hit shaded by
+//           ShadeBlinnPhong with a central-difference gradient taken from the density texture (CalculateGradient)
+//   mode 4  cppvolrend/structured/DeferredShading/geometry_pass.comp:55-75,150-248 (v2 march to the FIRST hit -> position and
+//           normal G-buffers, RGBA32F), lighting_pass.comp:26-58 and post_process.frag:14-26 (exposure 1, gamma 2.2:
+//           DeferredShading.cpp:538-539) evaluated per pixel; the G-buffer fetch `texture(g, pixel / size)` with GL_NEAREST
+//           (DeferredShading.cpp:166-175) is the pixel's own texel.  Uniforms as in the steady state of the reference:
+//           Ka/Kd/Ks/shininess from the rendering parameters (UpdateLightingPassUniforms, :474-484), lightColor = 1 (:216; the
+//           values LightingPass stages are bound by the next Update, so the first frames after Init light with lightColor 0).
+//           max(NaN, 0) = 0 as the hardware's FMNMX (a zero gradient normalises to NaN).
 // and K5: ComputeBlocksFromVolume (rc1pisocustom/rc1custompisoadaptrenderer.cpp:20-113).
 // Reference quirks are kept on purpose (SURVEY.md §7 "Hard parts"): v1 refine `t -= tt`, v1 tilted-ray bail-out,
 // v1 step-size choice from the stale prevDensity, block textures with the GL default GL_REPEAT wrap, shader
@@ -26,6 +35,7 @@ struct IsoCtx {
   const float* bmin; const float* bmax;   // numBlocks.x * y * z floats, x fastest (order bz,by,bx of push_back)
   vec3 grid_size, nb;
   PhongCtx ph;                            // ApplyGradientPhongShading == 1: gradient texture + light (ph.grad != NULL)
+  float* gpos = nullptr; float* gnrm = nullptr;   // mode 4: optional G-buffer outputs, width*height*4 floats each
 };
 
 inline float sgn(float x) { return x > 0.0f ? 1.0f : (x < 0.0f ? -1.0f : 0.0f); }
@@ -94,6 +104,64 @@ inline void composite(const IsoCtx& c, vec4& dst, vec3 s_tex_pos) {
   dst = dst + (1.0f - dst.w) * src;
 }
 
+inline float fmax_nv(float a, float b) { return std::isnan(a) ? b : (std::isnan(b) ? a : (a < b ? b : a)); }
+
+// CalculateGradient (ForwardRendering.comp:98-118, geometry_pass.comp:55-75)
+vec3 calculate_gradient(const IsoCtx& c, vec3 pos) {
+  const float h = 1.0f;
+  vec3 g;
+  g.x = (fetch(c, pos + vec3(h, 0, 0)) - fetch(c, pos - vec3(h, 0, 0))) / (2.0f * h);
+  g.y = (fetch(c, pos + vec3(0, h, 0)) - fetch(c, pos - vec3(0, h, 0))) / (2.0f * h);
+  g.z = (fetch(c, pos + vec3(0, 0, h)) - fetch(c, pos - vec3(0, 0, h))) / (2.0f * h);
+  return normalize(g);
+}
+// ShadeBlinnPhong of ForwardRendering.comp:119-144 + the composition of the hit (:262-270)
+void composite_forward(const IsoCtx& c, vec4& dst, vec3 Tpos) {
+  const orc_iso_params& p = *c.p;
+  vec3 clr(p.color[0], p.color[1], p.color[2]);
+  vec3 N = calculate_gradient(c, Tpos);
+  vec3 rgb = clr;
+  if (!(length(N) < 0.0001f)) {
+    vec3 Wpos = Tpos - (c.grid_size * 0.5f);
+    vec3 L = normalize(vec3(p.light_pos[0], p.light_pos[1], p.light_pos[2]) - Wpos);
+    vec3 V = normalize(vec3(p.eye[0], p.eye[1], p.eye[2]) - Wpos);
+    vec3 H = normalize(L + V);
+    float NdotL = fmax_nv(dot(N, L), 0.0f), NdotH = fmax_nv(dot(N, H), 0.0f);
+    vec3 ambient = clr * p.ka;
+    vec3 diffuse = (clr * p.kd) * NdotL;
+    vec3 specular = (vec3(p.ispec[0], p.ispec[1], p.ispec[2]) * p.ks) * std::pow(NdotH, p.shininess);
+    rgb = (ambient + diffuse) + specular;
+  }
+  vec4 src(rgb.x * p.color[3], rgb.y * p.color[3], rgb.z * p.color[3], p.color[3]);
+  dst = dst + (1.0f - dst.w) * src;
+}
+// lighting_pass.comp:26-58 + post_process.frag:14-26 for one pixel
+void deferred_light(const IsoCtx& c, vec3 pos, vec3 normal, float out[4]) {
+  const orc_iso_params& p = *c.p;
+  vec4 lit;
+  if (length(pos) < 0.001f || length(normal) < 0.001f) lit = vec4(1.0f, 1.0f, 1.0f, 1.0f);
+  else {
+    vec3 lightDir = normalize(vec3(p.light_pos[0], p.light_pos[1], p.light_pos[2]) - pos);
+    vec3 viewDir = normalize(vec3(p.eye[0], p.eye[1], p.eye[2]) - pos);
+    vec3 halfDir = normalize(lightDir + viewDir);
+    float diff = fmax_nv(dot(normal, lightDir), 0.0f);
+    float spec = std::pow(fmax_nv(dot(normal, halfDir), 0.0f), p.shininess);
+    const vec3 lightColor(1.0f, 1.0f, 1.0f), obj(p.color[0], p.color[1], p.color[2]);
+    vec3 ambient = (p.ka * lightColor) * obj;
+    vec3 diffuse = ((p.kd * diff) * lightColor) * obj;
+    vec3 specular = (p.ks * spec) * lightColor;
+    vec3 r = (ambient + diffuse) + specular;
+    lit = vec4(r.x, r.y, r.z, p.color[3]);
+  }
+  const float exposure = 1.0f, inv_gamma = 1.0f / 2.2f;
+  float rgb[3] = {lit.x, lit.y, lit.z};
+  for (int k = 0; k < 3; k++) {
+    float v = 1.0f - std::exp(-rgb[k] * exposure);
+    out[k] = round_f16(std::pow(v, inv_gamma));
+  }
+  out[3] = round_f16(lit.w);
+}
+
 uint32_t shade_pixel(const IsoCtx& c, int px, int py, float out[4], bool* hit) {
   const orc_iso_params& p = *c.p;
   vec3 eye(p.eye[0], p.eye[1], p.eye[2]);
@@ -101,6 +169,11 @@ uint32_t shade_pixel(const IsoCtx& c, int px, int py, float out[4], bool* hit) {
   Ray r; float tnear, tfar;
   bool inbox = ray_aabb_intersection(eye, camera_dir, c.grid_size, r, tnear, tfar);
   *hit = inbox;
+  if (c.p->mode == 4) {                        // every pixel of the deferred renderer goes through lighting + post-process
+    *hit = true;
+    if (c.gpos) for (int k = 0; k < 4; k++) { c.gpos[4 * ((size_t)py * c.p->width + px) + k] = 0.0f; c.gnrm[4 * ((size_t)py * c.p->width + px) + k] = 0.0f; }
+    if (!inbox) { deferred_light(c, vec3(0.0f), vec3(0.0f), out); return 0; }
+  }
   if (!inbox) return 0;
   const float iso = p.isovalue;
   vec4 dst(0.0f);
@@ -184,10 +257,23 @@ uint32_t shade_pixel(const IsoCtx& c, int px, int py, float out[4], bool* hit) {
       if (crossing(prev, iso, density)) {
         float tt = (iso - prev) / (density - prev);
         t = t - h * (1.0f - tt);                                                   // :246
-        composite(c, dst, r.Origin + r.Dir * t + half);                            // :247
+        vec3 s_tex_pos = r.Origin + r.Dir * t + half;
+        if (p.mode == 4) {                                                         // geometry_pass.comp:225-235: first hit, return
+          vec3 normal = calculate_gradient(c, s_tex_pos);
+          if (c.gpos) {
+            size_t o = 4 * ((size_t)py * p.width + px);
+            c.gpos[o] = s_tex_pos.x; c.gpos[o + 1] = s_tex_pos.y; c.gpos[o + 2] = s_tex_pos.z; c.gpos[o + 3] = 1.0f;
+            c.gnrm[o] = normal.x; c.gnrm[o + 1] = normal.y; c.gnrm[o + 2] = normal.z; c.gnrm[o + 3] = 1.0f;
+          }
+          deferred_light(c, s_tex_pos, normal, out);
+          return n;
+        }
+        if (p.mode == 3) composite_forward(c, dst, s_tex_pos);                     // ForwardRendering.comp:262-270
+        else composite(c, dst, s_tex_pos);                                         // :247
         if (dst.w > 0.99f) break;
       }
     }
+    if (p.mode == 4) { deferred_light(c, vec3(0.0f), vec3(0.0f), out); return n; } // no hit: zero G-buffers (:243-245)
   }
   out[0] = round_f16(dst.x); out[1] = round_f16(dst.y); out[2] = round_f16(dst.z); out[3] = round_f16(dst.w);
   return n;
@@ -226,9 +312,22 @@ extern "C" void orc_block_minmax(const void* voxels, int dtype, int w, int h, in
       }
 }
 
+static uint64_t iso_render(const orc_iso_params* p, const float* vol_r16f, const float* block_min, const float* block_max,
+                           float* out_rgba, uint32_t* out_iters, const float* grad_rgb, float* gpos, float* gnrm);
+
 extern "C" uint64_t orc_iso_render(const orc_iso_params* p, const float* vol_r16f, const float* block_min,
                                    const float* block_max, float* out_rgba, uint32_t* out_iters, const float* grad_rgb) {
-  IsoCtx c; c.p = p;
+  return iso_render(p, vol_r16f, block_min, block_max, out_rgba, out_iters, grad_rgb, nullptr, nullptr);
+}
+// mode 4 with the two RGBA32F G-buffers of the geometry pass (width*height*4 floats each, row 0 = bottom)
+extern "C" uint64_t orc_iso_render_deferred(const orc_iso_params* p, const float* vol_r16f, const float* block_min,
+                                            const float* block_max, float* out_rgba, uint32_t* out_iters, float* out_gpos, float* out_gnrm) {
+  return iso_render(p, vol_r16f, block_min, block_max, out_rgba, out_iters, nullptr, out_gpos, out_gnrm);
+}
+
+static uint64_t iso_render(const orc_iso_params* p, const float* vol_r16f, const float* block_min, const float* block_max,
+                           float* out_rgba, uint32_t* out_iters, const float* grad_rgb, float* gpos, float* gnrm) {
+  IsoCtx c; c.p = p; c.gpos = gpos; c.gnrm = gnrm;
   c.vol.w = p->vol_w; c.vol.h = p->vol_h; c.vol.d = p->vol_d; c.vol.data = vol_r16f; c.vol.wmode = p->weight_mode;
   c.bmin = block_min; c.bmax = block_max;
   c.grid_size = vec3((float)p->vol_w, (float)p->vol_h, (float)p->vol_d) * vec3(p->voxel[0], p->voxel[1], p->voxel[2]);

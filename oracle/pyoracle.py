@@ -316,6 +316,18 @@ def iso_render(p, vol_r16f, block_min=None, block_max=None, want_iters=False, gr
     return out, int(total), it
 
 
+def iso_render_deferred(p, vol_r16f, block_min, block_max):
+    """mode 4 (DeferredShading): (frame [h, w, 4], iterations, gPosition [h, w, 4], gNormal [h, w, 4])."""
+    vol = np.ascontiguousarray(vol_r16f, np.float32)
+    out = np.zeros((p.height, p.width, 4), np.float32)
+    gpos = np.zeros((p.height, p.width, 4), np.float32); gnrm = np.zeros((p.height, p.width, 4), np.float32)
+    f = lib().orc_iso_render_deferred
+    f.restype = C.c_uint64
+    f.argtypes = [_P] * 8
+    total = f(C.byref(p), _ptr(vol), _ptr(block_min), _ptr(block_max), _ptr(out), None, _ptr(gpos), _ptr(gnrm))
+    return out, int(total), gpos, gnrm
+
+
 def ext_sat3d(voxels, table, extinction_type=False, want_ext=False):
     """GenerateExtinctionSAT3DTex: float32 SAT indexed [z, y, x] of shape (d+2, h+2, w+2)."""
     v = np.ascontiguousarray(voxels)
