@@ -48,6 +48,15 @@ int vrbh_read_volume(const char* path, int dims[3], int* bytes_per_voxel, void* 
   return 0;
 }
 
+// The voxel scale a reader sets (PVM2/PVM3 scale line, SliceThickness of a .dat; 1 otherwise).
+int vrbh_read_volume_scale(const char* path, double scale[3]) {
+  vis::StructuredGridVolume* v = vis::VolumeReader().ReadVolume(path);
+  if (!v) return -1;
+  scale[0] = v->GetScaleX(); scale[1] = v->GetScaleY(); scale[2] = v->GetScaleZ();
+  delete v;
+  return 0;
+}
+
 // Camera uniforms as Update() binds them.
 void vrbh_camera_uniforms(const float eye[3], const float center[3], const float up[3], float fovy_deg, int w, int h, vrb_camera* out) {
   vis::Camera cam;

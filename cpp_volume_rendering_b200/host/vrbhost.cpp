@@ -10,6 +10,9 @@
 #include <mutex>
 #include <sstream>
 #include <stdexcept>
+#include <fstream>
+#include <iterator>
+#include <vector>
 
 // ---- libvrb200.so loader -----------------------------------------------------------------------------------
 const VrbApi* VrbApi::Get(std::string* why) {
@@ -149,7 +152,239 @@ static bool ends_with(const std::string& s, const char* suf) { size_t n = std::s
 StructuredGridVolume* VolumeReader::ReadVolume(const std::string& path) {
   if (ends_with(path, ".raw")) return readraw(path);
   if (ends_with(path, ".syn")) return readsyn(path);
-  return nullptr;   // .pvm / .nrrd / .dat are outside the path's scope
+  if (ends_with(path, ".pvm")) return readpvm(path);
+  if (ends_with(path, ".nrrd")) return readnrrd(path);
+  if (ends_with(path, ".nhrd")) return readnhrd(path);            // the reference's spelling of the extension (reader.cpp:50)
+  if (ends_with(path, ".dat")) return readdat(path);
+  return nullptr;   // .pvmold: the pre-2.0 PVM layout of pvm_old.cpp is not read
+}
+
+// ---- header + detached raw file formats (reader.cpp:373-628) ------------------------------------------------
+namespace {
+
+std::string dir_of(const std::string& path) {
+  const size_t t = path.find_last_of("/\\");
+  return t == std::string::npos ? path : path.substr(0, t);        // reader.cpp:381-389: no separator -> the path itself
+}
+// "key: value" with the blanks after the colon skipped (reader.cpp:413-421); CR of CRLF files dropped
+bool split_key(const std::string& line_in, std::string& key, std::string& content) {
+  std::string line = line_in;
+  while (!line.empty() && (line.back() == '\r' || line.back() == '\n')) line.pop_back();
+  key = line.substr(0, line.find_first_of(':'));
+  const size_t c = line.find_first_of(':');
+  content = c == std::string::npos ? line : line.substr(c + 1);
+  size_t skip = 0;
+  while (skip < content.size() && (content[skip] == ' ' || content[skip] == '\t')) skip++;
+  content = content.substr(skip);
+  return true;
+}
+template <typename T, typename F>
+std::vector<T> split_numbers(const std::string& s, F conv) {
+  std::vector<T> v;
+  std::istringstream ss(s);
+  std::string tok;
+  while (ss >> tok) v.push_back(conv(tok));
+  return v;
+}
+// SetArrayDataFromRawFile (reader.cpp:62-98): w*h*d values of 1 or 2 bytes from the start of the file
+bool set_array_from_raw(const std::string& file, vis::StructuredGridVolume* sg, int bytes_per_value) {
+  const size_t n = (size_t)sg->GetWidth() * sg->GetHeight() * sg->GetDepth() * (size_t)bytes_per_value;
+  std::ifstream f(file, std::ios::binary);
+  if (!f) return false;
+  void* data = std::malloc(n);
+  f.read((char*)data, (std::streamsize)n);
+  if ((size_t)f.gcount() != n) { std::free(data); return false; }
+  sg->SetArrayData(data, bytes_per_value == 1 ? vis::DataStorageSize::_8_BITS : vis::DataStorageSize::_16_BITS);
+  return true;
+}
+
+}  // namespace
+
+// NRRD with a detached data file (reader.cpp:373-491): "type", "sizes" and "data file" are used; spacing is left at 1
+// ("space directions" is parsed to the identity and never applied); raw encoding only.
+StructuredGridVolume* VolumeReader::readnrrd(const std::string& path) {
+  std::ifstream f(path);
+  if (!f) return nullptr;
+  std::string line, type, data_file;
+  std::vector<int> sizes;
+  std::getline(f, line);                                           // "NRRD000x"
+  while (std::getline(f, line)) {
+    if (line.find_first_of('#') == 0) continue;
+    std::string key, content;
+    split_key(line, key, content);
+    if (key.find("type") == 0) type = content;
+    else if (key.find("sizes") == 0) sizes = split_numbers<int>(content, [](const std::string& t) { return std::atoi(t.c_str()); });
+    else if (key.find("data file") == 0) data_file = content;
+  }
+  if (sizes.size() < 3 || sizes[0] <= 0 || sizes[1] <= 0 || sizes[2] <= 0 || data_file.empty()) return nullptr;
+  const size_t slash = path.find_last_of("/\\");
+  auto* vol = new StructuredGridVolume(slash == std::string::npos ? path : path.substr(slash + 1), sizes[0], sizes[1], sizes[2]);
+  vol->SetScale(1.0, 1.0, 1.0);
+  int bytes = 1;                                                   // :470-476
+  if (type.find("uint8") != std::string::npos) bytes = 1;
+  if (type.find("uint16") != std::string::npos) bytes = 2;
+  if (!set_array_from_raw(dir_of(path) + "/" + data_file, vol, bytes)) { delete vol; return nullptr; }
+  return vol;
+}
+StructuredGridVolume* VolumeReader::readnhrd(const std::string& path) { return readnrrd(path); }   // reader.cpp:493-496
+
+// .dat header of the "ObjectFileName / Resolution / SliceThickness / Format" kind (reader.cpp:498-628)
+StructuredGridVolume* VolumeReader::readdat(const std::string& path) {
+  std::ifstream f(path);
+  if (!f) return nullptr;
+  std::string line, object_file, format;
+  std::vector<int> res;
+  std::vector<float> thick;
+  while (std::getline(f, line)) {
+    std::string key, content;
+    split_key(line, key, content);
+    if (key.find("ObjectFileName") == 0) object_file = content;
+    else if (key.find("Resolution") == 0) res = split_numbers<int>(content, [](const std::string& t) { return std::atoi(t.c_str()); });
+    else if (key.find("SliceThickness") == 0) thick = split_numbers<float>(content, [](const std::string& t) { return (float)std::atof(t.c_str()); });
+    else if (key.find("Format") == 0) format = content;
+  }
+  if (res.size() < 3 || res[0] <= 0 || res[1] <= 0 || res[2] <= 0 || object_file.empty()) return nullptr;
+  const size_t slash = path.find_last_of("/\\");
+  auto* vol = new StructuredGridVolume(slash == std::string::npos ? path : path.substr(slash + 1), res[0], res[1], res[2]);
+  if (thick.size() >= 3) vol->SetScale(thick[0], thick[1], thick[2]); else vol->SetScale(1.0, 1.0, 1.0);
+  int bytes = 1;                                                   // :607-613
+  if (format.find("UCHAR") != std::string::npos) bytes = 1;
+  else if (format.find("USHORT") != std::string::npos) bytes = 2;
+  if (!set_array_from_raw(dir_of(path) + "/" + object_file, vol, bytes)) { delete vol; return nullptr; }
+  return vol;
+}
+
+// ---- .pvm (reader.cpp:100-160, libs/file_utils/pvm.cpp — the V^3 volume format of S. Roettger) ---------------
+// Container: "PVM\n" [# comment lines] "W H D\n" "C\n" voxels | "PVM2\n" "W H D\n" "sx sy sz\n" "C\n" voxels | "PVM3\n" as PVM2 + four
+// NUL-terminated strings after the voxels (pvm.cpp:220-262).  The file is either that byte string as it stands or a
+// differential data stream ("DDS v3d\n" / "DDS v3e\n", pvm.cpp:382-441,518-571): a big-endian bit stream of
+//   skip - 1 (2 bits), strip - 1 (16 bits), then runs { count (7 bits, 0 ends the stream), code (3 bits; width = code + 1 for
+//   code >= 1, else 0), count x residual (width bits, biased by 2^width / 2) },
+// each byte predicted from its predecessor plus, past the first strip, the difference one strip back; bytes wrap modulo 256.
+// The decoded bytes are then re-interleaved: `skip` planes of every skip-th byte (whole stream for v3d, blocks of skip * 2^24
+// bytes for v3e).
+namespace {
+
+struct BitReader {
+  const uint8_t* p; size_t n, pos = 0; uint32_t buf = 0; unsigned have = 0;
+  BitReader(const uint8_t* d, size_t size) : p(d), n(size) {}
+  uint32_t word() {                                                // next 32 bits, zero-padded past the end
+    uint32_t w = 0;
+    for (int k = 0; k < 4; k++) { w <<= 8; if (pos < n) w |= p[pos]; pos++; }
+    return w;
+  }
+  uint32_t read(unsigned bits) {
+    uint32_t v = 0;
+    while (bits) {
+      if (!have) { buf = word(); have = 32; }
+      const unsigned take = bits < have ? bits : have;
+      const uint32_t chunk = take == 32 ? buf : ((buf >> (have - take)) & ((1u << take) - 1u));
+      v = take == 32 ? chunk : ((v << take) | chunk);
+      have -= take; bits -= take;
+    }
+    return v;
+  }
+  bool exhausted() const { return pos >= n + 8; }                  // a stream without its end marker: stop on the padding
+};
+
+void dds_restore_planes(uint8_t* data, size_t bytes, unsigned skip) {
+  std::vector<uint8_t> tmp(bytes);
+  size_t src = 0;
+  for (unsigned i = 0; i < skip; i++)
+    for (size_t j = i; j < bytes; j += skip) tmp[j] = data[src++];
+  std::memcpy(data, tmp.data(), bytes);
+}
+
+bool dds_decode(const std::vector<uint8_t>& chunk, size_t block, std::vector<uint8_t>& out) {
+  BitReader br(chunk.data(), chunk.size());
+  const unsigned skip = br.read(2) + 1, strip = br.read(16) + 1;
+  int act = 0;
+  out.clear();
+  for (;;) {
+    const unsigned count = br.read(7);
+    if (count == 0) break;
+    if (br.exhausted()) return false;
+    const unsigned code = br.read(3), width = code >= 1 ? code + 1 : 0;
+    for (unsigned k = 0; k < count; k++) {
+      const size_t cnt = out.size();
+      const int residual = (int)(width ? br.read(width) : 0) - (1 << width) / 2;
+      if (strip == 1 || cnt <= strip) act += residual;
+      else act += (int)out[cnt - strip] - (int)out[cnt - strip - 1] + residual;
+      while (act < 0) act += 256;
+      while (act > 255) act -= 256;
+      out.push_back((uint8_t)act);
+    }
+  }
+  if (skip > 1 && !out.empty()) {
+    if (block == 0) dds_restore_planes(out.data(), out.size(), skip);
+    else {
+      const size_t span = (size_t)skip * block;
+      size_t k = 0;
+      for (; k < out.size() / span; k++) dds_restore_planes(out.data() + k * span, span, skip);
+      dds_restore_planes(out.data() + k * span, out.size() - k * span, skip);
+    }
+  }
+  return true;
+}
+
+bool read_all(const std::string& path, std::vector<uint8_t>& bytes) {
+  std::ifstream f(path, std::ios::binary);
+  if (!f) return false;
+  bytes.assign(std::istreambuf_iterator<char>(f), std::istreambuf_iterator<char>());
+  return true;
+}
+
+}  // namespace
+
+StructuredGridVolume* VolumeReader::readpvm(const std::string& path) {
+  std::vector<uint8_t> file, data;
+  if (!read_all(path, file)) return nullptr;
+  const char id_d[] = "DDS v3d\n", id_e[] = "DDS v3e\n";
+  if (file.size() >= 8 && (std::memcmp(file.data(), id_d, 8) == 0 || std::memcmp(file.data(), id_e, 8) == 0)) {
+    const bool v3e = file[6] == 'e';
+    std::vector<uint8_t> chunk(file.begin() + 8, file.end());
+    if (!dds_decode(chunk, v3e ? ((size_t)1 << 24) : 0, data)) return nullptr;
+  } else data.swap(file);
+  if (data.size() < 5) return nullptr;
+  data.push_back(0);
+  const char* txt = (const char*)data.data();
+  const char* end = txt + data.size() - 1;
+  int version = 1;
+  const char* ptr;
+  unsigned w = 0, h = 0, d = 0, comps = 0;
+  float sx = 1.0f, sy = 1.0f, sz = 1.0f;
+  auto next_line = [&](const char* q) -> const char* { const char* nl = std::strchr(q, '\n'); return nl ? nl + 1 : nullptr; };
+  if (std::strncmp(txt, "PVM\n", 4) != 0) {
+    if (std::strncmp(txt, "PVM2\n", 5) == 0) version = 2;
+    else if (std::strncmp(txt, "PVM3\n", 5) == 0) version = 3;
+    else return nullptr;
+    ptr = txt + 5;
+    if (std::sscanf(ptr, "%u %u %u\n%g %g %g\n", &w, &h, &d, &sx, &sy, &sz) != 6) return nullptr;
+    if (w < 1 || h < 1 || d < 1 || sx <= 0.0f || sy <= 0.0f || sz <= 0.0f) return nullptr;
+    ptr = next_line(ptr);                                          // past "W H D"; the scale line is skipped below
+  } else {
+    ptr = txt + 4;
+    while (ptr && *ptr == '#') ptr = next_line(ptr);
+    if (!ptr || std::sscanf(ptr, "%u %u %u\n", &w, &h, &d) != 3 || w < 1 || h < 1 || d < 1) return nullptr;
+  }
+  if (!ptr || !(ptr = next_line(ptr))) return nullptr;
+  if (std::sscanf(ptr, "%u\n", &comps) != 1 || (comps != 1 && comps != 2)) return nullptr;   // reader.cpp:119-146: 8 or 16 bits
+  if (!(ptr = next_line(ptr))) return nullptr;
+  const size_t voxels = (size_t)w * h * d, need = voxels * comps;
+  if ((size_t)(end - ptr) < need) return nullptr;
+  if (version < 3 && (size_t)(end - ptr) != need) return nullptr;  // pvm.cpp:262: the sizes must add up
+  const uint8_t* raw = (const uint8_t*)ptr;
+  void* out = std::malloc(need);
+  if (comps == 1) std::memcpy(out, raw, need);
+  else {
+    // Pvm::PostProcessData (pvm.cpp:80-108): value = byte[2i + 1] * 256 + byte[2i]
+    uint16_t* o = (uint16_t*)out;
+    for (size_t i = 0; i < voxels; i++) o[i] = (uint16_t)(raw[2 * i + 1] * 256u + raw[2 * i]);
+  }
+  auto* vol = new StructuredGridVolume(path, w, h, d);
+  vol->SetScale(sx, sy, sz);
+  vol->SetArrayData(out, comps == 1 ? DataStorageSize::_8_BITS : DataStorageSize::_16_BITS);
+  return vol;
 }
 
 // <name>.<bytes per voxel>.<W>x<H>x<D>.raw, voxels x fastest (reader.cpp:172-205, :62-98)

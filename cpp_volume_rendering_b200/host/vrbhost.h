@@ -130,12 +130,17 @@ class TransferFunction1D {
   std::vector<double> m_table;
 };
 
-// ---- libs/volvis_utils/reader.cpp: .raw (:162-225 + :62-98), .syn (:283-371), .tf1d (:744-814) -------------
+// ---- libs/volvis_utils/reader.cpp: .raw (:162-225 + :62-98), .syn (:283-371), .pvm (:100-160 + file_utils/pvm.cpp), .nrrd / .nhrd
+// (:373-496), .dat (:498-628), .tf1d (:744-814) ---------------------------------------------------------------
 class VolumeReader {
  public:
   StructuredGridVolume* ReadVolume(const std::string& path);   // dispatch on extension; nullptr on failure
   StructuredGridVolume* readraw(const std::string& path);
   StructuredGridVolume* readsyn(const std::string& path);
+  StructuredGridVolume* readpvm(const std::string& path);      // PVM / PVM2 / PVM3, plain or DDS v3d / v3e compressed, 8 or 16 bits
+  StructuredGridVolume* readnrrd(const std::string& path);     // detached header: type, sizes, data file
+  StructuredGridVolume* readnhrd(const std::string& path);
+  StructuredGridVolume* readdat(const std::string& path);      // ObjectFileName, Resolution, SliceThickness, Format
 };
 class TransferFunctionReader {
  public:

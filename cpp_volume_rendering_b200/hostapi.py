@@ -59,6 +59,13 @@ def read_volume(path):
     return out
 
 
+def read_volume_scale(path):
+    sc = (C.c_double * 3)()
+    if lib().vrbh_read_volume_scale(path.encode(), sc) != 0:
+        raise RuntimeError(f"cannot read {path}")
+    return tuple(sc)
+
+
 def camera_uniforms(eye, center=(0, 0, 0), up=(0, 1, 0), fovy_deg=45.0, width=1, height=1):
     e, c, u = (np.asarray(t, np.float32) for t in (eye, center, up))
     cam = _capi.Camera()

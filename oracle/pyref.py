@@ -128,3 +128,16 @@ def filter_digital2d(kernel, img):
     a = np.ascontiguousarray(img, np.float32).copy()
     lib().ref_filter_digital2d(int(kernel), _ptr(a), a.shape[1], a.shape[0])
     return a
+
+
+def pvm_read(path):
+    """Pvm(path) of libs/file_utils/pvm.cpp: (voxels [d, h, w] uint8 / uint16, scale)."""
+    dims = (C.c_uint * 3)(); comps = C.c_uint(); sc = (C.c_double * 3)()
+    f = lib().ref_pvm_read
+    f.argtypes = [C.c_char_p, _P, _P, _P, _P, C.c_longlong]; f.restype = C.c_int
+    if f(path.encode(), dims, C.byref(comps), sc, None, 0) != 0:
+        raise RuntimeError(f"reference cannot read {path}")
+    w, h, d = dims
+    out = np.empty((d, h, w), np.uint8 if comps.value == 1 else np.uint16)
+    f(path.encode(), dims, C.byref(comps), sc, _ptr(out), out.nbytes)
+    return out, tuple(sc)

@@ -16,6 +16,7 @@
 #include <volvis_utils/transferfunction1d.h>
 #include <structured/rc1pdosct/conegaussiansampler.h>
 #include <math_utils/utils.h>
+#include <file_utils/pvm.h>
 #include <stdlib.h>                 // ::abs(float) overloads, as MSVC's <cmath> gives the filter headers (`x = abs(x)`)
 #include <math.h>
 #include <filters_utils_gxx.inc>    // the reference's filters/utils.hpp, see the Makefile
@@ -148,6 +149,18 @@ void ref_filter_digital2d(int kernel, float* img, int w, int h) {
   for (int y = 0; y < h; y++) for (int x = 0; x < w; x++) f[y][x] = img[(size_t)y * w + x];
   if (kernel == 4) vis::CardinalBspline3().digital_filter2D(f); else vis::CardinalOMOMS3().digital_filter2D(f);
   for (int y = 0; y < h; y++) for (int x = 0; x < w; x++) img[(size_t)y * w + x] = f[y][x];
+}
+
+// ---- Pvm (libs/file_utils/pvm.cpp): the reference's .pvm reader, DDS decompression included --------------------------------
+// out: width*height*depth values of `components` bytes, as Pvm::GetData() hands them to VolumeReader::readpvm.
+int ref_pvm_read(const char* path, unsigned dims[3], unsigned* components, double scale[3], void* out, long long cap_bytes) {
+  Pvm f(path);
+  f.GetDimensions(&dims[0], &dims[1], &dims[2]);
+  *components = (unsigned)f.GetComponents();
+  f.GetScale(&scale[0], &scale[1], &scale[2]);
+  const long long need = (long long)dims[0] * dims[1] * dims[2] * (long long)*components;
+  if (out && cap_bytes >= need && f.GetData()) memcpy(out, f.GetData(), (size_t)need);
+  return f.GetData() ? 0 : -1;
 }
 
 }  // extern "C"
