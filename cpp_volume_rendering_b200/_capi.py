@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("VRB200_LIB") or os.path.join(_HERE, "libvrb200.so")  
 
 VRB_U8, VRB_U16, VRB_F32 = 0, 1, 2
 (VRB_RC1PASS, VRB_ISO_ADAPT, VRB_ISO_SKIP_V1, VRB_ISO_SKIP_V2, VRB_DOS_CONE, VRB_EBS_SAT, VRB_VCT,
- VRB_SBTM_DOS, VRB_ISO_FORWARD, VRB_ISO_DEFERRED) = range(10)
+ VRB_SBTM_DOS, VRB_ISO_FORWARD, VRB_ISO_DEFERRED, VRB_CRT_GT) = range(11)
 VRB_FRAME_RGBA16F, VRB_FRAME_RGB8_OVER_WHITE, VRB_FRAME_RGBA32F = 0, 1, 2
 VRB_FRAME_GENERATED = 0x100
 VRB_MS_SINGLE, VRB_MS_MULTIPLE_RAYS_PER_PIXEL, VRB_MS_DOWN_SCALING, VRB_MS_UP_SCALING = 0, 1, 2, 3
@@ -46,6 +46,15 @@ class IsoParams(C.Structure):
     _fields_ = [("isovalue", C.c_float), ("step_size_small", C.c_float), ("step_size_large", C.c_float),
                 ("step_size_range", C.c_float), ("color", C.c_float * 4), ("apply_gradient_shading", C.c_int),
                 ("num_blocks", C.c_int * 3), ("count_iterations", C.c_int)]
+
+
+class CrtgtParams(C.Structure):
+    _fields_ = [("step_size", C.c_float), ("light_ray_initial_step", C.c_float), ("light_ray_step_size", C.c_float),
+                ("apply_occlusion", C.c_int), ("occ_cone_aperture_angle", C.c_float), ("occ_cone_distance_eval", C.c_float),
+                ("apply_shadows", C.c_int), ("sdw_cone_aperture_angle", C.c_float), ("sdw_cone_distance_eval", C.c_float),
+                ("shadow_type", C.c_int), ("apply_gradient_shading", C.c_int), ("show_frame_texture", C.c_int),
+                ("samples_per_redraw", C.c_int), ("light_cam_forward", C.c_float * 3), ("light_cam_up", C.c_float * 3),
+                ("light_cam_right", C.c_float * 3), ("count_samples", C.c_int)]
 
 
 class EbsParams(C.Structure):
@@ -126,6 +135,8 @@ SIGNATURES = {
     "vrb_vct_read_lut": (C.c_int, [_P, _P, C.POINTER(C.c_int * 2), C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
     "vrb_iso_read_blocks": (C.c_int, [_P, _P, _P]),
     "vrb_iso_read_gbuffers": (C.c_int, [_P, _P, _P]),
+    "vrb_crtgt_set_kernels": (C.c_int, [_P, _P, C.c_int, _P, C.c_int]),
+    "vrb_crtgt_read_state": (C.c_int, [_P, _P, C.POINTER(C.c_longlong)]),
     "vrb_renderer_set_partition": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
     "vrb_renderer_frame_export": (C.c_int, [_P, _P]),
     "vrb_renderer_wait_peers": (C.c_int, [_P]),
@@ -393,6 +404,17 @@ class Renderer:
         pos = np.empty((h, w, 4), np.float32); nrm = np.empty((h, w, 4), np.float32)
         _check(lib().vrb_iso_read_gbuffers(self._h, pos.ctypes.data_as(_P), nrm.ctypes.data_as(_P)))
         return pos, nrm
+
+    def crtgt_set_kernels(self, occ_xyz, sdw_xyz):
+        occ = np.ascontiguousarray(occ_xyz, np.float32).reshape(-1, 3); sdw = np.ascontiguousarray(sdw_xyz, np.float32).reshape(-1, 3)
+        _check(lib().vrb_crtgt_set_kernels(self._h, occ.ctypes.data_as(_P), len(occ), sdw.ctypes.data_as(_P), len(sdw)))
+
+    def crtgt_read_state(self):
+        """(state [h, w, 2] float32: ray distance and done flag, pixels left unfinished by the last redraw)."""
+        w, h = self.render_size()
+        st = np.empty((h, w, 2), np.float32); left = C.c_longlong()
+        _check(lib().vrb_crtgt_read_state(self._h, st.ctypes.data_as(_P), C.byref(left)))
+        return st, int(left.value)
 
     def set_partition(self, rank, n_ranks, tile=32):
         _check(lib().vrb_renderer_set_partition(self._h, rank, n_ranks, tile))

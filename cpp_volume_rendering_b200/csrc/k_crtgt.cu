@@ -1,0 +1,375 @@
+// K24 — RC1PConeLightGroundTruthSteps (cppvolrend/structured/rc1pcrtgt): the ray-cast cone "ground truth" of the occlusion and
+// shadow approximations of the DOS / EBS / VCT renderers.  gt_ray_marching.comp takes ONE primary sample per pixel and
+// dispatch (every sample casts OccNumberOfSampledRays + SdwNumberOfSampledRays secondary rays through the volume) and keeps
+// the ray's distance + a done flag in an RG16F state image and the colour in the RGBA16F frame between dispatches
+// (crtgtrenderer.cpp:273-325).  Here one launch folds `samples_per_redraw` dispatches: distance and colour stay in registers
+// and are rounded to half after every sample exactly as the two images would round them, so N folded samples equal N Redraws of
+// the reference.  vol_intersection.comp (the face-coloured box shown while no frame is generated) is the other kernel.
+// Bound: texture fetch latency of the secondary rays (each a serial chain of dependent exp() products).
+#include "vrb_internal.cuh"
+#include "vrb_ray.cuh"
+#include <cmath>
+#include <vector>
+
+namespace vrb {
+
+struct GtArgs {
+  cudaTextureObject_t quad;
+  const uint2* tf_lin; int tf_n;
+  int width, height;
+  float res[3], sizes[3], eye[3], lookat[9], tan_fovy, aspect;
+  float step, gap, lstep;
+  int apply_occlusion, n_occ; float occ_dist;
+  int apply_shadow, n_sdw; float sdw_dist;
+  int shadow_type;
+  float light_pos[3], fwd[3], up[3], right[3], ka, kd;
+  PhongParams phong;
+  const float* occ; const float* sdw;          // kernel vectors, half-representable floats, 3 per ray
+  uint2* frame; __half2* state;
+  int samples;
+  unsigned long long* count; unsigned* unfinished;
+};
+
+__device__ __forceinline__ float round_half(float v) { return __half2float(__float2half_rn(v)); }
+__device__ __forceinline__ f3 cross_rn(f3 a, f3 b) {
+  return mk3(__fsub_rn(__fmul_rn(a.y, b.z), __fmul_rn(a.z, b.y)), __fsub_rn(__fmul_rn(a.z, b.x), __fmul_rn(a.x, b.z)),
+             __fsub_rn(__fmul_rn(a.x, b.y), __fmul_rn(a.y, b.x)));
+}
+
+// texture(TexTransferFunc, texture(TexVolume, tx / VolumeGridSize).r), both GL_LINEAR with float32 weights
+__device__ __forceinline__ float4 gt_classify(const GtArgs& a, f3 tx) {
+  const f3 p = div3(tx, mk3(a.sizes[0], a.sizes[1], a.sizes[2]));
+  const float density = tex3d_f32_exact(a.quad, p, mk3(a.res[0], a.res[1], a.res[2]));
+  const float u = fminf(fmaxf(fmaf(density, (float)a.tf_n, -0.5f), 0.0f), (float)(a.tf_n - 1));
+  const int j = (int)u;
+  const float w = u - (float)j;
+  const uint2 e0 = __ldg(a.tf_lin + j), e1 = __ldg(a.tf_lin + min(j + 1, a.tf_n - 1));
+  const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e0.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&e0.y));
+  const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e1.x)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&e1.y));
+  return make_float4(fmaf(w, r1.x - r0.x, r0.x), fmaf(w, r1.y - r0.y, r0.y), fmaf(w, b1.x - b0.x, b0.x), fmaf(w, b1.y - b0.y, b0.y));
+}
+
+// the loop both cone functions share (gt_ray_marching.comp:124-157, :206-239): transparency along one secondary ray
+__device__ float gt_ray_transparency(const GtArgs& a, f3 tx_pos, f3 dir, float dist) {
+  float Vt = 1.0f;
+  float s = a.gap;
+  float st0 = gt_classify(a, add3(tx_pos, scale3(dir, s))).w;
+  while (s < dist) {
+    const float h = gmin(a.lstep, __fsub_rn(dist, s));
+    const f3 at = add3(tx_pos, scale3(dir, __fadd_rn(s, h)));
+    if (at.x < 0.0f || at.x > a.sizes[0] || at.y < 0.0f || at.y > a.sizes[1] || at.z < 0.0f || at.z > a.sizes[2]) break;
+    const float st1 = gt_classify(a, at).w;
+    Vt = __fmul_rn(Vt, expf(__fmul_rn(-__fmul_rn(__fadd_rn(st0, st1), 0.5f), h)));
+    if (__fsub_rn(1.0f, Vt) > 0.99f) break;
+    st0 = st1;
+    s = __fadd_rn(s, h);
+  }
+  return Vt;
+}
+
+__device__ float gt_cone(const GtArgs& a, const float* kernel, int n, f3 tx_pos, f3 v_right, f3 v_up, f3 v_dir, float dist) {
+  float S = 0.0f, W = 0.0f;
+  for (int rayid = 0; rayid < n; rayid++) {
+    const float kx = __ldg(kernel + 3 * rayid), ky = __ldg(kernel + 3 * rayid + 1), kz = __ldg(kernel + 3 * rayid + 2);
+    const f3 ray = normalize_rn(add3(add3(scale3(v_right, kx), scale3(v_up, ky)), scale3(v_dir, kz)));
+    const float Vt = gt_ray_transparency(a, tx_pos, ray, dist);
+    const float wgt = dot_rn(v_dir, ray);
+    S = __fadd_rn(S, __fmul_rn(Vt, wgt));
+    W = __fadd_rn(W, wgt);
+  }
+  return __fdiv_rn(S, W);
+}
+
+// ShadeSample (gt_ray_marching.comp:254-368)
+__device__ __noinline__ f3 gt_shade_sample(const GtArgs& a, float4 clr, f3 Tpos, f3 camera_dir, f3 v_up, f3 v_right) {
+  float ka = 0.0f, kd = 0.0f, Iocc = 0.0f, Isdw = 0.0f;
+  const f3 sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]);
+  if (a.apply_occlusion) {
+    ka = a.ka;
+    Iocc = gt_cone(a, a.occ, a.n_occ, Tpos, v_right, v_up, normalize_rn(mk3(-camera_dir.x, -camera_dir.y, -camera_dir.z)), a.occ_dist);
+  }
+  if (a.apply_shadow) {
+    kd = a.kd;
+    const f3 Wpos = sub3(Tpos, scale3(sizes, 0.5f));
+    const f3 fwd = mk3(a.fwd[0], a.fwd[1], a.fwd[2]), up = mk3(a.up[0], a.up[1], a.up[2]), right = mk3(a.right[0], a.right[1], a.right[2]);
+    f3 d, u, r;
+    bool dark = false;
+    if (a.shadow_type == 0 || a.shadow_type == 1) {
+      d = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), Wpos));
+      u = normalize_rn(cross_rn(d, right));
+      r = normalize_rn(cross_rn(d, u));
+      dark = a.shadow_type == 1 && dot_rn(d, fwd) < 30.0f;                         // :188
+    } else { d = fwd; u = up; r = right; }
+    Isdw = dark ? 0.0f : gt_cone(a, a.sdw, a.n_sdw, Tpos, r, u, d, a.sdw_dist);
+  }
+  float4 L = clr;
+  if (!phong_shade_sample(0, a.phong, Tpos, sizes, mk3(a.res[0], a.res[1], a.res[2]), mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]),
+                          mk3(a.eye[0], a.eye[1], a.eye[2]), ka, kd, a.apply_shadow != 0, Iocc, Isdw, L)) {
+    const float k = __fdiv_rn(1.0f, __fadd_rn(ka, kd));                            // :364
+    L.x = __fmul_rn(k, __fadd_rn(__fmul_rn(__fmul_rn(clr.x, Iocc), ka), __fmul_rn(__fmul_rn(clr.x, Isdw), kd)));
+    L.y = __fmul_rn(k, __fadd_rn(__fmul_rn(__fmul_rn(clr.y, Iocc), ka), __fmul_rn(__fmul_rn(clr.y, Isdw), kd)));
+    L.z = __fmul_rn(k, __fadd_rn(__fmul_rn(__fmul_rn(clr.z, Iocc), ka), __fmul_rn(__fmul_rn(clr.z, Isdw), kd)));
+  }
+  return mk3(L.x, L.y, L.z);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(32) crtgt_kernel(const __grid_constant__ GtArgs a) {
+  const int lane = threadIdx.x;
+  const int px = blockIdx.x * 8 + (lane & 7), py = blockIdx.y * 4 + (lane >> 3);
+  unsigned n = 0;
+  bool pending = false;
+  if (px < a.width && py < a.height) {
+    const size_t o = (size_t)py * a.width + px;
+    float2 st = __half22float2(a.state[o]);
+    if (st.y < 0.5f) {
+      const f3 sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]), half = scale3(sizes, 0.5f);
+      const f3 eye = mk3(a.eye[0], a.eye[1], a.eye[2]);
+      const f3 cdir = camera_ray_dir(px, py, a.width, a.height, a.tan_fovy, a.aspect, a.lookat);
+      f3 dir; float tnear, tfar;
+      if (!ray_aabb(eye, cdir, mk3(-half.x, -half.y, -half.z), half, dir, tnear, tfar)) {
+        a.state[o] = __floats2half2_rn(0.0f, 1.0f);                                // :477
+      } else {
+        const f3 v_right = normalize_rn(cross_rn(cdir, mk3(0.f, 1.f, 0.f)));
+        const f3 v_up = normalize_rn(cross_rn(mk3(-cdir.x, -cdir.y, -cdir.z), v_right));
+        const float D = __fsub_rn(tfar, tnear);
+        const f3 tex_pos = add3(add3(eye, scale3(dir, tnear)), half);
+        float4 color = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (st.x > 0.0f) {
+          const uint2 t = a.frame[o];
+          const float2 c0 = __half22float2(*reinterpret_cast<const __half2*>(&t.x)), c1 = __half22float2(*reinterpret_cast<const __half2*>(&t.y));
+          color = make_float4(c0.x, c0.y, c1.x, c1.y);
+        }
+        // `samples` dispatches of main(): one primary sample each, state and colour through half in between
+        for (int k = 0; k < a.samples && st.y < 0.5f; k++) {
+          if (!(st.x > 0.0f)) color = make_float4(0.f, 0.f, 0.f, 0.f);               // :399-401: the stored colour counts only past s = 0
+          float s = st.x;
+          if (s < D) {
+            const float h = gmin(a.step, __fsub_rn(D, s));
+            const f3 tx = add3(tex_pos, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));
+            float4 src = gt_classify(a, tx);
+            if (COUNT) n++;
+            bool done = false;
+            if (src.w > 0.0f) {
+              const f3 rgb = gt_shade_sample(a, src, tx, cdir, v_up, v_right);
+              src.w = __fsub_rn(1.0f, expf(-__fmul_rn(src.w, h)));
+              const float wgt = __fsub_rn(1.0f, color.w);
+              color.x = __fadd_rn(color.x, __fmul_rn(wgt, __fmul_rn(rgb.x, src.w)));
+              color.y = __fadd_rn(color.y, __fmul_rn(wgt, __fmul_rn(rgb.y, src.w)));
+              color.z = __fadd_rn(color.z, __fmul_rn(wgt, __fmul_rn(rgb.z, src.w)));
+              color.w = __fadd_rn(color.w, __fmul_rn(wgt, src.w));
+              if (color.w > 0.99f) { st = make_float2(round_half(s), 1.0f); done = true; }      // :448-452
+            }
+            if (!done) {
+              s = __fadd_rn(s, h);
+              st = make_float2(round_half(s), (s < D) ? 0.0f : 1.0f);                          // :457-468
+            }
+          }
+          // a dispatch whose loop does not run (s >= D with the flag still clear) stores the colour and leaves the state
+          color = make_float4(round_half(color.x), round_half(color.y), round_half(color.z), round_half(color.w));
+          if (!(s < D) && st.y < 0.5f) break;
+        }
+        a.frame[o] = make_uint2(pack_half2(color.x, color.y), pack_half2(color.z, color.w));
+        a.state[o] = __floats2half2_rn(st.x, st.y);
+        pending = st.y < 0.5f;
+      }
+    }
+  }
+  const unsigned left = __popc(__ballot_sync(0xffffffffu, pending));
+  if (lane == 0 && left) atomicAdd(a.unfinished, left);
+  if (COUNT) {
+    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    if (lane == 0 && n) atomicAdd(a.count, (unsigned long long)n);
+  }
+}
+
+// vol_intersection.comp main() (:60-108)
+__global__ void __launch_bounds__(256) crtgt_cube_kernel(const __grid_constant__ GtArgs a) {
+  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (px >= a.width || py >= a.height) return;
+  const f3 half = scale3(mk3(a.sizes[0], a.sizes[1], a.sizes[2]), 0.5f);
+  const f3 eye = mk3(a.eye[0], a.eye[1], a.eye[2]);
+  const f3 cdir = camera_ray_dir(px, py, a.width, a.height, a.tan_fovy, a.aspect, a.lookat);
+  f3 dir; float tnear, tfar;
+  if (!ray_aabb(eye, cdir, mk3(-half.x, -half.y, -half.z), half, dir, tnear, tfar)) return;
+  const f3 wld = add3(eye, scale3(dir, tnear));
+  const f3 cp = div3(mk3(fabsf(wld.x), fabsf(wld.y), fabsf(wld.z)), half);
+  float r = 0.f, g = 0.f, b = 0.f, al = 0.f;
+  if (cp.z >= cp.x && cp.z >= cp.y) { b = 1.f; al = 1.f; }
+  else if (cp.y >= cp.x && cp.y >= cp.z) { g = 1.f; al = 1.f; }
+  else if (cp.x >= cp.y && cp.x >= cp.z) { r = 1.f; al = 1.f; }
+  a.frame[(size_t)py * a.width + px] = make_uint2(pack_half2(r, g), pack_half2(b, al));
+}
+
+class CrtgtRenderer : public RendererImpl {
+ public:
+  explicit CrtgtRenderer(vrb_ctx* c) : RendererImpl(c, VRB_CRT_GT) {
+    // RC1PConeLightGroundTruthSteps ctor (crtgtrenderer.cpp:23-52)
+    prm_.step_size = 0.5f; prm_.light_ray_initial_step = 1.0f; prm_.light_ray_step_size = 0.5f;
+    prm_.apply_occlusion = 0; prm_.occ_cone_aperture_angle = 90.0f; prm_.occ_cone_distance_eval = 100.0f;
+    prm_.apply_shadows = 0; prm_.sdw_cone_aperture_angle = 1.0f; prm_.sdw_cone_distance_eval = 100.0f;
+    prm_.shadow_type = 0; prm_.apply_gradient_shading = 0; prm_.show_frame_texture = 0; prm_.samples_per_redraw = 1;
+    prm_.light_cam_forward[0] = 0.f; prm_.light_cam_forward[1] = 0.f; prm_.light_cam_forward[2] = -1.f;
+    prm_.light_cam_up[0] = 0.f; prm_.light_cam_up[1] = 1.f; prm_.light_cam_up[2] = 0.f;
+    prm_.light_cam_right[0] = 1.f; prm_.light_cam_right[1] = 0.f; prm_.light_cam_right[2] = 0.f;
+    prm_.count_samples = 0;
+  }
+
+  int init(int w, int h) override {
+    VRB_REQUIRE(ctx->vol.tex != 0, VRB_ERR_NO_VOLUME, "RC1PConeLightGroundTruthSteps::Init: no volume texture");
+    VRB_REQUIRE(ctx->tf.lin_rgbt != nullptr, VRB_ERR_INVALID, "RC1PConeLightGroundTruthSteps::Init: no transfer function");
+    int rc = ensure_quad(ctx);
+    if (rc != VRB_OK) return rc;
+    rc = alloc_frame(w, h);
+    if (rc != VRB_OK) return rc;
+    rc = alloc_state();
+    if (rc != VRB_OK) return rc;
+    const Volume& v = ctx->vol;
+    // crtgtrenderer.cpp:106-113: step from the voxel scale, evaluation distances from the diagonal
+    prm_.step_size = (float)((0.5 / std::sqrt(3.0)) * std::sqrt((double)v.sx * v.sx + (double)v.sy * v.sy + (double)v.sz * v.sz));
+    const double dw = (double)v.w * v.sx, dh = (double)v.h * v.sy, dd = (double)v.d * v.sz;
+    const double diag = std::sqrt(dw * dw + dh * dh + dd * dd);
+    prm_.occ_cone_distance_eval = (float)(diag * 0.50f);
+    prm_.sdw_cone_distance_eval = (float)(diag * 0.75f);
+    if (!d_occ_) { const float axis[3] = {0.f, 0.f, 1.f}; rc = set_kernels(axis, 1, axis, 1); if (rc != VRB_OK) return rc; }
+    if (!d_unfinished_) { VRB_CUDA(cudaMalloc(&d_unfinished_, sizeof(unsigned))); VRB_CUDA(cudaMemset(d_unfinished_, 0, sizeof(unsigned))); }
+    fresh_ = true;
+    built = true;
+    return VRB_OK;
+  }
+  void clean() override {
+    if (d_state_) cudaFree(d_state_);
+    if (d_occ_) cudaFree(d_occ_);
+    if (d_sdw_) cudaFree(d_sdw_);
+    if (d_unfinished_) cudaFree(d_unfinished_);
+    d_state_ = nullptr; d_occ_ = d_sdw_ = nullptr; d_unfinished_ = nullptr; state_px_ = 0;
+  }
+
+  int set_params(const void* pod, size_t size) override {
+    VRB_REQUIRE(pod && size == sizeof(vrb_crtgt_params), VRB_ERR_INVALID, "crtgt set_params: size %zu != sizeof(vrb_crtgt_params) %zu", size, sizeof(vrb_crtgt_params));
+    const vrb_crtgt_params p = *(const vrb_crtgt_params*)pod;
+    VRB_REQUIRE(p.step_size > 0.0f && p.light_ray_step_size > 0.0f && p.light_ray_initial_step >= 0.0f, VRB_ERR_INVALID, "crtgt set_params: steps must be positive");
+    VRB_REQUIRE(p.shadow_type >= 0 && p.shadow_type <= 2 && p.samples_per_redraw >= 1, VRB_ERR_INVALID, "crtgt set_params: shadow_type %d samples_per_redraw %d", p.shadow_type, p.samples_per_redraw);
+    prm_ = p;
+    return VRB_OK;
+  }
+  int get_params(void* pod, size_t size) override {
+    VRB_REQUIRE(pod && size == sizeof(vrb_crtgt_params), VRB_ERR_INVALID, "crtgt get_params: bad size");
+    *(vrb_crtgt_params*)pod = prm_;
+    return VRB_OK;
+  }
+
+  // crtgtrenderer.cpp:125-179: the two RGB16F kernel textures (values rounded to half here, as SetData(GL_RGB16F) does)
+  int set_kernels(const float* occ, int n_occ, const float* sdw, int n_sdw) {
+    VRB_REQUIRE(occ && sdw && n_occ >= 1 && n_sdw >= 1 && n_occ <= 65536 && n_sdw <= 65536, VRB_ERR_INVALID, "vrb_crtgt_set_kernels: %d / %d rays", n_occ, n_sdw);
+    VRB_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (d_occ_) cudaFree(d_occ_);
+    if (d_sdw_) cudaFree(d_sdw_);
+    d_occ_ = d_sdw_ = nullptr;
+    std::vector<float> o((size_t)n_occ * 3), s((size_t)n_sdw * 3);
+    for (size_t i = 0; i < o.size(); i++) o[i] = __half2float(__float2half_rn(occ[i]));
+    for (size_t i = 0; i < s.size(); i++) s[i] = __half2float(__float2half_rn(sdw[i]));
+    VRB_CUDA(cudaMalloc(&d_occ_, o.size() * sizeof(float)));
+    VRB_CUDA(cudaMalloc(&d_sdw_, s.size() * sizeof(float)));
+    VRB_CUDA(cudaMemcpy(d_occ_, o.data(), o.size() * sizeof(float), cudaMemcpyHostToDevice));
+    VRB_CUDA(cudaMemcpy(d_sdw_, s.data(), s.size() * sizeof(float), cudaMemcpyHostToDevice));
+    n_occ_ = n_occ; n_sdw_ = n_sdw;
+    return VRB_OK;
+  }
+
+  int read_state(float* host_rg, long long* unfinished) {
+    VRB_REQUIRE(built && d_state_, VRB_ERR_INVALID, "vrb_crtgt_read_state before Init");
+    VRB_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (host_rg) {
+      std::vector<__half2> tmp(state_px_);
+      VRB_CUDA(cudaMemcpy(tmp.data(), d_state_, state_px_ * sizeof(__half2), cudaMemcpyDeviceToHost));
+      for (size_t i = 0; i < state_px_; i++) { const float2 f = __half22float2(tmp[i]); host_rg[2 * i] = f.x; host_rg[2 * i + 1] = f.y; }
+    }
+    if (unfinished) {
+      unsigned u = 0;
+      VRB_CUDA(cudaMemcpy(&u, d_unfinished_, sizeof(u), cudaMemcpyDeviceToHost));
+      *unfinished = fresh_ ? (long long)state_px_ : (long long)u;
+    }
+    return VRB_OK;
+  }
+
+  int redraw(int /*mode*/) override {
+    VRB_REQUIRE(built && have_cam, VRB_ERR_INVALID, "RC1PConeLightGroundTruthSteps::Redraw before Init/Update");
+    VRB_REQUIRE(n_ranks == 1 && gather_mode == VRB_GATHER_NONE && brick_ranks == 0, VRB_ERR_UNSUPPORTED,
+                "RC1PConeLightGroundTruthSteps: one GPU per frame (the per-pixel state is not partitioned)");
+    int rc = ensure_quad(ctx);
+    if (rc != VRB_OK) return rc;
+    if ((size_t)width * height != state_px_) { rc = alloc_state(); if (rc != VRB_OK) return rc; }
+    const Volume& v = ctx->vol;
+    cudaStream_t s = ctx->stream;
+    GtArgs a{};
+    a.quad = v.tex_quad; a.tf_lin = (const uint2*)ctx->tf.lin_rgbt; a.tf_n = ctx->tf.n;
+    a.width = width; a.height = height;
+    a.res[0] = (float)v.w; a.res[1] = (float)v.h; a.res[2] = (float)v.d;
+    a.sizes[0] = (float)v.w * v.sx; a.sizes[1] = (float)v.h * v.sy; a.sizes[2] = (float)v.d * v.sz;
+    for (int i = 0; i < 3; i++) { a.eye[i] = cam.eye[i]; a.light_pos[i] = light.position[i]; a.fwd[i] = prm_.light_cam_forward[i]; a.up[i] = prm_.light_cam_up[i]; a.right[i] = prm_.light_cam_right[i]; }
+    for (int i = 0; i < 9; i++) a.lookat[i] = cam.lookat[i];
+    a.tan_fovy = cam.tan_fovy; a.aspect = cam.aspect;
+    a.frame = (uint2*)frame; a.state = d_state_;
+    if (!prm_.show_frame_texture) {
+      // PreRedraw (:262-271) + RedrawCube (:327-338): the frame generation starts over, the box is shown
+      VRB_CUDA(cudaMemsetAsync(frame, 0, frame_bytes, s));
+      VRB_CUDA(cudaMemsetAsync(d_state_, 0, state_px_ * sizeof(__half2), s));
+      fresh_ = true;
+      crtgt_cube_kernel<<<dim3((width + 31) / 32, (height + 7) / 8), 256, 0, s>>>(a);
+      VRB_CUDA(cudaGetLastError());
+      return VRB_OK;
+    }
+    a.step = prm_.step_size; a.gap = prm_.light_ray_initial_step; a.lstep = prm_.light_ray_step_size;
+    a.apply_occlusion = prm_.apply_occlusion; a.n_occ = n_occ_; a.occ_dist = prm_.occ_cone_distance_eval; a.occ = d_occ_;
+    a.apply_shadow = prm_.apply_shadows; a.n_sdw = n_sdw_; a.sdw_dist = prm_.sdw_cone_distance_eval; a.sdw = d_sdw_;
+    a.shadow_type = prm_.shadow_type; a.ka = light.ka; a.kd = light.kd;
+    a.phong.grad_pt = 0;
+    if (prm_.apply_gradient_shading) {
+      VRB_REQUIRE(v.tex_grad && v.grad_gen == v.generation, VRB_ERR_INVALID, "RC1PConeLightGroundTruthSteps: gradient shading needs vrb_volume_gradient() for the current volume");
+      a.phong.grad_pt = v.tex_grad_pt; a.phong.ks = light.ks; a.phong.shininess = light.shininess;
+      a.phong.ispec[0] = a.phong.ispec[1] = a.phong.ispec[2] = 1.0f;                 // `vec3(1) * (IShadow * ks * pow(...))` (:358)
+    }
+    a.samples = prm_.samples_per_redraw;
+    a.count = d_samples; a.unfinished = d_unfinished_;
+    if (fresh_) {   // the first dispatch after a PreRedraw reads a cleared frame (the box drawn meanwhile is not part of it)
+      VRB_CUDA(cudaMemsetAsync(frame, 0, frame_bytes, s));
+      fresh_ = false;
+    }
+    VRB_CUDA(cudaMemsetAsync(d_unfinished_, 0, sizeof(unsigned), s));
+    if (prm_.count_samples) VRB_CUDA(cudaMemsetAsync(d_samples, 0, sizeof(unsigned long long), s));
+    const dim3 grid((width + 7) / 8, (height + 3) / 4);
+    if (prm_.count_samples) crtgt_kernel<true><<<grid, 32, 0, s>>>(a); else crtgt_kernel<false><<<grid, 32, 0, s>>>(a);
+    VRB_CUDA(cudaGetLastError());
+    return VRB_OK;
+  }
+
+ private:
+  int alloc_state() {
+    if (d_state_) cudaFree(d_state_);
+    d_state_ = nullptr;
+    state_px_ = (size_t)width * height;
+    VRB_CUDA(cudaMalloc(&d_state_, state_px_ * sizeof(__half2)));
+    VRB_CUDA(cudaMemsetAsync(d_state_, 0, state_px_ * sizeof(__half2), ctx->stream));
+    fresh_ = true;
+    return VRB_OK;
+  }
+  vrb_crtgt_params prm_{};
+  __half2* d_state_ = nullptr; size_t state_px_ = 0;
+  float* d_occ_ = nullptr; float* d_sdw_ = nullptr; int n_occ_ = 0, n_sdw_ = 0;
+  unsigned* d_unfinished_ = nullptr;
+  bool fresh_ = true;
+};
+
+RendererImpl* make_crtgt(vrb_ctx* ctx) { return new CrtgtRenderer(ctx); }
+
+int crtgt_set_kernels(RendererImpl* impl, const float* occ, int n_occ, const float* sdw, int n_sdw) {
+  VRB_REQUIRE(impl->kind == VRB_CRT_GT, VRB_ERR_INVALID, "vrb_crtgt_set_kernels: not a ground-truth renderer");
+  return static_cast<CrtgtRenderer*>(impl)->set_kernels(occ, n_occ, sdw, n_sdw);
+}
+int crtgt_read_state(RendererImpl* impl, float* host_rg, long long* unfinished) {
+  VRB_REQUIRE(impl->kind == VRB_CRT_GT, VRB_ERR_INVALID, "vrb_crtgt_read_state: not a ground-truth renderer");
+  return static_cast<CrtgtRenderer*>(impl)->read_state(host_rg, unfinished);
+}
+
+}  // namespace vrb

@@ -217,6 +217,9 @@ int ebs_read_sat(RendererImpl* impl, float* host, int dims[3], float* build_ms);
 RendererImpl* make_vct(vrb_ctx* ctx);
 RendererImpl* make_sbtm(vrb_ctx* ctx);
 RendererImpl* make_dos(vrb_ctx* ctx);
+RendererImpl* make_crtgt(vrb_ctx* ctx);
+int crtgt_set_kernels(RendererImpl* impl, const float* occ, int n_occ, const float* sdw, int n_sdw);
+int crtgt_read_state(RendererImpl* impl, float* host_rg, long long* unfinished);
 int dos_read_extcoef(RendererImpl* impl, int level, float* host, int dims[3], int* n_levels, float* build_ms);
 int dos_read_sections(RendererImpl* impl, int which, float* rgba, int cap, int* n, float axes30[30], int counts[3], float* adj7);
 int sbtm_read_occlusion(RendererImpl* impl, float* host, int* n_slices);

@@ -155,6 +155,7 @@ int vrb_renderer_create(vrb_ctx* ctx, int kind, vrb_renderer** out) {
     case VRB_VCT: impl = make_vct(ctx); break;
     case VRB_DOS_CONE: impl = make_dos(ctx); break;
     case VRB_SBTM_DOS: impl = make_sbtm(ctx); break;
+    case VRB_CRT_GT: impl = make_crtgt(ctx); break;
     default:
       set_error("vrb_renderer_create: renderer kind %d is not built yet", kind);
       return VRB_ERR_UNSUPPORTED;
@@ -227,7 +228,7 @@ int vrb_renderer_set_multiscaling(vrb_renderer* r, int mode, int kernel) {
   RendererImpl* p = r->impl;
   VRB_REQUIRE(mode >= 0 && mode <= 3 && kernel >= 0 && kernel <= 5, VRB_ERR_INVALID, "vrb_renderer_set_multiscaling: mode %d kernel %d", mode, kernel);
   // vr_pixel_multiscaling_support: rc1prenderer.cpp:25, ebsrenderer.cpp:51, vctrenderer.cpp:52, dosrcrenderer.cpp:68, sbtmdosrenderer.cpp:46
-  VRB_REQUIRE(mode == 0 || p->kind == VRB_RC1PASS || p->kind == VRB_EBS_SAT || p->kind == VRB_VCT || p->kind == VRB_DOS_CONE || p->kind == VRB_SBTM_DOS,
+  VRB_REQUIRE(mode == 0 || p->kind == VRB_RC1PASS || p->kind == VRB_EBS_SAT || p->kind == VRB_VCT || p->kind == VRB_DOS_CONE || p->kind == VRB_SBTM_DOS || p->kind == VRB_CRT_GT,
               VRB_ERR_UNSUPPORTED, "vrb_renderer_set_multiscaling: renderer kind %d has no pixel multiscaling", p->kind);
   VRB_REQUIRE(mode == 0 || (p->gather_mode == VRB_GATHER_NONE && p->brick_ranks == 0 && p->n_ranks == 1), VRB_ERR_UNSUPPORTED,
               "vrb_renderer_set_multiscaling: not with an image partition, peers or bricks (filter the gathered frame on one rank)");
@@ -519,6 +520,15 @@ int vrb_light_cache_read(vrb_renderer* r, float* host_rg, int dims[3], float* bu
 int vrb_dos_read_sections(vrb_renderer* r, int which, float* rgba, int cap, int* n, float axes30[30], int counts[3], float* adj7) {
   VRB_REQUIRE(r && (which == 0 || which == 1), VRB_ERR_INVALID, "vrb_dos_read_sections: bad argument");
   return dos_read_sections(r->impl, which, rgba, cap, n, axes30, counts, adj7);
+}
+
+int vrb_crtgt_set_kernels(vrb_renderer* r, const float* occ_xyz, int n_occ, const float* sdw_xyz, int n_sdw) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_crtgt_set_kernels: null renderer");
+  return crtgt_set_kernels(r->impl, occ_xyz, n_occ, sdw_xyz, n_sdw);
+}
+int vrb_crtgt_read_state(vrb_renderer* r, float* host_rg, long long* unfinished) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_crtgt_read_state: null renderer");
+  return crtgt_read_state(r->impl, host_rg, unfinished);
 }
 
 int vrb_iso_read_gbuffers(vrb_renderer* r, float* host_position, float* host_normal) {

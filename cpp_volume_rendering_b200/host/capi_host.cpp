@@ -3,6 +3,7 @@
 #include "volrenderbase.h"
 
 #include <cstring>
+#include <algorithm>
 
 extern "C" {
 
@@ -84,8 +85,9 @@ static void register_all(RenderingManager* m) {
   m->AddVolumeRenderer(new CudaSBTMDirectionalOcclusionShading());      // 7
   m->AddVolumeRenderer(new CudaRayCasting1PassIso(VRB_ISO_FORWARD));    // 8  (main.cpp:75)
   m->AddVolumeRenderer(new CudaRayCasting1PassIso(VRB_ISO_DEFERRED));   // 9  (main.cpp:73)
+  m->AddVolumeRenderer(new CudaRC1PConeLightGroundTruthSteps());        // 10 (main.cpp:67)
 }
-int vrbh_num_renderers(void) { return 10; }
+int vrbh_num_renderers(void) { return 11; }
 
 // Test hook: what the ImGui "light cache" checkbox / resolution fields (PreIlluminationStructuredVolume::SetImGuiComponents,
 // preillumination.cpp:82-116) would set on the next session's DOS / EBS / VCT renderer.  active < 0 leaves the constructor's state.
@@ -112,6 +114,22 @@ static void apply_multiscaling(BaseVolumeRenderer* r) {
   r->SetCurrentMultiScalingMode(g_ms_mode);
 }
 
+// Test hook: the ground-truth renderer's panel for the next session (crtgtrenderer.cpp SetImGuiComponents): cones on, rays per
+// cone, and "generate frame" (m_show_frame_texture) with `fold` samples per Redraw.  rays < 0 leaves the constructor's state.
+static int g_gt_rays = -1, g_gt_fold = 1;
+void vrbh_session_ground_truth(int rays, int fold) { g_gt_rays = rays; g_gt_fold = fold; }
+static void apply_ground_truth(BaseVolumeRenderer* r) {
+  auto* g = dynamic_cast<CudaRC1PConeLightGroundTruthSteps*>(r);
+  if (!g || g_gt_rays < 0) return;
+  g->m_apply_occlusion = g->m_apply_shadows = g_gt_rays > 0;
+  g->m_occ_num_rays_sampled = g->m_sdw_num_rays_sampled = std::max(g_gt_rays, 1);
+  g->m_sdw_cone_aperture_angle = 10.0f;
+  g->m_samples_per_redraw = g_gt_fold;
+  g->m_light_parameters_outdated = true;
+  g->m_show_frame_texture = true;
+  g->SetOutdated();
+}
+
 // One headless session: read the dataset + TF from disk, register the plugins, select `renderer`, optionally run
 // the evaluation sweep (eval_dir != NULL; `numframes` frames per sample, CSV in the reference's schema), else
 // render `numframes` frames.  The last frame is returned as RGBA32F (w*h*4 floats, row 0 = bottom) and RGB8.
@@ -133,6 +151,7 @@ int vrbh_run_session(const char* volume_path, const char* tf_path, int renderer,
     if (!m->SetCurrentVolumeRenderer(renderer)) { fail("SetCurrentVolumeRenderer: " + m->LastError()); break; }
     apply_light_cache(m->CurrentRenderer());
     apply_multiscaling(m->CurrentRenderer());
+    apply_ground_truth(m->CurrentRenderer());
     if (out_name && name_cap > 0) { std::strncpy(out_name, m->CurrentRenderer()->GetName(), name_cap - 1); out_name[name_cap - 1] = 0; }
     bool ok = true;
     if (eval_dir) {

@@ -4,6 +4,9 @@
 
 #include <sys/stat.h>
 #include <algorithm>
+#include <cmath>
+#include <random>
+#include <vector>
 
 // ---- BaseVolumeRenderer (cppvolrend/volrenderbase.cpp:5-119) -------------------------------------------------
 BaseVolumeRenderer::BaseVolumeRenderer() {}
@@ -354,6 +357,94 @@ bool CudaSBTMDirectionalOcclusionShading::Update(vis::Camera* camera) {
   p.grid_size[0] = grid_size[0]; p.grid_size[1] = grid_size[1]; p.max_number_of_passes = max_number_of_passes;
   if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
   return PushCameraAndLight(camera);
+}
+
+// ---- cone ray-traced ground truth ------------------------------------------------------------------------------
+CudaRC1PConeLightGroundTruthSteps::CudaRC1PConeLightGroundTruthSteps()        // crtgtrenderer.cpp:23-56
+    : m_show_frame_texture(false), m_apply_gradient(false), m_apply_occlusion(false), m_apply_shadows(false), m_light_parameters_outdated(true),
+      m_u_step_size(0.5f), m_u_light_ray_initial_step(1.0f), m_u_light_ray_step_size(0.5f), m_occ_num_rays_sampled(1), m_sdw_num_rays_sampled(1),
+      m_shadow_type(0), m_occ_cone_aperture_angle(90.0f), m_occ_cone_distance_eval(100.0f), m_sdw_cone_aperture_angle(1.0f),
+      m_sdw_cone_distance_eval(100.0f), m_samples_per_redraw(1), m_frame_outdated(true) {}
+
+bool CudaRC1PConeLightGroundTruthSteps::Init(int w, int h) {
+  if (IsBuilt()) Clean();
+  if (!CreateDeviceRenderer(VRB_CRT_GT, w, h)) return false;
+  vrb_crtgt_params p;
+  if (VrbApi::Get()->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  m_u_step_size = p.step_size;                                                // estimated at Init (:106-113)
+  m_occ_cone_distance_eval = p.occ_cone_distance_eval; m_sdw_cone_distance_eval = p.sdw_cone_distance_eval;
+  m_light_parameters_outdated = true; m_frame_outdated = true;
+  SetBuilt(true);
+  SetOutdated();
+  return true;
+}
+
+// math_utils RodriguesRotation, float overload (libs/math_utils/utils.cpp:149-156)
+static void rodrigues(const float v[3], float teta, const float k[3], float out[3]) {
+  const float c = std::cos(teta), s = std::sin(teta);
+  const float kxv[3] = {k[1] * v[2] - k[2] * v[1], k[2] * v[0] - k[0] * v[2], k[0] * v[1] - k[1] * v[0]};
+  const float kv = k[0] * v[0] + k[1] * v[1] + k[2] * v[2];
+  float r[3];
+  for (int i = 0; i < 3; i++) r[i] = v[i] * c + kxv[i] * s + k[i] * kv * (1.0f - c);
+  const float len = std::sqrt(r[0] * r[0] + r[1] * r[1] + r[2] * r[2]);
+  for (int i = 0; i < 3; i++) out[i] = r[i] / len;
+}
+
+bool CudaRC1PConeLightGroundTruthSteps::Update(vis::Camera* camera) {
+  if (!m_dev || !camera) return false;
+  const VrbApi* a = VrbApi::Get();
+  if (m_light_parameters_outdated) {
+    // crtgtrenderer.cpp:125-179: uniform samples of the two cones.  std::default_random_engine is implementation-defined (libstdc++:
+    // minstd_rand0; the reference's MSVC build: mt19937), so the vectors differ from a Windows run's while their distribution does not.
+    std::default_random_engine generator;
+    std::uniform_real_distribution<float> distribution(0.0, 1.0);
+    const float gtray[3] = {0.f, 0.f, 1.f}, yaxis[3] = {0.f, 1.f, 0.f};
+    const float pi = 3.14159265358979323846f;
+    auto sample = [&](int n, float aperture, std::vector<float>& out) {
+      out.resize((size_t)std::max(n, 1) * 3);
+      for (int i = 0; i < std::max(n, 1); i++) {
+        const float theta = distribution(generator) * (pi * (aperture / 180.f));
+        const float phi = distribution(generator) * (pi * (360.f / 180.f));
+        float t[3], r[3];
+        rodrigues(gtray, theta, yaxis, t);
+        rodrigues(t, phi, gtray, r);
+        out[3 * i] = r[0]; out[3 * i + 1] = r[1]; out[3 * i + 2] = r[2];
+      }
+    };
+    std::vector<float> occ, sdw;
+    sample(m_occ_num_rays_sampled, m_occ_cone_aperture_angle, occ);
+    sample(m_sdw_num_rays_sampled, m_sdw_cone_aperture_angle, sdw);
+    if (a->crtgt_set_kernels(m_dev, occ.data(), (int)occ.size() / 3, sdw.data(), (int)sdw.size() / 3) != VRB_OK) return Fail("vrb_crtgt_set_kernels");
+    m_light_parameters_outdated = false;
+  }
+  vrb_crtgt_params p;
+  if (a->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_get_params");
+  p.step_size = m_u_step_size; p.light_ray_initial_step = m_u_light_ray_initial_step; p.light_ray_step_size = m_u_light_ray_step_size;
+  p.apply_occlusion = m_apply_occlusion ? 1 : 0; p.occ_cone_aperture_angle = m_occ_cone_aperture_angle; p.occ_cone_distance_eval = m_occ_cone_distance_eval;
+  p.apply_shadows = m_apply_shadows ? 1 : 0; p.sdw_cone_aperture_angle = m_sdw_cone_aperture_angle; p.sdw_cone_distance_eval = m_sdw_cone_distance_eval;
+  p.shadow_type = m_shadow_type;
+  p.apply_gradient_shading = (m_apply_gradient && m_ext_data_manager->HasGradientTexture()) ? 1 : 0;     // :211-212
+  p.show_frame_texture = m_show_frame_texture ? 1 : 0; p.samples_per_redraw = std::max(m_samples_per_redraw, 1);
+  if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
+  return PushCameraAndLight(camera);
+}
+
+// Redraw (:340-350): PreRedraw + RedrawFrameTexture / RedrawCube.  m_show_frame_texture is a member the panel flips between
+// Updates, so it is pushed with every Redraw.
+void CudaRC1PConeLightGroundTruthSteps::Redraw() {
+  if (!m_dev) return;
+  const VrbApi* a = VrbApi::Get();
+  vrb_crtgt_params p;
+  if (a->renderer_get_params(m_dev, &p, sizeof(p)) != VRB_OK) { Fail("vrb_renderer_get_params"); return; }
+  p.show_frame_texture = m_show_frame_texture ? 1 : 0;
+  if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) { Fail("vrb_renderer_set_params"); return; }
+  if (m_show_frame_texture && !m_frame_outdated) return;                      // the finished frame stays (crtgtrenderer.cpp:322-325)
+  if (a->renderer_redraw(m_dev, 0) != VRB_OK) { Fail("vrb_renderer_redraw"); return; }
+  if (m_show_frame_texture) {
+    long long left = 0;
+    if (a->crtgt_read_state(m_dev, nullptr, &left) != VRB_OK) { Fail("vrb_crtgt_read_state"); return; }
+    m_frame_outdated = left > 0;                                              // :311-320
+  } else m_frame_outdated = true;
 }
 
 // ---- RenderingManager ----------------------------------------------------------------------------------------

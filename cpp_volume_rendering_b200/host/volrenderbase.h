@@ -183,6 +183,32 @@ class CudaSBTMDirectionalOcclusionShading : public BaseVolumeRenderer {
   int grid_size[2], max_number_of_passes;
 };
 
+// RC1PConeLightGroundTruthSteps (structured/rc1pcrtgt/crtgtrenderer.{h,cpp}): members as in crtgtrenderer.h:79-104, public here as
+// the ImGui panel is absent.  m_show_frame_texture = false draws the face-coloured box and restarts the frame generation (PreRedraw);
+// true advances every unfinished ray by one sample per Redraw until IsFrameOutdated() turns false.
+class CudaRC1PConeLightGroundTruthSteps : public BaseVolumeRenderer {
+ public:
+  CudaRC1PConeLightGroundTruthSteps();
+  const char* GetName() override { return "1-Pass - Ray Casting - Cone Ground Truth (Steps) (CUDA B200)"; }
+  const char* GetAbbreviationName() override { return "cu_s_1rc_gt_c"; }
+  vis::GRID_VOLUME_DATA_TYPE GetDataTypeSupport() override { return vis::GRID_VOLUME_DATA_TYPE::STRUCTURED; }
+  bool Init(int w, int h) override;
+  bool Update(vis::Camera* camera) override;
+  void Redraw() override;
+  void MultiSampleRedraw() override { Redraw(); }      // compiled in only with MULTISAMPLE_AVAILABLE (crtgtrenderer.cpp:53-55)
+  void DownScalingRedraw() override { Redraw(); }
+  void UpScalingRedraw() override { Redraw(); }
+  bool IsFrameOutdated() const { return m_frame_outdated; }
+  void ResetOutputFrameGeneration() { m_show_frame_texture = false; m_frame_outdated = true; }   // crtgtrenderer.cpp:613-617
+  bool m_show_frame_texture, m_apply_gradient, m_apply_occlusion, m_apply_shadows, m_light_parameters_outdated;
+  float m_u_step_size, m_u_light_ray_initial_step, m_u_light_ray_step_size;
+  int m_occ_num_rays_sampled, m_sdw_num_rays_sampled, m_shadow_type;
+  float m_occ_cone_aperture_angle, m_occ_cone_distance_eval, m_sdw_cone_aperture_angle, m_sdw_cone_distance_eval;
+  int m_samples_per_redraw;            // new: dispatches folded into one Redraw (1 = the reference)
+ private:
+  bool m_frame_outdated;
+};
+
 // ---- RenderingManager: registry + Display() order + evaluation loop ----------------------------------------
 class RenderingManager {
  public:

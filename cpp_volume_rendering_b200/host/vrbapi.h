@@ -22,6 +22,8 @@ struct VrbApi {
   int (*renderer_update)(vrb_renderer*, const vrb_camera*, const vrb_light*);
   int (*renderer_redraw)(vrb_renderer*, int);
   int (*renderer_set_multiscaling)(vrb_renderer*, int, int);
+  int (*crtgt_set_kernels)(vrb_renderer*, const float*, int, const float*, int);
+  int (*crtgt_read_state)(vrb_renderer*, float*, long long*);
   int (*renderer_frame)(vrb_renderer*, void**, int*, int*);
   int (*renderer_read_frame)(vrb_renderer*, void*, int);
   int (*renderer_counters)(vrb_renderer*, uint64_t*, double*);

@@ -44,6 +44,7 @@ const VrbApi* VrbApi::Get(std::string* why) {
     SYM(renderer_update, "vrb_renderer_update"); SYM(renderer_redraw, "vrb_renderer_redraw");
     SYM(renderer_frame, "vrb_renderer_frame"); SYM(renderer_read_frame, "vrb_renderer_read_frame");
     SYM(renderer_counters, "vrb_renderer_counters"); SYM(renderer_set_multiscaling, "vrb_renderer_set_multiscaling");
+    SYM(crtgt_set_kernels, "vrb_crtgt_set_kernels"); SYM(crtgt_read_state, "vrb_crtgt_read_state");
 #undef SYM
     ok = all;
   });

@@ -13,7 +13,7 @@ _P = C.c_void_p
 _lib = None
 
 RENDERERS = {"rc1pass": 0, "iso": 1, "iso_skip_v1": 2, "iso_skip_v2": 3, "dos": 4, "ebs": 5, "vct": 6, "sbtm": 7, "iso_forward": 8,
-             "iso_deferred": 9}
+             "iso_deferred": 9, "crtgt": 10}
 
 
 def lib():
@@ -81,6 +81,12 @@ def session_light_cache(active, res=(32, 32, 32)):
 def session_multiscaling(mode, kernel=1):
     """Sets (mode 0..3, vis::IMAGE_FILTER_KERNEL 0..5) or resets (mode < 0) the multiscaling choice of the next run_session."""
     lib().vrbh_session_multiscaling(int(mode), int(kernel))
+
+
+def session_ground_truth(rays, fold=1):
+    """Next run_session's ground-truth renderer: `rays` rays per cone (0: cones off, < 0: constructor state = box preview),
+    frame generation on with `fold` samples per Redraw."""
+    lib().vrbh_session_ground_truth(int(rays), int(fold))
 
 
 def run_session(volume_path, tf_path, renderer, width, height, eye, eval_dir=None, numframes=1, max_samples=0, device=0):

@@ -47,7 +47,8 @@ typedef enum {
   VRB_VCT = 6,         /* RC1PVoxelConeTracingSGPU              structured/rc1pvctsg        */
   VRB_SBTM_DOS = 7,    /* SBTMDirectionalOcclusionShading       structured/sbtmdos          */
   VRB_ISO_FORWARD = 8, /* FowardRendering                       structured/ForwardRender    */
-  VRB_ISO_DEFERRED = 9 /* DeferredShading                       structured/DeferredShading  */
+  VRB_ISO_DEFERRED = 9,/* DeferredShading                       structured/DeferredShading  */
+  VRB_CRT_GT = 10      /* RC1PConeLightGroundTruthSteps         structured/rc1pcrtgt        */
 } vrb_renderer_kind;
 
 typedef enum { VRB_FRAME_RGBA16F = 0, VRB_FRAME_RGB8_OVER_WHITE = 1, VRB_FRAME_RGBA32F = 2 } vrb_frame_format;
@@ -272,6 +273,31 @@ int vrb_renderer_read_frame(vrb_renderer* r, void* host, int format);
 /* samples: march-loop iterations of the last redraw (only if count_samples was set, else 0);
  * ms: device time of the last redraw measured with CUDA events on the context stream. */
 int vrb_renderer_counters(vrb_renderer* r, uint64_t* samples, double* ms);
+
+/* RC1PConeLightGroundTruthSteps (crtgtrenderer.h:60-115; constructor defaults crtgtrenderer.cpp:23-52, Init :106-113). */
+typedef struct {
+  float step_size;                 /* m_u_step_size; Init: (0.5 / sqrt 3) * |voxel scale| */
+  float light_ray_initial_step;    /* m_u_light_ray_initial_step = 1 */
+  float light_ray_step_size;       /* m_u_light_ray_step_size = 0.5 */
+  int   apply_occlusion;           /* m_apply_occlusion = false */
+  float occ_cone_aperture_angle;   /* 90: feeds the kernel generation on the host only */
+  float occ_cone_distance_eval;    /* Init: diagonal * 0.5 */
+  int   apply_shadows;             /* m_apply_shadows = false */
+  float sdw_cone_aperture_angle;   /* 1 */
+  float sdw_cone_distance_eval;    /* Init: diagonal * 0.75 */
+  int   shadow_type;               /* 0 point, 1 spot, 2 directional */
+  int   apply_gradient_shading;    /* m_apply_gradient */
+  int   show_frame_texture;        /* m_show_frame_texture: 0 = Redraw clears the frame generation and draws the face-coloured box
+                                      (vol_intersection.comp), 1 = every Redraw advances every unfinished ray */
+  int   samples_per_redraw;        /* extension: dispatches of gt_ray_marching.comp folded into one Redraw (1 = the reference) */
+  float light_cam_forward[3], light_cam_up[3], light_cam_right[3];   /* LightCamForward / Up / Right (crtgtrenderer.cpp:222-236) */
+  int   count_samples;
+} vrb_crtgt_params;
+/* Replaces the two RGB16F kernel textures of Update() (crtgtrenderer.cpp:125-179): n x {x, y, z} cone ray coefficients each. */
+int vrb_crtgt_set_kernels(vrb_renderer* r, const float* occ_xyz, int n_occ, const float* sdw_xyz, int n_sdw);
+/* The RG16F state image (ray distance, done flag) as float32, width*height*2 (host_rg may be NULL), and the number of pixels the
+ * last Redraw left unfinished = RedrawFrameTexture's m_frame_outdated scan (crtgtrenderer.cpp:311-320).  Synchronises. */
+int vrb_crtgt_read_state(vrb_renderer* r, float* host_rg, long long* unfinished);
 
 /* Test hook for K5 (ComputeBlocksFromVolume, rc1custompisoadaptrenderer.cpp:20-113, moved to the GPU): the block
  * min / max grids of a VRB_ISO_SKIP_V1 / _V2 renderer, num_blocks[0]*[1]*[2] floats each, x fastest. */

@@ -225,6 +225,29 @@ uint64_t orc_obj_render(const orc_obj_params* p, const float* vol_r16f, const fl
  * 0 box, 1 hat, 2 Catmull-Rom, 3 Mitchell-Netravali, 4 cardinal B-spline 3, 5 cardinal O-MOMS 3.  src: sw*sh*4 floats (rounded to
  * half on entry, row 0 = bottom), dst: tw*th*4 floats holding half-representable values. */
 void orc_frame_multiscale(int mode, int kernel, const float* src_rgba, int sw, int sh, float* dst_rgba, int tw, int th);
+/* RC1PConeLightGroundTruthSteps (orc_crtgt.cpp; cppvolrend/structured/rc1pcrtgt). */
+typedef struct {
+  int   width, height;
+  int   vol_w, vol_h, vol_d;
+  float voxel[3];
+  float eye[3], lookat[9], tan_fovy, aspect;
+  float step_size;                             /* StepSize */
+  float light_ray_initial_gap, light_ray_step_size;
+  int   apply_occlusion, occ_num_rays; float occ_cone_distance_eval;
+  int   apply_shadow, sdw_num_rays;    float sdw_cone_distance_eval;
+  int   shadow_type;                           /* 0 point, 1 spot, 2 directional */
+  float light_pos[3], light_cam_forward[3], light_cam_up[3], light_cam_right[3];
+  float ka, kd;
+  int   weight_mode, threads;
+} orc_crtgt_params;
+/* `dispatches` runs of gt_ray_marching.comp main() over every pixel; frame_rgba (w*h*4) and state_rg (w*h*2) are read and
+ * written (zero them for a new frame: PreRedraw).  occ_xyz / sdw_xyz: the kernel vectors, 3 floats per ray.  ApplyGradientPhongShading
+ * through orc_set_phong (ispec = 1).  Returns primary samples taken. */
+uint64_t orc_crtgt_dispatch(const orc_crtgt_params* p, const float* vol_r16f, const float* tf_rgbt, int tf_n, const float* occ_xyz,
+                            const float* sdw_xyz, float* frame_rgba, float* state_rg, int dispatches);
+/* vol_intersection.comp over every pixel (pixels missing the box keep their value). */
+void orc_crtgt_cube(const orc_crtgt_params* p, float* frame_rgba);
+
 float orc_frame_kernel_weight(int kernel, float x);
 void orc_frame_digital_filter(int kernel, float* rgba, int w, int h, int round_half);
 

@@ -48,6 +48,18 @@ class EbsParams(C.Structure):
                 ("row_begin", C.c_int), ("row_end", C.c_int), ("row_stride", C.c_int), ("threads", C.c_int)]
 
 
+class CrtgtParams(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("vol_w", C.c_int), ("vol_h", C.c_int), ("vol_d", C.c_int),
+                ("voxel", C.c_float * 3), ("eye", C.c_float * 3), ("lookat", C.c_float * 9),
+                ("tan_fovy", C.c_float), ("aspect", C.c_float), ("step_size", C.c_float),
+                ("light_ray_initial_gap", C.c_float), ("light_ray_step_size", C.c_float),
+                ("apply_occlusion", C.c_int), ("occ_num_rays", C.c_int), ("occ_cone_distance_eval", C.c_float),
+                ("apply_shadow", C.c_int), ("sdw_num_rays", C.c_int), ("sdw_cone_distance_eval", C.c_float),
+                ("shadow_type", C.c_int), ("light_pos", C.c_float * 3), ("light_cam_forward", C.c_float * 3),
+                ("light_cam_up", C.c_float * 3), ("light_cam_right", C.c_float * 3), ("ka", C.c_float), ("kd", C.c_float),
+                ("weight_mode", C.c_int), ("threads", C.c_int)]
+
+
 class VctParams(C.Structure):
     _fields_ = [("width", C.c_int), ("height", C.c_int), ("vol_w", C.c_int), ("vol_h", C.c_int), ("vol_d", C.c_int),
                 ("voxel", C.c_float * 3), ("eye", C.c_float * 3), ("lookat", C.c_float * 9),
@@ -370,6 +382,48 @@ def ebs_render(p, vol_r16f, tf_rgbt, sat):
     shaded = C.c_uint64()
     total = lib().orc_ebs_render(C.byref(p), _ptr(vol), _ptr(tf), tf.shape[0], _ptr(s), _ptr(out), C.byref(shaded))
     return out, int(total), int(shaded.value)
+
+
+def crtgt_params(cam, width, height, vol_shape_zyx, prm, light, voxel=(1.0, 1.0, 1.0), threads=0):
+    """prm: the device library's CrtgtParams after set_params (so both sides use the same numbers)."""
+    p = CrtgtParams()
+    p.width, p.height = width, height
+    p.vol_d, p.vol_h, p.vol_w = vol_shape_zyx
+    p.voxel[:] = voxel
+    p.eye[:] = list(cam.eye); p.lookat[:] = list(cam.lookat); p.tan_fovy = cam.tan_fovy; p.aspect = cam.aspect
+    p.step_size = prm.step_size
+    p.light_ray_initial_gap = prm.light_ray_initial_step; p.light_ray_step_size = prm.light_ray_step_size
+    p.apply_occlusion = prm.apply_occlusion; p.occ_cone_distance_eval = prm.occ_cone_distance_eval
+    p.apply_shadow = prm.apply_shadows; p.sdw_cone_distance_eval = prm.sdw_cone_distance_eval
+    p.shadow_type = prm.shadow_type
+    p.light_pos[:] = list(light.position)
+    p.light_cam_forward[:] = list(prm.light_cam_forward); p.light_cam_up[:] = list(prm.light_cam_up); p.light_cam_right[:] = list(prm.light_cam_right)
+    p.ka, p.kd = light.ka, light.kd
+    p.threads = threads
+    return p
+
+
+def crtgt_dispatch(p, vol_r16f, tf_rgbt, occ_xyz, sdw_xyz, frame=None, state=None, dispatches=1):
+    """`dispatches` runs of gt_ray_marching.comp; (frame [h, w, 4], state [h, w, 2], primary samples).  None: a cleared frame."""
+    vol = np.ascontiguousarray(vol_r16f, np.float32); tf = np.ascontiguousarray(tf_rgbt, np.float32)
+    occ = np.ascontiguousarray(occ_xyz, np.float32).reshape(-1, 3); sdw = np.ascontiguousarray(sdw_xyz, np.float32).reshape(-1, 3)
+    p.occ_num_rays, p.sdw_num_rays = len(occ), len(sdw)
+    frame = np.zeros((p.height, p.width, 4), np.float32) if frame is None else np.ascontiguousarray(frame, np.float32).copy()
+    state = np.zeros((p.height, p.width, 2), np.float32) if state is None else np.ascontiguousarray(state, np.float32).copy()
+    f = lib().orc_crtgt_dispatch
+    f.restype = C.c_uint64
+    f.argtypes = [C.POINTER(CrtgtParams), _P, _P, C.c_int, _P, _P, _P, _P, C.c_int]
+    n = f(C.byref(p), _ptr(vol), _ptr(tf), tf.shape[0], _ptr(occ), _ptr(sdw), _ptr(frame), _ptr(state), int(dispatches))
+    return frame, state, int(n)
+
+
+def crtgt_cube(p, frame=None):
+    frame = np.zeros((p.height, p.width, 4), np.float32) if frame is None else np.ascontiguousarray(frame, np.float32).copy()
+    f = lib().orc_crtgt_cube
+    f.restype = None
+    f.argtypes = [C.POINTER(CrtgtParams), _P]
+    f(C.byref(p), _ptr(frame))
+    return frame
 
 
 _MAXDENS = {np.dtype(np.uint8): 255.0, np.dtype(np.uint16): 65535.0, np.dtype(np.float32): 1.0}
