@@ -8,6 +8,7 @@
 // Bound: texture fetch latency of the secondary rays (each a serial chain of dependent exp() products).
 #include "vrb_internal.cuh"
 #include "vrb_ray.cuh"
+#include <algorithm>
 #include <cmath>
 #include <vector>
 
@@ -23,11 +24,14 @@ struct GtArgs {
   int apply_shadow, n_sdw; float sdw_dist;
   int shadow_type;
   float light_pos[3], fwd[3], up[3], right[3], ka, kd;
+  float res_over_size[3];                      // VolumeGridResolution / VolumeGridSize (secondary-ray fetches)
   PhongParams phong;
   const float* occ; const float* sdw;          // kernel vectors, half-representable floats, 3 per ray
   uint2* frame; __half2* state;
   int samples;
   unsigned long long* count; unsigned* unfinished;
+  unsigned* queue;                             // pixel queue of crtgt_kernel (zero at launch)
+  unsigned long long* sec_count;               // count_samples == 2: classified fetches of the secondary rays (0: not counted)
 };
 
 __device__ __forceinline__ float round_half(float v) { return __half2float(__float2half_rn(v)); }
@@ -49,59 +53,126 @@ __device__ __forceinline__ float4 gt_classify(const GtArgs& a, f3 tx) {
   return make_float4(fmaf(w, r1.x - r0.x, r0.x), fmaf(w, r1.y - r0.y, r0.y), fmaf(w, b1.x - b0.x, b0.x), fmaf(w, b1.y - b0.y, b0.y));
 }
 
+// The density fetch of gt_classify split in two: the texture instructions are issued one secondary-ray step ahead of their use
+// (the positions along a ray do not depend on the transparency accumulated so far), the filter + transfer-function lookup
+// run when the step is consumed.  A fetch issued for a step the ray never reaches (early out at 1 - T > 0.99) is harmless.
+#ifndef VRB_GT_AHEAD
+#define VRB_GT_AHEAD 4
+#endif
+constexpr int GT_AHEAD = VRB_GT_AHEAD;
+struct GtFetch { uint2 q0, q1; float ax, ay, az; };
+// Texel coordinate = tx * (resolution / size) - 0.5 with the ratio formed once on the host: the shader's `tx / VolumeGridSize`
+// followed by the sampler's `* resolution` costs three IEEE divisions per fetch, a third of this kernel's instructions; the
+// two agree to 1 ulp of the coordinate (exactly for unit voxels), far below what the half-rounded colour resolves.
+__device__ __forceinline__ GtFetch gt_issue(const GtArgs& a, f3 tx) {
+  const float X = fmaf(tx.x, a.res_over_size[0], -0.5f), Y = fmaf(tx.y, a.res_over_size[1], -0.5f), Z = fmaf(tx.z, a.res_over_size[2], -0.5f);
+  float fx = floorf(X), fy = floorf(Y), fz = floorf(Z);
+  GtFetch f;
+  f.ax = fx < 0.0f ? 0.0f : __fsub_rn(X, fx); f.ay = fy < 0.0f ? 0.0f : __fsub_rn(Y, fy); f.az = __fsub_rn(Z, fz);
+  fx = fminf(fmaxf(fx, -1.0f), a.res[0]); fy = fminf(fmaxf(fy, -1.0f), a.res[1]); fz = fminf(fmaxf(fz, -1.0f), a.res[2]);
+  f.q0 = tex3D<uint2>(a.quad, fx + 0.5f, fy + 0.5f, fz + 0.5f);
+  f.q1 = tex3D<uint2>(a.quad, fx + 0.5f, fy + 0.5f, fz + 1.5f);
+  return f;
+}
+// the rest of tex3d_f32_exact (vrb_ray.cuh) + the alpha channel of the transfer-function lookup of gt_classify
+__device__ __forceinline__ float gt_sigma(const GtArgs& a, const GtFetch& f) {
+  const float2 a0 = __half22float2(*reinterpret_cast<const __half2*>(&f.q0.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&f.q0.y));
+  const float2 a1 = __half22float2(*reinterpret_cast<const __half2*>(&f.q1.x)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&f.q1.y));
+  const float c00 = __fadd_rn(a0.x, __fmul_rn(f.ax, __fsub_rn(a0.y, a0.x))), c10 = __fadd_rn(b0.x, __fmul_rn(f.ax, __fsub_rn(b0.y, b0.x)));
+  const float c01 = __fadd_rn(a1.x, __fmul_rn(f.ax, __fsub_rn(a1.y, a1.x))), c11 = __fadd_rn(b1.x, __fmul_rn(f.ax, __fsub_rn(b1.y, b1.x)));
+  const float c0 = __fadd_rn(c00, __fmul_rn(f.ay, __fsub_rn(c10, c00))), c1 = __fadd_rn(c01, __fmul_rn(f.ay, __fsub_rn(c11, c01)));
+  const float density = __fadd_rn(c0, __fmul_rn(f.az, __fsub_rn(c1, c0)));
+  const float u = fminf(fmaxf(fmaf(density, (float)a.tf_n, -0.5f), 0.0f), (float)(a.tf_n - 1));
+  const int j = (int)u;
+  const float w = u - (float)j;
+  const uint2 e0 = __ldg(a.tf_lin + j), e1 = __ldg(a.tf_lin + min(j + 1, a.tf_n - 1));
+  const float t0 = __half2float(__ushort_as_half((unsigned short)(e0.y >> 16))), t1 = __half2float(__ushort_as_half((unsigned short)(e1.y >> 16)));
+  return fmaf(w, t1 - t0, t0);
+}
+
 // the loop both cone functions share (gt_ray_marching.comp:124-157, :206-239): transparency along one secondary ray
-__device__ float gt_ray_transparency(const GtArgs& a, f3 tx_pos, f3 dir, float dist) {
+__device__ float gt_ray_transparency(const GtArgs& a, f3 tx_pos, f3 dir, float dist, unsigned& nsec) {
   float Vt = 1.0f;
   float s = a.gap;
-  float st0 = gt_classify(a, add3(tx_pos, scale3(dir, s))).w;
-  while (s < dist) {
-    const float h = gmin(a.lstep, __fsub_rn(dist, s));
-    const f3 at = add3(tx_pos, scale3(dir, __fadd_rn(s, h)));
-    if (at.x < 0.0f || at.x > a.sizes[0] || at.y < 0.0f || at.y > a.sizes[1] || at.z < 0.0f || at.z > a.sizes[2]) break;
-    const float st1 = gt_classify(a, at).w;
-    Vt = __fmul_rn(Vt, expf(__fmul_rn(-__fmul_rn(__fadd_rn(st0, st1), 0.5f), h)));
-    if (__fsub_rn(1.0f, Vt) > 0.99f) break;
-    st0 = st1;
-    s = __fadd_rn(s, h);
+  float st0 = gt_sigma(a, gt_issue(a, add3(tx_pos, scale3(dir, s))));
+  nsec++;
+  auto step = [&](float s_, float& h_, f3& at_) -> bool {           // the loop head: `s < dist`, h, atpos and the box test
+    if (!(s_ < dist)) return false;
+    h_ = gmin(a.lstep, __fsub_rn(dist, s_));
+    at_ = add3(tx_pos, scale3(dir, __fadd_rn(s_, h_)));
+    return !(at_.x < 0.0f || at_.x > a.sizes[0] || at_.y < 0.0f || at_.y > a.sizes[1] || at_.z < 0.0f || at_.z > a.sizes[2]);
+  };
+  // GT_AHEAD steps in flight: slot j is refilled with the step GT_AHEAD further on as soon as its own step is consumed
+  // (slots rotate by name through the unrolled loop: a copy out of a fetch's destination registers would wait for the fetch)
+  GtFetch f[GT_AHEAD]; float hh[GT_AHEAD]; bool vv[GT_AHEAD];
+  float s_next = s; bool open = true;
+  auto setup = [&](int j) {
+    float h_ = 0.f; f3 at_ = tx_pos;
+    const bool ok = open && step(s_next, h_, at_);
+    vv[j] = ok; hh[j] = h_;
+    if (ok) { f[j] = gt_issue(a, at_); s_next = __fadd_rn(s_next, h_); } else open = false;
+  };
+#pragma unroll
+  for (int j = 0; j < GT_AHEAD; j++) setup(j);
+  for (;;) {
+#pragma unroll
+    for (int j = 0; j < GT_AHEAD; j++) {
+      if (!vv[j]) return Vt;
+      const float st1 = gt_sigma(a, f[j]);
+      nsec++;
+      Vt = __fmul_rn(Vt, __expf(__fmul_rn(-__fmul_rn(__fadd_rn(st0, st1), 0.5f), hh[j])));
+      if (__fsub_rn(1.0f, Vt) > 0.99f) return Vt;
+      st0 = st1;
+      setup(j);
+    }
   }
-  return Vt;
 }
 
-__device__ float gt_cone(const GtArgs& a, const float* kernel, int n, f3 tx_pos, f3 v_right, f3 v_up, f3 v_dir, float dist) {
-  float S = 0.0f, W = 0.0f;
-  for (int rayid = 0; rayid < n; rayid++) {
-    const float kx = __ldg(kernel + 3 * rayid), ky = __ldg(kernel + 3 * rayid + 1), kz = __ldg(kernel + 3 * rayid + 2);
-    const f3 ray = normalize_rn(add3(add3(scale3(v_right, kx), scale3(v_up, ky)), scale3(v_dir, kz)));
-    const float Vt = gt_ray_transparency(a, tx_pos, ray, dist);
-    const float wgt = dot_rn(v_dir, ray);
-    S = __fadd_rn(S, __fmul_rn(Vt, wgt));
-    W = __fadd_rn(W, wgt);
-  }
-  return __fdiv_rn(S, W);
-}
-
-// ShadeSample (gt_ray_marching.comp:254-368)
-__device__ __noinline__ f3 gt_shade_sample(const GtArgs& a, float4 clr, f3 Tpos, f3 camera_dir, f3 v_up, f3 v_right) {
+// ShadeSample (gt_ray_marching.comp:254-368), one sample shaded by a whole warp: the OccNumberOfSampledRays +
+// SdwNumberOfSampledRays secondary rays of ConeOcclusionEvaluationRayCasting (:109-168) and ConeShadowsEvaluationRayCasting
+// (:171-251) are dealt to the lanes, their `Vt * r_weight` / `r_weight` terms summed afterwards in ray order (so the float32
+// sums are the serial loop's).  Every lane returns the same colour.
+__device__ __forceinline__ f3 gt_shade_sample(const GtArgs& a, float4 clr, f3 Tpos, f3 camera_dir, f3 v_up, f3 v_right, unsigned& nsec) {
+  const int lane = threadIdx.x & 31;
   float ka = 0.0f, kd = 0.0f, Iocc = 0.0f, Isdw = 0.0f;
   const f3 sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]);
-  if (a.apply_occlusion) {
-    ka = a.ka;
-    Iocc = gt_cone(a, a.occ, a.n_occ, Tpos, v_right, v_up, normalize_rn(mk3(-camera_dir.x, -camera_dir.y, -camera_dir.z)), a.occ_dist);
-  }
+  const f3 occ_d = normalize_rn(mk3(-camera_dir.x, -camera_dir.y, -camera_dir.z));
+  f3 sd = occ_d, su = v_up, sr = v_right;
+  bool dark = false;
+  if (a.apply_occlusion) ka = a.ka;
   if (a.apply_shadow) {
     kd = a.kd;
     const f3 Wpos = sub3(Tpos, scale3(sizes, 0.5f));
     const f3 fwd = mk3(a.fwd[0], a.fwd[1], a.fwd[2]), up = mk3(a.up[0], a.up[1], a.up[2]), right = mk3(a.right[0], a.right[1], a.right[2]);
-    f3 d, u, r;
-    bool dark = false;
     if (a.shadow_type == 0 || a.shadow_type == 1) {
-      d = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), Wpos));
-      u = normalize_rn(cross_rn(d, right));
-      r = normalize_rn(cross_rn(d, u));
-      dark = a.shadow_type == 1 && dot_rn(d, fwd) < 30.0f;                         // :188
-    } else { d = fwd; u = up; r = right; }
-    Isdw = dark ? 0.0f : gt_cone(a, a.sdw, a.n_sdw, Tpos, r, u, d, a.sdw_dist);
+      sd = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), Wpos));
+      su = normalize_rn(cross_rn(sd, right));
+      sr = normalize_rn(cross_rn(sd, su));
+      dark = a.shadow_type == 1 && dot_rn(sd, fwd) < 30.0f;                        // :188
+    } else { sd = fwd; su = up; sr = right; }
   }
+  const int n_occ = a.apply_occlusion ? a.n_occ : 0, n_sdw = (a.apply_shadow && !dark) ? a.n_sdw : 0, total = n_occ + n_sdw;
+  float So = 0.0f, Wo = 0.0f, Ss = 0.0f, Ws = 0.0f;
+  for (int base = 0; base < total; base += 32) {
+    const int q = base + lane;
+    float vw = 0.0f, wgt = 0.0f;
+    if (q < total) {
+      const bool is_occ = q < n_occ;
+      const float* k = is_occ ? a.occ + 3 * q : a.sdw + 3 * (q - n_occ);
+      const f3 r = is_occ ? v_right : sr, u = is_occ ? v_up : su, d = is_occ ? occ_d : sd;
+      const f3 ray = normalize_rn(add3(add3(scale3(r, __ldg(k)), scale3(u, __ldg(k + 1))), scale3(d, __ldg(k + 2))));
+      const float Vt = gt_ray_transparency(a, Tpos, ray, is_occ ? a.occ_dist : a.sdw_dist, nsec);
+      wgt = dot_rn(d, ray);
+      vw = __fmul_rn(Vt, wgt);
+    }
+    const int cnt = min(32, total - base);
+    for (int j = 0; j < cnt; j++) {
+      const float v = __shfl_sync(0xffffffffu, vw, j), ww = __shfl_sync(0xffffffffu, wgt, j);
+      if (base + j < n_occ) { So = __fadd_rn(So, v); Wo = __fadd_rn(Wo, ww); } else { Ss = __fadd_rn(Ss, v); Ws = __fadd_rn(Ws, ww); }
+    }
+  }
+  if (a.apply_occlusion) Iocc = __fdiv_rn(So, Wo);
+  if (a.apply_shadow) Isdw = dark ? 0.0f : __fdiv_rn(Ss, Ws);
   float4 L = clr;
   if (!phong_shade_sample(0, a.phong, Tpos, sizes, mk3(a.res[0], a.res[1], a.res[2]), mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]),
                           mk3(a.eye[0], a.eye[1], a.eye[2]), ka, kd, a.apply_shadow != 0, Iocc, Isdw, L)) {
@@ -113,73 +184,119 @@ __device__ __noinline__ f3 gt_shade_sample(const GtArgs& a, float4 clr, f3 Tpos,
   return mk3(L.x, L.y, L.z);
 }
 
+#ifndef VRB_GT_WARPS
+#define VRB_GT_WARPS 8
+#endif
+constexpr int GT_WARPS = VRB_GT_WARPS, GT_THREADS = 32 * GT_WARPS;
+
+// What one dispatch of main() needs from its primary sample: everything but the composition.
+struct GtSample { float rgb[3]; float sigma; int visible; };
+
+// One CTA per pixel.  A pixel's cost is its visible samples x rays x ray length — orders of magnitude apart between pixels — and
+// the samples of one ray, shaded one after the other, set the frame time.  The shading of a sample does not depend on the
+// samples in front of it (only whether the ray got that far does), so the CTA's warps shade GT_WARPS consecutive dispatches'
+// samples at once, each warp dealing its sample's secondary rays to its lanes; then every thread replays the dispatches in
+// order from shared memory — colour reset, composition, half rounding of colour and distance, the three ways a dispatch ends —
+// exactly as the serial loop would.  A sample shaded beyond the one that ends the ray is thrown away.
 template <bool COUNT>
-__global__ void __launch_bounds__(32) crtgt_kernel(const __grid_constant__ GtArgs a) {
-  const int lane = threadIdx.x;
-  const int px = blockIdx.x * 8 + (lane & 7), py = blockIdx.y * 4 + (lane >> 3);
-  unsigned n = 0;
-  bool pending = false;
-  if (px < a.width && py < a.height) {
+__global__ void __launch_bounds__(GT_THREADS) crtgt_kernel(const __grid_constant__ GtArgs a) {
+  __shared__ GtSample sh[GT_WARPS];
+  __shared__ int sh_item;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tiles_x = (a.width + 7) / 8, n_items = tiles_x * ((a.height + 3) / 4) * 32;
+  unsigned n = 0, nsec = 0, left = 0;
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) sh_item = (int)atomicAdd(a.queue, 1u);
+    __syncthreads();
+    const int item = sh_item;
+    if (item >= n_items) break;
+    const int tile = item >> 5, sub = item & 31;
+    const int px = (tile % tiles_x) * 8 + (sub & 7), py = (tile / tiles_x) * 4 + (sub >> 3);
+    if (px >= a.width || py >= a.height) continue;
     const size_t o = (size_t)py * a.width + px;
     float2 st = __half22float2(a.state[o]);
-    if (st.y < 0.5f) {
-      const f3 sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]), half = scale3(sizes, 0.5f);
-      const f3 eye = mk3(a.eye[0], a.eye[1], a.eye[2]);
-      const f3 cdir = camera_ray_dir(px, py, a.width, a.height, a.tan_fovy, a.aspect, a.lookat);
-      f3 dir; float tnear, tfar;
-      if (!ray_aabb(eye, cdir, mk3(-half.x, -half.y, -half.z), half, dir, tnear, tfar)) {
-        a.state[o] = __floats2half2_rn(0.0f, 1.0f);                                // :477
-      } else {
-        const f3 v_right = normalize_rn(cross_rn(cdir, mk3(0.f, 1.f, 0.f)));
-        const f3 v_up = normalize_rn(cross_rn(mk3(-cdir.x, -cdir.y, -cdir.z), v_right));
-        const float D = __fsub_rn(tfar, tnear);
-        const f3 tex_pos = add3(add3(eye, scale3(dir, tnear)), half);
-        float4 color = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (st.x > 0.0f) {
-          const uint2 t = a.frame[o];
-          const float2 c0 = __half22float2(*reinterpret_cast<const __half2*>(&t.x)), c1 = __half22float2(*reinterpret_cast<const __half2*>(&t.y));
-          color = make_float4(c0.x, c0.y, c1.x, c1.y);
-        }
-        // `samples` dispatches of main(): one primary sample each, state and colour through half in between
-        for (int k = 0; k < a.samples && st.y < 0.5f; k++) {
-          if (!(st.x > 0.0f)) color = make_float4(0.f, 0.f, 0.f, 0.f);               // :399-401: the stored colour counts only past s = 0
-          float s = st.x;
-          if (s < D) {
-            const float h = gmin(a.step, __fsub_rn(D, s));
-            const f3 tx = add3(tex_pos, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));
-            float4 src = gt_classify(a, tx);
-            if (COUNT) n++;
-            bool done = false;
-            if (src.w > 0.0f) {
-              const f3 rgb = gt_shade_sample(a, src, tx, cdir, v_up, v_right);
-              src.w = __fsub_rn(1.0f, expf(-__fmul_rn(src.w, h)));
-              const float wgt = __fsub_rn(1.0f, color.w);
-              color.x = __fadd_rn(color.x, __fmul_rn(wgt, __fmul_rn(rgb.x, src.w)));
-              color.y = __fadd_rn(color.y, __fmul_rn(wgt, __fmul_rn(rgb.y, src.w)));
-              color.z = __fadd_rn(color.z, __fmul_rn(wgt, __fmul_rn(rgb.z, src.w)));
-              color.w = __fadd_rn(color.w, __fmul_rn(wgt, src.w));
-              if (color.w > 0.99f) { st = make_float2(round_half(s), 1.0f); done = true; }      // :448-452
-            }
-            if (!done) {
-              s = __fadd_rn(s, h);
-              st = make_float2(round_half(s), (s < D) ? 0.0f : 1.0f);                          // :457-468
-            }
-          }
-          // a dispatch whose loop does not run (s >= D with the flag still clear) stores the colour and leaves the state
-          color = make_float4(round_half(color.x), round_half(color.y), round_half(color.z), round_half(color.w));
-          if (!(s < D) && st.y < 0.5f) break;
-        }
-        a.frame[o] = make_uint2(pack_half2(color.x, color.y), pack_half2(color.z, color.w));
-        a.state[o] = __floats2half2_rn(st.x, st.y);
-        pending = st.y < 0.5f;
+    if (!(st.y < 0.5f)) continue;
+    const f3 sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]), half = scale3(sizes, 0.5f);
+    const f3 eye = mk3(a.eye[0], a.eye[1], a.eye[2]);
+    const f3 cdir = camera_ray_dir(px, py, a.width, a.height, a.tan_fovy, a.aspect, a.lookat);
+    f3 dir; float tnear, tfar;
+    if (!ray_aabb(eye, cdir, mk3(-half.x, -half.y, -half.z), half, dir, tnear, tfar)) {
+      if (threadIdx.x == 0) a.state[o] = __floats2half2_rn(0.0f, 1.0f);            // :477
+      continue;
+    }
+    const f3 v_right = normalize_rn(cross_rn(cdir, mk3(0.f, 1.f, 0.f)));
+    const f3 v_up = normalize_rn(cross_rn(mk3(-cdir.x, -cdir.y, -cdir.z), v_right));
+    const float D = __fsub_rn(tfar, tnear);
+    const f3 tex_pos = add3(add3(eye, scale3(dir, tnear)), half);
+    float4 color = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (st.x > 0.0f) {
+      const uint2 t = a.frame[o];
+      const float2 c0 = __half22float2(*reinterpret_cast<const __half2*>(&t.x)), c1 = __half22float2(*reinterpret_cast<const __half2*>(&t.y));
+      color = make_float4(c0.x, c0.y, c1.x, c1.y);
+    }
+    // `samples` dispatches of main(), GT_WARPS at a time.  st, color and k are the same in every thread of the CTA.
+    int k = 0;
+    bool stuck = false;
+    while (k < a.samples && st.y < 0.5f && !stuck) {
+      // this warp's dispatch: `warp` dispatches after the group's first, if none of those ends the ray by distance
+      float s = st.x;
+      bool mine = k + warp < a.samples;
+      for (int i = 0; i < warp && mine; i++) {
+        if (!(s < D)) { mine = false; break; }
+        s = __fadd_rn(s, gmin(a.step, __fsub_rn(D, s)));
+        if (!(s < D)) { mine = false; break; }                                     // that dispatch set the done flag
+        s = round_half(s);                                                         // through the RG16F state image
       }
+      if (mine && s < D) {
+        const float h = gmin(a.step, __fsub_rn(D, s));
+        const f3 tx = add3(tex_pos, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));
+        const float4 src = gt_classify(a, tx);
+        f3 rgb = mk3(0.f, 0.f, 0.f);
+        if (src.w > 0.0f) rgb = gt_shade_sample(a, src, tx, cdir, v_up, v_right, nsec);
+        if (lane == 0) { sh[warp].rgb[0] = rgb.x; sh[warp].rgb[1] = rgb.y; sh[warp].rgb[2] = rgb.z; sh[warp].sigma = src.w; sh[warp].visible = src.w > 0.0f; }
+      }
+      __syncthreads();
+      for (int g = 0; g < GT_WARPS && k < a.samples && st.y < 0.5f; g++, k++) {
+        if (!(st.x > 0.0f)) color = make_float4(0.f, 0.f, 0.f, 0.f);               // :399-401: the stored colour counts only past s = 0
+        float sg = st.x;
+        if (sg < D) {
+          const float h = gmin(a.step, __fsub_rn(D, sg));
+          if (COUNT && threadIdx.x == 0) n++;
+          bool done = false;
+          if (sh[g].visible) {
+            const float alpha = __fsub_rn(1.0f, expf(-__fmul_rn(sh[g].sigma, h)));
+            const float wgt = __fsub_rn(1.0f, color.w);
+            color.x = __fadd_rn(color.x, __fmul_rn(wgt, __fmul_rn(sh[g].rgb[0], alpha)));
+            color.y = __fadd_rn(color.y, __fmul_rn(wgt, __fmul_rn(sh[g].rgb[1], alpha)));
+            color.z = __fadd_rn(color.z, __fmul_rn(wgt, __fmul_rn(sh[g].rgb[2], alpha)));
+            color.w = __fadd_rn(color.w, __fmul_rn(wgt, alpha));
+            if (color.w > 0.99f) { st = make_float2(round_half(sg), 1.0f); done = true; }   // :448-452
+          }
+          if (!done) {
+            sg = __fadd_rn(sg, h);
+            st = make_float2(round_half(sg), (sg < D) ? 0.0f : 1.0f);                      // :457-468
+          }
+        }
+        // a dispatch whose loop does not run (s >= D with the flag still clear) stores the colour and leaves the state
+        color = make_float4(round_half(color.x), round_half(color.y), round_half(color.z), round_half(color.w));
+        if (!(sg < D) && st.y < 0.5f) { stuck = true; k++; break; }
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      a.frame[o] = make_uint2(pack_half2(color.x, color.y), pack_half2(color.z, color.w));
+      a.state[o] = __floats2half2_rn(st.x, st.y);
+      if (st.y < 0.5f) left++;
     }
   }
-  const unsigned left = __popc(__ballot_sync(0xffffffffu, pending));
-  if (lane == 0 && left) atomicAdd(a.unfinished, left);
+  if (threadIdx.x == 0 && left) atomicAdd(a.unfinished, left);
   if (COUNT) {
-    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
-    if (lane == 0 && n) atomicAdd(a.count, (unsigned long long)n);
+    if (threadIdx.x == 0 && n) atomicAdd(a.count, (unsigned long long)n);
+    if (a.sec_count) {
+      for (int o = 16; o > 0; o >>= 1) nsec += __shfl_xor_sync(0xffffffffu, nsec, o);
+      if (lane == 0 && nsec) atomicAdd(a.sec_count, (unsigned long long)nsec);
+    }
   }
 }
 
@@ -233,6 +350,7 @@ class CrtgtRenderer : public RendererImpl {
     prm_.sdw_cone_distance_eval = (float)(diag * 0.75f);
     if (!d_occ_) { const float axis[3] = {0.f, 0.f, 1.f}; rc = set_kernels(axis, 1, axis, 1); if (rc != VRB_OK) return rc; }
     if (!d_unfinished_) { VRB_CUDA(cudaMalloc(&d_unfinished_, sizeof(unsigned))); VRB_CUDA(cudaMemset(d_unfinished_, 0, sizeof(unsigned))); }
+    if (!d_unfinished_ll_) { VRB_CUDA(cudaMalloc(&d_unfinished_ll_, sizeof(unsigned long long))); VRB_CUDA(cudaMemset(d_unfinished_ll_, 0, sizeof(unsigned long long))); }
     fresh_ = true;
     built = true;
     return VRB_OK;
@@ -242,6 +360,8 @@ class CrtgtRenderer : public RendererImpl {
     if (d_occ_) cudaFree(d_occ_);
     if (d_sdw_) cudaFree(d_sdw_);
     if (d_unfinished_) cudaFree(d_unfinished_);
+    if (d_unfinished_ll_) cudaFree(d_unfinished_ll_);
+    d_unfinished_ll_ = nullptr;
     d_state_ = nullptr; d_occ_ = d_sdw_ = nullptr; d_unfinished_ = nullptr; state_px_ = 0;
   }
 
@@ -307,6 +427,7 @@ class CrtgtRenderer : public RendererImpl {
     a.width = width; a.height = height;
     a.res[0] = (float)v.w; a.res[1] = (float)v.h; a.res[2] = (float)v.d;
     a.sizes[0] = (float)v.w * v.sx; a.sizes[1] = (float)v.h * v.sy; a.sizes[2] = (float)v.d * v.sz;
+    for (int i = 0; i < 3; i++) a.res_over_size[i] = a.res[i] / a.sizes[i];
     for (int i = 0; i < 3; i++) { a.eye[i] = cam.eye[i]; a.light_pos[i] = light.position[i]; a.fwd[i] = prm_.light_cam_forward[i]; a.up[i] = prm_.light_cam_up[i]; a.right[i] = prm_.light_cam_right[i]; }
     for (int i = 0; i < 9; i++) a.lookat[i] = cam.lookat[i];
     a.tan_fovy = cam.tan_fovy; a.aspect = cam.aspect;
@@ -332,14 +453,22 @@ class CrtgtRenderer : public RendererImpl {
     }
     a.samples = prm_.samples_per_redraw;
     a.count = d_samples; a.unfinished = d_unfinished_;
+    if (prm_.count_samples == 2) { a.sec_count = d_samples; a.count = d_unfinished_ll_; }   // the counter reports secondary fetches
     if (fresh_) {   // the first dispatch after a PreRedraw reads a cleared frame (the box drawn meanwhile is not part of it)
       VRB_CUDA(cudaMemsetAsync(frame, 0, frame_bytes, s));
       fresh_ = false;
     }
     VRB_CUDA(cudaMemsetAsync(d_unfinished_, 0, sizeof(unsigned), s));
     if (prm_.count_samples) VRB_CUDA(cudaMemsetAsync(d_samples, 0, sizeof(unsigned long long), s));
-    const dim3 grid((width + 7) / 8, (height + 3) / 4);
-    if (prm_.count_samples) crtgt_kernel<true><<<grid, 32, 0, s>>>(a); else crtgt_kernel<false><<<grid, 32, 0, s>>>(a);
+    a.queue = d_queue;
+    VRB_CUDA(cudaMemsetAsync(d_queue, 0, 2 * sizeof(unsigned), s));
+    const int items = ((width + 7) / 8) * ((height + 3) / 4) * 32;
+    int per_sm = 0;
+    if (prm_.count_samples) VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, crtgt_kernel<true>, GT_THREADS, 0));
+    else VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, crtgt_kernel<false>, GT_THREADS, 0));
+    const int grid = std::min(std::max(per_sm, 1) * ctx->sm_count, items);
+    if (prm_.count_samples) crtgt_kernel<true><<<grid, GT_THREADS, 0, s>>>(a); else crtgt_kernel<false><<<grid, GT_THREADS, 0, s>>>(a);
+    VRB_CUDA(cudaMemsetAsync(d_queue, 0, 2 * sizeof(unsigned), s));                // the queue words are zero between launches
     VRB_CUDA(cudaGetLastError());
     return VRB_OK;
   }
@@ -358,6 +487,7 @@ class CrtgtRenderer : public RendererImpl {
   __half2* d_state_ = nullptr; size_t state_px_ = 0;
   float* d_occ_ = nullptr; float* d_sdw_ = nullptr; int n_occ_ = 0, n_sdw_ = 0;
   unsigned* d_unfinished_ = nullptr;
+  unsigned long long* d_unfinished_ll_ = nullptr;   // scratch counter (primary samples while the public counter holds secondary fetches)
   bool fresh_ = true;
 };
 

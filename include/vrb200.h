@@ -291,7 +291,7 @@ typedef struct {
                                       (vol_intersection.comp), 1 = every Redraw advances every unfinished ray */
   int   samples_per_redraw;        /* extension: dispatches of gt_ray_marching.comp folded into one Redraw (1 = the reference) */
   float light_cam_forward[3], light_cam_up[3], light_cam_right[3];   /* LightCamForward / Up / Right (crtgtrenderer.cpp:222-236) */
-  int   count_samples;
+  int   count_samples;             /* 1: vrb_renderer_counters reports primary samples of the last Redraw, 2: fetches of the secondary rays */
 } vrb_crtgt_params;
 /* Replaces the two RGB16F kernel textures of Update() (crtgtrenderer.cpp:125-179): n x {x, y, z} cone ray coefficients each. */
 int vrb_crtgt_set_kernels(vrb_renderer* r, const float* occ_xyz, int n_occ, const float* sdw_xyz, int n_sdw);
