@@ -9,6 +9,7 @@
 #include "vrb_internal.cuh"
 #include "vrb_ray.cuh"
 #include <algorithm>
+#include <cstdlib>
 #include <cmath>
 #include <vector>
 
@@ -90,124 +91,59 @@ __device__ __forceinline__ float gt_sigma(const GtArgs& a, const GtFetch& f) {
   return fmaf(w, t1 - t0, t0);
 }
 
-// the loop both cone functions share (gt_ray_marching.comp:124-157, :206-239): transparency along one secondary ray
-__device__ float gt_ray_transparency(const GtArgs& a, f3 tx_pos, f3 dir, float dist, unsigned& nsec) {
-  float Vt = 1.0f;
-  float s = a.gap;
-  float st0 = gt_sigma(a, gt_issue(a, add3(tx_pos, scale3(dir, s))));
-  nsec++;
-  auto step = [&](float s_, float& h_, f3& at_) -> bool {           // the loop head: `s < dist`, h, atpos and the box test
-    if (!(s_ < dist)) return false;
-    h_ = gmin(a.lstep, __fsub_rn(dist, s_));
-    at_ = add3(tx_pos, scale3(dir, __fadd_rn(s_, h_)));
-    return !(at_.x < 0.0f || at_.x > a.sizes[0] || at_.y < 0.0f || at_.y > a.sizes[1] || at_.z < 0.0f || at_.z > a.sizes[2]);
-  };
-  // GT_AHEAD steps in flight: slot j is refilled with the step GT_AHEAD further on as soon as its own step is consumed
-  // (slots rotate by name through the unrolled loop: a copy out of a fetch's destination registers would wait for the fetch)
-  GtFetch f[GT_AHEAD]; float hh[GT_AHEAD]; bool vv[GT_AHEAD];
-  float s_next = s; bool open = true;
-  auto setup = [&](int j) {
-    float h_ = 0.f; f3 at_ = tx_pos;
-    const bool ok = open && step(s_next, h_, at_);
-    vv[j] = ok; hh[j] = h_;
-    if (ok) { f[j] = gt_issue(a, at_); s_next = __fadd_rn(s_next, h_); } else open = false;
-  };
-#pragma unroll
-  for (int j = 0; j < GT_AHEAD; j++) setup(j);
-  for (;;) {
-#pragma unroll
-    for (int j = 0; j < GT_AHEAD; j++) {
-      if (!vv[j]) return Vt;
-      const float st1 = gt_sigma(a, f[j]);
-      nsec++;
-      Vt = __fmul_rn(Vt, __expf(__fmul_rn(-__fmul_rn(__fadd_rn(st0, st1), 0.5f), hh[j])));
-      if (__fsub_rn(1.0f, Vt) > 0.99f) return Vt;
-      st0 = st1;
-      setup(j);
-    }
-  }
+constexpr int GT_GROUP = 32;            // dispatches shaded together (at most; fewer when a sample has many rays)
+constexpr int GT_POOL = 2048;           // secondary rays of one group (shared-memory results)
+
+// dispatches per group: about three rays per lane of the largest CTA in the pool (more only adds samples shaded past the end of
+// the ray), never more rays than the pool holds
+__host__ __device__ inline int gt_group(int rays) {
+  if (rays <= 0) return GT_GROUP;
+  int g = 768 / rays;
+  g = g < 8 ? 8 : g;
+  g = g > GT_GROUP ? GT_GROUP : g;
+  const int cap = GT_POOL / rays < 1 ? 1 : GT_POOL / rays;
+  return g < cap ? g : cap;
 }
 
-// ShadeSample (gt_ray_marching.comp:254-368), one sample shaded by a whole warp: the OccNumberOfSampledRays +
-// SdwNumberOfSampledRays secondary rays of ConeOcclusionEvaluationRayCasting (:109-168) and ConeShadowsEvaluationRayCasting
-// (:171-251) are dealt to the lanes, their `Vt * r_weight` / `r_weight` terms summed afterwards in ray order (so the float32
-// sums are the serial loop's).  Every lane returns the same colour.
-__device__ __forceinline__ f3 gt_shade_sample(const GtArgs& a, float4 clr, f3 Tpos, f3 camera_dir, f3 v_up, f3 v_right, unsigned& nsec) {
-  const int lane = threadIdx.x & 31;
-  float ka = 0.0f, kd = 0.0f, Iocc = 0.0f, Isdw = 0.0f;
-  const f3 sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]);
-  const f3 occ_d = normalize_rn(mk3(-camera_dir.x, -camera_dir.y, -camera_dir.z));
-  f3 sd = occ_d, su = v_up, sr = v_right;
-  bool dark = false;
-  if (a.apply_occlusion) ka = a.ka;
-  if (a.apply_shadow) {
-    kd = a.kd;
-    const f3 Wpos = sub3(Tpos, scale3(sizes, 0.5f));
-    const f3 fwd = mk3(a.fwd[0], a.fwd[1], a.fwd[2]), up = mk3(a.up[0], a.up[1], a.up[2]), right = mk3(a.right[0], a.right[1], a.right[2]);
-    if (a.shadow_type == 0 || a.shadow_type == 1) {
-      sd = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), Wpos));
-      su = normalize_rn(cross_rn(sd, right));
-      sr = normalize_rn(cross_rn(sd, su));
-      dark = a.shadow_type == 1 && dot_rn(sd, fwd) < 30.0f;                        // :188
-    } else { sd = fwd; su = up; sr = right; }
-  }
-  const int n_occ = a.apply_occlusion ? a.n_occ : 0, n_sdw = (a.apply_shadow && !dark) ? a.n_sdw : 0, total = n_occ + n_sdw;
-  float So = 0.0f, Wo = 0.0f, Ss = 0.0f, Ws = 0.0f;
-  for (int base = 0; base < total; base += 32) {
-    const int q = base + lane;
-    float vw = 0.0f, wgt = 0.0f;
-    if (q < total) {
-      const bool is_occ = q < n_occ;
-      const float* k = is_occ ? a.occ + 3 * q : a.sdw + 3 * (q - n_occ);
-      const f3 r = is_occ ? v_right : sr, u = is_occ ? v_up : su, d = is_occ ? occ_d : sd;
-      const f3 ray = normalize_rn(add3(add3(scale3(r, __ldg(k)), scale3(u, __ldg(k + 1))), scale3(d, __ldg(k + 2))));
-      const float Vt = gt_ray_transparency(a, Tpos, ray, is_occ ? a.occ_dist : a.sdw_dist, nsec);
-      wgt = dot_rn(d, ray);
-      vw = __fmul_rn(Vt, wgt);
-    }
-    const int cnt = min(32, total - base);
-    for (int j = 0; j < cnt; j++) {
-      const float v = __shfl_sync(0xffffffffu, vw, j), ww = __shfl_sync(0xffffffffu, wgt, j);
-      if (base + j < n_occ) { So = __fadd_rn(So, v); Wo = __fadd_rn(Wo, ww); } else { Ss = __fadd_rn(Ss, v); Ws = __fadd_rn(Ws, ww); }
-    }
-  }
-  if (a.apply_occlusion) Iocc = __fdiv_rn(So, Wo);
-  if (a.apply_shadow) Isdw = dark ? 0.0f : __fdiv_rn(Ss, Ws);
-  float4 L = clr;
-  if (!phong_shade_sample(0, a.phong, Tpos, sizes, mk3(a.res[0], a.res[1], a.res[2]), mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]),
-                          mk3(a.eye[0], a.eye[1], a.eye[2]), ka, kd, a.apply_shadow != 0, Iocc, Isdw, L)) {
-    const float k = __fdiv_rn(1.0f, __fadd_rn(ka, kd));                            // :364
-    L.x = __fmul_rn(k, __fadd_rn(__fmul_rn(__fmul_rn(clr.x, Iocc), ka), __fmul_rn(__fmul_rn(clr.x, Isdw), kd)));
-    L.y = __fmul_rn(k, __fadd_rn(__fmul_rn(__fmul_rn(clr.y, Iocc), ka), __fmul_rn(__fmul_rn(clr.y, Isdw), kd)));
-    L.z = __fmul_rn(k, __fadd_rn(__fmul_rn(__fmul_rn(clr.z, Iocc), ka), __fmul_rn(__fmul_rn(clr.z, Isdw), kd)));
-  }
-  return mk3(L.x, L.y, L.z);
-}
+// What the dispatches of one group need from their primary samples.  One entry per dispatch, filled by thread g.
+struct GtGroup {
+  float tx[GT_GROUP][3];                // s_tex_pos
+  float src[GT_GROUP][4];               // texture(TexTransferFunc, density)
+  float sd[GT_GROUP][3], su[GT_GROUP][3], sr[GT_GROUP][3];   // v_dir / v_up / v_right of ConeShadowsEvaluationRayCasting
+  float rgb[GT_GROUP][3];               // ShadeSample's result
+  int state[GT_GROUP];                  // 0: this dispatch takes no sample, 1: transparent sample, 2: visible, 3: visible, no shadow rays (:188)
+  int vis[GT_GROUP], n_vis;             // the visible dispatches, in order
+  float vw[GT_POOL], w[GT_POOL];        // Vt * r_weight and r_weight of ray r of visible dispatch v at [v * rays + r]
+  int next;                             // ray pool cursor
+};
 
-#ifndef VRB_GT_WARPS
-#define VRB_GT_WARPS 8
-#endif
-constexpr int GT_WARPS = VRB_GT_WARPS, GT_THREADS = 32 * GT_WARPS;
-
-// What one dispatch of main() needs from its primary sample: everything but the composition.
-struct GtSample { float rgb[3]; float sigma; int visible; };
-
-// One CTA per pixel.  A pixel's cost is its visible samples x rays x ray length — orders of magnitude apart between pixels — and
-// the samples of one ray, shaded one after the other, set the frame time.  The shading of a sample does not depend on the
-// samples in front of it (only whether the ray got that far does), so the CTA's warps shade GT_WARPS consecutive dispatches'
-// samples at once, each warp dealing its sample's secondary rays to its lanes; then every thread replays the dispatches in
-// order from shared memory — colour reset, composition, half rounding of colour and distance, the three ways a dispatch ends —
-// exactly as the serial loop would.  A sample shaded beyond the one that ends the ray is thrown away.
-template <bool COUNT>
-__global__ void __launch_bounds__(GT_THREADS) crtgt_kernel(const __grid_constant__ GtArgs a) {
-  __shared__ GtSample sh[GT_WARPS];
+// One CTA per pixel.  A pixel's cost is its visible samples x rays x ray length — orders of magnitude apart between pixels —
+// and secondary rays end anywhere between their first step and OccConeDistanceEvaluation / SdwConeDistanceEvaluation, so
+// neither a thread per pixel (the samples of the longest ray set the frame time) nor a lane per ray of one sample (a quarter
+// of the lanes busy on average) keeps the machine full.  The shading of a sample does not depend on the samples in front of
+// it — only whether the ray got that far does — so up to GT_GROUP consecutive dispatches' samples are classified at once, all
+// secondary rays of the visible ones go into one pool that the CTA's lanes drain (a lane takes the next ray when its own has
+// ended; the loops of gt_ray_marching.comp:124-157 and :206-239 with GT_AHEAD fetches in flight), the rays' terms are summed
+// per sample in ray order, and then every thread replays the dispatches in order — colour reset, composition, half rounding
+// of colour and distance, the three ways a dispatch ends — exactly as the serial loop would.  Samples shaded beyond the one
+// that ends the ray are thrown away.
+// WARPS: lanes for the pool — few rays per group leave most of a big CTA idle while each pixel still waits out its longest ray,
+// so the host picks the CTA size from the pool size and small CTAs put more pixels in flight.
+template <bool COUNT, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS) crtgt_kernel(const __grid_constant__ GtArgs a) {
+  __shared__ GtGroup sh;
   __shared__ int sh_item;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31, tid = threadIdx.x;
   const int tiles_x = (a.width + 7) / 8, n_items = tiles_x * ((a.height + 3) / 4) * 32;
+  const int n_occ = a.apply_occlusion ? a.n_occ : 0, n_sdw = a.apply_shadow ? a.n_sdw : 0, rays = n_occ + n_sdw;
+  // dispatches per group: about three rays per lane in the pool (more only adds samples shaded past the end of the ray)
+  const int group = gt_group(rays);
+  const f3 sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]), half = scale3(sizes, 0.5f);
+  const f3 eye = mk3(a.eye[0], a.eye[1], a.eye[2]);
   unsigned n = 0, nsec = 0, left = 0;
   for (;;) {
     __syncthreads();
-    if (threadIdx.x == 0) sh_item = (int)atomicAdd(a.queue, 1u);
+    if (tid == 0) sh_item = (int)atomicAdd(a.queue, 1u);
     __syncthreads();
     const int item = sh_item;
     if (item >= n_items) break;
@@ -217,16 +153,15 @@ __global__ void __launch_bounds__(GT_THREADS) crtgt_kernel(const __grid_constant
     const size_t o = (size_t)py * a.width + px;
     float2 st = __half22float2(a.state[o]);
     if (!(st.y < 0.5f)) continue;
-    const f3 sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]), half = scale3(sizes, 0.5f);
-    const f3 eye = mk3(a.eye[0], a.eye[1], a.eye[2]);
     const f3 cdir = camera_ray_dir(px, py, a.width, a.height, a.tan_fovy, a.aspect, a.lookat);
     f3 dir; float tnear, tfar;
     if (!ray_aabb(eye, cdir, mk3(-half.x, -half.y, -half.z), half, dir, tnear, tfar)) {
-      if (threadIdx.x == 0) a.state[o] = __floats2half2_rn(0.0f, 1.0f);            // :477
+      if (tid == 0) a.state[o] = __floats2half2_rn(0.0f, 1.0f);                    // :477
       continue;
     }
     const f3 v_right = normalize_rn(cross_rn(cdir, mk3(0.f, 1.f, 0.f)));
     const f3 v_up = normalize_rn(cross_rn(mk3(-cdir.x, -cdir.y, -cdir.z), v_right));
+    const f3 occ_d = normalize_rn(mk3(-cdir.x, -cdir.y, -cdir.z));                 // ConeOcclusionEvaluationRayCasting's v_dir (:115)
     const float D = __fsub_rn(tfar, tnear);
     const f3 tex_pos = add3(add3(eye, scale3(dir, tnear)), half);
     float4 color = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -235,41 +170,160 @@ __global__ void __launch_bounds__(GT_THREADS) crtgt_kernel(const __grid_constant
       const float2 c0 = __half22float2(*reinterpret_cast<const __half2*>(&t.x)), c1 = __half22float2(*reinterpret_cast<const __half2*>(&t.y));
       color = make_float4(c0.x, c0.y, c1.x, c1.y);
     }
-    // `samples` dispatches of main(), GT_WARPS at a time.  st, color and k are the same in every thread of the CTA.
+    // `samples` dispatches of main(), `group` at a time.  st, color and k are the same in every thread of the CTA.
     int k = 0;
     bool stuck = false;
     while (k < a.samples && st.y < 0.5f && !stuck) {
-      // this warp's dispatch: `warp` dispatches after the group's first, if none of those ends the ray by distance
-      float s = st.x;
-      bool mine = k + warp < a.samples;
-      for (int i = 0; i < warp && mine; i++) {
-        if (!(s < D)) { mine = false; break; }
-        s = __fadd_rn(s, gmin(a.step, __fsub_rn(D, s)));
-        if (!(s < D)) { mine = false; break; }                                     // that dispatch set the done flag
-        s = round_half(s);                                                         // through the RG16F state image
-      }
-      if (mine && s < D) {
-        const float h = gmin(a.step, __fsub_rn(D, s));
-        const f3 tx = add3(tex_pos, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));
-        const float4 src = gt_classify(a, tx);
-        f3 rgb = mk3(0.f, 0.f, 0.f);
-        if (src.w > 0.0f) rgb = gt_shade_sample(a, src, tx, cdir, v_up, v_right, nsec);
-        if (lane == 0) { sh[warp].rgb[0] = rgb.x; sh[warp].rgb[1] = rgb.y; sh[warp].rgb[2] = rgb.z; sh[warp].sigma = src.w; sh[warp].visible = src.w > 0.0f; }
+      // ---- A: thread g classifies the sample of dispatch k + g, if the dispatches before it do not end the ray by distance
+      if (tid < group) {
+        float s = st.x;
+        bool mine = k + tid < a.samples;
+        for (int i = 0; i < tid && mine; i++) {
+          if (!(s < D)) { mine = false; break; }
+          s = __fadd_rn(s, gmin(a.step, __fsub_rn(D, s)));
+          if (!(s < D)) { mine = false; break; }                                   // that dispatch set the done flag
+          s = round_half(s);                                                       // through the RG16F state image
+        }
+        int state = 0;
+        if (mine && s < D) {
+          const float h = gmin(a.step, __fsub_rn(D, s));
+          const f3 tx = add3(tex_pos, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));
+          const float4 src = gt_classify(a, tx);
+          sh.tx[tid][0] = tx.x; sh.tx[tid][1] = tx.y; sh.tx[tid][2] = tx.z;
+          sh.src[tid][0] = src.x; sh.src[tid][1] = src.y; sh.src[tid][2] = src.z; sh.src[tid][3] = src.w;
+          state = src.w > 0.0f ? 2 : 1;
+          if (state == 2 && a.apply_shadow) {                                      // ConeShadowsEvaluationRayCasting's basis (:176-200)
+            const f3 fwd = mk3(a.fwd[0], a.fwd[1], a.fwd[2]), up = mk3(a.up[0], a.up[1], a.up[2]), right = mk3(a.right[0], a.right[1], a.right[2]);
+            f3 d = fwd, u = up, r = right;
+            if (a.shadow_type == 0 || a.shadow_type == 1) {
+              d = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), sub3(tx, half)));
+              u = normalize_rn(cross_rn(d, right));
+              r = normalize_rn(cross_rn(d, u));
+              if (a.shadow_type == 1 && dot_rn(d, fwd) < 30.0f) state = 3;          // :188
+            }
+            sh.sd[tid][0] = d.x; sh.sd[tid][1] = d.y; sh.sd[tid][2] = d.z;
+            sh.su[tid][0] = u.x; sh.su[tid][1] = u.y; sh.su[tid][2] = u.z;
+            sh.sr[tid][0] = r.x; sh.sr[tid][1] = r.y; sh.sr[tid][2] = r.z;
+          }
+        }
+        sh.state[tid] = state;
       }
       __syncthreads();
-      for (int g = 0; g < GT_WARPS && k < a.samples && st.y < 0.5f; g++, k++) {
+      if (tid == 0) {
+        int nv = 0;
+        for (int g = 0; g < group; g++) if (sh.state[g] >= 2) sh.vis[nv++] = g;
+        sh.n_vis = nv; sh.next = 0;
+      }
+      __syncthreads();
+      // ---- B: the ray pool.  Item q = ray q % rays of visible dispatch q / rays; a lane refills between groups of GT_AHEAD steps.
+      {
+        const int total = sh.n_vis * rays;
+        bool active = false, out_of_work = total == 0;
+        int q = 0;
+        f3 tx_pos = mk3(0.f, 0.f, 0.f), rdir = mk3(0.f, 0.f, 0.f);
+        float dist = 0.f, wgt = 0.f, Vt = 1.f, st0 = 0.f, s_next = 0.f;
+        bool open = false;
+        GtFetch f[GT_AHEAD]; float hh[GT_AHEAD]; bool vv[GT_AHEAD];
+        auto step = [&](float s_, float& h_, f3& at_) -> bool {       // the loop head: `s < dist`, h, atpos and the box test
+          if (!(s_ < dist)) return false;
+          h_ = gmin(a.lstep, __fsub_rn(dist, s_));
+          at_ = add3(tx_pos, scale3(rdir, __fadd_rn(s_, h_)));
+          return !(at_.x < 0.0f || at_.x > a.sizes[0] || at_.y < 0.0f || at_.y > a.sizes[1] || at_.z < 0.0f || at_.z > a.sizes[2]);
+        };
+        auto setup = [&](int j) {
+          float h_ = 0.f; f3 at_ = tx_pos;
+          const bool ok = open && step(s_next, h_, at_);
+          vv[j] = ok; hh[j] = h_;
+          if (ok) { f[j] = gt_issue(a, at_); s_next = __fadd_rn(s_next, h_); } else open = false;
+        };
+        while (!out_of_work) {
+          if (!active) {
+            q = atomicAdd(&sh.next, 1);
+            if (q >= total) { out_of_work = true; break; }
+            const int g = sh.vis[q / rays], r = q % rays;
+            const bool is_occ = r < n_occ;
+            f3 bd, bu, br;
+            if (is_occ) { bd = occ_d; bu = v_up; br = v_right; }
+            else { bd = mk3(sh.sd[g][0], sh.sd[g][1], sh.sd[g][2]); bu = mk3(sh.su[g][0], sh.su[g][1], sh.su[g][2]); br = mk3(sh.sr[g][0], sh.sr[g][1], sh.sr[g][2]); }
+            if (!is_occ && sh.state[g] == 3) { sh.vw[q] = 0.0f; sh.w[q] = 0.0f; continue; }   // spot light outside its cone: no rays
+            const float* kv = is_occ ? a.occ + 3 * r : a.sdw + 3 * (r - n_occ);
+            rdir = normalize_rn(add3(add3(scale3(br, __ldg(kv)), scale3(bu, __ldg(kv + 1))), scale3(bd, __ldg(kv + 2))));
+            wgt = dot_rn(bd, rdir);
+            tx_pos = mk3(sh.tx[g][0], sh.tx[g][1], sh.tx[g][2]);
+            dist = is_occ ? a.occ_dist : a.sdw_dist;
+            Vt = 1.0f;
+            st0 = gt_sigma(a, gt_issue(a, add3(tx_pos, scale3(rdir, a.gap))));
+            nsec++;
+            s_next = a.gap; open = true;
+#pragma unroll
+            for (int j = 0; j < GT_AHEAD; j++) setup(j);
+            active = true;
+          }
+#pragma unroll
+          for (int j = 0; j < GT_AHEAD; j++) {
+            if (active) {
+              bool ended = !vv[j];
+              if (!ended) {
+                const float st1 = gt_sigma(a, f[j]);
+                nsec++;
+                Vt = __fmul_rn(Vt, __expf(__fmul_rn(-__fmul_rn(__fadd_rn(st0, st1), 0.5f), hh[j])));
+                ended = __fsub_rn(1.0f, Vt) > 0.99f;
+                st0 = st1;
+                if (!ended) setup(j);
+              }
+              if (ended) { sh.vw[q] = __fmul_rn(Vt, wgt); sh.w[q] = wgt; active = false; }
+            }
+          }
+        }
+      }
+      __syncthreads();
+      // ---- C: thread g finishes ShadeSample (:254-368) of dispatch g: the cones' sums in ray order, then the colour
+      if (tid < group && sh.state[tid] >= 2) {
+        int v = 0;
+        while (sh.vis[v] != tid) v++;
+        const float* vw = sh.vw + v * rays; const float* ww = sh.w + v * rays;
+        float ka = 0.0f, kd = 0.0f, Iocc = 0.0f, Isdw = 0.0f;
+        if (a.apply_occlusion) {
+          ka = a.ka;
+          float S = 0.0f, W = 0.0f;
+          for (int r = 0; r < n_occ; r++) { S = __fadd_rn(S, vw[r]); W = __fadd_rn(W, ww[r]); }
+          Iocc = __fdiv_rn(S, W);
+        }
+        if (a.apply_shadow) {
+          kd = a.kd;
+          if (sh.state[tid] != 3) {
+            float S = 0.0f, W = 0.0f;
+            for (int r = n_occ; r < rays; r++) { S = __fadd_rn(S, vw[r]); W = __fadd_rn(W, ww[r]); }
+            Isdw = __fdiv_rn(S, W);
+          }
+        }
+        const float4 clr = make_float4(sh.src[tid][0], sh.src[tid][1], sh.src[tid][2], sh.src[tid][3]);
+        const f3 Tpos = mk3(sh.tx[tid][0], sh.tx[tid][1], sh.tx[tid][2]);
+        float4 L = clr;
+        if (!phong_shade_sample(0, a.phong, Tpos, sizes, mk3(a.res[0], a.res[1], a.res[2]), mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]),
+                                eye, ka, kd, a.apply_shadow != 0, Iocc, Isdw, L)) {
+          const float kk = __fdiv_rn(1.0f, __fadd_rn(ka, kd));                      // :364
+          L.x = __fmul_rn(kk, __fadd_rn(__fmul_rn(__fmul_rn(clr.x, Iocc), ka), __fmul_rn(__fmul_rn(clr.x, Isdw), kd)));
+          L.y = __fmul_rn(kk, __fadd_rn(__fmul_rn(__fmul_rn(clr.y, Iocc), ka), __fmul_rn(__fmul_rn(clr.y, Isdw), kd)));
+          L.z = __fmul_rn(kk, __fadd_rn(__fmul_rn(__fmul_rn(clr.z, Iocc), ka), __fmul_rn(__fmul_rn(clr.z, Isdw), kd)));
+        }
+        sh.rgb[tid][0] = L.x; sh.rgb[tid][1] = L.y; sh.rgb[tid][2] = L.z;
+      }
+      __syncthreads();
+      // ---- D: the dispatches, in order
+      for (int g = 0; g < group && k < a.samples && st.y < 0.5f; g++, k++) {
         if (!(st.x > 0.0f)) color = make_float4(0.f, 0.f, 0.f, 0.f);               // :399-401: the stored colour counts only past s = 0
         float sg = st.x;
         if (sg < D) {
           const float h = gmin(a.step, __fsub_rn(D, sg));
-          if (COUNT && threadIdx.x == 0) n++;
+          if (COUNT && tid == 0) n++;
           bool done = false;
-          if (sh[g].visible) {
-            const float alpha = __fsub_rn(1.0f, expf(-__fmul_rn(sh[g].sigma, h)));
+          if (sh.state[g] >= 2) {
+            const float alpha = __fsub_rn(1.0f, expf(-__fmul_rn(sh.src[g][3], h)));
             const float wgt = __fsub_rn(1.0f, color.w);
-            color.x = __fadd_rn(color.x, __fmul_rn(wgt, __fmul_rn(sh[g].rgb[0], alpha)));
-            color.y = __fadd_rn(color.y, __fmul_rn(wgt, __fmul_rn(sh[g].rgb[1], alpha)));
-            color.z = __fadd_rn(color.z, __fmul_rn(wgt, __fmul_rn(sh[g].rgb[2], alpha)));
+            color.x = __fadd_rn(color.x, __fmul_rn(wgt, __fmul_rn(sh.rgb[g][0], alpha)));
+            color.y = __fadd_rn(color.y, __fmul_rn(wgt, __fmul_rn(sh.rgb[g][1], alpha)));
+            color.z = __fadd_rn(color.z, __fmul_rn(wgt, __fmul_rn(sh.rgb[g][2], alpha)));
             color.w = __fadd_rn(color.w, __fmul_rn(wgt, alpha));
             if (color.w > 0.99f) { st = make_float2(round_half(sg), 1.0f); done = true; }   // :448-452
           }
@@ -284,15 +338,15 @@ __global__ void __launch_bounds__(GT_THREADS) crtgt_kernel(const __grid_constant
       }
       __syncthreads();
     }
-    if (threadIdx.x == 0) {
+    if (tid == 0) {
       a.frame[o] = make_uint2(pack_half2(color.x, color.y), pack_half2(color.z, color.w));
       a.state[o] = __floats2half2_rn(st.x, st.y);
       if (st.y < 0.5f) left++;
     }
   }
-  if (threadIdx.x == 0 && left) atomicAdd(a.unfinished, left);
+  if (tid == 0 && left) atomicAdd(a.unfinished, left);
   if (COUNT) {
-    if (threadIdx.x == 0 && n) atomicAdd(a.count, (unsigned long long)n);
+    if (tid == 0 && n) atomicAdd(a.count, (unsigned long long)n);
     if (a.sec_count) {
       for (int o = 16; o > 0; o >>= 1) nsec += __shfl_xor_sync(0xffffffffu, nsec, o);
       if (lane == 0 && nsec) atomicAdd(a.sec_count, (unsigned long long)nsec);
@@ -381,7 +435,7 @@ class CrtgtRenderer : public RendererImpl {
 
   // crtgtrenderer.cpp:125-179: the two RGB16F kernel textures (values rounded to half here, as SetData(GL_RGB16F) does)
   int set_kernels(const float* occ, int n_occ, const float* sdw, int n_sdw) {
-    VRB_REQUIRE(occ && sdw && n_occ >= 1 && n_sdw >= 1 && n_occ <= 65536 && n_sdw <= 65536, VRB_ERR_INVALID, "vrb_crtgt_set_kernels: %d / %d rays", n_occ, n_sdw);
+    VRB_REQUIRE(occ && sdw && n_occ >= 1 && n_sdw >= 1 && n_occ + n_sdw <= GT_POOL, VRB_ERR_INVALID, "vrb_crtgt_set_kernels: %d + %d rays (at most %d together)", n_occ, n_sdw, GT_POOL);
     VRB_CUDA(cudaStreamSynchronize(ctx->stream));
     if (d_occ_) cudaFree(d_occ_);
     if (d_sdw_) cudaFree(d_sdw_);
@@ -463,11 +517,19 @@ class CrtgtRenderer : public RendererImpl {
     a.queue = d_queue;
     VRB_CUDA(cudaMemsetAsync(d_queue, 0, 2 * sizeof(unsigned), s));
     const int items = ((width + 7) / 8) * ((height + 3) / 4) * 32;
+    const int rays = (prm_.apply_occlusion ? n_occ_ : 0) + (prm_.apply_shadows ? n_sdw_ : 0);
+    const int pool = gt_group(rays) * rays;                          // rays of a full group of visible samples
+    int warps = pool >= 512 ? 8 : (pool >= 192 ? 4 : (pool >= 64 ? 2 : 1));
+    if (const char* e = getenv("VRB_GT_WARPS")) { const int w = atoi(e); if (w == 1 || w == 2 || w == 4 || w == 8) warps = w; }   // measurement override
     int per_sm = 0;
-    if (prm_.count_samples) VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, crtgt_kernel<true>, GT_THREADS, 0));
-    else VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, crtgt_kernel<false>, GT_THREADS, 0));
-    const int grid = std::min(std::max(per_sm, 1) * ctx->sm_count, items);
-    if (prm_.count_samples) crtgt_kernel<true><<<grid, GT_THREADS, 0, s>>>(a); else crtgt_kernel<false><<<grid, GT_THREADS, 0, s>>>(a);
+#define GT_LAUNCH(C, W)                                                                                          \
+  do {                                                                                                           \
+    VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, crtgt_kernel<C, W>, 32 * W, 0));             \
+    crtgt_kernel<C, W><<<std::min(std::max(per_sm, 1) * ctx->sm_count, items), 32 * W, 0, s>>>(a);               \
+  } while (0)
+    if (prm_.count_samples) { if (warps == 8) GT_LAUNCH(true, 8); else if (warps == 4) GT_LAUNCH(true, 4); else if (warps == 2) GT_LAUNCH(true, 2); else GT_LAUNCH(true, 1); }
+    else { if (warps == 8) GT_LAUNCH(false, 8); else if (warps == 4) GT_LAUNCH(false, 4); else if (warps == 2) GT_LAUNCH(false, 2); else GT_LAUNCH(false, 1); }
+#undef GT_LAUNCH
     VRB_CUDA(cudaMemsetAsync(d_queue, 0, 2 * sizeof(unsigned), s));                // the queue words are zero between launches
     VRB_CUDA(cudaGetLastError());
     return VRB_OK;
