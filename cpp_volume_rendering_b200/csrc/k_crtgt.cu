@@ -58,7 +58,7 @@ __device__ __forceinline__ float4 gt_classify(const GtArgs& a, f3 tx) {
 // (the positions along a ray do not depend on the transparency accumulated so far), the filter + transfer-function lookup
 // run when the step is consumed.  A fetch issued for a step the ray never reaches (early out at 1 - T > 0.99) is harmless.
 #ifndef VRB_GT_AHEAD
-#define VRB_GT_AHEAD 4
+#define VRB_GT_AHEAD 2                  // measured with VRB_GT_RESIDENT (24 rays): 2/768 10.9 ms, 3/768 11.1, 4/768 11.7, 4/512 11.7, 2/1024 11.4, 4/1024 14.2
 #endif
 constexpr int GT_AHEAD = VRB_GT_AHEAD;
 struct GtFetch { uint2 q0, q1; float ax, ay, az; };
@@ -129,8 +129,11 @@ struct GtGroup {
 // that ends the ray are thrown away.
 // WARPS: lanes for the pool — few rays per group leave most of a big CTA idle while each pixel still waits out its longest ray,
 // so the host picks the CTA size from the pool size and small CTAs put more pixels in flight.
+#ifndef VRB_GT_RESIDENT
+#define VRB_GT_RESIDENT 768               // threads per SM the register allocation leaves room for
+#endif
 template <bool COUNT, int WARPS>
-__global__ void __launch_bounds__(32 * WARPS) crtgt_kernel(const __grid_constant__ GtArgs a) {
+__global__ void __launch_bounds__(32 * WARPS, VRB_GT_RESIDENT / (32 * WARPS)) crtgt_kernel(const __grid_constant__ GtArgs a) {
   __shared__ GtGroup sh;
   __shared__ int sh_item;
   const int lane = threadIdx.x & 31, tid = threadIdx.x;

@@ -185,3 +185,27 @@ def test_ground_truth_plugin_session(tmp_path, ctx, bonsai_table):
         assert not np.array_equal(plain, one)
     finally:
         hostapi.session_ground_truth(-1)
+
+
+def test_ground_truth_with_multiscaling(ctx, bonsai_table):
+    """vr_pixel_multiscaling_support of the ground-truth renderer (crtgtrenderer.cpp:53-55): the state image follows the scaled
+    render size and the converged frame goes through the filter pass."""
+    occ = _cone_kernel(3, 60.0, 5); sdw = _cone_kernel(2, 5.0, 6)
+    r, prm, vox, cam, light, w, h = _setup(ctx, bonsai_table, n=24, size=(32, 24), show_frame_texture=1, apply_occlusion=1, apply_shadows=1,
+                                           samples_per_redraw=200)
+    try:
+        r.crtgt_set_kernels(occ, sdw)
+        r.set_multiscaling(2, 1)
+        assert r.render_size() == (64, 48)
+        r.redraw(2)
+        st, left = r.crtgt_read_state()
+        assert st.shape == (48, 64, 2) and left == 0
+        gen = r.read_frame(_capi.VRB_FRAME_RGBA16F | _capi.VRB_FRAME_GENERATED)
+        got = r.read_frame(_capi.VRB_FRAME_RGBA16F)
+    finally:
+        r.close()
+    ref = O.frame_multiscale(2, 1, gen.astype(np.float32), (w, h)).astype(np.float16)
+    assert got.shape == (h, w, 4) and np.array_equal(got.view(np.uint16), ref.view(np.uint16))
+    p = O.crtgt_params(inputs.make_camera((24, 24, 48.0), (0, 0, 0), (0, 1, 0), 45.0, 64, 48), 64, 48, vox.shape, prm, light)
+    full, _, _ = O.crtgt_dispatch(p, O.volume_r16f(vox), O.tf_texture(bonsai_table), occ, sdw, None, None, 200)
+    assert float(np.abs(gen.astype(np.float32) - full).max()) * 255.0 <= 2.0
