@@ -124,6 +124,8 @@ SIGNATURES = {
     "vrb_frame_multiscale": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_int, C.c_int, _P, C.c_int, C.c_int]),
     "vrb_renderer_frame": (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "vrb_renderer_read_frame": (C.c_int, [_P, _P, C.c_int]),
+    "vrb_renderer_read_frame_async": (C.c_int, [_P, _P, C.c_int]),
+    "vrb_renderer_read_frame_wait": (C.c_int, [_P]),
     "vrb_renderer_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_double)]),
     "vrb_ebs_read_sat": (C.c_int, [_P, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_float)]),
     "vrb_dos_read_extcoef": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
@@ -302,6 +304,12 @@ class Renderer:
 
     def read_frame_into(self, host_ptr, fmt=VRB_FRAME_RGBA16F):
         _check(lib().vrb_renderer_read_frame(self._h, _P(host_ptr), fmt))
+
+    def read_frame_async(self, host_ptr, fmt=VRB_FRAME_RGBA16F):
+        _check(lib().vrb_renderer_read_frame_async(self._h, _P(host_ptr), fmt))
+
+    def read_frame_wait(self):
+        _check(lib().vrb_renderer_read_frame_wait(self._h))
 
     def counters(self):
         s, ms = C.c_uint64(), C.c_double()

@@ -171,6 +171,12 @@ struct RendererImpl {
   int ms_mode = 0, ms_kernel = 1;         // m_kernel_filter(K2_HAT), renderoutputframe.cpp:34
   int screen_w = 0, screen_h = 0;        // size given to Init / Reshape
   __half* filtered = nullptr;
+  // vrb_renderer_read_frame_async: the frame is copied (or converted) into one of two device staging buffers on the render stream,
+  // then to the host on a second stream, so the next redraw overlaps the transfer of this one
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_staged = nullptr, ev_copied[2] = {nullptr, nullptr};
+  void* rd_staging[2] = {nullptr, nullptr}; size_t rd_staging_cap[2] = {0, 0}; int rd_staging_idx = 0;
+  void free_async();
   bool show_filtered = false;            // the last redraw ran the filter pass: vrb_renderer_frame / read_frame return `filtered`
   int render_size(int sw, int sh, int* rw, int* rh) const;
   int alloc_filtered();

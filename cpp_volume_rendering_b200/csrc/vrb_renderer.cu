@@ -49,6 +49,15 @@ int RendererImpl::alloc_filtered() {
   return VRB_OK;
 }
 
+void RendererImpl::free_async() {
+  if (copy_stream) { cudaStreamSynchronize(copy_stream); cudaStreamDestroy(copy_stream); copy_stream = nullptr; }
+  if (ev_staged) { cudaEventDestroy(ev_staged); ev_staged = nullptr; }
+  for (int i = 0; i < 2; i++) {
+    if (ev_copied[i]) { cudaEventDestroy(ev_copied[i]); ev_copied[i] = nullptr; }
+    if (rd_staging[i]) { cudaFree(rd_staging[i]); rd_staging[i] = nullptr; rd_staging_cap[i] = 0; }
+  }
+}
+
 void RendererImpl::close_peers() {
   for (int i = 0; i < MAX_PEERS; i++) if (peer_opened[i]) { cudaIpcCloseMemHandle(peer_opened[i]); peer_opened[i] = nullptr; }
   n_peer_frames = 0; gather_mode = 0; gather_ranks = 1;
@@ -180,6 +189,7 @@ int vrb_renderer_destroy(vrb_renderer* r) {
   p->clean();
   p->free_frame();
   if (p->filtered) cudaFree(p->filtered);
+  p->free_async();
   if (p->d_samples) cudaFree(p->d_samples);
   if (p->d_done) cudaFree(p->d_done);
   if (p->d_lattice) cudaFree(p->d_lattice);
@@ -352,6 +362,52 @@ int vrb_renderer_read_frame(vrb_renderer* r, void* host, int format) {
   cudaFree(tmp);
   if (rc != VRB_OK) return rc;
   VRB_CUDA(e);
+  return VRB_OK;
+}
+
+// The asynchronous half of GetFrontBufferPixelData: the copy is ordered after the redraws issued so far and runs on its own
+// stream; the host buffer (pinned, for a copy that really overlaps) is valid after vrb_renderer_read_frame_wait.
+int vrb_renderer_read_frame_async(vrb_renderer* r, void* host, int format) {
+  VRB_REQUIRE(r && host, VRB_ERR_INVALID, "vrb_renderer_read_frame_async: null argument");
+  RendererImpl* p = r->impl;
+  VRB_REQUIRE(p->frame, VRB_ERR_INVALID, "vrb_renderer_read_frame_async before Init");
+  const bool gen = (format & VRB_FRAME_GENERATED) != 0 || !p->show_filtered;
+  format &= ~VRB_FRAME_GENERATED;
+  VRB_REQUIRE(format == VRB_FRAME_RGBA16F || format == VRB_FRAME_RGB8_OVER_WHITE || format == VRB_FRAME_RGBA32F, VRB_ERR_INVALID,
+              "vrb_renderer_read_frame_async: bad format %d", format);
+  const __half* src = gen ? p->frame : p->filtered;
+  const int64_t n = gen ? (int64_t)p->width * p->height : (int64_t)p->screen_w * p->screen_h;
+  const size_t bytes = (size_t)n * (format == VRB_FRAME_RGBA16F ? 8 : (format == VRB_FRAME_RGB8_OVER_WHITE ? 3 : 16));
+  cudaStream_t s = p->ctx->stream;
+  if (!p->copy_stream) {
+    VRB_CUDA(cudaStreamCreateWithFlags(&p->copy_stream, cudaStreamNonBlocking));
+    VRB_CUDA(cudaEventCreateWithFlags(&p->ev_staged, cudaEventDisableTiming));
+    for (int i = 0; i < 2; i++) VRB_CUDA(cudaEventCreateWithFlags(&p->ev_copied[i], cudaEventDisableTiming));
+  }
+  const int i = p->rd_staging_idx ^= 1;
+  if (p->rd_staging_cap[i] < bytes) {
+    VRB_CUDA(cudaStreamSynchronize(p->copy_stream));
+    if (p->rd_staging[i]) cudaFree(p->rd_staging[i]);
+    p->rd_staging[i] = nullptr; p->rd_staging_cap[i] = 0;
+    VRB_CUDA(cudaMalloc(&p->rd_staging[i], bytes));
+    p->rd_staging_cap[i] = bytes;
+  }
+  VRB_CUDA(cudaStreamWaitEvent(s, p->ev_copied[i], 0));        // the transfer that last read this staging buffer
+  int rc = VRB_OK;
+  if (format == VRB_FRAME_RGBA16F) VRB_CUDA(cudaMemcpyAsync(p->rd_staging[i], src, bytes, cudaMemcpyDeviceToDevice, s));
+  else if (format == VRB_FRAME_RGB8_OVER_WHITE) rc = frame_to_rgb8_over_white(s, src, n, (uint8_t*)p->rd_staging[i]);
+  else rc = frame_to_rgba32f(s, src, n, (float*)p->rd_staging[i]);
+  if (rc != VRB_OK) return rc;
+  VRB_CUDA(cudaEventRecord(p->ev_staged, s));
+  VRB_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_staged, 0));
+  VRB_CUDA(cudaMemcpyAsync(host, p->rd_staging[i], bytes, cudaMemcpyDeviceToHost, p->copy_stream));
+  VRB_CUDA(cudaEventRecord(p->ev_copied[i], p->copy_stream));
+  return VRB_OK;
+}
+
+int vrb_renderer_read_frame_wait(vrb_renderer* r) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_read_frame_wait: null renderer");
+  if (r->impl->copy_stream) VRB_CUDA(cudaStreamSynchronize(r->impl->copy_stream));
   return VRB_OK;
 }
 

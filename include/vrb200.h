@@ -270,6 +270,11 @@ int vrb_renderer_frame(vrb_renderer* r, void** dev_rgba16f, int* width, int* hei
 /* Replaces the blit + glReadPixels of RenderingManager::GetFrontBufferPixelData
  * (renderingmanager.cpp:476-492).  Synchronises. host must hold W*H*{8,3,16} bytes. */
 int vrb_renderer_read_frame(vrb_renderer* r, void* host, int format);
+/* The same read split in two (glReadPixels into a pixel-pack buffer + a later map): _async orders a copy of the current frame after
+ * the redraws issued so far and returns; the transfer runs on a second stream from a staging copy, so the next redraw may start
+ * at once.  host (pinned memory for a transfer that overlaps) holds the frame after _wait, which waits for every _async so far. */
+int vrb_renderer_read_frame_async(vrb_renderer* r, void* host, int format);
+int vrb_renderer_read_frame_wait(vrb_renderer* r);
 /* samples: march-loop iterations of the last redraw (only if count_samples was set, else 0);
  * ms: device time of the last redraw measured with CUDA events on the context stream. */
 int vrb_renderer_counters(vrb_renderer* r, uint64_t* samples, double* ms);

@@ -332,3 +332,27 @@ def test_full_size_c2_parity(ctx, bonsai_table, skip):
         assert abs(samples - total) <= 2e-3 * total
     else:
         assert samples < total
+
+
+def test_async_frame_read_equals_blocking_read(ctx, bonsai_table):
+    """vrb_renderer_read_frame_async + _wait: same bytes as the blocking read, for every format, with a redraw issued while the
+    transfer of the previous frame is in flight (two staging buffers)."""
+    import torch
+    n, w, h = 48, 160, 96
+    vox = inputs.synth_volume(n, np.uint8)
+    ctx.upload_volume(vox); ctx.upload_tf(bonsai_table)
+    r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
+    try:
+        r.init(w, h)
+        cams = [inputs.make_camera((n * a, n, 2.0 * n), width=w, height=h) for a in (1.0, -0.5, 0.3)]
+        for fmt, dt, ch in [(_capi.VRB_FRAME_RGBA16F, torch.float16, 4), (_capi.VRB_FRAME_RGB8_OVER_WHITE, torch.uint8, 3), (_capi.VRB_FRAME_RGBA32F, torch.float32, 4)]:
+            bufs = [torch.empty((h, w, ch), dtype=dt).pin_memory() for _ in cams]
+            for cam, b in zip(cams, bufs):                 # three frames in flight, no wait in between
+                r.update(cam); r.redraw(); r.read_frame_async(b.data_ptr(), fmt)
+            r.read_frame_wait()
+            for cam, b in zip(cams, bufs):
+                r.update(cam); r.redraw()
+                assert np.array_equal(b.numpy().view(np.uint8), r.read_frame(fmt).view(np.uint8))
+            assert not np.array_equal(bufs[0].numpy().view(np.uint8), bufs[1].numpy().view(np.uint8))
+    finally:
+        r.close()
