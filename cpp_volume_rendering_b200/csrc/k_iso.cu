@@ -218,7 +218,10 @@ __device__ __forceinline__ void iso_block_bounds(const IsoArgs& a, const IsoRay&
 __device__ __forceinline__ float fsign(float x) { return x > 0.0f ? 1.0f : (x < 0.0f ? -1.0f : 0.0f); }
 
 template <int MODE, bool COUNT>
-__global__ void __launch_bounds__(ISO_THREADS, 6) iso_kernel(const __grid_constant__ IsoArgs a) {
+#ifndef VRB_ISO_MINB
+#define VRB_ISO_MINB 6
+#endif
+__global__ void __launch_bounds__(ISO_THREADS, VRB_ISO_MINB) iso_kernel(const __grid_constant__ IsoArgs a) {
   const int lane = threadIdx.x & 31;
   const int per_tile_x = a.tile / ISO_WARP_W, per_tile = per_tile_x * (a.tile / ISO_WARP_H);
   unsigned nit = 0;
