@@ -177,6 +177,7 @@ struct RendererImpl {
   cudaEvent_t ev_staged = nullptr, ev_copied[2] = {nullptr, nullptr};
   void* rd_staging[2] = {nullptr, nullptr}; size_t rd_staging_cap[2] = {0, 0}; int rd_staging_idx = 0;
   void free_async();
+  int pending_filter = 0;                // multi-rank: the filter pass of the last redraw waits for the peers' pixels (vrb_renderer_wait_peers)
   bool show_filtered = false;            // the last redraw ran the filter pass: vrb_renderer_frame / read_frame return `filtered`
   int render_size(int sw, int sh, int* rw, int* rh) const;
   int alloc_filtered();

@@ -240,9 +240,11 @@ int vrb_renderer_set_multiscaling(vrb_renderer* r, int mode, int kernel) {
   // vr_pixel_multiscaling_support: rc1prenderer.cpp:25, ebsrenderer.cpp:51, vctrenderer.cpp:52, dosrcrenderer.cpp:68, sbtmdosrenderer.cpp:46
   VRB_REQUIRE(mode == 0 || p->kind == VRB_RC1PASS || p->kind == VRB_EBS_SAT || p->kind == VRB_VCT || p->kind == VRB_DOS_CONE || p->kind == VRB_SBTM_DOS || p->kind == VRB_CRT_GT,
               VRB_ERR_UNSUPPORTED, "vrb_renderer_set_multiscaling: renderer kind %d has no pixel multiscaling", p->kind);
-  VRB_REQUIRE(mode == 0 || (p->gather_mode == VRB_GATHER_NONE && p->brick_ranks == 0 && p->n_ranks == 1), VRB_ERR_UNSUPPORTED,
-              "vrb_renderer_set_multiscaling: not with an image partition, peers or bricks (filter the gathered frame on one rank)");
+  VRB_REQUIRE(mode == 0 || p->brick_ranks == 0, VRB_ERR_UNSUPPORTED, "vrb_renderer_set_multiscaling: not with sort-last bricks");
   const bool resize = mode != p->ms_mode;
+  // the frame allocation changes size: peers hold handles of the old one
+  VRB_REQUIRE(!(resize && p->built && p->gather_mode != VRB_GATHER_NONE), VRB_ERR_INVALID,
+              "vrb_renderer_set_multiscaling: set the mode before vrb_renderer_frame_export / vrb_renderer_set_peers");
   p->ms_mode = mode; p->ms_kernel = kernel;
   if (!p->built || !resize) return VRB_OK;
   VRB_CUDA(cudaStreamSynchronize(p->ctx->stream));
@@ -312,11 +314,18 @@ int vrb_renderer_redraw(vrb_renderer* r, int mode) {
   int rc = p->redraw(mode);
   if (rc != VRB_OK) return rc;
   // DrawMultiSampleHigherResolutionMode / DrawHigherResolutionWithDownScale / DrawLowerResolutionWithUpScale (renderoutputframe.cpp:265-539)
-  p->show_filtered = mode != 0;
-  if (mode != 0) {
+  // With an image partition the filter needs the other ranks' pixels: it runs in vrb_renderer_wait_peers, on the ranks that
+  // collect the whole frame (every rank with VRB_GATHER_ALL, rank 0 with VRB_GATHER_ROOT).
+  const bool partitioned = p->n_ranks > 1;
+  VRB_REQUIRE(mode == 0 || !partitioned || p->gather_mode != VRB_GATHER_NONE, VRB_ERR_UNSUPPORTED,
+              "vrb_renderer_redraw: multiscaling mode %d over an image partition needs vrb_renderer_set_peers (the filter reads the whole frame)", mode);
+  const bool collects = !partitioned || p->gather_mode == VRB_GATHER_ALL || p->rank == 0;
+  p->show_filtered = mode != 0 && collects;
+  p->pending_filter = 0;
+  if (mode != 0 && !partitioned) {
     rc = frame_multiscale(s, mode, p->ms_kernel, p->frame, p->width, p->height, p->filtered, p->screen_w, p->screen_h);
     if (rc != VRB_OK) return rc;
-  }
+  } else if (mode != 0 && collects) p->pending_filter = mode;
   VRB_CUDA(cudaEventRecord(p->ev1, s));
   p->timed = true;
   return VRB_OK;
@@ -447,7 +456,6 @@ int vrb_renderer_set_peers(vrb_renderer* r, const void* handles, int n_ranks, in
   VRB_CUDA(cudaStreamSynchronize(p->ctx->stream));
   p->close_peers();
   if (mode == VRB_GATHER_NONE || n_ranks <= 1) return VRB_OK;
-  VRB_REQUIRE(p->ms_mode == 0, VRB_ERR_UNSUPPORTED, "vrb_renderer_set_peers: multiscaling mode %d is set", p->ms_mode);
   VRB_REQUIRE(handles && rank >= 0 && rank < n_ranks && n_ranks - 1 <= RendererImpl::MAX_PEERS, VRB_ERR_INVALID,
               "vrb_renderer_set_peers: bad rank %d of %d", rank, n_ranks);
   VRB_REQUIRE(mode == VRB_GATHER_ROOT || mode == VRB_GATHER_ALL, VRB_ERR_INVALID, "vrb_renderer_set_peers: bad mode %d", mode);
@@ -531,12 +539,17 @@ int vrb_renderer_wait_peers(vrb_renderer* r) {
     const unsigned want = p->frame_seq * (unsigned)(p->gather_ranks - 1);
     const int rc = wait(p->ctx->stream, (unsigned long long)(uintptr_t)(p->flags() + RendererImpl::FRAME_FLAGS - 1), want, 0x0u /* GEQ */);
     VRB_REQUIRE(rc == 0, VRB_ERR_CUDA, "cuStreamWaitValue32 failed: %d", rc);
-    return VRB_OK;
+  } else {
+    for (int q = 0; q < p->gather_ranks; q++) {
+      if (q == p->rank) continue;
+      const int rc = wait(p->ctx->stream, (unsigned long long)(uintptr_t)(p->flags() + q), p->frame_seq, 0x0u /* CU_STREAM_WAIT_VALUE_GEQ */);
+      VRB_REQUIRE(rc == 0, VRB_ERR_CUDA, "cuStreamWaitValue32 failed: %d", rc);
+    }
   }
-  for (int q = 0; q < p->gather_ranks; q++) {
-    if (q == p->rank) continue;
-    const int rc = wait(p->ctx->stream, (unsigned long long)(uintptr_t)(p->flags() + q), p->frame_seq, 0x0u /* CU_STREAM_WAIT_VALUE_GEQ */);
-    VRB_REQUIRE(rc == 0, VRB_ERR_CUDA, "cuStreamWaitValue32 failed: %d", rc);
+  if (p->pending_filter) {                      // the whole generated frame is here: RenderFrameToScreen's filter pass of this redraw
+    const int mode = p->pending_filter;
+    p->pending_filter = 0;
+    return frame_multiscale(p->ctx->stream, mode, p->ms_kernel, p->frame, p->width, p->height, p->filtered, p->screen_w, p->screen_h);
   }
   return VRB_OK;
 }
@@ -602,7 +615,6 @@ int vrb_renderer_set_partition(vrb_renderer* r, int rank, int n_ranks, int tile)
   VRB_REQUIRE(n_ranks >= 1 && rank >= 0 && rank < n_ranks, VRB_ERR_INVALID, "bad partition rank %d of %d", rank, n_ranks);
   VRB_REQUIRE(tile == 16 || tile == 32 || tile == 64 || tile == 128, VRB_ERR_INVALID, "partition tile must be 16, 32, 64 or 128");
   RendererImpl* p = r->impl;
-  VRB_REQUIRE(n_ranks == 1 || p->ms_mode == 0, VRB_ERR_UNSUPPORTED, "vrb_renderer_set_partition: multiscaling mode %d is set", p->ms_mode);
   p->rank = rank; p->n_ranks = n_ranks; p->part_tile = tile;
   if (p->frame) {  // tiles owned by other ranks must read 0
     VRB_CUDA(cudaMemsetAsync(p->frame_base, 0, 2 * p->frame_bytes, p->ctx->stream));

@@ -256,7 +256,9 @@ int vrb_renderer_redraw(vrb_renderer* r, int multiscaling_mode);
 /* Replaces SetCurrentMultiScalingMode (volrenderbase.h:71) + RenderFrameToScreen::SetImageFilterKernel (renderoutputframe.cpp:541-546)
  * + the Reshape that follows (volrenderbase.cpp:48-75): the renderer draws at screen * 2 (modes 1, 2) or screen / 2 (mode 3); a
  * redraw in that mode filters the generated frame to the size given to Init / Reshape.  Renderers with
- * vr_pixel_multiscaling_support only (1-pass, EBS, VCT, DOS, SBTM); not with a partition, peers or bricks. */
+ * vr_pixel_multiscaling_support only (1-pass, EBS, VCT, DOS, SBTM, ground truth).  Over an image partition (set the mode before the
+ * frame export): the ranks exchange the generated frame and the filter pass runs in vrb_renderer_wait_peers on the ranks that
+ * collect it.  Not with sort-last bricks. */
 int vrb_renderer_set_multiscaling(vrb_renderer* r, int mode, int image_filter_kernel);
 /* Replaces RenderFrameToScreen::GetWidth / GetHeight (renderoutputframe.cpp:148-158): the size the renderer draws at. */
 int vrb_renderer_render_size(vrb_renderer* r, int* width, int* height);

@@ -123,12 +123,10 @@ def test_multiscaling_errors(ctx, bonsai_table):
         r.set_multiscaling(2, 1)
         with pytest.raises(_capi.VrbError):
             r.redraw(3)                               # another mode than the one set
-        with pytest.raises(_capi.VrbError):
-            r.set_partition(0, 2, 32)                 # the filter pass needs the whole frame on one rank
-        r.set_multiscaling(0, 1)
         r.set_partition(0, 2, 32)
         with pytest.raises(_capi.VrbError):
-            r.set_multiscaling(1, 1)
+            r.redraw(2)                               # a partition without peers: no rank holds the frame the filter reads
+        r.redraw(0)
     finally:
         r.close()
     iso = _renderer(ctx, _capi.VRB_ISO_ADAPT, 32, 32, 32)   # vr_pixel_multiscaling_support stays false for the iso renderers

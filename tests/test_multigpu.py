@@ -195,3 +195,70 @@ def test_sort_last_two_ranks_one_gpu(ctx, bonsai_table):
                 p.kill()
     assert np.array_equal(res[0], local) and np.array_equal(res[1], local)
     assert np.abs(local - plain).max() <= 2.0 ** -9 and (local[..., 3] > 0).mean() > 0.05
+
+
+def _ms_worker(rank, world, port, mode, kernel, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from cpp_volume_rendering_b200 import _capi, inputs, multigpu
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    n, w, h = 48, 96, 64
+    vox = inputs.synth_volume(n, np.uint8)
+    table = inputs.tf_build_linear(inputs.bonsai_tf())
+    cam = inputs.default_camera(n, w, h)
+    with _capi.Context(0) as ctx:
+        ctx.upload_volume(vox); ctx.upload_tf(table)
+        r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
+        r.set_multiscaling(mode, kernel)             # before the frames are exported: they take the scaled size
+        r.init(w, h)
+        multigpu.setup_fused_gather(r, rank, world, tile=16, mode=_capi.VRB_GATHER_ALL)
+        r.update(cam)
+        for _ in range(2):
+            r.redraw(mode)
+            ctx.synchronize()
+            dist.barrier()
+            r.wait_peers()                           # the waits find their flags raised; the filter pass runs behind them
+        out = r.read_frame(_capi.VRB_FRAME_RGBA16F)
+        gen = r.read_frame(_capi.VRB_FRAME_RGBA16F | _capi.VRB_FRAME_GENERATED)
+        dist.barrier()
+        r.set_peers([], rank, _capi.VRB_GATHER_NONE)
+        dist.barrier()
+        r.close()
+    q.put((rank, (out, gen)))
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode,kernel", [(2, 3), (1, 1)])
+def test_multiscaling_over_an_image_partition(ctx, bonsai_table, mode, kernel):
+    """DownScalingRedraw / MultiSampleRedraw with the generated frame split over two ranks: every rank ends up with the filtered
+    frame of the single-rank renderer, bit for bit."""
+    import torch.multiprocessing as mp
+    from cpp_volume_rendering_b200 import _capi, inputs
+    n, w, h = 48, 96, 64
+    vox = inputs.synth_volume(n, np.uint8)
+    ctx.upload_volume(vox); ctx.upload_tf(bonsai_table)
+    r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
+    r.set_multiscaling(mode, kernel); r.init(w, h); r.update(inputs.default_camera(n, w, h)); r.redraw(mode)
+    full = r.read_frame(_capi.VRB_FRAME_RGBA16F); full_gen = r.read_frame(_capi.VRB_FRAME_RGBA16F | _capi.VRB_FRAME_GENERATED)
+    r.close()
+    mpc = mp.get_context("spawn")
+    q = mpc.Queue()
+    port = _free_port()
+    procs = [mpc.Process(target=_ms_worker, args=(rk, 2, port, mode, kernel, q)) for rk in range(2)]
+    for p in procs:
+        p.start()
+    try:
+        res = dict(q.get(timeout=150) for _ in range(2))
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+    finally:
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+    assert full.shape == (h, w, 4) and (full[..., 3] > 0).mean() > 0.05
+    for rk in range(2):
+        out, gen = res[rk]
+        assert np.array_equal(gen.view(np.uint16), full_gen.view(np.uint16))
+        assert np.array_equal(out.view(np.uint16), full.view(np.uint16))
