@@ -76,7 +76,8 @@ __device__ __forceinline__ GtFetch gt_issue(const GtArgs& a, f3 tx) {
   return f;
 }
 // the rest of tex3d_f32_exact (vrb_ray.cuh) + the alpha channel of the transfer-function lookup of gt_classify
-__device__ __forceinline__ float gt_sigma(const GtArgs& a, const GtFetch& f) {
+constexpr int GT_TF_SMEM = 512;            // transfer functions up to this many entries keep {alpha[i], alpha[i + 1] - alpha[i]} in shared memory
+__device__ __forceinline__ float gt_sigma(const GtArgs& a, const GtFetch& f, const float2* s_tfa) {
   const float2 a0 = __half22float2(*reinterpret_cast<const __half2*>(&f.q0.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&f.q0.y));
   const float2 a1 = __half22float2(*reinterpret_cast<const __half2*>(&f.q1.x)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&f.q1.y));
   const float c00 = __fadd_rn(a0.x, __fmul_rn(f.ax, __fsub_rn(a0.y, a0.x))), c10 = __fadd_rn(b0.x, __fmul_rn(f.ax, __fsub_rn(b0.y, b0.x)));
@@ -86,13 +87,14 @@ __device__ __forceinline__ float gt_sigma(const GtArgs& a, const GtFetch& f) {
   const float u = fminf(fmaxf(fmaf(density, (float)a.tf_n, -0.5f), 0.0f), (float)(a.tf_n - 1));
   const int j = (int)u;
   const float w = u - (float)j;
+  if (a.tf_n <= GT_TF_SMEM) { const float2 e = s_tfa[j]; return fmaf(w, e.y, e.x); }
   const uint2 e0 = __ldg(a.tf_lin + j), e1 = __ldg(a.tf_lin + min(j + 1, a.tf_n - 1));
   const float t0 = __half2float(__ushort_as_half((unsigned short)(e0.y >> 16))), t1 = __half2float(__ushort_as_half((unsigned short)(e1.y >> 16)));
   return fmaf(w, t1 - t0, t0);
 }
 
 constexpr int GT_GROUP = 32;            // dispatches shaded together (at most; fewer when a sample has many rays)
-constexpr int GT_POOL = 2048;           // secondary rays of one group (shared-memory results)
+constexpr int GT_POOL = 1024;           // secondary rays of one group (shared-memory results)
 
 // dispatches per group: about three rays per lane of the largest CTA in the pool (more only adds samples shaded past the end of
 // the ray), never more rays than the pool holds
@@ -136,6 +138,14 @@ template <bool COUNT, int WARPS>
 __global__ void __launch_bounds__(32 * WARPS, VRB_GT_RESIDENT / (32 * WARPS)) crtgt_kernel(const __grid_constant__ GtArgs a) {
   __shared__ GtGroup sh;
   __shared__ int sh_item;
+  __shared__ float2 s_tfa[GT_TF_SMEM];
+  if (a.tf_n <= GT_TF_SMEM) {
+    for (int i = threadIdx.x; i < a.tf_n; i += 32 * WARPS) {
+      const uint2 e0 = a.tf_lin[i], e1 = a.tf_lin[min(i + 1, a.tf_n - 1)];
+      const float t0 = __half2float(__ushort_as_half((unsigned short)(e0.y >> 16))), t1 = __half2float(__ushort_as_half((unsigned short)(e1.y >> 16)));
+      s_tfa[i] = make_float2(t0, t1 - t0);
+    }
+  }
   const int lane = threadIdx.x & 31, tid = threadIdx.x;
   const int tiles_x = (a.width + 7) / 8, n_items = tiles_x * ((a.height + 3) / 4) * 32;
   const int n_occ = a.apply_occlusion ? a.n_occ : 0, n_sdw = a.apply_shadow ? a.n_sdw : 0, rays = n_occ + n_sdw;
@@ -255,7 +265,7 @@ __global__ void __launch_bounds__(32 * WARPS, VRB_GT_RESIDENT / (32 * WARPS)) cr
             tx_pos = mk3(sh.tx[g][0], sh.tx[g][1], sh.tx[g][2]);
             dist = is_occ ? a.occ_dist : a.sdw_dist;
             Vt = 1.0f;
-            st0 = gt_sigma(a, gt_issue(a, add3(tx_pos, scale3(rdir, a.gap))));
+            st0 = gt_sigma(a, gt_issue(a, add3(tx_pos, scale3(rdir, a.gap))), s_tfa);
             nsec++;
             s_next = a.gap; open = true;
 #pragma unroll
@@ -267,7 +277,7 @@ __global__ void __launch_bounds__(32 * WARPS, VRB_GT_RESIDENT / (32 * WARPS)) cr
             if (active) {
               bool ended = !vv[j];
               if (!ended) {
-                const float st1 = gt_sigma(a, f[j]);
+                const float st1 = gt_sigma(a, f[j], s_tfa);
                 nsec++;
                 Vt = __fmul_rn(Vt, __expf(__fmul_rn(-__fmul_rn(__fadd_rn(st0, st1), 0.5f), hh[j])));
                 ended = __fsub_rn(1.0f, Vt) > 0.99f;
