@@ -232,7 +232,7 @@ __global__ void __launch_bounds__(32 * WARPS, VRB_GT_RESIDENT / (32 * WARPS)) cr
       {
         const int total = sh.n_vis * rays;
         bool active = false, out_of_work = total == 0;
-        int q = 0;
+        int q = 0, slot = 0;
         f3 tx_pos = mk3(0.f, 0.f, 0.f), rdir = mk3(0.f, 0.f, 0.f);
         float dist = 0.f, wgt = 0.f, Vt = 1.f, st0 = 0.f, s_next = 0.f;
         bool open = false;
@@ -253,12 +253,15 @@ __global__ void __launch_bounds__(32 * WARPS, VRB_GT_RESIDENT / (32 * WARPS)) cr
           if (!active) {
             q = atomicAdd(&sh.next, 1);
             if (q >= total) { out_of_work = true; break; }
-            const int g = sh.vis[q / rays], r = q % rays;
+            // ray-major order: neighbouring lanes take the SAME ray of consecutive samples — parallel paths half a voxel apart,
+            // the same texels and nearly the same length
+            const int r = q / sh.n_vis, v = q % sh.n_vis, g = sh.vis[v];
+            slot = v * rays + r;
             const bool is_occ = r < n_occ;
             f3 bd, bu, br;
             if (is_occ) { bd = occ_d; bu = v_up; br = v_right; }
             else { bd = mk3(sh.sd[g][0], sh.sd[g][1], sh.sd[g][2]); bu = mk3(sh.su[g][0], sh.su[g][1], sh.su[g][2]); br = mk3(sh.sr[g][0], sh.sr[g][1], sh.sr[g][2]); }
-            if (!is_occ && sh.state[g] == 3) { sh.vw[q] = 0.0f; sh.w[q] = 0.0f; continue; }   // spot light outside its cone: no rays
+            if (!is_occ && sh.state[g] == 3) { sh.vw[slot] = 0.0f; sh.w[slot] = 0.0f; continue; }   // spot light outside its cone: no rays
             const float* kv = is_occ ? a.occ + 3 * r : a.sdw + 3 * (r - n_occ);
             rdir = normalize_rn(add3(add3(scale3(br, __ldg(kv)), scale3(bu, __ldg(kv + 1))), scale3(bd, __ldg(kv + 2))));
             wgt = dot_rn(bd, rdir);
@@ -284,7 +287,7 @@ __global__ void __launch_bounds__(32 * WARPS, VRB_GT_RESIDENT / (32 * WARPS)) cr
                 st0 = st1;
                 if (!ended) setup(j);
               }
-              if (ended) { sh.vw[q] = __fmul_rn(Vt, wgt); sh.w[q] = wgt; active = false; }
+              if (ended) { sh.vw[slot] = __fmul_rn(Vt, wgt); sh.w[slot] = wgt; active = false; }
             }
           }
         }
