@@ -535,8 +535,8 @@ class CrtgtRenderer : public RendererImpl {
     const int items = ((width + 7) / 8) * ((height + 3) / 4) * 32;
     const int rays = (prm_.apply_occlusion ? n_occ_ : 0) + (prm_.apply_shadows ? n_sdw_ : 0);
     const int pool = gt_group(rays) * rays;                          // rays of a full group of visible samples
-    // measured (tools/bench_crtgt.py, 6 / 24 / 64 rays): 64-thread CTAs 3.8 / 11.7 / 23.2 ms, 128: 5.6 / 11.8 / 22.0, 256: 10.2 / 14.9 / 24.7, 32: 5.0 / 18.3 / 38.0
-    int warps = pool >= 1024 ? 4 : (pool >= 48 ? 2 : 1);
+    // measured (tools/bench_crtgt.py, 24 / 64 rays, ray-major pool): 32-thread CTAs 11.8 / 26.5 ms, 64: 7.6 / 16.6, 128: 7.8 / 15.2, 256: 10.3 / 17.3
+    int warps = rays >= 48 ? 4 : (pool >= 48 ? 2 : 1);
     if (const char* e = getenv("VRB_GT_WARPS")) { const int w = atoi(e); if (w == 1 || w == 2 || w == 4 || w == 8) warps = w; }   // measurement override
     int per_sm = 0;
 #define GT_LAUNCH(C, W)                                                                                          \
