@@ -43,6 +43,22 @@ def workload_name(skip):
     return f"rc1pass_{VOL_N}c_u16_{IMG_W}x{IMG_H}_step{STEP}_{s}"
 
 
+def workload_config():
+    """The keys both arms print under `config`: the workload only, nothing measured and nothing arm-specific."""
+    return {"workload": workload_name(0), "volume": f"{VOL_N}^3 u16 -> R16F texture", "image": f"{IMG_W}x{IMG_H}",
+            "step_voxels": STEP, "tf": "bonsai_01.tf1d", "camera": "Initial State (N,N,2N)",
+            "l2_policy": "inputs_larger_than_l2 (256 MiB R16F volume vs 126 MB L2)"}
+
+
+def host_threads():
+    """Host cores this process may use.  torch.distributed.run exports OMP_NUM_THREADS=1 to its workers: the CPU arm
+    asks the oracle for this count explicitly so that it is the same at every N."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def make_inputs(n=VOL_N, w=IMG_W, h=IMG_H):
     from cpp_volume_rendering_b200 import inputs
     vox = inputs.synth_volume(n, np.uint16)
@@ -103,15 +119,16 @@ def cpu_frame(vox, table, cam, skip_rows=None, repeats=1):
     vol = O.volume_r16f(vox)
     rgbt = O.tf_texture(table)
     rows = skip_rows or (0, IMG_H, 1)
-    p = O.rc1pass_params(cam, IMG_W, IMG_H, vox.shape, STEP, rows=rows)
-    O.rc1pass_render(O.rc1pass_params(cam, IMG_W, IMG_H, vox.shape, STEP, rows=(0, IMG_H, 64)), vol, rgbt)  # warm-up
+    nt = host_threads()
+    p = O.rc1pass_params(cam, IMG_W, IMG_H, vox.shape, STEP, rows=rows, threads=nt)
+    O.rc1pass_render(O.rc1pass_params(cam, IMG_W, IMG_H, vox.shape, STEP, rows=(0, IMG_H, 64), threads=nt), vol, rgbt)  # warm-up
     best, total = None, 0
     for _ in range(repeats):
         t0 = time.perf_counter()
         _, total, _ = O.rc1pass_render(p, vol, rgbt)
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
-    return total / best, O.max_threads(), total, best
+    return total / best, nt, total, best
 
 
 def ncu_traffic():
@@ -179,9 +196,10 @@ def run_reference(args):
     vox, table, cam, _ = make_inputs()
     vol = O.volume_r16f(vox)
     rgbt = O.tf_texture(table)
-    p = O.rc1pass_params(cam, IMG_W, IMG_H, vox.shape, STEP)
+    cores = host_threads()          # explicit: under torch.distributed.run OMP_NUM_THREADS is 1
+    p = O.rc1pass_params(cam, IMG_W, IMG_H, vox.shape, STEP, threads=cores)
     for _ in range(max(args.warmup, 1)):
-        O.rc1pass_render(O.rc1pass_params(cam, IMG_W, IMG_H, vox.shape, STEP, rows=(0, IMG_H, 16)), vol, rgbt)
+        O.rc1pass_render(O.rc1pass_params(cam, IMG_W, IMG_H, vox.shape, STEP, rows=(0, IMG_H, 16), threads=cores), vol, rgbt)
     times, total = [], 0
     for _ in range(args.steps):
         t0 = time.perf_counter()
@@ -189,11 +207,12 @@ def run_reference(args):
         times.append(time.perf_counter() - t0)
     ms = 1e3 * sum(times) / len(times)
     val = total / (ms * 1e-3)
-    cores = O.max_threads()
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(0), "samples_per_frame": total, "fps": 1e3 / ms},
+            "config": workload_config(),
+            "measured": {"samples_per_frame": total, "fps": 1e3 / ms,
+                         "ms_per_step_min_median_max": [1e3 * min(times), 1e3 * float(np.median(times)), 1e3 * max(times)]},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": "full 1024x1024 frame per step, OpenMP over rows, oracle/liboracle.so"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -276,14 +295,17 @@ def run_cuda(args):
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # one event per step boundary: the K steps are timed as one region (first to last event), the per-step spread comes
+    # from the events in between
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     kernel_ms = []
-    e0.record(stream)
-    for _ in range(args.steps):
+    evs[0].record(stream)
+    for i in range(args.steps):
         step()
-    e1.record(stream)
+        evs[i + 1].record(stream)
     barrier()
-    total_ms = e0.elapsed_time(e1)
+    total_ms = evs[0].elapsed_time(evs[-1])
+    per_step = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
     clk = clocks.stop() if rank == 0 else None
     t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -300,7 +322,7 @@ def run_cuda(args):
     # fewer fetches — reported beside the headline, which keeps every lattice sample
     skip_info = {}
     if not args.skip:
-        for blk in (8,):
+        for blk in (4, 8, 16, 32):
             prm.skip_block = blk
             r.set_params(prm)
             for _ in range(3):
@@ -359,7 +381,7 @@ def run_cuda(args):
 
     if rank == 0:
         import ctypes
-        tex_peak = ctx.tex_peak() if world == 1 or True else None
+        tex_peak = ctx.tex_peak()
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -374,13 +396,13 @@ def run_cuda(args):
             "metric": METRIC, "value": fetched_total / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args.skip), "volume": f"{VOL_N}^3 u16 -> R16F texture", "image": f"{IMG_W}x{IMG_H}",
-                       "step_voxels": STEP, "tf": "bonsai_01.tf1d", "camera": "Initial State (N,N,2N)",
-                       "partition": f"image tiles {PART_TILE}x{PART_TILE} round-robin over {world} rank(s)" + (", fused peer-memory gather into every rank's frame + per-frame flag wait (no collective)" if world > 1 else ""),
-                       "l2_policy": "inputs_larger_than_l2 (256 MiB R16F volume vs 126 MB L2)",
-                       "e2e_path": "update + redraw + vrb_renderer_read_frame_async into pinned host memory every step; the transfer of frame k overlaps the render of frame k + 1",
-                       "samples_per_frame": fetched_total, "fps": 1e3 / ms_per_step, "init_ms_volume_upload": init_ms,
-                       "tf_in_smem": args.tf_smem, "exact_filter": args.exact, "skip_block": args.skip, "depth_split": depth_split, "with_skipping": skip_info},
+            "config": dict(workload_config(), workload=workload_name(args.skip)),
+            "setup": {"partition": f"image tiles {PART_TILE}x{PART_TILE} round-robin over {world} rank(s)" + (", fused peer-memory gather into every rank's frame + per-frame flag wait (no collective)" if world > 1 else ""),
+                      "e2e_path": "update + redraw + vrb_renderer_read_frame_async into pinned host memory every step; the transfer of frame k overlaps the render of frame k + 1",
+                      "init_ms_volume_upload": init_ms, "tf_in_smem": args.tf_smem, "exact_filter": args.exact, "skip_block": args.skip, "depth_split": depth_split},
+            "measured": {"samples_per_frame": fetched_total, "fps": 1e3 / ms_per_step,
+                         "ms_per_step_min_median_max": [float(min(per_step)), float(np.median(per_step)), float(max(per_step))],
+                         "with_skipping": skip_info},
             "e2e": {"value": fetched_total / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": ctypes.sizeof(_capi.Camera) + ctypes.sizeof(_capi.Light),
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "fps": 1e3 / e2e_ms},
             "gpu_launches": args.steps,

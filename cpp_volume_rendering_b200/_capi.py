@@ -39,7 +39,8 @@ class Light(C.Structure):
 
 class Rc1PassParams(C.Structure):
     _fields_ = [("step_size", C.c_float), ("apply_gradient_shading", C.c_int), ("skip_block", C.c_int),
-                ("count_samples", C.c_int), ("tf_in_smem", C.c_int), ("exact_filter", C.c_int), ("depth_split", C.c_int)]
+                ("count_samples", C.c_int), ("tf_in_smem", C.c_int), ("exact_filter", C.c_int), ("depth_split", C.c_int),
+                ("split_groups", C.c_int)]
 
 
 class IsoParams(C.Structure):

@@ -432,7 +432,7 @@ class CrtgtRenderer : public RendererImpl {
     if (d_unfinished_) cudaFree(d_unfinished_);
     if (d_unfinished_ll_) cudaFree(d_unfinished_ll_);
     d_unfinished_ll_ = nullptr;
-    d_state_ = nullptr; d_occ_ = d_sdw_ = nullptr; d_unfinished_ = nullptr; state_px_ = 0;
+    d_state_ = nullptr; d_occ_ = d_sdw_ = nullptr; d_unfinished_ = nullptr; state_px_ = 0; state_w_ = state_h_ = 0;
   }
 
   int set_params(const void* pod, size_t size) override {
@@ -489,7 +489,8 @@ class CrtgtRenderer : public RendererImpl {
                 "RC1PConeLightGroundTruthSteps: one GPU per frame (the per-pixel state is not partitioned)");
     int rc = ensure_quad(ctx);
     if (rc != VRB_OK) return rc;
-    if ((size_t)width * height != state_px_) { rc = alloc_state(); if (rc != VRB_OK) return rc; }
+    // keyed on (width, height), not on the pixel count: a reshape W x H -> H x W must not keep the per-pixel state of the old layout
+    if (width != state_w_ || height != state_h_) { rc = alloc_state(); if (rc != VRB_OK) return rc; }
     const Volume& v = ctx->vol;
     cudaStream_t s = ctx->stream;
     GtArgs a{};
@@ -556,14 +557,14 @@ class CrtgtRenderer : public RendererImpl {
   int alloc_state() {
     if (d_state_) cudaFree(d_state_);
     d_state_ = nullptr;
-    state_px_ = (size_t)width * height;
+    state_px_ = (size_t)width * height; state_w_ = width; state_h_ = height;
     VRB_CUDA(cudaMalloc(&d_state_, state_px_ * sizeof(__half2)));
     VRB_CUDA(cudaMemsetAsync(d_state_, 0, state_px_ * sizeof(__half2), ctx->stream));
     fresh_ = true;
     return VRB_OK;
   }
   vrb_crtgt_params prm_{};
-  __half2* d_state_ = nullptr; size_t state_px_ = 0;
+  __half2* d_state_ = nullptr; size_t state_px_ = 0; int state_w_ = 0, state_h_ = 0;
   float* d_occ_ = nullptr; float* d_sdw_ = nullptr; int n_occ_ = 0, n_sdw_ = 0;
   unsigned* d_unfinished_ = nullptr;
   unsigned long long* d_unfinished_ll_ = nullptr;   // scratch counter (primary samples while the public counter holds secondary fetches)

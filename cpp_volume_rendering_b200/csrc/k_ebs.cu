@@ -332,7 +332,7 @@ class EbsRenderer : public RendererImpl {
     a.n_tiles = a.tiles_x * ((height + part_tile - 1) / part_tile);
     const int my_tiles = (a.n_tiles - rank + n_ranks - 1) / n_ranks;
     a.n_items = my_tiles * (part_tile / 8) * (part_tile / 4);
-    if (a.n_items <= 0) return VRB_OK;
+    if (a.n_items <= 0 && n_peer_frames == 0) return VRB_OK;   // with peers the (empty) launch still raises this rank's flag
     unsigned sc = (unsigned)(a.n_items * 0.6180339887) | 1u;
     auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned t = x % y; x = y; y = t; } return x; };
     while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
@@ -348,7 +348,7 @@ class EbsRenderer : public RendererImpl {
     VRB_REQUIRE(smem <= 200 * 1024, VRB_ERR_UNSUPPORTED, "transfer function of %d entries does not fit shared memory", a.tf_n);
     cudaStream_t s = ctx->stream;
     if (prm_.count_samples) VRB_CUDA(cudaMemsetAsync(d_samples, 0, sizeof(unsigned long long), s));
-    const int max_ctas = (a.n_items + EBS_THREADS / 32 - 1) / (EBS_THREADS / 32);
+    const int max_ctas = std::max(1, (a.n_items + EBS_THREADS / 32 - 1) / (EBS_THREADS / 32));   // a rank without items still signals its peers
     int per_sm = 0;
     if (prm_.count_samples) {
       if (smem > 48 * 1024) VRB_CUDA(cudaFuncSetAttribute(ebs_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

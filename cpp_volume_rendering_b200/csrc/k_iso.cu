@@ -482,7 +482,7 @@ class IsoRenderer : public RendererImpl {
     a.n_tiles = a.tiles_x * ((height + part_tile - 1) / part_tile);
     const int my_tiles = (a.n_tiles - rank + n_ranks - 1) / n_ranks;
     a.n_items = my_tiles * (part_tile / ISO_WARP_W) * (part_tile / ISO_WARP_H);
-    if (a.n_items <= 0) return VRB_OK;
+    if (a.n_items <= 0 && n_peer_frames == 0) return VRB_OK;   // with peers the (empty) launch still raises this rank's flag
     unsigned sc = (unsigned)(a.n_items * 0.6180339887) | 1u;
     auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned t = x % y; x = y; y = t; } return x; };
     while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
@@ -494,7 +494,7 @@ class IsoRenderer : public RendererImpl {
     }
     a.queue = d_queue;
     fill_peer_signal(*this, a.sig);
-    const int max_ctas = (a.n_items + ISO_THREADS / 32 - 1) / (ISO_THREADS / 32);
+    const int max_ctas = std::max(1, (a.n_items + ISO_THREADS / 32 - 1) / (ISO_THREADS / 32));   // a rank without items still signals its peers
     cudaStream_t s = ctx->stream;
     if (prm_.count_iterations) VRB_CUDA(cudaMemsetAsync(d_samples, 0, sizeof(unsigned long long), s));
     int per_sm = 0;

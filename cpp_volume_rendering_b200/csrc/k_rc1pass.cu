@@ -643,7 +643,7 @@ class Rc1Pass : public RendererImpl {
   explicit Rc1Pass(vrb_ctx* c) : RendererImpl(c, VRB_RC1PASS) {
     prm_.step_size = 0.5f;               // m_u_step_size(0.5f)            rc1prenderer.cpp:21
     prm_.apply_gradient_shading = 0;     // m_apply_gradient_shading(false) rc1prenderer.cpp:22
-    prm_.skip_block = 0; prm_.count_samples = 0; prm_.tf_in_smem = 1; prm_.exact_filter = 1; prm_.depth_split = 0;
+    prm_.skip_block = 0; prm_.count_samples = 0; prm_.tf_in_smem = 1; prm_.exact_filter = 1; prm_.depth_split = 0; prm_.split_groups = 0;
   }
 
   // Init (rc1prenderer.cpp:50-70): requires a volume texture, takes the RGBt transfer-function texture,
@@ -671,6 +671,7 @@ class Rc1Pass : public RendererImpl {
                 VRB_ERR_INVALID, "RayCasting1Pass::set_params: skip_block must be 0, 4, 8, 16 or 32");
     VRB_REQUIRE(p.depth_split == 0 || p.depth_split == 1 || p.depth_split == 2 || p.depth_split == 4 || p.depth_split == 8,
                 VRB_ERR_INVALID, "RayCasting1Pass::set_params: depth_split must be 0, 1, 2, 4 or 8");
+    VRB_REQUIRE(p.split_groups >= 0 && p.split_groups <= 64, VRB_ERR_INVALID, "RayCasting1Pass::set_params: split_groups must be 0..64");
     prm_ = p;
     return VRB_OK;
   }
@@ -710,7 +711,7 @@ class Rc1Pass : public RendererImpl {
     a.n_tiles = a.tiles_x * ((height + part_tile - 1) / part_tile);
     const int my_tiles = (a.n_tiles - rank + n_ranks - 1) / n_ranks;
     a.n_items = my_tiles * (part_tile / WARP_W) * (part_tile / WARP_H);
-    if (a.n_items <= 0) return VRB_OK;
+    if (a.n_items <= 0 && n_peer_frames == 0) return VRB_OK;   // with peers the (empty) launch still raises this rank's flag
     // scrambled item order: multiply by an odd constant near n/golden-ratio that is coprime to n
     unsigned sc = (unsigned)(a.n_items * 0.6180339887) | 1u;
     auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned t = x % y; x = y; y = t; } return x; };
@@ -724,7 +725,7 @@ class Rc1Pass : public RendererImpl {
     a.queue = d_queue;
     fill_peer_signal(*this, a.sig);
     // persistent grid: as many CTAs as fit on the GPU at once (occupancy query below), never more than there are items
-    const int max_ctas = (a.n_items + CTA_THREADS / 32 - 1) / (CTA_THREADS / 32);
+    const int max_ctas = std::max(1, (a.n_items + CTA_THREADS / 32 - 1) / (CTA_THREADS / 32));   // a rank without items still signals its peers
     if (prm_.skip_block) {
       int rc = skip_.ensure(ctx, prm_.skip_block);
       if (rc != VRB_OK) return rc;
@@ -759,10 +760,9 @@ class Rc1Pass : public RendererImpl {
       const int rc_o = ensure_tile_order();
       if (rc_o != VRB_OK) return rc_o;
       a.tile_order = d_tile_order; a.scramble = 0u;
-      static const int env_g = []() { const char* e = getenv("VRB_SPLIT_G"); return e ? atoi(e) : 0; }();
-      a.split_g = env_g > 0 ? env_g : 2;
+      a.split_g = prm_.split_groups > 0 ? prm_.split_groups : 2;
       a.n_items = my_tiles * (part_tile / fw) * (part_tile / fh);
-      const int ctas = (a.n_items + CTA_THREADS / 32 - 1) / (CTA_THREADS / 32);
+      const int ctas = std::max(1, (a.n_items + CTA_THREADS / 32 - 1) / (CTA_THREADS / 32));
       int occ = 0;
 #define SPLIT(C, KK)                                                                                                          \
   {                                                                                                                          \

@@ -127,6 +127,10 @@ struct RendererImpl {
   int gather_mode = 0, gather_ranks = 1;
   void close_peers();
   void begin_frame();                    // advances frame_seq and selects the buffers (vrb_renderer_redraw)
+  void abort_frame();                    // undoes begin_frame when the redraw failed before its launch
+  // VRB_GATHER_ROOT back-pressure (frame_credit, vrb_renderer.cu): rank 0 maps the senders' allocations only to write their credit word
+  void* credit_opened[MAX_PEERS] = {}; int n_credit_peers = 0; unsigned** d_credit_words = nullptr;
+  int frame_credit();
   unsigned* flags() const { return (unsigned*)((char*)frame_base + 2 * frame_bytes); }
   // Sort-last bricks (vrb_renderer_set_bricks, vrb_sortlast.cuh): the volume box is cut into brick_grid[0] x [1] x [2] bricks, one per
   // rank.  Every rank marches, for ALL pixels, the lattice samples inside its brick; the premultiplied float32 partials go to the rank

@@ -224,7 +224,7 @@ inline bool fill_march_args(const RendererImpl& r, float step, int apply_occlusi
   a.n_tiles = a.tiles_x * ((r.height + r.part_tile - 1) / r.part_tile);
   const int my_tiles = (a.n_tiles - r.rank + r.n_ranks - 1) / r.n_ranks;
   a.n_items = my_tiles * (r.part_tile / 8) * (r.part_tile / 4);
-  if (a.n_items <= 0) return false;
+  if (a.n_items <= 0 && r.n_peer_frames == 0) return false;   // with peers the (empty) launch still raises this rank's flag
   unsigned sc = (unsigned)(a.n_items * 0.6180339887) | 1u;
   auto gcd = [](unsigned x, unsigned y) { while (y) { unsigned tt = x % y; x = y; y = tt; } return x; };
   while (gcd(sc, (unsigned)a.n_items) != 1u) sc += 2;
@@ -246,7 +246,7 @@ int launch_march_t(const RendererImpl& r, const MarchArgs& a, const typename S::
   if (smem > 48 * 1024) VRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
   VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH_THREADS, smem));
-  const int max_ctas = (a.n_items + MARCH_THREADS / 32 - 1) / (MARCH_THREADS / 32);
+  const int max_ctas = std::max(1, (a.n_items + MARCH_THREADS / 32 - 1) / (MARCH_THREADS / 32));   // a rank without items still signals its peers
   kern<<<std::min(std::max(per_sm, 1) * r.ctx->sm_count, max_ctas), MARCH_THREADS, smem, r.ctx->stream>>>(a, sa);
   VRB_CUDA(cudaGetLastError());
   return VRB_OK;

@@ -60,7 +60,8 @@ void RendererImpl::free_async() {
 
 void RendererImpl::close_peers() {
   for (int i = 0; i < MAX_PEERS; i++) if (peer_opened[i]) { cudaIpcCloseMemHandle(peer_opened[i]); peer_opened[i] = nullptr; }
-  n_peer_frames = 0; gather_mode = 0; gather_ranks = 1;
+  for (int i = 0; i < MAX_PEERS; i++) if (credit_opened[i]) { cudaIpcCloseMemHandle(credit_opened[i]); credit_opened[i] = nullptr; }
+  n_peer_frames = 0; n_credit_peers = 0; gather_mode = 0; gather_ranks = 1;
   frame_seq = 0;
   if (frame_base) frame = (__half*)frame_base;
 }
@@ -146,6 +147,36 @@ void RendererImpl::begin_frame() {
   for (int q = 0; q < n_peer_frames; q++) peer_frames[q] = (char*)peer_opened[q] + off;
 }
 
+// A redraw that failed before its launch gives its frame number back, so this rank's flag sequence stays in step with its peers.
+void RendererImpl::abort_frame() {
+  if (gather_mode == VRB_GATHER_NONE || frame_seq == 0) return;
+  frame_seq--;
+  const size_t off = (size_t)(frame_seq & 1u) * frame_bytes;
+  frame = (__half*)((char*)frame_base + off);
+  for (int q = 0; q < n_peer_frames; q++) peer_frames[q] = (char*)peer_opened[q] + off;
+}
+
+// VRB_GATHER_ROOT back-pressure.  Only rank 0 waits for its peers in that mode, so nothing else stops a sender from running
+// ahead: frame k + 2 goes into the buffer of frame k.  Credit word (FRAME_FLAGS - 3 of every sender's flag block): when rank 0
+// issues redraw s, every read of frame s - 1 it will ever issue is already in its stream, so it writes credit s - 1 behind them
+// (one-thread kernel, system-scope store into each sender's allocation); a sender's redraw s waits, on its stream, for
+// credit >= s - 2 — the frame that last used the buffer it is about to overwrite has been consumed.
+__global__ void frame_credit_kernel(unsigned* const* words, int n, unsigned value) {
+  for (int q = threadIdx.x; q < n; q += blockDim.x) *(volatile unsigned*)words[q] = value;
+  __threadfence_system();
+}
+int RendererImpl::frame_credit() {
+  if (gather_mode != VRB_GATHER_ROOT || gather_ranks <= 1) return VRB_OK;
+  if (rank == 0) {
+    if (frame_seq < 2 || n_credit_peers == 0) return VRB_OK;
+    frame_credit_kernel<<<1, 32, 0, ctx->stream>>>(d_credit_words, n_credit_peers, frame_seq - 1);
+    VRB_CUDA(cudaGetLastError());
+    return VRB_OK;
+  }
+  if (frame_seq <= 2) return VRB_OK;
+  return stream_wait_geq(ctx->stream, flags() + FRAME_FLAGS - 3, frame_seq - 2);
+}
+
 }  // namespace vrb
 
 using namespace vrb;
@@ -195,6 +226,7 @@ int vrb_renderer_destroy(vrb_renderer* r) {
   if (p->d_lattice) cudaFree(p->d_lattice);
   if (p->d_queue) cudaFree(p->d_queue);
   if (p->d_tile_order) cudaFree(p->d_tile_order);
+  if (p->d_credit_words) cudaFree(p->d_credit_words);
   if (p->ev0) cudaEventDestroy(p->ev0);
   if (p->ev1) cudaEventDestroy(p->ev1);
   delete p;
@@ -308,11 +340,13 @@ int vrb_renderer_redraw(vrb_renderer* r, int mode) {
   VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_redraw: null renderer");
   RendererImpl* p = r->impl;
   cudaStream_t s = p->ctx->stream;
-  VRB_CUDA(cudaEventRecord(p->ev0, s));
-  p->begin_frame();
   VRB_REQUIRE(mode == 0 || mode == p->ms_mode, VRB_ERR_INVALID, "vrb_renderer_redraw: mode %d but multiscaling mode %d is set", mode, p->ms_mode);
-  int rc = p->redraw(mode);
-  if (rc != VRB_OK) return rc;
+  VRB_REQUIRE(p->built && p->have_cam, VRB_ERR_INVALID, "vrb_renderer_redraw before Init / Update");
+  VRB_CUDA(cudaEventRecord(p->ev0, s));
+  p->begin_frame();            // after the argument checks: a rejected call must not advance the peers' frame sequence
+  int rc = p->frame_credit();
+  if (rc == VRB_OK) rc = p->redraw(mode);
+  if (rc != VRB_OK) { p->abort_frame(); return rc; }
   // DrawMultiSampleHigherResolutionMode / DrawHigherResolutionWithDownScale / DrawLowerResolutionWithUpScale (renderoutputframe.cpp:265-539)
   // With an image partition the filter needs the other ranks' pixels: it runs in vrb_renderer_wait_peers, on the ranks that
   // collect the whole frame (every rank with VRB_GATHER_ALL, rank 0 with VRB_GATHER_ROOT).
@@ -461,14 +495,24 @@ int vrb_renderer_set_peers(vrb_renderer* r, const void* handles, int n_ranks, in
   VRB_REQUIRE(mode == VRB_GATHER_ROOT || mode == VRB_GATHER_ALL, VRB_ERR_INVALID, "vrb_renderer_set_peers: bad mode %d", mode);
   for (int q = 0; q < n_ranks; q++) {
     if (q == rank) continue;
-    if (mode == VRB_GATHER_ROOT && q != 0) continue;        // only rank 0 collects
+    if (mode == VRB_GATHER_ROOT && q != 0 && rank != 0) continue;        // only rank 0 collects
     cudaIpcMemHandle_t h;
     memcpy(&h, (const char*)handles + (size_t)q * VRB_IPC_HANDLE_BYTES, sizeof(h));
     void* ptr = nullptr;
     VRB_CUDA(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    if (mode == VRB_GATHER_ROOT && rank == 0) {             // rank 0 stores no pixels into the senders, only their credit word
+      p->credit_opened[p->n_credit_peers++] = ptr;
+      continue;
+    }
     p->peer_opened[p->n_peer_frames] = ptr;
     p->peer_flags[p->n_peer_frames] = (unsigned*)((char*)ptr + 2 * p->frame_bytes) + rank;
     p->peer_frames[p->n_peer_frames++] = ptr;
+  }
+  if (p->n_credit_peers) {
+    unsigned* words[RendererImpl::MAX_PEERS];
+    for (int q = 0; q < p->n_credit_peers; q++) words[q] = (unsigned*)((char*)p->credit_opened[q] + 2 * p->frame_bytes) + (RendererImpl::FRAME_FLAGS - 3);
+    if (!p->d_credit_words) VRB_CUDA(cudaMalloc(&p->d_credit_words, RendererImpl::MAX_PEERS * sizeof(unsigned*)));
+    VRB_CUDA(cudaMemcpy(p->d_credit_words, words, p->n_credit_peers * sizeof(unsigned*), cudaMemcpyHostToDevice));
   }
   p->gather_mode = mode; p->gather_ranks = n_ranks;
   // flags restart from 0 with the sequence; the caller synchronises the ranks before the first redraw (multigpu.py)

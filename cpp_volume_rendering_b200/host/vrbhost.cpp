@@ -296,6 +296,7 @@ void dds_restore_planes(uint8_t* data, size_t bytes, unsigned skip) {
   std::memcpy(data, tmp.data(), bytes);
 }
 
+constexpr size_t DDS_MAX_DECODED = (size_t)1 << 34;   // 16 GiB: beyond any volume the header fields below admit in practice
 bool dds_decode(const std::vector<uint8_t>& chunk, size_t block, std::vector<uint8_t>& out) {
   BitReader br(chunk.data(), chunk.size());
   const unsigned skip = br.read(2) + 1, strip = br.read(16) + 1;
@@ -315,6 +316,8 @@ bool dds_decode(const std::vector<uint8_t>& chunk, size_t block, std::vector<uin
       while (act > 255) act -= 256;
       out.push_back((uint8_t)act);
     }
+    // a run costs 10 header bits and may emit 127 bytes: a crafted stream must not grow the output without bound
+    if (br.exhausted() || out.size() > DDS_MAX_DECODED) return false;
   }
   if (skip > 1 && !out.empty()) {
     if (block == 0) dds_restore_planes(out.data(), out.size(), skip);
@@ -371,6 +374,8 @@ StructuredGridVolume* VolumeReader::readpvm(const std::string& path) {
   if (!ptr || !(ptr = next_line(ptr))) return nullptr;
   if (std::sscanf(ptr, "%u\n", &comps) != 1 || (comps != 1 && comps != 2)) return nullptr;   // reader.cpp:119-146: 8 or 16 bits
   if (!(ptr = next_line(ptr))) return nullptr;
+  // three unchecked 32-bit header fields: keep each axis sane so that w*h*d*comps cannot wrap size_t
+  if (w > 65536u || h > 65536u || d > 65536u) return nullptr;
   const size_t voxels = (size_t)w * h * d, need = voxels * comps;
   if ((size_t)(end - ptr) < need) return nullptr;
   if (version < 3 && (size_t)(end - ptr) != need) return nullptr;  // pvm.cpp:262: the sizes must add up

@@ -97,6 +97,7 @@ typedef struct {
                                     termination sample, sums re-associated): shortens the per-ray dependent chain when a GPU
                                     owns few pixels (image split over many GPUs).  Ignored with skip_block, tf_in_smem = 0 or
                                     exact_filter = 0. */
+  int   split_groups;            /* depth_split > 1: groups of 4 samples a lane marches per chunk; 0 = default (2) */
 } vrb_rc1pass_params;
 
 /* Run-time parameters of the three iso-surface ray casters: their ImGui-mutable members
@@ -389,7 +390,9 @@ int vrb_renderer_set_peers(vrb_renderer* r, const void* handles, int n_ranks, in
  * context stream wait (cuStreamWaitValue32, no spinning kernel) until every sender's flag has reached the frame number
  * of this rank's last redraw.  Frames are double-buffered, so a peer may already render frame k + 1 into this rank's
  * other buffer while frame k is read here.  All ranks must call redraw the same number of times.
- * VRB_GATHER_ROOT: only rank 0 waits; other ranks return at once. */
+ * VRB_GATHER_ROOT: only rank 0 waits; other ranks return at once.  A sender may therefore run ahead of rank 0, by at most one
+ * frame: redraw s of a sender waits on its stream for a credit that rank 0 writes (into the sender's allocation) when it issues
+ * its own redraw s - 1, i.e. behind every read of frame s - 2 — the frame that last used the buffer redraw s overwrites. */
 int vrb_renderer_wait_peers(vrb_renderer* r);
 
 /* ---- measurement ---------------------------------------------------------------------------- */

@@ -262,3 +262,76 @@ def test_multiscaling_over_an_image_partition(ctx, bonsai_table, mode, kernel):
         out, gen = res[rk]
         assert np.array_equal(gen.view(np.uint16), full_gen.view(np.uint16))
         assert np.array_equal(out.view(np.uint16), full.view(np.uint16))
+
+
+def _runahead_cams(n, w, h, frames):
+    from cpp_volume_rendering_b200 import inputs
+    return [inputs.make_camera((n * (1.0 + 0.15 * k), n * (1.0 - 0.1 * k), 2.0 * n), width=w, height=h) for k in range(frames)]
+
+
+def _runahead_worker(rank, world, port, frames, tile, size, q):
+    """VRB_GATHER_ROOT without a host barrier per frame: rank 1 issues every redraw at once, rank 0 dawdles and reads each frame."""
+    sys.path.insert(0, ROOT)
+    import time
+    import torch.distributed as dist
+    from cpp_volume_rendering_b200 import _capi, inputs, multigpu
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    n, (w, h) = 48, size
+    vox = inputs.synth_volume(n, np.uint8)
+    table = inputs.tf_build_linear(inputs.bonsai_tf())
+    cams = _runahead_cams(n, w, h, frames)
+    out = []
+    with _capi.Context(0) as ctx:
+        ctx.upload_volume(vox); ctx.upload_tf(table)
+        r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
+        r.init(w, h)
+        multigpu.setup_fused_gather(r, rank, world, tile=tile, mode=_capi.VRB_GATHER_ROOT)
+        for k in range(frames):
+            r.update(cams[k])
+            r.redraw()
+            r.wait_peers()                           # rank 1: returns at once
+            if rank == 0:
+                time.sleep(0.05)                     # let the sender get as far ahead as the library allows
+                out.append(r.read_frame(_capi.VRB_FRAME_RGBA32F))
+        ctx.synchronize()
+        dist.barrier()
+        r.set_peers([], rank, _capi.VRB_GATHER_NONE)
+        dist.barrier()
+        r.close()
+    q.put((rank, out))
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tile,size", [(16, (96, 80)), (128, (64, 64))])
+def test_root_gather_sender_runs_ahead(ctx, bonsai_table, tile, size):
+    """ROOT mode has no per-frame barrier: the sender's redraw k + 2 must not land in the buffer rank 0 still reads frame k
+    from (credit word, vrb_renderer.cu frame_credit).  Second case: one 128-pixel tile over two ranks — rank 1 owns no
+    pixels and must still raise its flag every frame, or rank 0's stream wait never returns."""
+    import torch.multiprocessing as mp
+    from cpp_volume_rendering_b200 import _capi, inputs
+    n, (w, h), frames = 48, size, 6
+    ctx.upload_volume(inputs.synth_volume(n, np.uint8)); ctx.upload_tf(bonsai_table)
+    r = _capi.Renderer(ctx, _capi.VRB_RC1PASS); r.init(w, h)
+    full = []
+    for cam in _runahead_cams(n, w, h, frames):
+        r.update(cam); r.redraw(); full.append(r.read_frame(_capi.VRB_FRAME_RGBA32F))
+    r.close()
+    assert not np.array_equal(full[0], full[2])
+    mpc = mp.get_context("spawn")
+    q = mpc.Queue()
+    port = _free_port()
+    procs = [mpc.Process(target=_runahead_worker, args=(rk, 2, port, frames, tile, size, q)) for rk in range(2)]
+    for p in procs:
+        p.start()
+    try:
+        res = dict(q.get(timeout=150) for _ in range(2))
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+    finally:
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+    for k in range(frames):
+        assert np.array_equal(res[0][k], full[k]), f"frame {k} on rank 0 mixes redraws"

@@ -29,7 +29,7 @@ def main():
                 r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
                 r.init(w, h)
                 prm = r.get_params(_capi.Rc1PassParams()); prm.step_size = 0.5; prm.depth_split = K
-                prm.exact_filter = int(os.environ.get("SWEEP_EXACT", "1")); prm.tf_in_smem = int(os.environ.get("SWEEP_TFSMEM", "1")); prm.skip_block = int(os.environ.get("SWEEP_SKIP", "0"))
+                prm.exact_filter = int(os.environ.get("SWEEP_EXACT", "1")); prm.tf_in_smem = int(os.environ.get("SWEEP_TFSMEM", "1")); prm.skip_block = int(os.environ.get("SWEEP_SKIP", "0")); prm.split_groups = int(os.environ.get("VRB_SPLIT_G", "0"))
                 r.set_params(prm)
                 r.set_partition(rank, world, 32)
                 r.update(cam, inputs.default_light(n))
