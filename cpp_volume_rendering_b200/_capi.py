@@ -145,6 +145,7 @@ SIGNATURES = {
     "vrb_renderer_wait_peers": (C.c_int, [_P]),
     "vrb_renderer_set_peers": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int]),
     "vrb_bench_tex_peak": (C.c_int, [_P, C.POINTER(C.c_double)]),
+    "vrb_sat3d_build_noalloc": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
 }
 
 _lib = None

@@ -395,6 +395,22 @@ int vrb_renderer_set_peers(vrb_renderer* r, const void* handles, int n_ranks, in
  * its own redraw s - 1, i.e. behind every read of frame s - 2 — the frame that last used the buffer redraw s overwrites. */
 int vrb_renderer_wait_peers(vrb_renderer* r);
 
+/* ---- allocation-free entry point ------------------------------------------------------------ */
+/* No counterpart in the reference; added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  The summed-area table of K12's exact builder
+ * (SummedAreaTable3D::BuildSAT's recurrence in double, float32 result, bit-identical to the table a VRB_EBS_SAT renderer builds
+ * with fast_sat = 0 from the same extinctions) with its double accumulators in a static __device__ array inside the library
+ * instead of a cudaMalloc'ed buffer: the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ *   dev_extinction: w*h*d float32 extinction coefficients (GetExtN of every voxel), x fastest, DEVICE memory of the current device;
+ *   dev_sat:        (w+2)*(h+2)*(d+2) float32 cells, x fastest, DEVICE memory: the bordered table (zero planes at index 0);
+ *   stream:         cudaStream_t to launch on (NULL = the default stream).  Asynchronous: the table is complete when the stream is.
+ * Limit: (w+2)*(h+2)*(d+2) <= VRB_SAT_NOALLOC_MAX_CELLS (a 128^3 volume; 17.6 MB of scratch per GPU that loads the library, held
+ * until exit); larger volumes are rejected with VRB_ERR_INVALID.  Every call shares the one scratch array: calls that overlap on
+ * the GPU (different streams or host threads) race — serialise them.  The first call on a device looks the array's address up
+ * (cudaGetSymbolAddress): make it outside any stream capture. */
+#define VRB_SAT_NOALLOC_MAX_CELLS 2197000   /* (128 + 2)^3 */
+int vrb_sat3d_build_noalloc(const float* dev_extinction, int w, int h, int d, float* dev_sat, void* stream);
+
 /* ---- measurement ---------------------------------------------------------------------------- */
 /* Cache-resident trilinear R16F tex3D microbenchmark: the texture-fetch roofline denominator P_tex
  * (SURVEY.md §8d).  Returns fetches per second of the whole GPU. */
