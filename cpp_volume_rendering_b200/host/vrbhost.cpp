@@ -95,7 +95,8 @@ namespace vis {
 // ---- Camera ------------------------------------------------------------------------------------------------
 static inline vec3 sub(vec3 a, vec3 b) { vec3 r; r.x = a.x - b.x; r.y = a.y - b.y; r.z = a.z - b.z; return r; }
 static inline vec3 crossv(vec3 a, vec3 b) { vec3 r; r.x = a.y * b.z - b.y * a.z; r.y = a.z * b.x - b.z * a.x; r.z = a.x * b.y - b.x * a.y; return r; }
-static inline vec3 normv(vec3 a) { float l = std::sqrt((a.x * a.x + a.y * a.y) + a.z * a.z); vec3 r; r.x = a.x / l; r.y = a.y / l; r.z = a.z / l; return r; }
+// glm::normalize as the reference's GLM 0.9.5 evaluates it: x * (1.0f / sqrt(dot(x, x))) (detail/func_geometric.inl:257-266)
+static inline vec3 normv(vec3 a) { const float inv = 1.0f / std::sqrt((a.x * a.x + a.y * a.y) + a.z * a.z); vec3 r; r.x = a.x * inv; r.y = a.y * inv; r.z = a.z * inv; return r; }
 
 Camera::Camera() : m_fovy(45.0f), m_aspect(1.0f) { m_eye.z = 1.0f; m_up.y = 1.0f; }
 void Camera::SetInitialConfig(vec3 eye, vec3 center, vec3 up) { m_eye = eye; m_center = center; m_up = up; }

@@ -116,8 +116,9 @@ def bonsai_tf():
 # ---------------------------------------------------------------------------------------------
 def _norm(v):
     v = np.asarray(v, np.float32)
-    l = np.sqrt(np.float32(np.float32(v[0] * v[0] + v[1] * v[1]) + v[2] * v[2]))
-    return (v / l).astype(np.float32)
+    # glm::normalize of the reference's GLM 0.9.5: x * (1.0f / sqrt(dot(x, x))), not x / length (func_geometric.inl:257-266)
+    inv = np.float32(1.0) / np.sqrt(np.float32(np.float32(v[0] * v[0] + v[1] * v[1]) + v[2] * v[2]))
+    return (v * inv).astype(np.float32)
 
 
 def _cross(a, b):

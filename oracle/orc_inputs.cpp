@@ -98,10 +98,17 @@ void orc_volume_r16f(const void* voxels, int dtype, int64_t n, float* out) {
 
 // glm::lookAt (GLM 0.9.5.3 gtc/matrix_transform.inl): f = normalize(center-eye); s = normalize(cross(f,up));
 // u = cross(s,f);  M[0]=(s.x,u.x,-f.x) M[1]=(s.y,u.y,-f.y) M[2]=(s.z,u.z,-f.z)  (camera.cpp:281-284)
+// glm::normalize of that GLM (detail/func_geometric.inl:257-266): x * inversesqrt(dot) with inversesqrt = 1.0f / sqrt — not x / length
+// (1 ulp apart on some components; pinned against the reference's camera.cpp in tests/test_ref_pins.py)
+static inline vec3 glm_normalize(vec3 x) {
+  const float sqr = x.x * x.x + x.y * x.y + x.z * x.z;
+  const float inv = 1.0f / std::sqrt(sqr);
+  return vec3(x.x * inv, x.y * inv, x.z * inv);
+}
 void orc_lookat3(const float eye[3], const float center[3], const float up[3], float m[9]) {
   vec3 e(eye[0], eye[1], eye[2]), c(center[0], center[1], center[2]), upv(up[0], up[1], up[2]);
-  vec3 f = normalize(c - e);
-  vec3 s = normalize(cross(f, upv));
+  vec3 f = glm_normalize(c - e);
+  vec3 s = glm_normalize(cross(f, upv));
   vec3 u = cross(s, f);
   m[0] = s.x; m[1] = u.x; m[2] = -f.x;
   m[3] = s.y; m[4] = u.y; m[5] = -f.y;

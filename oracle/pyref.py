@@ -141,3 +141,70 @@ def pvm_read(path):
     out = np.empty((d, h, w), np.uint8 if comps.value == 1 else np.uint16)
     f(path.encode(), dims, C.byref(comps), sc, _ptr(out), out.nbytes)
     return out, tuple(sc)
+
+
+def compute_blocks(voxels, num_blocks):
+    """ComputeBlocksFromVolume (rc1custompisoadaptrenderer.cpp:20-113): (min, max) float32 [nbz, nby, nbx]."""
+    v = np.ascontiguousarray(voxels)
+    d, h, w = v.shape
+    nbx, nby, nbz = num_blocks
+    mn = np.empty((nbz, nby, nbx), np.float32); mx = np.empty_like(mn)
+    f = lib().ref_compute_blocks
+    f.argtypes = [_P] + [C.c_int] * 7 + [_P, _P]; f.restype = C.c_int
+    if f(_ptr(v), _DT[v.dtype], w, h, d, nbx, nby, nbz, _ptr(mn), _ptr(mx)) != 0:
+        raise RuntimeError("reference ComputeBlocksFromVolume returned an unexpected number of blocks")
+    return mn, mx
+
+
+class RefVct:
+    """VCTPreProcessing (rc1pvctsg/preprocessingstages.cpp): PreProcessSuperVoxels at construction; levels() = the float RG data of
+    every glTexImage3D(GL_RG16F) upload, lut(tf) = PreProcessPreIntegrationTable's float data (GL_R16F)."""
+
+    def __init__(self, voxels):
+        v = np.ascontiguousarray(voxels)
+        d, h, w = v.shape
+        L = lib()
+        L.ref_vct_create.argtypes = [_P] + [C.c_int] * 4; L.ref_vct_create.restype = _P
+        L.ref_vct_destroy.argtypes = [_P]; L.ref_vct_num_levels.argtypes = [_P]
+        L.ref_vct_max_std.argtypes = [_P]; L.ref_vct_max_std.restype = C.c_double
+        L.ref_vct_level.argtypes = [_P, C.c_int, _P, _P]; L.ref_vct_lut.argtypes = [_P, _P, _P, _P]
+        self.h = L.ref_vct_create(_ptr(v), _DT[v.dtype], w, h, d)
+
+    def levels(self):
+        out = []
+        for i in range(lib().ref_vct_num_levels(self.h)):
+            dims = (C.c_int * 3)()
+            assert lib().ref_vct_level(self.h, i, None, dims) == 0
+            a = np.empty((dims[2], dims[1], dims[0], 2), np.float32)
+            assert lib().ref_vct_level(self.h, i, _ptr(a), dims) == 0
+            out.append(a)
+        return out
+
+    def max_std(self):
+        return lib().ref_vct_max_std(self.h)
+
+    def lut(self, ref_tf):
+        dims = (C.c_int * 2)()
+        assert lib().ref_vct_lut(self.h, ref_tf.h, None, dims) == 0
+        a = np.empty((dims[1], dims[0]), np.float32)
+        if a.size:
+            assert lib().ref_vct_lut(self.h, ref_tf.h, _ptr(a), dims) == 0
+        return a
+
+    def close(self):
+        if self.h:
+            lib().ref_vct_destroy(self.h)
+            self.h = None
+
+
+def camera_uniforms(eye, center=(0, 0, 0), up=(0, 1, 0), width=1, height=1):
+    """vis::Camera (libs/vis_utils/camera.cpp) + RayCasting1Pass::Update's expressions (rc1prenderer.cpp:88-101):
+    (eye[3], mat3(LookAt) column-major [9], tan_fovy, aspect, fovy)."""
+    f = lib().ref_camera_uniforms
+    f.argtypes = [_P, _P, _P, C.c_int, C.c_int, _P, _P, _P, _P, _P]; f.restype = None
+    e, c, u = (np.ascontiguousarray(t, np.float32) for t in (eye, center, up))
+    eo = np.zeros(3, np.float32); m = np.zeros(16, np.float32)
+    t, a, fy = C.c_float(), C.c_float(), C.c_float()
+    f(_ptr(e), _ptr(c), _ptr(u), int(width), int(height), _ptr(eo), _ptr(m), C.byref(t), C.byref(a), C.byref(fy))
+    m = m.reshape(4, 4)                      # [column][row]
+    return eo, m[:3, :3].reshape(9).copy(), t.value, a.value, fy.value

@@ -6,4 +6,8 @@
 #define sscanf_s sscanf
 typedef int errno_t;
 static inline int fopen_s(FILE** f, const char* name, const char* mode) { *f = std::fopen(name, mode); return *f ? 0 : 1; }
+#ifdef __cplusplus
+#include <cmath>
+using std::sin; using std::cos;   // MSVC's <cmath> puts the float overloads in the global namespace (camera.cpp: sin(float) * glm::vec3)
+#endif
 #endif

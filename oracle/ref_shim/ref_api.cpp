@@ -17,6 +17,7 @@
 #include <structured/rc1pdosct/conegaussiansampler.h>
 #include <math_utils/utils.h>
 #include <file_utils/pvm.h>
+#include <vis_utils/camera.h>
 #include <stdlib.h>                 // ::abs(float) overloads, as MSVC's <cmath> gives the filter headers (`x = abs(x)`)
 #include <math.h>
 #include <filters_utils_gxx.inc>    // the reference's filters/utils.hpp, see the Makefile
@@ -27,6 +28,13 @@
 #include <vis_utils/filters/bspline3.hpp>
 #include <vis_utils/filters/omoms3.hpp>
 #include <rodrigues_excerpt.inc>   // the reference's RodriguesRotation bodies, extracted by the Makefile
+#include <stdexcept>
+#include <limits>
+#include <algorithm>
+#include <compute_blocks_excerpt.inc>   // the reference's ComputeBlocksFromVolume (rc1custompisoadaptrenderer.cpp:14-113), extracted by the Makefile
+#include <volvis_utils/utils.h>
+#include <glm/gtc/constants.hpp>
+#include <vct_preprocessingstages.inc>  // the reference's VCTPreProcessing (rc1pvctsg/preprocessingstages.{h,cpp}), see the Makefile
 
 extern "C" {
 
@@ -85,6 +93,81 @@ void ref_sat3d_build(const double* in, int w, int h, int d, double* out) {
       for (int x = 0; x < w; x++) sat.SetValue(in[(size_t)x + (size_t)w * ((size_t)y + (size_t)h * z)], x, y, z);
   sat.BuildSAT();
   std::memcpy(out, sat.GetData(), sizeof(double) * (size_t)w * h * d);
+}
+
+// ---- ComputeBlocksFromVolume (cppvolrend/structured/rc1pisocustom/rc1custompisoadaptrenderer.cpp:20-113) ------------------
+static vis::StructuredGridVolume* make_volume(const void* voxels, int dtype, int w, int h, int d) {
+  vis::StructuredGridVolume* vol = new vis::StructuredGridVolume("ref", w, h, d);
+  const size_t n = (size_t)w * h * d, bytes = n * (dtype == 0 ? 1 : (dtype == 1 ? 2 : 4));
+  void* copy = std::malloc(bytes);                    // SetArrayData takes ownership
+  std::memcpy(copy, voxels, bytes);
+  vol->SetArrayData(copy, dtype == 0 ? vis::DataStorageSize::_8_BITS
+                                     : (dtype == 1 ? vis::DataStorageSize::_16_BITS : vis::DataStorageSize::_NORMALIZED_F));
+  return vol;
+}
+// mn / mx: nbx*nby*nbz floats in the order the reference pushes them (bz outermost, bx innermost).
+int ref_compute_blocks(const void* voxels, int dtype, int w, int h, int d, int nbx, int nby, int nbz, float* mn, float* mx) {
+  vis::StructuredGridVolume* vol = make_volume(voxels, dtype, w, h, d);
+  std::vector<float> a, b;
+  ComputeBlocksFromVolume(vol, glm::vec3(nbx, nby, nbz), a, b, glm::vec3(1.0f));
+  delete vol;
+  if (a.size() != (size_t)nbx * nby * nbz || b.size() != a.size()) return -1;
+  std::memcpy(mn, a.data(), a.size() * sizeof(float));
+  std::memcpy(mx, b.data(), b.size() * sizeof(float));
+  return 0;
+}
+
+// ---- VCTPreProcessing (cppvolrend/structured/rc1pvctsg/preprocessingstages.cpp:35-202) --------------------------------------
+// PreProcessSuperVoxels on a volume; the float RG data of every glTexImage3D(GL_RG16F) level is recorded by the GL stub.
+struct RefVct { VCTPreProcessing pre; vis::StructuredGridVolume* vol; std::vector<ref_gl_capture::Level> levels; };
+void* ref_vct_create(const void* voxels, int dtype, int w, int h, int d) {
+  RefVct* v = new RefVct();
+  v->vol = make_volume(voxels, dtype, w, h, d);
+  ref_gl_capture::levels().clear();
+  v->pre.PreProcessSuperVoxels(v->vol);
+  v->levels.swap(ref_gl_capture::levels());
+  return v;
+}
+void ref_vct_destroy(void* h) { RefVct* v = (RefVct*)h; v->pre.Destroy(); delete v->vol; delete v; }
+int ref_vct_num_levels(void* h) { return (int)((RefVct*)h)->levels.size(); }
+double ref_vct_max_std(void* h) { return ((RefVct*)h)->pre.maximum_standard_deviation; }
+// out_rg (may be NULL): w*h*d*2 floats as handed to glTexImage3D(GL_RG16F, GL_RG, GL_FLOAT); returns 0 if the upload was RG16F/2 channels
+int ref_vct_level(void* h, int level, float* out_rg, int dims[3]) {
+  RefVct* v = (RefVct*)h;
+  if (level < 0 || level >= (int)v->levels.size()) return -1;
+  const ref_gl_capture::Level& L = v->levels[level];
+  dims[0] = L.w; dims[1] = L.h; dims[2] = L.d;
+  if (out_rg) std::memcpy(out_rg, L.data.data(), L.data.size() * sizeof(float));
+  return (L.level == level && L.internal == GL_RG16F && L.channels == 2) ? 0 : -2;
+}
+// PreProcessPreIntegrationTable with a TransferFunction1D of ref_tf_create: the float data handed to SetData(GL_R16F).
+int ref_vct_lut(void* h, void* tf, float* out, int dims[2]) {
+  RefVct* v = (RefVct*)h;
+  if (v->pre.glsl_preintegration_lookup) { delete v->pre.glsl_preintegration_lookup; v->pre.glsl_preintegration_lookup = nullptr; }
+  v->pre.PreProcessPreIntegrationTable(v->vol, (vis::TransferFunction1D*)tf);
+  gl::Texture2D* t = v->pre.glsl_preintegration_lookup;
+  if (!t) return -1;
+  dims[0] = (int)t->width; dims[1] = (int)t->height;
+  if (out) std::memcpy(out, t->captured.data(), t->captured.size() * sizeof(float));
+  return (t->internal == GL_R16F && t->min_filter == GL_LINEAR && t->wrap_s == GL_CLAMP_TO_EDGE) ? 0 : -2;
+}
+
+// ---- vis::Camera (libs/vis_utils/camera.cpp:281-347) + the uniform expressions of RayCasting1Pass::Update (rc1prenderer.cpp:88-101) ---
+// lookat16: camera->LookAt() column-major; tan_fovy / aspect as bound to u_TanCameraFovY / u_CameraAspectRatio.
+void ref_camera_uniforms(const float eye[3], const float center[3], const float up[3], int width, int height,
+                         float eye_out[3], float lookat16[16], float* tan_fovy, float* aspect, float* fovy) {
+  vis::Camera cam;
+  vis::CameraData d;                       // fovy 45, near 1, far 5000 (camera.cpp:17-54)
+  d.eye = glm::vec3(eye[0], eye[1], eye[2]); d.center = glm::vec3(center[0], center[1], center[2]); d.up = glm::vec3(up[0], up[1], up[2]);
+  cam.SetData(&d);
+  cam.UpdateAspectRatio((float)width, (float)height);        // renderingmanager.cpp:326
+  const glm::vec3 e = cam.GetEye();
+  eye_out[0] = e.x; eye_out[1] = e.y; eye_out[2] = e.z;
+  const glm::mat4 m = cam.LookAt();
+  std::memcpy(lookat16, &m[0][0], 16 * sizeof(float));
+  *tan_fovy = (float)tan(DEGREE_TO_RADIANS(cam.GetFovY()) / 2.0);
+  *aspect = cam.GetAspectRatio();
+  *fovy = cam.GetFovY();
 }
 
 // ---- ParameterSpace (cppvolrend/utils/parameterspace.{h,cpp}) -----------------------------------------------

@@ -20,3 +20,16 @@ typedef float GLfloat; typedef int GLsizei; typedef unsigned char GLubyte; typed
 #define GL_RGB16F 0x881B
 #define GL_RGBA16F 0x881A
 #define GL_RGBA32F 0x8814
+#define GL_TEXTURE_3D 0x806F
+// glTexImage3D of a float RG / R image: recorded per level (ref_api.cpp reads ref_gl_capture::levels)
+#include <vector>
+namespace ref_gl_capture {
+struct Level { int level, internal, w, h, d, channels; std::vector<float> data; };
+inline std::vector<Level>& levels() { static std::vector<Level> v; return v; }
+}
+inline void glTexImage3D(GLenum, GLint level, GLint internalformat, GLsizei w, GLsizei h, GLsizei d, GLint, GLenum format, GLenum type, const void* data) {
+  const int ch = format == GL_RED ? 1 : (format == GL_RG ? 2 : (format == GL_RGB ? 3 : 4));
+  ref_gl_capture::Level L{level, internalformat, w, h, d, ch, {}};
+  if (type == GL_FLOAT && data) L.data.assign((const float*)data, (const float*)data + (size_t)w * h * d * ch);
+  ref_gl_capture::levels().push_back(L);
+}

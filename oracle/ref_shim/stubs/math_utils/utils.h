@@ -6,3 +6,6 @@
 #include <glm/glm.hpp>
 glm::vec3 RodriguesRotation(glm::vec3 v, float teta, glm::vec3 k);
 glm::dvec3 RodriguesRotation(glm::dvec3 v, double teta, glm::dvec3 k);
+// DEGREE_TO_RADIANS: the reference's own macro, extracted at build time (oracle/Makefile)
+#include <glm/gtc/constants.hpp>
+#include <degree_to_radians_excerpt.inc>

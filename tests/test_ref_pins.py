@@ -111,3 +111,68 @@ def test_digital_filter_matches_reference(kernel, shape):
     ref = R.filter_digital2d(kernel, img)
     for c in range(4):
         assert np.array_equal(got[..., c], ref)
+
+
+@pytest.mark.parametrize("shape", [(9, 7, 5), (64, 64, 64), (1, 1, 1), (3, 70, 2)])
+def test_buildsat_matches_reference(shape, bonsai_table):
+    """SummedAreaTable3D<double>::BuildSAT of the reference (libs/vis_utils/summedareatable.h:218-278) on the bordered extinction grid
+    of GenerateExtinctionSAT3DTex == the oracle's recurrence: the double table cast to float32 equals O.ext_sat3d bit for bit."""
+    w, h, d = shape
+    vox = inputs.synth_volume(0, np.uint8, shape=shape)
+    sat, ext = O.ext_sat3d(vox, bonsai_table, want_ext=True)
+    assert ext.shape == (d + 2, h + 2, w + 2) and not ext[0].any() and not ext[:, 0].any() and not ext[:, :, 0].any()
+    ref = R.sat3d_build(ext.astype(np.float64))                     # SetValue(double(float ext)) per cell, then BuildSAT
+    assert np.array_equal(ref.astype(np.float32), sat)
+    # and the table is an inclusive prefix sum: last cell == sum of all extinctions (exactly, for these sizes, up to double rounding)
+    assert abs(ref[-1, -1, -1] - ext.astype(np.float64).sum()) <= 1e-9 * max(1.0, ref[-1, -1, -1])
+
+
+@pytest.mark.parametrize("dtype,shape,nb", [(np.uint8, (40, 33, 21), (4, 4, 4)), (np.uint16, (32, 32, 32), (32, 32, 32)),
+                                            (np.float32, (17, 9, 30), (4, 3, 5)), (np.uint8, (10, 10, 10), (3, 3, 3))])
+def test_block_minmax_matches_reference(dtype, shape, nb):
+    """ComputeBlocksFromVolume of the reference (rc1custompisoadaptrenderer.cpp:20-113, extracted at build time) == O.block_minmax:
+    ragged last blocks, one voxel per block, float volumes."""
+    vox = inputs.synth_volume(0, dtype, shape=shape)
+    mn, mx = O.block_minmax(vox, nb)
+    rmn, rmx = R.compute_blocks(vox, nb)
+    assert np.array_equal(mn, rmn) and np.array_equal(mx, rmx)
+    assert (mx >= mn).all() or shape == (10, 10, 10)      # 10 voxels over 3 blocks of 4: no block is empty here either
+
+
+@pytest.mark.parametrize("dtype,shape", [(np.uint8, (32, 32, 32)), (np.uint16, (20, 12, 9)), (np.uint8, (7, 5, 3)), (np.float32, (16, 8, 8))])
+def test_vct_supervoxels_and_lut_match_reference(dtype, shape, ref_bonsai, bonsai_table):
+    """PreProcessSuperVoxels / PreProcessPreIntegrationTable of the reference (rc1pvctsg/preprocessingstages.cpp:35-202, compiled with its
+    GL includes removed) == O.vct_supervoxels / O.vct_preintegration: every RG16F level, the maximum standard deviation (double) and the
+    R16F table."""
+    vox = inputs.synth_volume(0, dtype, shape=shape)
+    levels, max_std = O.vct_supervoxels(vox)
+    r = R.RefVct(vox)
+    try:
+        ref_levels = r.levels()
+        assert len(ref_levels) == len(levels)
+        for a, b in zip(levels, ref_levels):
+            assert a.shape == b.shape and np.array_equal(a, _f16(b))
+        assert r.max_std() == max_std
+        if dtype != np.uint16:        # the table is O(max_density^2 x max_stddev): minutes on the CPU for a 16-bit volume, on both sides
+            lut = O.vct_preintegration(bonsai_table, dtype, max_std)
+            ref_lut = r.lut(ref_bonsai)
+            assert lut.shape == ref_lut.shape and np.array_equal(lut, _f16(ref_lut), equal_nan=True)
+    finally:
+        r.close()
+
+
+@pytest.mark.parametrize("eye,up,size", [((256, 256, 512), (0, 1, 0), (768, 768)), ((-30.0, 260.0, 20.0), (0, 0, 1), (640, 360)),
+                                         ((512, 512, 1024), (0, 1, 0), (1024, 1024)), ((0.3, -900.0, 11.0), (1, 0, 0), (3840, 2160))])
+def test_camera_uniforms_match_reference(eye, up, size):
+    """The reference's own vis::Camera (camera.cpp compiled into libref: glm::lookAt of its vendored GLM, fovy 45 default, aspect =
+    w / h) and the uniform expressions of RayCasting1Pass::Update == the Python camera of the tests and bench, the oracle's lookat3 and
+    the host mirror's vis::Camera::FillUniforms, bit for bit."""
+    from cpp_volume_rendering_b200 import hostapi
+    e, m3, tan_fovy, aspect, fovy = R.camera_uniforms(eye, up=up, width=size[0], height=size[1])
+    cam = inputs.make_camera(eye, up=up, width=size[0], height=size[1])
+    assert fovy == 45.0
+    assert list(cam.eye) == list(e) and np.array_equal(np.array(cam.lookat, np.float32), m3)
+    assert cam.tan_fovy == tan_fovy and cam.aspect == aspect
+    assert np.array_equal(O.lookat3(eye, (0, 0, 0), up), m3)
+    h = hostapi.camera_uniforms(eye, up=up, width=size[0], height=size[1])
+    assert np.array_equal(np.array(h.lookat, np.float32), m3) and h.tan_fovy == tan_fovy and h.aspect == aspect
