@@ -419,6 +419,11 @@ def run_cuda(args):
         if world == 1 and not args.no_cpu:
             r.close(); r = None
             line["extras"] = {"sat": sat_extra(ctx, table, hbm_peak)}
+            # the other BASELINE configs at their stated sizes (C1, C3 with and without shadows, C4's render, and the single-GPU halves
+            # of C5 at 512^3): frame time, counted work and a roofline block each (tools/bench_configs.py)
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import bench_configs
+            line["extras"]["configs"] = bench_configs.measure(ctx, set(bench_configs.ALL), 5, 2, tex_peak, hbm_peak)
             v, cores, total, secs = cpu_frame(vox, table, cam, repeats=2)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"full {IMG_W}x{IMG_H} frame ({total} samples, best of 2, {secs:.2f} s), oracle/liboracle.so OpenMP over rows"}

@@ -552,6 +552,7 @@ class DosRenderer : public RendererImpl {
     const bool phong = prm_.apply_gradient_shading != 0;   // ApplyPhongShading = m_apply_gradient_shading && GetCurrentGradientTexture()
     VRB_REQUIRE(!phong || (ctx->vol.tex_grad_pt && ctx->vol.grad_gen == ctx->vol.generation), VRB_ERR_INVALID, "RC1PConeTracingDirOcclusionShading: gradient shading needs vrb_volume_gradient() for the current volume");
     if (!fill_march_args(*this, prm_.step_size, prm_.apply_occlusion, prm_.apply_shadow, a, phong)) return VRB_OK;
+    if (prm_.count_samples == 2) a.count_mode = 2;   // shaded samples (each evaluates every section of its cones: counts x rays fetches)
     DosShader::Args s{};
     s.n_levels = pyr_.n_levels;
     for (int l = 0; l < pyr_.n_levels; l++) { s.mip[l] = pyr_.tex[l]; s.mip_res[l][0] = (float)pyr_.lw[l]; s.mip_res[l][1] = (float)pyr_.lh[l]; s.mip_res[l][2] = (float)pyr_.ld[l]; }

@@ -27,6 +27,7 @@ struct EbsArgs {
   uint2* frame; uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
   PeerSignal sig;
   unsigned long long* samples;
+  int count_mode;                    // COUNT kernel: 1 = march-loop iterations, 2 = shaded samples, 3 = SAT boxes evaluated (8 taps each)
   int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; const int* tile_order; unsigned* queue;
 };
 
@@ -81,7 +82,7 @@ __device__ Edge cone_edges(float cs_s, float cs_m, float angle) {
   Edge e; e.a1 = e1.x; e.b1 = e1.z; e.a2 = e2.x; e.b2 = e2.z;
   return e;
 }
-__device__ float cone_axis(const EbsArgs& a, const EbsConst& c, f3 pos, f3 cone, int m, int u, int v) {
+__device__ float cone_axis(const EbsArgs& a, const EbsConst& c, f3 pos, f3 cone, int m, int u, int v, unsigned& nbox) {
   float Stau = 0.0f;
   const float cm = comp(cone, m), signal = cm < 0.0f ? -1.0f : 1.0f;
   const Edge eu = cone_edges(comp(cone, u), cm, a.cone_angle), ev = cone_edges(comp(cone, v), cm, a.cone_angle);
@@ -105,20 +106,21 @@ __device__ float cone_axis(const EbsArgs& a, const EbsConst& c, f3 pos, f3 cone,
     setc(p1, m, gmin(m_pos, e)); setc(p1, u, u1); setc(p1, v, v1);
     setc(p2, m, gmax(m_pos, e)); setc(p2, u, u2); setc(p2, v, v2);
     Stau = __fadd_rn(Stau, eval_shadow_sat3d(a, c, add3(pos, p1), add3(pos, p2)));
+    nbox++;
     m_pos = e;
   }
   return Stau;
 }
 // ExtinctionDirectionalShadows (:432-456)
-__device__ float directional_shadows(const EbsArgs& a, const EbsConst& c, f3 tx) {
+__device__ float directional_shadows(const EbsArgs& a, const EbsConst& c, f3 tx, unsigned& nbox) {
   const f3 realpos = sub3(tx, scale3(c.sizes, 0.5f));
   const f3 cone = a.type_of_shadow == 0 ? normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), realpos))
                                         : normalize_rn(mk3(a.light_fwd[0], a.light_fwd[1], a.light_fwd[2]));
   const float ax = fabsf(cone.x), ay = fabsf(cone.y), az = fabsf(cone.z);
   float Stau;
-  if (az > ax && az > ay) Stau = cone_axis(a, c, tx, cone, 2, 0, 1);
-  else if (ay > ax) Stau = cone_axis(a, c, tx, cone, 1, 0, 2);
-  else Stau = cone_axis(a, c, tx, cone, 0, 1, 2);
+  if (az > ax && az > ay) Stau = cone_axis(a, c, tx, cone, 2, 0, 1, nbox);
+  else if (ay > ax) Stau = cone_axis(a, c, tx, cone, 1, 0, 2, nbox);
+  else Stau = cone_axis(a, c, tx, cone, 0, 1, 2, nbox);
   return expf(-Stau);
 }
 
@@ -143,7 +145,8 @@ struct EbsShader {
   static __device__ __forceinline__ Const prepare(const MarchArgs&, const Args& s) { return make_ebs_const(s); }
   static __device__ void shade_cell(const MarchArgs& a, const Args& s, const Const& c, f3 tx, float& Iocc, float& Isdw) {
     if (a.apply_occlusion) Iocc = extinction_ao(s, c, tx);
-    if (a.apply_shadow) Isdw = directional_shadows(s, c, tx);
+    unsigned unused = 0;
+    if (a.apply_shadow) Isdw = directional_shadows(s, c, tx, unused);
   }
 };
 
@@ -193,7 +196,7 @@ __global__ void __launch_bounds__(EBS_THREADS, 4) ebs_kernel(const __grid_consta
         const float h = gmin(a.step, __fsub_rn(D, s));
         const f3 tx = add3(wd, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));      // :598
         const f3 p = mul3(tx, inv_sizes);
-        if (COUNT) nsamp++;
+        if (COUNT && a.count_mode == 1) nsamp++;
         const float d_hw = tex3D<float>(a.vol, p.x, p.y, p.z);
         int j = (int)fminf(fmaxf(fmaf(d_hw, tfn, -0.5f), 0.0f), tfmax);
         if ((s_mask[j >> 5] >> (j & 31)) & 1u) {
@@ -208,8 +211,11 @@ __global__ void __launch_bounds__(EBS_THREADS, 4) ebs_kernel(const __grid_consta
           if (src.w > 0.0f) {
             // ShadeSample (:500-551)
             float ka = 0.0f, kd = 0.0f, Iocc = 0.0f, Isdw = 0.0f;
-            if (a.apply_occlusion) { ka = a.ka; Iocc = extinction_ao(a, c, tx); }
-            if (a.apply_shadow) { kd = a.kd; Isdw = directional_shadows(a, c, tx); }
+            unsigned nbox = 0;
+            if (a.apply_occlusion) { ka = a.ka; Iocc = extinction_ao(a, c, tx); nbox += (unsigned)a.ao_shells; }
+            if (a.apply_shadow) { kd = a.kd; Isdw = directional_shadows(a, c, tx, nbox); }
+            if (COUNT && a.count_mode == 2) nsamp++;
+            if (COUNT && a.count_mode == 3) nsamp += nbox;
             if (!phong_shade_sample(1, a.phong, tx, c.sizes, res, mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]),
                                     mk3(a.eye[0], a.eye[1], a.eye[2]), ka, kd, a.apply_shadow != 0, Iocc, Isdw, src)) {   // :524-545
               const float k = 1.0f / (ka + kd);
@@ -325,6 +331,7 @@ class EbsRenderer : public RendererImpl {
       return redraw_object_space<EbsShader>(*this, cache_, prm_.light_cache_resolution, m, a, prm_.count_samples != 0);
     }
     a.frame = (uint2*)frame; a.samples = d_samples;
+    a.count_mode = (prm_.count_samples == 2 || prm_.count_samples == 3) ? prm_.count_samples : 1;
     a.n_peers = n_peer_frames;
     for (int q = 0; q < n_peer_frames; q++) a.peer[q] = (uint2*)peer_frames[q];
     a.rank = rank; a.n_ranks = n_ranks; a.tile = part_tile;

@@ -322,6 +322,7 @@ struct VctShader {
     if (!a.apply_shadow) return;
     if (s.cone_samples > VCT_CONE_TABLE) { if (need) shade(a, s, c, tx, cd, Iocc, Isdw); return; }
     const int lane = threadIdx.x & 31;
+    unsigned nsteps = 0;               // cone steps this lane evaluated (instrumented launches only: count_mode 3)
     unsigned m = __ballot_sync(0xffffffffu, need);
     while (m) {
       const int src = __ffs(m) - 1;
@@ -334,6 +335,7 @@ struct VctShader {
         const float xl = s_vct_cone[0][is];
         const f3 wpos = add3(p, scale3(cone, xl));
         if (wpos.x < 0.0f || wpos.x > c.sizes.x || wpos.y < 0.0f || wpos.y > c.sizes.y || wpos.z < 0.0f || wpos.z > c.sizes.z) continue;
+        nsteps++;
         const float2 g = texture_lod(s, div3(wpos, c.sizes), s_vct_cone[1][is]);
         float opacity = lut_fetch(s, __fdiv_rn(__fadd_rn(g.x, 0.5f), s.vol_max_density), __fdiv_rn(__fadd_rn(g.y, 0.5f), s.vol_max_std));
         opacity = 1.0f - powf(1.0f - opacity, s_vct_cone[2][is]);
@@ -343,6 +345,7 @@ struct VctShader {
       for (int o = 16; o > 0; o >>= 1) T *= __shfl_xor_sync(0xffffffffu, T, o);
       if (lane == src) Isdw = T;
     }
+    if (a.count_mode == 3 && nsteps) atomicAdd(a.samples, (unsigned long long)nsteps);
   }
   // main() of rc1pvctsg/lightcachecomputation.comp: Iao stays 1, Ivd = EvaluationVoxelConeTracing at the cell centre
   static __device__ void shade_cell(const MarchArgs& a, const Args& s, const Const& c, f3 tx, float&, float& Isdw) {
@@ -426,6 +429,7 @@ class VctRenderer : public RendererImpl {
     const bool phong = prm_.apply_gradient_shading != 0;   // ApplyPhongShading = m_apply_gradient_shading && GetCurrentGradientTexture() (vctrenderer.cpp:211)
     VRB_REQUIRE(!phong || (ctx->vol.tex_grad_pt && ctx->vol.grad_gen == ctx->vol.generation), VRB_ERR_INVALID, "RC1PVoxelConeTracingSGPU: gradient shading needs vrb_volume_gradient() for the current volume");
     if (!fill_march_args(*this, prm_.step_size, prm_.apply_ambient_occlusion, prm_.apply_directional_shadows, a, phong)) return VRB_OK;
+    if (prm_.count_samples == 2 || prm_.count_samples == 3) a.count_mode = prm_.count_samples;   // shaded samples / cone steps
     VctShader::Args s{};
     s.n_levels = pyr_.n_levels;
     for (int l = 0; l < pyr_.n_levels; l++) { s.mip[l] = pyr_.tex[l]; s.mip_res[l][0] = (float)pyr_.lw[l]; s.mip_res[l][1] = (float)pyr_.lh[l]; s.mip_res[l][2] = (float)pyr_.ld[l]; }

@@ -26,6 +26,8 @@ struct MarchArgs {
   uint2* frame; uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
   PeerSignal sig;
   unsigned long long* samples;
+  int count_mode;                    // COUNT kernels: 1 = march-loop iterations, 2 = shaded (non-transparent) samples, 3 = the shader's own unit
+                                     // (VCT: cone steps inside the volume), added to `samples` by the shader
   int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; const int* tile_order; unsigned* queue;
   // sort-last bricks (vrb_sortlast.cuh): only lattice samples with brick_lo <= tx < brick_hi are marched; the premultiplied partial
   // goes to slot brick_id of the staging buffer of the rank that owns the pixel's strip of strip_h rows
@@ -127,7 +129,7 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
         }
         if (alive && inside) {
           const f3 p = mul3(tx, inv_sizes);
-          if (COUNT) nsamp++;
+          if (COUNT && a.count_mode == 1) nsamp++;
           const float d_hw = tex3D<float>(a.vol, p.x, p.y, p.z);
           int j = (int)fminf(fmaxf(fmaf(d_hw, tfn, -0.5f), 0.0f), tfmax);
           if ((s_mask[j >> 5] >> (j & 31)) & 1u) {
@@ -153,6 +155,7 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
       if (SL != 1) {
         float Iocc = 0.0f, Isdw = 0.0f;
         S::shade_warp(a, sa, sc, need, tx, cdir, Iocc, Isdw);
+        if (COUNT && a.count_mode == 2 && need) nsamp++;
         if (need) {
           float ka = 0.0f, kd = 0.0f;
           if (a.apply_occlusion) ka = a.ka;
@@ -216,7 +219,7 @@ inline bool fill_march_args(const RendererImpl& r, float step, int apply_occlusi
   a.tan_fovy = r.cam.tan_fovy; a.aspect = r.cam.aspect; a.step = step;
   a.ka = r.light.ka; a.kd = r.light.kd; a.apply_occlusion = apply_occlusion; a.apply_shadow = apply_shadow;
   fill_phong(r, phong, a.phong);
-  a.frame = (uint2*)r.frame; a.samples = r.d_samples;
+  a.frame = (uint2*)r.frame; a.samples = r.d_samples; a.count_mode = 1;
   a.n_peers = r.n_peer_frames;
   for (int q = 0; q < r.n_peer_frames; q++) a.peer[q] = (uint2*)r.peer_frames[q];
   a.rank = r.rank; a.n_ranks = r.n_ranks; a.tile = r.part_tile;

@@ -192,6 +192,19 @@ def write_syn(path, vox):
     return path
 
 
+def write_syn_native(path, vox):
+    """The same file as write_syn, written by libvrbhost.so (vrbh_write_syn): for volumes with millions of runs."""
+    assert vox.dtype == np.uint8 and vox.flags["C_CONTIGUOUS"]
+    d, h, w = vox.shape
+    L = hostlib()
+    L.vrbh_write_syn.restype = C.c_longlong
+    L.vrbh_write_syn.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int]
+    n = L.vrbh_write_syn(path.encode(), vox.ctypes.data_as(C.c_void_p), w, h, d)
+    if n < 0:
+        raise OSError(f"cannot write {path}")
+    return path
+
+
 def write_tf1d(path, text=BONSAI_TF1D):
     with open(path, "w") as f:
         f.write(text + "\n")

@@ -133,7 +133,7 @@ typedef struct {
   int   type_of_shadow;                    /* 0 point light, 1 directional */
   float light_cam_forward[3];              /* RenderingParameters::GetBlinnPhongLightSourceCameraForward() */
   int   fast_sat;                          /* new: 0 = SAT by the reference's recurrence (bit-identical), 1 = reduce-then-scan (<= 1 ulp), 2 = separable scan */
-  int   count_samples;
+  int   count_samples;                     /* vrb_renderer_counters: 1 = march-loop iterations, 2 = shaded (non-transparent) samples, 3 = SAT boxes evaluated (8 taps each) */
   int   use_light_cache;                   /* PreIlluminationStructuredVolume::IsActive(), false: object-space mode (see vrb_light_cache_read) */
   int   light_cache_resolution[3];         /* 32^3 (SetLightCacheResolution in the renderer's constructor) */
 } vrb_ebs_params;
@@ -152,7 +152,7 @@ typedef struct {
   int   apply_correction_factor;    /* true */
   float opacity_correction_factor;  /* 2.0 */
   int   cone_number_of_samples;     /* 50 */
-  int   count_samples;
+  int   count_samples;              /* vrb_renderer_counters: 1 = march-loop iterations, 2 = shaded samples, 3 = cone steps inside the volume */
   int   use_light_cache;                   /* PreIlluminationStructuredVolume::IsActive(), false: object-space mode (see vrb_light_cache_read) */
   int   light_cache_resolution[3];         /* 32^3 (SetLightCacheResolution in the renderer's constructor) */
 } vrb_vct_params;
@@ -198,7 +198,7 @@ typedef struct {
   float base_level_sigma0;                   /* 1.0 */
   int   use_custom_resolution;               /* true: the pyramid base is custom_resolution, else the volume's size */
   int   custom_resolution[3];                /* 128^3 */
-  int   count_samples;
+  int   count_samples;                       /* vrb_renderer_counters: 1 = march-loop iterations, 2 = shaded samples (each evaluates every section of its cones) */
   int   use_light_cache;                   /* PreIlluminationStructuredVolume::IsActive(), false: object-space mode (see vrb_light_cache_read) */
   int   light_cache_resolution[3];         /* 32^3 (SetLightCacheResolution in the renderer's constructor) */
 } vrb_dos_params;
