@@ -146,6 +146,11 @@ SIGNATURES = {
     "vrb_renderer_set_peers": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int]),
     "vrb_bench_tex_peak": (C.c_int, [_P, C.POINTER(C.c_double)]),
     "vrb_sat3d_build_noalloc": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "vrb_volume_upload_region": (C.c_int, [_P, _P, C.c_int, C.c_int, _P, _P, _P, C.c_float, C.c_float, C.c_float]),
+    "vrb_volume_synth": (C.c_int, [_P, C.c_int, _P, C.c_uint64, _P, _P, C.c_float, C.c_float, C.c_float]),
+    "vrb_volume_read_raw": (C.c_int, [_P, _P]),
+    "vrb_vct_region_begin": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int), C.POINTER(C.c_double)]),
+    "vrb_vct_region_finish": (C.c_int, [_P, _P, C.c_double]),
 }
 
 _lib = None
@@ -200,11 +205,37 @@ class Context:
         d, h, w = v.shape
         _check(lib().vrb_volume_upload(self._h, v.ctypes.data_as(_P), _DTYPES[v.dtype], w, h, d, *map(float, scale)))
         self.vol_shape = (d, h, w)
+        self.vol_dtype = v.dtype
 
     def upload_volume_device(self, dev_ptr, dtype, shape_zyx, scale=(1.0, 1.0, 1.0)):
         d, h, w = shape_zyx
         _check(lib().vrb_volume_upload_device(self._h, _P(dev_ptr), _DTYPES[np.dtype(dtype)], w, h, d, *map(float, scale)))
         self.vol_shape = (d, h, w)
+        self.vol_dtype = np.dtype(dtype)
+
+    def upload_volume_region(self, voxels, origin_xyz, full_xyz, scale=(1.0, 1.0, 1.0)):
+        """voxels [d, h, w]: the region of a bricked volume that starts at voxel origin_xyz of a full_xyz volume."""
+        v = np.ascontiguousarray(voxels)
+        d, h, w = v.shape
+        A = C.c_int64 * 3
+        _check(lib().vrb_volume_upload_region(self._h, v.ctypes.data_as(_P), 0, _DTYPES[v.dtype], A(w, h, d), A(*origin_xyz), A(*full_xyz), *map(float, scale)))
+        self.vol_shape = (d, h, w)
+        self.vol_dtype = v.dtype
+
+    def synth_volume(self, dtype, full_xyz, seed=0xB2000001, origin_xyz=None, region_xyz=None, scale=(1.0, 1.0, 1.0)):
+        """The synthetic volume (inputs.synth_volume's twin) generated on the device: whole, or the region given."""
+        A = C.c_int64 * 3
+        o = A(*origin_xyz) if origin_xyz is not None else None
+        r = A(*region_xyz) if region_xyz is not None else None
+        _check(lib().vrb_volume_synth(self._h, _DTYPES[np.dtype(dtype)], A(*full_xyz), seed, o, r, *map(float, scale)))
+        w, h, d = region_xyz if region_xyz is not None else full_xyz
+        self.vol_shape = (d, h, w)
+        self.vol_dtype = np.dtype(dtype)
+
+    def read_volume_raw(self, dtype=None):
+        out = np.empty(self.vol_shape, np.dtype(dtype) if dtype is not None else self.vol_dtype)
+        _check(lib().vrb_volume_read_raw(self._h, out.ctypes.data_as(_P)))
+        return out
 
     def volume_gradient(self, model, want_data=False):
         """Builds (model 1 Sobel-Feldman, 2 central differences) or frees (0) the gradient texture; optionally returns
@@ -340,6 +371,15 @@ class Renderer:
             out = np.empty((dims[2], dims[1], dims[0]), np.float32)
             _check(lib().vrb_ebs_read_sat(self._h, out.ctypes.data_as(_P), C.byref(dims), C.byref(ms)))
         return out, ms.value
+
+    def vct_region_begin(self, dev_ptr=None):
+        """(level L, dims (w, h, d) of the whole level L, local max stddev); with dev_ptr the brick's level-L means are written."""
+        dims = (C.c_int * 3)(); lvl = C.c_int(); mx = C.c_double()
+        _check(lib().vrb_vct_region_begin(self._h, _P(dev_ptr) if dev_ptr else None, dims, C.byref(lvl), C.byref(mx)))
+        return lvl.value, tuple(dims), mx.value
+
+    def vct_region_finish(self, dev_ptr, global_max_std):
+        _check(lib().vrb_vct_region_finish(self._h, _P(dev_ptr), float(global_max_std)))
 
     def read_vct_level(self, level):
         """RG16F (mean, stddev) texels of one supervoxel level as float32 [d, h, w, 2]."""

@@ -78,7 +78,7 @@ int sort_last_composite(const RendererImpl& r, const SortLastPlan& pl, int owner
 void sort_last_plan(const RendererImpl& r, SortLastPlan& pl) {
   const Volume& v = r.ctx->vol;
   const int g[3] = {r.brick_grid[0], r.brick_grid[1], r.brick_grid[2]};
-  const float res[3] = {(float)v.w, (float)v.h, (float)v.d}, sc[3] = {v.sx, v.sy, v.sz};
+  const float res[3] = {(float)v.fw, (float)v.fh, (float)v.fd}, sc[3] = {v.sx, v.sy, v.sz};   // the whole volume, also when this rank stores a region
   pl.n = g[0] * g[1] * g[2];
   int eye_cell[3];
   for (int a = 0; a < 3; a++) {

@@ -101,6 +101,20 @@ struct VctPyramid {
   double max_std = 0.0; double vol_max_density = 0.0;
   uint64_t vol_gen = 0, tf_gen = 0;
   float build_ms = 0.f;
+  // Region (bricked) volumes: levels < lb are built from, and stored for, this rank's region only (texel origin loff of the stored
+  // array inside the whole level); levels >= lb cover the whole volume on every rank and are built from the level lb - 1 means that
+  // the ranks exchange (vrb_vct_region_begin / _finish).  flw / flh / fld: dims of the WHOLE level (what the shader's normalised
+  // coordinates refer to); equal to lw / lh / ld for an unbricked volume.
+  int flw[VCT_MAX_LEVELS], flh[VCT_MAX_LEVELS], fld[VCT_MAX_LEVELS], loff[VCT_MAX_LEVELS][3] = {};
+  int lb = 0;                          // 0: not a region pyramid
+  bool region_ready = false;
+  double* region_means = nullptr;      // level lb - 1 means of the region, until region_finish
+  double local_max_std = 0.0;
+  int blo[3] = {0, 0, 0}, bhi[3] = {0, 0, 0};   // this rank's brick [blo, bhi) in voxels
+  int ensure_region(vrb_ctx* ctx, const int brick_lo[3], const int brick_hi[3], float reach_voxels);
+  int region_begin(vrb_ctx* ctx, double* dev_means, int dims[3], int* level, double* local_max);
+  int region_finish(vrb_ctx* ctx, const double* dev_means, double global_max_std);
+  int build_quads(vrb_ctx* ctx, int l0, int l1);
   void release_lut() { if (lut) cudaFree(lut); lut = nullptr; lut_w = lut_h = 0; tf_gen = 0; }
   void release() {
     for (int l = 0; l < VCT_MAX_LEVELS; l++) {
@@ -109,7 +123,9 @@ struct VctPyramid {
       if (lin[l]) cudaFree(lin[l]);
       tex[l] = 0; arr[l] = nullptr; lin[l] = nullptr;
     }
-    n_levels = 0; vol_gen = 0;
+    n_levels = 0; vol_gen = 0; lb = 0; region_ready = false;
+    if (region_means) cudaFree(region_means);
+    region_means = nullptr;
     release_lut();
   }
   int ensure(vrb_ctx* ctx, bool with_lut);
@@ -153,11 +169,218 @@ static int build_levels(vrb_ctx* ctx, VctPyramid& p, const T* raw, double maxv) 
   return rc;
 }
 
+// footprint textures of levels [l0, l1) from their linear RG16F copies
+int VctPyramid::build_quads(vrb_ctx* ctx, int l0, int l1) {
+  cudaStream_t s = ctx->stream;
+  cudaChannelFormatDesc desc = cudaCreateChannelDesc<uint4>();
+  cudaTextureDesc td{};
+  td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+  td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
+  for (int l = l0; l < l1; l++) {
+    VRB_CUDA(cudaMalloc3DArray(&arr[l], &desc, make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]), cudaArraySurfaceLoadStore));
+    cudaResourceDesc rd{}; rd.resType = cudaResourceTypeArray; rd.res.array.array = arr[l];
+    cudaSurfaceObject_t dst = 0;
+    VRB_CUDA(cudaCreateSurfaceObject(&dst, &rd));
+    cudaError_t e = cudaCreateTextureObject(&tex[l], &rd, &td, nullptr);
+    if (e == cudaSuccess) {
+      vct_quad_kernel<<<dim3((lw[l] + 255) / 256, lh[l], ld[l]), 256, 0, s>>>((const unsigned*)lin[l], dst, lw[l], lh[l], ld[l]);
+      e = cudaGetLastError();
+      if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    }
+    cudaDestroySurfaceObject(dst);
+    VRB_CUDA(e);
+  }
+  return VRB_OK;
+}
+
+// ---- region (bricked) pyramid ------------------------------------------------------------------------------------------------
+// Copies the block [lo, hi) (whole-level texel coordinates) of the region's level means into the whole-level buffer.
+__global__ void __launch_bounds__(256) vct_block_copy_kernel(const double* __restrict__ src, int sw, int sh, int sox, int soy, int soz,
+                                                             double* __restrict__ dst, int dw, int dh, int lox, int loy, int loz, int nx, int ny, int nz) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
+  if (x >= nx || y >= ny || z >= nz) return;
+  const size_t si = (size_t)(lox + x - sox) + (size_t)sw * ((size_t)(loy + y - soy) + (size_t)sh * (size_t)(loz + z - soz));
+  dst[(size_t)(lox + x) + (size_t)dw * ((size_t)(loy + y) + (size_t)dh * (size_t)(loz + z))] = src[si];
+}
+
+template <typename T>
+static int build_region_levels(vrb_ctx* ctx, VctPyramid& p, const T* raw, double maxv) {
+  cudaStream_t s = ctx->stream;
+  unsigned long long* d_max = nullptr;
+  double* dbl[2] = {nullptr, nullptr};
+  auto body = [&]() -> int {
+    VRB_CUDA(cudaMalloc(&d_max, sizeof(unsigned long long)));
+    VRB_CUDA(cudaMemsetAsync(d_max, 0, sizeof(unsigned long long), s));
+    const size_t n0 = (size_t)p.lw[0] * p.lh[0] * p.ld[0];
+    VRB_CUDA(cudaMalloc(&p.lin[0], n0 * sizeof(__half2)));
+    vct_level0_kernel<T><<<(unsigned)((n0 + 255) / 256), 256, 0, s>>>(raw, n0, maxv, p.lin[0]);
+    const size_t n1 = (size_t)p.lw[1] * p.lh[1] * p.ld[1];
+    VRB_CUDA(cudaMalloc(&dbl[0], n1 * sizeof(double)));
+    VRB_CUDA(cudaMalloc(&dbl[1], std::max<size_t>((size_t)p.lw[2 < p.lb ? 2 : 1] * p.lh[2 < p.lb ? 2 : 1] * p.ld[2 < p.lb ? 2 : 1], 1) * sizeof(double)));
+    for (int l = 1; l < p.lb; l++) {
+      const size_t nl = (size_t)p.lw[l] * p.lh[l] * p.ld[l];
+      VRB_CUDA(cudaMalloc(&p.lin[l], nl * sizeof(__half2)));
+      dim3 g((p.lw[l] + 255) / 256, p.lh[l], p.ld[l]);
+      vct_reduce_kernel<T><<<g, 256, 0, s>>>(l == 1 ? raw : nullptr, maxv, l == 1 ? nullptr : dbl[l & 1], p.lw[l - 1], p.lh[l - 1],
+                                             p.lw[l], p.lh[l], p.ld[l], dbl[(l + 1) & 1], p.lin[l], d_max);
+    }
+    VRB_CUDA(cudaGetLastError());
+    unsigned long long bits = 0;
+    VRB_CUDA(cudaMemcpyAsync(&bits, d_max, sizeof(bits), cudaMemcpyDeviceToHost, s));
+    VRB_CUDA(cudaStreamSynchronize(s));
+    memcpy(&p.local_max_std, &bits, sizeof(double));
+    p.region_means = dbl[p.lb & 1];               // means of level lb - 1 (written by iteration l = lb - 1 into dbl[(l + 1) & 1])
+    dbl[p.lb & 1] = nullptr;
+    return VRB_OK;
+  };
+  const int rc = body();
+  if (d_max) cudaFree(d_max);
+  if (dbl[0]) cudaFree(dbl[0]);
+  if (dbl[1]) cudaFree(dbl[1]);
+  return rc;
+}
+
+// Levels 0 .. lb - 1 of the region.  brick: this rank's voxels [lo, hi); reach: how far (in voxels, along any axis) a cone sample may
+// lie from a lattice sample of the brick.  Level l is local while the region is aligned to 2^l, the brick cuts are, and the region
+// holds every level-l texel a cone fetch can touch: reach + two texels of 2^l voxels around the brick (or up to the volume's boundary).
+int VctPyramid::ensure_region(vrb_ctx* ctx, const int brick_lo[3], const int brick_hi[3], float reach) {
+  const Volume& v = ctx->vol;
+  cudaStream_t s = ctx->stream;
+  if (lb > 0 && vol_gen == v.generation && memcmp(blo, brick_lo, sizeof(blo)) == 0 && memcmp(bhi, brick_hi, sizeof(bhi)) == 0) return VRB_OK;
+  release();
+  VRB_REQUIRE(v.raw, VRB_ERR_NO_VOLUME, "supervoxels: no volume uploaded");
+  const int full[3] = {(int)v.fw, (int)v.fh, (int)v.fd}, org[3] = {(int)v.ox, (int)v.oy, (int)v.oz}, ext[3] = {(int)v.w, (int)v.h, (int)v.d};
+  int w = full[0], h = full[1], d = full[2];
+  n_levels = 0;
+  while ((long long)w * h * d >= 1 && n_levels < VCT_MAX_LEVELS) { flw[n_levels] = w; flh[n_levels] = h; fld[n_levels] = d; n_levels++; w /= 2; h /= 2; d /= 2; }
+  const int r = (int)std::ceil(reach);
+  int nl = 0;
+  for (int l = 0; l < n_levels; l++) {
+    const int t = 1 << l;
+    bool ok = true;
+    for (int a = 0; a < 3 && ok; a++) {
+      const int end = org[a] + ext[a];
+      ok = org[a] % t == 0 && (end % t == 0 || end == full[a]) && brick_lo[a] % t == 0 && (brick_hi[a] % t == 0 || brick_hi[a] == full[a]);
+      ok = ok && org[a] <= std::max(0, brick_lo[a] - r - 2 * t) && end >= std::min(full[a], brick_hi[a] + r + 2 * t);
+    }
+    if (!ok) break;
+    nl = l + 1;
+  }
+  VRB_REQUIRE(nl >= 2, VRB_ERR_INVALID,
+              "bricked supervoxel pyramid: the region (%d,%d,%d)+(%d,%d,%d) must hold the brick (%d,%d,%d)-(%d,%d,%d) plus %d + 4 ghost voxels per side "
+              "(cone reach + two texels of level 1) and be aligned to 2 voxels", org[0], org[1], org[2], ext[0], ext[1], ext[2],
+              brick_lo[0], brick_lo[1], brick_lo[2], brick_hi[0], brick_hi[1], brick_hi[2], r);
+  lb = std::min(nl, n_levels);
+  for (int l = 0; l < lb; l++) {
+    const int fl[3] = {flw[l], flh[l], fld[l]};
+    int dims[3];
+    for (int a = 0; a < 3; a++) {
+      const int end = org[a] + ext[a];
+      loff[l][a] = org[a] >> l;
+      dims[a] = (end == full[a] ? fl[a] : (end >> l)) - loff[l][a];
+    }
+    lw[l] = dims[0]; lh[l] = dims[1]; ld[l] = dims[2];
+  }
+  memcpy(blo, brick_lo, sizeof(blo)); memcpy(bhi, brick_hi, sizeof(bhi));
+  cudaEvent_t e0, e1;
+  VRB_CUDA(cudaEventCreate(&e0)); VRB_CUDA(cudaEventCreate(&e1));
+  VRB_CUDA(cudaEventRecord(e0, s));
+  int rc;
+  if (v.dtype == VRB_U8) { vol_max_density = 255.0; rc = build_region_levels<uint8_t>(ctx, *this, (const uint8_t*)v.raw, 256.0 - 1.0); }
+  else if (v.dtype == VRB_U16) { vol_max_density = 65535.0; rc = build_region_levels<uint16_t>(ctx, *this, (const uint16_t*)v.raw, 65536.0 - 1.0); }
+  else { vol_max_density = 1.0; rc = build_region_levels<float>(ctx, *this, (const float*)v.raw, 1.0); }
+  if (rc == VRB_OK) { cudaEventRecord(e1, s); cudaEventSynchronize(e1); cudaEventElapsedTime(&build_ms, e0, e1); }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  if (rc == VRB_OK) rc = build_quads(ctx, 0, lb);
+  if (rc != VRB_OK) { release(); return rc; }
+  vol_gen = v.generation;
+  region_ready = false;
+  return VRB_OK;
+}
+
+// This rank's brick-interior means of level lb - 1, written at their place in the caller's whole-level buffer (zero elsewhere: the
+// ranks' buffers then add up to the whole level, exactly — every cell is one value plus zeros).
+int VctPyramid::region_begin(vrb_ctx* ctx, double* dev_means, int dims[3], int* level, double* local_max) {
+  VRB_REQUIRE(lb >= 2 && region_means, VRB_ERR_INVALID, "vrb_vct_region_begin: no region pyramid (bricked volume + vrb_renderer_set_bricks first)");
+  const int l = lb - 1;
+  if (dims) { dims[0] = flw[l]; dims[1] = flh[l]; dims[2] = fld[l]; }
+  if (level) *level = l;
+  if (local_max) *local_max = local_max_std;
+  if (!dev_means) return VRB_OK;
+  const int full[3] = {flw[l], flh[l], fld[l]};
+  int lo[3], n[3];
+  for (int a = 0; a < 3; a++) {
+    lo[a] = blo[a] >> l;
+    const int hi = bhi[a] == (a == 0 ? flw[0] : (a == 1 ? flh[0] : fld[0])) ? full[a] : (bhi[a] >> l);
+    n[a] = hi - lo[a];
+  }
+  if (n[0] > 0 && n[1] > 0 && n[2] > 0) {
+    vct_block_copy_kernel<<<dim3((n[0] + 255) / 256, n[1], n[2]), 256, 0, ctx->stream>>>(region_means, lw[l], lh[l], loff[l][0], loff[l][1], loff[l][2],
+                                                                                       dev_means, full[0], full[1], lo[0], lo[1], lo[2], n[0], n[1], n[2]);
+    VRB_CUDA(cudaGetLastError());
+  }
+  VRB_CUDA(cudaStreamSynchronize(ctx->stream));
+  return VRB_OK;
+}
+
+// Levels lb .. n - 1 over the whole volume from the exchanged level lb - 1 means; global_max_std: maximum over the ranks of the
+// local_max_std vrb_vct_region_begin reported.
+int VctPyramid::region_finish(vrb_ctx* ctx, const double* dev_means, double global_max_std) {
+  VRB_REQUIRE(lb >= 2 && dev_means, VRB_ERR_INVALID, "vrb_vct_region_finish: no region pyramid or null buffer");
+  cudaStream_t s = ctx->stream;
+  for (int l = lb; l < n_levels; l++) {                       // a second call rebuilds the top
+    if (tex[l]) cudaDestroyTextureObject(tex[l]);
+    if (arr[l]) cudaFreeArray(arr[l]);
+    if (lin[l]) cudaFree(lin[l]);
+    tex[l] = 0; arr[l] = nullptr; lin[l] = nullptr;
+  }
+  unsigned long long* d_max = nullptr;
+  double* dbl[2] = {nullptr, nullptr};
+  auto body = [&]() -> int {
+    VRB_CUDA(cudaMalloc(&d_max, sizeof(unsigned long long)));
+    VRB_CUDA(cudaMemsetAsync(d_max, 0, sizeof(unsigned long long), s));
+    if (lb < n_levels) {
+      const size_t n1 = (size_t)flw[lb] * flh[lb] * fld[lb];
+      VRB_CUDA(cudaMalloc(&dbl[0], n1 * sizeof(double)));
+      VRB_CUDA(cudaMalloc(&dbl[1], std::max<size_t>(n1 / 8, 1) * sizeof(double)));
+    }
+    const double* child = dev_means;
+    for (int l = lb; l < n_levels; l++) {
+      lw[l] = flw[l]; lh[l] = flh[l]; ld[l] = fld[l]; loff[l][0] = loff[l][1] = loff[l][2] = 0;
+      const size_t nl = (size_t)lw[l] * lh[l] * ld[l];
+      VRB_CUDA(cudaMalloc(&lin[l], nl * sizeof(__half2)));
+      double* out = dbl[(l - lb) & 1];
+      vct_reduce_kernel<uint8_t><<<dim3((lw[l] + 255) / 256, lh[l], ld[l]), 256, 0, s>>>(nullptr, 1.0, child, flw[l - 1], flh[l - 1], lw[l], lh[l], ld[l], out, lin[l], d_max);
+      child = out;
+    }
+    VRB_CUDA(cudaGetLastError());
+    unsigned long long bits = 0;
+    VRB_CUDA(cudaMemcpyAsync(&bits, d_max, sizeof(bits), cudaMemcpyDeviceToHost, s));
+    VRB_CUDA(cudaStreamSynchronize(s));
+    double top = 0.0;
+    memcpy(&top, &bits, sizeof(double));
+    max_std = std::max(std::max(global_max_std, local_max_std), top);
+    return VRB_OK;
+  };
+  int rc = body();
+  if (d_max) cudaFree(d_max);
+  if (dbl[0]) cudaFree(dbl[0]);
+  if (dbl[1]) cudaFree(dbl[1]);
+  if (rc == VRB_OK) rc = build_quads(ctx, lb, n_levels);
+  if (rc != VRB_OK) return rc;
+  release_lut();
+  region_ready = true;
+  return VRB_OK;
+}
+
 int VctPyramid::ensure(vrb_ctx* ctx, bool with_lut) {
   const Volume& v = ctx->vol;
   const TransferFunction& t = ctx->tf;
   cudaStream_t s = ctx->stream;
-  if (!(n_levels && vol_gen == v.generation)) {
+  if (v.is_region()) {
+    VRB_REQUIRE(lb > 0 && region_ready && vol_gen == v.generation, VRB_ERR_INVALID,
+                "bricked volume: the supervoxel pyramid needs vrb_renderer_set_bricks, vrb_vct_region_begin, the exchange of the level means and vrb_vct_region_finish first");
+  } else if (!(n_levels && vol_gen == v.generation)) {
     release();
     VRB_REQUIRE(v.raw, VRB_ERR_NO_VOLUME, "supervoxels: no volume uploaded");
     int w = (int)v.w, h = (int)v.h, d = (int)v.d;
@@ -178,24 +401,9 @@ int VctPyramid::ensure(vrb_ctx* ctx, bool with_lut) {
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     if (rc != VRB_OK) { release(); return rc; }
-    cudaChannelFormatDesc desc = cudaCreateChannelDesc<uint4>();
-    cudaTextureDesc td{};
-    td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
-    td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
-    for (int l = 0; l < n_levels; l++) {
-      VRB_CUDA(cudaMalloc3DArray(&arr[l], &desc, make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]), cudaArraySurfaceLoadStore));
-      cudaResourceDesc rd{}; rd.resType = cudaResourceTypeArray; rd.res.array.array = arr[l];
-      cudaSurfaceObject_t dst = 0;
-      VRB_CUDA(cudaCreateSurfaceObject(&dst, &rd));
-      cudaError_t e = cudaCreateTextureObject(&tex[l], &rd, &td, nullptr);
-      if (e == cudaSuccess) {
-        vct_quad_kernel<<<dim3((lw[l] + 255) / 256, lh[l], ld[l]), 256, 0, s>>>((const unsigned*)lin[l], dst, lw[l], lh[l], ld[l]);
-        e = cudaGetLastError();
-        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
-      }
-      cudaDestroySurfaceObject(dst);
-      VRB_CUDA(e);
-    }
+    for (int l = 0; l < n_levels; l++) { flw[l] = lw[l]; flh[l] = lh[l]; fld[l] = ld[l]; loff[l][0] = loff[l][1] = loff[l][2] = 0; }
+    rc = build_quads(ctx, 0, n_levels);
+    if (rc != VRB_OK) { release(); return rc; }
     vol_gen = v.generation;
     release_lut();
   }
@@ -231,7 +439,8 @@ struct VctShader {
   static constexpr int PHONG_KIND = 1;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   struct Args {
     cudaTextureObject_t mip[VCT_MAX_LEVELS];
-    float mip_res[VCT_MAX_LEVELS][3];
+    float mip_res[VCT_MAX_LEVELS][3];          // dims of the whole level
+    float mip_off[VCT_MAX_LEVELS][3];          // texel origin of the stored array inside the level (region pyramids; else 0)
     int n_levels;
     const float* lut; int lut_w, lut_h;
     float cone_step, cone_rate, cone_initial, tan_apex, corr_fact, vol_max_density, vol_max_std;
@@ -259,7 +468,7 @@ struct VctShader {
     const float X = __fsub_rn(__fmul_rn(p.x, res.x), 0.5f), Y = __fsub_rn(__fmul_rn(p.y, res.y), 0.5f), Z = __fsub_rn(__fmul_rn(p.z, res.z), 0.5f);
     float fx = floorf(X), fy = floorf(Y), fz = floorf(Z);
     const float ax = fx < 0.0f ? 0.0f : __fsub_rn(X, fx), ay = fy < 0.0f ? 0.0f : __fsub_rn(Y, fy), az = __fsub_rn(Z, fz);
-    fx = fminf(fmaxf(fx, -1.0f), res.x); fy = fminf(fmaxf(fy, -1.0f), res.y); fz = fminf(fmaxf(fz, -1.0f), res.z);
+    fx = fminf(fmaxf(fx, -1.0f), res.x) - s.mip_off[l][0]; fy = fminf(fmaxf(fy, -1.0f), res.y) - s.mip_off[l][1]; fz = fminf(fmaxf(fz, -1.0f), res.z) - s.mip_off[l][2];
     const uint4 q0 = tex3D<uint4>(s.mip[l], fx + 0.5f, fy + 0.5f, fz + 0.5f);
     const uint4 q1 = tex3D<uint4>(s.mip[l], fx + 0.5f, fy + 0.5f, fz + 1.5f);
     auto H = [](unsigned u) { return __half22float2(*reinterpret_cast<const __half2*>(&u)); };
@@ -371,7 +580,9 @@ class VctRenderer : public RendererImpl {
     VRB_REQUIRE(v.tex != 0, VRB_ERR_NO_VOLUME, "RC1PVoxelConeTracingSGPU::Init: no volume texture");
     VRB_REQUIRE(ctx->tf.tex_rgbt != 0, VRB_ERR_INVALID, "RC1PVoxelConeTracingSGPU::Init: no transfer function");
     int rc = ensure_quad(ctx);
-    if (rc == VRB_OK) rc = pyr_.ensure(ctx, false);          // PreProcessSuperVoxels (:86-91); the table follows at the first Redraw
+    // PreProcessSuperVoxels (:86-91); the table follows at the first Redraw.  A bricked volume builds its pyramid once the brick is
+    // known (vrb_renderer_set_bricks -> vrb_vct_region_begin / _finish).
+    if (rc == VRB_OK && !v.is_region()) rc = pyr_.ensure(ctx, false);
     if (rc != VRB_OK) return rc;
     const double sx = v.sx, sy = v.sy, sz = v.sz;
     prm_.step_size = float((0.5f / sqrtf(3.0f)) * sqrt(sx * sx + sy * sy + sz * sz));
@@ -420,9 +631,51 @@ class VctRenderer : public RendererImpl {
     }
     return VRB_OK;
   }
+  // how far from a lattice sample a cone step can lie, in voxels along any axis (the recurrence of prepare_block)
+  float cone_reach_voxels() const {
+    float apex = prm_.cone_initial_step, step = prm_.cone_step_size, reach = 0.0f;
+    for (int is = 0; is < prm_.cone_number_of_samples; is++) { reach = std::max(reach, apex + step * 0.5f); apex += step; step *= prm_.cone_step_increase_rate; }
+    const Volume& v = ctx->vol;
+    return reach / std::min(v.sx, std::min(v.sy, v.sz));
+  }
+  int region_brick(int lo[3], int hi[3]) const {
+    const Volume& v = ctx->vol;
+    VRB_REQUIRE(v.is_region(), VRB_ERR_INVALID, "vrb_vct_region_*: the context holds a whole volume");
+    VRB_REQUIRE(brick_ranks > 0 && brick_rank >= 0, VRB_ERR_INVALID, "vrb_vct_region_*: vrb_renderer_set_bricks(rank, n, grid) first (one brick per rank)");
+    const int full[3] = {(int)v.fw, (int)v.fh, (int)v.fd};
+    const int idx[3] = {brick_rank % brick_grid[0], (brick_rank / brick_grid[0]) % brick_grid[1], brick_rank / (brick_grid[0] * brick_grid[1])};
+    for (int a = 0; a < 3; a++) {     // sort_last_cut: floor(i * res / g) voxels
+      lo[a] = (int)std::floor((float)idx[a] * (float)full[a] / (float)brick_grid[a]);
+      hi[a] = idx[a] == brick_grid[a] - 1 ? full[a] : (int)std::floor((float)(idx[a] + 1) * (float)full[a] / (float)brick_grid[a]);
+    }
+    return VRB_OK;
+  }
+  int region_begin(double* dev_means, int dims[3], int* level, double* local_max) {
+    int lo[3], hi[3];
+    int rc = region_brick(lo, hi);
+    if (rc == VRB_OK) rc = pyr_.ensure_region(ctx, lo, hi, cone_reach_voxels());
+    if (rc == VRB_OK) rc = pyr_.region_begin(ctx, dev_means, dims, level, local_max);
+    return rc;
+  }
+  int region_finish(const double* dev_means, double global_max) { return pyr_.region_finish(ctx, dev_means, global_max); }
+
   int redraw(int) override {
     VRB_REQUIRE(built && have_cam, VRB_ERR_INVALID, "RC1PVoxelConeTracingSGPU::Redraw before Init/Update");
     int rc = ensure_quad(ctx);
+    if (rc == VRB_OK && ctx->vol.is_region()) {
+      // the region must still hold everything this rank's samples and cones touch (the cone parameters may have changed)
+      int lo[3], hi[3];
+      rc = region_brick(lo, hi);
+      VRB_REQUIRE(rc != VRB_OK || !prm_.use_light_cache, VRB_ERR_UNSUPPORTED, "bricked volumes render in sort-last mode only");
+      if (rc == VRB_OK) {
+        const Volume& v = ctx->vol;
+        const int org[3] = {(int)v.ox, (int)v.oy, (int)v.oz}, ext[3] = {(int)v.w, (int)v.h, (int)v.d}, full[3] = {(int)v.fw, (int)v.fh, (int)v.fd};
+        const int r = (int)std::ceil(cone_reach_voxels());
+        for (int a = 0; a < 3; a++)
+          VRB_REQUIRE(org[a] <= std::max(0, lo[a] - r - 4) && org[a] + ext[a] >= std::min(full[a], hi[a] + r + 4), VRB_ERR_INVALID,
+                      "bricked volume: the region's ghost layer is thinner than the cone reach (%d voxels + 4)", r);
+      }
+    }
     if (rc == VRB_OK) rc = pyr_.ensure(ctx, true);
     if (rc != VRB_OK) return rc;
     MarchArgs a{};
@@ -432,7 +685,10 @@ class VctRenderer : public RendererImpl {
     if (prm_.count_samples == 2 || prm_.count_samples == 3) a.count_mode = prm_.count_samples;   // shaded samples / cone steps
     VctShader::Args s{};
     s.n_levels = pyr_.n_levels;
-    for (int l = 0; l < pyr_.n_levels; l++) { s.mip[l] = pyr_.tex[l]; s.mip_res[l][0] = (float)pyr_.lw[l]; s.mip_res[l][1] = (float)pyr_.lh[l]; s.mip_res[l][2] = (float)pyr_.ld[l]; }
+    for (int l = 0; l < pyr_.n_levels; l++) {
+      s.mip[l] = pyr_.tex[l]; s.mip_res[l][0] = (float)pyr_.flw[l]; s.mip_res[l][1] = (float)pyr_.flh[l]; s.mip_res[l][2] = (float)pyr_.fld[l];
+      for (int i = 0; i < 3; i++) s.mip_off[l][i] = (float)pyr_.loff[l][i];
+    }
     s.lut = pyr_.lut; s.lut_w = pyr_.lut_w; s.lut_h = pyr_.lut_h;
     s.cone_step = prm_.cone_step_size; s.cone_rate = prm_.cone_step_increase_rate; s.cone_initial = prm_.cone_initial_step;
     s.tan_apex = std::tan(prm_.cone_apex_angle * 3.14159265358979323846f / 180.0f);                  // vctrenderer.cpp:145 (float)
@@ -456,6 +712,14 @@ RendererImpl* make_vct(vrb_ctx* ctx) { return new VctRenderer(ctx); }
 int vct_read_level(RendererImpl* impl, int level, float* host_rg, int dims[3]) {
   VRB_REQUIRE(impl->kind == VRB_VCT, VRB_ERR_INVALID, "vrb_vct_read_level: not a voxel-cone-tracing renderer");
   return static_cast<VctRenderer*>(impl)->read_level(level, host_rg, dims);
+}
+int vct_region_begin(RendererImpl* impl, double* dev_means, int dims[3], int* level, double* local_max) {
+  VRB_REQUIRE(impl->kind == VRB_VCT, VRB_ERR_INVALID, "vrb_vct_region_begin: not a voxel-cone-tracing renderer");
+  return static_cast<VctRenderer*>(impl)->region_begin(dev_means, dims, level, local_max);
+}
+int vct_region_finish(RendererImpl* impl, const double* dev_means, double global_max) {
+  VRB_REQUIRE(impl->kind == VRB_VCT, VRB_ERR_INVALID, "vrb_vct_region_finish: not a voxel-cone-tracing renderer");
+  return static_cast<VctRenderer*>(impl)->region_finish(dev_means, global_max);
 }
 int vct_read_lut(RendererImpl* impl, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms) {
   VRB_REQUIRE(impl->kind == VRB_VCT, VRB_ERR_INVALID, "vrb_vct_read_lut: not a voxel-cone-tracing renderer");

@@ -141,23 +141,43 @@ static int build_volume_texture(vrb_ctx* ctx) {
   return VRB_OK;
 }
 
-static int upload_volume_common(vrb_ctx* ctx, const void* src, bool src_on_device, int dtype, int64_t w, int64_t h,
-                                int64_t d, float sx, float sy, float sz) {
-  VRB_REQUIRE(ctx && src, VRB_ERR_INVALID, "vrb_volume_upload: null argument");
+int begin_volume_upload(vrb_ctx* ctx, int dtype, int64_t w, int64_t h, int64_t d, const int64_t full[3], const int64_t origin[3], float sx, float sy, float sz) {
+  VRB_REQUIRE(ctx, VRB_ERR_INVALID, "vrb_volume_upload: null context");
   VRB_REQUIRE(dtype >= VRB_U8 && dtype <= VRB_F32, VRB_ERR_INVALID, "vrb_volume_upload: bad dtype %d", dtype);
   VRB_REQUIRE(w > 0 && h > 0 && d > 0 && w <= 16384 && h <= 16384 && d <= 16384, VRB_ERR_INVALID,
               "vrb_volume_upload: bad size %lldx%lldx%lld", (long long)w, (long long)h, (long long)d);
+  VRB_REQUIRE(full[0] <= 16384 && full[1] <= 16384 && full[2] <= 16384 && origin[0] >= 0 && origin[1] >= 0 && origin[2] >= 0 &&
+              origin[0] + w <= full[0] && origin[1] + h <= full[1] && origin[2] + d <= full[2], VRB_ERR_INVALID,
+              "vrb_volume_upload: region %lldx%lldx%lld at (%lld, %lld, %lld) does not lie inside %lldx%lldx%lld", (long long)w, (long long)h, (long long)d,
+              (long long)origin[0], (long long)origin[1], (long long)origin[2], (long long)full[0], (long long)full[1], (long long)full[2]);
   VRB_CUDA(cudaSetDevice(ctx->device));
   release_volume(ctx->vol);
   Volume& v = ctx->vol;
   v.w = w; v.h = h; v.d = d; v.sx = sx; v.sy = sy; v.sz = sz; v.dtype = dtype;
+  v.fw = full[0]; v.fh = full[1]; v.fd = full[2]; v.ox = origin[0]; v.oy = origin[1]; v.oz = origin[2];
   const size_t bytes = (size_t)w * h * d * v.voxel_bytes();
-  VRB_CUDA(cudaMalloc(&v.raw, bytes));
-  VRB_CUDA(cudaMemcpyAsync(v.raw, src, bytes, src_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
-  int rc = build_volume_texture(ctx);
-  if (rc != VRB_OK) { release_volume(ctx->vol); return rc; }
-  v.generation++;
+  cudaError_t e = cudaMalloc(&v.raw, bytes);
+  if (e != cudaSuccess) { set_error("vrb_volume_upload: %zu bytes of voxels: %s", bytes, cudaGetErrorString(e)); release_volume(ctx->vol); return VRB_ERR_CUDA; }
   return VRB_OK;
+}
+
+int finish_volume_upload(vrb_ctx* ctx) {
+  const int rc = build_volume_texture(ctx);
+  if (rc != VRB_OK) { release_volume(ctx->vol); return rc; }
+  ctx->vol.generation++;
+  return VRB_OK;
+}
+
+static int upload_volume_common(vrb_ctx* ctx, const void* src, bool src_on_device, int dtype, int64_t w, int64_t h,
+                                int64_t d, float sx, float sy, float sz, const int64_t* full = nullptr, const int64_t* origin = nullptr) {
+  VRB_REQUIRE(ctx && src, VRB_ERR_INVALID, "vrb_volume_upload: null argument");
+  const int64_t whole[3] = {w, h, d}, zero[3] = {0, 0, 0};
+  int rc = begin_volume_upload(ctx, dtype, w, h, d, full ? full : whole, origin ? origin : zero, sx, sy, sz);
+  if (rc != VRB_OK) return rc;
+  Volume& v = ctx->vol;
+  const size_t bytes = (size_t)w * h * d * v.voxel_bytes();
+  VRB_CUDA(cudaMemcpyAsync(v.raw, src, bytes, src_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
+  return finish_volume_upload(ctx);
 }
 
 }  // namespace vrb
@@ -224,6 +244,21 @@ int vrb_volume_upload(vrb_ctx* ctx, const void* voxels, int dtype, int64_t w, in
 
 int vrb_volume_upload_device(vrb_ctx* ctx, const void* dev_voxels, int dtype, int64_t w, int64_t h, int64_t d, float sx, float sy, float sz) {
   return upload_volume_common(ctx, dev_voxels, true, dtype, w, h, d, sx, sy, sz);
+}
+
+int vrb_volume_upload_region(vrb_ctx* ctx, const void* voxels, int on_device, int dtype, const int64_t region[3], const int64_t origin[3],
+                             const int64_t full[3], float sx, float sy, float sz) {
+  VRB_REQUIRE(region && origin && full, VRB_ERR_INVALID, "vrb_volume_upload_region: null argument");
+  return upload_volume_common(ctx, voxels, on_device != 0, dtype, region[0], region[1], region[2], sx, sy, sz, full, origin);
+}
+
+int vrb_volume_read_raw(vrb_ctx* ctx, void* host_out) {
+  VRB_REQUIRE(ctx && host_out, VRB_ERR_INVALID, "vrb_volume_read_raw: null argument");
+  Volume& v = ctx->vol;
+  VRB_REQUIRE(v.raw, VRB_ERR_NO_VOLUME, "vrb_volume_read_raw: no volume uploaded");
+  VRB_CUDA(cudaMemcpyAsync(host_out, v.raw, (size_t)v.w * v.h * v.d * v.voxel_bytes(), cudaMemcpyDeviceToHost, ctx->stream));
+  VRB_CUDA(cudaStreamSynchronize(ctx->stream));
+  return VRB_OK;
 }
 
 int vrb_volume_read_r16f(vrb_ctx* ctx, float* host_out) {

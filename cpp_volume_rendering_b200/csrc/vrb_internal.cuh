@@ -33,7 +33,12 @@ void set_error(const char* fmt, ...);
 // Volume resident in HBM: the R16F texture the ray casters sample (GL_LINEAR, CLAMP_TO_EDGE,
 // normalised coordinates) plus the raw voxels for the precompute stages.
 struct Volume {
-  int64_t w = 0, h = 0, d = 0;
+  int64_t w = 0, h = 0, d = 0;          // stored voxels: the whole volume, or the region of a bricked one
+  // Region (bricked) volumes (vrb_volume_upload_region / vrb_volume_synth): this context holds only the voxels
+  // [ox, ox + w) x [oy, oy + h) x [oz, oz + d) of an fw x fh x fd volume — a sort-last brick plus its ghost layers.  The box the rays
+  // intersect, the sample lattice and every normalised coordinate stay those of the full volume; fetches subtract the origin.
+  int64_t fw = 0, fh = 0, fd = 0, ox = 0, oy = 0, oz = 0;
+  bool is_region() const { return w != fw || h != fh || d != fd; }
   float sx = 1, sy = 1, sz = 1;
   int dtype = VRB_U8;
   void* raw = nullptr;                  // device copy of the voxel array (x fastest)
@@ -236,6 +241,8 @@ int dos_read_sections(RendererImpl* impl, int which, float* rgba, int cap, int* 
 int sbtm_read_occlusion(RendererImpl* impl, float* host, int* n_slices);
 int vct_read_level(RendererImpl* impl, int level, float* host_rg, int dims[3]);
 int vct_read_lut(RendererImpl* impl, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms);
+int vct_region_begin(RendererImpl* impl, double* dev_means, int dims[3], int* level, double* local_max);
+int vct_region_finish(RendererImpl* impl, const double* dev_means, double global_max);
 int iso_read_blocks(RendererImpl* impl, float* host_min, float* host_max);
 int iso_read_gbuffers(RendererImpl* impl, float* host_pos, float* host_nrm);
 
@@ -248,6 +255,10 @@ int build_gradient(vrb_ctx* ctx, int model, float* host_rgb);
 
 // vrb_ctx.cu: builds Volume::tex_quad on the context stream if it does not exist yet.
 int ensure_quad(vrb_ctx* ctx);
+// vrb_ctx.cu: replaces the context's volume by w x h x d voxels at `origin` of a `full` volume; raw == nullptr allocates the device
+// array and leaves it to the caller to fill (k_synth.cu) before finish_volume_upload builds the textures.
+int begin_volume_upload(vrb_ctx* ctx, int dtype, int64_t w, int64_t h, int64_t d, const int64_t full[3], const int64_t origin[3], float sx, float sy, float sz);
+int finish_volume_upload(vrb_ctx* ctx);
 
 // k_frame.cu
 int frame_to_rgb8_over_white(cudaStream_t s, const __half* frame, int64_t n_pixels, uint8_t* dev_out);

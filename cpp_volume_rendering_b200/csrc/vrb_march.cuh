@@ -26,6 +26,9 @@ struct MarchArgs {
   uint2* frame; uint2* peer[RendererImpl::MAX_PEERS]; int n_peers;
   PeerSignal sig;
   unsigned long long* samples;
+  // region (bricked) volumes: normalised coordinate of the stored region = p * vscale + vbias (1 and 0 for a whole volume), texel
+  // offset of the region inside the volume for the point-sampled footprint texture
+  float vscale[3], vbias[3], voff[3];
   int count_mode;                    // COUNT kernels: 1 = march-loop iterations, 2 = shaded (non-transparent) samples, 3 = the shader's own unit
                                      // (VCT: cone steps inside the volume), added to `samples` by the shader
   int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; const int* tile_order; unsigned* queue;
@@ -130,10 +133,10 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
         if (alive && inside) {
           const f3 p = mul3(tx, inv_sizes);
           if (COUNT && a.count_mode == 1) nsamp++;
-          const float d_hw = tex3D<float>(a.vol, p.x, p.y, p.z);
+          const float d_hw = tex3D<float>(a.vol, fmaf(p.x, a.vscale[0], a.vbias[0]), fmaf(p.y, a.vscale[1], a.vbias[1]), fmaf(p.z, a.vscale[2], a.vbias[2]));
           int j = (int)fminf(fmaxf(fmaf(d_hw, tfn, -0.5f), 0.0f), tfmax);
           if ((s_mask[j >> 5] >> (j & 31)) & 1u) {
-            const float density = tex3d_f32_exact(a.vol_quad, p, res);
+            const float density = tex3d_f32_exact(a.vol_quad, p, res, mk3(a.voff[0], a.voff[1], a.voff[2]));
             const float u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
             j = (int)u;
             const float w = u - (float)j;
@@ -212,7 +215,9 @@ inline bool fill_march_args(const RendererImpl& r, float step, int apply_occlusi
   a.vol = v.tex; a.vol_quad = v.tex_quad;
   a.tf_lin = (const uint2*)t.lin_rgbt; a.vis_mask = t.vis_mask; a.tf_n = t.n; a.vis_words = t.vis_words;
   a.width = r.width; a.height = r.height;
-  a.res[0] = (float)v.w; a.res[1] = (float)v.h; a.res[2] = (float)v.d;
+  a.res[0] = (float)v.fw; a.res[1] = (float)v.fh; a.res[2] = (float)v.fd;          // the box is the whole volume's, also for a region
+  const float lres[3] = {(float)v.w, (float)v.h, (float)v.d}, org[3] = {(float)v.ox, (float)v.oy, (float)v.oz};
+  for (int i = 0; i < 3; i++) { a.vscale[i] = a.res[i] / lres[i]; a.vbias[i] = -org[i] / lres[i]; a.voff[i] = org[i]; }
   a.scales[0] = v.sx; a.scales[1] = v.sy; a.scales[2] = v.sz;
   for (int i = 0; i < 3; i++) { a.sizes[i] = a.res[i] * a.scales[i]; a.eye[i] = r.cam.eye[i]; a.light_pos[i] = r.light.position[i]; }
   for (int i = 0; i < 9; i++) a.lookat[i] = r.cam.lookat[i];

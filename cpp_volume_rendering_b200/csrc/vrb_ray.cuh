@@ -71,13 +71,16 @@ __device__ __forceinline__ f3 max3(f3 a, f3 b) { return mk3(gmax(a.x, b.x), gmax
 // texture(TexVolume, p) on the R16F volume, GL_LINEAR / CLAMP_TO_EDGE with float32 weights, bit-identical to
 // oracle Tex3D::linear: two point fetches of the footprint texture (Volume::tex_quad) give the 2x2 texel quads of
 // slices i0z and i1z; below texel 0 GL clamps both i0 and i1 to 0, which a zero weight reproduces exactly.
-__device__ __forceinline__ float tex3d_f32_exact(cudaTextureObject_t quad, f3 p, f3 res) {
+// off: texel origin of a region (bricked) volume inside the whole one (integers; 0 for a whole volume): the texel indices are those of
+// the whole volume, the stored array starts at `off`.  A region holds every texel its samples touch (ghost layer), and where it ends at
+// the volume's own boundary the array's clamp addressing is the volume's CLAMP_TO_EDGE.
+__device__ __forceinline__ float tex3d_f32_exact(cudaTextureObject_t quad, f3 p, f3 res, f3 off = f3{0.0f, 0.0f, 0.0f}) {
   const float X = __fsub_rn(__fmul_rn(p.x, res.x), 0.5f), Y = __fsub_rn(__fmul_rn(p.y, res.y), 0.5f);
   const float Z = __fsub_rn(__fmul_rn(p.z, res.z), 0.5f);
   float fx = floorf(X), fy = floorf(Y), fz = floorf(Z);
   const float ax = fx < 0.0f ? 0.0f : __fsub_rn(X, fx), ay = fy < 0.0f ? 0.0f : __fsub_rn(Y, fy), az = __fsub_rn(Z, fz);
   // clamp before the +0.5 so that far-away coordinates stay finite texel addresses
-  fx = fminf(fmaxf(fx, -1.0f), res.x); fy = fminf(fmaxf(fy, -1.0f), res.y); fz = fminf(fmaxf(fz, -1.0f), res.z);
+  fx = fminf(fmaxf(fx, -1.0f), res.x) - off.x; fy = fminf(fmaxf(fy, -1.0f), res.y) - off.y; fz = fminf(fmaxf(fz, -1.0f), res.z) - off.z;
   const uint2 q0 = tex3D<uint2>(quad, fx + 0.5f, fy + 0.5f, fz + 0.5f);
   const uint2 q1 = tex3D<uint2>(quad, fx + 0.5f, fy + 0.5f, fz + 1.5f);
   const float2 a0 = __half22float2(*reinterpret_cast<const __half2*>(&q0.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&q0.y));

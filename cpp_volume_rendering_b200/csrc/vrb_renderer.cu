@@ -103,7 +103,7 @@ int LightCache::read(cudaStream_t s, float* host_rg, int out_dims[3], float* ms)
 
 int RendererImpl::ensure_lattice(float step) {
   const Volume& v = ctx->vol;
-  const double sx = (double)v.w * v.sx, sy = (double)v.h * v.sy, sz = (double)v.d * v.sz;
+  const double sx = (double)v.fw * v.sx, sy = (double)v.fh * v.sy, sz = (double)v.fd * v.sz;
   const double need = std::sqrt(sx * sx + sy * sy + sz * sz) / (double)step + 8.0;
   VRB_REQUIRE(step > 0.0f && need < (double)(1 << 24), VRB_ERR_INVALID, "march lattice of %.0f samples", need);
   const int n = (int)need;
@@ -240,6 +240,8 @@ int vrb_renderer_init(vrb_renderer* r, int width, int height) {
   RendererImpl* p = r->impl;
   VRB_CUDA(cudaSetDevice(p->ctx->device));
   if (p->built) { p->clean(); p->built = false; }
+  VRB_REQUIRE(!p->ctx->vol.is_region() || p->kind == VRB_VCT, VRB_ERR_UNSUPPORTED,
+              "vrb_renderer_init: the context holds a region of a bricked volume: only the voxel-cone-tracing renderer's sort-last mode renders those");
   p->screen_w = width; p->screen_h = height;
   int rw = 0, rh = 0;
   int rc = p->render_size(width, height, &rw, &rh);
@@ -611,6 +613,17 @@ int vrb_vct_read_level(vrb_renderer* r, int level, float* host_rg, int dims[3]) 
 int vrb_vct_read_lut(vrb_renderer* r, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms) {
   VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_vct_read_lut: null renderer");
   return vct_read_lut(r->impl, host, dims, max_std, n_levels, build_ms);
+}
+
+int vrb_vct_region_begin(vrb_renderer* r, double* dev_level_means, int dims[3], int* level, double* local_max_std) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_vct_region_begin: null renderer");
+  VRB_CUDA(cudaSetDevice(r->impl->ctx->device));
+  return vct_region_begin(r->impl, dev_level_means, dims, level, local_max_std);
+}
+int vrb_vct_region_finish(vrb_renderer* r, const double* dev_level_means, double global_max_std) {
+  VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_vct_region_finish: null renderer");
+  VRB_CUDA(cudaSetDevice(r->impl->ctx->device));
+  return vct_region_finish(r->impl, dev_level_means, global_max_std);
 }
 
 int vrb_sbtm_read_occlusion(vrb_renderer* r, float* host, int* n_slices) {

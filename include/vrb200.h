@@ -232,6 +232,21 @@ int vrb_volume_gradient(vrb_ctx* ctx, int model, float* host_rgb);
 /* Same, voxels already resident in DEVICE memory (used when a step's inputs must be in HBM). */
 int vrb_volume_upload_device(vrb_ctx* ctx, const void* dev_voxels, int dtype, int64_t w, int64_t h, int64_t d,
                              float sx, float sy, float sz);
+/* Bricked (region) volumes, for volumes that do not fit one GPU (BASELINE config 5: 2048^3) — no reference counterpart:
+ * the reference holds one volume on one GPU and its `int` voxel indices overflow at this size (libs/volvis_utils/reader.cpp:64-93,
+ * structuredgridvolume.cpp:133).  The context stores only region[0] x [1] x [2] voxels starting at voxel `origin` of a
+ * full[0] x [1] x [2] volume: a sort-last brick plus ghost layers.  The bounding box, the sample lattice and all normalised
+ * coordinates remain those of the whole volume.  Only the voxel-cone-tracing renderer in sort-last mode (vrb_renderer_set_bricks
+ * with one brick per rank) renders a region; its ghost layer must cover the cone reach (checked at Redraw).
+ * voxels: host (on_device = 0) or device memory, x fastest, region-sized. */
+int vrb_volume_upload_region(vrb_ctx* ctx, const void* voxels, int on_device, int dtype, const int64_t region[3], const int64_t origin[3],
+                             const int64_t full[3], float sx, float sy, float sz);
+/* The synthetic volume of SURVEY.md 8(d) (host twin: vrbh_synth_volume of libvrbhost.so, bit-identical) generated on the device,
+ * whole (origin = region = NULL) or one region of it: config 5's volume is generated per brick and never exists on the host. */
+int vrb_volume_synth(vrb_ctx* ctx, int dtype, const int64_t full[3], uint64_t seed, const int64_t* origin, const int64_t* region,
+                     float sx, float sy, float sz);
+/* Test hook: the stored voxels (whole volume or region), in their dtype, x fastest. */
+int vrb_volume_read_raw(vrb_ctx* ctx, void* host_out);
 /* Read back the R16F texture contents as float32 (test hook for bit-exactness of the quantisation). */
 int vrb_volume_read_r16f(vrb_ctx* ctx, float* host_out);
 
@@ -326,6 +341,16 @@ int vrb_ebs_read_sat(vrb_renderer* r, float* host, int dims[3], float* build_ms)
  *             standard deviation (double, unrounded), the number of levels and the device time of the pyramid build.
  * Any output pointer may be NULL. */
 int vrb_vct_read_level(vrb_renderer* r, int level, float* host_rg, int dims[3]);
+/* Supervoxel pyramid of a bricked volume (PreProcessSuperVoxels over bricks; the one exchange step of the path).  After
+ * vrb_renderer_set_bricks: _begin builds the levels this rank can build from its region (levels 0 .. L, while the region is aligned
+ * and its ghost covers the cones' fetches at that level) and reports L, the dims of the WHOLE level L and the largest standard
+ * deviation it saw; with dev_level_means != NULL (device memory, dims[0]*dims[1]*dims[2] doubles, zero-filled by the caller) it
+ * also writes the level-L means of its brick at their place.  The host sums the buffers of all ranks (every cell is one rank's value
+ * plus zeros: exact; torch.distributed all_reduce over NCCL here) and takes the maximum of the deviations; _finish builds the
+ * levels above L for the whole volume from the summed buffer on every rank, and the pre-integration table's extent from the
+ * global maximum — all values bit-identical to the pyramid of the unbricked volume. */
+int vrb_vct_region_begin(vrb_renderer* r, double* dev_level_means, int dims[3], int* level, double* local_max_std);
+int vrb_vct_region_finish(vrb_renderer* r, const double* dev_level_means, double global_max_std);
 int vrb_vct_read_lut(vrb_renderer* r, float* host, int dims[2], double* max_std, int* n_levels, float* build_ms);
 
 /* Test / measurement hooks for K6 / K7 of a VRB_DOS_CONE renderer.
@@ -369,8 +394,10 @@ int vrb_renderer_set_partition(vrb_renderer* r, int rank, int n_ranks, int tile)
  * set_peers(..., VRB_GATHER_ALL), then Update / Redraw / wait_peers per frame.
  * rank = -1: this one renderer marches every brick in turn and composites all strips (single-GPU form, no peers).
  * n_ranks = 0 (grid may be NULL): back to the unpartitioned renderer.
- * The frame equals the single-GPU frame up to the blending order of the partials (same samples, same termination).  The shading
- * pyramids / tables and, in this version, the classification volume stay replicated on every rank. */
+ * The frame equals the single-GPU frame up to the blending order of the partials (same samples, same termination).  With a whole
+ * volume in every context the shading pyramids / tables and the classification volume are replicated; with a region volume
+ * (vrb_volume_upload_region / vrb_volume_synth, VRB_VCT only) each rank holds its brick plus ghost layers of the volume and of the
+ * pyramid's fine levels (vrb_vct_region_begin / _finish). */
 int vrb_renderer_set_bricks(vrb_renderer* r, int rank, int n_ranks, const int grid[3]);
 
 /* Fused gather: instead of a collective after the launch, the render kernels store every finished pixel into the

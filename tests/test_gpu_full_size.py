@@ -13,13 +13,14 @@ pytestmark = pytest.mark.gpu
 
 def _compare(got, got8, ref, tag):
     ref8 = O.blit_over_white(ref)
-    # a shader that divides 0 by 0 (EBS: a shadow box of zero volume, ebs_ray_bbox_marching.comp:126-160) stores NaN: the same pixels
-    # must be NaN on both sides, the bar applies to the rest
-    nan = np.isnan(ref)
-    assert np.array_equal(np.isnan(got), nan), f"{tag}: NaN pixels differ ({int(np.isnan(got).sum())} vs {int(nan.sum())})"
-    if nan.any():
-        print(f"{tag}: {int(nan.any(axis=2).sum())} pixels are NaN on both sides")
-    d16 = float(np.abs(np.where(nan, 0.0, got) - np.where(nan, 0.0, ref)).max()) * 255.0
+    # a shader that divides by zero (EBS: a shadow box of zero volume, ebs_ray_bbox_marching.comp:126-160) stores NaN or inf: the same
+    # pixels must hold the same non-finite values on both sides, the bar applies to the rest
+    bad = ~np.isfinite(ref)
+    assert np.array_equal(~np.isfinite(got), bad) and np.array_equal(got[bad], ref[bad], equal_nan=True), \
+        f"{tag}: non-finite pixels differ ({int((~np.isfinite(got)).sum())} vs {int(bad.sum())} values)"
+    if bad.any():
+        print(f"{tag}: {int(bad.any(axis=2).sum())} pixels are non-finite (NaN / inf), identically on both sides")
+    d16 = float(np.abs(np.where(bad, 0.0, got) - np.where(bad, 0.0, ref)).max()) * 255.0
     d8 = metrics.max_abs_delta(got8, ref8)
     s = metrics.ssim(got8, ref8)
     print(f"{tag}: max|d| rgba16f {d16:.3f}/255, rgb8 {d8:.0f}/255, SSIM {s:.6f}, covered {(ref[..., 3] > 0).mean():.3f}")
