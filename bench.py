@@ -379,6 +379,7 @@ def run_cuda(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_ms = float(t.item())
 
+    line = None
     if rank == 0:
         import ctypes
         tex_peak = ctx.tex_peak()
@@ -427,7 +428,6 @@ def run_cuda(args):
             v, cores, total, secs = cpu_frame(vox, table, cam, repeats=2)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"full {IMG_W}x{IMG_H} frame ({total} samples, best of 2, {secs:.2f} s), oracle/liboracle.so OpenMP over rows"}
-        emit(line)
     if world > 1:
         barrier()
         r.set_peers([], rank, _capi.VRB_GATHER_NONE)
@@ -435,6 +435,41 @@ def run_cuda(args):
     if r is not None:
         r.close()
     ctx.close()
+    # BASELINE config 5 beside the headline whenever the path has ranks to shard over: sort-last VCT on the bricked 2048^3 volume
+    # (1536^3 at N = 2) at 3840x2160 and the slice-based renderer as N replicas (tools/bench_c5.py).  Every rank takes part.
+    if world > 1 and not args.no_c5:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_c5
+        try:
+            c5 = bench_c5.run(world, rank, local, steps=3, warmup=1)
+        except Exception as e:  # noqa: BLE001  (reported in the line, the headline stands)
+            c5 = {"error": f"{type(e).__name__}: {e}"}
+        if rank == 0:
+            line.setdefault("extras", {})["c5"] = c5
+    if rank == 0:
+        emit(line)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_c5(args):
+    """--config c5: BASELINE config 5 alone (tools/bench_c5.py), as a bench line: value = VCT march samples per second, all ranks."""
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import bench_c5
+    world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    res = bench_c5.run(world, rank, local, steps=max(args.steps, 2), warmup=max(min(args.warmup, 2), 1))
+    if rank == 0:
+        v = res["vct"]
+        emit({"metric": METRIC, "value": v["samples_per_s"], "unit": UNIT, "n_gpus": world, "steps": max(args.steps, 2), "warmup": max(min(args.warmup, 2), 1),
+              "ms_per_step": v["ms_per_frame"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+              "config": {"workload": res["workload"], "volume": res["volume"], "image": res["image"], "step_voxels": STEP, "tf": "bonsai_01.tf1d",
+                         "camera": "Initial State (N,N,2N)", "l2_policy": "inputs_larger_than_l2"},
+              "measured": res})
     if world > 1:
         dist.destroy_process_group()
 
@@ -450,6 +485,8 @@ def main():
     ap.add_argument("--exact", type=int, default=1, help="float32 re-filtering of possibly-visible samples")
     ap.add_argument("--no-cpu", action="store_true", help="omit the cpu_baseline leg")
     ap.add_argument("--depth-split", type=int, default=-1, help="lanes per ray (0/1, 2, 4, 8); -1 = by the number of GPUs")
+    ap.add_argument("--no-c5", action="store_true", help="omit extras.c5 (config 5 on the bricked 2048^3 volume) at N >= 2")
+    ap.add_argument("--config", default="c2", choices=["c2", "c5"], help="c2: the headline (RayCasting1Pass, config 2); c5: config 5 alone")
     args = ap.parse_args()
     # The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on the first
     # collective), so everything but the result line goes to stderr: fd 1 is pointed at fd 2 and the line is written to the
@@ -460,6 +497,8 @@ def main():
     os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
+    elif args.config == "c5":
+        run_c5(args)
     else:
         run_cuda(args)
 
