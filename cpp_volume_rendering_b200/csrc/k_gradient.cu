@@ -1,6 +1,7 @@
 // Gradient texture for the Blinn-Phong path (DataManager::GenerateStructuredGradientTexture, datamanager.cpp:332-352):
 //   model 1  GenerateSobelFeldmanGradientTexture  libs/volvis_utils/utils.cpp:287-350
 //   model 2  GenerateGradientTexture (defaults: sample size 1, no filter, normalised)  utils.cpp:146-285
+//   model 3  GenerateGradientWithComputeShader  datamanager.cpp:623-718 + sobelfeldman_generator.comp (float32, from the R16F texture)
 // The reference evaluates both on the CPU in double; the kernels keep double and the reference's term order with
 // single-rounding intrinsics, so the RGB16F texels are bit-identical to the CPU build.  Stored as an RGBA16F 3D
 // texture (CUDA has no 3-channel format), GL_LINEAR / CLAMP_TO_EDGE, normalised coordinates.
@@ -47,6 +48,34 @@ __global__ void __launch_bounds__(128) gradient_kernel(const T* __restrict__ v, 
   }
 }
 
+// model 3 — COMPUTE_SHADER_SOBEL: main() of shader/_gradient_shading/sobelfeldman_generator.comp:22-66 (the variant the reference runs on
+// the GPU, DataManager::GenerateGradientWithComputeShader, datamanager.cpp:623-718).  The shader samples the R16F volume texture at
+// texel centres (the texel itself; 0 outside the grid) and accumulates in float32 in the written order; one rounding per operation.
+__global__ void __launch_bounds__(128) gradient_sobel_cs_kernel(cudaTextureObject_t vol_pt, int w, int h, int d, cudaSurfaceObject_t dst, float* __restrict__ lin_rgb) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
+  if (x >= w) return;
+  auto G = [&](int px, int py, int pz) -> float {
+    if (px < 0 || py < 0 || pz < 0 || px > w - 1 || py > h - 1 || pz > d - 1) return 0.0f;      // GetScalarValue (:13-20)
+    return tex3D<float>(vol_pt, (float)px + 0.5f, (float)py + 0.5f, (float)pz + 0.5f);
+  };
+  float sx = 0.0f, sy = 0.0f, sz = 0.0f;
+  for (int v1 = -1; v1 < 2; v1++)
+    for (int v2 = -1; v2 < 2; v2++) {
+      const int e = (v1 < 0 ? -v1 : v1) + (v2 < 0 ? -v2 : v2);
+      const float wp = e == 0 ? 4.0f : (e == 1 ? 2.0f : 1.0f), wn = -wp;                            // 4 / pow(2, |v1| + |v2|)
+      sz = __fadd_rn(__fadd_rn(sz, __fmul_rn(G(x + v1, y + v2, z - 1), wp)), __fmul_rn(G(x + v1, y + v2, z + 1), wn));
+      sy = __fadd_rn(__fadd_rn(sy, __fmul_rn(G(x + v1, y - 1, z + v2), wp)), __fmul_rn(G(x + v1, y + 1, z + v2), wn));
+      sx = __fadd_rn(__fadd_rn(sx, __fmul_rn(G(x - 1, y + v2, z + v1), wp)), __fmul_rn(G(x + 1, y + v2, z + v1), wn));
+    }
+  const __half hx = __float2half_rn(sx), hy = __float2half_rn(sy), hz = __float2half_rn(sz);       // imageStore to the three R16F images
+  const unsigned lo = (unsigned)__half_as_ushort(hx) | ((unsigned)__half_as_ushort(hy) << 16), hi = (unsigned)__half_as_ushort(hz);
+  surf3Dwrite(make_uint2(lo, hi), dst, x * 8, y, z);
+  if (lin_rgb) {
+    float* o = lin_rgb + 3 * ((size_t)x + ((size_t)y * w) + ((size_t)z * w * h));
+    o[0] = __half2float(hx); o[1] = __half2float(hy); o[2] = __half2float(hz);
+  }
+}
+
 void release_gradient(Volume& v) {
   if (v.tex_grad) cudaDestroyTextureObject(v.tex_grad);
   if (v.tex_grad_pt) cudaDestroyTextureObject(v.tex_grad_pt);
@@ -57,7 +86,8 @@ void release_gradient(Volume& v) {
 // Builds (or frees, model 0) the gradient texture of the current volume; host_rgb (optional) receives the texels.
 int build_gradient(vrb_ctx* ctx, int model, float* host_rgb) {
   Volume& v = ctx->vol;
-  VRB_REQUIRE(model >= 0 && model <= 2, VRB_ERR_UNSUPPORTED, "gradient model %d (0 none, 1 Sobel-Feldman, 2 central differences)", model);
+  VRB_REQUIRE(model >= 0 && model <= 3, VRB_ERR_UNSUPPORTED, "gradient model %d (0 none, 1 Sobel-Feldman, 2 central differences, 3 compute-shader Sobel)", model);
+  VRB_REQUIRE(!v.is_region() || model == 0, VRB_ERR_UNSUPPORTED, "vrb_volume_gradient: the context holds a region of a bricked volume");
   if (model == 0) { release_gradient(v); return VRB_OK; }
   VRB_REQUIRE(v.raw, VRB_ERR_NO_VOLUME, "vrb_volume_gradient: no volume uploaded");
   cudaStream_t s = ctx->stream;
@@ -80,7 +110,8 @@ int build_gradient(vrb_ctx* ctx, int model, float* host_rgb) {
     if (host_rgb) e = cudaMalloc(&lin, n * 3 * sizeof(float));
     if (e == cudaSuccess) {
       const dim3 g((unsigned)((v.w + 127) / 128), (unsigned)v.h, (unsigned)v.d);
-      if (v.dtype == VRB_U8) gradient_kernel<uint8_t><<<g, 128, 0, s>>>((const uint8_t*)v.raw, 256.0 - 1.0, (int)v.w, (int)v.h, (int)v.d, model, dst, lin);
+      if (model == 3) gradient_sobel_cs_kernel<<<g, 128, 0, s>>>(v.tex_pt, (int)v.w, (int)v.h, (int)v.d, dst, lin);
+      else if (v.dtype == VRB_U8) gradient_kernel<uint8_t><<<g, 128, 0, s>>>((const uint8_t*)v.raw, 256.0 - 1.0, (int)v.w, (int)v.h, (int)v.d, model, dst, lin);
       else if (v.dtype == VRB_U16) gradient_kernel<uint16_t><<<g, 128, 0, s>>>((const uint16_t*)v.raw, 65536.0 - 1.0, (int)v.w, (int)v.h, (int)v.d, model, dst, lin);
       else gradient_kernel<float><<<g, 128, 0, s>>>((const float*)v.raw, 1.0, (int)v.w, (int)v.h, (int)v.d, model, dst, lin);
       e = cudaGetLastError();

@@ -69,6 +69,9 @@ void vrbh_camera_uniforms(const float eye[3], const float center[3], const float
   cam.FillUniforms(out);
 }
 
+// Test hook for the PNG writer of the eval folder.
+int vrbh_write_png(const char* path, const uint8_t* rgb_bottom_up, int w, int h) { return WritePngRGB8(path, rgb_bottom_up, w, h) ? 0 : -1; }
+
 static char g_err[1024];
 const char* vrbh_last_error(void) { return g_err; }
 static int fail(const std::string& s) { std::strncpy(g_err, s.c_str(), sizeof(g_err) - 1); g_err[sizeof(g_err) - 1] = 0; return -1; }

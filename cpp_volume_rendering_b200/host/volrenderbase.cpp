@@ -507,9 +507,12 @@ bool RenderingManager::Display() {
   const double time_per_frame = m_eval_accum_ms / m_eval_numframes, fps = 1000.0 / time_per_frame;
   std::string img = std::to_string(m_eval_currsample);
   img = std::string(4 - std::min<size_t>(4, img.size()), '0') + img + ".png";
-  if (m_sink) {
+  {                                                                     // SaveScreenshot(m_eval_imgdirectory + "/" + imagefilename) (:276)
     std::vector<uint8_t> rgb; int w = 0, h = 0;
-    if (r->ReadFrameRGB8(rgb, &w, &h)) m_sink(m_sink_user, img.c_str(), rgb.data(), w, h);
+    if (r->ReadFrameRGB8(rgb, &w, &h)) {
+      if (m_sink) m_sink(m_sink_user, img.c_str(), rgb.data(), w, h);
+      else if (!WritePngRGB8(m_eval_imgdirectory + "/" + img, rgb.data(), w, h)) m_err = "cannot write " + m_eval_imgdirectory + "/" + img;
+    }
   }
   for (int i = 0; i < m_eval_paramspace.GetNumDimensions(); i++) m_eval_csvfile << m_eval_paramspace.GetDimensionValue(i) << ",";
   m_eval_csvfile << std::to_string(time_per_frame) << "," << std::to_string(fps) << ",\"" << img << "\"\n";
@@ -523,10 +526,56 @@ bool RenderingManager::Display() {
   return true;
 }
 
+// SaveScreenshot -> GenerateImgFile (renderingmanager.cpp:409-419, 1284-1300): the RGB8 back-buffer pixels as a PNG, top row first
+// (glReadPixels hands them bottom-up).  No image library in the headless build: an 8-bit RGB PNG with stored (uncompressed)
+// deflate blocks — IHDR, one IDAT, IEND; CRC-32 per chunk, Adler-32 over the filtered scanlines.
+namespace {
+uint32_t crc32_update(uint32_t c, const uint8_t* p, size_t n) {
+  static uint32_t table[256]; static bool init = false;
+  if (!init) { for (uint32_t i = 0; i < 256; i++) { uint32_t v = i; for (int k = 0; k < 8; k++) v = (v & 1u) ? 0xEDB88320u ^ (v >> 1) : v >> 1; table[i] = v; } init = true; }
+  for (size_t i = 0; i < n; i++) c = table[(c ^ p[i]) & 0xFFu] ^ (c >> 8);
+  return c;
+}
+void put_be32(std::vector<uint8_t>& v, uint32_t x) { v.push_back((uint8_t)(x >> 24)); v.push_back((uint8_t)(x >> 16)); v.push_back((uint8_t)(x >> 8)); v.push_back((uint8_t)x); }
+void put_chunk(std::vector<uint8_t>& out, const char type[4], const std::vector<uint8_t>& data) {
+  put_be32(out, (uint32_t)data.size());
+  const size_t at = out.size();
+  out.insert(out.end(), type, type + 4);
+  out.insert(out.end(), data.begin(), data.end());
+  put_be32(out, crc32_update(0xFFFFFFFFu, out.data() + at, out.size() - at) ^ 0xFFFFFFFFu);
+}
+}  // namespace
+bool WritePngRGB8(const std::string& path, const uint8_t* rgb_bottom_up, int w, int h) {
+  if (w <= 0 || h <= 0 || !rgb_bottom_up) return false;
+  std::vector<uint8_t> raw;                                  // filter byte 0 + scanline, top row first
+  raw.reserve((size_t)h * (3 * (size_t)w + 1));
+  for (int y = h - 1; y >= 0; y--) { raw.push_back(0); raw.insert(raw.end(), rgb_bottom_up + (size_t)y * w * 3, rgb_bottom_up + (size_t)(y + 1) * w * 3); }
+  std::vector<uint8_t> z = {0x78, 0x01};
+  uint32_t a = 1, b = 0;
+  for (size_t off = 0; off < raw.size(); off += 65535) {
+    const size_t n = std::min<size_t>(65535, raw.size() - off);
+    z.push_back(off + n == raw.size() ? 1 : 0);
+    z.push_back((uint8_t)(n & 0xFF)); z.push_back((uint8_t)(n >> 8)); z.push_back((uint8_t)(~n & 0xFF)); z.push_back((uint8_t)((~n >> 8) & 0xFF));
+    z.insert(z.end(), raw.begin() + off, raw.begin() + off + n);
+    for (size_t i = 0; i < n; i++) { a = (a + raw[off + i]) % 65521u; b = (b + a) % 65521u; }
+  }
+  put_be32(z, (b << 16) | a);
+  std::vector<uint8_t> png = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A}, ihdr;
+  put_be32(ihdr, (uint32_t)w); put_be32(ihdr, (uint32_t)h);
+  ihdr.push_back(8); ihdr.push_back(2); ihdr.push_back(0); ihdr.push_back(0); ihdr.push_back(0);   // 8 bits, RGB, deflate, no filter method, no interlace
+  put_chunk(png, "IHDR", ihdr); put_chunk(png, "IDAT", z); put_chunk(png, "IEND", std::vector<uint8_t>());
+  std::ofstream f(path, std::ios::binary);
+  if (!f) return false;
+  f.write((const char*)png.data(), (std::streamsize)png.size());
+  return (bool)f;
+}
+
 bool RenderingManager::StartEvaluation(const std::string& dir, int numframes) {
   BaseVolumeRenderer* r = CurrentRenderer();
   if (!r) { m_err = "no current renderer"; return false; }
   ::mkdir(dir.c_str(), 0755);
+  m_eval_imgdirectory = dir + "/img";                                   // :829-833
+  ::mkdir(m_eval_imgdirectory.c_str(), 0755);
   m_eval_csvfile.open(dir + "/eval.csv");
   if (!m_eval_csvfile.is_open()) { m_err = "cannot open " + dir + "/eval.csv"; return false; }
   m_eval_numframes = std::max(numframes, 1);

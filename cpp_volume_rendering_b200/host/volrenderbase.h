@@ -210,6 +210,9 @@ class CudaRC1PConeLightGroundTruthSteps : public BaseVolumeRenderer {
 };
 
 // ---- RenderingManager: registry + Display() order + evaluation loop ----------------------------------------
+// 8-bit RGB PNG of a bottom-up RGB8 frame (GenerateImgFile of the reference, without an image library)
+bool WritePngRGB8(const std::string& path, const uint8_t* rgb_bottom_up, int w, int h);
+
 class RenderingManager {
  public:
   static RenderingManager* Instance();
@@ -227,7 +230,8 @@ class RenderingManager {
   void Reshape(int w, int h);                                          // :321-335
   bool Display();                                                      // :174-319 (PrepareRender -> Redraw -> eval bookkeeping)
   // "Start Evaluation" (:819-867): opens <dir>/eval.csv with the reference's header, then Display() advances the
-  // parameter space every m_eval_numframes frames.  write_png_cb (optional) receives each sample's RGB8 frame.
+  // parameter space every m_eval_numframes frames and saves the sample's last frame as <dir>/img/NNNN.png (SaveScreenshot, :276);
+  // a frame sink, when set, receives the RGB8 frame instead.
   bool StartEvaluation(const std::string& dir, int numframes);
   bool IsEvaluationRunning() const { return m_eval_running; }
   typedef void (*FrameSink)(void* user, const char* filename, const uint8_t* rgb8, int w, int h);
@@ -247,6 +251,7 @@ class RenderingManager {
   int m_eval_numframes = 100, m_eval_currframe = 0, m_eval_currsample = 0;
   double m_eval_accum_ms = 0.0;
   std::ofstream m_eval_csvfile;
+  std::string m_eval_imgdirectory;                                     // <dir>/img, one NNNN.png per sample (:829)
   FrameSink m_sink = nullptr; void* m_sink_user = nullptr;
   std::string m_err;
 };

@@ -513,7 +513,8 @@ bool DataManager::GenerateStructuredGradientTexture() {
   const VrbApi* a = VrbApi::Get(&m_err);
   if (!a) return false;
   const int model = curr_gradient_comp_model == STRUCTURED_GRADIENT_TYPE::SOBEL_FELDMAN_FILTER ? 1
-                  : (curr_gradient_comp_model == STRUCTURED_GRADIENT_TYPE::FINITE_DIFERENCES ? 2 : 0);
+                  : (curr_gradient_comp_model == STRUCTURED_GRADIENT_TYPE::FINITE_DIFERENCES ? 2
+                  : (curr_gradient_comp_model == STRUCTURED_GRADIENT_TYPE::COMPUTE_SHADER_SOBEL ? 3 : 0));
   if (a->volume_gradient(m_ctx, model, nullptr) != VRB_OK) { m_err = a->last_error(); return false; }
   m_has_gradient = model != 0;
   return true;

@@ -160,7 +160,7 @@ class RenderingParameters {
 // Owns the vrb context: SetCurrentVolume / SetCurrentTransferFunction replace GenerateRTexture and
 // GenerateTexture_1D_* (the device textures live in libvrb200.so).
 // libs/volvis_utils/datamanager.h: how the gradient texture of the Blinn-Phong path is computed
-enum class STRUCTURED_GRADIENT_TYPE { NONE_GRADIENT = 0, SOBEL_FELDMAN_FILTER = 1, FINITE_DIFERENCES = 2 };
+enum class STRUCTURED_GRADIENT_TYPE { NONE_GRADIENT = 0, SOBEL_FELDMAN_FILTER = 1, FINITE_DIFERENCES = 2, COMPUTE_SHADER_SOBEL = 3 };   // datamanager.h:64-69 (values = vrb_volume_gradient models)
 
 class DataManager {
  public:

@@ -225,7 +225,8 @@ int vrb_volume_upload(vrb_ctx* ctx, const void* voxels, int dtype, int64_t w, in
 /* DataManager::GenerateStructuredGradientTexture (datamanager.cpp:332-352), moved to the GPU: builds the RGB16F gradient
  * texture of the current volume that gradient (Blinn-Phong) shading samples.  model 0 = none (frees it; the reference's
  * default, datamanager.cpp:27), 1 = SOBEL_FELDMAN_FILTER (utils.cpp:287-350), 2 = FINITE_DIFERENCES (utils.cpp:146-285
- * with its default arguments).  The compute-shader Sobel variant is not provided.  host_rgb (optional, test hook):
+ * with its default arguments), 3 = COMPUTE_SHADER_SOBEL (GenerateGradientWithComputeShader, datamanager.cpp:623-718, running
+ * shader/_gradient_shading/sobelfeldman_generator.comp: float32 from the R16F texture).  host_rgb (optional, test hook):
  * receives the w*h*d*3 texel values.  Must be called again after a new volume upload. */
 int vrb_volume_gradient(vrb_ctx* ctx, int model, float* host_rgb);
 

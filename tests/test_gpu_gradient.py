@@ -9,7 +9,7 @@ from oracle import pyoracle as O
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("model", [1, 2])
+@pytest.mark.parametrize("model", [1, 2, 3])
 @pytest.mark.parametrize("dtype,shape", [(np.uint8, (40, 33, 21)), (np.uint16, (32, 32, 32)), (np.float32, (24, 20, 18)), (np.uint8, (1, 2, 3))])
 def test_gradient_texture_bit_identical(ctx, model, dtype, shape):
     vox = inputs.synth_volume(0, dtype, shape=shape)
@@ -20,7 +20,7 @@ def test_gradient_texture_bit_identical(ctx, model, dtype, shape):
     ctx.volume_gradient(0)
 
 
-@pytest.mark.parametrize("model", [1, 2])
+@pytest.mark.parametrize("model", [1, 2, 3])
 @pytest.mark.parametrize("n,dtype,size,eye_s", [(48, np.uint8, (96, 96), (1, 1, 2)), (64, np.uint16, (120, 80), (-1.2, 0.4, 1.1))])
 def test_blinn_phong_image_parity(ctx, bonsai_table, model, n, dtype, size, eye_s):
     w, h = size

@@ -146,3 +146,35 @@ def test_evaluation_writes_reference_csv_schema(tmp_path):
     assert rows[1][:2] == ["1", "0.100000"] and rows[2][:2] == ["1", "0.200000"]
     wrap = [i for i in range(2, 26) if rows[i][1] == "0.100000"]
     assert wrap and rows[wrap[0]][0] == "2"                         # the last dimension runs fastest (validated against libref)
+
+
+def test_png_writer_and_eval_report(tmp_path):
+    """WritePngRGB8 (the headless GenerateImgFile: stored-deflate PNG, top row first) read back with PIL, and tools/eval_report.py — the
+    reference's eval.py table (Image, SSIM; Missing / Error rows; mean / min / max) — over two eval image folders."""
+    import ctypes as C
+    import sys
+    from PIL import Image
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import eval_report
+    L = hostapi.lib()
+    L.vrbh_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
+    rng = np.random.default_rng(3)
+    a_dir, b_dir = tmp_path / "evalA" / "img", tmp_path / "evalB" / "img"
+    a_dir.mkdir(parents=True); b_dir.mkdir(parents=True)
+    frames = []
+    for i, (w, h) in enumerate([(37, 23), (300, 219), (64, 64)]):      # 300 x 219 x 3 > 65535 bytes: several stored blocks
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)           # row 0 = bottom, as the frames of the library
+        frames.append(img)
+        assert L.vrbh_write_png(str(a_dir / f"{i:04d}.png").encode(), img.ctypes.data_as(C.c_void_p), w, h) == 0
+        back = np.asarray(Image.open(a_dir / f"{i:04d}.png"))
+        assert back.shape == (h, w, 3) and np.array_equal(back, img[::-1])   # PNG rows run top-down
+    noisy = np.clip(frames[0].astype(np.int32) + rng.integers(-40, 41, frames[0].shape), 0, 255).astype(np.uint8)
+    L.vrbh_write_png(str(b_dir / "0000.png").encode(), noisy.ctypes.data_as(C.c_void_p), 37, 23)
+    L.vrbh_write_png(str(b_dir / "0001.png").encode(), frames[1].ctypes.data_as(C.c_void_p), 300, 219)
+    (b_dir / "0003.png").write_bytes(b"not a png")
+    L.vrbh_write_png(str(a_dir / "0003.png").encode(), frames[2].ctypes.data_as(C.c_void_p), 64, 64)
+    rows, valid = eval_report.compare_folders(str(tmp_path / "evalA"), str(tmp_path / "evalB"), count=5)
+    assert [r["Image"] for r in rows] == [f"{i:04d}.png" for i in range(5)]
+    assert rows[1]["SSIM"] == 1.0 and 0.0 < rows[0]["SSIM"] < 0.99
+    assert rows[2]["SSIM"] == "Missing" and rows[3]["SSIM"] == "Error" and rows[4]["SSIM"] == "Missing"
+    assert len(valid) == 2

@@ -173,3 +173,16 @@ def test_blit_over_white():
     # out = rgb*a + (1-a): premultiplied colour is multiplied by alpha again
     want = np.array([[255, 255, 255], [255, 0, 0], [round((0.125 + 0.5) * 255), round(0.75 * 255), round(0.5 * 255)], [255, 255, 255]], np.uint8)
     assert np.array_equal(got, want)
+
+
+def test_compute_shader_sobel_matches_the_cpu_sobel_up_to_its_float32_arithmetic():
+    """sobelfeldman_generator.comp restated (gradient model 3: float32 sums over the R16F TEXTURE) against the CPU Sobel-Feldman filter
+    (model 1: double sums over the normalised voxels): same stencil, so they agree up to the binary16 quantisation of the volume
+    (18 taps of weight <= 4, each off by <= 2^-12) plus the output rounding; exactly on a volume whose voxels binary16 holds exactly."""
+    from cpp_volume_rendering_b200 import inputs
+    vox = inputs.synth_volume(0, np.uint8, shape=(20, 17, 13))
+    g1, g3 = O.gradient(vox, 1), O.gradient(vox, 3)
+    assert g1.shape == g3.shape == (13, 17, 20, 3)
+    assert np.abs(g1 - g3).max() <= 32 * 2.0 ** -12 + np.abs(g1).max() * 2.0 ** -10 and np.abs(g3).max() > 0.5
+    exact = (np.random.default_rng(1).integers(0, 5, (9, 8, 7)) * 0.25).astype(np.float32)      # 0, 0.25, ..., 1: exact in binary16
+    assert np.array_equal(O.gradient(exact, 1), O.gradient(exact, 3))
