@@ -221,7 +221,26 @@ struct Geo {
   int w, h, d, seglen, nbands, nseg;
 };
 
-template <typename T>
+// Elementwise E = GetExtN(sample) of a float volume, at full occupancy (small CTAs, 4 voxels per thread): the double lerp / division /
+// logarithm of GetExtN is a long dependent chain, and inside the one-CTA-per-SM tile kernel below nothing hides it (ncu r1d: 0.69 of
+// the 1.04 ms build, DRAM 19 % busy).  Here 8 CTAs per SM do.  HBM-bound: 4 B read + 4 B written per voxel.
+__global__ void __launch_bounds__(256, 4) sat_ext_kernel(const float* __restrict__ raw, const double* __restrict__ table, int max_density, int ext_type,
+                                                         size_t n4, const LogTab* __restrict__ logtab, float zero_below, float* __restrict__ E) {
+  __shared__ LogTab s_log[LOG_BINS];
+  for (int i = threadIdx.x; i < LOG_BINS; i += blockDim.x) s_log[i] = logtab[i];
+  __syncthreads();
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    const float4 v = __ldcs(reinterpret_cast<const float4*>(raw) + i);
+    const float nv[4] = {v.x, v.y, v.z, v.w};
+    float e[4];
+    ext_of_float4(table, max_density, ext_type, nv, s_log, zero_below, e);
+    reinterpret_cast<float4*>(E)[i] = make_float4(e[0], e[1], e[2], e[3]);
+  }
+}
+
+// MODE 0: extinction from the raw voxels (table for integers, GetExtN for floats), E written out;  MODE 1: `raw` already holds E
+// (float), nothing written;  MODE 2: integer voxels through the table, nothing written (the scan pass looks the table up again).
+template <typename T, int MODE>
 __global__ void __launch_bounds__(THREADS, 1) sat_reduce_kernel(const T* __restrict__ raw, const float* __restrict__ lut,
                                                                 const double* __restrict__ table, int max_density, int ext_type, Geo g,
                                                                 float* __restrict__ E, double* __restrict__ cs, double* __restrict__ zs,
@@ -231,7 +250,7 @@ __global__ void __launch_bounds__(THREADS, 1) sat_reduce_kernel(const T* __restr
   V* stage = reinterpret_cast<V*>(s_raw);                                                   // [STAGES][R][THREADS]
   double* red = reinterpret_cast<double*>(s_raw + (size_t)STAGES * R * THREADS * sizeof(V));  // [2][YW][XSPAN]
   LogTab* s_log = reinterpret_cast<LogTab*>(red + 2 * YW * XSPAN);                          // [LOG_BINS] (float volumes)
-  if (sizeof(T) == 4) {
+  if (sizeof(T) == 4 && MODE == 0) {
     for (int i = threadIdx.x; i < LOG_BINS; i += THREADS) s_log[i] = logtab[i];
     __syncthreads();
   }
@@ -273,16 +292,19 @@ __global__ void __launch_bounds__(THREADS, 1) sat_reduce_kernel(const T* __restr
       const bool p = xin && y < g.h;
       const V v = stage[(st * R + r) * THREADS + tid];
       float e[C];
-      if (sizeof(T) != 4) {
+      if (MODE == 1) {
 #pragma unroll
-        for (int c = 0; c < C; c++) e[c] = p ? lut[(unsigned)v.v[c]] : 0.0f;
+        for (int c = 0; c < C; c++) e[c] = p ? (float)v.v[c] : 0.0f;
+      } else if (sizeof(T) != 4) {
+#pragma unroll
+        for (int c = 0; c < C; c++) e[c] = p ? __ldg(lut + (unsigned)v.v[c]) : 0.0f;
       } else {
         const float nv4[C] = {(float)v.v[0], (float)v.v[1], (float)v.v[2], (float)v.v[3]};
         ext_of_float4(table, max_density, ext_type, nv4, s_log, zero_below, e);         // staged zeros outside the volume: computed, not stored
 #pragma unroll
         for (int c = 0; c < C; c++) e[c] = p ? e[c] : 0.0f;
       }
-      if (p) *reinterpret_cast<float4*>(E + ((size_t)x0 + (size_t)g.w * ((size_t)y + (size_t)g.h * (size_t)z))) = make_float4(e[0], e[1], e[2], e[3]);
+      if (MODE == 0 && p) *reinterpret_cast<float4*>(E + ((size_t)x0 + (size_t)g.w * ((size_t)y + (size_t)g.h * (size_t)z))) = make_float4(e[0], e[1], e[2], e[3]);
 #pragma unroll
       for (int c = 0; c < C; c++) { acc[r][c] += (double)e[c]; col[c] += (double)e[c]; }
     }
@@ -383,13 +405,22 @@ __device__ __forceinline__ void scan_row(double (&a)[C], double (&run)[C], doubl
   for (int c = 0; c < C; c++) { run[c] += a[c] + excl; acc[c] += run[c]; }
 }
 
-__global__ void __launch_bounds__(THREADS, 1) sat_scan_kernel(const float* __restrict__ E, const double* __restrict__ csx, const double* __restrict__ ZS,
+// T = float: E holds the extinctions.  T = uint8_t / uint16_t: E holds the raw voxels and the extinction is looked up again in `lut`
+// (256 entries in shared memory, 65536 through the read-only cache) — the float copy of the volume is never written.
+template <typename T>
+__global__ void __launch_bounds__(THREADS, 1) sat_scan_kernel(const T* __restrict__ E, const float* __restrict__ lut, const double* __restrict__ csx, const double* __restrict__ ZS,
                                                               const double* __restrict__ ZSY, Geo g, float* __restrict__ out) {
   extern __shared__ __align__(16) unsigned char s_raw[];
-  float4* stage = reinterpret_cast<float4*>(s_raw);                                   // [STAGES][R][THREADS]
-  double2* cstage = reinterpret_cast<double2*>(stage + STAGES * R * THREADS);         // [STAGES][2][32 * XW] (wy == 0 warps)
+  using V = Raw4<T>;
+  V* stage = reinterpret_cast<V*>(s_raw);                                             // [STAGES][R][THREADS]
+  double2* cstage = reinterpret_cast<double2*>(s_raw + (size_t)STAGES * R * THREADS * 16);   // [STAGES][2][32 * XW] (wy == 0 warps)
   double* right = reinterpret_cast<double*>(cstage + STAGES * 2 * 32 * XW);          // [2][YW][R][XW]
   double* bottom = right + 2 * YW * R * XW;                                           // [2][YW][XSPAN]
+  float* s_lut = reinterpret_cast<float*>(bottom + 2 * YW * XSPAN);                   // [256] (8-bit volumes)
+  if (sizeof(T) == 1) {
+    for (int i = threadIdx.x; i < 256; i += THREADS) s_lut[i] = lut[i];
+    __syncthreads();
+  }
   const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5, wx = wq & (XW - 1), wy = wq / XW;
   const int band = blockIdx.x, seg = blockIdx.y;
   const int xl = wx * 32 * C + lane * C, x0 = xl, yb = band * BAND + wy * R;
@@ -402,8 +433,8 @@ __global__ void __launch_bounds__(THREADS, 1) sat_scan_kernel(const float* __res
       for (int r = 0; r < R; r++) {
         const int y = yb + r;
         const bool p = xin && y < g.h;
-        const float* src = p ? E + ((size_t)x0 + (size_t)g.w * ((size_t)y + (size_t)g.h * (size_t)z)) : E;
-        cp_async<16>(&stage[(st * R + r) * THREADS + tid], src, p);
+        const T* src = p ? E + ((size_t)x0 + (size_t)g.w * ((size_t)y + (size_t)g.h * (size_t)z)) : E;
+        cp_async<(int)sizeof(V)>(&stage[(st * R + r) * THREADS + tid], src, p);
       }
       if (wy == 0) {
         const double* src = xin ? csx + ((size_t)z * g.nbands + band) * (size_t)g.w + x0 : csx;
@@ -446,8 +477,16 @@ __global__ void __launch_bounds__(THREADS, 1) sat_scan_kernel(const float* __res
       double run[C] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
       for (int r = 0; r < R; r++) {
-        const float4 v = stage[(st * R + r) * THREADS + tid];       // zero-filled outside the volume
-        double a[C] = {(double)v.x, (double)v.y, (double)v.z, (double)v.w};
+        const V v = stage[(st * R + r) * THREADS + tid];            // zero-filled outside the volume
+        double a[C];
+        if (sizeof(T) == 4) {
+#pragma unroll
+          for (int c = 0; c < C; c++) a[c] = (double)v.v[c];
+        } else {
+          const bool p = xin && yb + r < g.h;                       // a zero-filled voxel is voxel value 0, whose extinction need not be 0
+#pragma unroll
+          for (int c = 0; c < C; c++) a[c] = p ? (double)(sizeof(T) == 1 ? s_lut[(unsigned)v.v[c]] : __ldg(lut + (unsigned)v.v[c])) : 0.0;
+        }
         if (r == 0 && wy == 0) {
           const double2 u = cstage[(st * 2 + 0) * 32 * XW + wx * 32 + lane], t = cstage[(st * 2 + 1) * 32 * XW + wx * 32 + lane];
           a[0] += u.x; a[1] += u.y; a[2] += t.x; a[3] += t.y;
@@ -566,7 +605,7 @@ int ExtSat::ensure(vrb_ctx* ctx, int fast) {
       g.seglen = (g.d + g.nseg - 1) / g.nseg;
       g.nseg = (g.d + g.seglen - 1) / g.seglen;
       const size_t wz = (size_t)g.w;
-      VRB_CUDA(cudaMalloc(&E, wz * g.h * g.d * sizeof(float)));
+      if (v.dtype == VRB_F32) VRB_CUDA(cudaMalloc(&E, wz * g.h * g.d * sizeof(float)));    // integer volumes: the scan pass looks the table up again
       VRB_CUDA(cudaMalloc(&cs, wz * g.nbands * g.d * sizeof(double)));
       VRB_CUDA(cudaMalloc(&zs, wz * g.h * g.nseg * sizeof(double)));
       VRB_CUDA(cudaMalloc(&bzs, 2 * wz * g.nbands * g.nseg * sizeof(double)));
@@ -597,23 +636,34 @@ int ExtSat::ensure(vrb_ctx* ctx, int fast) {
       const size_t sm1 = (size_t)sat2::STAGES * sat2::R * sat2::THREADS * esz + (size_t)2 * sat2::YW * sat2::XSPAN * sizeof(double) +
                          sat2::LOG_BINS * sizeof(sat2::LogTab);
       const size_t sm2 = (size_t)sat2::STAGES * sat2::R * sat2::THREADS * 16 + (size_t)sat2::STAGES * 2 * 32 * sat2::XW * 16 +
-                         (size_t)2 * sat2::YW * sat2::R * sat2::XW * sizeof(double) + (size_t)2 * sat2::YW * sat2::XSPAN * sizeof(double);
+                         (size_t)2 * sat2::YW * sat2::R * sat2::XW * sizeof(double) + (size_t)2 * sat2::YW * sat2::XSPAN * sizeof(double) + 256 * sizeof(float);
       const int maxd2 = t.n - 1;
+      const unsigned ba = (unsigned)((wz * g.d + 255) / 256), bb = (unsigned)((wz * g.h + 255) / 256), bc = (unsigned)((wz * g.nbands + 255) / 256);
       if (v.dtype == VRB_U8) {
-        VRB_CUDA(cudaFuncSetAttribute(sat2::sat_reduce_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
-        sat2::sat_reduce_kernel<uint8_t><<<grid, sat2::THREADS, sm1, s>>>((const uint8_t*)v.raw, lut, t.table, maxd2, t.extinction_type, g, E, cs, zs, bzs, logtab, zero_below);
+        VRB_CUDA(cudaFuncSetAttribute(sat2::sat_reduce_kernel<uint8_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
+        sat2::sat_reduce_kernel<uint8_t, 2><<<grid, sat2::THREADS, sm1, s>>>((const uint8_t*)v.raw, lut, t.table, maxd2, t.extinction_type, g, nullptr, cs, zs, bzs, logtab, zero_below);
       } else if (v.dtype == VRB_U16) {
-        VRB_CUDA(cudaFuncSetAttribute(sat2::sat_reduce_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
-        sat2::sat_reduce_kernel<uint16_t><<<grid, sat2::THREADS, sm1, s>>>((const uint16_t*)v.raw, lut, t.table, maxd2, t.extinction_type, g, E, cs, zs, bzs, logtab, zero_below);
+        VRB_CUDA(cudaFuncSetAttribute(sat2::sat_reduce_kernel<uint16_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
+        sat2::sat_reduce_kernel<uint16_t, 2><<<grid, sat2::THREADS, sm1, s>>>((const uint16_t*)v.raw, lut, t.table, maxd2, t.extinction_type, g, nullptr, cs, zs, bzs, logtab, zero_below);
       } else {
-        VRB_CUDA(cudaFuncSetAttribute(sat2::sat_reduce_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
-        sat2::sat_reduce_kernel<float><<<grid, sat2::THREADS, sm1, s>>>((const float*)v.raw, nullptr, t.table, maxd2, t.extinction_type, g, E, cs, zs, bzs, logtab, zero_below);
+        // float volumes: GetExtN elementwise at full occupancy, then the carries from E
+        const size_t n4 = wz * g.h * g.d / 4;                 // w % 4 == 0
+        sat2::sat_ext_kernel<<<ctx->sm_count * 8, 256, 0, s>>>((const float*)v.raw, t.table, maxd2, t.extinction_type, n4, logtab, zero_below, E);
+        VRB_CUDA(cudaFuncSetAttribute(sat2::sat_reduce_kernel<float, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
+        sat2::sat_reduce_kernel<float, 1><<<grid, sat2::THREADS, sm1, s>>>(E, nullptr, t.table, maxd2, t.extinction_type, g, nullptr, cs, zs, bzs, logtab, zero_below);
       }
       VRB_CUDA(cudaGetLastError());
-      const unsigned ba = (unsigned)((wz * g.d + 255) / 256), bb = (unsigned)((wz * g.h + 255) / 256), bc = (unsigned)((wz * g.nbands + 255) / 256);
       sat2::sat_mid_kernel<<<ba + bb + bc, 256, 0, s>>>(cs, zs, bzs, zsy, g, ba, bb);
-      VRB_CUDA(cudaFuncSetAttribute(sat2::sat_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
-      sat2::sat_scan_kernel<<<grid, sat2::THREADS, sm2, s>>>(E, cs, zs, zsy, g, sat);
+      if (v.dtype == VRB_U8) {
+        VRB_CUDA(cudaFuncSetAttribute(sat2::sat_scan_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+        sat2::sat_scan_kernel<uint8_t><<<grid, sat2::THREADS, sm2, s>>>((const uint8_t*)v.raw, lut, cs, zs, zsy, g, sat);
+      } else if (v.dtype == VRB_U16) {
+        VRB_CUDA(cudaFuncSetAttribute(sat2::sat_scan_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+        sat2::sat_scan_kernel<uint16_t><<<grid, sat2::THREADS, sm2, s>>>((const uint16_t*)v.raw, lut, cs, zs, zsy, g, sat);
+      } else {
+        VRB_CUDA(cudaFuncSetAttribute(sat2::sat_scan_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+        sat2::sat_scan_kernel<float><<<grid, sat2::THREADS, sm2, s>>>(E, nullptr, cs, zs, zsy, g, sat);
+      }
       const size_t faces = 2 * ((size_t)H * D + (size_t)W * D + (size_t)W * H);
       sat2::sat_border_kernel<<<(unsigned)((faces + 255) / 256), 256, 0, s>>>(sat, g.w, g.h, g.d);
     } else {
