@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("VRB200_LIB") or os.path.join(_HERE, "libvrb200.so")  
 
 VRB_U8, VRB_U16, VRB_F32 = 0, 1, 2
 (VRB_RC1PASS, VRB_ISO_ADAPT, VRB_ISO_SKIP_V1, VRB_ISO_SKIP_V2, VRB_DOS_CONE, VRB_EBS_SAT, VRB_VCT,
- VRB_SBTM_DOS, VRB_ISO_FORWARD, VRB_ISO_DEFERRED, VRB_CRT_GT) = range(11)
+ VRB_SBTM_DOS, VRB_ISO_FORWARD, VRB_ISO_DEFERRED, VRB_CRT_GT, VRB_ISO_ADVANCED_DEFERRED) = range(12)
 VRB_FRAME_RGBA16F, VRB_FRAME_RGB8_OVER_WHITE, VRB_FRAME_RGBA32F = 0, 1, 2
 VRB_FRAME_GENERATED = 0x100
 VRB_MS_SINGLE, VRB_MS_MULTIPLE_RAYS_PER_PIXEL, VRB_MS_DOWN_SCALING, VRB_MS_UP_SCALING = 0, 1, 2, 3
@@ -47,6 +47,11 @@ class IsoParams(C.Structure):
     _fields_ = [("isovalue", C.c_float), ("step_size_small", C.c_float), ("step_size_large", C.c_float),
                 ("step_size_range", C.c_float), ("color", C.c_float * 4), ("apply_gradient_shading", C.c_int),
                 ("num_blocks", C.c_int * 3), ("count_iterations", C.c_int)]
+
+
+class AdsParams(C.Structure):
+    _fields_ = [("iso", IsoParams), ("current_time", C.c_float), ("flow_speed", C.c_float), ("flow_scale", C.c_float),
+                ("accessibility_strength", C.c_float), ("show_ridges", C.c_int), ("show_valleys", C.c_int)]
 
 
 class CrtgtParams(C.Structure):
@@ -138,6 +143,7 @@ SIGNATURES = {
     "vrb_vct_read_lut": (C.c_int, [_P, _P, C.POINTER(C.c_int * 2), C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
     "vrb_iso_read_blocks": (C.c_int, [_P, _P, _P]),
     "vrb_iso_read_gbuffers": (C.c_int, [_P, _P, _P]),
+    "vrb_ads_read_curvature": (C.c_int, [_P, _P, _P]),
     "vrb_crtgt_set_kernels": (C.c_int, [_P, _P, C.c_int, _P, C.c_int]),
     "vrb_crtgt_read_state": (C.c_int, [_P, _P, C.POINTER(C.c_longlong)]),
     "vrb_renderer_set_partition": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
@@ -454,6 +460,13 @@ class Renderer:
         pos = np.empty((h, w, 4), np.float32); nrm = np.empty((h, w, 4), np.float32)
         _check(lib().vrb_iso_read_gbuffers(self._h, pos.ctypes.data_as(_P), nrm.ctypes.data_as(_P)))
         return pos, nrm
+
+    def read_curvature(self):
+        """VRB_ISO_ADVANCED_DEFERRED: (gCurvatureMax, gCurvatureMin) of the last redraw, [h, w] float32 each."""
+        w, h = self.render_size()
+        k1 = np.empty((h, w), np.float32); k2 = np.empty((h, w), np.float32)
+        _check(lib().vrb_ads_read_curvature(self._h, k1.ctypes.data_as(_P), k2.ctypes.data_as(_P)))
+        return k1, k2
 
     def crtgt_set_kernels(self, occ_xyz, sdw_xyz):
         occ = np.ascontiguousarray(occ_xyz, np.float32).reshape(-1, 3); sdw = np.ascontiguousarray(sdw_xyz, np.float32).reshape(-1, 3)

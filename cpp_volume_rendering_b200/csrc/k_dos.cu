@@ -313,6 +313,7 @@ struct DosCone {
 };
 
 struct DosShader {
+  static constexpr int ADVANCE = 4, BATCH = 16;   // park-and-shade schedule of the shared march (vrb_march.cuh): measured at C3 (512^3, 1024^2): lockstep (1, 1) 7.1 / 23.0 ms without / with shadows, (4, 16) 5.6 / 15.7 ms, (8, 24) 6.5 / 16.3 ms
   static constexpr bool OBJECT_SPACE = false;
   static constexpr int PHONG_KIND = 0;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   struct Args {

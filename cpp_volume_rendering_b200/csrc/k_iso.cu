@@ -14,6 +14,7 @@
 #include "vrb_ray.cuh"
 #include <algorithm>
 #include <cfloat>
+#include <vector>
 
 namespace vrb {
 
@@ -248,7 +249,11 @@ __global__ void __launch_bounds__(ISO_THREADS, VRB_ISO_MINB) iso_kernel(const __
     float tnear, tfar;
     const bool hit = ray_aabb(r.org, cdir, mk3(-r.half.x, -r.half.y, -r.half.z), r.half, r.dir, tnear, tfar);
     float4 dst = make_float4(0.f, 0.f, 0.f, 0.f);
-    f3 gp = mk3(0.f, 0.f, 0.f), gn = mk3(0.f, 0.f, 0.f); float gw = 0.0f;     // MODE 4: G-buffer texel of this pixel
+    // MODE 4 / 5: G-buffer texel of this pixel.  A ray that misses the box stores nothing (geometry_pass.comp:158): the texel keeps
+    // the glClear value, (1,1,1,0) in DeferredShading (the application's clear colour, renderingmanager.cpp:40,108-109), (1,1,1,1) in
+    // AdvancedDeferredShading (its Redraw sets it, :723-725).  A ray inside the box without a crossing stores zeros (:243-245).
+    f3 gp = mk3(0.f, 0.f, 0.f), gn = mk3(0.f, 0.f, 0.f); float gw = 0.0f;
+    if (MODE >= 4 && !hit) { gp = gn = mk3(1.f, 1.f, 1.f); gw = MODE == 4 ? 0.0f : 1.0f; }
     if (hit) {
       const float iso = a.iso;
       bool crossed = false;
@@ -338,7 +343,7 @@ __global__ void __launch_bounds__(ISO_THREADS, VRB_ISO_MINB) iso_kernel(const __
           }
           if (crossed) {
             const f3 s_tex_pos = add3(add3(r.org, scale3(r.dir, t)), r.half);        // at the refined t (v1 :227, v2 :247)
-            if (MODE == 4) { gp = s_tex_pos; gn = iso_calculate_gradient(a, s_tex_pos); gw = 1.0f; break; }   // geometry_pass.comp:225-235
+            if (MODE >= 4) { gp = s_tex_pos; gn = iso_calculate_gradient(a, s_tex_pos); gw = 1.0f; break; }   // geometry_pass.comp:225-235
             if (MODE == 3) iso_composite_forward(a, dst, s_tex_pos);
             else iso_composite(a, dst, s_tex_pos);
             crossed = false;
@@ -348,9 +353,10 @@ __global__ void __launch_bounds__(ISO_THREADS, VRB_ISO_MINB) iso_kernel(const __
       }
     }
     const size_t o = (size_t)py * a.width + px;
-    if (MODE == 4) {
-      dst = iso_deferred_light(a, gp, gn);
+    if (MODE >= 4) {
       if (a.gpos) { a.gpos[o] = make_float4(gp.x, gp.y, gp.z, gw); a.gnrm[o] = make_float4(gn.x, gn.y, gn.z, gw); }
+      if (MODE == 5) continue;             // AdvancedDeferredShading: the frame comes from the passes of k_ads.cu
+      dst = iso_deferred_light(a, gp, gn);
     }
     const uint2 texel = make_uint2(pack_half2(dst.x, dst.y), pack_half2(dst.z, dst.w));
     a.frame[o] = texel;
@@ -362,6 +368,11 @@ __global__ void __launch_bounds__(ISO_THREADS, VRB_ISO_MINB) iso_kernel(const __
   }
   finish_launch(a.queue, a.sig);
 }
+
+// k_ads.cu: the passes behind AdvancedDeferredShading's geometry pass
+void ads_make_maps(std::vector<float>& color, std::vector<float>& ridge);
+int ads_run_passes(cudaStream_t s, int W, int H, const float4* gpos, const float4* gnrm, float* k1, float* k2, const float* color_map,
+                   const float* ridge_map, const float eye[3], const float light_pos[3], float alpha, const vrb_ads_params& prm, uint2* frame);
 
 // ---------------------------------------------------------------------------------------------
 // Host drivers: RayCasting1PassIsoAdapt (rc1pisoadaptrenderer.cpp), CustomRayCasting1PassIsoAdapt
@@ -376,6 +387,9 @@ class IsoRenderer : public RendererImpl {
     // and (4,4,4) again in FowardRendering.cpp:190 and DeferredShading.cpp (geometry pass set-up)
     const int nb = k == VRB_ISO_SKIP_V2 ? 32 : 4;
     prm_.num_blocks[0] = prm_.num_blocks[1] = prm_.num_blocks[2] = nb;
+    // AdvancedDeferredShading.h:129-133; m_current_time is the wall clock since Init there, a parameter here
+    ads_.current_time = 0.0f; ads_.flow_speed = 1.0f; ads_.flow_scale = 10.0f; ads_.accessibility_strength = 0.5f;
+    ads_.show_ridges = 1; ads_.show_valleys = 1;
   }
 
   int init(int w, int h) override {
@@ -388,19 +402,39 @@ class IsoRenderer : public RendererImpl {
     }
     rc = alloc_frame(w, h);
     if (rc != VRB_OK) return rc;
+    if (kind == VRB_ISO_ADVANCED_DEFERRED) {      // CreateGBuffer, InitCurvaturePass, CreateTransferFunctions (AdvancedDeferredShading.cpp:541-544)
+      rc = ensure_ads_buffers();
+      if (rc != VRB_OK) return rc;
+    }
     built = true;
     return VRB_OK;
   }
   void clean() override {
     blocks_.release();
     if (gbuf_) { cudaFree(gbuf_); gbuf_ = nullptr; gbuf_px_ = 0; }
+    if (k1k2_) { cudaFree(k1k2_); k1k2_ = nullptr; k1k2_px_ = 0; }
+    if (maps_) { cudaFree(maps_); maps_ = nullptr; }
   }
-
-  // Test hook: the deferred renderer's G-buffers.  They exist only for this call: the frame is redrawn with the two
-  // buffers attached, then they are copied out.
-  int read_gbuffers(float* host_pos, float* host_nrm) {
-    VRB_REQUIRE(kind == VRB_ISO_DEFERRED, VRB_ERR_INVALID, "vrb_iso_read_gbuffers: not a deferred-shading renderer");
-    VRB_REQUIRE(built && have_cam, VRB_ERR_INVALID, "vrb_iso_read_gbuffers before Init/Update");
+  int ensure_ads_buffers() {       // sized for the current frame (Init and after a Reshape)
+    int rc = ensure_gbuffers();
+    if (rc != VRB_OK) return rc;
+    const size_t px = (size_t)width * height;
+    if (k1k2_px_ != px) {
+      if (k1k2_) cudaFree(k1k2_);
+      k1k2_ = nullptr; k1k2_px_ = 0;
+      VRB_CUDA(cudaMalloc(&k1k2_, 2 * px * sizeof(float)));
+      k1k2_px_ = px;
+    }
+    if (!maps_) {
+      std::vector<float> color, ridge;
+      ads_make_maps(color, ridge);
+      VRB_CUDA(cudaMalloc(&maps_, (color.size() + ridge.size()) * sizeof(float)));
+      VRB_CUDA(cudaMemcpy(maps_, color.data(), color.size() * sizeof(float), cudaMemcpyHostToDevice));
+      VRB_CUDA(cudaMemcpy(maps_ + color.size(), ridge.data(), ridge.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
+    return VRB_OK;
+  }
+  int ensure_gbuffers() {
     const size_t px = (size_t)width * height;
     if (gbuf_px_ != px) {
       if (gbuf_) cudaFree(gbuf_);
@@ -408,8 +442,19 @@ class IsoRenderer : public RendererImpl {
       VRB_CUDA(cudaMalloc(&gbuf_, 2 * px * sizeof(float4)));
       gbuf_px_ = px;
     }
+    return VRB_OK;
+  }
+
+  // Test hook: the deferred renderer's G-buffers.  They exist only for this call: the frame is redrawn with the two
+  // buffers attached, then they are copied out.
+  int read_gbuffers(float* host_pos, float* host_nrm) {
+    VRB_REQUIRE(kind == VRB_ISO_DEFERRED || kind == VRB_ISO_ADVANCED_DEFERRED, VRB_ERR_INVALID, "vrb_iso_read_gbuffers: not a deferred-shading renderer");
+    VRB_REQUIRE(built && have_cam, VRB_ERR_INVALID, "vrb_iso_read_gbuffers before Init/Update");
+    const size_t px = (size_t)width * height;
+    int rc = ensure_gbuffers();
+    if (rc != VRB_OK) return rc;
     keep_gbuffers_ = true;
-    const int rc = redraw(0);
+    rc = redraw(0);
     keep_gbuffers_ = false;
     if (rc != VRB_OK) return rc;
     VRB_CUDA(cudaMemcpyAsync(host_pos, gbuf_, px * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
@@ -418,7 +463,25 @@ class IsoRenderer : public RendererImpl {
     return VRB_OK;
   }
 
+  // gCurvatureMax / gCurvatureMin of the last Redraw (curvature_pass.comp:129-130), width*height floats each
+  int read_curvature(float* host_k1, float* host_k2) {
+    VRB_REQUIRE(kind == VRB_ISO_ADVANCED_DEFERRED && k1k2_ && k1k2_px_ == (size_t)width * height, VRB_ERR_INVALID, "vrb_ads_read_curvature: not an initialised advanced-deferred renderer");
+    const size_t px = (size_t)width * height;
+    VRB_CUDA(cudaMemcpyAsync(host_k1, k1k2_, px * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    VRB_CUDA(cudaMemcpyAsync(host_k2, k1k2_ + px, px * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    VRB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VRB_OK;
+  }
+
   int set_params(const void* pod, size_t size) override {
+    if (kind == VRB_ISO_ADVANCED_DEFERRED && size == sizeof(vrb_ads_params)) {
+      VRB_REQUIRE(pod, VRB_ERR_INVALID, "ads set_params: null");
+      const vrb_ads_params p = *(const vrb_ads_params*)pod;
+      const int rc = set_params(&p.iso, sizeof(vrb_iso_params));
+      if (rc != VRB_OK) return rc;
+      ads_ = p;
+      return VRB_OK;
+    }
     VRB_REQUIRE(pod && size == sizeof(vrb_iso_params), VRB_ERR_INVALID, "iso set_params: size %zu != sizeof(vrb_iso_params) %zu", size, sizeof(vrb_iso_params));
     const vrb_iso_params p = *(const vrb_iso_params*)pod;
     VRB_REQUIRE(p.step_size_small > 0.0f && p.step_size_large > 0.0f, VRB_ERR_INVALID, "iso set_params: step sizes must be positive");
@@ -427,6 +490,11 @@ class IsoRenderer : public RendererImpl {
     return VRB_OK;
   }
   int get_params(void* pod, size_t size) override {
+    if (kind == VRB_ISO_ADVANCED_DEFERRED && pod && size == sizeof(vrb_ads_params)) {
+      ads_.iso = prm_;
+      *(vrb_ads_params*)pod = ads_;
+      return VRB_OK;
+    }
     VRB_REQUIRE(pod && size == sizeof(vrb_iso_params), VRB_ERR_INVALID, "iso get_params: bad size");
     *(vrb_iso_params*)pod = prm_;
     return VRB_OK;
@@ -443,8 +511,12 @@ class IsoRenderer : public RendererImpl {
 
   int redraw(int /*mode*/) override {
     VRB_REQUIRE(built && have_cam, VRB_ERR_INVALID, "iso Redraw before Init/Update");
+    const bool ads = kind == VRB_ISO_ADVANCED_DEFERRED;
+    // the curvature and ridge / valley passes read neighbouring pixels: an image partition would need the G-buffers of other ranks
+    VRB_REQUIRE(!ads || (n_ranks == 1 && n_peer_frames == 0), VRB_ERR_UNSUPPORTED, "AdvancedDeferredShading renders whole frames (replicas only): no image partition, no peers");
     int rc = ensure_quad(ctx);
     if (rc != VRB_OK) return rc;
+    if (ads) { rc = ensure_ads_buffers(); if (rc != VRB_OK) return rc; }
     const Volume& v = ctx->vol;
     IsoArgs a{};
     a.quad = v.tex_quad;
@@ -457,12 +529,12 @@ class IsoRenderer : public RendererImpl {
     a.iso = prm_.isovalue; a.step_small = prm_.step_size_small; a.step_large = prm_.step_size_large; a.step_range = prm_.step_size_range;
     for (int i = 0; i < 4; i++) a.color[i] = prm_.color[i];
     a.grad = 0;
-    if (kind == VRB_ISO_FORWARD || kind == VRB_ISO_DEFERRED) {
+    if (kind == VRB_ISO_FORWARD || kind == VRB_ISO_DEFERRED || ads) {
       // ForwardRendering.comp shades every hit from the density texture (its ApplyGradientPhongShading uniform is never read);
       // the deferred lighting pass takes Ka/Kd/Ks/shininess from the rendering parameters (DeferredShading.cpp:474-484)
       a.ka = light.ka; a.kd = light.kd; a.ks = light.ks; a.shininess = light.shininess;
       for (int i = 0; i < 3; i++) { a.ispec[i] = light.ispecular[i]; a.light_pos[i] = light.position[i]; }
-      if (keep_gbuffers_) { a.gpos = gbuf_; a.gnrm = gbuf_ + gbuf_px_; }
+      if (keep_gbuffers_ || ads) { a.gpos = gbuf_; a.gnrm = gbuf_ + gbuf_px_; }
     } else if (prm_.apply_gradient_shading) {      // m_apply_gradient_shading && GetCurrentGradientTexture() (rc1pisoadaptrenderer.cpp Update)
       VRB_REQUIRE(v.tex_grad && v.grad_gen == v.generation, VRB_ERR_INVALID, "iso renderer: gradient shading needs vrb_volume_gradient() for the current volume");
       a.grad = v.tex_grad; a.grad_pt = v.tex_grad_pt; a.ka = light.ka; a.kd = light.kd; a.ks = light.ks; a.shininess = light.shininess;
@@ -508,9 +580,16 @@ class IsoRenderer : public RendererImpl {
     else if (kind == VRB_ISO_SKIP_V1) { if (c) LAUNCH(1, true); else LAUNCH(1, false); }
     else if (kind == VRB_ISO_SKIP_V2) { if (c) LAUNCH(2, true); else LAUNCH(2, false); }
     else if (kind == VRB_ISO_FORWARD) { if (c) LAUNCH(3, true); else LAUNCH(3, false); }
-    else { if (c) LAUNCH(4, true); else LAUNCH(4, false); }
+    else if (kind == VRB_ISO_DEFERRED) { if (c) LAUNCH(4, true); else LAUNCH(4, false); }
+    else { if (c) LAUNCH(5, true); else LAUNCH(5, false); }
 #undef LAUNCH
     VRB_CUDA(cudaGetLastError());
+    if (ads) {
+      const size_t px = (size_t)width * height;
+      ads_.iso = prm_;
+      return ads_run_passes(s, width, height, gbuf_, gbuf_ + gbuf_px_, k1k2_, k1k2_ + px, maps_, maps_ + 256 * 3, cam.eye, light.position, prm_.color[3], ads_,
+                            (uint2*)frame);
+    }
     return VRB_OK;
   }
 
@@ -518,18 +597,25 @@ class IsoRenderer : public RendererImpl {
   vrb_iso_params prm_{};
   BlockGrid blocks_;
   float4* gbuf_ = nullptr; size_t gbuf_px_ = 0; bool keep_gbuffers_ = false;
+  vrb_ads_params ads_{}; float* k1k2_ = nullptr; size_t k1k2_px_ = 0; float* maps_ = nullptr;
 };
 
 RendererImpl* make_iso(vrb_ctx* ctx, int kind) { return new IsoRenderer(ctx, kind); }
 
 int iso_read_blocks(RendererImpl* impl, float* host_min, float* host_max) {
-  VRB_REQUIRE(impl->kind == VRB_ISO_SKIP_V1 || impl->kind == VRB_ISO_SKIP_V2 || impl->kind == VRB_ISO_FORWARD || impl->kind == VRB_ISO_DEFERRED,
+  VRB_REQUIRE(impl->kind == VRB_ISO_SKIP_V1 || impl->kind == VRB_ISO_SKIP_V2 || impl->kind == VRB_ISO_FORWARD || impl->kind == VRB_ISO_DEFERRED ||
+              impl->kind == VRB_ISO_ADVANCED_DEFERRED,
               VRB_ERR_INVALID, "vrb_iso_read_blocks: renderer has no block grid");
   return static_cast<IsoRenderer*>(impl)->read_blocks(host_min, host_max);
 }
 
+int ads_read_curvature(RendererImpl* impl, float* host_k1, float* host_k2) {
+  VRB_REQUIRE(impl->kind == VRB_ISO_ADVANCED_DEFERRED, VRB_ERR_INVALID, "vrb_ads_read_curvature: not an advanced-deferred renderer");
+  return static_cast<IsoRenderer*>(impl)->read_curvature(host_k1, host_k2);
+}
+
 int iso_read_gbuffers(RendererImpl* impl, float* host_pos, float* host_nrm) {
-  VRB_REQUIRE(impl->kind == VRB_ISO_DEFERRED, VRB_ERR_INVALID, "vrb_iso_read_gbuffers: not a deferred-shading renderer");
+  VRB_REQUIRE(impl->kind == VRB_ISO_DEFERRED || impl->kind == VRB_ISO_ADVANCED_DEFERRED, VRB_ERR_INVALID, "vrb_iso_read_gbuffers: not a deferred-shading renderer");
   return static_cast<IsoRenderer*>(impl)->read_gbuffers(host_pos, host_nrm);
 }
 

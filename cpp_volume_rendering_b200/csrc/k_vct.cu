@@ -435,6 +435,7 @@ constexpr int VCT_CONE_TABLE = 256;
 __shared__ float s_vct_cone[3][VCT_CONE_TABLE];
 
 struct VctShader {
+  static constexpr int ADVANCE = 1, BATCH = 1;   // park-and-shade schedule of the shared march (vrb_march.cuh): the cone of ONE sample is spread over the warp, so parking samples gains nothing: lockstep 12.7 ms, (4, 16) 13.0 ms at 512^3 / 1024^2
   static constexpr bool OBJECT_SPACE = false;
   static constexpr int PHONG_KIND = 1;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   struct Args {

@@ -245,6 +245,7 @@ int vct_region_begin(RendererImpl* impl, double* dev_means, int dims[3], int* le
 int vct_region_finish(RendererImpl* impl, const double* dev_means, double global_max);
 int iso_read_blocks(RendererImpl* impl, float* host_min, float* host_max);
 int iso_read_gbuffers(RendererImpl* impl, float* host_pos, float* host_nrm);
+int ads_read_curvature(RendererImpl* impl, float* host_k1, float* host_k2);
 
 // vrb_renderer.cu: cuStreamWaitValue32(stream, addr, value, GEQ) through the runtime's driver entry point lookup
 int stream_wait_geq(cudaStream_t s, const unsigned* addr, unsigned value);

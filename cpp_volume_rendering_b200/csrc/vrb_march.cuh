@@ -1,7 +1,7 @@
 // Shared front-to-back march of the shadowed DVR renderers (VCT, DOS cone tracing): the common part of
 // vct_ray_bbox_marching.comp:191-264 and crtgt_ray_bbox_marching.comp — ray setup, half-step sampling, classification,
 // `k*(c*Iocc*ka + c*Isdw*kd)` shading, exp() opacity, ERT at 0.99 — around a per-renderer shading functor.
-//   struct Shader { static constexpr bool OBJECT_SPACE; static constexpr int PHONG_KIND; struct Args {...}; struct Const {...};
+//   struct Shader { static constexpr bool OBJECT_SPACE; static constexpr int PHONG_KIND, ADVANCE, BATCH; struct Args {...}; struct Const {...};
 //     static __device__ void  prepare_block(const MarchArgs&, const Args&);   // all threads, before the CTA barrier: shared tables
 //     static __device__ Const prepare(const MarchArgs&, const Args&);
 //     // called by all 32 lanes of the converged warp; lanes with need == true get their sample at tx shaded
@@ -29,6 +29,9 @@ struct MarchArgs {
   // region (bricked) volumes: normalised coordinate of the stored region = p * vscale + vbias (1 and 0 for a whole volume), texel
   // offset of the region inside the volume for the point-sampled footprint texture
   float vscale[3], vbias[3], voff[3];
+  // park-and-shade schedule: `advance` samples a lane marches between two looks at the warp, `batch` lanes that must hold a parked
+  // sample before the warp shades (1, 1 = lockstep: shade as soon as any lane has a sample)
+  int advance, batch;
   int count_mode;                    // COUNT kernels: 1 = march-loop iterations, 2 = shaded (non-transparent) samples, 3 = the shader's own unit
                                      // (VCT: cone steps inside the volume), added to `samples` by the shader
   int rank, n_ranks, tile, tiles_x, n_tiles, n_items; unsigned scramble; const int* tile_order; unsigned* queue;
@@ -112,72 +115,85 @@ __global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __
       while (k > 0 && !(a.step <= __fsub_rn(D, __ldg(a.lattice + k - 1)))) k--;
       s = __ldg(a.lattice + k);
     }
-    while (__any_sync(0xffffffffu, alive)) {
-      bool need = false;                       // this lane has a sample to shade in this iteration
-      float h = 0.0f;
-      f3 tx = mk3(0.f, 0.f, 0.f);
-      float4 src = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (alive && !(s < D)) alive = false;
-      if (alive) {
-        h = gmin(a.step, __fsub_rn(D, s));
-        tx = add3(wd, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));
-        bool inside = true;
-        if (SL) {
-          // every rank evaluates the same float32 lattice, so each sample belongs to exactly one brick; a brick is convex:
-          // once the ray has left it, it is done
-          inside = tx.x >= a.brick_lo[0] && tx.x < a.brick_hi[0] && tx.y >= a.brick_lo[1] && tx.y < a.brick_hi[1] &&
-                   tx.z >= a.brick_lo[2] && tx.z < a.brick_hi[2];
-          if (!inside && entered) alive = false;
-          entered = entered || inside;
-        }
-        if (alive && inside) {
-          const f3 p = mul3(tx, inv_sizes);
-          if (COUNT && a.count_mode == 1) nsamp++;
-          const float d_hw = tex3D<float>(a.vol, fmaf(p.x, a.vscale[0], a.vbias[0]), fmaf(p.y, a.vscale[1], a.vbias[1]), fmaf(p.z, a.vscale[2], a.vbias[2]));
-          int j = (int)fminf(fmaxf(fmaf(d_hw, tfn, -0.5f), 0.0f), tfmax);
-          if ((s_mask[j >> 5] >> (j & 31)) & 1u) {
-            const float density = tex3d_f32_exact(a.vol_quad, p, res, mk3(a.voff[0], a.voff[1], a.voff[2]));
-            const float u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
-            j = (int)u;
-            const float w = u - (float)j;
-            const uint4 e = s_tf[j];
-            const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&e.y));
-            const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
-            src = make_float4(fmaf(w, r1.x - r0.x, r0.x), fmaf(w, r1.y - r0.y, r0.y), fmaf(w, b1.x - b0.x, b0.x), fmaf(w, b1.y - b0.y, b0.y));
-            if (SL == 1) {                     // opacity only: what the bricks behind need to know
-              if (src.w > 0.0f) {
-                dst.w += (1.0f - dst.w) * (1.0f - expf(-src.w * h));
-                if (dst.w > 0.99f) alive = false;
+    // The rays march independently but SHADE together: a lane that reaches a non-transparent sample parks it (`pending`) while the
+    // other lanes march on; once MARCH_BATCH lanes hold a sample — or nobody can march on — S::shade_warp runs for all of them at
+    // once.  A few per cent of the samples are shaded and each costs tens to hundreds of fetches, so without the parking most lanes
+    // of a shading warp idle (ncu r2: 16-17 of 32 lanes per instruction for the cone tracers).  Neighbouring rays park neighbouring
+    // samples, which keeps the cones' fetches close in the caches.  Every ray composites its own samples in order: same bits.
+    bool pending = false;
+    float pend_h = 0.0f;
+    f3 pend_tx = mk3(0.f, 0.f, 0.f);
+    float4 pend_src = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (;;) {
+#pragma unroll 1
+      for (int it = 0; it < a.advance && alive && !pending; it++) {
+        if (!(s < D)) alive = false;
+        if (alive) {
+          const float h = gmin(a.step, __fsub_rn(D, s));
+          const f3 tx = add3(wd, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));
+          bool inside = true;
+          if (SL) {
+            // every rank evaluates the same float32 lattice, so each sample belongs to exactly one brick; a brick is convex:
+            // once the ray has left it, it is done
+            inside = tx.x >= a.brick_lo[0] && tx.x < a.brick_hi[0] && tx.y >= a.brick_lo[1] && tx.y < a.brick_hi[1] &&
+                     tx.z >= a.brick_lo[2] && tx.z < a.brick_hi[2];
+            if (!inside && entered) alive = false;
+            entered = entered || inside;
+          }
+          if (alive && inside) {
+            const f3 p = mul3(tx, inv_sizes);
+            if (COUNT && a.count_mode == 1) nsamp++;
+            const float d_hw = tex3D<float>(a.vol, fmaf(p.x, a.vscale[0], a.vbias[0]), fmaf(p.y, a.vscale[1], a.vbias[1]), fmaf(p.z, a.vscale[2], a.vbias[2]));
+            int j = (int)fminf(fmaxf(fmaf(d_hw, tfn, -0.5f), 0.0f), tfmax);
+            if ((s_mask[j >> 5] >> (j & 31)) & 1u) {
+              const float density = tex3d_f32_exact(a.vol_quad, p, res, mk3(a.voff[0], a.voff[1], a.voff[2]));
+              const float u = fminf(fmaxf(fmaf(density, tfn, -0.5f), 0.0f), tfmax);
+              j = (int)u;
+              const float w = u - (float)j;
+              const uint4 e = s_tf[j];
+              const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&e.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&e.y));
+              const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&e.z)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&e.w));
+              const float4 src = make_float4(fmaf(w, r1.x - r0.x, r0.x), fmaf(w, r1.y - r0.y, r0.y), fmaf(w, b1.x - b0.x, b0.x), fmaf(w, b1.y - b0.y, b0.y));
+              if (SL == 1) {                     // opacity only: what the bricks behind need to know
+                if (src.w > 0.0f) {
+                  dst.w += (1.0f - dst.w) * (1.0f - expf(-src.w * h));
+                  if (dst.w > 0.99f) alive = false;
+                }
+              } else if (src.w > 0.0f) {
+                if (!S::OBJECT_SPACE || a.apply_occlusion || a.apply_shadow) {   // obj_ray_marching.comp:312
+                  pending = true; pend_tx = tx; pend_src = src; pend_h = h;
+                }
               }
-            } else {
-              need = src.w > 0.0f && (!S::OBJECT_SPACE || a.apply_occlusion || a.apply_shadow);   // obj_ray_marching.comp:312
             }
           }
+          if (alive) s = __fadd_rn(s, h);
         }
       }
-      if (SL != 1) {
-        float Iocc = 0.0f, Isdw = 0.0f;
-        S::shade_warp(a, sa, sc, need, tx, cdir, Iocc, Isdw);
-        if (COUNT && a.count_mode == 2 && need) nsamp++;
-        if (need) {
-          float ka = 0.0f, kd = 0.0f;
-          if (a.apply_occlusion) ka = a.ka;
-          if (a.apply_shadow) kd = a.kd;
-          if (!phong_shade_sample(S::PHONG_KIND, a.phong, tx, sizes, res, mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]),
-                                  mk3(a.eye[0], a.eye[1], a.eye[2]), ka, kd, a.apply_shadow != 0, Iocc, Isdw, src)) {
-            const float k = 1.0f / (ka + kd);
-            src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
-            src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
-            src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
-          }
-          const float alpha = 1.0f - expf(-src.w * h);
-          const float wgt = (1.0f - dst.w) * alpha;
-          dst.x = fmaf(wgt, src.x, dst.x); dst.y = fmaf(wgt, src.y, dst.y); dst.z = fmaf(wgt, src.z, dst.z); dst.w += wgt;
-          if (SL == 2) { if (1.0f - t_front * (1.0f - dst.w) > 0.99f) alive = false; }   // the single march's accumulated opacity
-          else if (dst.w > 0.99f) alive = false;
+      const unsigned pm = __ballot_sync(0xffffffffu, pending), am = __ballot_sync(0xffffffffu, alive && !pending);
+      if (pm == 0u && am == 0u) break;
+      if (SL == 1 || (__popc(pm) < a.batch && am != 0u)) continue;              // keep marching: too few samples to shade yet
+      float Iocc = 0.0f, Isdw = 0.0f;
+      S::shade_warp(a, sa, sc, pending, pend_tx, cdir, Iocc, Isdw);
+      if (COUNT && a.count_mode == 2 && pending) nsamp++;
+      if (pending) {
+        float4 src = pend_src;
+        float ka = 0.0f, kd = 0.0f;
+        if (a.apply_occlusion) ka = a.ka;
+        if (a.apply_shadow) kd = a.kd;
+        if (!phong_shade_sample(S::PHONG_KIND, a.phong, pend_tx, sizes, res, mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]),
+                                mk3(a.eye[0], a.eye[1], a.eye[2]), ka, kd, a.apply_shadow != 0, Iocc, Isdw, src)) {
+          const float k = 1.0f / (ka + kd);
+          src.x = k * (src.x * Iocc * ka + src.x * Isdw * kd);
+          src.y = k * (src.y * Iocc * ka + src.y * Isdw * kd);
+          src.z = k * (src.z * Iocc * ka + src.z * Isdw * kd);
         }
+        const float alpha = 1.0f - expf(-src.w * pend_h);
+        const float wgt = (1.0f - dst.w) * alpha;
+        dst.x = fmaf(wgt, src.x, dst.x); dst.y = fmaf(wgt, src.y, dst.y); dst.z = fmaf(wgt, src.z, dst.z); dst.w += wgt;
+        if (SL == 2) { if (1.0f - t_front * (1.0f - dst.w) > 0.99f) alive = false; }   // the single march's accumulated opacity
+        else if (dst.w > 0.99f) alive = false;
+        pending = false;
       }
-      if (alive) s = __fadd_rn(s, h);
     }
     if (!in_image) continue;
     if (SL == 1) {
@@ -225,6 +241,7 @@ inline bool fill_march_args(const RendererImpl& r, float step, int apply_occlusi
   a.ka = r.light.ka; a.kd = r.light.kd; a.apply_occlusion = apply_occlusion; a.apply_shadow = apply_shadow;
   fill_phong(r, phong, a.phong);
   a.frame = (uint2*)r.frame; a.samples = r.d_samples; a.count_mode = 1;
+  a.advance = 1; a.batch = 1;          // lockstep; launch_march_t takes the shader's own schedule (S::ADVANCE, S::BATCH)
   a.n_peers = r.n_peer_frames;
   for (int q = 0; q < r.n_peer_frames; q++) a.peer[q] = (uint2*)r.peer_frames[q];
   a.rank = r.rank; a.n_ranks = r.n_ranks; a.tile = r.part_tile;
@@ -247,7 +264,9 @@ inline bool fill_march_args(const RendererImpl& r, float step, int apply_occlusi
 }
 
 template <class S, bool COUNT, int SL = 0>
-int launch_march_t(const RendererImpl& r, const MarchArgs& a, const typename S::Args& sa) {
+int launch_march_t(const RendererImpl& r, const MarchArgs& a_in, const typename S::Args& sa) {
+  MarchArgs a = a_in;
+  a.advance = S::ADVANCE; a.batch = S::BATCH;
   const size_t smem = (size_t)a.tf_n * sizeof(uint4) + (size_t)a.vis_words * sizeof(uint32_t);
   VRB_REQUIRE(smem <= 200 * 1024, VRB_ERR_UNSUPPORTED, "transfer function of %d entries does not fit shared memory", a.tf_n);
   auto kern = shaded_march_kernel<S, COUNT, SL>;

@@ -190,7 +190,7 @@ int vrb_renderer_create(vrb_ctx* ctx, int kind, vrb_renderer** out) {
   RendererImpl* impl = nullptr;
   switch (kind) {
     case VRB_RC1PASS: impl = make_rc1pass(ctx); break;
-    case VRB_ISO_ADAPT: case VRB_ISO_SKIP_V1: case VRB_ISO_SKIP_V2: case VRB_ISO_FORWARD: case VRB_ISO_DEFERRED: impl = make_iso(ctx, kind); break;
+    case VRB_ISO_ADAPT: case VRB_ISO_SKIP_V1: case VRB_ISO_SKIP_V2: case VRB_ISO_FORWARD: case VRB_ISO_DEFERRED: case VRB_ISO_ADVANCED_DEFERRED: impl = make_iso(ctx, kind); break;
     case VRB_EBS_SAT: impl = make_ebs(ctx); break;
     case VRB_VCT: impl = make_vct(ctx); break;
     case VRB_DOS_CONE: impl = make_dos(ctx); break;
@@ -660,6 +660,11 @@ int vrb_crtgt_read_state(vrb_renderer* r, float* host_rg, long long* unfinished)
 int vrb_iso_read_gbuffers(vrb_renderer* r, float* host_position, float* host_normal) {
   VRB_REQUIRE(r && host_position && host_normal, VRB_ERR_INVALID, "vrb_iso_read_gbuffers: null argument");
   return iso_read_gbuffers(r->impl, host_position, host_normal);
+}
+
+int vrb_ads_read_curvature(vrb_renderer* r, float* host_k1, float* host_k2) {
+  VRB_REQUIRE(r && host_k1 && host_k2, VRB_ERR_INVALID, "vrb_ads_read_curvature: null argument");
+  return ads_read_curvature(r->impl, host_k1, host_k2);
 }
 
 int vrb_iso_read_blocks(vrb_renderer* r, float* host_min, float* host_max) {

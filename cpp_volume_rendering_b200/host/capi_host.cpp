@@ -89,8 +89,9 @@ static void register_all(RenderingManager* m) {
   m->AddVolumeRenderer(new CudaRayCasting1PassIso(VRB_ISO_FORWARD));    // 8  (main.cpp:75)
   m->AddVolumeRenderer(new CudaRayCasting1PassIso(VRB_ISO_DEFERRED));   // 9  (main.cpp:73)
   m->AddVolumeRenderer(new CudaRC1PConeLightGroundTruthSteps());        // 10 (main.cpp:67)
+  m->AddVolumeRenderer(new CudaRayCasting1PassIso(VRB_ISO_ADVANCED_DEFERRED));   // 11 (main.cpp:74)
 }
-int vrbh_num_renderers(void) { return 11; }
+int vrbh_num_renderers(void) { return 12; }
 
 // Test hook: what the ImGui "light cache" checkbox / resolution fields (PreIlluminationStructuredVolume::SetImGuiComponents,
 // preillumination.cpp:82-116) would set on the next session's DOS / EBS / VCT renderer.  active < 0 leaves the constructor's state.

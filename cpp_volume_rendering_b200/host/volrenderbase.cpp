@@ -157,7 +157,8 @@ void CudaRayCasting1Pass::FillParameterSpace(ParameterSpace& pspace) {
 // ---- CudaRayCasting1PassIso ----------------------------------------------------------------------------------
 CudaRayCasting1PassIso::CudaRayCasting1PassIso(int kind)
     : m_u_isovalue(0.5f), m_u_step_size_small(0.05f), m_u_step_size_large(1.0f), m_u_step_size_range(0.1f),
-      m_apply_gradient_shading(false), m_kind(kind) {   // rc1pisoadaptrenderer.cpp:13-20
+      m_apply_gradient_shading(false), m_flow_speed(1.0f), m_flow_scale(10.0f), m_accessibility_strength(0.5f), m_current_time(0.0f),
+      m_show_ridges(true), m_show_valleys(true), m_kind(kind) {   // rc1pisoadaptrenderer.cpp:13-20
   m_u_color[0] = 0.66f; m_u_color[1] = 0.6f; m_u_color[2] = 0.05f; m_u_color[3] = 1.0f;
   m_num_blocks[0] = m_num_blocks[1] = m_num_blocks[2] = kind == VRB_ISO_SKIP_V2 ? 32 : 4;
 }
@@ -167,6 +168,7 @@ const char* CudaRayCasting1PassIso::GetName() {
     case VRB_ISO_SKIP_V2: return "Empty Sapce Skipping V2 (CUDA B200)";
     case VRB_ISO_FORWARD: return "Forward Bulin Phong Shading (CUDA B200)";      // FowardRendering.cpp:136-139
     case VRB_ISO_DEFERRED: return "Deferred Rendering (CUDA B200)";               // DeferredShading.cpp:139-142
+    case VRB_ISO_ADVANCED_DEFERRED: return "Advanced Deferred Rendering (CUDA B200)";   // AdvancedDeferredShading.cpp:143-146
     default: return "1-Pass - Isosurface Raycaster Adaptive (CUDA B200)";
   }
 }
@@ -198,6 +200,13 @@ bool CudaRayCasting1PassIso::Update(vis::Camera* camera) {
   // ApplyGradientPhongShading = m_apply_gradient_shading && GetCurrentGradientTexture() (rc1pisoadaptrenderer.cpp:92,157)
   p.apply_gradient_shading = (m_apply_gradient_shading && m_ext_data_manager->HasGradientTexture()) ? 1 : 0;
   if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");
+  if (m_kind == VRB_ISO_ADVANCED_DEFERRED) {      // UpdateLightingPassUniforms (AdvancedDeferredShading.cpp:371-378)
+    vrb_ads_params q;
+    if (a->renderer_get_params(m_dev, &q, sizeof(q)) != VRB_OK) return Fail("vrb_renderer_get_params");
+    q.current_time = m_current_time; q.flow_speed = m_flow_speed; q.flow_scale = m_flow_scale; q.accessibility_strength = m_accessibility_strength;
+    q.show_ridges = m_show_ridges ? 1 : 0; q.show_valleys = m_show_valleys ? 1 : 0;
+    if (a->renderer_set_params(m_dev, &q, sizeof(q)) != VRB_OK) return Fail("vrb_renderer_set_params");
+  }
   vrb_camera c; vrb_light l;
   camera->FillUniforms(&c);
   m_ext_rendering_parameters->FillUniforms(&l);

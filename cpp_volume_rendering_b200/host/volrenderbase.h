@@ -79,10 +79,11 @@ class CudaRayCasting1Pass : public BaseVolumeRenderer {
 };
 
 // RayCasting1PassIsoAdapt / CustomRayCasting1PassIsoAdapt / CustomRayCasting1PassIsodfsAdapt / FowardRendering
-// (structured/ForwardRender) / DeferredShading (structured/DeferredShading): same members, same parameter space
+// (structured/ForwardRender) / DeferredShading (structured/DeferredShading) / AdvancedDeferredShading
+// (structured/AdvancedDeferredShading): same members, same parameter space; the last adds the members of its lighting pass
 class CudaRayCasting1PassIso : public BaseVolumeRenderer {
  public:
-  explicit CudaRayCasting1PassIso(int kind);          // VRB_ISO_ADAPT, VRB_ISO_SKIP_V1, VRB_ISO_SKIP_V2, VRB_ISO_FORWARD, VRB_ISO_DEFERRED
+  explicit CudaRayCasting1PassIso(int kind);          // VRB_ISO_ADAPT, VRB_ISO_SKIP_V1, VRB_ISO_SKIP_V2, VRB_ISO_FORWARD, VRB_ISO_DEFERRED, VRB_ISO_ADVANCED_DEFERRED
   const char* GetName() override;
   const char* GetAbbreviationName() override { return "cu_iso"; }
   vis::GRID_VOLUME_DATA_TYPE GetDataTypeSupport() override { return vis::GRID_VOLUME_DATA_TYPE::STRUCTURED; }
@@ -93,6 +94,9 @@ class CudaRayCasting1PassIso : public BaseVolumeRenderer {
   float m_u_color[4];
   bool m_apply_gradient_shading;                                // rc1pisoadaptrenderer.h (off by default)
   int m_num_blocks[3];
+  // AdvancedDeferredShading.h:129-133,164 (m_current_time: the wall clock since Init there; set by the caller here, 0 by default)
+  float m_flow_speed, m_flow_scale, m_accessibility_strength, m_current_time;
+  bool m_show_ridges, m_show_valleys;
  private:
   int m_kind;
 };

@@ -13,7 +13,7 @@ _P = C.c_void_p
 _lib = None
 
 RENDERERS = {"rc1pass": 0, "iso": 1, "iso_skip_v1": 2, "iso_skip_v2": 3, "dos": 4, "ebs": 5, "vct": 6, "sbtm": 7, "iso_forward": 8,
-             "iso_deferred": 9, "crtgt": 10}
+             "iso_deferred": 9, "crtgt": 10, "iso_advanced_deferred": 11}
 
 
 def lib():

@@ -48,7 +48,8 @@ typedef enum {
   VRB_SBTM_DOS = 7,    /* SBTMDirectionalOcclusionShading       structured/sbtmdos          */
   VRB_ISO_FORWARD = 8, /* FowardRendering                       structured/ForwardRender    */
   VRB_ISO_DEFERRED = 9,/* DeferredShading                       structured/DeferredShading  */
-  VRB_CRT_GT = 10      /* RC1PConeLightGroundTruthSteps         structured/rc1pcrtgt        */
+  VRB_CRT_GT = 10,     /* RC1PConeLightGroundTruthSteps         structured/rc1pcrtgt        */
+  VRB_ISO_ADVANCED_DEFERRED = 11 /* AdvancedDeferredShading           structured/AdvancedDeferredShading */
 } vrb_renderer_kind;
 
 typedef enum { VRB_FRAME_RGBA16F = 0, VRB_FRAME_RGB8_OVER_WHITE = 1, VRB_FRAME_RGBA32F = 2 } vrb_frame_format;
@@ -114,6 +115,20 @@ typedef struct {
   int   num_blocks[3];          /* numBlocks of the block min/max grid (skipping renderers) */
   int   count_iterations;       /* 1 = instrumented kernel that counts march-loop iterations */
 } vrb_iso_params;
+
+/* Run-time parameters of AdvancedDeferredShading: the geometry pass's (= vrb_iso_params; AdvancedDeferredShading.h:59-72) and the
+ * ImGui-mutable members of its lighting pass (AdvancedDeferredShading.h:129-133, .cpp:824-828).  current_time replaces m_current_time
+ * (the wall clock since Init there, .cpp:696).  A VRB_ISO_ADVANCED_DEFERRED renderer accepts set/get_params with either
+ * sizeof(vrb_ads_params) or sizeof(vrb_iso_params) (the geometry part alone). */
+typedef struct {
+  vrb_iso_params iso;
+  float current_time;            /* "time" uniform of lighting_pass.comp        0 */
+  float flow_speed;              /* m_flow_speed                                1.0 */
+  float flow_scale;              /* m_flow_scale                                10.0 */
+  float accessibility_strength;  /* m_accessibility_strength                    0.5 */
+  int   show_ridges;             /* m_show_ridges                               1 */
+  int   show_valleys;            /* m_show_valleys                              1 */
+} vrb_ads_params;
 
 /* Run-time parameters of RC1PExtinctionBasedShading: its ImGui-mutable members (ebsrenderer.cpp:18-42).
  * Init overwrites step_size (0.5/sqrt(3)*|voxel scale|, :115-116) and dir_cone_max_distance (0.75 * diagonal, :99-105). */
@@ -327,8 +342,14 @@ int vrb_crtgt_read_state(vrb_renderer* r, float* host_rg, long long* unfinished)
  * min / max grids of a VRB_ISO_SKIP_V1 / _V2 renderer, num_blocks[0]*[1]*[2] floats each, x fastest. */
 int vrb_iso_read_blocks(vrb_renderer* r, float* host_min, float* host_max);
 /* Test hook of a VRB_ISO_DEFERRED renderer: the gPosition / gNormal attachments of the geometry pass (geometry_pass.comp:4-5,
- * RGBA32F, width*height*4 floats each, row 0 = bottom).  The render keeps them in registers; this call redraws with both attached. */
+ * RGBA32F, width*height*4 floats each, row 0 = bottom).  The render keeps them in registers; this call redraws with both attached.
+ * Texels of rays that miss the volume box hold the glClear value the reference leaves there, (1,1,1,0) (DeferredShading.cpp:506-507
+ * with the application's clear colour, renderingmanager.cpp:40). */
 int vrb_iso_read_gbuffers(vrb_renderer* r, float* host_position, float* host_normal);
+/* Test hook of a VRB_ISO_ADVANCED_DEFERRED renderer: the gCurvatureMax / gCurvatureMin images of the last Redraw
+ * (curvature_pass.comp:129-130, R32F), width*height floats each, row 0 = bottom.  vrb_iso_read_gbuffers works for this kind too
+ * (its box-missing texels hold the (1,1,1,1) clear value of AdvancedDeferredShading.cpp:723-725).  Synchronises. */
+int vrb_ads_read_curvature(vrb_renderer* r, float* host_k1, float* host_k2);
 
 /* Test / measurement hook for K12 (GenerateExtinctionSAT3DTex, ebsrenderer.cpp:624-722, moved to the GPU): the
  * float32 table of a VRB_EBS_SAT renderer, dims = volume + 2 per axis, x fastest; build_ms = device time of the

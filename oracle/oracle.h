@@ -77,7 +77,7 @@ typedef struct {
   float eye[3];
   float lookat[9];
   float tan_fovy, aspect;
-  int   mode;                   /* 0 rc1pisoadapt, 1 rc1pisocustom (skipping v1), 2 rc1pisodfscustom (skipping v2), 3 ForwardRender, 4 DeferredShading */
+  int   mode;                   /* 0 rc1pisoadapt, 1 rc1pisocustom (skipping v1), 2 rc1pisodfscustom (skipping v2), 3 ForwardRender, 4 DeferredShading, 5 AdvancedDeferredShading's geometry pass */
   float isovalue, step_small, step_large, step_range;   /* Isovalue, StepSizeSmall, StepSizeLarge, StepSizeRange */
   float color[4];               /* Color */
   int   num_blocks[3];          /* numBlocks (modes 1, 2) */
@@ -99,6 +99,17 @@ uint64_t orc_iso_render(const orc_iso_params* p, const float* vol_r16f, const fl
 /* mode 4 (DeferredShading) with the geometry pass's G-buffers: position and normal, width*height*4 floats each. */
 uint64_t orc_iso_render_deferred(const orc_iso_params* p, const float* vol_r16f, const float* block_min, const float* block_max,
                                  float* out_rgba, uint32_t* out_iters, float* out_gpos, float* out_gnrm);
+
+/* AdvancedDeferredShading (structured/AdvancedDeferredShading): orc_iso_render_deferred with p->mode = 5 gives the geometry pass's
+ * G-buffers (box-missing pixels keep the glClear value (1,1,1,1)); orc_ads_passes runs curvature_pass.comp, lighting_pass.comp and
+ * post_process.frag over them (orc_ads.cpp states the conventions for what the reference leaves undefined).  out_k1 / out_k2:
+ * width*height floats (gCurvatureMax / gCurvatureMin); out_rgba: width*height*4, RGBA16F-rounded.  Returns the number of pixels whose
+ * ridge / valley test fetched at a non-finite coordinate.  orc_ads_maps: the 256 x RGB curvature colour map and the 256 x 256 R
+ * channel of the ridge / valley map of CreateTransferFunctions. */
+uint64_t orc_ads_passes(int width, int height, const float* gpos, const float* gnrm, const float eye[3], const float light_pos[3],
+                        const float color[4], float time, float flow_speed, float flow_scale, int show_ridges, int show_valleys,
+                        float accessibility_strength, float* out_k1, float* out_k2, float* out_rgba);
+void orc_ads_maps(float* color_rgb_256, float* ridge_256x256);
 
 /* ---- extinction-based shading (K12 SAT, K13 ray caster) ------------------------------------------------ */
 typedef struct {

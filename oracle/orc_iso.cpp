@@ -169,10 +169,19 @@ uint32_t shade_pixel(const IsoCtx& c, int px, int py, float out[4], bool* hit) {
   Ray r; float tnear, tfar;
   bool inbox = ray_aabb_intersection(eye, camera_dir, c.grid_size, r, tnear, tfar);
   *hit = inbox;
-  if (c.p->mode == 4) {                        // every pixel of the deferred renderer goes through lighting + post-process
+  if (c.p->mode >= 4) {                        // every pixel of the deferred renderers goes through lighting + post-process
     *hit = true;
-    if (c.gpos) for (int k = 0; k < 4; k++) { c.gpos[4 * ((size_t)py * c.p->width + px) + k] = 0.0f; c.gnrm[4 * ((size_t)py * c.p->width + px) + k] = 0.0f; }
-    if (!inbox) { deferred_light(c, vec3(0.0f), vec3(0.0f), out); return 0; }
+    // A ray that misses the box stores nothing (geometry_pass.comp:158): its G-buffer texels keep the value of the glClear that
+    // precedes the dispatch — the application's clear colour (1, 1, 1, 0) (renderingmanager.cpp:40,108-109; DeferredShading.cpp:506-507),
+    // (1, 1, 1, 1) in AdvancedDeferredShading (its Redraw sets it, :723-725) — and the lighting pass shades them like a surface.
+    const float cw = c.p->mode == 4 ? 0.0f : 1.0f;
+    const float g = inbox ? 0.0f : 1.0f;
+    if (c.gpos) {
+      const size_t o = 4 * ((size_t)py * c.p->width + px);
+      for (int k = 0; k < 3; k++) { c.gpos[o + k] = g; c.gnrm[o + k] = g; }
+      c.gpos[o + 3] = inbox ? 0.0f : cw; c.gnrm[o + 3] = inbox ? 0.0f : cw;
+    }
+    if (!inbox) { if (c.p->mode == 4) deferred_light(c, vec3(1.0f), vec3(1.0f), out); return 0; }
   }
   if (!inbox) return 0;
   const float iso = p.isovalue;
@@ -258,14 +267,14 @@ uint32_t shade_pixel(const IsoCtx& c, int px, int py, float out[4], bool* hit) {
         float tt = (iso - prev) / (density - prev);
         t = t - h * (1.0f - tt);                                                   // :246
         vec3 s_tex_pos = r.Origin + r.Dir * t + half;
-        if (p.mode == 4) {                                                         // geometry_pass.comp:225-235: first hit, return
+        if (p.mode >= 4) {                                                         // geometry_pass.comp:225-235: first hit, return
           vec3 normal = calculate_gradient(c, s_tex_pos);
           if (c.gpos) {
             size_t o = 4 * ((size_t)py * p.width + px);
             c.gpos[o] = s_tex_pos.x; c.gpos[o + 1] = s_tex_pos.y; c.gpos[o + 2] = s_tex_pos.z; c.gpos[o + 3] = 1.0f;
             c.gnrm[o] = normal.x; c.gnrm[o + 1] = normal.y; c.gnrm[o + 2] = normal.z; c.gnrm[o + 3] = 1.0f;
           }
-          deferred_light(c, s_tex_pos, normal, out);
+          if (p.mode == 4) deferred_light(c, s_tex_pos, normal, out);
           return n;
         }
         if (p.mode == 3) composite_forward(c, dst, s_tex_pos);                     // ForwardRendering.comp:262-270
@@ -273,7 +282,7 @@ uint32_t shade_pixel(const IsoCtx& c, int px, int py, float out[4], bool* hit) {
         if (dst.w > 0.99f) break;
       }
     }
-    if (p.mode == 4) { deferred_light(c, vec3(0.0f), vec3(0.0f), out); return n; } // no hit: zero G-buffers (:243-245)
+    if (p.mode >= 4) { if (p.mode == 4) deferred_light(c, vec3(0.0f), vec3(0.0f), out); return n; } // no hit: zero G-buffers (:243-245)
   }
   out[0] = round_f16(dst.x); out[1] = round_f16(dst.y); out[2] = round_f16(dst.z); out[3] = round_f16(dst.w);
   return n;

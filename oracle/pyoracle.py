@@ -340,6 +340,23 @@ def iso_render_deferred(p, vol_r16f, block_min, block_max):
     return out, int(total), gpos, gnrm
 
 
+def ads_render(p, vol_r16f, block_min, block_max, light_pos, time=0.0, flow_speed=1.0, flow_scale=10.0, show_ridges=1, show_valleys=1,
+               accessibility=0.5):
+    """AdvancedDeferredShading: geometry pass (p.mode = 5) + curvature / lighting / post-process passes.
+    Returns (frame [h, w, 4], gPosition, gNormal, k1 [h, w], k2 [h, w], pixels whose ridge / valley test fetched at +-inf)."""
+    p.mode = 5
+    _, _, gpos, gnrm = iso_render_deferred(p, vol_r16f, block_min, block_max)
+    h, w = p.height, p.width
+    k1 = np.zeros((h, w), np.float32); k2 = np.zeros((h, w), np.float32); out = np.zeros((h, w, 4), np.float32)
+    f = lib().orc_ads_passes
+    f.restype = C.c_uint64
+    f.argtypes = [C.c_int, C.c_int, _P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_float, _P, _P, _P]
+    eye = np.array(list(p.eye), np.float32); lp = np.array(list(light_pos), np.float32); col = np.array(list(p.color), np.float32)
+    n_inf = f(w, h, _ptr(gpos), _ptr(gnrm), _ptr(eye), _ptr(lp), _ptr(col), time, flow_speed, flow_scale, int(show_ridges), int(show_valleys),
+              accessibility, _ptr(k1), _ptr(k2), _ptr(out))
+    return out, gpos, gnrm, k1, k2, int(n_inf)
+
+
 def ext_sat3d(voxels, table, extinction_type=False, want_ext=False):
     """GenerateExtinctionSAT3DTex: float32 SAT indexed [z, y, x] of shape (d+2, h+2, w+2)."""
     v = np.ascontiguousarray(voxels)

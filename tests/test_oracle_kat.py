@@ -186,3 +186,87 @@ def test_compute_shader_sobel_matches_the_cpu_sobel_up_to_its_float32_arithmetic
     assert np.abs(g1 - g3).max() <= 32 * 2.0 ** -12 + np.abs(g1).max() * 2.0 ** -10 and np.abs(g3).max() > 0.5
     exact = (np.random.default_rng(1).integers(0, 5, (9, 8, 7)) * 0.25).astype(np.float32)      # 0, 0.25, ..., 1: exact in binary16
     assert np.array_equal(O.gradient(exact, 1), O.gradient(exact, 3))
+
+
+def _ads_passes(gpos, gnrm, eye, light_pos, alpha=1.0, time=0.0, speed=1.0, scale=10.0, ridges=1, valleys=1, access=0.5):
+    import ctypes as C
+    h, w = gpos.shape[:2]
+    k1 = np.zeros((h, w), np.float32); k2 = np.zeros((h, w), np.float32); out = np.zeros((h, w, 4), np.float32)
+    f = O.lib().orc_ads_passes
+    f.restype = C.c_uint64
+    P = C.c_void_p
+    f.argtypes = [C.c_int, C.c_int, P, P, P, P, P, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_float, P, P, P]
+    arr = lambda v: np.ascontiguousarray(v, np.float32)
+    gpos, gnrm, eye, light_pos, col = arr(gpos), arr(gnrm), arr(eye), arr(light_pos), arr([0.66, 0.6, 0.05, alpha])
+    n = f(w, h, gpos.ctypes.data, gnrm.ctypes.data, eye.ctypes.data, light_pos.ctypes.data, col.ctypes.data, time, speed, scale, ridges, valleys, access,
+          k1.ctypes.data, k2.ctypes.data, out.ctypes.data)
+    return out, k1, k2, int(n)
+
+
+def test_advanced_deferred_maps_closed_form():
+    """CreateTransferFunctions (AdvancedDeferredShading.cpp:239-300) with s = 0.6, v = 0.2: an HSV hue sweep and max(0, k1) [k1 > k2]."""
+    import colorsys
+    color = np.zeros((256, 3), np.float32); ridge = np.zeros((256, 256), np.float32)
+    O.lib().orc_ads_maps(color.ctypes.data_as(O._P), ridge.ctypes.data_as(O._P))
+    # hue in [0, 5/6) covers the first five sextants of the conversion; the reference's last branch (h >= 4) also serves h in [5, 6]
+    for i in (0, 17, 42, 43, 85, 100, 128, 170, 200, 212):
+        want = colorsys.hsv_to_rgb(i / 255.0, 0.6, 0.2)
+        assert np.allclose(color[i], want, atol=2e-7), i
+    assert np.allclose(color[255], [0.08, 0.08, 0.2], atol=1e-6)     # h = 6: x = c (1 - |0 - 1|) = 0 in the else branch -> (m, m, v)
+    x = np.arange(256, dtype=np.float32) / np.float32(255) * np.float32(2) - np.float32(1)
+    want = np.maximum(x[None, :], 0) * (x[None, :] > x[:, None])
+    assert np.array_equal(ridge, want.astype(np.float32))
+
+
+def test_advanced_deferred_flat_wall_closed_form():
+    """A plane facing the camera: every normal equal -> the shape operator vanishes, k1 = k2 = 0; mean curvature 0 looks the colour
+    map up at 0.5; accessibility = 1 - strength (1 - n.v); no ridge / valley; flow from the ridge map.  The frame value in float64."""
+    w, h = 24, 16
+    gpos = np.zeros((h, w, 4), np.float32); gnrm = np.zeros((h, w, 4), np.float32)
+    ys, xs = np.mgrid[0:h, 0:w]
+    gpos[..., 0] = xs; gpos[..., 1] = ys; gpos[..., 2] = 5.0; gpos[..., 3] = 1.0
+    gnrm[..., 2] = 2.0; gnrm[..., 3] = 1.0                            # not unit length: the passes normalise
+    eye = np.array([12.0, 8.0, 40.0]); lp = np.array([40.0, 30.0, 25.0])
+    out, k1, k2, n_inf = _ads_passes(gpos, gnrm, eye, lp, alpha=0.75, time=0.3, speed=2.0, scale=7.0, access=0.8)
+    assert np.all(k1 == 0) and np.all(k2 == 0) and n_inf == 0
+    color = np.zeros((256, 3), np.float32); ridge = np.zeros((256, 256), np.float32)
+    O.lib().orc_ads_maps(color.ctypes.data_as(O._P), ridge.ctypes.data_as(O._P))
+
+    def lin(u):
+        X = u * 256.0 - 0.5; f = np.floor(X)
+        return int(np.clip(f, 0, 255)), int(np.clip(f + 1, 0, 255)), X - f
+
+    def ridge_at(u, v):
+        x0, x1, ax = lin(u); y0, y1, ay = lin(v)
+        c0 = ridge[y0, x0] + ax * (ridge[y0, x1] - ridge[y0, x0]); c1 = ridge[y1, x0] + ax * (ridge[y1, x1] - ridge[y1, x0])
+        return c0 + ay * (c1 - c0)
+
+    i0, i1, a = lin(0.5)
+    cc = color[i0] + a * (color[i1] - color[i0])
+    for (x, y) in [(0, 0), (5, 3), (23, 15), (11, 9)]:
+        pos = np.array([x, y, 5.0]); n = np.array([0.0, 0.0, 1.0])
+        L = (lp - pos) / np.linalg.norm(lp - pos); V = (eye - pos) / np.linalg.norm(eye - pos); H = (L + V) / np.linalg.norm(L + V)
+        base = 0.1 + 0.7 * max(n @ L, 0) + 0.2 * max(n @ H, 0) ** 32
+        access = np.clip(1 - 0.8 * (0 + (1 - max(n @ V, 0))), 0, 1)
+        fx, fy = x / w * 7.0 + 0.3 * 2.0, y / h * 7.0
+        flow = 0.5 * ridge_at(fx, fy) + 0.5 * ridge_at(fx * 2 + 0.15, fy * 2 + 0.15)
+        c = base * access
+        c = c * 0.7 + cc * 0.3
+        c = c * 0.8 + flow * 0.2
+        want = (1 - np.exp(-c)) ** (1 / 2.2)
+        assert np.allclose(out[y, x, :3], want, atol=1.5e-3), (x, y)          # RGBA16F rounding of values below 1
+        assert out[y, x, 3] == 0.75
+
+
+def test_advanced_deferred_background_and_clear_value():
+    """Zero normals (ray through the box, no crossing) give the white of lighting_pass.comp:190-194 after tone mapping; texels left at
+    the glClear value (1, 1, 1, 1) are shaded like a surface with normal (1,1,1)/sqrt(3) — not white."""
+    w, h = 8, 8
+    gpos = np.zeros((h, w, 4), np.float32); gnrm = np.zeros((h, w, 4), np.float32)
+    gpos[4:] = 1.0; gnrm[4:] = 1.0
+    out, k1, k2, _ = _ads_passes(gpos, gnrm, [0, 0, 30], [10, 20, 30])
+    bg = (1.0 - math.exp(-1.0)) ** (1.0 / 2.2)
+    assert np.allclose(out[:4, :, :3], bg, atol=1e-3) and np.all(out[:4, :, 3] == 1.0)
+    assert np.all(k1[:4] == 0) and np.all(k2[:4] == 0)
+    assert np.all(np.abs(out[5:7, 1:7, :3] - bg) > 0.05)
+    assert np.all(k1[5:7, 1:7] == 0)                                   # constant normals inside the cleared region: flat

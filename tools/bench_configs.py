@@ -31,7 +31,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 ALL = ("c1", "c3", "c3s", "c4", "vct", "sbtm")
-NCU = {"c1": "r2_ncu_full_c1_rc1pass.csv", "c3": "r2_ncu_full_c3_dos.csv", "c3s": "r2_ncu_full_c3_dos_shadow.csv", "c4": "r2_ncu_full_c4_ebs.csv",
+NCU = {"c1": "r2_ncu_full_c1.csv", "c3": "r2_ncu_full_c3.csv", "c3s": "r2_ncu_full_c3s.csv", "c4": "r2_ncu_full_c4.csv",
        "vct": "r2_ncu_full_vct.csv", "sbtm": "r2_ncu_full_sbtm.csv"}
 
 

@@ -15,7 +15,7 @@ for k in "$@"; do
     c1)   cap c1 rc1pass_kernel 2 ;;
     c3)   cap c3 shaded_march_kernel 3 ;;
     c3s)  cap c3s shaded_march_kernel 3 ;;
-    c4)   cap c4 shaded_march_kernel 4 ;;
+    c4)   cap c4 ebs_kernel 4 ;;
     vct)  cap vct shaded_march_kernel 4 ;;
     sbtm) cap sbtm sbtm_kernel 2 ;;
   esac
