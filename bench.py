@@ -263,7 +263,7 @@ def run_cuda(args):
         # IPC peer memory over NVLink) and then raises a per-frame flag there; the stream waits on the flags
         # (cuStreamWaitValue32) — no collective on the frame and none for the end-of-frame synchronisation
         from cpp_volume_rendering_b200 import multigpu
-        multigpu.setup_fused_gather(r, rank, world, tile=PART_TILE, mode=_capi.VRB_GATHER_ALL)
+        multigpu.setup_fused_gather(r, rank, world, tile=PART_TILE, mode=_capi.VRB_GATHER_ALL if args.gather == "all" else _capi.VRB_GATHER_ROOT)
 
     # sample count of this frame (instrumented launch, untimed)
     prm.count_samples = 1
@@ -344,33 +344,54 @@ def run_cuda(args):
     # e2e through the C ABI with host buffers: camera/light structs in, RGBA16F frame out to pinned memory
     # Two pinned frames: the transfer of frame k (vrb_renderer_read_frame_async, second stream) runs under the render of
     # frame k + 1; the host takes frame k once that render has been launched.  Every frame is transferred inside the timed region.
-    pinned = [torch.empty((IMG_H, IMG_W, 4), dtype=torch.float16).pin_memory() for _ in range(2)]
-    d2h = pinned[0].numel() * 2
-    reader = rank == 0 or world == 1
+    # N = 1: two pinned frames, vrb_renderer_read_frame_async.  N > 1: no gather at all in this leg — every rank stores ITS OWN tiles
+    # into one host frame in shared memory over its own PCIe link (vrb_renderer_read_tiles_async, multigpu.SharedHostFrame); rank 0 is
+    # the consumer and polls one arrival word per rank.  Either way the host holds frame k - 1 complete before step k + 1 begins.
+    d2h = IMG_W * IMG_H * 8
     e2e_k = [0]
+    shf = None
+    if world > 1:
+        barrier()
+        r.set_peers([], rank, _capi.VRB_GATHER_NONE)     # the partition stays; no peer stores, no arrival waits
+        barrier()
+        name = [f"vrb200_e2e_{os.getpid()}_{int(time.time() * 1e3) & 0xffffff}"]
+        dist.broadcast_object_list(name, src=0)
+        shf = multigpu.SharedHostFrame(ctx, name[0], IMG_W, IMG_H, rank, world, barrier=dist.barrier)
 
-    def e2e_step():
-        r.update(cam, light)          # h2d: the step's inputs are the camera + light uniforms (kernel arguments)
-        r.redraw()
-        if world > 1:
-            r.wait_peers()
-        if reader:
+        def e2e_step():
+            e2e_k[0] += 1
+            k = e2e_k[0]
+            r.update(cam, light)
+            r.redraw()
+            shf.submit(r, k)                                           # this rank's tiles of frame k -> the shared host frame
+            if rank == 0 and k > 1:
+                shf.wait(k - 1); shf.release(k - 1)                    # frame k - 1 is complete on the host
+
+        def e2e_drain():
+            if rank == 0:
+                shf.wait(e2e_k[0]); shf.release(e2e_k[0])
+            r.read_frame_wait()
+    else:
+        pinned = [torch.empty((IMG_H, IMG_W, 4), dtype=torch.float16).pin_memory() for _ in range(2)]
+
+        def e2e_step():
+            r.update(cam, light)          # h2d: the step's inputs are the camera + light uniforms (kernel arguments)
+            r.redraw()
             r.read_frame_wait()                                        # frame k - 1 is on the host
             r.read_frame_async(pinned[e2e_k[0] & 1].data_ptr())        # d2h of frame k, ordered after its redraw
-        else:
-            ctx.synchronize()
-        e2e_k[0] += 1
+            e2e_k[0] += 1
+
+        def e2e_drain():
+            r.read_frame_wait()
 
     for _ in range(3):
         e2e_step()
-    if reader:
-        r.read_frame_wait()
+    e2e_drain()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         e2e_step()
-    if reader:
-        r.read_frame_wait()                                            # the last frame too
+    e2e_drain()                                                        # the last frame too
     ctx.synchronize()
     barrier()
     e2e_ms = 1e3 * (time.perf_counter() - t0) / args.steps
@@ -398,8 +419,9 @@ def run_cuda(args):
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": dict(workload_config(), workload=workload_name(args.skip)),
-            "setup": {"partition": f"image tiles {PART_TILE}x{PART_TILE} round-robin over {world} rank(s)" + (", fused peer-memory gather into every rank's frame + per-frame flag wait (no collective)" if world > 1 else ""),
-                      "e2e_path": "update + redraw + vrb_renderer_read_frame_async into pinned host memory every step; the transfer of frame k overlaps the render of frame k + 1",
+            "setup": {"partition": f"image tiles {PART_TILE}x{PART_TILE} round-robin over {world} rank(s)" + ((", fused peer-memory gather into every rank's frame" if args.gather == "all" else ", fused peer-memory gather into rank 0's frame (credit back-pressure)") + " + per-frame flag wait (no collective)" if world > 1 else ""),
+                      "e2e_path": ("update + redraw + vrb_renderer_read_frame_async into pinned host memory every step; the transfer of frame k overlaps the render of frame k + 1" if world == 1 else
+                                   "update + redraw + vrb_renderer_read_tiles_async every step: no gather, every rank stores its own tiles into one shared pinned host frame over its own PCIe link, rank 0 polls the per-rank arrival words; the stores of frame k overlap the render of frame k + 1"),
                       "init_ms_volume_upload": init_ms, "tf_in_smem": args.tf_smem, "exact_filter": args.exact, "skip_block": args.skip, "depth_split": depth_split},
             "measured": {"samples_per_frame": fetched_total, "fps": 1e3 / ms_per_step,
                          "ms_per_step_min_median_max": [float(min(per_step)), float(np.median(per_step)), float(max(per_step))],
@@ -428,10 +450,8 @@ def run_cuda(args):
             v, cores, total, secs = cpu_frame(vox, table, cam, repeats=2)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"full {IMG_W}x{IMG_H} frame ({total} samples, best of 2, {secs:.2f} s), oracle/liboracle.so OpenMP over rows"}
-    if world > 1:
-        barrier()
-        r.set_peers([], rank, _capi.VRB_GATHER_NONE)
-        barrier()
+    if shf is not None:
+        shf.close(barrier=dist.barrier)
     if r is not None:
         r.close()
     ctx.close()
@@ -485,6 +505,7 @@ def main():
     ap.add_argument("--exact", type=int, default=1, help="float32 re-filtering of possibly-visible samples")
     ap.add_argument("--no-cpu", action="store_true", help="omit the cpu_baseline leg")
     ap.add_argument("--depth-split", type=int, default=-1, help="lanes per ray (0/1, 2, 4, 8); -1 = by the number of GPUs")
+    ap.add_argument("--gather", default="all", choices=["all", "root"], help="N > 1, device-timed leg: every rank collects the frame (all) or rank 0 only (root)")
     ap.add_argument("--no-c5", action="store_true", help="omit extras.c5 (config 5 on the bricked 2048^3 volume) at N >= 2")
     ap.add_argument("--config", default="c2", choices=["c2", "c5"], help="c2: the headline (RayCasting1Pass, config 2); c5: config 5 alone")
     args = ap.parse_args()

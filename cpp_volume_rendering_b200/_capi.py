@@ -80,7 +80,7 @@ class VctParams(C.Structure):
                 ("cone_step_increase_rate", C.c_float), ("cone_initial_step", C.c_float), ("cone_apex_angle", C.c_float),
                 ("apply_correction_factor", C.c_int), ("opacity_correction_factor", C.c_float),
                 ("cone_number_of_samples", C.c_int), ("count_samples", C.c_int),
-                ("use_light_cache", C.c_int), ("light_cache_resolution", C.c_int * 3)]
+                ("use_light_cache", C.c_int), ("light_cache_resolution", C.c_int * 3), ("exact_cone_filter", C.c_int)]
 
 
 class SbtmParams(C.Structure):
@@ -99,7 +99,8 @@ class DosParams(C.Structure):
                 ("type_of_shadow", C.c_int), ("spot_light_max_angle", C.c_float),
                 ("light_cam_forward", C.c_float * 3), ("light_cam_up", C.c_float * 3), ("light_cam_right", C.c_float * 3),
                 ("base_level_sigma0", C.c_float), ("use_custom_resolution", C.c_int), ("custom_resolution", C.c_int * 3),
-                ("count_samples", C.c_int), ("use_light_cache", C.c_int), ("light_cache_resolution", C.c_int * 3)]
+                ("count_samples", C.c_int), ("use_light_cache", C.c_int), ("light_cache_resolution", C.c_int * 3),
+                ("exact_cone_filter", C.c_int)]
 
 
 # name -> (restype, argtypes); the list doubles as the "every declared symbol is exported" check.
@@ -132,6 +133,9 @@ SIGNATURES = {
     "vrb_renderer_read_frame": (C.c_int, [_P, _P, C.c_int]),
     "vrb_renderer_read_frame_async": (C.c_int, [_P, _P, C.c_int]),
     "vrb_renderer_read_frame_wait": (C.c_int, [_P]),
+    "vrb_renderer_read_tiles_async": (C.c_int, [_P, _P, _P, C.c_uint]),
+    "vrb_host_register": (C.c_int, [_P, _P, C.c_size_t]),
+    "vrb_host_unregister": (C.c_int, [_P, _P]),
     "vrb_renderer_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_double)]),
     "vrb_ebs_read_sat": (C.c_int, [_P, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_float)]),
     "vrb_dos_read_extcoef": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int * 3), C.POINTER(C.c_int), C.POINTER(C.c_float)]),
@@ -198,6 +202,12 @@ class Context:
 
     def synchronize(self):
         _check(lib().vrb_ctx_synchronize(self._h))
+
+    def host_register(self, ptr, nbytes):
+        _check(lib().vrb_host_register(self._h, _P(ptr), nbytes))
+
+    def host_unregister(self, ptr):
+        _check(lib().vrb_host_unregister(self._h, _P(ptr)))
 
     @property
     def stream(self):
@@ -349,6 +359,10 @@ class Renderer:
 
     def read_frame_wait(self):
         _check(lib().vrb_renderer_read_frame_wait(self._h))
+
+    def read_tiles_async(self, host_frame_ptr, host_flag_ptr, flag_value):
+        """This rank's partition tiles of the current frame -> a row-major host frame mapped by every rank (multigpu.SharedHostFrame)."""
+        _check(lib().vrb_renderer_read_tiles_async(self._h, _P(host_frame_ptr), _P(host_flag_ptr) if host_flag_ptr else None, flag_value))
 
     def counters(self):
         s, ms = C.c_uint64(), C.c_double()

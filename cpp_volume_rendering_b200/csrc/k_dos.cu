@@ -198,6 +198,8 @@ struct ExtCoefPyramid {
   int lw[DOS_MAX_LEVELS], lh[DOS_MAX_LEVELS], ld[DOS_MAX_LEVELS];
   cudaArray_t arr[DOS_MAX_LEVELS] = {};
   cudaTextureObject_t tex[DOS_MAX_LEVELS] = {};
+  cudaArray_t arr_hw[DOS_MAX_LEVELS] = {};       // the same R16F texels as plain arrays behind the texture unit's own trilinear filter
+  cudaTextureObject_t tex_hw[DOS_MAX_LEVELS] = {};
   unsigned short* tau16[DOS_MAX_LEVELS] = {};   // linear binary16 copies (test hook)
   uint64_t vol_gen = 0, tf_gen = 0;
   int res[3] = {0, 0, 0}; float sigma0 = 0.f;
@@ -206,6 +208,9 @@ struct ExtCoefPyramid {
     for (int l = 0; l < DOS_MAX_LEVELS; l++) {
       if (tex[l]) cudaDestroyTextureObject(tex[l]);
       if (arr[l]) cudaFreeArray(arr[l]);
+      if (tex_hw[l]) cudaDestroyTextureObject(tex_hw[l]);
+      if (arr_hw[l]) cudaFreeArray(arr_hw[l]);
+      tex_hw[l] = 0; arr_hw[l] = nullptr;
       if (tau16[l]) cudaFree(tau16[l]);
       tex[l] = 0; arr[l] = nullptr; tau16[l] = nullptr;
     }
@@ -291,6 +296,22 @@ int ExtCoefPyramid::ensure(vrb_ctx* ctx, const int want_res[3], float s0) {
       cudaDestroySurfaceObject(dst);
       VRB_CUDA(e);
     }
+    {   // hardware-filtered twins (GL_LINEAR / CLAMP_TO_EDGE on R16F, as the reference's own textureLod taps are filtered)
+      cudaChannelFormatDesc hd = cudaCreateChannelDescHalf();
+      cudaTextureDesc th{};
+      th.addressMode[0] = th.addressMode[1] = th.addressMode[2] = cudaAddressModeClamp;
+      th.filterMode = cudaFilterModeLinear; th.readMode = cudaReadModeElementType; th.normalizedCoords = 1;
+      for (int l = 0; l < nl; l++) {
+        VRB_CUDA(cudaMalloc3DArray(&arr_hw[l], &hd, make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]), 0));
+        cudaMemcpy3DParms cp{};
+        cp.srcPtr = make_cudaPitchedPtr(tau16[l], (size_t)lw[l] * sizeof(unsigned short), (size_t)lw[l], (size_t)lh[l]);
+        cp.dstArray = arr_hw[l]; cp.extent = make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]); cp.kind = cudaMemcpyDeviceToDevice;
+        VRB_CUDA(cudaMemcpy3DAsync(&cp, s));
+        cudaResourceDesc rh{}; rh.resType = cudaResourceTypeArray; rh.res.array.array = arr_hw[l];
+        VRB_CUDA(cudaCreateTextureObject(&tex_hw[l], &rh, &th, nullptr));
+      }
+      VRB_CUDA(cudaStreamSynchronize(s));
+    }
     cudaEventElapsedTime(&build_ms, e0, e1);
     return VRB_OK;
   };
@@ -318,6 +339,7 @@ struct DosShader {
   static constexpr int PHONG_KIND = 0;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   struct Args {
     cudaTextureObject_t mip[DOS_MAX_LEVELS]; float mip_res[DOS_MAX_LEVELS][3]; int n_levels;
+    cudaTextureObject_t mip_hw[DOS_MAX_LEVELS]; int hw_filter;
     DosCone occ, sdw;
     int type_of_shadow; float spot_cos;
     float light_fwd[3], light_up[3], light_right[3];
@@ -335,6 +357,7 @@ struct DosShader {
                __fsub_rn(__fmul_rn(a.x, b.y), __fmul_rn(b.x, a.y)));
   }
   static __device__ __forceinline__ float level_sample(const Args& s, int l, f3 p) {
+    if (s.hw_filter) return tex3D<float>(s.mip_hw[l], p.x, p.y, p.z);
     return tex3d_f32_exact(s.mip[l], p, mk3(s.mip_res[l][0], s.mip_res[l][1], s.mip_res[l][2]));
   }
   // textureLod on the pyramid (min LINEAR_MIPMAP_LINEAR, mag LINEAR)
@@ -471,6 +494,7 @@ class DosRenderer : public RendererImpl {
     prm_.count_samples = 0;
     prm_.use_light_cache = 0;                                                                   // :63-64
     prm_.light_cache_resolution[0] = prm_.light_cache_resolution[1] = prm_.light_cache_resolution[2] = 32;
+    prm_.exact_cone_filter = 0;
   }
   ~DosRenderer() override { clean(); }
   LightCache* light_cache() override { return &cache_; }
@@ -556,7 +580,8 @@ class DosRenderer : public RendererImpl {
     if (prm_.count_samples == 2) a.count_mode = 2;   // shaded samples (each evaluates every section of its cones: counts x rays fetches)
     DosShader::Args s{};
     s.n_levels = pyr_.n_levels;
-    for (int l = 0; l < pyr_.n_levels; l++) { s.mip[l] = pyr_.tex[l]; s.mip_res[l][0] = (float)pyr_.lw[l]; s.mip_res[l][1] = (float)pyr_.lh[l]; s.mip_res[l][2] = (float)pyr_.ld[l]; }
+    for (int l = 0; l < pyr_.n_levels; l++) { s.mip[l] = pyr_.tex[l]; s.mip_hw[l] = pyr_.tex_hw[l]; s.mip_res[l][0] = (float)pyr_.lw[l]; s.mip_res[l][1] = (float)pyr_.lh[l]; s.mip_res[l][2] = (float)pyr_.ld[l]; }
+    s.hw_filter = (prm_.exact_cone_filter == 0 && !prm_.use_light_cache) ? 1 : 0;
     auto fill = [](DosCone& c, const ConeTable& t, const float* dev, float initial_step, float uiw) {
       c.sections = (const float4*)dev;
       for (int i = 0; i < 3; i++) c.counts[i] = t.counts[i];

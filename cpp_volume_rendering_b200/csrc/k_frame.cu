@@ -43,6 +43,64 @@ int frame_to_rgba32f(cudaStream_t s, const __half* frame, int64_t n, float* dev_
   return VRB_OK;
 }
 
+// Multi-GPU read-back without a gather (vrb_renderer_read_tiles_async): a rank's partition tiles (tile ids rank, rank + n, ...)
+// are packed tile-major into a staging buffer on the render stream, then stored from there into a row-major host frame that is
+// mapped into the device's address space (every rank of the job writes its own tiles of the same host frame over its own PCIe
+// link).  One CTA per tile; a thread moves 16 bytes (two RGBA16F pixels), so a tile row is one 128-byte (16-wide) or longer run.
+__global__ void __launch_bounds__(128) pack_tiles_kernel(const uint4* __restrict__ frame, uint4* __restrict__ staging, int w, int h, int tile,
+                                                         int tiles_x, int rank, int n_ranks) {
+  const int tile_id = rank + blockIdx.x * n_ranks;
+  const int x0 = (tile_id % tiles_x) * tile, y0 = (tile_id / tiles_x) * tile;
+  const int half = tile / 2;                                   // uint4 = 2 pixels; w is even or the last pixel is handled below
+  uint4* dst = staging + (size_t)blockIdx.x * tile * half;
+  for (int i = threadIdx.x; i < tile * half; i += blockDim.x) {
+    const int ty = i / half, tx = (i % half) * 2;
+    const int x = x0 + tx, y = y0 + ty;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    const uint2* f2 = reinterpret_cast<const uint2*>(frame);
+    if (y < h && x + 1 < w && !(w & 1)) v = frame[((size_t)y * w + x) / 2];      // even width: the pixel pair is 16-byte aligned
+    else if (y < h) {
+      if (x < w) { const uint2 t = f2[(size_t)y * w + x]; v.x = t.x; v.y = t.y; }
+      if (x + 1 < w) { const uint2 t = f2[(size_t)y * w + x + 1]; v.z = t.x; v.w = t.y; }
+    }
+    dst[i] = v;
+  }
+}
+__global__ void __launch_bounds__(128) store_tiles_kernel(const uint4* __restrict__ staging, uint4* __restrict__ host_frame, int w, int h, int tile,
+                                                          int tiles_x, int rank, int n_ranks) {
+  const int tile_id = rank + blockIdx.x * n_ranks;
+  const int x0 = (tile_id % tiles_x) * tile, y0 = (tile_id / tiles_x) * tile;
+  const int half = tile / 2;
+  const uint4* src = staging + (size_t)blockIdx.x * tile * half;
+  for (int i = threadIdx.x; i < tile * half; i += blockDim.x) {
+    const int ty = i / half, tx = (i % half) * 2;
+    const int x = x0 + tx, y = y0 + ty;
+    const uint4 v = src[i];
+    uint2* h2 = reinterpret_cast<uint2*>(host_frame);
+    if (y < h && x + 1 < w && !(w & 1)) host_frame[((size_t)y * w + x) / 2] = v;
+    else if (y < h) {
+      if (x < w) h2[(size_t)y * w + x] = make_uint2(v.x, v.y);
+      if (x + 1 < w) h2[(size_t)y * w + x + 1] = make_uint2(v.z, v.w);
+    }
+  }
+}
+__global__ void host_flag_kernel(volatile unsigned* flag, unsigned value) {
+  __threadfence_system();
+  *flag = value;
+}
+int frame_pack_tiles(cudaStream_t s, const __half* frame, void* staging, int w, int h, int tile, int rank, int n_ranks, int my_tiles) {
+  if (my_tiles > 0) pack_tiles_kernel<<<my_tiles, 128, 0, s>>>((const uint4*)frame, (uint4*)staging, w, h, tile, (w + tile - 1) / tile, rank, n_ranks);
+  VRB_CUDA(cudaGetLastError());
+  return VRB_OK;
+}
+int frame_store_tiles(cudaStream_t s, const void* staging, void* mapped_frame, unsigned* mapped_flag, unsigned value, int w, int h, int tile, int rank,
+                      int n_ranks, int my_tiles) {
+  if (my_tiles > 0) store_tiles_kernel<<<my_tiles, 128, 0, s>>>((const uint4*)staging, (uint4*)mapped_frame, w, h, tile, (w + tile - 1) / tile, rank, n_ranks);
+  if (mapped_flag) host_flag_kernel<<<1, 1, 0, s>>>(mapped_flag, value);
+  VRB_CUDA(cudaGetLastError());
+  return VRB_OK;
+}
+
 // P_tex: trilinear R16F tex3D fetches per second with a working set that stays in L1TEX.  Each warp
 // marches 8x4 neighbouring rays through a 32^3 half volume at a 0.5-texel step — the access pattern
 // of the renderer with every miss removed.  4 independent fetch chains per thread hide latency.

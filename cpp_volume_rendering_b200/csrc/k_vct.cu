@@ -96,6 +96,8 @@ struct VctPyramid {
   int lw[VCT_MAX_LEVELS], lh[VCT_MAX_LEVELS], ld[VCT_MAX_LEVELS];
   cudaArray_t arr[VCT_MAX_LEVELS] = {};
   cudaTextureObject_t tex[VCT_MAX_LEVELS] = {};
+  cudaArray_t arr_hw[VCT_MAX_LEVELS] = {};      // the same RG16F texels as plain arrays behind the texture unit's own trilinear filter
+  cudaTextureObject_t tex_hw[VCT_MAX_LEVELS] = {};
   __half2* lin[VCT_MAX_LEVELS] = {};          // linear RG16F copies (test hook)
   float* lut = nullptr; int lut_w = 0, lut_h = 0;
   double max_std = 0.0; double vol_max_density = 0.0;
@@ -121,7 +123,9 @@ struct VctPyramid {
       if (tex[l]) cudaDestroyTextureObject(tex[l]);
       if (arr[l]) cudaFreeArray(arr[l]);
       if (lin[l]) cudaFree(lin[l]);
-      tex[l] = 0; arr[l] = nullptr; lin[l] = nullptr;
+      if (tex_hw[l]) cudaDestroyTextureObject(tex_hw[l]);
+      if (arr_hw[l]) cudaFreeArray(arr_hw[l]);
+      tex[l] = 0; arr[l] = nullptr; lin[l] = nullptr; tex_hw[l] = 0; arr_hw[l] = nullptr;
     }
     n_levels = 0; vol_gen = 0; lb = 0; region_ready = false;
     if (region_means) cudaFree(region_means);
@@ -189,6 +193,19 @@ int VctPyramid::build_quads(vrb_ctx* ctx, int l0, int l1) {
     }
     cudaDestroySurfaceObject(dst);
     VRB_CUDA(e);
+    // hardware-filtered twin: GL_LINEAR / CLAMP_TO_EDGE on RG16F in texel coordinates (so that a region pyramid's offset applies)
+    cudaChannelFormatDesc hd = cudaCreateChannelDescHalf2();
+    cudaTextureDesc th{};
+    th.addressMode[0] = th.addressMode[1] = th.addressMode[2] = cudaAddressModeClamp;
+    th.filterMode = cudaFilterModeLinear; th.readMode = cudaReadModeElementType; th.normalizedCoords = 0;
+    VRB_CUDA(cudaMalloc3DArray(&arr_hw[l], &hd, make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]), 0));
+    cudaMemcpy3DParms cp{};
+    cp.srcPtr = make_cudaPitchedPtr(lin[l], (size_t)lw[l] * sizeof(__half2), (size_t)lw[l], (size_t)lh[l]);
+    cp.dstArray = arr_hw[l]; cp.extent = make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]); cp.kind = cudaMemcpyDeviceToDevice;
+    VRB_CUDA(cudaMemcpy3DAsync(&cp, s));
+    cudaResourceDesc rh{}; rh.resType = cudaResourceTypeArray; rh.res.array.array = arr_hw[l];
+    VRB_CUDA(cudaCreateTextureObject(&tex_hw[l], &rh, &th, nullptr));
+    VRB_CUDA(cudaStreamSynchronize(s));
   }
   return VRB_OK;
 }
@@ -440,6 +457,7 @@ struct VctShader {
   static constexpr int PHONG_KIND = 1;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   struct Args {
     cudaTextureObject_t mip[VCT_MAX_LEVELS];
+    cudaTextureObject_t mip_hw[VCT_MAX_LEVELS]; int hw_filter;
     float mip_res[VCT_MAX_LEVELS][3];          // dims of the whole level
     float mip_off[VCT_MAX_LEVELS][3];          // texel origin of the stored array inside the level (region pyramids; else 0)
     int n_levels;
@@ -466,6 +484,7 @@ struct VctShader {
   // texture(sampler3D RG16F, p) on one level: GL_LINEAR / CLAMP_TO_EDGE, float32 weights (oracle sample_level)
   static __device__ __forceinline__ float2 sample_level(const Args& s, int l, f3 p) {
     const f3 res = mk3(s.mip_res[l][0], s.mip_res[l][1], s.mip_res[l][2]);
+    if (s.hw_filter == 1 || (s.hw_filter == 2 && l > 0)) return tex3D<float2>(s.mip_hw[l], p.x * res.x - s.mip_off[l][0], p.y * res.y - s.mip_off[l][1], p.z * res.z - s.mip_off[l][2]);
     const float X = __fsub_rn(__fmul_rn(p.x, res.x), 0.5f), Y = __fsub_rn(__fmul_rn(p.y, res.y), 0.5f), Z = __fsub_rn(__fmul_rn(p.z, res.z), 0.5f);
     float fx = floorf(X), fy = floorf(Y), fz = floorf(Z);
     const float ax = fx < 0.0f ? 0.0f : __fsub_rn(X, fx), ay = fy < 0.0f ? 0.0f : __fsub_rn(Y, fy), az = __fsub_rn(Z, fz);
@@ -574,6 +593,7 @@ class VctRenderer : public RendererImpl {
     prm_.cone_number_of_samples = 50; prm_.count_samples = 0;
     prm_.use_light_cache = 0;                                                                  // :47-48
     prm_.light_cache_resolution[0] = prm_.light_cache_resolution[1] = prm_.light_cache_resolution[2] = 32;
+    prm_.exact_cone_filter = 2;
   }
   LightCache* light_cache() override { return &cache_; }
   int init(int w, int h) override {
@@ -687,7 +707,7 @@ class VctRenderer : public RendererImpl {
     VctShader::Args s{};
     s.n_levels = pyr_.n_levels;
     for (int l = 0; l < pyr_.n_levels; l++) {
-      s.mip[l] = pyr_.tex[l]; s.mip_res[l][0] = (float)pyr_.flw[l]; s.mip_res[l][1] = (float)pyr_.flh[l]; s.mip_res[l][2] = (float)pyr_.fld[l];
+      s.mip[l] = pyr_.tex[l]; s.mip_hw[l] = pyr_.tex_hw[l]; s.mip_res[l][0] = (float)pyr_.flw[l]; s.mip_res[l][1] = (float)pyr_.flh[l]; s.mip_res[l][2] = (float)pyr_.fld[l];
       for (int i = 0; i < 3; i++) s.mip_off[l][i] = (float)pyr_.loff[l][i];
     }
     s.lut = pyr_.lut; s.lut_w = pyr_.lut_w; s.lut_h = pyr_.lut_h;
@@ -696,6 +716,7 @@ class VctRenderer : public RendererImpl {
     s.corr_fact = (float)prm_.apply_correction_factor * prm_.opacity_correction_factor;
     s.vol_max_density = (float)pyr_.vol_max_density; s.vol_max_std = (float)pyr_.max_std;
     s.cone_samples = prm_.cone_number_of_samples;
+    s.hw_filter = prm_.use_light_cache ? 0 : (prm_.exact_cone_filter == 0 ? 1 : (prm_.exact_cone_filter == 2 ? 2 : 0));
     if (brick_ranks > 0) {
       VRB_REQUIRE(!prm_.use_light_cache, VRB_ERR_UNSUPPORTED, "sort-last bricks and the light-cache mode do not combine");
       return redraw_sort_last<VctShader>(*this, a, s, prm_.count_samples != 0);

@@ -264,6 +264,9 @@ int finish_volume_upload(vrb_ctx* ctx);
 // k_frame.cu
 int frame_to_rgb8_over_white(cudaStream_t s, const __half* frame, int64_t n_pixels, uint8_t* dev_out);
 int frame_to_rgba32f(cudaStream_t s, const __half* frame, int64_t n_pixels, float* dev_out);
+int frame_pack_tiles(cudaStream_t s, const __half* frame, void* staging, int w, int h, int tile, int rank, int n_ranks, int my_tiles);
+int frame_store_tiles(cudaStream_t s, const void* staging, void* mapped_frame, unsigned* mapped_flag, unsigned value, int w, int h, int tile, int rank,
+                      int n_ranks, int my_tiles);
 // k_multiscale.cu: mode 1 multisample, 2 downscale, 3 upscale (filters `src` in place for kernels 4 and 5); kernel 0..5
 int frame_multiscale(cudaStream_t s, int mode, int kernel, __half* src, int sw, int sh, __half* dst, int tw, int th);
 

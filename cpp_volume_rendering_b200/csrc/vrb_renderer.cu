@@ -450,6 +450,63 @@ int vrb_renderer_read_frame_async(vrb_renderer* r, void* host, int format) {
   return VRB_OK;
 }
 
+// Multi-GPU read-back without a gather: this rank's partition tiles go to a host frame every rank of the job has mapped.
+int vrb_renderer_read_tiles_async(vrb_renderer* r, void* host_frame, unsigned* host_flag, unsigned flag_value) {
+  VRB_REQUIRE(r && host_frame, VRB_ERR_INVALID, "vrb_renderer_read_tiles_async: null argument");
+  RendererImpl* p = r->impl;
+  VRB_REQUIRE(p->frame, VRB_ERR_INVALID, "vrb_renderer_read_tiles_async before Init");
+  VRB_REQUIRE(!p->show_filtered, VRB_ERR_UNSUPPORTED, "vrb_renderer_read_tiles_async: not with a multiscaling mode (the filter pass needs the whole generated frame)");
+  void* dev_frame = nullptr; void* dev_flag = nullptr;
+  cudaError_t e = cudaHostGetDevicePointer(&dev_frame, host_frame, 0);
+  if (e == cudaSuccess && host_flag) e = cudaHostGetDevicePointer(&dev_flag, host_flag, 0);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    set_error("vrb_renderer_read_tiles_async: the host frame / flag is not mapped into the device's address space (vrb_host_register): %s", cudaGetErrorString(e));
+    return VRB_ERR_INVALID;
+  }
+  const int tile = p->part_tile, tiles_x = (p->width + tile - 1) / tile, n_tiles = tiles_x * ((p->height + tile - 1) / tile);
+  const int my_tiles = (n_tiles - p->rank + p->n_ranks - 1) / p->n_ranks;
+  const size_t bytes = std::max<size_t>((size_t)std::max(my_tiles, 0) * tile * tile * 8, 16);
+  cudaStream_t s = p->ctx->stream;
+  if (!p->copy_stream) {
+    VRB_CUDA(cudaStreamCreateWithFlags(&p->copy_stream, cudaStreamNonBlocking));
+    VRB_CUDA(cudaEventCreateWithFlags(&p->ev_staged, cudaEventDisableTiming));
+    for (int i = 0; i < 2; i++) VRB_CUDA(cudaEventCreateWithFlags(&p->ev_copied[i], cudaEventDisableTiming));
+  }
+  const int i = p->rd_staging_idx ^= 1;
+  if (p->rd_staging_cap[i] < bytes) {
+    VRB_CUDA(cudaStreamSynchronize(p->copy_stream));
+    if (p->rd_staging[i]) cudaFree(p->rd_staging[i]);
+    p->rd_staging[i] = nullptr; p->rd_staging_cap[i] = 0;
+    VRB_CUDA(cudaMalloc(&p->rd_staging[i], bytes));
+    p->rd_staging_cap[i] = bytes;
+  }
+  VRB_CUDA(cudaStreamWaitEvent(s, p->ev_copied[i], 0));        // the stores that last read this staging buffer
+  int rc = frame_pack_tiles(s, p->frame, p->rd_staging[i], p->width, p->height, tile, p->rank, p->n_ranks, my_tiles);
+  if (rc != VRB_OK) return rc;
+  VRB_CUDA(cudaEventRecord(p->ev_staged, s));
+  VRB_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_staged, 0));
+  rc = frame_store_tiles(p->copy_stream, p->rd_staging[i], dev_frame, (unsigned*)dev_flag, flag_value, p->width, p->height, tile, p->rank, p->n_ranks, my_tiles);
+  if (rc != VRB_OK) return rc;
+  VRB_CUDA(cudaEventRecord(p->ev_copied[i], p->copy_stream));
+  return VRB_OK;
+}
+
+// cudaHostRegister(Mapped | Portable) of a host range some other owner allocated (a POSIX shared-memory segment every rank of a job
+// maps), so that kernels of this process can store into it.
+int vrb_host_register(vrb_ctx* ctx, void* host, size_t bytes) {
+  VRB_REQUIRE(ctx && host && bytes, VRB_ERR_INVALID, "vrb_host_register: null argument");
+  VRB_CUDA(cudaSetDevice(ctx->device));
+  VRB_CUDA(cudaHostRegister(host, bytes, cudaHostRegisterMapped | cudaHostRegisterPortable));
+  return VRB_OK;
+}
+int vrb_host_unregister(vrb_ctx* ctx, void* host) {
+  VRB_REQUIRE(ctx && host, VRB_ERR_INVALID, "vrb_host_unregister: null argument");
+  VRB_CUDA(cudaSetDevice(ctx->device));
+  VRB_CUDA(cudaHostUnregister(host));
+  return VRB_OK;
+}
+
 int vrb_renderer_read_frame_wait(vrb_renderer* r) {
   VRB_REQUIRE(r, VRB_ERR_INVALID, "vrb_renderer_read_frame_wait: null renderer");
   if (r->impl->copy_stream) VRB_CUDA(cudaStreamSynchronize(r->impl->copy_stream));

@@ -262,6 +262,7 @@ bool CudaRC1PConeTracingDirOcclusionShading::Update(vis::Camera* camera) {
   p.sdw_cone_half_angle = sdw_cone_half_angle; p.sdw_initial_step = sdw_initial_step; p.sdw_covered_distance = sdw_covered_distance;
   p.sdw_ui_weight = sdw_ui_weight; p.sdw_max_packing = sdw_max_packing;
   p.base_level_sigma0 = base_level_sigma0; p.use_custom_resolution = use_custom_resolution ? 1 : 0;
+  p.exact_cone_filter = exact_cone_filter ? 1 : 0;
   for (int i = 0; i < 3; i++) p.custom_resolution[i] = custom_resolution[i];
   p.use_light_cache = m_pre_illum_str_vol.IsActive() ? 1 : 0;
   for (int i = 0; i < 3; i++) p.light_cache_resolution[i] = m_pre_illum_str_vol.GetLightCacheResolution()[i];

@@ -133,6 +133,7 @@ class CudaRC1PConeTracingDirOcclusionShading : public BaseVolumeRenderer {
   float occ_cone_half_angle, occ_initial_step, occ_covered_distance, occ_ui_weight;   int occ_max_packing;
   float sdw_cone_half_angle, sdw_initial_step, sdw_covered_distance, sdw_ui_weight;   int sdw_max_packing;
   float base_level_sigma0;
+  bool exact_cone_filter = false;      // new: float32 weights for the cones' textureLod taps instead of the texture unit's filter (vrb_dos_params)
   bool use_custom_resolution;
   int custom_resolution[3];
   PreIlluminationStructuredVolume m_pre_illum_str_vol;   // SetActive(false), 32^3 in the constructor

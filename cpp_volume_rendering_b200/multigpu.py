@@ -110,3 +110,91 @@ def frame_barrier(device=None, group=None):
     if device is not None:
         torch.cuda.synchronize(device)
     dist.barrier(group=group)
+
+
+class SharedHostFrame:
+    """One row-major RGBA16F host frame (+ one 32-bit arrival word per rank, each on its own 64-byte line) in a POSIX shared-memory
+    segment that every rank of the job maps and registers with its device (vrb_host_register): every rank stores its own partition
+    tiles into it over its own PCIe link (Renderer.read_tiles_async) and the consumer polls the arrival words.  `buffers` frames
+    alternate so that the stores of frame k + 1 never land in the frame the consumer is still reading.  Rank 0 creates the segment;
+    the others attach after `barrier()` (a callable, e.g. dist.barrier)."""
+    FLAG_STRIDE = 16          # uint32 words per rank
+
+    def __init__(self, ctx, name, width, height, rank, world, barrier=None, buffers=2):
+        import mmap
+        import os
+        import numpy as np
+        self.ctx, self.rank, self.world, self.buffers = ctx, rank, world, buffers
+        self.frame_bytes = width * height * 8
+        flags_bytes = 4 * self.FLAG_STRIDE * (world * buffers + 1)          # + the consumer's "released up to frame" word
+        total = ((self.frame_bytes * buffers + flags_bytes + 4095) // 4096) * 4096
+        # a plain file in /dev/shm mapped by every rank (multiprocessing.shared_memory would hand the name to Python's resource
+        # tracker, which unlinks it when the first attached process exits)
+        self.path = os.path.join("/dev/shm", name)
+        if rank == 0:
+            fd = os.open(self.path, os.O_CREAT | os.O_EXCL | os.O_RDWR, 0o600)
+            os.ftruncate(fd, total)
+        if barrier is not None:
+            barrier()
+        if rank != 0:
+            fd = os.open(self.path, os.O_RDWR)
+        self.map = mmap.mmap(fd, total)
+        os.close(fd)
+        self._arr = np.frombuffer(self.map, dtype=np.uint8, count=total)
+        self.base = self._arr.ctypes.data
+        self.total = total
+        ctx.host_register(self.base, total)
+        self.frames = [self._arr[b * self.frame_bytes:(b + 1) * self.frame_bytes].view(np.float16).reshape(height, width, 4) for b in range(buffers)]
+        off = self.frame_bytes * buffers
+        words = self._arr[off:off + flags_bytes].view(np.uint32)
+        self.flags = words[:world * buffers * self.FLAG_STRIDE].reshape(buffers, world, self.FLAG_STRIDE)
+        self.released = words[world * buffers * self.FLAG_STRIDE:]            # [0]: every frame <= this number may be overwritten
+        if barrier is not None:
+            barrier()
+
+    def frame_ptr(self, b):
+        return self.base + b * self.frame_bytes
+
+    def flag_ptr(self, b, rank=None):
+        rank = self.rank if rank is None else rank
+        return self.base + self.frame_bytes * self.buffers + 4 * self.FLAG_STRIDE * (b * self.world + rank)
+
+    def submit(self, renderer, k, timeout_s=30.0):
+        """Order the stores of frame number k (1, 2, ...) of `renderer` into buffer k % buffers.  Back-pressure: waits (host) until the
+        consumer has released frame k - buffers, the last one that lived in that buffer."""
+        import time
+        b = k % self.buffers
+        t0 = time.perf_counter()
+        while int(self.released[0]) < k - self.buffers:
+            if time.perf_counter() - t0 > timeout_s:
+                raise TimeoutError(f"SharedHostFrame.submit({k}): consumer released only up to {int(self.released[0])}")
+        renderer.read_tiles_async(self.frame_ptr(b), self.flag_ptr(b), k)
+
+    def release(self, k):
+        """Consumer: frames up to k have been used; their buffers may be overwritten."""
+        self.released[0] = k
+
+    def wait(self, k, timeout_s=30.0):
+        """Block until every rank's tiles of frame k have landed; returns the frame (a view: valid until frame k + buffers is submitted)."""
+        import time
+        b = k % self.buffers
+        col = self.flags[b, :, 0]
+        t0 = time.perf_counter()
+        while int(col.min()) < k:
+            if time.perf_counter() - t0 > timeout_s:
+                raise TimeoutError(f"SharedHostFrame.wait({k}): arrival words {col.tolist()}")
+        return self.frames[b]
+
+    def close(self, barrier=None):
+        self.ctx.synchronize()
+        self.ctx.host_unregister(self.base)
+        self.frames = self.flags = self.released = self._arr = None
+        if barrier is not None:
+            barrier()
+        import os
+        try:
+            self.map.close()
+        except BufferError:           # a caller still holds a view of a frame: the mapping goes with the process
+            pass
+        if self.rank == 0:
+            os.unlink(self.path)

@@ -170,6 +170,12 @@ typedef struct {
   int   count_samples;              /* vrb_renderer_counters: 1 = march-loop iterations, 2 = shaded samples, 3 = cone steps inside the volume */
   int   use_light_cache;                   /* PreIlluminationStructuredVolume::IsActive(), false: object-space mode (see vrb_light_cache_read) */
   int   light_cache_resolution[3];         /* 32^3 (SetLightCacheResolution in the renderer's constructor) */
+  int   exact_cone_filter;                 /* new-build knob, as in vrb_dos_params: 0 = the cone's textureLod taps through the texture unit's
+                                              trilinear filter (1.8 fixed-point weights), 1 = float32 weights on every level, 2 (default) =
+                                              float32 weights on pyramid level 0 (the voxels themselves, where neighbouring texels differ
+                                              most) and the texture unit on the coarser levels.  Measured against the float32 oracle on the
+                                              parity cases: worst 1.56 / 0.13 / 0.25 of the 2/255 bar; 512^3 / 1024^2 frame 8.7 / 13.1 / 10.2 ms.
+                                              The light-cache pass always uses float32 weights. */
 } vrb_vct_params;
 
 /* Run-time parameters of SBTMDirectionalOcclusionShading: its ImGui-mutable members (sbtmdosrenderer.cpp:20-46).
@@ -216,6 +222,11 @@ typedef struct {
   int   count_samples;                       /* vrb_renderer_counters: 1 = march-loop iterations, 2 = shaded samples (each evaluates every section of its cones) */
   int   use_light_cache;                   /* PreIlluminationStructuredVolume::IsActive(), false: object-space mode (see vrb_light_cache_read) */
   int   light_cache_resolution[3];         /* 32^3 (SetLightCacheResolution in the renderer's constructor) */
+  int   exact_cone_filter;                 /* new-build knob.  0 (default): the textureLod taps of the cones go through the texture unit's own
+                                              trilinear filter (1.8 fixed-point weights, as the reference's GLSL taps on the same hardware);
+                                              1: float32 weights (the filter the GL specification writes down, and the oracle's).  Measured
+                                              against the float32 oracle: worst 0.44 / 0.13 of the 2/255 bar at 512^3 / 1024^2 (C3), frame
+                                              4.9 / 5.8 ms (11.9 / 15.7 ms with shadows).  The light-cache pass always uses float32 weights. */
 } vrb_dos_params;
 
 /* ---- library / context ------------------------------------------------------------------- */
@@ -308,6 +319,16 @@ int vrb_renderer_read_frame(vrb_renderer* r, void* host, int format);
  * the redraws issued so far and returns; the transfer runs on a second stream from a staging copy, so the next redraw may start
  * at once.  host (pinned memory for a transfer that overlaps) holds the frame after _wait, which waits for every _async so far. */
 int vrb_renderer_read_frame_async(vrb_renderer* r, void* host, int format);
+/* Multi-GPU read-back without a gather (no reference counterpart: the reference has one GPU and one glReadPixels).  With an image
+ * partition set (vrb_renderer_set_partition) every rank stores ITS OWN tiles of the current frame into one row-major RGBA16F host
+ * frame that all ranks of the job have mapped — e.g. a POSIX shared-memory segment, registered in every process with
+ * vrb_host_register — each over its own PCIe link, instead of one rank transferring the whole gathered frame.  Ordered after the
+ * redraws issued so far; the stores run on a second stream from a staging copy (the next redraw may start at once).  When they
+ * are done the 32-bit word *host_flag (in registered memory too; may be NULL) is set to flag_value: the consumer polls one word
+ * per rank.  _read_frame_wait waits for this rank's stores.  RGBA16F, generated frame only (no multiscaling mode). */
+int vrb_renderer_read_tiles_async(vrb_renderer* r, void* host_frame, unsigned* host_flag, unsigned flag_value);
+int vrb_host_register(vrb_ctx* ctx, void* host, size_t bytes);     /* cudaHostRegister, mapped + portable */
+int vrb_host_unregister(vrb_ctx* ctx, void* host);
 int vrb_renderer_read_frame_wait(vrb_renderer* r);
 /* samples: march-loop iterations of the last redraw (only if count_samples was set, else 0);
  * ms: device time of the last redraw measured with CUDA events on the context stream. */

@@ -169,7 +169,7 @@ def test_fork_renderers_through_the_plugin_classes(tmp_path, ctx, bonsai_table):
         r.init(w, h); r.update(cam, inputs.default_light(256)); r.redraw()
         direct = r.read_frame(_capi.VRB_FRAME_RGBA32F)
         r.close()
-        assert np.array_equal(rgba, direct), name
+        assert np.array_equal(rgba, direct, equal_nan=True), name      # the advanced renderer's frame holds NaN where a neighbour's normal has zero length
 
 
 def test_gbuffer_hook_is_deferred_only(ctx):

@@ -75,9 +75,13 @@ def test_vct_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, kw):
         for k, v in kw.items():
             setattr(prm, k, v)
         prm.count_samples = 1
-        r.set_params(prm)
-        r.update(cam, light); r.redraw()
-        got = r.read_frame(_capi.VRB_FRAME_RGBA32F); got8 = r.read_frame(_capi.VRB_FRAME_RGB8_OVER_WHITE)
+        frames = {}
+        for mode in (0, 2, 1):                     # cone taps: texture unit's filter / float32 on level 0 only / float32 everywhere
+            prm.exact_cone_filter = mode
+            r.set_params(prm)
+            r.update(cam, light); r.redraw()
+            frames[mode] = (r.read_frame(_capi.VRB_FRAME_RGBA32F), r.read_frame(_capi.VRB_FRAME_RGB8_OVER_WHITE))
+        got, got8 = frames[1]
         samples, _ = r.counters()
         lut, max_std, _, _ = r.read_vct_lut()
     finally:
@@ -102,6 +106,11 @@ def test_vct_image_parity(ctx, bonsai_table, n, dtype, size, eye_s, kw):
     s = metrics.ssim(got8, ref8)
     print(f"VCT {kw}: max|d| {d16:.3f}/255 rgb8 {d8:.0f} SSIM {s:.5f} samples {samples}/{total}")
     assert d16 <= 2.0 and d8 <= 2 and s >= 0.995
+    for mode in (0, 2):
+        g, g8 = frames[mode]
+        dm = float(np.abs(g - ref).max()) * 255.0; dm8 = metrics.max_abs_delta(g8, ref8); sm = metrics.ssim(g8, ref8)
+        print(f"    exact_cone_filter={mode}: max|d| {dm:.3f}/255 rgb8 {dm8:.0f} SSIM {sm:.5f}")
+        assert dm <= 2.0 and dm8 <= 2 and sm >= 0.995
     assert abs(samples - total) <= 2e-3 * total
     assert (ref[..., 3] > 0).mean() > 0.05
 

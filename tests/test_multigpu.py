@@ -335,3 +335,139 @@ def test_root_gather_sender_runs_ahead(ctx, bonsai_table, tile, size):
                 p.kill()
     for k in range(frames):
         assert np.array_equal(res[0][k], full[k]), f"frame {k} on rank 0 mixes redraws"
+
+
+# ---- read-back without a gather: every rank stores its own tiles into one shared host frame -------------------------------------
+class _FakeCtx:
+    """Host logic only (CPU test): registration is a no-op."""
+    def host_register(self, ptr, nbytes): pass
+    def host_unregister(self, ptr): pass
+    def synchronize(self): pass
+
+
+class _FakeRenderer:
+    """Stands in for Renderer.read_tiles_async: writes this rank's tiles of a frame whose every pixel holds the frame number."""
+    def __init__(self, shf, owner, rank):
+        self.shf, self.mine, self.rank = shf, owner == rank, rank
+    def read_tiles_async(self, frame_ptr, flag_ptr, k):
+        b = (frame_ptr - self.shf.base) // self.shf.frame_bytes
+        self.shf.frames[b][self.mine] = np.float16(k)
+        self.shf.flags[b, self.rank, 0] = k
+
+
+def _shf_cpu_worker(rank, world, port, name, frames, q):
+    sys.path.insert(0, ROOT)
+    import time
+    import torch.distributed as dist
+    from cpp_volume_rendering_b200 import multigpu
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    w, h, tile = 70, 50, 16
+    shf = multigpu.SharedHostFrame(_FakeCtx(), name, w, h, rank, world, barrier=dist.barrier)
+    r = _FakeRenderer(shf, multigpu.tile_owner_map(w, h, tile, world), rank)
+    seen = []
+    for k in range(1, frames + 1):
+        shf.submit(r, k)                             # rank 1 runs ahead until the back-pressure stops it
+        if rank == 0:
+            time.sleep(0.02)
+            f = shf.wait(k)
+            seen.append((float(f.min()), float(f.max())))
+            shf.release(k)
+    dist.barrier()
+    shf.close(barrier=dist.barrier)
+    q.put((rank, seen))
+    dist.destroy_process_group()
+
+
+def test_shared_host_frame_protocol_world2():
+    """Arrival words, buffer alternation and the consumer's release word over two processes (gloo, no GPU): every frame rank 0 takes
+    holds exactly one frame number although rank 1 never waits for rank 0 except through the release word."""
+    import torch.multiprocessing as mp
+    mpc = mp.get_context("spawn")
+    q = mpc.Queue()
+    port = _free_port()
+    name = f"vrb200_test_{os.getpid()}_{port}"
+    frames = 9
+    procs = [mpc.Process(target=_shf_cpu_worker, args=(rk, 2, port, name, frames, q)) for rk in range(2)]
+    for p in procs:
+        p.start()
+    try:
+        res = dict(q.get(timeout=120) for _ in range(2))
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+    finally:
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+    assert res[0] == [(float(k), float(k)) for k in range(1, frames + 1)]
+    assert not os.path.exists("/dev/shm/" + name)
+
+
+def _shf_gpu_worker(rank, world, port, name, frames, tile, size, q):
+    sys.path.insert(0, ROOT)
+    import time
+    import torch.distributed as dist
+    from cpp_volume_rendering_b200 import _capi, inputs, multigpu
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    n, (w, h) = 48, size
+    vox = inputs.synth_volume(n, np.uint8)
+    table = inputs.tf_build_linear(inputs.bonsai_tf())
+    cams = _runahead_cams(n, w, h, frames)
+    out = []
+    with _capi.Context(0) as ctx:
+        ctx.upload_volume(vox); ctx.upload_tf(table)
+        r = _capi.Renderer(ctx, _capi.VRB_RC1PASS)
+        r.init(w, h)
+        r.set_partition(rank, world, tile)
+        shf = multigpu.SharedHostFrame(ctx, name, w, h, rank, world, barrier=dist.barrier)
+        for k in range(1, frames + 1):
+            r.update(cams[k - 1]); r.redraw()
+            shf.submit(r, k)
+            if rank == 0:
+                time.sleep(0.03)
+                out.append(np.array(shf.wait(k), dtype=np.float32))
+                shf.release(k)
+        r.read_frame_wait()
+        dist.barrier()
+        shf.close(barrier=dist.barrier)
+        r.close()
+    q.put((rank, out))
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tile,size", [(16, (96, 80)), (32, (77, 53))])
+def test_tiles_to_shared_host_frame_two_ranks(ctx, bonsai_table, tile, size):
+    """vrb_renderer_read_tiles_async: two ranks (sharing the test box's GPU) store their own tiles into one host frame in shared
+    memory; rank 0 takes every frame from there, bit-identical to the single-rank frame, odd width and ragged edge tiles included."""
+    import torch.multiprocessing as mp
+    from cpp_volume_rendering_b200 import _capi, inputs
+    n, (w, h), frames = 48, size, 5
+    ctx.upload_volume(inputs.synth_volume(n, np.uint8)); ctx.upload_tf(bonsai_table)
+    r = _capi.Renderer(ctx, _capi.VRB_RC1PASS); r.init(w, h)
+    full = []
+    for cam in _runahead_cams(n, w, h, frames):
+        r.update(cam); r.redraw(); full.append(r.read_frame(_capi.VRB_FRAME_RGBA32F))
+    # an unregistered host buffer is refused
+    plain = np.zeros((h, w, 4), np.float16)
+    with pytest.raises(_capi.VrbError):
+        r.read_tiles_async(plain.ctypes.data, 0, 1)
+    r.close()
+    mpc = mp.get_context("spawn")
+    q = mpc.Queue()
+    port = _free_port()
+    name = f"vrb200_test_{os.getpid()}_{port}"
+    procs = [mpc.Process(target=_shf_gpu_worker, args=(rk, 2, port, name, frames, tile, size, q)) for rk in range(2)]
+    for p in procs:
+        p.start()
+    try:
+        res = dict(q.get(timeout=150) for _ in range(2))
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+    finally:
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+    for k in range(frames):
+        assert np.array_equal(res[0][k], full[k]), f"frame {k}"

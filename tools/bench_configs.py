@@ -123,11 +123,14 @@ def measure(ctx, which, steps, warmup, tex_peak, hbm_peak):
             _, _, counts, _ = r.read_dos_sections(which_cone)
             per += int(counts[0]) * 1 + int(counts[1]) * 3 + int(counts[2]) * 7
         med, lo, hi = _frames(r, steps, warmup, flush)
+        prm.exact_cone_filter = 1; r.set_params(prm); r.update(cam, light)          # the same frame with float32-weight cone taps
+        med_exact, _, _ = _frames(r, steps, warmup, flush)
         r.close()
         fetches = samples + shaded * per
         out[key] = {"workload": f"dos_cone{'_shadow' if shadow else ''}_512c_u8_1024x1024_step0.5_pyramid128", "ms_per_frame": med, "ms_min_max": [lo, hi],
                     "fps": 1e3 / med, "samples_per_frame": samples, "shaded_samples_per_frame": shaded, "pyramid_fetches_per_shaded_sample": per,
                     "samples_per_s": samples / (med * 1e-3), "precompute_ms": {"ext_coef_pyramid_128c": build_ms},
+                    "cone_filter": "texture unit (default)", "ms_per_frame_exact_cone_filter": med_exact,
                     "roofline": _tex_block("shaded_march_kernel<DosShader>", fetches, med, tex_peak, key,
                                            "march samples + shaded samples x (sections x rays) trilinear pyramid fetches")}
 
@@ -143,11 +146,17 @@ def measure(ctx, which, steps, warmup, tex_peak, hbm_peak):
         steps_in = _count(r, _capi.VctParams, "count_samples", 3)
         _, _, _, build_ms = r.read_vct_lut()
         med, lo, hi = _frames(r, steps, warmup, flush)
+        by_filter = {}
+        default_filter = int(prm.exact_cone_filter)
+        for mode in (0, 1, 2):
+            prm.exact_cone_filter = mode; r.set_params(prm); r.update(cam, light)
+            by_filter[str(mode)] = _frames(r, steps, warmup, flush)[0]
         r.close()
         fetches = samples + 3 * steps_in
         out["vct"] = {"workload": "vct_512c_u8_1024x1024_step0.5", "ms_per_frame": med, "ms_min_max": [lo, hi], "fps": 1e3 / med,
                       "samples_per_frame": samples, "shaded_samples_per_frame": shaded, "cone_steps_per_frame": steps_in,
                       "samples_per_s": samples / (med * 1e-3), "precompute_ms": {"supervoxel_pyramid": build_ms},
+                      "exact_cone_filter": default_filter, "ms_per_frame_by_exact_cone_filter": by_filter,
                       "roofline": _tex_block("shaded_march_kernel<VctShader>", fetches, med, tex_peak, "vct",
                                              "march samples + cone steps x (2 trilinear RG16F pyramid + 1 bilinear table fetch)")}
 

@@ -150,7 +150,8 @@ def main():
         vox16 = inputs.synth_volume(n, np.uint16)
         ctx.upload_volume(vox16); ctx.upload_tf(table)
         for name, kind in (("iso_adapt", _capi.VRB_ISO_ADAPT), ("iso_skip_v1", _capi.VRB_ISO_SKIP_V1), ("iso_skip_v2", _capi.VRB_ISO_SKIP_V2),
-                           ("iso_forward", _capi.VRB_ISO_FORWARD), ("iso_deferred", _capi.VRB_ISO_DEFERRED)):
+                           ("iso_forward", _capi.VRB_ISO_FORWARD), ("iso_deferred", _capi.VRB_ISO_DEFERRED),
+                           ("iso_advanced_deferred", _capi.VRB_ISO_ADVANCED_DEFERRED)):
             r = _capi.Renderer(ctx, kind)
             r.init(w, h)
             prm = r.get_params(_capi.IsoParams()); prm.count_iterations = 1; r.set_params(prm)
