@@ -198,8 +198,8 @@ struct ExtCoefPyramid {
   int lw[DOS_MAX_LEVELS], lh[DOS_MAX_LEVELS], ld[DOS_MAX_LEVELS];
   cudaArray_t arr[DOS_MAX_LEVELS] = {};
   cudaTextureObject_t tex[DOS_MAX_LEVELS] = {};
-  cudaArray_t arr_hw[DOS_MAX_LEVELS] = {};       // the same R16F texels as plain arrays behind the texture unit's own trilinear filter
-  cudaTextureObject_t tex_hw[DOS_MAX_LEVELS] = {};
+  cudaMipmappedArray_t mip_hw = nullptr;         // the same R16F texels as one mipmapped array behind the texture unit's own filter:
+  cudaTextureObject_t tex_hw = 0;                // GL_LINEAR_MIPMAP_LINEAR / CLAMP_TO_EDGE, one tex3DLod per textureLod
   unsigned short* tau16[DOS_MAX_LEVELS] = {};   // linear binary16 copies (test hook)
   uint64_t vol_gen = 0, tf_gen = 0;
   int res[3] = {0, 0, 0}; float sigma0 = 0.f;
@@ -208,12 +208,13 @@ struct ExtCoefPyramid {
     for (int l = 0; l < DOS_MAX_LEVELS; l++) {
       if (tex[l]) cudaDestroyTextureObject(tex[l]);
       if (arr[l]) cudaFreeArray(arr[l]);
-      if (tex_hw[l]) cudaDestroyTextureObject(tex_hw[l]);
-      if (arr_hw[l]) cudaFreeArray(arr_hw[l]);
-      tex_hw[l] = 0; arr_hw[l] = nullptr;
+
       if (tau16[l]) cudaFree(tau16[l]);
       tex[l] = 0; arr[l] = nullptr; tau16[l] = nullptr;
     }
+    if (tex_hw) cudaDestroyTextureObject(tex_hw);
+    if (mip_hw) cudaFreeMipmappedArray(mip_hw);
+    tex_hw = 0; mip_hw = nullptr;
     n_levels = 0; vol_gen = tf_gen = 0;
   }
   int ensure(vrb_ctx* ctx, const int want_res[3], float s0);
@@ -296,20 +297,23 @@ int ExtCoefPyramid::ensure(vrb_ctx* ctx, const int want_res[3], float s0) {
       cudaDestroySurfaceObject(dst);
       VRB_CUDA(e);
     }
-    {   // hardware-filtered twins (GL_LINEAR / CLAMP_TO_EDGE on R16F, as the reference's own textureLod taps are filtered)
+    {   // hardware-filtered twin: the level sizes max(res >> l, 1) are exactly a mip chain's
       cudaChannelFormatDesc hd = cudaCreateChannelDescHalf();
-      cudaTextureDesc th{};
-      th.addressMode[0] = th.addressMode[1] = th.addressMode[2] = cudaAddressModeClamp;
-      th.filterMode = cudaFilterModeLinear; th.readMode = cudaReadModeElementType; th.normalizedCoords = 1;
+      VRB_CUDA(cudaMallocMipmappedArray(&mip_hw, &hd, make_cudaExtent((size_t)lw[0], (size_t)lh[0], (size_t)ld[0]), (unsigned)nl, 0));
       for (int l = 0; l < nl; l++) {
-        VRB_CUDA(cudaMalloc3DArray(&arr_hw[l], &hd, make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]), 0));
+        cudaArray_t lvl = nullptr;
+        VRB_CUDA(cudaGetMipmappedArrayLevel(&lvl, mip_hw, (unsigned)l));
         cudaMemcpy3DParms cp{};
         cp.srcPtr = make_cudaPitchedPtr(tau16[l], (size_t)lw[l] * sizeof(unsigned short), (size_t)lw[l], (size_t)lh[l]);
-        cp.dstArray = arr_hw[l]; cp.extent = make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]); cp.kind = cudaMemcpyDeviceToDevice;
+        cp.dstArray = lvl; cp.extent = make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]); cp.kind = cudaMemcpyDeviceToDevice;
         VRB_CUDA(cudaMemcpy3DAsync(&cp, s));
-        cudaResourceDesc rh{}; rh.resType = cudaResourceTypeArray; rh.res.array.array = arr_hw[l];
-        VRB_CUDA(cudaCreateTextureObject(&tex_hw[l], &rh, &th, nullptr));
       }
+      cudaTextureDesc th{};
+      th.addressMode[0] = th.addressMode[1] = th.addressMode[2] = cudaAddressModeClamp;
+      th.filterMode = cudaFilterModeLinear; th.mipmapFilterMode = cudaFilterModeLinear; th.readMode = cudaReadModeElementType; th.normalizedCoords = 1;
+      th.minMipmapLevelClamp = 0.0f; th.maxMipmapLevelClamp = (float)(nl - 1);
+      cudaResourceDesc rh{}; rh.resType = cudaResourceTypeMipmappedArray; rh.res.mipmap.mipmap = mip_hw;
+      VRB_CUDA(cudaCreateTextureObject(&tex_hw, &rh, &th, nullptr));
       VRB_CUDA(cudaStreamSynchronize(s));
     }
     cudaEventElapsedTime(&build_ms, e0, e1);
@@ -339,15 +343,16 @@ struct DosShader {
   static constexpr int PHONG_KIND = 0;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   struct Args {
     cudaTextureObject_t mip[DOS_MAX_LEVELS]; float mip_res[DOS_MAX_LEVELS][3]; int n_levels;
-    cudaTextureObject_t mip_hw[DOS_MAX_LEVELS]; int hw_filter;
+    cudaTextureObject_t mip_hw; int hw_filter;        // hw_filter: the whole pyramid as one mipmapped texture, one tex3DLod per tap
     DosCone occ, sdw;
     int type_of_shadow; float spot_cos;
     float light_fwd[3], light_up[3], light_right[3];
   };
-  struct Const { f3 sizes, eye; };
+  struct Const { f3 sizes, eye, inv_sizes; };
   static __device__ __forceinline__ void prepare_block(const MarchArgs&, const Args&) {}
   static __device__ __forceinline__ Const prepare(const MarchArgs& a, const Args&) {
-    Const c; c.sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]); c.eye = mk3(a.eye[0], a.eye[1], a.eye[2]); return c;
+    Const c; c.sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]); c.eye = mk3(a.eye[0], a.eye[1], a.eye[2]);
+    c.inv_sizes = mk3(1.0f / c.sizes.x, 1.0f / c.sizes.y, 1.0f / c.sizes.z); return c;
   }
   static __device__ __forceinline__ void shade_warp(const MarchArgs& a, const Args& s, const Const& c, bool need, f3 tx, f3 cd, float& Iocc, float& Isdw) {
     if (need) shade(a, s, c, tx, cd, Iocc, Isdw);
@@ -357,11 +362,11 @@ struct DosShader {
                __fsub_rn(__fmul_rn(a.x, b.y), __fmul_rn(b.x, a.y)));
   }
   static __device__ __forceinline__ float level_sample(const Args& s, int l, f3 p) {
-    if (s.hw_filter) return tex3D<float>(s.mip_hw[l], p.x, p.y, p.z);
     return tex3d_f32_exact(s.mip[l], p, mk3(s.mip_res[l][0], s.mip_res[l][1], s.mip_res[l][2]));
   }
   // textureLod on the pyramid (min LINEAR_MIPMAP_LINEAR, mag LINEAR)
   static __device__ __forceinline__ float texture_lod(const Args& s, f3 p, float lod) {
+    if (s.hw_filter) return tex3DLod<float>(s.mip_hw, p.x, p.y, p.z, lod);       // lod clamped to [0, q] by the texture object
     const int q = s.n_levels - 1;
     if (!(lod > 0.0f)) return level_sample(s, 0, p);
     if (lod >= (float)q) return level_sample(s, q, p);
@@ -373,7 +378,7 @@ struct DosShader {
   }
   // GetGaussianExtinction (ray_bbox_marching.comp:92-112), CONSIDER_BORDERS
   static __device__ __forceinline__ float gaussian_extinction(const Args& s, const Const& c, f3 pos, float mip) {
-    float rg = texture_lod(s, div3(pos, c.sizes), mip);
+    float rg = texture_lod(s, s.hw_filter ? mul3(pos, c.inv_sizes) : div3(pos, c.sizes), mip);
     if (pos.x < 0.0f || pos.x > c.sizes.x || pos.y < 0.0f || pos.y > c.sizes.y || pos.z < 0.0f || pos.z > c.sizes.z) {
       const float sg = exp2f(mip);
       const f3 cl = sub3(min3(max3(pos, mk3(0.f, 0.f, 0.f)), c.sizes), pos);
@@ -580,7 +585,8 @@ class DosRenderer : public RendererImpl {
     if (prm_.count_samples == 2) a.count_mode = 2;   // shaded samples (each evaluates every section of its cones: counts x rays fetches)
     DosShader::Args s{};
     s.n_levels = pyr_.n_levels;
-    for (int l = 0; l < pyr_.n_levels; l++) { s.mip[l] = pyr_.tex[l]; s.mip_hw[l] = pyr_.tex_hw[l]; s.mip_res[l][0] = (float)pyr_.lw[l]; s.mip_res[l][1] = (float)pyr_.lh[l]; s.mip_res[l][2] = (float)pyr_.ld[l]; }
+    for (int l = 0; l < pyr_.n_levels; l++) { s.mip[l] = pyr_.tex[l]; s.mip_res[l][0] = (float)pyr_.lw[l]; s.mip_res[l][1] = (float)pyr_.lh[l]; s.mip_res[l][2] = (float)pyr_.ld[l]; }
+    s.mip_hw = pyr_.tex_hw;
     s.hw_filter = (prm_.exact_cone_filter == 0 && !prm_.use_light_cache) ? 1 : 0;
     auto fill = [](DosCone& c, const ConeTable& t, const float* dev, float initial_step, float uiw) {
       c.sections = (const float4*)dev;

@@ -482,11 +482,34 @@ int vrb_renderer_read_tiles_async(vrb_renderer* r, void* host_frame, unsigned* h
     p->rd_staging_cap[i] = bytes;
   }
   VRB_CUDA(cudaStreamWaitEvent(s, p->ev_copied[i], 0));        // the stores that last read this staging buffer
-  int rc = frame_pack_tiles(s, p->frame, p->rd_staging[i], p->width, p->height, tile, p->rank, p->n_ranks, my_tiles);
-  if (rc != VRB_OK) return rc;
-  VRB_CUDA(cudaEventRecord(p->ev_staged, s));
-  VRB_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_staged, 0));
-  rc = frame_store_tiles(p->copy_stream, p->rd_staging[i], dev_frame, (unsigned*)dev_flag, flag_value, p->width, p->height, tile, p->rank, p->n_ranks, my_tiles);
+  int rc = VRB_OK;
+  // When the tiles of a rank form whole columns of the image (tiles per row divisible by the number of ranks, width a multiple of the
+  // tile) the rank's pixels are a regular 3-level pattern — tile-wide segments, n_ranks * tile apart, in every row — which the copy
+  // engines move by themselves: one strided -> compact device copy into the staging buffer on the render stream, one compact -> strided
+  // copy into the host frame on the second stream.  Otherwise two small kernels do the same through the mapped host pointer.
+  const bool columns = p->width % tile == 0 && tiles_x % p->n_ranks == 0 && my_tiles > 0;
+  if (columns) {
+    const size_t seg = (size_t)tile * 8, ncol = (size_t)(tiles_x / p->n_ranks), rows = (size_t)p->height;
+    cudaMemcpy3DParms a{};
+    a.srcPtr = make_cudaPitchedPtr((char*)p->frame + (size_t)p->rank * seg, seg * p->n_ranks, seg, ncol);
+    a.dstPtr = make_cudaPitchedPtr(p->rd_staging[i], seg, seg, ncol);
+    a.extent = make_cudaExtent(seg, ncol, rows); a.kind = cudaMemcpyDeviceToDevice;
+    VRB_CUDA(cudaMemcpy3DAsync(&a, s));
+    VRB_CUDA(cudaEventRecord(p->ev_staged, s));
+    VRB_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_staged, 0));
+    cudaMemcpy3DParms b{};
+    b.srcPtr = make_cudaPitchedPtr(p->rd_staging[i], seg, seg, ncol);
+    b.dstPtr = make_cudaPitchedPtr((char*)host_frame + (size_t)p->rank * seg, seg * p->n_ranks, seg, ncol);
+    b.extent = make_cudaExtent(seg, ncol, rows); b.kind = cudaMemcpyDeviceToHost;
+    VRB_CUDA(cudaMemcpy3DAsync(&b, p->copy_stream));
+    rc = frame_store_tiles(p->copy_stream, nullptr, nullptr, (unsigned*)dev_flag, flag_value, p->width, p->height, tile, p->rank, p->n_ranks, 0);   // the flag only
+  } else {
+    rc = frame_pack_tiles(s, p->frame, p->rd_staging[i], p->width, p->height, tile, p->rank, p->n_ranks, my_tiles);
+    if (rc != VRB_OK) return rc;
+    VRB_CUDA(cudaEventRecord(p->ev_staged, s));
+    VRB_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_staged, 0));
+    rc = frame_store_tiles(p->copy_stream, p->rd_staging[i], dev_frame, (unsigned*)dev_flag, flag_value, p->width, p->height, tile, p->rank, p->n_ranks, my_tiles);
+  }
   if (rc != VRB_OK) return rc;
   VRB_CUDA(cudaEventRecord(p->ev_copied[i], p->copy_stream));
   return VRB_OK;
