@@ -98,6 +98,8 @@ struct VctPyramid {
   cudaTextureObject_t tex[VCT_MAX_LEVELS] = {};
   cudaArray_t arr_hw[VCT_MAX_LEVELS] = {};      // the same RG16F texels as plain arrays behind the texture unit's own trilinear filter
   cudaTextureObject_t tex_hw[VCT_MAX_LEVELS] = {};
+  cudaMipmappedArray_t mip1 = nullptr;           // levels 1 .. n-1 of an unbricked pyramid as one mip chain: a tap whose two levels are both
+  cudaTextureObject_t tex_mip1 = 0;              // coarser than the voxels is one tex3DLod (exact_cone_filter 0 and 2)
   __half2* lin[VCT_MAX_LEVELS] = {};          // linear RG16F copies (test hook)
   float* lut = nullptr; int lut_w = 0, lut_h = 0;
   double max_std = 0.0; double vol_max_density = 0.0;
@@ -117,6 +119,7 @@ struct VctPyramid {
   int region_begin(vrb_ctx* ctx, double* dev_means, int dims[3], int* level, double* local_max);
   int region_finish(vrb_ctx* ctx, const double* dev_means, double global_max_std);
   int build_quads(vrb_ctx* ctx, int l0, int l1);
+  int build_mip1(vrb_ctx* ctx);
   void release_lut() { if (lut) cudaFree(lut); lut = nullptr; lut_w = lut_h = 0; tf_gen = 0; }
   void release() {
     for (int l = 0; l < VCT_MAX_LEVELS; l++) {
@@ -127,6 +130,9 @@ struct VctPyramid {
       if (arr_hw[l]) cudaFreeArray(arr_hw[l]);
       tex[l] = 0; arr[l] = nullptr; lin[l] = nullptr; tex_hw[l] = 0; arr_hw[l] = nullptr;
     }
+    if (tex_mip1) cudaDestroyTextureObject(tex_mip1);
+    if (mip1) cudaFreeMipmappedArray(mip1);
+    tex_mip1 = 0; mip1 = nullptr;
     n_levels = 0; vol_gen = 0; lb = 0; region_ready = false;
     if (region_means) cudaFree(region_means);
     region_means = nullptr;
@@ -207,6 +213,30 @@ int VctPyramid::build_quads(vrb_ctx* ctx, int l0, int l1) {
     VRB_CUDA(cudaCreateTextureObject(&tex_hw[l], &rh, &th, nullptr));
     VRB_CUDA(cudaStreamSynchronize(s));
   }
+  return VRB_OK;
+}
+
+// levels 1 .. n-1 (sizes floor(w / 2^l): a mip chain with level 1 as its base) as one mipmapped RG16F array
+int VctPyramid::build_mip1(vrb_ctx* ctx) {
+  if (n_levels < 2) return VRB_OK;
+  cudaStream_t s = ctx->stream;
+  cudaChannelFormatDesc hd = cudaCreateChannelDescHalf2();
+  VRB_CUDA(cudaMallocMipmappedArray(&mip1, &hd, make_cudaExtent((size_t)lw[1], (size_t)lh[1], (size_t)ld[1]), (unsigned)(n_levels - 1), 0));
+  for (int l = 1; l < n_levels; l++) {
+    cudaArray_t lvl = nullptr;
+    VRB_CUDA(cudaGetMipmappedArrayLevel(&lvl, mip1, (unsigned)(l - 1)));
+    cudaMemcpy3DParms cp{};
+    cp.srcPtr = make_cudaPitchedPtr(lin[l], (size_t)lw[l] * sizeof(__half2), (size_t)lw[l], (size_t)lh[l]);
+    cp.dstArray = lvl; cp.extent = make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]); cp.kind = cudaMemcpyDeviceToDevice;
+    VRB_CUDA(cudaMemcpy3DAsync(&cp, s));
+  }
+  cudaTextureDesc th{};
+  th.addressMode[0] = th.addressMode[1] = th.addressMode[2] = cudaAddressModeClamp;
+  th.filterMode = cudaFilterModeLinear; th.mipmapFilterMode = cudaFilterModeLinear; th.readMode = cudaReadModeElementType; th.normalizedCoords = 1;
+  th.minMipmapLevelClamp = 0.0f; th.maxMipmapLevelClamp = (float)(n_levels - 2);
+  cudaResourceDesc rh{}; rh.resType = cudaResourceTypeMipmappedArray; rh.res.mipmap.mipmap = mip1;
+  VRB_CUDA(cudaCreateTextureObject(&tex_mip1, &rh, &th, nullptr));
+  VRB_CUDA(cudaStreamSynchronize(s));
   return VRB_OK;
 }
 
@@ -420,6 +450,7 @@ int VctPyramid::ensure(vrb_ctx* ctx, bool with_lut) {
     if (rc != VRB_OK) { release(); return rc; }
     for (int l = 0; l < n_levels; l++) { flw[l] = lw[l]; flh[l] = lh[l]; fld[l] = ld[l]; loff[l][0] = loff[l][1] = loff[l][2] = 0; }
     rc = build_quads(ctx, 0, n_levels);
+    if (rc == VRB_OK) rc = build_mip1(ctx);
     if (rc != VRB_OK) { release(); return rc; }
     vol_gen = v.generation;
     release_lut();
@@ -458,6 +489,7 @@ struct VctShader {
   struct Args {
     cudaTextureObject_t mip[VCT_MAX_LEVELS];
     cudaTextureObject_t mip_hw[VCT_MAX_LEVELS]; int hw_filter;
+    cudaTextureObject_t mip1;                    // 0: none (region pyramids)
     float mip_res[VCT_MAX_LEVELS][3];          // dims of the whole level
     float mip_off[VCT_MAX_LEVELS][3];          // texel origin of the stored array inside the level (region pyramids; else 0)
     int n_levels;
@@ -503,6 +535,7 @@ struct VctShader {
   static __device__ __forceinline__ float2 texture_lod(const Args& s, f3 p, float lod) {
     const int q = s.n_levels - 1;
     if (!(lod > 0.0f)) return sample_level(s, 0, p);
+    if (s.hw_filter && s.mip1 && lod >= 1.0f) return tex3DLod<float2>(s.mip1, p.x, p.y, p.z, lod - 1.0f);   // both levels coarser than the voxels; lod clamped to q by the texture object
     if (lod >= (float)q) return sample_level(s, q, p);
     const float fl = floorf(lod); const int d1 = (int)fl; const float f = __fsub_rn(lod, fl);
     const float2 v1 = sample_level(s, d1, p), v2 = sample_level(s, d1 + 1, p);
@@ -716,6 +749,7 @@ class VctRenderer : public RendererImpl {
     s.corr_fact = (float)prm_.apply_correction_factor * prm_.opacity_correction_factor;
     s.vol_max_density = (float)pyr_.vol_max_density; s.vol_max_std = (float)pyr_.max_std;
     s.cone_samples = prm_.cone_number_of_samples;
+    s.mip1 = pyr_.tex_mip1;
     s.hw_filter = prm_.use_light_cache ? 0 : (prm_.exact_cone_filter == 0 ? 1 : (prm_.exact_cone_filter == 2 ? 2 : 0));
     if (brick_ranks > 0) {
       VRB_REQUIRE(!prm_.use_light_cache, VRB_ERR_UNSUPPORTED, "sort-last bricks and the light-cache mode do not combine");

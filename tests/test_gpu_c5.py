@@ -39,7 +39,7 @@ FULL, GRID, GHOST, SIZE = (128, 64, 64), (2, 1, 1), 24, (120, 90)
 CONE = dict(cone_number_of_samples=6)          # reach 13 voxels: the 24-voxel ghost holds it plus two level-2 texels
 
 
-def _bricked_worker(rank, world, port, bricked, q):
+def _bricked_worker(rank, world, port, bricked, cone_filter, q):
     sys.path.insert(0, ROOT)
     import torch
     import torch.distributed as dist
@@ -65,6 +65,7 @@ def _bricked_worker(rank, world, port, bricked, q):
         prm = r.get_params(_capi.VctParams())
         for k, v in CONE.items():
             setattr(prm, k, v)
+        prm.exact_cone_filter = cone_filter
         r.set_params(prm)
         if bricked:
             _, out["level"] = multigpu.setup_bricked_vct(r, rank, world, GRID)
@@ -86,12 +87,12 @@ def _bricked_worker(rank, world, port, bricked, q):
     dist.destroy_process_group()
 
 
-def _run_two(bricked):
+def _run_two(bricked, cone_filter=1):
     import torch.multiprocessing as mp
     mpc = mp.get_context("spawn")
     q = mpc.Queue()
     port = _free_port()
-    procs = [mpc.Process(target=_bricked_worker, args=(rk, 2, port, bricked, q)) for rk in range(2)]
+    procs = [mpc.Process(target=_bricked_worker, args=(rk, 2, port, bricked, cone_filter, q)) for rk in range(2)]
     for p in procs:
         p.start()
     try:
@@ -109,7 +110,10 @@ def _run_two(bricked):
 def test_bricked_vct_two_ranks_equals_replicated_and_unbricked(ctx, bonsai_table):
     """Two processes, each holding ONLY its brick + 24 ghost voxels of the volume (generated on the device per region) and of the
     supervoxel pyramid's fine levels; the coarse levels come from the exchanged level means.  The frame equals, bit for bit, the
-    sort-last frame of two ranks that each hold the whole volume, and the unpartitioned frame up to the blending order."""
+    sort-last frame of two ranks that each hold the whole volume, and the unpartitioned frame up to the blending order — with
+    float32-weight cone taps (exact_cone_filter 1).  With the default filter (float32 on level 0, the texture unit above) the coarse
+    taps of a region pyramid go through per-level textures in texel coordinates while an unbricked pyramid uses one mipmapped
+    texture: the same filter up to the hardware's fixed-point weights, compared within 1/255."""
     w, h = SIZE
     n = FULL[0]
     ctx.synth_volume(np.uint8, FULL); ctx.upload_tf(bonsai_table)
@@ -117,8 +121,11 @@ def test_bricked_vct_two_ranks_equals_replicated_and_unbricked(ctx, bonsai_table
     prm = r.get_params(_capi.VctParams())
     for k, v in CONE.items():
         setattr(prm, k, v)
+    assert prm.exact_cone_filter == 2
     r.set_params(prm)
     r.update(inputs.make_camera((1.1 * n, 0.9 * n, 1.7 * n), width=w, height=h), inputs.default_light(n)); r.redraw()
+    plain_default = r.read_frame(_capi.VRB_FRAME_RGBA32F)
+    prm.exact_cone_filter = 1; r.set_params(prm); r.redraw()
     plain = r.read_frame(_capi.VRB_FRAME_RGBA32F)
     _, max_std, n_levels, _ = r.read_vct_lut()
     r.close()
@@ -131,6 +138,10 @@ def test_bricked_vct_two_ranks_equals_replicated_and_unbricked(ctx, bonsai_table
         assert np.array_equal(bricked[rk]["frame"], replicated[rk]["frame"])
         assert np.array_equal(bricked[rk]["frame"], bricked[0]["frame"])
     assert np.abs(bricked[0]["frame"] - plain).max() <= 2.0 ** -9 and (plain[..., 3] > 0).mean() > 0.05
+    bricked_default = _run_two(True, cone_filter=2)
+    d = float(np.abs(bricked_default[0]["frame"] - plain_default).max()) * 255.0
+    print(f"bricked VCT, default cone filter, against the unbricked frame: max|d| {d:.3f}/255")
+    assert d <= 1.0 and np.array_equal(bricked_default[0]["frame"], bricked_default[1]["frame"])
 
 
 def test_region_volume_is_refused_where_it_cannot_be_rendered(ctx, bonsai_table):
