@@ -505,7 +505,7 @@ def main():
     ap.add_argument("--exact", type=int, default=1, help="float32 re-filtering of possibly-visible samples")
     ap.add_argument("--no-cpu", action="store_true", help="omit the cpu_baseline leg")
     ap.add_argument("--depth-split", type=int, default=-1, help="lanes per ray (0/1, 2, 4, 8); -1 = by the number of GPUs")
-    ap.add_argument("--gather", default="all", choices=["all", "root"], help="N > 1, device-timed leg: every rank collects the frame (all) or rank 0 only (root)")
+    ap.add_argument("--gather", default="root", choices=["all", "root"], help="N > 1, device-timed leg: every rank collects the frame (all) or rank 0 only (root)")
     ap.add_argument("--no-c5", action="store_true", help="omit extras.c5 (config 5 on the bricked 2048^3 volume) at N >= 2")
     ap.add_argument("--config", default="c2", choices=["c2", "c5"], help="c2: the headline (RayCasting1Pass, config 2); c5: config 5 alone")
     args = ap.parse_args()

@@ -120,6 +120,7 @@ struct VctPyramid {
   int region_finish(vrb_ctx* ctx, const double* dev_means, double global_max_std);
   int build_quads(vrb_ctx* ctx, int l0, int l1);
   int build_mip1(vrb_ctx* ctx);
+  int build_hw_level(vrb_ctx* ctx, int l);
   void release_lut() { if (lut) cudaFree(lut); lut = nullptr; lut_w = lut_h = 0; tf_gen = 0; }
   void release() {
     for (int l = 0; l < VCT_MAX_LEVELS; l++) {
@@ -199,20 +200,27 @@ int VctPyramid::build_quads(vrb_ctx* ctx, int l0, int l1) {
     }
     cudaDestroySurfaceObject(dst);
     VRB_CUDA(e);
-    // hardware-filtered twin: GL_LINEAR / CLAMP_TO_EDGE on RG16F in texel coordinates (so that a region pyramid's offset applies)
-    cudaChannelFormatDesc hd = cudaCreateChannelDescHalf2();
-    cudaTextureDesc th{};
-    th.addressMode[0] = th.addressMode[1] = th.addressMode[2] = cudaAddressModeClamp;
-    th.filterMode = cudaFilterModeLinear; th.readMode = cudaReadModeElementType; th.normalizedCoords = 0;
-    VRB_CUDA(cudaMalloc3DArray(&arr_hw[l], &hd, make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]), 0));
-    cudaMemcpy3DParms cp{};
-    cp.srcPtr = make_cudaPitchedPtr(lin[l], (size_t)lw[l] * sizeof(__half2), (size_t)lw[l], (size_t)lh[l]);
-    cp.dstArray = arr_hw[l]; cp.extent = make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]); cp.kind = cudaMemcpyDeviceToDevice;
-    VRB_CUDA(cudaMemcpy3DAsync(&cp, s));
-    cudaResourceDesc rh{}; rh.resType = cudaResourceTypeArray; rh.res.array.array = arr_hw[l];
-    VRB_CUDA(cudaCreateTextureObject(&tex_hw[l], &rh, &th, nullptr));
-    VRB_CUDA(cudaStreamSynchronize(s));
+    if (l > 0) { const int rc = build_hw_level(ctx, l); if (rc != VRB_OK) return rc; }   // level 0's twin (as large as the volume) only when asked for
   }
+  return VRB_OK;
+}
+
+// hardware-filtered twin of one level: GL_LINEAR / CLAMP_TO_EDGE on RG16F in texel coordinates (so that a region pyramid's offset applies)
+int VctPyramid::build_hw_level(vrb_ctx* ctx, int l) {
+  if (tex_hw[l]) return VRB_OK;
+  cudaStream_t s = ctx->stream;
+  cudaChannelFormatDesc hd = cudaCreateChannelDescHalf2();
+  cudaTextureDesc th{};
+  th.addressMode[0] = th.addressMode[1] = th.addressMode[2] = cudaAddressModeClamp;
+  th.filterMode = cudaFilterModeLinear; th.readMode = cudaReadModeElementType; th.normalizedCoords = 0;
+  VRB_CUDA(cudaMalloc3DArray(&arr_hw[l], &hd, make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]), 0));
+  cudaMemcpy3DParms cp{};
+  cp.srcPtr = make_cudaPitchedPtr(lin[l], (size_t)lw[l] * sizeof(__half2), (size_t)lw[l], (size_t)lh[l]);
+  cp.dstArray = arr_hw[l]; cp.extent = make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]); cp.kind = cudaMemcpyDeviceToDevice;
+  VRB_CUDA(cudaMemcpy3DAsync(&cp, s));
+  cudaResourceDesc rh{}; rh.resType = cudaResourceTypeArray; rh.res.array.array = arr_hw[l];
+  VRB_CUDA(cudaCreateTextureObject(&tex_hw[l], &rh, &th, nullptr));
+  VRB_CUDA(cudaStreamSynchronize(s));
   return VRB_OK;
 }
 
@@ -732,6 +740,7 @@ class VctRenderer : public RendererImpl {
     }
     if (rc == VRB_OK) rc = pyr_.ensure(ctx, true);
     if (rc != VRB_OK) return rc;
+    if (prm_.exact_cone_filter == 0 && !prm_.use_light_cache) { rc = pyr_.build_hw_level(ctx, 0); if (rc != VRB_OK) return rc; }
     MarchArgs a{};
     const bool phong = prm_.apply_gradient_shading != 0;   // ApplyPhongShading = m_apply_gradient_shading && GetCurrentGradientTexture() (vctrenderer.cpp:211)
     VRB_REQUIRE(!phong || (ctx->vol.tex_grad_pt && ctx->vol.grad_gen == ctx->vol.generation), VRB_ERR_INVALID, "RC1PVoxelConeTracingSGPU: gradient shading needs vrb_volume_gradient() for the current volume");
