@@ -33,8 +33,7 @@ struct SbtmArgs {
   unsigned long long* fragments;
 };
 
-constexpr int SBTM_THREADS = 512;      // few, large CTAs: the grid barrier between slices costs one atomic per CTA (128-thread CTAs: 19.5 ms per 512^3 / 1024^2 frame)
-constexpr int SBTM_RANGE_REGS = 4;     // a warp keeps the slice ranges of up to 32 * 4 of its tiles in registers
+constexpr int SBTM_THREADS = 128;
 
 __device__ __forceinline__ float occ_ld(const __half* p) { return __half2float(__ushort_as_half(__ldcg(reinterpret_cast<const unsigned short*>(p)))); }
 
@@ -53,7 +52,7 @@ __device__ __forceinline__ float occ_bilinear(const __half* occ, int W, int H, f
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(SBTM_THREADS, 2) sbtm_kernel(const __grid_constant__ SbtmArgs a) {
+__global__ void __launch_bounds__(SBTM_THREADS) sbtm_kernel(const __grid_constant__ SbtmArgs a) {
   cg::grid_group grid = cg::this_grid();
   extern __shared__ uint4 s_dyn[];
   uint4* s_tf = s_dyn;
@@ -87,15 +86,8 @@ __global__ void __launch_bounds__(SBTM_THREADS, 2) sbtm_kernel(const __grid_cons
                dot_rn(v, mk3(a.lookat[6], a.lookat[7], a.lookat[8])));
   };
 
-  // prologue: clear the targets (glClearTexImage, :197-201) and find, per owned tile, the slices that can touch the box.  The k-th tile
-  // of a warp (t = gw + k * n_warps) keeps its range in lane k % 32, register k / 32; warps with more tiles use the global array.
-  const int my_tiles = gw < n_tiles ? (n_tiles - gw + n_warps - 1) / n_warps : 0;
-  const bool in_regs = my_tiles <= 32 * SBTM_RANGE_REGS;
-  int rlo[SBTM_RANGE_REGS], rhi[SBTM_RANGE_REGS];
-#pragma unroll
-  for (int q = 0; q < SBTM_RANGE_REGS; q++) { rlo[q] = 0x7fffffff; rhi[q] = -1; }
-  int kt = 0;
-  for (int t = gw; t < n_tiles; t += n_warps, kt++) {
+  // prologue: clear the targets (glClearTexImage, :197-201) and find, per owned tile, the slices that can touch the box
+  for (int t = gw; t < n_tiles; t += n_warps) {
     const int px = (t % tiles_x) * 8 + lx, py = (t / tiles_x) * 4 + ly;
     int lo = 0x7fffffff, hi = -1;
     if (px < W && py < H) {
@@ -116,9 +108,6 @@ __global__ void __launch_bounds__(SBTM_THREADS, 2) sbtm_kernel(const __grid_cons
     }
     for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
     if (lane == 0) a.tile_range[t] = make_int2(lo, hi);
-#pragma unroll
-    for (int q = 0; q < SBTM_RANGE_REGS; q++)
-      if (q == (kt >> 5) && lane == (kt & 31)) { rlo[q] = lo; rhi[q] = hi; }
   }
   grid.sync();
 
@@ -130,25 +119,9 @@ __global__ void __launch_bounds__(SBTM_THREADS, 2) sbtm_kernel(const __grid_cons
     const float zs = __fadd_rn(a.base, pfn);
     const f3 C = add3(center0, scale3(fwd, pfn));
     const float cvx = __fdiv_rn(a.P00, zs), cvy = __fdiv_rn(a.P11, zs);            // Equation 12
-    // the tiles of this warp that slice i can touch: one ballot per range register instead of a range load per tile
-    static_assert(SBTM_RANGE_REGS == 4, "two 64-bit masks below");
-    unsigned long long m0 = (unsigned long long)__ballot_sync(0xffffffffu, i >= rlo[0] && i <= rhi[0]) |
-                            ((unsigned long long)__ballot_sync(0xffffffffu, i >= rlo[1] && i <= rhi[1]) << 32);
-    unsigned long long m1 = (unsigned long long)__ballot_sync(0xffffffffu, i >= rlo[2] && i <= rhi[2]) |
-                            ((unsigned long long)__ballot_sync(0xffffffffu, i >= rlo[3] && i <= rhi[3]) << 32);
-    int t_fallback = gw;
-    for (;;) {
-      int t;
-      if (in_regs) {
-        if (m0) { t = gw + (__ffsll((long long)m0) - 1) * n_warps; m0 &= m0 - 1; }
-        else if (m1) { t = gw + (64 + __ffsll((long long)m1) - 1) * n_warps; m1 &= m1 - 1; }
-        else break;
-      } else {
-        if (t_fallback >= n_tiles) break;
-        t = t_fallback; t_fallback += n_warps;
-        const int2 rg = a.tile_range[t];
-        if (i < rg.x || i > rg.y) continue;
-      }
+    for (int t = gw; t < n_tiles; t += n_warps) {
+      const int2 rg = a.tile_range[t];
+      if (i < rg.x || i > rg.y) continue;
       const int px = (t % tiles_x) * 8 + lx, py = (t / tiles_x) * 4 + ly;
       if (px >= W || py >= H) continue;
       float vx, vy;

@@ -37,7 +37,8 @@ def test_struct_sizes_match_header(tmp_path):
     import subprocess
     pairs = [("vrb_camera", _capi.Camera), ("vrb_light", _capi.Light), ("vrb_rc1pass_params", _capi.Rc1PassParams),
              ("vrb_iso_params", _capi.IsoParams), ("vrb_ebs_params", _capi.EbsParams), ("vrb_vct_params", _capi.VctParams),
-             ("vrb_sbtm_params", _capi.SbtmParams), ("vrb_dos_params", _capi.DosParams)]
+             ("vrb_sbtm_params", _capi.SbtmParams), ("vrb_dos_params", _capi.DosParams), ("vrb_ads_params", _capi.AdsParams),
+             ("vrb_crtgt_params", _capi.CrtgtParams)]
     src = tmp_path / "sizes.c"
     src.write_text('#include <stdio.h>\n#include "vrb200.h"\nint main(void) {\n' +
                    "".join(f'  printf("%zu\\n", sizeof({c}));\n' for c, _ in pairs) + "  return 0;\n}\n")
