@@ -1,5 +1,6 @@
-"""BASELINE.json configs 1, 3 and 4 at their stated sizes, CUDA path against the oracle (config 2: test_gpu_rc1pass.py
-test_full_size_c2_parity; config 5: test_gpu_c5.py).  Full frames, no row stride: accumulated float32 error over ~1800 samples per ray
+"""BASELINE.json configs 1, 3 and 4 at their stated sizes and both halves of config 5 at 512^3 / 1024^2 (the largest the CPU oracle
+finishes in seconds), CUDA path against the oracle (config 2: test_gpu_rc1pass.py test_full_size_c2_parity; config 5's bricks, region
+volumes and 64-bit indexing: test_gpu_c5.py).  Full frames, no row stride: accumulated float32 error over ~1800 samples per ray
 and cones that reach 0.5-0.75 of a 512-voxel diagonal are what the small cases cannot exercise.
 Bars (north_star): max |d| <= 2/255 per channel on RGBA16F*255 and on the RGB8-over-white image, SSIM >= 0.995."""
 import numpy as np
@@ -142,3 +143,74 @@ def test_c4_extinction_based_shading_full_size(ctx, bonsai_table):
     ref, total, shaded = O.ebs_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table), sat)
     _compare(got, got8, ref, f"C4 EBS 512^3 f32 -> 1024^2 ({ms:.2f} ms, SAT {build_ms:.2f} ms, {total} samples, {shaded} shaded)")
     assert abs(samples - total) <= 2e-3 * total
+
+
+def test_c5_vct_half_at_512_full_frame(ctx, bonsai_table):
+    """Config 5's ray-casting half on one GPU at the largest size the CPU oracle finishes in a minute: voxel cone tracing of a 512^3
+    uint8 volume at 1024x1024 (vct_ray_bbox_marching.comp, constructor defaults: 50 cone samples towards the light), supervoxel
+    pyramid and pre-integration table built on the GPU and compared with the oracle's first; the frame with the default cone-tap
+    filter (float32 on level 0, the texture unit's filter on the coarser levels) and with float32 weights everywhere.  The 2048^3 /
+    3840x2160 / 8-GPU form of the config is measured by bench.py --config c5; its machinery is tested in test_gpu_c5.py."""
+    n, w, h = 512, 1024, 1024
+    vox = inputs.synth_volume(n, np.uint8)
+    ctx.upload_volume(vox); ctx.upload_tf(bonsai_table)
+    cam = inputs.default_camera(n, w, h)
+    light = inputs.default_light(n)
+    r = _capi.Renderer(ctx, _capi.VRB_VCT)
+    frames = {}
+    try:
+        r.init(w, h)
+        prm = r.get_params(_capi.VctParams())
+        assert prm.exact_cone_filter == 2 and prm.cone_number_of_samples == 50
+        prm.step_size = 0.5; prm.count_samples = 1
+        for mode in (2, 1):
+            prm.exact_cone_filter = mode
+            r.set_params(prm)
+            r.update(cam, light); r.redraw()
+            frames[mode] = (r.read_frame(_capi.VRB_FRAME_RGBA32F), r.read_frame(_capi.VRB_FRAME_RGB8_OVER_WHITE), r.counters())
+        lut, max_std, n_levels, build_ms = r.read_vct_lut()
+    finally:
+        r.close()
+    levels, ref_max = O.vct_supervoxels(vox)
+    assert ref_max == max_std and len(levels) == n_levels
+    ref_lut = O.vct_preintegration(bonsai_table, np.uint8, ref_max)
+    assert lut.shape == ref_lut.shape and np.abs(lut - ref_lut).max() <= 2.0 ** -10 * max(float(ref_lut.max()), 1e-3)      # device exp / erf against libm, R16F
+    p = O.vct_params(cam, w, h, vox.shape, prm.step_size, list(light.position), 255.0, ref_max,
+                     apply_occlusion=prm.apply_ambient_occlusion, apply_shadow=prm.apply_directional_shadows,
+                     apex_angle_deg=prm.cone_apex_angle, cone_step_size=prm.cone_step_size, increase_rate=prm.cone_step_increase_rate,
+                     initial_step=prm.cone_initial_step, opacity_correction=prm.opacity_correction_factor,
+                     apply_correction=prm.apply_correction_factor, cone_samples=prm.cone_number_of_samples, ka=light.ka, kd=light.kd)
+    ref, total = O.vct_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table), levels, ref_lut)
+    for mode, label in ((2, "default cone filter"), (1, "float32 cone taps")):
+        got, got8, (samples, ms) = frames[mode]
+        _compare(got, got8, ref, f"C5 VCT half 512^3 -> 1024^2, {label} ({ms:.2f} ms, {total} samples, pyramid {build_ms:.1f} ms)")
+        assert abs(samples - total) <= 2e-3 * total
+
+
+def test_c5_sbtm_half_at_512_full_frame(ctx, bonsai_table):
+    """Config 5's slice-based half on one GPU: SBTMDirectionalOcclusionShading of a 512^3 uint8 volume at 1024x1024, step 0.5 (1673
+    slices, constructor defaults: 50 degree cone, 2 x 2 taps).  The occlusion buffer feeds back into itself once per slice, so a
+    full-size frame is the case that shows whether the per-slice arithmetic keeps to the oracle's over 1673 generations."""
+    n, w, h = 512, 1024, 1024
+    vox = inputs.synth_volume(n, np.uint8)
+    ctx.upload_volume(vox); ctx.upload_tf(bonsai_table)
+    cam = inputs.default_camera(n, w, h)
+    r = _capi.Renderer(ctx, _capi.VRB_SBTM_DOS)
+    try:
+        r.init(w, h)
+        prm = r.get_params(_capi.SbtmParams())
+        prm.step_size = 0.5; prm.count_fragments = 1
+        r.set_params(prm)
+        r.update(cam, inputs.default_light(n)); r.redraw()
+        got = r.read_frame(_capi.VRB_FRAME_RGBA32F); got8 = r.read_frame(_capi.VRB_FRAME_RGB8_OVER_WHITE)
+        frags, ms = r.counters()
+        occ, slices = r.read_sbtm_occlusion(w, h)
+    finally:
+        r.close()
+    p = O.sbtm_params(cam, w, h, vox.shape, prm.step_size, cone_half_angle=prm.cone_half_angle, grid=tuple(prm.grid_size),
+                      ui_weight=prm.occ_ui_weight_percentage, max_passes=prm.max_number_of_passes)
+    ref, ref_occ, total, ref_slices = O.sbtm_render(p, O.volume_r16f(vox), O.tf_texture(bonsai_table))
+    assert slices == ref_slices and frags == total
+    docc = float(np.abs(occ - ref_occ).max()) * 255.0
+    _compare(got, got8, ref, f"C5 SBTM half 512^3 -> 1024^2 ({ms:.2f} ms, {slices} slices, {total} fragments, occlusion buffer max|d| {docc:.3f}/255)")
+    assert docc <= 2.0
