@@ -337,17 +337,26 @@ struct DosCone {
   const float4* sections; int counts[3]; float axes[10][3]; float initial_step, adj7, ui_weight;
 };
 
-struct DosShader {
+#ifndef VRB_DOS_HW_MINB
+#define VRB_DOS_HW_MINB 6
+#endif
+struct DosArgs {
+  cudaTextureObject_t mip[DOS_MAX_LEVELS]; float mip_res[DOS_MAX_LEVELS][3]; int n_levels;
+  cudaTextureObject_t mip_hw;          // the whole pyramid as one mipmapped texture, one tex3DLod per tap (HW shader)
+  DosCone occ, sdw;
+  int type_of_shadow; float spot_cos;
+  float light_fwd[3], light_up[3], light_right[3];
+};
+
+// HW = the cone taps go through the texture unit's filter (exact_cone_filter 0), else float32 weights.  Two kernels, not a run-time
+// switch: the float32 path's footprint fetches and lerps are most of the shader's code and registers.
+template <bool HW>
+struct DosShaderT {
+  static constexpr int MIN_CTAS = HW ? VRB_DOS_HW_MINB : 4;   // resident CTAs per SM the kernel is compiled for (register cap 65536 / 128 / MIN_CTAS)
   static constexpr int ADVANCE = 4, BATCH = 16;   // park-and-shade schedule of the shared march (vrb_march.cuh): measured at C3 (512^3, 1024^2): lockstep (1, 1) 7.1 / 23.0 ms without / with shadows, (4, 16) 5.6 / 15.7 ms, (8, 24) 6.5 / 16.3 ms
   static constexpr bool OBJECT_SPACE = false;
   static constexpr int PHONG_KIND = 0;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
-  struct Args {
-    cudaTextureObject_t mip[DOS_MAX_LEVELS]; float mip_res[DOS_MAX_LEVELS][3]; int n_levels;
-    cudaTextureObject_t mip_hw; int hw_filter;        // hw_filter: the whole pyramid as one mipmapped texture, one tex3DLod per tap
-    DosCone occ, sdw;
-    int type_of_shadow; float spot_cos;
-    float light_fwd[3], light_up[3], light_right[3];
-  };
+  using Args = DosArgs;
   struct Const { f3 sizes, eye, inv_sizes; };
   static __device__ __forceinline__ void prepare_block(const MarchArgs&, const Args&) {}
   static __device__ __forceinline__ Const prepare(const MarchArgs& a, const Args&) {
@@ -366,7 +375,7 @@ struct DosShader {
   }
   // textureLod on the pyramid (min LINEAR_MIPMAP_LINEAR, mag LINEAR)
   static __device__ __forceinline__ float texture_lod(const Args& s, f3 p, float lod) {
-    if (s.hw_filter) return tex3DLod<float>(s.mip_hw, p.x, p.y, p.z, lod);       // lod clamped to [0, q] by the texture object
+    if (HW) return tex3DLod<float>(s.mip_hw, p.x, p.y, p.z, lod);       // lod clamped to [0, q] by the texture object
     const int q = s.n_levels - 1;
     if (!(lod > 0.0f)) return level_sample(s, 0, p);
     if (lod >= (float)q) return level_sample(s, q, p);
@@ -378,7 +387,7 @@ struct DosShader {
   }
   // GetGaussianExtinction (ray_bbox_marching.comp:92-112), CONSIDER_BORDERS
   static __device__ __forceinline__ float gaussian_extinction(const Args& s, const Const& c, f3 pos, float mip) {
-    float rg = texture_lod(s, s.hw_filter ? mul3(pos, c.inv_sizes) : div3(pos, c.sizes), mip);
+    float rg = texture_lod(s, HW ? mul3(pos, c.inv_sizes) : div3(pos, c.sizes), mip);
     if (pos.x < 0.0f || pos.x > c.sizes.x || pos.y < 0.0f || pos.y > c.sizes.y || pos.z < 0.0f || pos.z > c.sizes.z) {
       const float sg = exp2f(mip);
       const f3 cl = sub3(min3(max3(pos, mk3(0.f, 0.f, 0.f)), c.sizes), pos);
@@ -583,11 +592,11 @@ class DosRenderer : public RendererImpl {
     VRB_REQUIRE(!phong || (ctx->vol.tex_grad_pt && ctx->vol.grad_gen == ctx->vol.generation), VRB_ERR_INVALID, "RC1PConeTracingDirOcclusionShading: gradient shading needs vrb_volume_gradient() for the current volume");
     if (!fill_march_args(*this, prm_.step_size, prm_.apply_occlusion, prm_.apply_shadow, a, phong)) return VRB_OK;
     if (prm_.count_samples == 2) a.count_mode = 2;   // shaded samples (each evaluates every section of its cones: counts x rays fetches)
-    DosShader::Args s{};
+    DosArgs s{};
     s.n_levels = pyr_.n_levels;
     for (int l = 0; l < pyr_.n_levels; l++) { s.mip[l] = pyr_.tex[l]; s.mip_res[l][0] = (float)pyr_.lw[l]; s.mip_res[l][1] = (float)pyr_.lh[l]; s.mip_res[l][2] = (float)pyr_.ld[l]; }
     s.mip_hw = pyr_.tex_hw;
-    s.hw_filter = (prm_.exact_cone_filter == 0 && !prm_.use_light_cache) ? 1 : 0;
+    const bool hw = prm_.exact_cone_filter == 0 && !prm_.use_light_cache;
     auto fill = [](DosCone& c, const ConeTable& t, const float* dev, float initial_step, float uiw) {
       c.sections = (const float4*)dev;
       for (int i = 0; i < 3; i++) c.counts[i] = t.counts[i];
@@ -601,10 +610,10 @@ class DosRenderer : public RendererImpl {
     for (int i = 0; i < 3; i++) { s.light_fwd[i] = prm_.light_cam_forward[i]; s.light_up[i] = prm_.light_cam_up[i]; s.light_right[i] = prm_.light_cam_right[i]; }
     if (brick_ranks > 0) {
       VRB_REQUIRE(!prm_.use_light_cache, VRB_ERR_UNSUPPORTED, "sort-last bricks and the light-cache mode do not combine");
-      return redraw_sort_last<DosShader>(*this, a, s, prm_.count_samples != 0);
+      return hw ? redraw_sort_last<DosShaderT<true>>(*this, a, s, prm_.count_samples != 0) : redraw_sort_last<DosShaderT<false>>(*this, a, s, prm_.count_samples != 0);
     }
-    if (prm_.use_light_cache) return redraw_object_space<DosShader>(*this, cache_, prm_.light_cache_resolution, a, s, prm_.count_samples != 0);
-    return launch_march<DosShader>(*this, a, s, prm_.count_samples != 0);
+    if (prm_.use_light_cache) return redraw_object_space<DosShaderT<false>>(*this, cache_, prm_.light_cache_resolution, a, s, prm_.count_samples != 0);
+    return hw ? launch_march<DosShaderT<true>>(*this, a, s, prm_.count_samples != 0) : launch_march<DosShaderT<false>>(*this, a, s, prm_.count_samples != 0);
   }
  private:
   int ensure_precompute() {

@@ -187,6 +187,7 @@ constexpr int EBS_CONE_TABLE = 1024;
 __shared__ float s_ebs_mpos[3][EBS_CONE_TABLE];
 
 struct EbsShader {
+  static constexpr int MIN_CTAS = 4;
   static constexpr int ADVANCE = 1, BATCH = 1;   // park-and-shade schedule of the shared march (vrb_march.cuh): warp-cooperative form (VRB_EBS_WARPCOOP): one sample over the warp
   static constexpr bool OBJECT_SPACE = false;
   static constexpr int PHONG_KIND = 1;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)

@@ -490,21 +490,27 @@ namespace vrb {
 constexpr int VCT_CONE_TABLE = 256;
 __shared__ float s_vct_cone[3][VCT_CONE_TABLE];
 
-struct VctShader {
+struct VctArgs {
+  cudaTextureObject_t mip[VCT_MAX_LEVELS];
+  cudaTextureObject_t mip_hw[VCT_MAX_LEVELS];
+  cudaTextureObject_t mip1;                    // 0: none (region pyramids)
+  float mip_res[VCT_MAX_LEVELS][3];          // dims of the whole level
+  float mip_off[VCT_MAX_LEVELS][3];          // texel origin of the stored array inside the level (region pyramids; else 0)
+  int n_levels;
+  const float* lut; int lut_w, lut_h;
+  float cone_step, cone_rate, cone_initial, tan_apex, corr_fact, vol_max_density, vol_max_std;
+  int cone_samples;
+};
+
+// HWF: filter of the cone's pyramid taps, a compile-time property of the kernel (0 = float32 weights everywhere, 1 = the texture unit
+// everywhere, 2 = float32 on level 0 and the texture unit above: vrb_vct_params::exact_cone_filter 1 / 0 / 2)
+template <int HWF>
+struct VctShaderT {
+  static constexpr int MIN_CTAS = HWF ? 5 : 4;   // 94-95 registers with hardware taps: five resident CTAs per SM
   static constexpr int ADVANCE = 1, BATCH = 1;   // park-and-shade schedule of the shared march (vrb_march.cuh): the cone of ONE sample is spread over the warp, so parking samples gains nothing: lockstep 12.7 ms, (4, 16) 13.0 ms at 512^3 / 1024^2
   static constexpr bool OBJECT_SPACE = false;
   static constexpr int PHONG_KIND = 1;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
-  struct Args {
-    cudaTextureObject_t mip[VCT_MAX_LEVELS];
-    cudaTextureObject_t mip_hw[VCT_MAX_LEVELS]; int hw_filter;
-    cudaTextureObject_t mip1;                    // 0: none (region pyramids)
-    float mip_res[VCT_MAX_LEVELS][3];          // dims of the whole level
-    float mip_off[VCT_MAX_LEVELS][3];          // texel origin of the stored array inside the level (region pyramids; else 0)
-    int n_levels;
-    const float* lut; int lut_w, lut_h;
-    float cone_step, cone_rate, cone_initial, tan_apex, corr_fact, vol_max_density, vol_max_std;
-    int cone_samples;
-  };
+  using Args = VctArgs;
   struct Const { f3 sizes; };
   static __device__ __forceinline__ Const prepare(const MarchArgs& a, const Args&) { Const c; c.sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]); return c; }
   static __device__ __forceinline__ void prepare_block(const MarchArgs&, const Args& s) {
@@ -524,7 +530,7 @@ struct VctShader {
   // texture(sampler3D RG16F, p) on one level: GL_LINEAR / CLAMP_TO_EDGE, float32 weights (oracle sample_level)
   static __device__ __forceinline__ float2 sample_level(const Args& s, int l, f3 p) {
     const f3 res = mk3(s.mip_res[l][0], s.mip_res[l][1], s.mip_res[l][2]);
-    if (s.hw_filter == 1 || (s.hw_filter == 2 && l > 0)) return tex3D<float2>(s.mip_hw[l], p.x * res.x - s.mip_off[l][0], p.y * res.y - s.mip_off[l][1], p.z * res.z - s.mip_off[l][2]);
+    if (HWF == 1 || (HWF == 2 && l > 0)) return tex3D<float2>(s.mip_hw[l], p.x * res.x - s.mip_off[l][0], p.y * res.y - s.mip_off[l][1], p.z * res.z - s.mip_off[l][2]);
     const float X = __fsub_rn(__fmul_rn(p.x, res.x), 0.5f), Y = __fsub_rn(__fmul_rn(p.y, res.y), 0.5f), Z = __fsub_rn(__fmul_rn(p.z, res.z), 0.5f);
     float fx = floorf(X), fy = floorf(Y), fz = floorf(Z);
     const float ax = fx < 0.0f ? 0.0f : __fsub_rn(X, fx), ay = fy < 0.0f ? 0.0f : __fsub_rn(Y, fy), az = __fsub_rn(Z, fz);
@@ -543,7 +549,7 @@ struct VctShader {
   static __device__ __forceinline__ float2 texture_lod(const Args& s, f3 p, float lod) {
     const int q = s.n_levels - 1;
     if (!(lod > 0.0f)) return sample_level(s, 0, p);
-    if (s.hw_filter && s.mip1 && lod >= 1.0f) return tex3DLod<float2>(s.mip1, p.x, p.y, p.z, lod - 1.0f);   // both levels coarser than the voxels; lod clamped to q by the texture object
+    if (HWF != 0 && s.mip1 && lod >= 1.0f) return tex3DLod<float2>(s.mip1, p.x, p.y, p.z, lod - 1.0f);   // both levels coarser than the voxels; lod clamped to q by the texture object
     if (lod >= (float)q) return sample_level(s, q, p);
     const float fl = floorf(lod); const int d1 = (int)fl; const float f = __fsub_rn(lod, fl);
     const float2 v1 = sample_level(s, d1, p), v2 = sample_level(s, d1 + 1, p);
@@ -746,7 +752,7 @@ class VctRenderer : public RendererImpl {
     VRB_REQUIRE(!phong || (ctx->vol.tex_grad_pt && ctx->vol.grad_gen == ctx->vol.generation), VRB_ERR_INVALID, "RC1PVoxelConeTracingSGPU: gradient shading needs vrb_volume_gradient() for the current volume");
     if (!fill_march_args(*this, prm_.step_size, prm_.apply_ambient_occlusion, prm_.apply_directional_shadows, a, phong)) return VRB_OK;
     if (prm_.count_samples == 2 || prm_.count_samples == 3) a.count_mode = prm_.count_samples;   // shaded samples / cone steps
-    VctShader::Args s{};
+    VctArgs s{};
     s.n_levels = pyr_.n_levels;
     for (int l = 0; l < pyr_.n_levels; l++) {
       s.mip[l] = pyr_.tex[l]; s.mip_hw[l] = pyr_.tex_hw[l]; s.mip_res[l][0] = (float)pyr_.flw[l]; s.mip_res[l][1] = (float)pyr_.flh[l]; s.mip_res[l][2] = (float)pyr_.fld[l];
@@ -759,13 +765,15 @@ class VctRenderer : public RendererImpl {
     s.vol_max_density = (float)pyr_.vol_max_density; s.vol_max_std = (float)pyr_.max_std;
     s.cone_samples = prm_.cone_number_of_samples;
     s.mip1 = pyr_.tex_mip1;
-    s.hw_filter = prm_.use_light_cache ? 0 : (prm_.exact_cone_filter == 0 ? 1 : (prm_.exact_cone_filter == 2 ? 2 : 0));
+    const int hwf = prm_.use_light_cache ? 0 : (prm_.exact_cone_filter == 0 ? 1 : (prm_.exact_cone_filter == 2 ? 2 : 0));
     if (brick_ranks > 0) {
       VRB_REQUIRE(!prm_.use_light_cache, VRB_ERR_UNSUPPORTED, "sort-last bricks and the light-cache mode do not combine");
-      return redraw_sort_last<VctShader>(*this, a, s, prm_.count_samples != 0);
+      const bool c = prm_.count_samples != 0;
+      return hwf == 2 ? redraw_sort_last<VctShaderT<2>>(*this, a, s, c) : (hwf == 1 ? redraw_sort_last<VctShaderT<1>>(*this, a, s, c) : redraw_sort_last<VctShaderT<0>>(*this, a, s, c));
     }
-    if (prm_.use_light_cache) return redraw_object_space<VctShader>(*this, cache_, prm_.light_cache_resolution, a, s, prm_.count_samples != 0);
-    return launch_march<VctShader>(*this, a, s, prm_.count_samples != 0);
+    if (prm_.use_light_cache) return redraw_object_space<VctShaderT<0>>(*this, cache_, prm_.light_cache_resolution, a, s, prm_.count_samples != 0);
+    const bool c = prm_.count_samples != 0;
+    return hwf == 2 ? launch_march<VctShaderT<2>>(*this, a, s, c) : (hwf == 1 ? launch_march<VctShaderT<1>>(*this, a, s, c) : launch_march<VctShaderT<0>>(*this, a, s, c));
   }
  private:
   vrb_vct_params prm_{};

@@ -13,6 +13,7 @@ namespace vrb {
 
 #ifdef __CUDACC__
 struct LightCacheShader {
+  static constexpr int MIN_CTAS = 4;
   static constexpr int ADVANCE = 1, BATCH = 1;   // park-and-shade schedule of the shared march (vrb_march.cuh): shading is one trilinear fetch of the cache: nothing to batch
   static constexpr bool OBJECT_SPACE = true;
   static constexpr int PHONG_KIND = 1;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)

@@ -53,7 +53,7 @@ constexpr int MARCH_THREADS = 128;
 
 #ifdef __CUDACC__
 template <class S, bool COUNT, int SL = 0>
-__global__ void __launch_bounds__(MARCH_THREADS, 4) shaded_march_kernel(const __grid_constant__ MarchArgs a, const __grid_constant__ typename S::Args sa) {
+__global__ void __launch_bounds__(MARCH_THREADS, S::MIN_CTAS) shaded_march_kernel(const __grid_constant__ MarchArgs a, const __grid_constant__ typename S::Args sa) {
   extern __shared__ uint4 s_dyn[];
   uint4* s_tf = s_dyn;
   uint32_t* s_mask = reinterpret_cast<uint32_t*>(s_dyn + a.tf_n);

@@ -174,7 +174,7 @@ typedef struct {
                                               trilinear filter (1.8 fixed-point weights), 1 = float32 weights on every level, 2 (default) =
                                               float32 weights on pyramid level 0 (the voxels themselves, where neighbouring texels differ
                                               most) and the texture unit on the coarser levels.  Measured against the float32 oracle on the
-                                              parity cases: worst 1.56 / 0.13 / 0.62 of the 2/255 bar; 512^3 / 1024^2 frame 7.3 / 13.4 / 8.9 ms.
+                                              parity cases: worst 1.56 / 0.13 / 0.62 of the 2/255 bar; 512^3 / 1024^2 frame 6.6 / 12.8 / 8.2 ms.
                                               The light-cache pass always uses float32 weights. */
 } vrb_vct_params;
 
@@ -226,7 +226,7 @@ typedef struct {
                                               trilinear filter (1.8 fixed-point weights, as the reference's GLSL taps on the same hardware);
                                               1: float32 weights (the filter the GL specification writes down, and the oracle's).  Measured
                                               against the float32 oracle: worst 0.44 / 0.13 of the 2/255 bar at 512^3 / 1024^2 (C3), frame
-                                              4.1 / 5.8 ms (8.2 / 16.6 ms with shadows).  The light-cache pass always uses float32 weights. */
+                                              3.8 / 5.8 ms (6.7 / 16.6 ms with shadows).  The light-cache pass always uses float32 weights. */
 } vrb_dos_params;
 
 /* ---- library / context ------------------------------------------------------------------- */
