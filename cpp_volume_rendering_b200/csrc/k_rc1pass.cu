@@ -669,8 +669,8 @@ class Rc1Pass : public RendererImpl {
     if (p.step_size <= 0.0f) p.step_size = prm_.step_size;
     VRB_REQUIRE(p.skip_block == 0 || p.skip_block == 4 || p.skip_block == 8 || p.skip_block == 16 || p.skip_block == 32,
                 VRB_ERR_INVALID, "RayCasting1Pass::set_params: skip_block must be 0, 4, 8, 16 or 32");
-    VRB_REQUIRE(p.depth_split == 0 || p.depth_split == 1 || p.depth_split == 2 || p.depth_split == 4 || p.depth_split == 8,
-                VRB_ERR_INVALID, "RayCasting1Pass::set_params: depth_split must be 0, 1, 2, 4 or 8");
+    VRB_REQUIRE(p.depth_split == -1 || p.depth_split == 0 || p.depth_split == 1 || p.depth_split == 2 || p.depth_split == 4 || p.depth_split == 8,
+                VRB_ERR_INVALID, "RayCasting1Pass::set_params: depth_split must be -1 (chosen by the library), 0, 1, 2, 4 or 8");
     VRB_REQUIRE(p.split_groups >= 0 && p.split_groups <= 64, VRB_ERR_INVALID, "RayCasting1Pass::set_params: split_groups must be 0..64");
     prm_ = p;
     return VRB_OK;
@@ -753,9 +753,19 @@ class Rc1Pass : public RendererImpl {
       VRB_CUDA(cudaGetLastError());
       return VRB_OK;
     }
-    if (prm_.depth_split > 1 && !prm_.skip_block && prm_.tf_in_smem && prm_.exact_filter) {
+    int split = prm_.depth_split;
+    if (split == -1) {
+      // Chosen from what bounds the launch: few rays per GPU and long rays -> the dependent chain of the longest rays, which K lanes per
+      // ray shorten; many rays -> the texture unit, where the split's extra instructions only cost.  Thresholds from the measured table
+      // (tools/partition_sweep.py; 256^3 / 512^2: K = 2 0.097 against 0.106 ms, 512^3 / 512^2: 0.186 against 0.219 ms,
+      // 512^3 at 768^2 and above on one GPU: K = 1; 131 k rays of a 512^3 volume per GPU: K = 4).
+      const long long rays = (long long)my_tiles * part_tile * part_tile;
+      const float longest = std::sqrt(a.grid[0] * a.grid[0] + a.grid[1] * a.grid[1] + a.grid[2] * a.grid[2]) / a.step;    // samples on the box diagonal
+      split = rays <= 160000 && longest >= 1200.0f ? 4 : (rays <= 400000 ? 2 : 1);
+    }
+    if (split > 1 && !prm_.skip_block && prm_.tf_in_smem && prm_.exact_filter) {
       // depth-split march (see rc1pass_split_kernel): smaller pixel footprint per warp item, K lanes per ray
-      const int K = prm_.depth_split;
+      const int K = split;
       const int fw = K == 8 ? 2 : 4, fh = K == 2 ? 4 : 2;
       const int rc_o = ensure_tile_order();
       if (rc_o != VRB_OK) return rc_o;

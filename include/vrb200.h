@@ -93,7 +93,8 @@ typedef struct {
   int   tf_in_smem;              /* 1 (default) = TF in shared memory, float32 lerp; 0 = TF through the RGBA16F 1D texture unit */
   int   exact_filter;            /* 1 (default) = possibly-visible samples are re-filtered with float32 weights;
                                     0 = every sample uses the texture unit's 1.8 fixed-point trilinear filter */
-  int   depth_split;             /* 0/1 (default) = one lane per ray; 2/4/8 = that many lanes march consecutive depth segments of a
+  int   depth_split;             /* 0/1 (default) = one lane per ray; -1 = 1, 2 or 4 chosen by the library from the rays this GPU owns and
+                                    the length of the longest ray; 2/4/8 = that many lanes march consecutive depth segments of a
                                     ray and the partial results are folded with the over operator (same samples, same
                                     termination sample, sums re-associated): shortens the per-ray dependent chain when a GPU
                                     owns few pixels (image split over many GPUs).  Ignored with skip_block, tf_in_smem = 0 or

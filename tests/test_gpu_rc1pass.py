@@ -294,7 +294,7 @@ def test_image_partition_union_equals_full_frame(ctx, bonsai_table):
 
 
 @pytest.mark.parametrize("n,dtype,size,eye_s,up,step", CASES)
-@pytest.mark.parametrize("K", [2, 4, 8])
+@pytest.mark.parametrize("K", [2, 4, 8, -1])       # -1: the library picks 1, 2 or 4 from the rays it owns and the longest ray
 def test_depth_split_march_parity(ctx, bonsai_table, n, dtype, size, eye_s, up, step, K):
     """K lanes per ray, segments folded with the over operator, terminating segment re-marched from the exact prefix:
     same tolerance as the one-lane march, same sample count (the termination sample is found sequentially)."""

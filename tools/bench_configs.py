@@ -97,9 +97,12 @@ def measure(ctx, which, steps, warmup, tex_peak, hbm_peak):
         prm = r.get_params(_capi.Rc1PassParams()); prm.step_size = 0.5; r.set_params(prm)
         r.update(cam, light)
         samples = _count(r, _capi.Rc1PassParams, "count_samples", 1)
+        med1, _, _ = _frames(r, steps, warmup, flush)                         # one lane per ray (the parameter default)
+        prm = r.get_params(_capi.Rc1PassParams()); prm.depth_split = -1; r.set_params(prm)      # 262 k rays on one GPU: the library picks two lanes per ray
         med, lo, hi = _frames(r, steps, warmup, flush)
         r.close()
         out["c1"] = {"workload": "rc1pass_256c_u8_512x512_step0.5", "ms_per_frame": med, "ms_min_max": [lo, hi], "fps": 1e3 / med,
+                     "depth_split": "auto (-1)", "ms_per_frame_one_lane_per_ray": med1,
                      "samples_per_frame": samples, "samples_per_s": samples / (med * 1e-3),
                      "roofline": _tex_block("rc1pass_kernel", samples, med, tex_peak, "c1", "march samples x 1 trilinear R16F fetch")}
 
