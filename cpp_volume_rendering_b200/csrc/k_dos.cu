@@ -338,7 +338,7 @@ struct DosCone {
 };
 
 #ifndef VRB_DOS_HW_MINB
-#define VRB_DOS_HW_MINB 6
+#define VRB_DOS_HW_MINB 5
 #endif
 struct DosArgs {
   cudaTextureObject_t mip[DOS_MAX_LEVELS]; float mip_res[DOS_MAX_LEVELS][3]; int n_levels;

@@ -124,11 +124,34 @@ __global__ void __launch_bounds__(MARCH_THREADS, S::MIN_CTAS) shaded_march_kerne
     float pend_h = 0.0f;
     f3 pend_tx = mk3(0.f, 0.f, 0.f);
     float4 pend_src = make_float4(0.f, 0.f, 0.f, 0.f);
+    // Classification fetches run MARCH_G lattice samples ahead of the sample being looked at: the positions of the next samples depend
+    // on s and D only (s + min(Step, D - s), accumulated exactly as below), so their hardware-filtered densities are fetched together
+    // and the ray pays one texture round trip per MARCH_G samples instead of one per sample.  The buffer outlives a parked sample (the
+    // ray resumes behind it) and is simply dropped when the ray ends.
+    float dq0 = 0.0f, dq1 = 0.0f, dq2 = 0.0f, dq3 = 0.0f;
+    int dq_n = 0;                              // densities left in the buffer; dq0 is the one of the sample at s
     for (;;) {
 #pragma unroll 1
       for (int it = 0; it < a.advance && alive && !pending; it++) {
         if (!(s < D)) alive = false;
+        if (alive && dq_n == 0) {
+          float ss = s;
+          float dd[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+          for (int g = 0; g < 4; g++) {
+            if (ss < D) {
+              const float hg = gmin(a.step, __fsub_rn(D, ss));
+              const f3 pg = mul3(add3(wd, scale3(dir, __fadd_rn(ss, __fmul_rn(hg, 0.5f)))), inv_sizes);
+              dd[g] = tex3D<float>(a.vol, fmaf(pg.x, a.vscale[0], a.vbias[0]), fmaf(pg.y, a.vscale[1], a.vbias[1]), fmaf(pg.z, a.vscale[2], a.vbias[2]));
+              ss = __fadd_rn(ss, hg);
+            }
+          }
+          dq0 = dd[0]; dq1 = dd[1]; dq2 = dd[2]; dq3 = dd[3];
+          dq_n = 4;
+        }
         if (alive) {
+          const float d_next = dq0;              // the density of the sample at s, whether or not this rank classifies it
+          dq0 = dq1; dq1 = dq2; dq2 = dq3; dq_n--;
           const float h = gmin(a.step, __fsub_rn(D, s));
           const f3 tx = add3(wd, scale3(dir, __fadd_rn(s, __fmul_rn(h, 0.5f))));
           bool inside = true;
@@ -143,7 +166,7 @@ __global__ void __launch_bounds__(MARCH_THREADS, S::MIN_CTAS) shaded_march_kerne
           if (alive && inside) {
             const f3 p = mul3(tx, inv_sizes);
             if (COUNT && a.count_mode == 1) nsamp++;
-            const float d_hw = tex3D<float>(a.vol, fmaf(p.x, a.vscale[0], a.vbias[0]), fmaf(p.y, a.vscale[1], a.vbias[1]), fmaf(p.z, a.vscale[2], a.vbias[2]));
+            const float d_hw = d_next;
             int j = (int)fminf(fmaxf(fmaf(d_hw, tfn, -0.5f), 0.0f), tfmax);
             if ((s_mask[j >> 5] >> (j & 31)) & 1u) {
               const float density = tex3d_f32_exact(a.vol_quad, p, res, mk3(a.voff[0], a.voff[1], a.voff[2]));
