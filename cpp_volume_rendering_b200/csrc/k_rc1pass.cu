@@ -302,6 +302,7 @@ __device__ __forceinline__ float group_geom(float s, float D, float step, float 
 
 template <bool COUNT, bool TF_SMEM, bool EXACT, bool SKIP, bool GRAD = false>
 __global__ void __launch_bounds__(CTA_THREADS, VRB_RC1_MINB) rc1pass_kernel(const __grid_constant__ Rc1Args a) {
+  begin_launch(a.sig);
   extern __shared__ uint4 s_dyn[];
   uint4* s_tf = s_dyn;                                   // TF_SMEM: entry i = {texel i, texel min(i+1,n-1)}
   uint32_t* s_mask = reinterpret_cast<uint32_t*>(s_dyn + (TF_SMEM ? a.tf_n : 0));
@@ -539,6 +540,7 @@ __device__ __forceinline__ void march_groups(const Rc1Args& a, const uint4* s_tf
 template <bool COUNT, int K>
 __global__ void __launch_bounds__(CTA_THREADS, VRB_SPLIT_MINB) rc1pass_split_kernel(const __grid_constant__ Rc1Args a) {
   constexpr int PIX = 32 / K, FW = SplitGeom<K>::FW, FH = SplitGeom<K>::FH;
+  begin_launch(a.sig);
   extern __shared__ uint4 s_dyn[];
   uint4* s_tf = s_dyn;
   uint32_t* s_mask = reinterpret_cast<uint32_t*>(s_dyn + a.tf_n);
@@ -644,6 +646,7 @@ class Rc1Pass : public RendererImpl {
     prm_.step_size = 0.5f;               // m_u_step_size(0.5f)            rc1prenderer.cpp:21
     prm_.apply_gradient_shading = 0;     // m_apply_gradient_shading(false) rc1prenderer.cpp:22
     prm_.skip_block = 0; prm_.count_samples = 0; prm_.tf_in_smem = 1; prm_.exact_filter = 1; prm_.depth_split = 0; prm_.split_groups = 0;
+    credit_in_kernel = true;             // every kernel of this renderer starts with begin_launch()
   }
 
   // Init (rc1prenderer.cpp:50-70): requires a volume texture, takes the RGBt transfer-function texture,

@@ -135,6 +135,9 @@ struct RendererImpl {
   void abort_frame();                    // undoes begin_frame when the redraw failed before its launch
   // VRB_GATHER_ROOT back-pressure (frame_credit, vrb_renderer.cu): rank 0 maps the senders' allocations only to write their credit word
   void* credit_opened[MAX_PEERS] = {}; int n_credit_peers = 0; unsigned** d_credit_words = nullptr;
+  unsigned* credit_words_host[MAX_PEERS] = {};   // the same addresses, for kernels that write the credit themselves (PeerSignal)
+  bool credit_in_kernel = false;                 // the renderer's kernel calls begin_launch(): no separate one-thread launch per redraw
+  unsigned pending_credit = 0;                   // value the next launch writes (0: none)
   int frame_credit();
   unsigned* flags() const { return (unsigned*)((char*)frame_base + 2 * frame_bytes); }
   // Sort-last bricks (vrb_renderer_set_bricks, vrb_sortlast.cuh): the volume box is cut into brick_grid[0] x [1] x [2] bricks, one per
@@ -199,9 +202,14 @@ inline bool use_lpt_order() { static const bool v = []() { const char* e = geten
 // counter != 0 (VRB_GATHER_ALL): instead of its own flag word each sender bumps ONE arrival counter per consumer, so
 // the consumer needs a single stream wait (counter >= frame * senders).  Sound because in that mode every rank waits
 // for frame k before it launches frame k + 1: no arrival of frame k + 1 can precede the last arrival of frame k.
-struct PeerSignal { unsigned* flag[RendererImpl::MAX_PEERS]; int n; unsigned seq; int counter; };
+struct PeerSignal {
+  unsigned* flag[RendererImpl::MAX_PEERS]; int n; unsigned seq; int counter;
+  unsigned* credit[RendererImpl::MAX_PEERS]; int n_credit; unsigned credit_value;    // VRB_GATHER_ROOT, rank 0: written when the launch starts
+};
 inline void fill_peer_signal(const RendererImpl& r, PeerSignal& ps) {
   ps.n = r.n_peer_frames; ps.seq = r.frame_seq; ps.counter = r.gather_mode == VRB_GATHER_ALL ? 1 : 0;
+  ps.n_credit = (r.credit_in_kernel && r.pending_credit) ? r.n_credit_peers : 0; ps.credit_value = r.pending_credit;
+  for (int q = 0; q < ps.n_credit; q++) ps.credit[q] = r.credit_words_host[q];
   for (int q = 0; q < r.n_peer_frames; q++)
     ps.flag[q] = ps.counter ? (unsigned*)((char*)r.peer_opened[q] + 2 * r.frame_bytes) + (RendererImpl::FRAME_FLAGS - 1) : r.peer_flags[q];
 }
@@ -209,6 +217,12 @@ inline void fill_peer_signal(const RendererImpl& r, PeerSignal& ps) {
 // Called by every warp when it has no more work (all lanes).  The last warp of the launch re-arms the work queue for
 // the next redraw and, with peers, publishes the frame number: every warp's pixel stores to peer memory are made
 // visible system-wide before its increment, so a peer that sees the flag also sees the pixels.
+// Called once at the start of a kernel whose renderer sets credit_in_kernel: rank 0's consumed-frame credit to the senders
+// (RendererImpl::frame_credit) without a launch of its own in front of every redraw.  Stream order puts the kernel, hence the store,
+// behind every read of the consumed frame.
+__device__ __forceinline__ void begin_launch(const PeerSignal& ps) {
+  if (blockIdx.x == 0 && (int)threadIdx.x < ps.n_credit) { *(volatile unsigned*)ps.credit[threadIdx.x] = ps.credit_value; __threadfence_system(); }
+}
 __device__ __forceinline__ void finish_launch(unsigned* queue, const PeerSignal& ps) {
   __syncwarp();
   if ((threadIdx.x & 31) == 0) {

@@ -168,7 +168,9 @@ __global__ void frame_credit_kernel(unsigned* const* words, int n, unsigned valu
 int RendererImpl::frame_credit() {
   if (gather_mode != VRB_GATHER_ROOT || gather_ranks <= 1) return VRB_OK;
   if (rank == 0) {
+    pending_credit = 0;
     if (frame_seq < 2 || n_credit_peers == 0) return VRB_OK;
+    if (credit_in_kernel) { pending_credit = frame_seq - 1; return VRB_OK; }       // the redraw's own kernel stores it (begin_launch)
     frame_credit_kernel<<<1, 32, 0, ctx->stream>>>(d_credit_words, n_credit_peers, frame_seq - 1);
     VRB_CUDA(cudaGetLastError());
     return VRB_OK;
@@ -593,6 +595,7 @@ int vrb_renderer_set_peers(vrb_renderer* r, const void* handles, int n_ranks, in
   if (p->n_credit_peers) {
     unsigned* words[RendererImpl::MAX_PEERS];
     for (int q = 0; q < p->n_credit_peers; q++) words[q] = (unsigned*)((char*)p->credit_opened[q] + 2 * p->frame_bytes) + (RendererImpl::FRAME_FLAGS - 3);
+    for (int q = 0; q < p->n_credit_peers; q++) p->credit_words_host[q] = words[q];
     if (!p->d_credit_words) VRB_CUDA(cudaMalloc(&p->d_credit_words, RendererImpl::MAX_PEERS * sizeof(unsigned*)));
     VRB_CUDA(cudaMemcpy(p->d_credit_words, words, p->n_credit_peers * sizeof(unsigned*), cudaMemcpyHostToDevice));
   }
