@@ -543,6 +543,7 @@ class DosRenderer : public RendererImpl {
                     p.gaussian_sigma_limit_multiplier > 0.0f,
                 VRB_ERR_INVALID, "dos set_params: bad value");
     VRB_REQUIRE(light_cache_params_ok(p.use_light_cache, p.light_cache_resolution), VRB_ERR_INVALID, "dos set_params: bad light cache resolution");
+    VRB_REQUIRE(p.exact_cone_filter == 0 || p.exact_cone_filter == 1, VRB_ERR_INVALID, "dos set_params: exact_cone_filter must be 0 or 1");
     if (memcmp(&p, &prm_, sizeof(p)) != 0) cones_valid_ = false;
     prm_ = p;
     return VRB_OK;

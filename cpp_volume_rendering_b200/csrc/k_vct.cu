@@ -665,6 +665,7 @@ class VctRenderer : public RendererImpl {
     const vrb_vct_params p = *(const vrb_vct_params*)pod;
     VRB_REQUIRE(p.step_size > 0.0f && p.cone_step_size > 0.0f && p.cone_number_of_samples >= 0, VRB_ERR_INVALID, "vct set_params: bad value");
     VRB_REQUIRE(light_cache_params_ok(p.use_light_cache, p.light_cache_resolution), VRB_ERR_INVALID, "vct set_params: bad light cache resolution");
+    VRB_REQUIRE(p.exact_cone_filter >= 0 && p.exact_cone_filter <= 2, VRB_ERR_INVALID, "vct set_params: exact_cone_filter must be 0, 1 or 2");
     prm_ = p;
     return VRB_OK;
   }
