@@ -537,7 +537,12 @@ __device__ __forceinline__ void march_groups(const Rc1Args& a, const uint4* s_tf
   }
 }
 
-template <bool COUNT, int K>
+// SKIP: lattice-preserving empty-space skipping in front of every chunk.  The K lanes of a pixel run the same leap loop (same inputs,
+// same result): from the first sample of the next chunk the ray leaps over empty cubes of blocks exactly as rc1pass_kernel<.., SKIP> does,
+// and the chunk then starts at the group that holds the first sample outside them (up to UNROLL - 1 samples of the empty cube are
+// marched for nothing: they are transparent).  Same samples composited as without skipping; chunk boundaries, hence the association of
+// the over-operator folds, differ.
+template <bool COUNT, int K, bool SKIP>
 __global__ void __launch_bounds__(CTA_THREADS, VRB_SPLIT_MINB) rc1pass_split_kernel(const __grid_constant__ Rc1Args a) {
   constexpr int PIX = 32 / K, FW = SplitGeom<K>::FW, FH = SplitGeom<K>::FH;
   begin_launch(a.sig);
@@ -574,6 +579,7 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_SPLIT_MINB) rc1pass_split_ker
     r.dst = make_float4(0.f, 0.f, 0.f, 0.f);
     r.done = false;
     float D = 0.0f;
+    float pvx0 = 0.f, pvy0 = 0.f, pvz0 = 0.f, dvx = 1.f, dvy = 1.f, dvz = 1.f;      // SKIP: ray in voxel units (as in rc1pass_kernel)
     if (hit) {
       D = fabsf(__fsub_rn(tfar, tnear));
       const float tpx = __fadd_rn(__fadd_rn(eye.x, __fmul_rn(dir.x, tnear)), bmax.x);
@@ -581,16 +587,19 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_SPLIT_MINB) rc1pass_split_ker
       const float tpz = __fadd_rn(__fadd_rn(eye.z, __fmul_rn(dir.z, tnear)), bmax.z);
       r.ux0 = tpx * a.inv_grid[0]; r.uy0 = tpy * a.inv_grid[1]; r.uz0 = tpz * a.inv_grid[2];
       r.dux = dir.x * a.inv_grid[0]; r.duy = dir.y * a.inv_grid[1]; r.duz = dir.z * a.inv_grid[2];
+      if (SKIP) {
+        pvx0 = tpx * a.inv_voxel[0]; pvy0 = tpy * a.inv_voxel[1]; pvz0 = tpz * a.inv_voxel[2];
+        dvx = dir.x * a.inv_voxel[0]; dvy = dir.y * a.inv_voxel[1]; dvz = dir.z * a.inv_voxel[2];
+      }
     }
     const int SPLIT_G = a.split_g;
-    const float chunk_len = (float)(K * SPLIT_G * UNROLL) * a.step;
     float4 P = make_float4(0.f, 0.f, 0.f, 0.f);               // running prefix, identical in the K lanes of a pixel
     unsigned nseq = 0;                                        // samples of the sequential march so far
     bool open = hit;                                          // this pixel's ray has neither ended nor terminated
     // One march call per loop iteration: a pixel whose running alpha passes 0.99 inside segment kstar goes into the
     // "redo" state — in the next iteration only its lane kstar marches, the same segment again but from the exact prefix —
     // while the other pixels of the warp walk their next chunk.
-    int c = 0;                                                // chunk index of this pixel
+    int gb = 0;                                               // first group of this pixel's next chunk
     int redo_k = -1;                                          // >= 0: redo state, segment that holds the terminating sample
     float4 Pstar = P;
     while (__any_sync(0xffffffffu, open)) {
@@ -598,7 +607,32 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_SPLIT_MINB) rc1pass_split_ker
       if (redo) r.dst = Pstar; else r.dst = make_float4(0.f, 0.f, 0.f, 0.f);
       r.done = false;
       unsigned n1 = 0;
-      const int g0 = (c * K + seg) * SPLIT_G;
+      if (SKIP && open && !redo) {
+        const float step = a.step, fB = (float)a.skip_block, invB = 1.0f / fB, inv_step = 1.0f / step;
+        const float idx_ = 1.0f / dvx, idy_ = 1.0f / dvy, idz_ = 1.0f / dvz;   // +-inf where the ray is axis-parallel
+        int k = gb * UNROLL;
+        for (;;) {
+          const float s = (float)k * step;
+          if (!(s < D)) { open = false; break; }
+          const float h0 = fminf(step, D - s), t0 = fmaf(h0, 0.5f, s);
+          const int bx = min(max((int)floorf(fmaf(dvx, t0, pvx0) * invB), 0), a.nbx - 1);
+          const int by = min(max((int)floorf(fmaf(dvy, t0, pvy0) * invB), 0), a.nby - 1);
+          const int bz = min(max((int)floorf(fmaf(dvz, t0, pvz0) * invB), 0), a.nbz - 1);
+          const int run = a.skip_map[(size_t)bx + (size_t)a.nbx * ((size_t)by + (size_t)a.nby * bz)];
+          if (run <= 0) break;
+          const float ex = ((dvx > 0.0f ? (float)(bx + run) : (float)(bx - run + 1)) * fB - pvx0) * idx_;
+          const float ey = ((dvy > 0.0f ? (float)(by + run) : (float)(by - run + 1)) * fB - pvy0) * idy_;
+          const float ez = ((dvz > 0.0f ? (float)(bz + run) : (float)(bz - run + 1)) * fB - pvz0) * idz_;
+          float te = D;
+          if (dvx != 0.0f) te = fminf(te, ex);
+          if (dvy != 0.0f) te = fminf(te, ey);
+          if (dvz != 0.0f) te = fminf(te, ez);
+          const int kn = (int)ceilf(fmaf(te, inv_step, -0.5f));
+          k = max(kn, k + 1);
+        }
+        gb = k / UNROLL;
+      }
+      const int g0 = gb + seg * SPLIT_G;
       if (open && (!redo || redo_k == seg)) march_groups<COUNT>(a, s_tf, s_mask, r, D, g0, SPLIT_G, n1);
       int kstar = -1;
       float4 Pnew = P;
@@ -620,7 +654,7 @@ __global__ void __launch_bounds__(CTA_THREADS, VRB_SPLIT_MINB) rc1pass_split_ker
       P = Pnew; nseq = nnew;
       if (redo) { open = false; redo_k = -1; }
       else if (kstar >= 0) redo_k = kstar;                    // same chunk again, lane kstar only
-      else { if (!((float)(c + 1) * chunk_len < D)) open = false; c++; }
+      else if (open) { gb += K * SPLIT_G; if (!((float)(gb * UNROLL) * a.step < D)) open = false; }
     }
     if (seg == 0 && valid) {
       const float4 o4 = hit ? P : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -766,7 +800,7 @@ class Rc1Pass : public RendererImpl {
       const float longest = std::sqrt(a.grid[0] * a.grid[0] + a.grid[1] * a.grid[1] + a.grid[2] * a.grid[2]) / a.step;    // samples on the box diagonal
       split = rays <= 160000 && longest >= 1200.0f ? 4 : (rays <= 400000 ? 2 : 1);
     }
-    if (split > 1 && !prm_.skip_block && prm_.tf_in_smem && prm_.exact_filter) {
+    if (split > 1 && prm_.tf_in_smem && prm_.exact_filter) {
       // depth-split march (see rc1pass_split_kernel): smaller pixel footprint per warp item, K lanes per ray
       const int K = split;
       const int fw = K == 8 ? 2 : 4, fh = K == 2 ? 4 : 2;
@@ -777,15 +811,17 @@ class Rc1Pass : public RendererImpl {
       a.n_items = my_tiles * (part_tile / fw) * (part_tile / fh);
       const int ctas = std::max(1, (a.n_items + CTA_THREADS / 32 - 1) / (CTA_THREADS / 32));
       int occ = 0;
-#define SPLIT(C, KK)                                                                                                          \
+#define SPLIT_S(C, KK, S)                                                                                                     \
   {                                                                                                                          \
-    if (smem > 48 * 1024) VRB_CUDA(cudaFuncSetAttribute(rc1pass_split_kernel<C, KK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rc1pass_split_kernel<C, KK>, CTA_THREADS, smem));           \
-    rc1pass_split_kernel<C, KK><<<std::min(std::max(occ, 1) * ctx->sm_count, ctas), CTA_THREADS, smem, s>>>(a);             \
+    if (smem > 48 * 1024) VRB_CUDA(cudaFuncSetAttribute(rc1pass_split_kernel<C, KK, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    VRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rc1pass_split_kernel<C, KK, S>, CTA_THREADS, smem));        \
+    rc1pass_split_kernel<C, KK, S><<<std::min(std::max(occ, 1) * ctx->sm_count, ctas), CTA_THREADS, smem, s>>>(a);          \
   }
+#define SPLIT(C, KK) { if (prm_.skip_block) SPLIT_S(C, KK, true) else SPLIT_S(C, KK, false) }
       if (prm_.count_samples) { if (K == 2) SPLIT(true, 2) else if (K == 4) SPLIT(true, 4) else SPLIT(true, 8) }
       else { if (K == 2) SPLIT(false, 2) else if (K == 4) SPLIT(false, 4) else SPLIT(false, 8) }
 #undef SPLIT
+#undef SPLIT_S
       VRB_CUDA(cudaGetLastError());
       return VRB_OK;
     }

@@ -97,8 +97,8 @@ typedef struct {
                                     the length of the longest ray; 2/4/8 = that many lanes march consecutive depth segments of a
                                     ray and the partial results are folded with the over operator (same samples, same
                                     termination sample, sums re-associated): shortens the per-ray dependent chain when a GPU
-                                    owns few pixels (image split over many GPUs).  Ignored with skip_block, tf_in_smem = 0 or
-                                    exact_filter = 0. */
+                                    owns few pixels (image split over many GPUs).  With skip_block the ray leaps over empty cubes of
+                                    blocks in front of every chunk of segments.  Ignored with tf_in_smem = 0 or exact_filter = 0. */
   int   split_groups;            /* depth_split > 1: groups of 4 samples a lane marches per chunk; 0 = default (2) */
 } vrb_rc1pass_params;
 

@@ -148,6 +148,29 @@ def test_empty_space_skipping_preserves_the_lattice(ctx, bonsai_table, block):
         _check_images(got, got8, ref, f"skip{block} step{step}")
 
 
+@pytest.mark.parametrize("K", [2, 4, 8])
+@pytest.mark.parametrize("block", [4, 16])
+def test_depth_split_with_skipping(ctx, bonsai_table, K, block):
+    """K lanes per ray AND empty-space skipping: the leap in front of every chunk of segments removes only transparent samples, so the
+    frame equals the skipping march with one lane per ray up to the re-association of the folds, with fewer fetches than the split
+    march without skipping."""
+    vox = inputs.synth_volume(0, np.uint8, shape=(100, 77, 90))
+    ctx.upload_volume(vox)
+    ctx.upload_tf(bonsai_table)
+    w, h = 192, 160
+    for eye in [(100.0, 100.0, 200.0), (-30.0, 260.0, 20.0), (10.0, 5.0, -8.0)]:
+        cam = inputs.make_camera(eye, width=w, height=h)
+        one, one8, _, n_one, _ = _render_gpu(ctx, cam, w, h, count_samples=1, step_size=0.5, skip_block=block)
+        got, got8, _, n_got, _ = _render_gpu(ctx, cam, w, h, count_samples=1, step_size=0.5, skip_block=block, depth_split=K)
+        plain, _, _, n_plain, _ = _render_gpu(ctx, cam, w, h, count_samples=1, step_size=0.5, depth_split=K)
+        d = float(np.abs(got - one).max()) * 255.0
+        assert d <= 0.5, (eye, d)
+        assert np.array_equal(got[..., 3] > 0, one[..., 3] > 0)
+        assert n_got <= n_plain and (n_got < n_plain or eye[2] < 0)
+        ref, _, _ = O.rc1pass_render(O.rc1pass_params(cam, w, h, vox.shape, 0.5), O.volume_r16f(vox), O.tf_texture(bonsai_table))
+        _check_images(got, got8, ref, f"split{K} skip{block}")
+
+
 def test_skip_map_follows_tf_and_volume_changes(ctx, bonsai_table):
     vox = inputs.synth_volume(64, np.uint8)
     ctx.upload_volume(vox)
