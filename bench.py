@@ -322,8 +322,12 @@ def run_cuda(args):
     # fewer fetches — reported beside the headline, which keeps every lattice sample
     skip_info = {}
     if not args.skip:
+        # lanes per ray for the skipping march: its rays are short, so the split pays later than for the full march
+        # (profiles/r2t_ vs r2u_bench_n{2,4,8}.json: K = 1 is best at 2 GPUs, 2 at 4, 4 at 8)
+        skip_split = args.depth_split if args.depth_split >= 0 else (0 if world <= 2 else (2 if world <= 4 else 4))
         for blk in (4, 8, 16, 32):
             prm.skip_block = blk
+            prm.depth_split = skip_split
             r.set_params(prm)
             for _ in range(3):
                 step()
@@ -339,6 +343,7 @@ def run_cuda(args):
                 dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             skip_info[f"block{blk}"] = {"ms_per_step": float(tt.item()) / args.steps, "fps": 1e3 * args.steps / float(tt.item())}
         prm.skip_block = 0
+        prm.depth_split = depth_split
         r.set_params(prm)
 
     # e2e through the C ABI with host buffers: camera/light structs in, RGBA16F frame out to pinned memory
@@ -422,7 +427,7 @@ def run_cuda(args):
             "setup": {"partition": f"image tiles {PART_TILE}x{PART_TILE} round-robin over {world} rank(s)" + ((", fused peer-memory gather into every rank's frame" if args.gather == "all" else ", fused peer-memory gather into rank 0's frame (credit back-pressure)") + " + per-frame flag wait (no collective)" if world > 1 else ""),
                       "e2e_path": ("update + redraw + vrb_renderer_read_frame_async into pinned host memory every step; the transfer of frame k overlaps the render of frame k + 1" if world == 1 else
                                    "update + redraw + vrb_renderer_read_tiles_async every step: no gather, every rank stores its own tiles into one shared pinned host frame over its own PCIe link, rank 0 polls the per-rank arrival words; the stores of frame k overlap the render of frame k + 1"),
-                      "init_ms_volume_upload": init_ms, "tf_in_smem": args.tf_smem, "exact_filter": args.exact, "skip_block": args.skip, "depth_split": depth_split},
+                      "init_ms_volume_upload": init_ms, "tf_in_smem": args.tf_smem, "exact_filter": args.exact, "skip_block": args.skip, "depth_split": depth_split, "depth_split_with_skipping": None if args.skip else skip_split},
             "measured": {"samples_per_frame": fetched_total, "fps": 1e3 / ms_per_step,
                          "ms_per_step_min_median_max": [float(min(per_step)), float(np.median(per_step)), float(max(per_step))],
                          "with_skipping": skip_info},
