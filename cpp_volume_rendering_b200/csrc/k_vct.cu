@@ -33,26 +33,34 @@ __global__ void __launch_bounds__(256) vct_reduce_kernel(const T* __restrict__ r
                                                          int vw, int vh, int lw, int lh, int ld, double* __restrict__ out_mean,
                                                          __half2* __restrict__ lin, unsigned long long* __restrict__ max_std_bits) {
   const int iw = blockIdx.x * blockDim.x + threadIdx.x, ih = blockIdx.y, id = blockIdx.z;
-  if (iw >= lw) return;
-  const int x = iw * 2, y = ih * 2, z = id * 2;
-  double v[8];
+  const bool valid = iw < lw;
+  double sd = 0.0;
+  if (valid) {
+    const int x = iw * 2, y = ih * 2, z = id * 2;
+    double v[8];
 #pragma unroll
-  for (int k = 0; k < 8; k++) {   // order vm0..vm7: (x,y,z) (x,y,z+1) (x,y+1,z) (x,y+1,z+1) (x+1,y,z) ... (:76-83)
-    const size_t i = (size_t)(x + (k >> 2)) + ((size_t)(y + ((k >> 1) & 1)) * vw) + ((size_t)(z + (k & 1)) * vw * vh);
-    v[k] = raw ? mean0(raw, i, maxv) : child[i];
+    for (int k = 0; k < 8; k++) {   // order vm0..vm7: (x,y,z) (x,y,z+1) (x,y+1,z) (x,y+1,z+1) (x+1,y,z) ... (:76-83)
+      const size_t i = (size_t)(x + (k >> 2)) + ((size_t)(y + ((k >> 1) & 1)) * vw) + ((size_t)(z + (k & 1)) * vw * vh);
+      v[k] = raw ? mean0(raw, i, maxv) : child[i];
+    }
+    double sum = v[0];
+#pragma unroll
+    for (int k = 1; k < 8; k++) sum = __dadd_rn(sum, v[k]);
+    const double vmn = __ddiv_rn(sum, 8.0);
+    double acc = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) { const double dlt = __dsub_rn(v[k], vmn); const double sq = __dmul_rn(dlt, dlt); acc = k == 0 ? sq : __dadd_rn(acc, sq); }
+    sd = __dsqrt_rn(__ddiv_rn(acc, 8.0));
+    const size_t o = (size_t)iw + ((size_t)ih * lw) + ((size_t)id * lw * lh);
+    out_mean[o] = vmn;
+    lin[o] = __floats2half2_rn((float)vmn, (float)sd);
   }
-  double sum = v[0];
+  // maximum standard deviation: sd >= 0, so the bit pattern orders like the value.  One atomic per warp, and none for the warps of
+  // empty space (every thread an atomic on the one word serialised 19 M of them at 512^3: 13 of the 15 ms of the build)
+  unsigned long long m = (unsigned long long)__double_as_longlong(sd);
 #pragma unroll
-  for (int k = 1; k < 8; k++) sum = __dadd_rn(sum, v[k]);
-  const double vmn = __ddiv_rn(sum, 8.0);
-  double acc = 0.0;
-#pragma unroll
-  for (int k = 0; k < 8; k++) { const double dlt = __dsub_rn(v[k], vmn); const double sq = __dmul_rn(dlt, dlt); acc = k == 0 ? sq : __dadd_rn(acc, sq); }
-  const double sd = __dsqrt_rn(__ddiv_rn(acc, 8.0));
-  const size_t o = (size_t)iw + ((size_t)ih * lw) + ((size_t)id * lw * lh);
-  out_mean[o] = vmn;
-  lin[o] = __floats2half2_rn((float)vmn, (float)sd);
-  atomicMax(max_std_bits, (unsigned long long)__double_as_longlong(sd));     // sd >= 0: the bit pattern orders like the value
+  for (int o = 16; o > 0; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xffffffffu, m, o); m = t > m ? t : m; }
+  if ((threadIdx.x & 31) == 0 && m != 0ull) atomicMax(max_std_bits, m);
 }
 
 __global__ void __launch_bounds__(256) vct_quad_kernel(const unsigned* __restrict__ lin, cudaSurfaceObject_t dst, int w, int h, int d) {
