@@ -19,41 +19,46 @@
 namespace vrb {
 
 // ---- K5 ------------------------------------------------------------------------------------------------
-// One CTA per block.  min/max of v/maxDataValue in double == (min v)/maxDataValue because the division is monotone,
-// so the reduction runs on the raw voxels and one double division per block reproduces the reference bit for bit.
+// The reduction runs on the raw voxels (min / max are exact whatever the order), one double division per block at the end.
+// Two launches: (block, chunk of its z range) CTAs fold their part into per-block words with integer atomics on an order-preserving
+// encoding of the raw value (4^3 blocks of a 512^3 volume are 64 blocks of 2 M voxels: one CTA per block left 84 SMs idle, 6 ms), then
+// one thread per block converts.  Blocks without a voxel keep the encodings' initial values.
+template <typename T> __device__ __forceinline__ unsigned mm_encode(T v) { return (unsigned)v; }
+template <> __device__ __forceinline__ unsigned mm_encode<float>(float v) { const unsigned b = __float_as_uint(v); return (b & 0x80000000u) ? ~b : (b | 0x80000000u); }
+template <typename T> __device__ __forceinline__ double mm_decode(unsigned e) { return (double)(T)e; }
+template <> __device__ __forceinline__ double mm_decode<float>(unsigned e) { return (double)__uint_as_float((e & 0x80000000u) ? (e & 0x7fffffffu) : ~e); }
+
 template <typename T>
 __global__ void __launch_bounds__(256) block_minmax_kernel(const T* __restrict__ raw, int w, int h, int d, int bsx, int bsy,
-                                                           int bsz, int nbx, int nby, double maxv, float* __restrict__ out_min,
-                                                           float* __restrict__ out_max) {
-  const int b = blockIdx.x;
+                                                           int bsz, int nbx, int nby, int chunks, unsigned* __restrict__ enc_min,
+                                                           unsigned* __restrict__ enc_max) {
+  const int b = blockIdx.x / chunks, c = blockIdx.x % chunks;
   const int bx = b % nbx, by = (b / nbx) % nby, bz = b / (nbx * nby);
   const int sx = bx * bsx, sy = by * bsy, sz = bz * bsz;
   const int ex = min(sx + bsx, w), ey = min(sy + bsy, h), ez = min(sz + bsz, d);
   const int nx = max(ex - sx, 0), ny = max(ey - sy, 0), nz = max(ez - sz, 0);
-  const long long total = (long long)nx * ny * nz;
-  double mn = (double)FLT_MAX, mx = -(double)FLT_MAX;      // numeric_limits<float>::max() / lowest() (:56-57)
+  const int z_per = (nz + chunks - 1) / chunks, z0 = c * z_per, z1 = min(nz, z0 + z_per);
+  const long long plane = (long long)nx * ny, total = plane * max(z1 - z0, 0);
+  unsigned mn = 0xffffffffu, mx = 0u;
   for (long long i = threadIdx.x; i < total; i += blockDim.x) {
-    const int x = sx + (int)(i % nx), y = sy + (int)((i / nx) % ny), z = sz + (int)(i / ((long long)nx * ny));
-    const double v = (double)raw[(size_t)z * ((size_t)w * h) + (size_t)y * w + x];
-    mn = fmin(mn, v); mx = fmax(mx, v);
+    const int x = sx + (int)(i % nx), y = sy + (int)((i / nx) % ny), z = sz + z0 + (int)(i / plane);
+    const unsigned e = mm_encode<T>(raw[(size_t)z * ((size_t)w * h) + (size_t)y * w + x]);
+    mn = min(mn, e); mx = max(mx, e);
   }
-  // raw values are compared un-normalised; the sentinels must stay above/below every raw value
-  __shared__ double s_mn[256], s_mx[256];
-  __shared__ int s_any[256];
-  s_mn[threadIdx.x] = mn; s_mx[threadIdx.x] = mx; s_any[threadIdx.x] = threadIdx.x < total ? 1 : 0;
-  __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) {
-    if (threadIdx.x < o) {
-      s_mn[threadIdx.x] = fmin(s_mn[threadIdx.x], s_mn[threadIdx.x + o]);
-      s_mx[threadIdx.x] = fmax(s_mx[threadIdx.x], s_mx[threadIdx.x + o]);
-      s_any[threadIdx.x] |= s_any[threadIdx.x + o];
-    }
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) {
-    if (s_any[0]) { out_min[b] = (float)(s_mn[0] / maxv); out_max[b] = (float)(s_mx[0] / maxv); }
-    else { out_min[b] = FLT_MAX; out_max[b] = -FLT_MAX; }   // block entirely outside the volume: never touched (:104-105)
-  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o)); mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o)); }
+  if ((threadIdx.x & 31) == 0 && mx >= mn) { atomicMin(enc_min + b, mn); atomicMax(enc_max + b, mx); }
+}
+// min/max of v/maxDataValue in double == (min v)/maxDataValue because the division is monotone: one double division per block
+// reproduces the reference bit for bit.
+template <typename T>
+__global__ void block_minmax_finish_kernel(const unsigned* __restrict__ enc_min, const unsigned* __restrict__ enc_max, int nb, double maxv,
+                                           float* __restrict__ out_min, float* __restrict__ out_max) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nb) return;
+  const unsigned mn = enc_min[b], mx = enc_max[b];
+  if (mx >= mn) { out_min[b] = (float)(mm_decode<T>(mn) / maxv); out_max[b] = (float)(mm_decode<T>(mx) / maxv); }
+  else { out_min[b] = FLT_MAX; out_max[b] = -FLT_MAX; }   // block entirely outside the volume: never touched (:104-105)
 }
 
 struct BlockGrid {
@@ -74,13 +79,29 @@ struct BlockGrid {
     const int bsy = (int)(((float)(unsigned)v.h + (float)by - 1.0f) / (float)by);
     const int bsz = (int)(((float)(unsigned)v.d + (float)bz - 1.0f) / (float)bz);
     cudaStream_t s = ctx->stream;
-    if (v.dtype == VRB_U8)
-      block_minmax_kernel<uint8_t><<<(unsigned)nb, 256, 0, s>>>((const uint8_t*)v.raw, (int)v.w, (int)v.h, (int)v.d, bsx, bsy, bsz, bx, by, 255.0, mn, mx);
-    else if (v.dtype == VRB_U16)
-      block_minmax_kernel<uint16_t><<<(unsigned)nb, 256, 0, s>>>((const uint16_t*)v.raw, (int)v.w, (int)v.h, (int)v.d, bsx, bsy, bsz, bx, by, 65535.0, mn, mx);
-    else
-      block_minmax_kernel<float><<<(unsigned)nb, 256, 0, s>>>((const float*)v.raw, (int)v.w, (int)v.h, (int)v.d, bsx, bsy, bsz, bx, by, 1.0, mn, mx);
-    VRB_CUDA(cudaGetLastError());
+    // enough CTAs to fill the machine whatever the block count
+    const int chunks = (int)std::min<size_t>((size_t)std::max(bsz, 1), std::max<size_t>(1, (size_t)(8 * ctx->sm_count) / nb));
+    unsigned* enc = nullptr;
+    VRB_CUDA(cudaMalloc(&enc, 2 * nb * sizeof(unsigned)));
+    cudaError_t e = cudaMemsetAsync(enc, 0xff, nb * sizeof(unsigned), s);
+    if (e == cudaSuccess) e = cudaMemsetAsync(enc + nb, 0, nb * sizeof(unsigned), s);
+    const unsigned grid = (unsigned)(nb * chunks), fin = (unsigned)((nb + 255) / 256);
+    if (e == cudaSuccess) {
+      if (v.dtype == VRB_U8) {
+        block_minmax_kernel<uint8_t><<<grid, 256, 0, s>>>((const uint8_t*)v.raw, (int)v.w, (int)v.h, (int)v.d, bsx, bsy, bsz, bx, by, chunks, enc, enc + nb);
+        block_minmax_finish_kernel<uint8_t><<<fin, 256, 0, s>>>(enc, enc + nb, (int)nb, 255.0, mn, mx);
+      } else if (v.dtype == VRB_U16) {
+        block_minmax_kernel<uint16_t><<<grid, 256, 0, s>>>((const uint16_t*)v.raw, (int)v.w, (int)v.h, (int)v.d, bsx, bsy, bsz, bx, by, chunks, enc, enc + nb);
+        block_minmax_finish_kernel<uint16_t><<<fin, 256, 0, s>>>(enc, enc + nb, (int)nb, 65535.0, mn, mx);
+      } else {
+        block_minmax_kernel<float><<<grid, 256, 0, s>>>((const float*)v.raw, (int)v.w, (int)v.h, (int)v.d, bsx, bsy, bsz, bx, by, chunks, enc, enc + nb);
+        block_minmax_finish_kernel<float><<<fin, 256, 0, s>>>(enc, enc + nb, (int)nb, 1.0, mn, mx);
+      }
+      e = cudaGetLastError();
+      if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    }
+    cudaFree(enc);
+    VRB_CUDA(e);
     nbx = bx; nby = by; nbz = bz; vol_gen = v.generation;
     return VRB_OK;
   }
