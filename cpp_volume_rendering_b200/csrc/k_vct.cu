@@ -71,6 +71,17 @@ __global__ void __launch_bounds__(256) vct_quad_kernel(const unsigned* __restric
   surf3Dwrite(make_uint4(lin[b + (size_t)w * y + x], lin[b + (size_t)w * y + x1], lin[b + (size_t)w * y1 + x], lin[b + (size_t)w * y1 + x1]), dst, x * 16, y, z);
 }
 
+// Level 0 holds (voxel, 0): its footprint texel carries the four means only (8 bytes instead of 16: a quarter of the pyramid's memory)
+__global__ void __launch_bounds__(256) vct_quad0_kernel(const unsigned* __restrict__ lin, cudaSurfaceObject_t dst, int w, int h, int d) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
+  if (x >= w) return;
+  const int x1 = min(x + 1, w - 1), y1 = min(y + 1, h - 1);
+  const size_t b = (size_t)w * h * z;
+  const unsigned m00 = lin[b + (size_t)w * y + x] & 0xffffu, m10 = lin[b + (size_t)w * y + x1] & 0xffffu;
+  const unsigned m01 = lin[b + (size_t)w * y1 + x] & 0xffffu, m11 = lin[b + (size_t)w * y1 + x1] & 0xffffu;
+  surf3Dwrite(make_uint2(m00 | (m10 << 16), m01 | (m11 << 16)), dst, x * 8, y, z);
+}
+
 // ---- K16 -------------------------------------------------------------------------------------------------
 __device__ inline float tf_get_opc(const double* table, int max_density, int extinction_type, double value, double max_in) {
   if (max_in >= 0) value = value * ((double)max_density / max_in);           // TransferFunction1D::Get (:132-157)
@@ -191,18 +202,20 @@ static int build_levels(vrb_ctx* ctx, VctPyramid& p, const T* raw, double maxv) 
 // footprint textures of levels [l0, l1) from their linear RG16F copies
 int VctPyramid::build_quads(vrb_ctx* ctx, int l0, int l1) {
   cudaStream_t s = ctx->stream;
-  cudaChannelFormatDesc desc = cudaCreateChannelDesc<uint4>();
+  cudaChannelFormatDesc desc4 = cudaCreateChannelDesc<uint4>(), desc2 = cudaCreateChannelDesc<uint2>();
   cudaTextureDesc td{};
   td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
   td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
   for (int l = l0; l < l1; l++) {
+    const cudaChannelFormatDesc& desc = l == 0 ? desc2 : desc4;
     VRB_CUDA(cudaMalloc3DArray(&arr[l], &desc, make_cudaExtent((size_t)lw[l], (size_t)lh[l], (size_t)ld[l]), cudaArraySurfaceLoadStore));
     cudaResourceDesc rd{}; rd.resType = cudaResourceTypeArray; rd.res.array.array = arr[l];
     cudaSurfaceObject_t dst = 0;
     VRB_CUDA(cudaCreateSurfaceObject(&dst, &rd));
     cudaError_t e = cudaCreateTextureObject(&tex[l], &rd, &td, nullptr);
     if (e == cudaSuccess) {
-      vct_quad_kernel<<<dim3((lw[l] + 255) / 256, lh[l], ld[l]), 256, 0, s>>>((const unsigned*)lin[l], dst, lw[l], lh[l], ld[l]);
+      if (l == 0) vct_quad0_kernel<<<dim3((lw[l] + 255) / 256, lh[l], ld[l]), 256, 0, s>>>((const unsigned*)lin[l], dst, lw[l], lh[l], ld[l]);
+      else vct_quad_kernel<<<dim3((lw[l] + 255) / 256, lh[l], ld[l]), 256, 0, s>>>((const unsigned*)lin[l], dst, lw[l], lh[l], ld[l]);
       e = cudaGetLastError();
       if (e == cudaSuccess) e = cudaStreamSynchronize(s);
     }
@@ -543,11 +556,17 @@ struct VctShaderT {
     float fx = floorf(X), fy = floorf(Y), fz = floorf(Z);
     const float ax = fx < 0.0f ? 0.0f : __fsub_rn(X, fx), ay = fy < 0.0f ? 0.0f : __fsub_rn(Y, fy), az = __fsub_rn(Z, fz);
     fx = fminf(fmaxf(fx, -1.0f), res.x) - s.mip_off[l][0]; fy = fminf(fmaxf(fy, -1.0f), res.y) - s.mip_off[l][1]; fz = fminf(fmaxf(fz, -1.0f), res.z) - s.mip_off[l][2];
+    auto L = [](float a, float b, float w) { return __fadd_rn(a, __fmul_rn(w, __fsub_rn(b, a))); };
+    if (l == 0) {      // (voxel, 0) texels: the means alone; the lerps of the zero stddevs are zero
+      const uint2 m0 = tex3D<uint2>(s.mip[0], fx + 0.5f, fy + 0.5f, fz + 0.5f), m1 = tex3D<uint2>(s.mip[0], fx + 0.5f, fy + 0.5f, fz + 1.5f);
+      const float2 a0 = __half22float2(*reinterpret_cast<const __half2*>(&m0.x)), b0 = __half22float2(*reinterpret_cast<const __half2*>(&m0.y));
+      const float2 a1 = __half22float2(*reinterpret_cast<const __half2*>(&m1.x)), b1 = __half22float2(*reinterpret_cast<const __half2*>(&m1.y));
+      return make_float2(L(L(L(a0.x, a0.y, ax), L(b0.x, b0.y, ax), ay), L(L(a1.x, a1.y, ax), L(b1.x, b1.y, ax), ay), az), 0.0f);
+    }
     const uint4 q0 = tex3D<uint4>(s.mip[l], fx + 0.5f, fy + 0.5f, fz + 0.5f);
     const uint4 q1 = tex3D<uint4>(s.mip[l], fx + 0.5f, fy + 0.5f, fz + 1.5f);
     auto H = [](unsigned u) { return __half22float2(*reinterpret_cast<const __half2*>(&u)); };
     const float2 t000 = H(q0.x), t100 = H(q0.y), t010 = H(q0.z), t110 = H(q0.w), t001 = H(q1.x), t101 = H(q1.y), t011 = H(q1.z), t111 = H(q1.w);
-    auto L = [](float a, float b, float w) { return __fadd_rn(a, __fmul_rn(w, __fsub_rn(b, a))); };
     float2 r;
     r.x = L(L(L(t000.x, t100.x, ax), L(t010.x, t110.x, ax), ay), L(L(t001.x, t101.x, ax), L(t011.x, t111.x, ax), ay), az);
     r.y = L(L(L(t000.y, t100.y, ax), L(t010.y, t110.y, ax), ay), L(L(t001.y, t101.y, ax), L(t011.y, t111.y, ax), ay), az);
