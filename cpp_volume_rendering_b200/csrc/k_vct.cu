@@ -641,7 +641,9 @@ struct VctShaderT {
         nsteps++;
         const float2 g = texture_lod(s, div3(wpos, c.sizes), s_vct_cone[1][is]);
         float opacity = lut_fetch(s, __fdiv_rn(__fadd_rn(g.x, 0.5f), s.vol_max_density), __fdiv_rn(__fadd_rn(g.y, 0.5f), s.vol_max_std));
-        opacity = 1.0f - powf(1.0f - opacity, s_vct_cone[2][is]);
+        // with hardware-filtered taps the step's opacity correction uses the MUFU form of pow (ex2(y lg2 x)): its relative error (~1e-6)
+        // is far below the filter's; the float32-tap kernel keeps powf
+        opacity = 1.0f - (HWF != 0 ? __powf(1.0f - opacity, s_vct_cone[2][is]) : powf(1.0f - opacity, s_vct_cone[2][is]));
         T *= (1.0f - opacity);
       }
 #pragma unroll
