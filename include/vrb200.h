@@ -175,7 +175,7 @@ typedef struct {
                                               trilinear filter (1.8 fixed-point weights), 1 = float32 weights on every level, 2 (default) =
                                               float32 weights on pyramid level 0 (the voxels themselves, where neighbouring texels differ
                                               most) and the texture unit on the coarser levels.  Measured against the float32 oracle on the
-                                              parity cases: worst 1.56 / 0.13 / 0.62 of the 2/255 bar; 512^3 / 1024^2 frame 5.5 / 12.8 / 6.8 ms.
+                                              parity cases: worst 1.56 / 0.13 / 0.62 of the 2/255 bar; 512^3 / 1024^2 frame 12.8 ms (1) and 6.8 ms (2).
                                               The light-cache pass always uses float32 weights. */
 } vrb_vct_params;
 
