@@ -353,7 +353,10 @@ struct DosArgs {
 template <bool HW>
 struct DosShaderT {
   static constexpr int MIN_CTAS = HW ? VRB_DOS_HW_MINB : 4;   // resident CTAs per SM the kernel is compiled for (register cap 65536 / 128 / MIN_CTAS)
-  static constexpr int ADVANCE = 4, BATCH = 16;   // park-and-shade schedule of the shared march (vrb_march.cuh): measured at C3 (512^3, 1024^2): lockstep (1, 1) 7.1 / 23.0 ms without / with shadows, (4, 16) 5.6 / 15.7 ms, (8, 24) 6.5 / 16.3 ms
+  // park-and-shade schedule of the shared march (vrb_march.cuh), measured at C3 (512^3, 1024^2) without / with shadows.  float32 taps:
+  // lockstep (1, 1) 7.1 / 23.0 ms, (4, 16) 5.6 / 15.7 ms, (8, 24) 6.5 / 16.3 ms.  Hardware taps (a tap is one tex3DLod): waiting for many
+  // lanes costs more than the idle ones — (4, 16) 3.5 / 6.7 ms, (4, 8) 2.6 / 6.7, (4, 4) 2.4 / 6.7, (8, 8) 2.6 / 6.4, (8, 4) 2.4 / 6.3, (4, 1) 2.4 / 6.9
+  static constexpr int ADVANCE = HW ? 8 : 4, BATCH = HW ? 4 : 16;
   static constexpr bool OBJECT_SPACE = false;
   static constexpr int PHONG_KIND = 0;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   using Args = DosArgs;

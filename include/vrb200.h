@@ -227,7 +227,7 @@ typedef struct {
                                               trilinear filter (1.8 fixed-point weights, as the reference's GLSL taps on the same hardware);
                                               1: float32 weights (the filter the GL specification writes down, and the oracle's).  Measured
                                               against the float32 oracle: worst 0.44 / 0.13 of the 2/255 bar at 512^3 / 1024^2 (C3), frame
-                                              3.5 / 5.8 ms (6.7 / 16.6 ms with shadows).  The light-cache pass always uses float32 weights. */
+                                              2.5 / 5.8 ms (6.4 / 16.6 ms with shadows).  The light-cache pass always uses float32 weights. */
 } vrb_dos_params;
 
 /* ---- library / context ------------------------------------------------------------------- */
