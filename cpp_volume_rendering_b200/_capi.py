@@ -155,6 +155,7 @@ SIGNATURES = {
     "vrb_renderer_wait_peers": (C.c_int, [_P]),
     "vrb_renderer_set_peers": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int]),
     "vrb_bench_tex_peak": (C.c_int, [_P, C.POINTER(C.c_double)]),
+    "vrb_bench_tex_lod_peak": (C.c_int, [_P, C.c_float, C.POINTER(C.c_double)]),
     "vrb_sat3d_build_noalloc": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
     "vrb_volume_upload_region": (C.c_int, [_P, _P, C.c_int, C.c_int, _P, _P, _P, C.c_float, C.c_float, C.c_float]),
     "vrb_volume_synth": (C.c_int, [_P, C.c_int, _P, C.c_uint64, _P, _P, C.c_float, C.c_float, C.c_float]),
@@ -289,6 +290,11 @@ class Context:
     def tex_peak(self):
         v = C.c_double()
         _check(lib().vrb_bench_tex_peak(self._h, C.byref(v)))
+        return v.value
+
+    def tex_lod_peak(self, lod):
+        v = C.c_double()
+        _check(lib().vrb_bench_tex_lod_peak(self._h, float(lod), C.byref(v)))
         return v.value
 
 

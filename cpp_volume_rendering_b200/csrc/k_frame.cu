@@ -104,17 +104,21 @@ int frame_store_tiles(cudaStream_t s, const void* staging, void* mapped_frame, u
 // P_tex: trilinear R16F tex3D fetches per second with a working set that stays in L1TEX.  Each warp
 // marches 8x4 neighbouring rays through a 32^3 half volume at a 0.5-texel step — the access pattern
 // of the renderer with every miss removed.  4 independent fetch chains per thread hide latency.
-__global__ void __launch_bounds__(256) tex_peak_kernel(cudaTextureObject_t tex, int iters, float* sink) {
+// LOD: the same fetches through tex3DLod at a fixed level of detail on a mip-mapped array (GL_LINEAR_MIPMAP_LINEAR: two trilinear
+// footprints blended when the level is fractional) — the fetch the cone-tap filters of K7 / K14 issue.
+template <bool LOD>
+__global__ void __launch_bounds__(256) tex_peak_kernel(cudaTextureObject_t tex, int iters, float lod, float* sink) {
   const int lane = threadIdx.x & 31, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const float x0 = ((lane & 7) + 0.5f) / 32.0f + (warp & 3) * 0.2f, y0 = ((lane >> 3) + 0.5f) / 32.0f + ((warp >> 2) & 3) * 0.2f;
   float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
   float z = 0.0f;
   const float dz = 0.5f / 32.0f;
+  auto fetch = [&](float x, float y, float zz) { return LOD ? tex3DLod<float>(tex, x, y, zz, lod) : tex3D<float>(tex, x, y, zz); };
   for (int i = 0; i < iters; i++) {
-    acc0 += tex3D<float>(tex, x0, y0, z);
-    acc1 += tex3D<float>(tex, x0 + 0.011f, y0 + 0.007f, z + dz);
-    acc2 += tex3D<float>(tex, x0 + 0.022f, y0 + 0.014f, z + 2 * dz);
-    acc3 += tex3D<float>(tex, x0 + 0.033f, y0 + 0.021f, z + 3 * dz);
+    acc0 += fetch(x0, y0, z);
+    acc1 += fetch(x0 + 0.011f, y0 + 0.007f, z + dz);
+    acc2 += fetch(x0 + 0.022f, y0 + 0.014f, z + 2 * dz);
+    acc3 += fetch(x0 + 0.033f, y0 + 0.021f, z + 3 * dz);
     z += 4 * dz;
     if (z > 1.0f) z -= 1.0f;
   }
@@ -126,26 +130,41 @@ __global__ void __launch_bounds__(256) tex_peak_kernel(cudaTextureObject_t tex, 
 
 using namespace vrb;
 
-extern "C" int vrb_bench_tex_peak(vrb_ctx* ctx, double* fetches_per_s) {
-  VRB_REQUIRE(ctx && fetches_per_s, VRB_ERR_INVALID, "vrb_bench_tex_peak: null argument");
+static int tex_peak_run(vrb_ctx* ctx, bool mip, float lod, double* fetches_per_s) {
   VRB_CUDA(cudaSetDevice(ctx->device));
-  const int N = 32;
-  std::vector<__half> h((size_t)N * N * N);
-  for (size_t i = 0; i < h.size(); i++) h[i] = __float2half_rn((float)((i * 2654435761u) & 1023) / 1023.0f);
-  cudaArray_t arr = nullptr; cudaTextureObject_t tex = 0; float* sink = nullptr;
+  const int N = 32, LEVELS = 6;
+  cudaArray_t arr = nullptr; cudaMipmappedArray_t mm = nullptr; cudaTextureObject_t tex = 0; float* sink = nullptr;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   cudaChannelFormatDesc desc = cudaCreateChannelDescHalf();
   int rc = VRB_OK;
-  auto body = [&]() -> int {
-    VRB_CUDA(cudaMalloc3DArray(&arr, &desc, make_cudaExtent(N, N, N)));
+  auto upload = [&](cudaArray_t dst, int n, unsigned salt) -> int {
+    std::vector<__half> h((size_t)n * n * n);
+    for (size_t i = 0; i < h.size(); i++) h[i] = __float2half_rn((float)(((i + salt) * 2654435761u) & 1023) / 1023.0f);
     cudaMemcpy3DParms cp{};
-    cp.srcPtr = make_cudaPitchedPtr(h.data(), N * sizeof(__half), N, N);
-    cp.dstArray = arr; cp.extent = make_cudaExtent(N, N, N); cp.kind = cudaMemcpyHostToDevice;
+    cp.srcPtr = make_cudaPitchedPtr(h.data(), n * sizeof(__half), n, n);
+    cp.dstArray = dst; cp.extent = make_cudaExtent(n, n, n); cp.kind = cudaMemcpyHostToDevice;
     VRB_CUDA(cudaMemcpy3D(&cp));
-    cudaResourceDesc rd{}; rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
+    return VRB_OK;
+  };
+  auto body = [&]() -> int {
+    cudaResourceDesc rd{};
+    if (mip) {
+      VRB_CUDA(cudaMallocMipmappedArray(&mm, &desc, make_cudaExtent(N, N, N), LEVELS));
+      for (int l = 0; l < LEVELS; l++) {
+        cudaArray_t lv = nullptr;
+        VRB_CUDA(cudaGetMipmappedArrayLevel(&lv, mm, l));
+        const int r2 = upload(lv, N >> l, (unsigned)l); if (r2 != VRB_OK) return r2;
+      }
+      rd.resType = cudaResourceTypeMipmappedArray; rd.res.mipmap.mipmap = mm;
+    } else {
+      VRB_CUDA(cudaMalloc3DArray(&arr, &desc, make_cudaExtent(N, N, N)));
+      const int r2 = upload(arr, N, 0u); if (r2 != VRB_OK) return r2;
+      rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
+    }
     cudaTextureDesc td{};
     td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
     td.filterMode = cudaFilterModeLinear; td.readMode = cudaReadModeElementType; td.normalizedCoords = 1;
+    if (mip) { td.mipmapFilterMode = cudaFilterModeLinear; td.minMipmapLevelClamp = 0.0f; td.maxMipmapLevelClamp = (float)(LEVELS - 1); }
     VRB_CUDA(cudaCreateTextureObject(&tex, &rd, &td, nullptr));
     VRB_CUDA(cudaMalloc(&sink, sizeof(float)));
     VRB_CUDA(cudaEventCreate(&e0)); VRB_CUDA(cudaEventCreate(&e1));
@@ -153,7 +172,8 @@ extern "C" int vrb_bench_tex_peak(vrb_ctx* ctx, double* fetches_per_s) {
     double best = 0.0;
     for (int rep = 0; rep < 5; rep++) {
       VRB_CUDA(cudaEventRecord(e0, ctx->stream));
-      tex_peak_kernel<<<blocks, threads, 0, ctx->stream>>>(tex, iters, sink);
+      if (mip) tex_peak_kernel<true><<<blocks, threads, 0, ctx->stream>>>(tex, iters, lod, sink);
+      else tex_peak_kernel<false><<<blocks, threads, 0, ctx->stream>>>(tex, iters, 0.0f, sink);
       VRB_CUDA(cudaEventRecord(e1, ctx->stream));
       VRB_CUDA(cudaStreamSynchronize(ctx->stream));
       VRB_CUDA(cudaGetLastError());
@@ -167,8 +187,20 @@ extern "C" int vrb_bench_tex_peak(vrb_ctx* ctx, double* fetches_per_s) {
   rc = body();
   if (tex) cudaDestroyTextureObject(tex);
   if (arr) cudaFreeArray(arr);
+  if (mm) cudaFreeMipmappedArray(mm);
   if (sink) cudaFree(sink);
   if (e0) cudaEventDestroy(e0);
   if (e1) cudaEventDestroy(e1);
   return rc;
+}
+
+extern "C" int vrb_bench_tex_peak(vrb_ctx* ctx, double* fetches_per_s) {
+  VRB_REQUIRE(ctx && fetches_per_s, VRB_ERR_INVALID, "vrb_bench_tex_peak: null argument");
+  return tex_peak_run(ctx, false, 0.0f, fetches_per_s);
+}
+
+extern "C" int vrb_bench_tex_lod_peak(vrb_ctx* ctx, float lod, double* fetches_per_s) {
+  VRB_REQUIRE(ctx && fetches_per_s, VRB_ERR_INVALID, "vrb_bench_tex_lod_peak: null argument");
+  VRB_REQUIRE(lod >= 0.0f && lod <= 5.0f, VRB_ERR_INVALID, "vrb_bench_tex_lod_peak: lod outside [0, 5]");
+  return tex_peak_run(ctx, true, lod, fetches_per_s);
 }

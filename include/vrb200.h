@@ -486,6 +486,10 @@ int vrb_sat3d_build_noalloc(const float* dev_extinction, int w, int h, int d, fl
 /* Cache-resident trilinear R16F tex3D microbenchmark: the texture-fetch roofline denominator P_tex
  * (SURVEY.md §8d).  Returns fetches per second of the whole GPU. */
 int vrb_bench_tex_peak(vrb_ctx* ctx, double* fetches_per_s);
+/* The same fetch pattern through tex3DLod at level of detail `lod` (0..5) of a mip-mapped R16F array with
+ * GL_LINEAR_MIPMAP_LINEAR filtering — the fetch the hardware cone-tap filters of VRB_DOS_CONE / VRB_VCT issue: the
+ * denominator those kernels' roofline fractions are also quoted against (a fractional level blends two trilinear footprints). */
+int vrb_bench_tex_lod_peak(vrb_ctx* ctx, float lod, double* fetches_per_s);
 
 #ifdef __cplusplus
 }

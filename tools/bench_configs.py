@@ -18,6 +18,8 @@ algorithmic work of SURVEY.md 8(d), counted by instrumented launches of the same
   sbtm  slice-based DOS, 512^3 u8, 1024^2     HBM     fragments x 64 B (eye r/w 16 B, occlusion (1 + 2x2) reads + 1 write x 8 B)
 
 Peaks: P_tex = vrb_bench_tex_peak of the same job (cache-resident trilinear R16F fetches per second), HBM = MEASURED_PEAKS.json.
+The DOS lines also carry `frac_of_texture_unit_rates`: the cone taps are tex3DLod fetches at fractional levels, served at half P_tex
+(vrb_bench_tex_lod_peak; `--tex-peaks` prints the sweep over levels).
 """
 import argparse
 import json
@@ -76,7 +78,7 @@ def _hbm_block(kernel, nbytes, ms, hbm_peak, key, units):
             "ncu": _ncu_file(key)}
 
 
-def measure(ctx, which, steps, warmup, tex_peak, hbm_peak):
+def measure(ctx, which, steps, warmup, tex_peak, hbm_peak, lod_peak=None):
     """Returns {config key: result dict}.  ctx: a _capi.Context whose stream is torch's current stream (or synchronised by the caller)."""
     import torch
     from cpp_volume_rendering_b200 import _capi, inputs
@@ -136,6 +138,12 @@ def measure(ctx, which, steps, warmup, tex_peak, hbm_peak):
                     "cone_filter": "texture unit (default)", "ms_per_frame_exact_cone_filter": med_exact,
                     "roofline": _tex_block("shaded_march_kernel<DosShader>", fetches, med, tex_peak, key,
                                            "march samples + shaded samples x (sections x rays) trilinear pyramid fetches")}
+        if lod_peak is None:
+            lod_peak = ctx.tex_lod_peak(1.5)
+        # the cone taps are tex3DLod fetches at a fractional level: two trilinear footprints each, which the texture unit serves at half the
+        # rate of the plain fetch P_tex is measured with (vrb_bench_tex_lod_peak, same job) — the frame at the unit's own rates:
+        unit_ms = (samples / tex_peak + shaded * per / lod_peak) * 1e3
+        out[key]["roofline"].update({"lod_peak_fetches_per_s": lod_peak, "ms_at_texture_unit_rates": unit_ms, "frac_of_texture_unit_rates": unit_ms / med})
 
     if "vct" in which:
         n, w, h = 512, 1024, 1024
@@ -209,6 +217,7 @@ def main():
     ap.add_argument("--only", default=",".join(ALL))
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--tex-peaks", action="store_true", help="print only the texture-unit peaks: plain tex3D and tex3DLod at a sweep of levels")
     args = ap.parse_args()
     import torch
     from cpp_volume_rendering_b200 import _capi
@@ -218,6 +227,11 @@ def main():
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except OSError:
         peaks = {}
+    if args.tex_peaks:
+        print(json.dumps({"tex_peak_fetches_per_s": ctx.tex_peak(),
+                          "tex_lod_peak_fetches_per_s": {str(l): ctx.tex_lod_peak(l) for l in (0.0, 0.25, 0.5, 1.0, 1.5, 2.5, 3.5)}}), flush=True)
+        ctx.close()
+        return
     res = measure(ctx, set(x for x in args.only.split(",") if x), args.steps, args.warmup, ctx.tex_peak(), float(peaks.get("hbm_gbs", 6650.0)))
     for k, v in res.items():
         print(json.dumps({"config": k, **v}), flush=True)
