@@ -402,8 +402,77 @@ struct DosShaderT {
   static __device__ __forceinline__ f3 axis_dir(const DosCone& cn, int i, f3 k, f3 u, f3 v) {
     return add3(add3(scale3(k, cn.axes[i][2]), scale3(u, cn.axes[i][1])), scale3(v, cn.axes[i][0]));
   }
+  // ---- the hardware-tap cone: the same taps and sums as cone_trace below, with the per-tap arithmetic cut to what a tap needs -------
+  // The cone tracers are issue-bound, not fetch-bound (per-warp probe, profiles/README.md: a warp alone takes ~450 cycles per tap, 20 warps
+  // per SM take the same; more warps, fewer warps and more fetches in flight all leave the frame time where it is), and the plain tap is
+  // ~36 instructions around one TEX: the position in volume units, its product with 1 / sizes, six comparisons and two convergence
+  // barriers for CONSIDER_BORDERS.  Here a ray of the cone is (normalised origin, normalised direction, exit distance): the texture
+  // coordinate is three FMAs of the track distance, and the border term — which only exists outside the box — is looked at only once the
+  // track has passed the distance at which the ray leaves the box (minus a margin; beyond it the exact comparison of the reference decides).
+  struct HwRay { f3 dn; float t_exit; };
+  static __device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+  static __device__ __forceinline__ HwRay hw_ray(const Const& c, f3 pos, f3 d) {
+    HwRay r; r.dn = mul3(d, c.inv_sizes);
+    float t = 3.0e38f;                         // pos lies in the box: the first face the ray crosses, per axis
+    if (d.x != 0.0f) t = fminf(t, __fdividef((d.x > 0.0f ? c.sizes.x : 0.0f) - pos.x, d.x));
+    if (d.y != 0.0f) t = fminf(t, __fdividef((d.y > 0.0f ? c.sizes.y : 0.0f) - pos.y, d.y));
+    if (d.z != 0.0f) t = fminf(t, __fdividef((d.z > 0.0f ? c.sizes.z : 0.0f) - pos.z, d.z));
+    r.t_exit = t - fabsf(t) * 1.0e-4f - 1.0e-3f;
+    return r;
+  }
+  static __device__ __forceinline__ float tap_hw(const Args& s, const Const& c, f3 pos, f3 pos_n, const HwRay& r, float track, float mip) {
+    float rg = tex3DLod<float>(s.mip_hw, fmaf(r.dn.x, track, pos_n.x), fmaf(r.dn.y, track, pos_n.y), fmaf(r.dn.z, track, pos_n.z), mip);
+    if (track > r.t_exit) {                    // at or beyond the box: GetGaussianExtinction's factor (:100-110), exp(-dist / (2 (2^mip)^2))
+      const f3 p = add3(pos, scale3(mul3(r.dn, c.sizes), track));
+      const f3 cl = sub3(min3(max3(p, mk3(0.f, 0.f, 0.f)), c.sizes), p);      // zero on every axis <=> inside: the reference's comparison
+      const float dist = cl.x * cl.x + cl.y * cl.y + cl.z * cl.z;
+      if (dist > 0.0f) rg = rg * ex2_approx(-0.72134752f * dist * ex2_approx(-2.0f * mip));   // two MUFU.EX2 (2 ulp), no IEEE division
+    }
+    return rg;
+  }
+  template <int N>
+  static __device__ __forceinline__ void cone_stage_hw(const Args& s, const Const& c, const DosCone& cn, f3 pos, f3 pos_n, const HwRay* ray, int count,
+                                                       int& id, float& track, float* rays, float* last) {
+    for (int j = 0; j < count; j++, id++) {
+      const float4 si = __ldg(cn.sections + id);
+#pragma unroll
+      for (int i = 0; i < N; i++) {
+        const float amptau = tap_hw(s, c, pos, pos_n, ray[i], track, si.y) * si.w;
+        rays[i] += (last[i] + amptau) * si.z * cn.ui_weight;
+        last[i] = amptau;
+      }
+      track = __fadd_rn(track, si.x);
+    }
+  }
+  static __device__ float cone_trace_hw(const Args& s, const Const& c, const DosCone& cn, f3 pos, f3 k, f3 u, f3 v) {
+    const f3 pos_n = mul3(pos, c.inv_sizes);
+    float track = cn.initial_step;
+    float rays[7], last[7];
+    HwRay ray[7];
+    int id = 0;
+    rays[0] = 0.0f; last[0] = 0.0f; ray[0] = hw_ray(c, pos, k);
+    cone_stage_hw<1>(s, c, cn, pos, pos_n, ray, cn.counts[0], id, track, rays, last);
+    if (!(cn.counts[1] + cn.counts[2] > 0)) return expf(-rays[0]);
+    const float r0 = rays[0], l0 = last[0];
+#pragma unroll
+    for (int i = 0; i < 3; i++) { rays[i] = r0; last[i] = l0; ray[i] = hw_ray(c, pos, axis_dir(cn, i, k, u, v)); }
+    cone_stage_hw<3>(s, c, cn, pos, pos_n, ray, cn.counts[1], id, track, rays, last);
+    if (!(cn.counts[2] > 0)) return (expf(-rays[0]) + expf(-rays[1]) + expf(-rays[2])) / 3.0f;
+    rays[6] = rays[5] = rays[2]; rays[4] = rays[3] = rays[1];
+    const float avg = (rays[2] + rays[1] + rays[0]) / 3.0f;
+    rays[2] = rays[1] = rays[0]; rays[0] = avg;
+    last[6] = last[5] = last[2]; last[4] = last[3] = last[1];
+    const float avgt = (last[2] + last[1] + last[0]) / 3.0f;
+    last[2] = last[1] = last[0]; last[0] = avgt;
+#pragma unroll
+    for (int i = 0; i < 7; i++) ray[i] = hw_ray(c, pos, axis_dir(cn, 3 + i, k, u, v));
+    cone_stage_hw<7>(s, c, cn, pos, pos_n, ray, cn.counts[2], id, track, rays, last);
+    return (expf(-rays[0]) + (expf(-rays[1]) + expf(-rays[2]) + expf(-rays[3]) + expf(-rays[4]) + expf(-rays[5]) + expf(-rays[6])) * cn.adj7) /
+           (1.0f + cn.adj7 * 6.0f);
+  }
   // Cone1Ray* -> Cone3Ray* -> Cone7Ray* (:124-333 occlusion, :345-520 shadow)
   static __device__ float cone_trace(const Args& s, const Const& c, const DosCone& cn, f3 pos, f3 k, f3 u, f3 v) {
+    if constexpr (HW) return cone_trace_hw(s, c, cn, pos, k, u, v);
     float track = cn.initial_step;
     float r0 = 0.0f, l0 = 0.0f;
     int id = 0;

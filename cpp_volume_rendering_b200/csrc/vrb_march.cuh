@@ -52,6 +52,12 @@ struct MarchArgs {
 constexpr int MARCH_THREADS = 128;
 
 #ifdef __CUDACC__
+#ifdef VRB_MARCH_PROFILE
+// per-warp load-balance probe of an instrumented build (never defined in the product build): items served, busy cycles, the longest item and
+// its shading batches; launch_march_t dumps the buffer after every launch to $VRB_MP_DUMP_<launch index>.bin
+static __device__ long long mp_buf[8192 * 8];
+inline int& mp_launch_index() { static int v = 0; return v; }
+#endif
 template <class S, bool COUNT, int SL = 0>
 __global__ void __launch_bounds__(MARCH_THREADS, S::MIN_CTAS) shaded_march_kernel(const __grid_constant__ MarchArgs a, const __grid_constant__ typename S::Args sa) {
   extern __shared__ uint4 s_dyn[];
@@ -72,7 +78,13 @@ __global__ void __launch_bounds__(MARCH_THREADS, S::MIN_CTAS) shaded_march_kerne
   const int per_tile_x = a.tile / 8, per_tile = per_tile_x * (a.tile / 4);
   const float tfn = (float)a.tf_n, tfmax = (float)(a.tf_n - 1);
   unsigned nsamp = 0;
+#ifdef VRB_MARCH_PROFILE
+  const long long mp_w0 = clock64(); long long mp_max = 0, mp_shade = 0, mp_shade_max = 0; int mp_items = 0, mp_bmax = 0, mp_btot = 0;
+#endif
   for (;;) {
+#ifdef VRB_MARCH_PROFILE
+    const long long mp_t0 = clock64(); long long mp_sh = 0; int mp_nb = 0;
+#endif
     int raw = 0;
     if (lane == 0) raw = (int)atomicAdd(a.queue, 1u);
     raw = __shfl_sync(0xffffffffu, raw, 0);
@@ -196,7 +208,14 @@ __global__ void __launch_bounds__(MARCH_THREADS, S::MIN_CTAS) shaded_march_kerne
       if (pm == 0u && am == 0u) break;
       if (SL == 1 || (__popc(pm) < a.batch && am != 0u)) continue;              // keep marching: too few samples to shade yet
       float Iocc = 0.0f, Isdw = 0.0f;
+#ifdef VRB_MARCH_PROFILE
+      mp_nb++;
+      const long long mp_s0 = clock64();
+#endif
       S::shade_warp(a, sa, sc, pending, pend_tx, cdir, Iocc, Isdw);
+#ifdef VRB_MARCH_PROFILE
+      mp_sh += clock64() - mp_s0 + (long long)(Iocc == 123.0f);      // the use of Iocc keeps the read of the clock behind the shading
+#endif
       if (COUNT && a.count_mode == 2 && pending) nsamp++;
       if (pending) {
         float4 src = pend_src;
@@ -218,6 +237,9 @@ __global__ void __launch_bounds__(MARCH_THREADS, S::MIN_CTAS) shaded_march_kerne
         pending = false;
       }
     }
+#ifdef VRB_MARCH_PROFILE
+    { const long long dt = clock64() - mp_t0; mp_items++; mp_btot += mp_nb; mp_shade += mp_sh; if (dt > mp_max) { mp_max = dt; mp_bmax = mp_nb; mp_shade_max = mp_sh; } }
+#endif
     if (!in_image) continue;
     if (SL == 1) {
       for (int q = 0; q < a.n_alpha_out; q++) a.alpha_out[q][((size_t)a.brick_id * a.height + py) * a.width + px] = dst.w;
@@ -237,6 +259,12 @@ __global__ void __launch_bounds__(MARCH_THREADS, S::MIN_CTAS) shaded_march_kerne
     for (int o = 16; o > 0; o >>= 1) nsamp += __shfl_xor_sync(0xffffffffu, nsamp, o);
     if (lane == 0 && nsamp) atomicAdd(a.samples, (unsigned long long)nsamp);
   }
+#ifdef VRB_MARCH_PROFILE
+  if (lane == 0) {
+    long long* o = mp_buf + (size_t)(blockIdx.x * (MARCH_THREADS / 32) + (threadIdx.x >> 5)) * 8;
+    o[0] = mp_items; o[1] = clock64() - mp_w0; o[2] = mp_max; o[3] = mp_bmax; o[4] = mp_btot; o[5] = mp_w0; o[6] = mp_shade; o[7] = mp_shade_max;
+  }
+#endif
   finish_launch(a.queue, a.sig);
 }
 
@@ -299,6 +327,18 @@ int launch_march_t(const RendererImpl& r, const MarchArgs& a_in, const typename 
   const int max_ctas = std::max(1, (a.n_items + MARCH_THREADS / 32 - 1) / (MARCH_THREADS / 32));   // a rank without items still signals its peers
   kern<<<std::min(std::max(per_sm, 1) * r.ctx->sm_count, max_ctas), MARCH_THREADS, smem, r.ctx->stream>>>(a, sa);
   VRB_CUDA(cudaGetLastError());
+#ifdef VRB_MARCH_PROFILE
+  if (const char* dump = getenv("VRB_MP_DUMP")) {
+    const int warps = std::min(std::max(per_sm, 1) * r.ctx->sm_count, max_ctas) * (MARCH_THREADS / 32);
+    const size_t n = (size_t)std::min(warps, 8192) * 8;
+    long long* h = (long long*)malloc(n * sizeof(long long));
+    VRB_CUDA(cudaStreamSynchronize(r.ctx->stream));
+    VRB_CUDA(cudaMemcpyFromSymbol(h, mp_buf, n * sizeof(long long)));
+    char name[512]; snprintf(name, sizeof(name), "%s_%d_%d.bin", dump, mp_launch_index()++, (int)COUNT);
+    if (FILE* f = fopen(name, "wb")) { fwrite(h, sizeof(long long), n, f); fclose(f); }
+    free(h);
+  }
+#endif
   return VRB_OK;
 }
 template <class S>
