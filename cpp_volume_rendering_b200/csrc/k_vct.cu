@@ -509,6 +509,9 @@ namespace vrb {
 // Per-CTA table of the cone's step geometry: xl, mip level and opacity exponent of step i depend only on the renderer parameters
 // (vct_ray_bbox_marching.comp:108-141: apex += step; step *= rate), not on the sample, so each CTA runs the recurrence once.
 constexpr int VCT_CONE_TABLE = 256;
+#ifndef VRB_VCT_NS
+#define VRB_VCT_NS 2                  // samples whose cones a warp walks together (shade_warp)
+#endif
 __shared__ float s_vct_cone[3][VCT_CONE_TABLE];
 
 struct VctArgs {
@@ -532,8 +535,10 @@ struct VctShaderT {
   static constexpr bool OBJECT_SPACE = false;
   static constexpr int PHONG_KIND = 1;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   using Args = VctArgs;
-  struct Const { f3 sizes; };
-  static __device__ __forceinline__ Const prepare(const MarchArgs& a, const Args&) { Const c; c.sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]); return c; }
+  struct Const { f3 sizes, inv_sizes; };
+  static __device__ __forceinline__ Const prepare(const MarchArgs& a, const Args&) {
+    Const c; c.sizes = mk3(a.sizes[0], a.sizes[1], a.sizes[2]); c.inv_sizes = mk3(1.0f / c.sizes.x, 1.0f / c.sizes.y, 1.0f / c.sizes.z); return c;
+  }
   static __device__ __forceinline__ void prepare_block(const MarchArgs&, const Args& s) {
     if (threadIdx.x == 0) {
       float apex = s.cone_initial, step = s.cone_step;
@@ -616,39 +621,96 @@ struct VctShaderT {
     }
     Isdw = Tvd;
   }
+  // textureLod of NS positions at one level of detail (the level depends on the cone step alone): the branch on the level is taken once
+  // and the fetches of the NS positions are issued together inside it.
+  template <int NS>
+  static __device__ __forceinline__ void texture_lod_n(const Args& s, const f3 (&p)[NS], const bool (&in)[NS], float lod, float2 (&g)[NS]) {
+    const int q = s.n_levels - 1;
+#pragma unroll
+    for (int k = 0; k < NS; k++) g[k] = make_float2(0.0f, 0.0f);
+    if (!(lod > 0.0f)) {
+#pragma unroll
+      for (int k = 0; k < NS; k++) if (in[k]) g[k] = sample_level(s, 0, p[k]);
+      return;
+    }
+    if (HWF != 0 && s.mip1 && lod >= 1.0f) {
+#pragma unroll
+      for (int k = 0; k < NS; k++) if (in[k]) g[k] = tex3DLod<float2>(s.mip1, p[k].x, p[k].y, p[k].z, lod - 1.0f);
+      return;
+    }
+    if (lod >= (float)q) {
+#pragma unroll
+      for (int k = 0; k < NS; k++) if (in[k]) g[k] = sample_level(s, q, p[k]);
+      return;
+    }
+    const float fl = floorf(lod); const int d1 = (int)fl; const float f = __fsub_rn(lod, fl);
+    float2 v1[NS], v2[NS];
+#pragma unroll
+    for (int k = 0; k < NS; k++) {
+      v1[k] = v2[k] = make_float2(0.0f, 0.0f);
+      if (in[k]) { v1[k] = sample_level(s, d1, p[k]); v2[k] = sample_level(s, d1 + 1, p[k]); }
+    }
+#pragma unroll
+    for (int k = 0; k < NS; k++)
+      g[k] = make_float2(__fadd_rn(__fmul_rn(__fsub_rn(1.0f, f), v1[k].x), __fmul_rn(f, v2[k].x)), __fadd_rn(__fmul_rn(__fsub_rn(1.0f, f), v1[k].y), __fmul_rn(f, v2[k].y)));
+  }
   // The same, with the cone of one sample spread over the warp: the steps of a cone are independent fetches (only the product of the
   // transmittances chains them), so for every lane that has a sample to shade the 32 lanes take steps lane, lane + 32, ... and
   // multiply their factors together.  A sample costs ceil(n / 32) dependent fetch rounds instead of n, and lanes without a visible
   // sample work instead of idling.  Leaving the volume: the steps lie on a ray, so "this step is outside" equals the shader's break.
+  // VRB_VCT_NS samples are walked together (their fetches of a step are issued back to back): a warp shades its samples one after the
+  // other, the frame ends with its slowest warp (per-warp probe, profiles/README.md), and a sample alone is two dependent round trips
+  // (pyramid, then table) per round.  Every sample's factors are multiplied in the same order as before: same bits.
   static __device__ void shade_warp(const MarchArgs& a, const Args& s, const Const& c, bool need, f3 tx, f3 cd, float& Iocc, float& Isdw) {
     Iocc = 1.0f; Isdw = 0.0f;
     if (!a.apply_shadow) return;
     if (s.cone_samples > VCT_CONE_TABLE) { if (need) shade(a, s, c, tx, cd, Iocc, Isdw); return; }
+    constexpr int NS = VRB_VCT_NS;
+    const float inv_max_density = 1.0f / s.vol_max_density, inv_max_std = 1.0f / s.vol_max_std;
     const int lane = threadIdx.x & 31;
     unsigned nsteps = 0;               // cone steps this lane evaluated (instrumented launches only: count_mode 3)
     unsigned m = __ballot_sync(0xffffffffu, need);
     while (m) {
-      const int src = __ffs(m) - 1;
-      m &= m - 1;
-      const f3 p = mk3(__shfl_sync(0xffffffffu, tx.x, src), __shfl_sync(0xffffffffu, tx.y, src), __shfl_sync(0xffffffffu, tx.z, src));
-      const f3 realpos = sub3(p, scale3(c.sizes, 0.5f));
-      const f3 cone = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), realpos));
-      float T = 1.0f;
+      int src[NS]; bool on[NS]; f3 p[NS], cone[NS]; float T[NS];
+#pragma unroll
+      for (int k = 0; k < NS; k++) {
+        on[k] = m != 0u;
+        src[k] = on[k] ? __ffs(m) - 1 : src[0];
+        m &= m - 1;                    // 0 stays 0
+        p[k] = mk3(__shfl_sync(0xffffffffu, tx.x, src[k]), __shfl_sync(0xffffffffu, tx.y, src[k]), __shfl_sync(0xffffffffu, tx.z, src[k]));
+        const f3 realpos = sub3(p[k], scale3(c.sizes, 0.5f));
+        cone[k] = normalize_rn(sub3(mk3(a.light_pos[0], a.light_pos[1], a.light_pos[2]), realpos));
+        T[k] = 1.0f;
+      }
       for (int is = lane; is < s.cone_samples; is += 32) {
-        const float xl = s_vct_cone[0][is];
-        const f3 wpos = add3(p, scale3(cone, xl));
-        if (wpos.x < 0.0f || wpos.x > c.sizes.x || wpos.y < 0.0f || wpos.y > c.sizes.y || wpos.z < 0.0f || wpos.z > c.sizes.z) continue;
-        nsteps++;
-        const float2 g = texture_lod(s, div3(wpos, c.sizes), s_vct_cone[1][is]);
-        float opacity = lut_fetch(s, __fdiv_rn(__fadd_rn(g.x, 0.5f), s.vol_max_density), __fdiv_rn(__fadd_rn(g.y, 0.5f), s.vol_max_std));
-        // with hardware-filtered taps the step's opacity correction uses the MUFU form of pow (ex2(y lg2 x)): its relative error (~1e-6)
-        // is far below the filter's; the float32-tap kernel keeps powf
-        opacity = 1.0f - (HWF != 0 ? __powf(1.0f - opacity, s_vct_cone[2][is]) : powf(1.0f - opacity, s_vct_cone[2][is]));
-        T *= (1.0f - opacity);
+        const float xl = s_vct_cone[0][is], lod = s_vct_cone[1][is], ex = s_vct_cone[2][is];
+        bool in[NS]; f3 q[NS]; float2 g[NS];
+#pragma unroll
+        for (int k = 0; k < NS; k++) {
+          const f3 wpos = add3(p[k], scale3(cone[k], xl));
+          in[k] = on[k] && !(wpos.x < 0.0f || wpos.x > c.sizes.x || wpos.y < 0.0f || wpos.y > c.sizes.y || wpos.z < 0.0f || wpos.z > c.sizes.z);
+          q[k] = HWF != 0 ? mul3(wpos, c.inv_sizes) : div3(wpos, c.sizes);   // hardware taps: the five IEEE divisions of a step become products
+          if (in[k]) nsteps++;
+        }
+        texture_lod_n<NS>(s, q, in, lod, g);
+#pragma unroll
+        for (int k = 0; k < NS; k++) {
+          // a step outside the volume looks the table up with g = 0 and is dropped: no branch between the NS look-ups
+          float opacity = HWF != 0 ? lut_fetch(s, __fadd_rn(g[k].x, 0.5f) * inv_max_density, __fadd_rn(g[k].y, 0.5f) * inv_max_std)
+                                   : lut_fetch(s, __fdiv_rn(__fadd_rn(g[k].x, 0.5f), s.vol_max_density), __fdiv_rn(__fadd_rn(g[k].y, 0.5f), s.vol_max_std));
+          // with hardware-filtered taps the step's opacity correction uses the MUFU form of pow (ex2(y lg2 x)): its relative error (~1e-6)
+          // is far below the filter's; the float32-tap kernel keeps powf
+          opacity = 1.0f - (HWF != 0 ? __powf(1.0f - opacity, ex) : powf(1.0f - opacity, ex));
+          if (in[k]) T[k] *= (1.0f - opacity);
+        }
       }
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) T *= __shfl_xor_sync(0xffffffffu, T, o);
-      if (lane == src) Isdw = T;
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int k = 0; k < NS; k++) T[k] *= __shfl_xor_sync(0xffffffffu, T[k], o);
+      }
+#pragma unroll
+      for (int k = 0; k < NS; k++) if (on[k] && lane == src[k]) Isdw = T[k];
     }
     if (a.count_mode == 3 && nsteps) atomicAdd(a.samples, (unsigned long long)nsteps);
   }
