@@ -338,7 +338,13 @@ struct DosCone {
 };
 
 #ifndef VRB_DOS_HW_MINB
-#define VRB_DOS_HW_MINB 5
+#define VRB_DOS_HW_MINB 3      // measured with the lean taps at C3 / C3 + shadows: 5 CTAs per SM (96 registers, spills) 2.27 / 5.18 ms, 4: 2.12 / 4.90, 3: 2.12 / 4.83
+#endif
+#ifndef VRB_DOS_HW_ADV
+#define VRB_DOS_HW_ADV 8
+#endif
+#ifndef VRB_DOS_HW_BATCH
+#define VRB_DOS_HW_BATCH 4
 #endif
 struct DosArgs {
   cudaTextureObject_t mip[DOS_MAX_LEVELS]; float mip_res[DOS_MAX_LEVELS][3]; int n_levels;
@@ -356,7 +362,7 @@ struct DosShaderT {
   // park-and-shade schedule of the shared march (vrb_march.cuh), measured at C3 (512^3, 1024^2) without / with shadows.  float32 taps:
   // lockstep (1, 1) 7.1 / 23.0 ms, (4, 16) 5.6 / 15.7 ms, (8, 24) 6.5 / 16.3 ms.  Hardware taps (a tap is one tex3DLod): waiting for many
   // lanes costs more than the idle ones — (4, 16) 3.5 / 6.7 ms, (4, 8) 2.6 / 6.7, (4, 4) 2.4 / 6.7, (8, 8) 2.6 / 6.4, (8, 4) 2.4 / 6.3, (4, 1) 2.4 / 6.9
-  static constexpr int ADVANCE = HW ? 8 : 4, BATCH = HW ? 4 : 16;
+  static constexpr int ADVANCE = HW ? VRB_DOS_HW_ADV : 4, BATCH = HW ? VRB_DOS_HW_BATCH : 16;
   static constexpr bool OBJECT_SPACE = false;
   static constexpr int PHONG_KIND = 0;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)
   using Args = DosArgs;
