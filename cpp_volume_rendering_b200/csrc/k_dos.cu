@@ -361,7 +361,8 @@ struct DosShaderT {
   static constexpr int MIN_CTAS = HW ? VRB_DOS_HW_MINB : 4;   // resident CTAs per SM the kernel is compiled for (register cap 65536 / 128 / MIN_CTAS)
   // park-and-shade schedule of the shared march (vrb_march.cuh), measured at C3 (512^3, 1024^2) without / with shadows.  float32 taps:
   // lockstep (1, 1) 7.1 / 23.0 ms, (4, 16) 5.6 / 15.7 ms, (8, 24) 6.5 / 16.3 ms.  Hardware taps (a tap is one tex3DLod): waiting for many
-  // lanes costs more than the idle ones — (4, 16) 3.5 / 6.7 ms, (4, 8) 2.6 / 6.7, (4, 4) 2.4 / 6.7, (8, 8) 2.6 / 6.4, (8, 4) 2.4 / 6.3, (4, 1) 2.4 / 6.9
+  // lanes costs more than the idle ones — (4, 16) 3.5 / 6.7 ms, (4, 8) 2.6 / 6.7, (4, 4) 2.4 / 6.7, (8, 8) 2.6 / 6.4, (8, 4) 2.4 / 6.3, (4, 1) 2.4 / 6.9;
+  // re-swept with the lean tap (cone_trace_hw): (8, 4) 2.1 / 4.8, (8, 8) 2.5 / 5.4, (4, 8) 2.5 / 5.4, (16, 8) 2.5 / 5.4, (8, 16) 3.2 / 5.7
   static constexpr int ADVANCE = HW ? VRB_DOS_HW_ADV : 4, BATCH = HW ? VRB_DOS_HW_BATCH : 16;
   static constexpr bool OBJECT_SPACE = false;
   static constexpr int PHONG_KIND = 0;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)

@@ -533,7 +533,7 @@ struct VctArgs {
 // everywhere, 2 = float32 on level 0 and the texture unit above: vrb_vct_params::exact_cone_filter 1 / 0 / 2)
 template <int HWF>
 struct VctShaderT {
-  static constexpr int MIN_CTAS = HWF ? VRB_VCT_HW_MINB : 4;   // 94-95 registers with hardware taps: five resident CTAs per SM
+  static constexpr int MIN_CTAS = HWF ? VRB_VCT_HW_MINB : 4;   // 96 registers with hardware taps: five resident CTAs per SM (5.18 ms; four or three: 5.46 ms)
   static constexpr int ADVANCE = 1, BATCH = 1;   // park-and-shade schedule of the shared march (vrb_march.cuh): the cone of ONE sample is spread over the warp, so parking samples gains nothing: lockstep 12.7 ms, (4, 16) 13.0 ms at 512^3 / 1024^2
   static constexpr bool OBJECT_SPACE = false;
   static constexpr int PHONG_KIND = 1;   // formula of the ApplyPhongShading branch (vrb_ray.cuh phong_shade_sample)

@@ -175,7 +175,7 @@ typedef struct {
                                               trilinear filter (1.8 fixed-point weights), 1 = float32 weights on every level, 2 (default) =
                                               float32 weights on pyramid level 0 (the voxels themselves, where neighbouring texels differ
                                               most) and the texture unit on the coarser levels.  Measured against the float32 oracle on the
-                                              parity cases: worst 1.56 / 0.13 / 0.62 of the 2/255 bar; 512^3 / 1024^2 frame 12.8 ms (1) and 6.8 ms (2).
+                                              parity cases: worst 1.56 / 0.13 / 0.62 of the 2/255 bar; 512^3 / 1024^2 frame 12.1 ms (1), 5.1 ms (2) and 4.6 ms (0).
                                               The light-cache pass always uses float32 weights. */
 } vrb_vct_params;
 
@@ -227,7 +227,7 @@ typedef struct {
                                               trilinear filter (1.8 fixed-point weights, as the reference's GLSL taps on the same hardware);
                                               1: float32 weights (the filter the GL specification writes down, and the oracle's).  Measured
                                               against the float32 oracle: worst 0.44 / 0.13 of the 2/255 bar at 512^3 / 1024^2 (C3), frame
-                                              2.5 / 5.8 ms (6.4 / 16.6 ms with shadows).  The light-cache pass always uses float32 weights. */
+                                              2.1 / 5.5 ms (4.7 / 15.6 ms with shadows).  The light-cache pass always uses float32 weights. */
 } vrb_dos_params;
 
 /* ---- library / context ------------------------------------------------------------------- */
