@@ -379,3 +379,15 @@ def test_async_frame_read_equals_blocking_read(ctx, bonsai_table):
             assert not np.array_equal(bufs[0].numpy().view(np.uint8), bufs[1].numpy().view(np.uint8))
     finally:
         r.close()
+
+
+def test_texture_unit_microbenchmarks(ctx):
+    """The roofline denominators (vrb200.h: vrb_bench_tex_peak / vrb_bench_tex_lod_peak): a plain trilinear fetch and a tex3DLod at an
+    integral level run at the same rate, a fractional level blends two footprints and runs at about half of it; bad levels are refused."""
+    plain = ctx.tex_peak()
+    assert plain > 1e11
+    lod0, lod_half, lod1 = ctx.tex_lod_peak(0.0), ctx.tex_lod_peak(0.5), ctx.tex_lod_peak(1.0)
+    assert 0.8 * plain < lod0 < 1.25 * plain and 0.8 * plain < lod1 < 1.25 * plain
+    assert 0.35 * plain < lod_half < 0.7 * plain
+    with pytest.raises(_capi.VrbError):
+        ctx.tex_lod_peak(7.5)
