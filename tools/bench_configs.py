@@ -33,8 +33,8 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 ALL = ("c1", "c3", "c3s", "c4", "vct", "sbtm")
-NCU = {"c1": "r2_ncu_full_c1.csv", "c3": "r2_ncu_full_c3.csv", "c3s": "r2_ncu_full_c3s.csv", "c4": "r2_ncu_full_c4.csv",
-       "vct": "r2_ncu_full_vct.csv", "sbtm": "r2_ncu_full_sbtm.csv"}
+NCU = {"c1": "r2_ncu_full_c1.csv", "c3": "r2fin_ncu_full_c3.csv", "c3s": "r2fin_ncu_full_c3s.csv", "c4": "r2_ncu_full_c4.csv",
+       "vct": "r2fin_ncu_full_vct.csv", "sbtm": "r2_ncu_full_sbtm.csv"}
 
 
 def _frames(r, steps, warmup, flush):
