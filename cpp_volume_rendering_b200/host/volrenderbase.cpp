@@ -338,6 +338,7 @@ bool CudaRC1PVoxelConeTracingSGPU::Update(vis::Camera* camera) {
   p.cone_step_size = cone_step_size; p.cone_step_increase_rate = cone_step_increase_rate; p.cone_initial_step = cone_initial_step;
   p.cone_apex_angle = cone_apex_angle; p.apply_correction_factor = apply_correction_factor ? 1 : 0;
   p.opacity_correction_factor = opacity_correction_factor; p.cone_number_of_samples = cone_number_of_samples;
+  p.exact_cone_filter = exact_cone_filter;
   p.use_light_cache = m_pre_illum_str_vol.IsActive() ? 1 : 0;
   for (int i = 0; i < 3; i++) p.light_cache_resolution[i] = m_pre_illum_str_vol.GetLightCacheResolution()[i];
   if (a->renderer_set_params(m_dev, &p, sizeof(p)) != VRB_OK) return Fail("vrb_renderer_set_params");

@@ -172,6 +172,7 @@ class CudaRC1PVoxelConeTracingSGPU : public BaseVolumeRenderer {
   bool apply_ambient_occlusion, apply_directional_shadows, apply_correction_factor;
   float cone_step_size, cone_step_increase_rate, cone_initial_step, cone_apex_angle, opacity_correction_factor;
   int cone_number_of_samples;
+  int exact_cone_filter = 2;           // new: filter of the cone taps (vrb_vct_params: 0 texture unit, 1 float32 weights, 2 float32 on level 0 only)
   PreIlluminationStructuredVolume m_pre_illum_str_vol;   // SetActive(false), 32^3 in the constructor
 };
 
