@@ -155,6 +155,7 @@ StructuredGridVolume* VolumeReader::ReadVolume(const std::string& path) {
   if (ends_with(path, ".raw")) return readraw(path);
   if (ends_with(path, ".syn")) return readsyn(path);
   if (ends_with(path, ".pvm")) return readpvm(path);
+  if (ends_with(path, ".pvmold")) return readpvmold(path);        // reader.cpp:39-40
   if (ends_with(path, ".nrrd")) return readnrrd(path);
   if (ends_with(path, ".nhrd")) return readnhrd(path);            // the reference's spelling of the extension (reader.cpp:50)
   if (ends_with(path, ".dat")) return readdat(path);
@@ -341,56 +342,99 @@ bool read_all(const std::string& path, std::vector<uint8_t>& bytes) {
 
 }  // namespace
 
-StructuredGridVolume* VolumeReader::readpvm(const std::string& path) {
-  std::vector<uint8_t> file, data;
-  if (!read_all(path, file)) return nullptr;
+namespace {
+// The container both .pvm readers of the reference open (DDSV3::readPVMvolume, pvm.cpp:191-308, and its copy DDSV3Old::readPVMvolume,
+// pvm_old.cpp:167-284): the decoded bytes stay in `data`, `raw` points at the first voxel.
+struct PvmContainer { unsigned w = 0, h = 0, d = 0, comps = 0; float sx = 1.0f, sy = 1.0f, sz = 1.0f; std::vector<uint8_t> data; const uint8_t* raw = nullptr; };
+bool read_pvm_container(const std::string& path, PvmContainer& c) {
+  std::vector<uint8_t> file;
+  std::vector<uint8_t>& data = c.data;
+  if (!read_all(path, file)) return false;
   const char id_d[] = "DDS v3d\n", id_e[] = "DDS v3e\n";
   if (file.size() >= 8 && (std::memcmp(file.data(), id_d, 8) == 0 || std::memcmp(file.data(), id_e, 8) == 0)) {
     const bool v3e = file[6] == 'e';
     std::vector<uint8_t> chunk(file.begin() + 8, file.end());
-    if (!dds_decode(chunk, v3e ? ((size_t)1 << 24) : 0, data)) return nullptr;
+    if (!dds_decode(chunk, v3e ? ((size_t)1 << 24) : 0, data)) return false;
   } else data.swap(file);
-  if (data.size() < 5) return nullptr;
+  if (data.size() < 5) return false;
   data.push_back(0);
   const char* txt = (const char*)data.data();
   const char* end = txt + data.size() - 1;
   int version = 1;
   const char* ptr;
-  unsigned w = 0, h = 0, d = 0, comps = 0;
-  float sx = 1.0f, sy = 1.0f, sz = 1.0f;
+  unsigned &w = c.w, &h = c.h, &d = c.d, &comps = c.comps;
+  float &sx = c.sx, &sy = c.sy, &sz = c.sz;
   auto next_line = [&](const char* q) -> const char* { const char* nl = std::strchr(q, '\n'); return nl ? nl + 1 : nullptr; };
   if (std::strncmp(txt, "PVM\n", 4) != 0) {
     if (std::strncmp(txt, "PVM2\n", 5) == 0) version = 2;
     else if (std::strncmp(txt, "PVM3\n", 5) == 0) version = 3;
-    else return nullptr;
+    else return false;
     ptr = txt + 5;
-    if (std::sscanf(ptr, "%u %u %u\n%g %g %g\n", &w, &h, &d, &sx, &sy, &sz) != 6) return nullptr;
-    if (w < 1 || h < 1 || d < 1 || sx <= 0.0f || sy <= 0.0f || sz <= 0.0f) return nullptr;
+    if (std::sscanf(ptr, "%u %u %u\n%g %g %g\n", &w, &h, &d, &sx, &sy, &sz) != 6) return false;
+    if (w < 1 || h < 1 || d < 1 || sx <= 0.0f || sy <= 0.0f || sz <= 0.0f) return false;
     ptr = next_line(ptr);                                          // past "W H D"; the scale line is skipped below
   } else {
     ptr = txt + 4;
     while (ptr && *ptr == '#') ptr = next_line(ptr);
-    if (!ptr || std::sscanf(ptr, "%u %u %u\n", &w, &h, &d) != 3 || w < 1 || h < 1 || d < 1) return nullptr;
+    if (!ptr || std::sscanf(ptr, "%u %u %u\n", &w, &h, &d) != 3 || w < 1 || h < 1 || d < 1) return false;
   }
-  if (!ptr || !(ptr = next_line(ptr))) return nullptr;
-  if (std::sscanf(ptr, "%u\n", &comps) != 1 || (comps != 1 && comps != 2)) return nullptr;   // reader.cpp:119-146: 8 or 16 bits
-  if (!(ptr = next_line(ptr))) return nullptr;
+  if (!ptr || !(ptr = next_line(ptr))) return false;
+  if (std::sscanf(ptr, "%u\n", &comps) != 1 || (comps != 1 && comps != 2)) return false;    // reader.cpp:119-146: 8 or 16 bits
+  if (!(ptr = next_line(ptr))) return false;
   // three unchecked 32-bit header fields: keep each axis sane so that w*h*d*comps cannot wrap size_t
-  if (w > 65536u || h > 65536u || d > 65536u) return nullptr;
+  if (w > 65536u || h > 65536u || d > 65536u) return false;
   const size_t voxels = (size_t)w * h * d, need = voxels * comps;
-  if ((size_t)(end - ptr) < need) return nullptr;
-  if (version < 3 && (size_t)(end - ptr) != need) return nullptr;  // pvm.cpp:262: the sizes must add up
-  const uint8_t* raw = (const uint8_t*)ptr;
+  if ((size_t)(end - ptr) < need) return false;
+  if (version < 3 && (size_t)(end - ptr) != need) return false;    // pvm.cpp:262: the sizes must add up
+  c.raw = (const uint8_t*)ptr;
+  return true;
+}
+}  // namespace
+
+StructuredGridVolume* VolumeReader::readpvm(const std::string& path) {
+  PvmContainer c;
+  if (!read_pvm_container(path, c)) return nullptr;
+  const size_t voxels = (size_t)c.w * c.h * c.d, need = voxels * c.comps;
   void* out = std::malloc(need);
-  if (comps == 1) std::memcpy(out, raw, need);
+  if (c.comps == 1) std::memcpy(out, c.raw, need);
   else {
     // Pvm::PostProcessData (pvm.cpp:80-108): value = byte[2i + 1] * 256 + byte[2i]
     uint16_t* o = (uint16_t*)out;
-    for (size_t i = 0; i < voxels; i++) o[i] = (uint16_t)(raw[2 * i + 1] * 256u + raw[2 * i]);
+    for (size_t i = 0; i < voxels; i++) o[i] = (uint16_t)(c.raw[2 * i + 1] * 256u + c.raw[2 * i]);
   }
-  auto* vol = new StructuredGridVolume(path, w, h, d);
-  vol->SetScale(sx, sy, sz);
-  vol->SetArrayData(out, comps == 1 ? DataStorageSize::_8_BITS : DataStorageSize::_16_BITS);
+  auto* vol = new StructuredGridVolume(path, c.w, c.h, c.d);
+  vol->SetScale(c.sx, c.sy, c.sz);
+  vol->SetArrayData(out, c.comps == 1 ? DataStorageSize::_8_BITS : DataStorageSize::_16_BITS);
+  return vol;
+}
+
+// .pvmold (reader.cpp:227-281 over libs/file_utils/pvm_old.cpp): the same container, read the way the application once did —
+// 16-bit voxels HIGH byte first (PvmOld::PostProcessData, pvm_old.cpp:131-153), the values stretched from [min, max] of the volume to
+// [0, 2^(8 components) - 1] in float32 (GenerateReescaledMinMaxData(false), :67-96), truncated to integers and stored as normalised
+// floats (reader.cpp:251-259).  A constant volume makes the reference divide 0 by 0 and convert NaN to int; here it is refused.
+StructuredGridVolume* VolumeReader::readpvmold(const std::string& path) {
+  PvmContainer c;
+  if (!read_pvm_container(path, c)) return nullptr;
+  const size_t voxels = (size_t)c.w * c.h * c.d;
+  std::vector<float> prc(voxels);
+  for (size_t i = 0; i < voxels; i++)
+    prc[i] = c.comps == 1 ? (float)c.raw[i] : (float)((int)c.raw[2 * i] * 256 + (int)c.raw[2 * i + 1]);
+  const float max_density_value = c.comps == 1 ? 255.0f : 65535.0f;        // pow(2, components * 8) - 1
+  float mn = max_density_value, mx = 0.0f;
+  for (size_t i = 0; i < voxels; i++) { mn = prc[i] < mn ? prc[i] : mn; mx = mx < prc[i] ? prc[i] : mx; }   // glm::min / glm::max
+  if (!(mx > mn)) return nullptr;
+  const double max_density = c.comps == 1 ? 255.0 : 65535.0;
+  float* out = (float*)std::malloc(voxels * sizeof(float));
+  const volatile float range = mx - mn;                                     // one float32 rounding per step, as the reference's loops
+  for (size_t i = 0; i < voxels; i++) {
+    volatile float v = (prc[i] - mn) / range;
+    v = v * max_density_value;
+    const double aux = (double)v;
+    out[i] = (float)((double)(float)((int)aux) / max_density);
+  }
+  auto* vol = new StructuredGridVolume(path, c.w, c.h, c.d);
+  vol->SetScale(c.sx, c.sy, c.sz);
+  vol->SetArrayData(out, DataStorageSize::_NORMALIZED_F);
   return vol;
 }
 

@@ -138,6 +138,7 @@ class VolumeReader {
   StructuredGridVolume* readraw(const std::string& path);
   StructuredGridVolume* readsyn(const std::string& path);
   StructuredGridVolume* readpvm(const std::string& path);      // PVM / PVM2 / PVM3, plain or DDS v3d / v3e compressed, 8 or 16 bits
+  StructuredGridVolume* readpvmold(const std::string& path);   // the same container through PvmOld: min-max stretched, normalised floats
   StructuredGridVolume* readnrrd(const std::string& path);     // detached header: type, sizes, data file
   StructuredGridVolume* readnhrd(const std::string& path);
   StructuredGridVolume* readdat(const std::string& path);      // ObjectFileName, Resolution, SliceThickness, Format

@@ -143,6 +143,18 @@ def pvm_read(path):
     return out, tuple(sc)
 
 
+def pvmold_read(path):
+    """PvmOld(path) + the conversion of VolumeReader::readpvmold (reader.cpp:227-281): (normalised float32 voxels [d, h, w], scale)."""
+    dims = (C.c_uint * 3)(); comps = C.c_uint(); sc = (C.c_double * 3)()
+    f = lib().ref_pvmold_read
+    f.argtypes = [C.c_char_p, _P, _P, _P, _P, C.c_longlong]; f.restype = C.c_int
+    f(path.encode(), dims, C.byref(comps), sc, None, 0)
+    w, h, d = dims
+    out = np.empty((d, h, w), np.float32)
+    f(path.encode(), dims, C.byref(comps), sc, _ptr(out), out.size)
+    return out, tuple(sc)
+
+
 def compute_blocks(voxels, num_blocks):
     """ComputeBlocksFromVolume (rc1custompisoadaptrenderer.cpp:20-113): (min, max) float32 [nbz, nby, nbx]."""
     v = np.ascontiguousarray(voxels)

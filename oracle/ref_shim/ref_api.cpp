@@ -17,6 +17,7 @@
 #include <structured/rc1pdosct/conegaussiansampler.h>
 #include <math_utils/utils.h>
 #include <file_utils/pvm.h>
+#include <file_utils/pvm_old.h>
 #include <vis_utils/camera.h>
 #include <stdlib.h>                 // ::abs(float) overloads, as MSVC's <cmath> gives the filter headers (`x = abs(x)`)
 #include <math.h>
@@ -244,6 +245,28 @@ int ref_pvm_read(const char* path, unsigned dims[3], unsigned* components, doubl
   const long long need = (long long)dims[0] * dims[1] * dims[2] * (long long)*components;
   if (out && cap_bytes >= need && f.GetData()) memcpy(out, f.GetData(), (size_t)need);
   return f.GetData() ? 0 : -1;
+}
+
+// ---- PvmOld (libs/file_utils/pvm_old.cpp): the reader behind the `.pvmold` extension (VolumeReader::readpvmold, reader.cpp:227-281) ----
+// out: width*height*depth normalised floats.  PvmOld's constructor and GenerateReescaledMinMaxData() are the reference's; the two loops
+// after them are reader.cpp:251-260 word for word (that file itself builds StructuredGridVolume through GL types and is not compiled here).
+int ref_pvmold_read(const char* path, unsigned dims[3], unsigned* components, double scale[3], float* out, long long cap_values) {
+  PvmOld f(path);
+  f.GetDimensions(&dims[0], &dims[1], &dims[2]);
+  *components = (unsigned)f.GetComponents();
+  f.GetScale(&scale[0], &scale[1], &scale[2]);
+  const long long n = (long long)dims[0] * dims[1] * dims[2];
+  if (!out || cap_values < n) return 0;
+  float* vol_data = f.GenerateReescaledMinMaxData();
+  double max_density = 1.0;
+  if (*components == 1) max_density = (256.0 - 1.0);
+  else if (*components == 2) max_density = (65536.0 - 1.0);
+  double* aux_output_data = new double[n];
+  for (long long i = 0; i < n; i++) aux_output_data[i] = (double)vol_data[i];
+  for (long long i = 0; i < n; i++) out[i] = ((float)((int)aux_output_data[i]) / max_density);
+  delete[] vol_data;
+  delete[] aux_output_data;
+  return 0;
 }
 
 }  // extern "C"

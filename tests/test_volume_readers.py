@@ -1,5 +1,5 @@
 """On-disk volume formats of the host mirror's vis::VolumeReader: .pvm (plain and DDS-compressed),
-.nrrd / .nhrd, .dat, next to the .raw / .syn readers of test_host_mirror.py.  CPU only.  The .pvm reader is pinned
+.pvmold, .nrrd / .nhrd, .dat, next to the .raw / .syn readers of test_host_mirror.py.  CPU only.  The .pvm reader is pinned
 against the reference's own Pvm class (libs/file_utils/pvm.cpp compiled into oracle/_ref); the differential data
 streams are produced by the encoder below, written from the stream layout the decoder defines."""
 import os
@@ -116,6 +116,36 @@ def test_dds_compressed_pvm(tmp_path, dtype, shape, skip, strip_kind, version):
     if R.available():
         ref, sc = R.pvm_read(p)
         assert np.array_equal(ref, got) and sc == (0.5, 0.5, 1.5)
+
+
+@pytest.mark.parametrize("dtype,shape", [(np.uint8, (5, 7, 9)), (np.uint16, (4, 10, 12)), (np.uint8, (3, 40, 50))])
+@pytest.mark.parametrize("compressed", [False, True])
+def test_pvmold(tmp_path, dtype, shape, compressed):
+    """`.pvmold` (reader.cpp:227-281 over PvmOld): the .pvm container, 16-bit voxels high byte first, stretched from the volume's
+    [min, max] to the full range in float32, truncated, normalised.  Mirror == the arithmetic restated here == the reference's PvmOld."""
+    vox = _smooth(shape, dtype, 11)
+    body = _pvm_bytes(vox, 3, scale=(0.5, 1.0, 1.5))
+    p = str(tmp_path / "v.pvmold")
+    open(p, "wb").write(dds_encode(body, 2, shape[2], 2, np.random.default_rng(5)) if compressed else body)
+    got = hostapi.read_volume(p)
+    assert got.dtype == np.float32 and got.shape == shape
+    assert hostapi.read_volume_scale(p) == (0.5, 1.0, 1.5)
+    comps = vox.dtype.itemsize
+    v = (vox.astype("<u2").byteswap() if comps == 2 else vox).astype(np.float32)     # the file holds the low byte first; PvmOld reads it as the high one
+    top = np.float32(255.0 if comps == 1 else 65535.0)
+    stretched = ((v - v.min()) / (v.max() - v.min())).astype(np.float32) * top
+    want = (np.trunc(stretched.astype(np.float64)).astype(np.float32).astype(np.float64) / float(top)).astype(np.float32)
+    assert np.array_equal(got, want)
+    if R.available():
+        ref, sc = R.pvmold_read(p)
+        assert np.array_equal(ref, got) and sc == (0.5, 1.0, 1.5)
+
+
+def test_pvmold_constant_volume_is_refused(tmp_path):
+    p = str(tmp_path / "flat.pvmold")
+    open(p, "wb").write(_pvm_bytes(np.full((2, 3, 4), 7, np.uint8), 2))
+    with pytest.raises(RuntimeError):
+        hostapi.read_volume(p)
 
 
 def test_dds_compresses_smooth_data(tmp_path):
