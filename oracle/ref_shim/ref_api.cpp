@@ -248,8 +248,9 @@ int ref_pvm_read(const char* path, unsigned dims[3], unsigned* components, doubl
 }
 
 // ---- PvmOld (libs/file_utils/pvm_old.cpp): the reader behind the `.pvmold` extension (VolumeReader::readpvmold, reader.cpp:227-281) ----
-// out: width*height*depth normalised floats.  PvmOld's constructor and GenerateReescaledMinMaxData() are the reference's; the two loops
-// after them are reader.cpp:251-260 word for word (that file itself builds StructuredGridVolume through GL types and is not compiled here).
+// out: width*height*depth normalised floats.  PvmOld's constructor and GenerateReescaledMinMaxData() are the reference's own code; the
+// conversion that follows them in VolumeReader::readpvmold (reader.cpp:251-260: float -> double -> int -> float / max density) is restated
+// here in one loop, because reader.cpp itself builds its StructuredGridVolume through GL types and is not compiled into this library.
 int ref_pvmold_read(const char* path, unsigned dims[3], unsigned* components, double scale[3], float* out, long long cap_values) {
   PvmOld f(path);
   f.GetDimensions(&dims[0], &dims[1], &dims[2]);
@@ -257,15 +258,13 @@ int ref_pvmold_read(const char* path, unsigned dims[3], unsigned* components, do
   f.GetScale(&scale[0], &scale[1], &scale[2]);
   const long long n = (long long)dims[0] * dims[1] * dims[2];
   if (!out || cap_values < n) return 0;
-  float* vol_data = f.GenerateReescaledMinMaxData();
-  double max_density = 1.0;
-  if (*components == 1) max_density = (256.0 - 1.0);
-  else if (*components == 2) max_density = (65536.0 - 1.0);
-  double* aux_output_data = new double[n];
-  for (long long i = 0; i < n; i++) aux_output_data[i] = (double)vol_data[i];
-  for (long long i = 0; i < n; i++) out[i] = ((float)((int)aux_output_data[i]) / max_density);
-  delete[] vol_data;
-  delete[] aux_output_data;
+  float* stretched = f.GenerateReescaledMinMaxData();
+  const double max_density = *components == 1 ? 255.0 : (*components == 2 ? 65535.0 : 1.0);
+  for (long long i = 0; i < n; i++) {
+    const double wide = (double)stretched[i];
+    out[i] = (float)((double)(float)(int)wide / max_density);
+  }
+  delete[] stretched;
   return 0;
 }
 
